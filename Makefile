@@ -1,0 +1,35 @@
+# Builds libelb200.so (device layer + host engine, sm_100a only) and the bring-up tools.
+# `python -c "import __graft_entry__ as g; g.build()"` drives the same commands.
+NVCC      ?= nvcc
+ARCH      := -gencode arch=compute_100a,code=sm_100a
+NVFLAGS   := -std=c++17 -O3 -lineinfo $(ARCH) -Xcompiler -fPIC,-Wall,-Wno-unused-function
+CSRC      := elemental_b200/csrc
+LIBDIR    := elemental_b200/lib
+CU_SRCS   := $(wildcard $(CSRC)/*.cu)
+CPP_SRCS  := $(wildcard $(CSRC)/*.cpp)
+OBJS      := $(patsubst $(CSRC)/%.cu,build/%.o,$(CU_SRCS)) $(patsubst $(CSRC)/%.cpp,build/%.cpp.o,$(CPP_SRCS))
+HDRS      := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh $(CSRC)/*.hpp include/*.h include/El/*.hpp include/*.hpp)
+NCCL_INC  ?= /usr/include
+NCCL_LIB  ?= $(shell python -c "import nvidia.nccl, os; print(os.path.join(list(nvidia.nccl.__path__)[0], 'lib'))" 2>/dev/null)
+
+all: $(LIBDIR)/libelb200.so tools/gemm_check
+
+build/%.o: $(CSRC)/%.cu $(HDRS)
+	@mkdir -p build
+	$(NVCC) $(NVFLAGS) -I$(NCCL_INC) -c $< -o $@
+
+build/%.cpp.o: $(CSRC)/%.cpp $(HDRS)
+	@mkdir -p build
+	$(NVCC) $(NVFLAGS) -I$(NCCL_INC) -x cu -c $< -o $@
+
+$(LIBDIR)/libelb200.so: $(OBJS)
+	@mkdir -p $(LIBDIR)
+	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -lcudart
+
+tools/gemm_check: tools/gemm_check.cu $(LIBDIR)/libelb200.so include/elb200.h
+	$(NVCC) $(NVFLAGS) -o $@ $< -L$(LIBDIR) -lelb200 -lcublas -Xlinker -rpath,'$$ORIGIN/../$(LIBDIR)'
+
+clean:
+	rm -rf build $(LIBDIR)/libelb200.so tools/gemm_check
+
+.PHONY: all clean

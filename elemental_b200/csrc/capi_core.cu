@@ -1,0 +1,139 @@
+// C-ABI glue for the device layer: status strings, error capture, GEMM argument checks.
+#include <cuda_runtime.h>
+#include <cstdio>
+#include <cstring>
+
+#include "elb200_internal.h"
+
+namespace elb {
+
+thread_local char g_last_error[512] = "";
+
+void set_last_error(const char* what, const char* detail) {
+    std::snprintf(g_last_error, sizeof(g_last_error), "%s: %s", what, detail ? detail : "");
+}
+
+int check_cuda(cudaError_t e, const char* what) {
+    if (e == cudaSuccess) return ELB200_OK;
+    set_last_error(what, cudaGetErrorString(e));
+    return ELB200_ERR_CUDA;
+}
+
+int device_sm_count() {
+    static int cached[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cached[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+            n = 148;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
+
+namespace {
+
+// Dimension / pointer checks shared by both GEMMs (the reference throws LogicError for
+// non-conformal arguments, src/blas_like/level3/Gemm.cpp:199-238).
+int check_gemm_args(int transA, int transB, int64_t m, int64_t n, int64_t k, const void* A,
+                    int64_t lda, const void* B, int64_t ldb, const void* C, int64_t ldc) {
+    if (transA < 0 || transA > 2 || transB < 0 || transB > 2) return ELB200_ERR_ARG;
+    if (m < 0 || n < 0 || k < 0) return ELB200_ERR_ARG;
+    const int64_t a_rows = transA ? k : m, b_rows = transB ? n : k;
+    if (lda < (a_rows > 1 ? a_rows : 1) || ldb < (b_rows > 1 ? b_rows : 1) ||
+        ldc < (m > 1 ? m : 1))
+        return ELB200_ERR_ARG;
+    if (m > 0 && n > 0 && !C) return ELB200_ERR_ARG;
+    if (m > 0 && n > 0 && k > 0 && (!A || !B)) return ELB200_ERR_ARG;
+    if (m > INT32_MAX || n > INT32_MAX || k > INT32_MAX) return ELB200_ERR_ARG;
+    return ELB200_OK;
+}
+
+}  // namespace
+}  // namespace elb
+
+using namespace elb;
+
+extern "C" {
+
+const char* elb200_status_string(int status) {
+    switch (status) {
+        case ELB200_OK: return "ok";
+        case ELB200_ERR_CUDA: return "CUDA error";
+        case ELB200_ERR_ARG: return "invalid argument";
+        case ELB200_ERR_TENSORMAP: return "tensor map encode failed";
+        case ELB200_ERR_NCCL: return "NCCL error";
+        case ELB200_ERR_STATE: return "library not initialised";
+        default: return "unknown status";
+    }
+}
+
+const char* elb200_last_error(void) { return g_last_error; }
+
+const char* elb200_build_info(void) {
+    return "libelb200 sm_100a: gemm_f32 tcgen05 3xTF32 (TMA+TMEM, cta_group 1/2), "
+           "gemm_f64 DMMA m8n8k4 (cp.async x4), blas1 vectorised, lattice pack/unpack, NCCL comm";
+}
+
+int elb200_gemm_f32_ex(int transA, int transB, int64_t m, int64_t n, int64_t k, float alpha,
+                       const float* A, int64_t lda, const float* B, int64_t ldb, float beta,
+                       float* C, int64_t ldc, int cta_group, void* stream) {
+    int st = check_gemm_args(transA, transB, m, n, k, A, lda, B, ldb, C, ldc);
+    if (st != ELB200_OK) return st;
+    if (m == 0 || n == 0) return ELB200_OK;
+    if (k == 0 || alpha == 0.f) return elb200_scale2d_f32(m, n, beta, C, ldc, stream);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    // TMA needs 16-byte aligned bases and row pitches; stage non-conforming operands.
+    const bool a_ok = (reinterpret_cast<uintptr_t>(A) & 15u) == 0 && (lda & 3) == 0;
+    const bool b_ok = (reinterpret_cast<uintptr_t>(B) & 15u) == 0 && (ldb & 3) == 0;
+    const float* Ause = A; const float* Buse = B;
+    int64_t lda_use = lda, ldb_use = ldb;
+    float* tmpA = nullptr; float* tmpB = nullptr;
+    if (!a_ok) {
+        const int64_t rows = transA ? k : m, cols = transA ? m : k;
+        lda_use = (rows + 3) & ~int64_t(3);
+        if (check_cuda(cudaMallocAsync(&tmpA, size_t(lda_use) * cols * 4, s), "cudaMallocAsync"))
+            return ELB200_ERR_CUDA;
+        st = elb200_copy2d_f32(rows, cols, A, 1, lda, tmpA, 1, lda_use, stream);
+        if (st != ELB200_OK) return st;
+        Ause = tmpA;
+    }
+    if (!b_ok) {
+        const int64_t rows = transB ? n : k, cols = transB ? k : n;
+        ldb_use = (rows + 3) & ~int64_t(3);
+        if (check_cuda(cudaMallocAsync(&tmpB, size_t(ldb_use) * cols * 4, s), "cudaMallocAsync"))
+            return ELB200_ERR_CUDA;
+        st = elb200_copy2d_f32(rows, cols, B, 1, ldb, tmpB, 1, ldb_use, stream);
+        if (st != ELB200_OK) return st;
+        Buse = tmpB;
+    }
+    st = gemm_f32_tensor(transA != 0, transB != 0, m, n, k, alpha, Ause, lda_use, Buse, ldb_use,
+                         beta, C, ldc, cta_group, s);
+    if (st == ELB200_ERR_CUDA) set_last_error("gemm_f32 launch", cudaGetErrorString(cudaGetLastError()));
+    if (tmpA) cudaFreeAsync(tmpA, s);
+    if (tmpB) cudaFreeAsync(tmpB, s);
+    return st;
+}
+
+int elb200_gemm_f32(int transA, int transB, int64_t m, int64_t n, int64_t k, float alpha,
+                    const float* A, int64_t lda, const float* B, int64_t ldb, float beta, float* C,
+                    int64_t ldc, void* stream) {
+    return elb200_gemm_f32_ex(transA, transB, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, 0,
+                              stream);
+}
+
+int elb200_gemm_f64(int transA, int transB, int64_t m, int64_t n, int64_t k, double alpha,
+                    const double* A, int64_t lda, const double* B, int64_t ldb, double beta,
+                    double* C, int64_t ldc, void* stream) {
+    int st = check_gemm_args(transA, transB, m, n, k, A, lda, B, ldb, C, ldc);
+    if (st != ELB200_OK) return st;
+    if (m == 0 || n == 0) return ELB200_OK;
+    if (k == 0 || alpha == 0.0) return elb200_scale2d_f64(m, n, beta, C, ldc, stream);
+    st = gemm_f64_dmma(transA != 0, transB != 0, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc,
+                       static_cast<cudaStream_t>(stream));
+    if (st == ELB200_ERR_CUDA) set_last_error("gemm_f64 launch", cudaGetErrorString(cudaGetLastError()));
+    return st;
+}
+
+}  // extern "C"

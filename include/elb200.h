@@ -1,0 +1,166 @@
+/* elb200.h — C ABI of libelb200.so: the B200 (sm_100a) device layer underneath the
+ * Hydrogen/Elemental `El::Gemm` hot path.
+ *
+ * Every entry point below is what the reference binds at the same place in its call stack; the
+ * reference interface each one replaces is cited as file:line relative to the reference tree.
+ * Conventions (same as the reference's gpu_blas layer):
+ *   - column-major matrices, leading dimensions and strides in ELEMENTS (not bytes);
+ *   - alpha/beta by value on the host (reference: CUBLAS_POINTER_MODE_HOST,
+ *     src/hydrogen/device/cuBLAS.cpp:66-68);
+ *   - every call is asynchronous on the caller's stream (`stream` is a cudaStream_t passed as
+ *     void*; the reference passes SyncInfo<Device::GPU>::Stream()); no hidden synchronisation;
+ *   - the return value is an elb200_status; nothing throws across this boundary. The C++ facade
+ *     (include/El.hpp) converts non-zero statuses into the reference's exception types.
+ *   - there is NO CPU fallback: without a CUDA device every compute entry point returns
+ *     ELB200_ERR_CUDA.
+ */
+#ifndef ELB200_H_
+#define ELB200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum elb200_status {
+    ELB200_OK = 0,
+    ELB200_ERR_CUDA = 1,      /* a CUDA runtime call or kernel launch failed            */
+    ELB200_ERR_ARG = 2,       /* non-conformal dimensions / null pointer / bad enum     */
+    ELB200_ERR_TENSORMAP = 3, /* cuTensorMapEncodeTiled rejected the operand            */
+    ELB200_ERR_NCCL = 4,      /* an NCCL call failed                                    */
+    ELB200_ERR_STATE = 5      /* library used before elb200 comm/grid initialisation    */
+} elb200_status;
+
+/* 'N' = 0, 'T' = 1, 'C' = 2 (== 'T' for real types); mirrors El::Orientation
+ * (include/El/core/types.hpp) and hydrogen::TransposeMode. */
+typedef enum elb200_op { ELB200_OP_N = 0, ELB200_OP_T = 1, ELB200_OP_C = 2 } elb200_op;
+
+const char* elb200_status_string(int status);
+/* Text of the last CUDA/NCCL error seen by the calling thread ("" if none). */
+const char* elb200_last_error(void);
+/* Compile-time facts: "sm_100a", kernel list. */
+const char* elb200_build_info(void);
+
+/* ------------------------------------------------------------------------------------------
+ * BLAS-3: local GEMM.  C(m x n) = alpha * op(A) * op(B) + beta * C
+ * Replaces gpu_blas::Gemm -> cublas{S,D}gemm
+ *   (include/hydrogen/blas/GPU_BLAS_impl.hpp:417-444,1036-1051;
+ *    src/hydrogen/device/cuBLAS_API.cpp:282-300), called from Gemm_impl<Device::GPU>
+ *   (src/blas_like/level3/Gemm.cpp:163-186).
+ * f32: tcgen05.mma kind::tf32 with an in-kernel 3xTF32 split (FP32-level accuracy), TMEM
+ *      accumulators, TMA operand loads.  f64: mma.sync m8n8k4 f64 (DMMA) + cp.async pipeline.
+ * k == 0 or alpha == 0 degenerate to C *= beta, like the reference (Gemm.cpp:240-247).
+ * ---------------------------------------------------------------------------------------- */
+int elb200_gemm_f32(int transA, int transB, int64_t m, int64_t n, int64_t k, float alpha,
+                    const float* A, int64_t lda, const float* B, int64_t ldb, float beta, float* C,
+                    int64_t ldc, void* stream);
+int elb200_gemm_f64(int transA, int transB, int64_t m, int64_t n, int64_t k, double alpha,
+                    const double* A, int64_t lda, const double* B, int64_t ldb, double beta,
+                    double* C, int64_t ldc, void* stream);
+/* Tuning/diagnostic variant: cta_group = 1 (one SM per tile) or 2 (CTA pair, cta_group::2). */
+int elb200_gemm_f32_ex(int transA, int transB, int64_t m, int64_t n, int64_t k, float alpha,
+                       const float* A, int64_t lda, const float* B, int64_t ldb, float beta,
+                       float* C, int64_t ldc, int cta_group, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * BLAS-1 entrywise kernels (HBM-bound, 128-bit vectorised where strides allow).
+ * ---------------------------------------------------------------------------------------- */
+/* dst(i,j) = src(i,j) with general 2-D strides.
+ * Replaces hydrogen::Copy_GPU_impl 2-D (include/hydrogen/blas/gpu/Copy.hpp:100-104,
+ * src/hydrogen/blas/gpu/Copy.cu:26-73,156-169) and gpu::Copy2DIntraDevice
+ * (include/hydrogen/device/gpu/cuda/CUDACopy.hpp:70-82) as used by copy::util::InterleaveMatrix
+ * (include/El/blas_like/level1/Copy/util.hpp:245-265). */
+int elb200_copy2d_f32(int64_t rows, int64_t cols, const float* src, int64_t src_row_stride,
+                      int64_t src_col_stride, float* dst, int64_t dst_row_stride,
+                      int64_t dst_col_stride, void* stream);
+int elb200_copy2d_f64(int64_t rows, int64_t cols, const double* src, int64_t src_row_stride,
+                      int64_t src_col_stride, double* dst, int64_t dst_row_stride,
+                      int64_t dst_col_stride, void* stream);
+
+/* B(cols x rows, ldb) = A(rows x cols, lda)^T.
+ * Replaces Transpose_GPU_impl / Copy2DImpl(transA) -> cublas?geam
+ * (include/hydrogen/blas/gpu/Transpose.hpp:40-44; GPU_BLAS_impl.hpp:178-198), reached from
+ * El::Transpose(Matrix<T,GPU>) (include/El/blas_like/level1/Transpose.hpp:161-181). */
+int elb200_transpose_f32(int64_t rows, int64_t cols, const float* A, int64_t lda, float* B,
+                         int64_t ldb, void* stream);
+int elb200_transpose_f64(int64_t rows, int64_t cols, const double* A, int64_t lda, double* B,
+                         int64_t ldb, void* stream);
+
+/* Y(i,j) += alpha * X(i,j), general 2-D strides.
+ * Replaces Axpy_GPU_impl 2-D (include/hydrogen/blas/gpu/Axpy.hpp:51-55,
+ * src/hydrogen/blas/gpu/Axpy.cu:84-150) = axpy::util::InterleaveMatrixUpdate
+ * (include/El/blas_like/level1/Axpy/util.hpp:40-52) and Axpy2DImpl -> geam
+ * (GPU_BLAS_impl.hpp:110-132). */
+int elb200_axpy2d_f32(int64_t rows, int64_t cols, float alpha, const float* X,
+                      int64_t x_row_stride, int64_t x_col_stride, float* Y, int64_t y_row_stride,
+                      int64_t y_col_stride, void* stream);
+int elb200_axpy2d_f64(int64_t rows, int64_t cols, double alpha, const double* X,
+                      int64_t x_row_stride, int64_t x_col_stride, double* Y, int64_t y_row_stride,
+                      int64_t y_col_stride, void* stream);
+
+/* B(rows x cols, ldb) += alpha * A(cols x rows, lda)^T.
+ * Replaces Axpy_GPU_impl(transpA,...) / Axpy2DImplTranspose -> geam
+ * (include/hydrogen/blas/gpu/Axpy.hpp:92-96; GPU_BLAS_impl.hpp:134-158), used by
+ * El::TransposeAxpy (include/El/blas_like/level1/TransposeAxpy.hpp). */
+int elb200_axpy2d_transpose_f32(int64_t rows, int64_t cols, float alpha, const float* A,
+                                int64_t lda, float* B, int64_t ldb, void* stream);
+int elb200_axpy2d_transpose_f64(int64_t rows, int64_t cols, double alpha, const double* A,
+                                int64_t lda, double* B, int64_t ldb, void* stream);
+
+/* A(i,j) *= alpha.  alpha == 0 writes exact zeros (no NaN propagation), like El::Scale -> Zero
+ * (include/El/blas_like/level1/Scale.hpp:17-30). Replaces Scale_GPU_impl 2-D / Scale2DImpl -> geam
+ * (include/hydrogen/blas/gpu/Scale.hpp:78-82; GPU_BLAS_impl.hpp:254-273). */
+int elb200_scale2d_f32(int64_t rows, int64_t cols, float alpha, float* A, int64_t lda,
+                       void* stream);
+int elb200_scale2d_f64(int64_t rows, int64_t cols, double alpha, double* A, int64_t lda,
+                       void* stream);
+
+/* A(i,j) = value.  Replaces Fill_GPU_impl (include/hydrogen/blas/gpu/Fill.hpp:23-25,
+ * src/hydrogen/blas/gpu/Fill.cu:19-78) as used by simple_buffer(size, value) and El::Zero. */
+int elb200_fill2d_f32(int64_t rows, int64_t cols, float value, float* A, int64_t lda,
+                      void* stream);
+int elb200_fill2d_f64(int64_t rows, int64_t cols, double value, double* A, int64_t lda,
+                      void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Redistribution pack/unpack: ONE launch moves every per-peer portion of an element-cyclic
+ * redistribution between a local column-major matrix and a staging buffer.
+ *
+ * Each segment s describes a 2-D lattice of the local matrix
+ *     M(row0 + i*row_step, col0 + j*col_step),  0 <= i < rows, 0 <= j < cols
+ * stored packed (column-major, leading dimension = rows) at buf + buf_offset.
+ * This single table-driven kernel replaces the reference's loops of cudaMemcpy2DAsync /
+ * copy_2d_kernel launches in copy::util::{RowStridedPack,RowStridedUnpack,ColStridedPack,
+ * ColStridedUnpack,PartialRow/ColStridedPack/Unpack,StridedPack,StridedUnpack}
+ * (include/El/blas_like/level1/Copy/util.hpp:232-355,359-417,460-552,667-718).
+ * ---------------------------------------------------------------------------------------- */
+typedef struct elb200_segment {
+    int64_t row0, row_step, rows; /* lattice rows of the local matrix        */
+    int64_t col0, col_step, cols; /* lattice columns of the local matrix     */
+    int64_t buf_offset;           /* element offset of the packed block      */
+} elb200_segment;
+
+#define ELB200_MAX_SEGMENTS 64
+
+/* buf[seg] <- M lattice   (mode 0)
+ * M lattice <- buf[seg]   (mode 1)
+ * M lattice += alpha*buf  (mode 2; the axpy-unpack after ReduceScatter,
+ *                          include/El/blas_like/level1/AxpyContract.hpp:334-337) */
+typedef enum elb200_pack_mode {
+    ELB200_PACK = 0,
+    ELB200_UNPACK = 1,
+    ELB200_UNPACK_AXPY = 2
+} elb200_pack_mode;
+
+int elb200_lattice_f32(int mode, int nseg, const elb200_segment* segs, float* M, int64_t ldm,
+                       float* buf, float alpha, void* stream);
+int elb200_lattice_f64(int mode, int nseg, const elb200_segment* segs, double* M, int64_t ldm,
+                       double* buf, double alpha, void* stream);
+
+#ifdef __cplusplus
+} /* extern "C" */
+#endif
+
+#endif /* ELB200_H_ */
