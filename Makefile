@@ -24,7 +24,7 @@ build/%.cpp.o: $(CSRC)/%.cpp $(HDRS)
 
 $(LIBDIR)/libelb200.so: $(OBJS)
 	@mkdir -p $(LIBDIR)
-	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -lcudart
+	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -lcudart -lnccl
 
 tools/gemm_check: tools/gemm_check.cu $(LIBDIR)/libelb200.so include/elb200.h
 	$(NVCC) $(NVFLAGS) -o $@ $< -L$(LIBDIR) -lelb200 -lcublas -Xlinker -rpath,'$$ORIGIN/../$(LIBDIR)'

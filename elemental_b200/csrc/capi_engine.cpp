@@ -1,0 +1,262 @@
+// extern "C" handle API over the host engine + the planner entry points. See include/elb200.h.
+#include <cmath>
+#include <cstring>
+#include <memory>
+
+#include "engine.hpp"
+#include "engine_dev.hpp"
+
+namespace elb {
+void set_last_error(const char* what, const char* detail);
+}
+using namespace elb;
+
+struct elb200_grid_s {
+    std::unique_ptr<Grid> g;
+};
+struct elb200_dm_s {
+    int dtype;
+    std::unique_ptr<DistMat<float>> f;
+    std::unique_ptr<DistMat<double>> d;
+    Grid* grid() const { return dtype == ELB200_F32 ? f->grid : d->grid; }
+};
+
+namespace {
+
+template <typename F>
+int guarded(const char* where, F&& fn) {
+    try {
+        fn();
+        return ELB200_OK;
+    } catch (const EngineError& e) {
+        set_last_error(where, e.what());
+        return e.status;
+    } catch (const std::exception& e) {
+        set_last_error(where, e.what());
+        return ELB200_ERR_STATE;
+    }
+}
+
+bool same_dtype(elb200_dm_t a, elb200_dm_t b) { return a && b && a->dtype == b->dtype; }
+
+DistSpec to_spec(const elb200_dist_spec& s) {
+    DistSpec d;
+    d.col = Dist(s.col_dist); d.row = Dist(s.row_dist);
+    d.col_align = s.col_align; d.row_align = s.row_align;
+    d.height = s.height; d.width = s.width;
+    return d;
+}
+elb200_message to_msg(const Message& m) {
+    elb200_message o;
+    o.peer = m.peer; o.valid = 1; o.seg = m.seg;
+    return o;
+}
+bool spec_ok(const GridShape& g, const elb200_dist_spec& s) {
+    if (!valid_pair(Dist(s.col_dist), Dist(s.row_dist))) return false;
+    if (s.height < 0 || s.width < 0) return false;
+    if (s.col_align < 0 || s.col_align >= dist_stride(g, Dist(s.col_dist))) return false;
+    if (s.row_align < 0 || s.row_align >= dist_stride(g, Dist(s.row_dist))) return false;
+    return true;
+}
+
+}  // namespace
+
+extern "C" {
+
+int64_t elb200_shift(int64_t rank, int64_t align, int64_t stride) { return Shift(rank, align, stride); }
+int64_t elb200_length(int64_t n, int64_t shift, int64_t stride) { return Length(n, shift, stride); }
+int64_t elb200_max_length(int64_t n, int64_t stride) { return MaxLength(n, stride); }
+
+int elb200_default_grid_height(int p) {
+    // reference Grid::DefaultHeight, src/core/Grid.cpp:57-63
+    if (p < 1) return 1;
+    int h = int(std::sqrt(double(p)));
+    if (h < 1) h = 1;
+    while (p % h != 0) ++h;
+    return h;
+}
+
+int elb200_gemm_resolve_alg(int ta, int tb, int64_t m, int64_t n, int64_t k, int alg) {
+    return ResolveGemmAlg(ta, tb, m, n, k, alg);
+}
+
+int elb200_plan_copy(int r, int c, int vc, const elb200_dist_spec* A, const elb200_dist_spec* B,
+                     elb200_copy_plan* out) {
+    if (!A || !B || !out || r < 1 || c < 1 || vc < 0 || vc >= r * c) return ELB200_ERR_ARG;
+    GridShape g; g.r = r; g.c = c;
+    if (r * c > ELB200_MAX_SEGMENTS || !spec_ok(g, *A) || !spec_ok(g, *B)) return ELB200_ERR_ARG;
+    if (A->height != B->height || A->width != B->width) return ELB200_ERR_ARG;
+    const CopyPlan p = plan_copy(g, coord_of_vc(g, vc), to_spec(*A), to_spec(*B));
+    std::memset(out, 0, sizeof(*out));
+    out->kind = p.kind; out->comm_dist = p.comm_dist; out->portion = p.portion;
+    out->nsend = int(p.sends.size()); out->nrecv = int(p.recvs.size());
+    out->has_self = p.has_self ? 1 : 0;
+    out->send_elems = p.send_elems; out->recv_elems = p.recv_elems;
+    if (p.has_self) { out->self_send = to_msg(p.self_send); out->self_recv = to_msg(p.self_recv); }
+    for (int i = 0; i < out->nsend; ++i) out->sends[i] = to_msg(p.sends[i]);
+    for (int i = 0; i < out->nrecv; ++i) out->recvs[i] = to_msg(p.recvs[i]);
+    return ELB200_OK;
+}
+
+int elb200_plan_contract(int r, int c, int vc, const elb200_dist_spec* A, const elb200_dist_spec* B,
+                         elb200_contract_plan* out) {
+    if (!A || !B || !out || r < 1 || c < 1 || vc < 0 || vc >= r * c) return ELB200_ERR_ARG;
+    GridShape g; g.r = r; g.c = c;
+    if (r * c > ELB200_MAX_SEGMENTS || !spec_ok(g, *A) || !spec_ok(g, *B)) return ELB200_ERR_ARG;
+    const ContractPlan p = plan_contract(g, coord_of_vc(g, vc), to_spec(*A), to_spec(*B));
+    std::memset(out, 0, sizeof(*out));
+    out->valid = p.valid ? 1 : 0; out->comm_dist = p.comm_dist; out->group = p.group;
+    out->my_index = p.my_index; out->portion = p.portion;
+    out->npack = int(p.packs.size());
+    for (int i = 0; i < out->npack; ++i) out->packs[i] = to_msg(p.packs[i]);
+    out->unpack = p.unpack;
+    return ELB200_OK;
+}
+
+int elb200_unique_id(void* out128) {
+    if (!out128) return ELB200_ERR_ARG;
+    static_assert(sizeof(ncclUniqueId) <= ELB200_UNIQUE_ID_BYTES, "unique id size");
+    ncclUniqueId id;
+    ncclResult_t r = ncclGetUniqueId(&id);
+    if (r != ncclSuccess) { set_last_error("ncclGetUniqueId", ncclGetErrorString(r)); return ELB200_ERR_NCCL; }
+    std::memset(out128, 0, ELB200_UNIQUE_ID_BYTES);
+    std::memcpy(out128, &id, sizeof(id));
+    return ELB200_OK;
+}
+
+int elb200_grid_create(int height, int width, int vc, const void* id128, int device, elb200_grid_t* out) {
+    if (!out) return ELB200_ERR_ARG;
+    *out = nullptr;
+    return guarded("elb200_grid_create", [&] {
+        ncclUniqueId id;
+        if (id128) std::memcpy(&id, id128, sizeof(id));
+        auto h = std::make_unique<elb200_grid_s>();
+        h->g = std::make_unique<Grid>(height, width, vc, id128 ? &id : nullptr, device);
+        *out = h.release();
+    });
+}
+int elb200_grid_destroy(elb200_grid_t g) {
+    if (!g) return ELB200_OK;
+    return guarded("elb200_grid_destroy", [&] { delete g; });
+}
+int elb200_grid_info(elb200_grid_t g, int* h, int* w, int* vc, int* mc, int* mr) {
+    if (!g) return ELB200_ERR_ARG;
+    if (h) *h = g->g->shape.r;
+    if (w) *w = g->g->shape.c;
+    if (vc) *vc = g->g->vc_rank;
+    if (mc) *mc = g->g->me.mc;
+    if (mr) *mr = g->g->me.mr;
+    return ELB200_OK;
+}
+void* elb200_grid_stream(elb200_grid_t g) { return g ? g->g->stream : nullptr; }
+int elb200_grid_sync(elb200_grid_t g) {
+    if (!g) return ELB200_ERR_ARG;
+    return guarded("elb200_grid_sync", [&] { cuda_check(cudaStreamSynchronize(g->g->stream), "cudaStreamSynchronize"); });
+}
+
+int elb200_blocksize(void) { return Grid::Blocksize(); }
+void elb200_set_blocksize(int nb) { Grid::SetBlocksize(nb); }
+void elb200_push_blocksize(int nb) { Grid::PushBlocksize(nb); }
+void elb200_pop_blocksize(void) { Grid::PopBlocksize(); }
+
+int elb200_dm_create(elb200_grid_t g, int dtype, int col, int row, elb200_dm_t* out) {
+    if (!g || !out || (dtype != ELB200_F32 && dtype != ELB200_F64)) return ELB200_ERR_ARG;
+    *out = nullptr;
+    return guarded("elb200_dm_create", [&] {
+        auto h = std::make_unique<elb200_dm_s>();
+        h->dtype = dtype;
+        if (dtype == ELB200_F32) h->f = std::make_unique<DistMat<float>>(*g->g, Dist(col), Dist(row));
+        else h->d = std::make_unique<DistMat<double>>(*g->g, Dist(col), Dist(row));
+        *out = h.release();
+    });
+}
+int elb200_dm_destroy(elb200_dm_t a) {
+    if (!a) return ELB200_OK;
+    return guarded("elb200_dm_destroy", [&] { delete a; });
+}
+
+#define ELB_ON(a, expr_f, expr_d) do { if ((a)->dtype == ELB200_F32) { auto& M = *(a)->f; expr_f; } else { auto& M = *(a)->d; expr_d; } } while (0)
+
+int elb200_dm_info(elb200_dm_t a, elb200_dm_info_t* o) {
+    if (!a || !o) return ELB200_ERR_ARG;
+    auto fill = [&](auto& M) {
+        o->dtype = a->dtype; o->col_dist = M.spec.col; o->row_dist = M.spec.row; o->is_view = M.owner ? 0 : 1;
+        o->height = M.spec.height; o->width = M.spec.width;
+        o->col_align = M.spec.col_align; o->row_align = M.spec.row_align;
+        o->col_shift = M.col_shift(); o->row_shift = M.row_shift();
+        o->col_stride = M.col_stride(); o->row_stride = M.row_stride();
+        o->local_height = M.lh(); o->local_width = M.lw(); o->ldim = M.ldim;
+        o->buffer = M.buf;
+    };
+    ELB_ON(a, fill(M), fill(M));
+    return ELB200_OK;
+}
+int elb200_dm_align(elb200_dm_t a, int64_t ca, int64_t ra) {
+    if (!a) return ELB200_ERR_ARG;
+    return guarded("elb200_dm_align", [&] { ELB_ON(a, M.Align(ca, ra), M.Align(ca, ra)); });
+}
+int elb200_dm_align_with(elb200_dm_t a, elb200_dm_t o) {
+    if (!a || !o) return ELB200_ERR_ARG;
+    return guarded("elb200_dm_align_with", [&] {
+        const DistSpec s = o->dtype == ELB200_F32 ? o->f->spec : o->d->spec;
+        ELB_ON(a, M.AlignWith(s), M.AlignWith(s));
+    });
+}
+int elb200_dm_resize(elb200_dm_t a, int64_t h, int64_t w) {
+    if (!a) return ELB200_ERR_ARG;
+    return guarded("elb200_dm_resize", [&] { ELB_ON(a, M.Resize(h, w), M.Resize(h, w)); });
+}
+int elb200_dm_attach(elb200_dm_t a, int64_t h, int64_t w, int64_t ca, int64_t ra, void* buf, int64_t ld) {
+    if (!a) return ELB200_ERR_ARG;
+    return guarded("elb200_dm_attach", [&] {
+        ELB_ON(a, M.Attach(h, w, ca, ra, static_cast<float*>(buf), ld), M.Attach(h, w, ca, ra, static_cast<double*>(buf), ld));
+    });
+}
+int elb200_dm_view(elb200_dm_t a, int64_t i0, int64_t i1, int64_t j0, int64_t j1, elb200_dm_t* out) {
+    if (!a || !out) return ELB200_ERR_ARG;
+    *out = nullptr;
+    return guarded("elb200_dm_view", [&] {
+        auto h = std::make_unique<elb200_dm_s>();
+        h->dtype = a->dtype;
+        if (a->dtype == ELB200_F32) h->f = std::make_unique<DistMat<float>>(a->f->View(i0, i1, j0, j1));
+        else h->d = std::make_unique<DistMat<double>>(a->d->View(i0, i1, j0, j1));
+        *out = h.release();
+    });
+}
+
+#define ELB_BINARY(NAME, CALL_F, CALL_D)                                                  \
+    if (!same_dtype(A, B)) return ELB200_ERR_ARG;                                         \
+    return guarded(NAME, [&] { if (A->dtype == ELB200_F32) { CALL_F; } else { CALL_D; } });
+
+int elb200_dm_copy(elb200_dm_t A, elb200_dm_t B) { ELB_BINARY("elb200_dm_copy", Copy(*A->f, *B->f), Copy(*A->d, *B->d)) }
+int elb200_dm_transpose(elb200_dm_t A, elb200_dm_t B) { ELB_BINARY("elb200_dm_transpose", TransposeCopy(*A->f, *B->f), TransposeCopy(*A->d, *B->d)) }
+int elb200_dm_axpy(double alpha, elb200_dm_t A, elb200_dm_t B) { ELB_BINARY("elb200_dm_axpy", Axpy(float(alpha), *A->f, *B->f), Axpy(alpha, *A->d, *B->d)) }
+int elb200_dm_axpy_contract(double alpha, elb200_dm_t A, elb200_dm_t B) { ELB_BINARY("elb200_dm_axpy_contract", AxpyContract(float(alpha), *A->f, *B->f), AxpyContract(alpha, *A->d, *B->d)) }
+int elb200_dm_contract(elb200_dm_t A, elb200_dm_t B) { ELB_BINARY("elb200_dm_contract", Contract(*A->f, *B->f), Contract(*A->d, *B->d)) }
+int elb200_dm_transpose_axpy_contract(double alpha, elb200_dm_t A, elb200_dm_t B) { ELB_BINARY("elb200_dm_transpose_axpy_contract", TransposeAxpyContract(float(alpha), *A->f, *B->f), TransposeAxpyContract(alpha, *A->d, *B->d)) }
+
+int elb200_dm_scale(double alpha, elb200_dm_t A) {
+    if (!A) return ELB200_ERR_ARG;
+    return guarded("elb200_dm_scale", [&] { ELB_ON(A, Scale(float(alpha), M), Scale(alpha, M)); });
+}
+int elb200_dm_zero(elb200_dm_t A) {
+    if (!A) return ELB200_ERR_ARG;
+    return guarded("elb200_dm_zero", [&] { ELB_ON(A, Zero(M), Zero(M)); });
+}
+int elb200_dm_local_gemm(int ta, int tb, double alpha, elb200_dm_t A, elb200_dm_t B, double beta, elb200_dm_t C) {
+    if (!same_dtype(A, B) || !same_dtype(A, C)) return ELB200_ERR_ARG;
+    return guarded("elb200_dm_local_gemm", [&] {
+        if (A->dtype == ELB200_F32) LocalGemm(ta, tb, float(alpha), *A->f, *B->f, float(beta), *C->f);
+        else LocalGemm(ta, tb, alpha, *A->d, *B->d, beta, *C->d);
+    });
+}
+int elb200_dist_gemm(int ta, int tb, double alpha, elb200_dm_t A, elb200_dm_t B, double beta, elb200_dm_t C, int alg) {
+    if (!same_dtype(A, B) || !same_dtype(A, C)) return ELB200_ERR_ARG;
+    if (ta < 0 || ta > 2 || tb < 0 || tb > 2 || alg < 0 || alg > 8) return ELB200_ERR_ARG;
+    return guarded("elb200_dist_gemm", [&] {
+        if (A->dtype == ELB200_F32) Gemm(ta, tb, float(alpha), *A->f, *B->f, float(beta), *C->f, alg);
+        else Gemm(ta, tb, alpha, *A->d, *B->d, beta, *C->d, alg);
+    });
+}
+
+}  // extern "C"

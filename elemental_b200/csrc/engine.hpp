@@ -1,0 +1,125 @@
+// Host engine: Grid, type-erased-by-template DistMat<T>, redistribution, contraction and the
+// SUMMA drivers. This is the C++ that sits between the El:: facade (include/El.hpp) / the handle
+// C ABI (elb200_grid_*, elb200_dm_*, elb200_dist_gemm) and the device C ABI (elb200_gemm_*,
+// elb200_lattice_*, ...). One process per GPU; NCCL communicators for the grid's MC / MR / VC
+// sub-communicators (reference: src/core/Grid.cpp:95-223 builds them with MPI_Cart_sub/Comm_split).
+#pragma once
+#include <cuda_runtime.h>
+#include <nccl.h>
+
+#include <cstdint>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "plan.hpp"
+
+namespace elb {
+
+struct EngineError : std::runtime_error {
+    int status;
+    EngineError(int st, const std::string& what) : std::runtime_error(what), status(st) {}
+};
+void throw_status(int status, const char* where);
+void cuda_check(cudaError_t e, const char* where);
+void nccl_check(ncclResult_t r, const char* where);
+
+// Mirrors El::GemmAlgorithm (reference include/El/blas_like/level3.hpp:22-35), same order.
+enum GemmAlg : int {
+    GEMM_DEFAULT = 0, GEMM_SUMMA_A = 1, GEMM_SUMMA_B = 2, GEMM_SUMMA_C = 3, GEMM_SUMMA_DOT = 4,
+    GEMM_CANNON = 5, GEMM_SUMMA_A_MS = 6, GEMM_SUMMA_B_MS = 7, GEMM_SUMMA_C_MS = 8
+};
+
+class Grid {
+public:
+    // nccl_id == nullptr: a grid without communicators (p must be 1, or plan-only use).
+    Grid(int height, int width, int vc_rank, const ncclUniqueId* nccl_id, int device);
+    ~Grid();
+    Grid(const Grid&) = delete;
+    Grid& operator=(const Grid&) = delete;
+
+    GridShape shape;
+    GridCoord me;
+    int vc_rank = 0;
+    int device = 0;
+    cudaStream_t stream = nullptr;       // compute stream (the reference's SyncInfo of C)
+    cudaStream_t comm_stream = nullptr;  // panel prefetch stream (overlap with the local GEMM)
+    ncclComm_t world = nullptr, mc_comm = nullptr, mr_comm = nullptr;
+
+    int size() const { return shape.size(); }
+    ncclComm_t comm_for(Dist d) const { return d == MC ? mc_comm : d == MR ? mr_comm : world; }
+    // Algorithmic blocksize stack (reference src/blas_like/blocksizes.cpp:35-67; default 128,
+    // src/core/environment.cpp:313-315). Process-global like the reference's.
+    static int Blocksize();
+    static void SetBlocksize(int nb);
+    static void PushBlocksize(int nb);
+    static void PopBlocksize();
+    // Internal SUMMA_C/A/B panel width: several algorithmic blocks are moved and multiplied per
+    // step so that one pass over the local C amortises >= this many k.
+    static int64_t PanelWidth(int elem_bytes);
+};
+
+template <typename T>
+class DistMat {
+public:
+    DistMat(Grid& g, Dist col, Dist row, cudaStream_t s = nullptr);
+    ~DistMat();
+    DistMat(const DistMat&) = delete;
+    DistMat& operator=(const DistMat&) = delete;
+    DistMat(DistMat&& o) noexcept;
+
+    Grid* grid;
+    DistSpec spec;
+    bool col_constrained = false, row_constrained = false;
+    T* buf = nullptr;
+    int64_t ldim = 1;
+    bool owner = true;
+    int64_t capacity = 0;  // elements owned
+    cudaStream_t stream;
+
+    int64_t lh() const { return local_height(grid->shape, spec, grid->me); }
+    int64_t lw() const { return local_width(grid->shape, spec, grid->me); }
+    int col_stride() const { return dist_stride(grid->shape, spec.col); }
+    int row_stride() const { return dist_stride(grid->shape, spec.row); }
+    int64_t col_shift() const { return Shift(dist_rank(grid->shape, spec.col, grid->me), spec.col_align, col_stride()); }
+    int64_t row_shift() const { return Shift(dist_rank(grid->shape, spec.row, grid->me), spec.row_align, row_stride()); }
+
+    void Align(int64_t col_align, int64_t row_align, bool constrain = true);
+    void AlignCols(int64_t col_align, bool constrain = true);
+    void AlignRows(int64_t row_align, bool constrain = true);
+    // Adopt whichever alignments of `other` are meaningful for this distribution
+    // (reference ElementalMatrix::AlignWith, src/core/DistMatrix/ElementMatrix.cpp).
+    void AlignWith(const DistSpec& other, bool constrain = true);
+    void Resize(int64_t height, int64_t width);
+    void Attach(int64_t height, int64_t width, int64_t col_align, int64_t row_align, T* buffer, int64_t ld);
+    // Zero-copy view of rows [i0,i1) x cols [j0,j1) (reference View/LockedView + operator()(IR,IR)).
+    DistMat View(int64_t i0, int64_t i1, int64_t j0, int64_t j1) const;
+};
+
+// ---- distributed BLAS-1 (reference include/El/blas_like/level1/*.hpp) -------------------------
+template <typename T> void Copy(const DistMat<T>& A, DistMat<T>& B);                // B = A
+template <typename T> void TransposeCopy(const DistMat<T>& A, DistMat<T>& B);       // B = A^T
+template <typename T> void AxpyContract(T alpha, const DistMat<T>& A, DistMat<T>& B);
+template <typename T> void Contract(const DistMat<T>& A, DistMat<T>& B);
+template <typename T> void TransposeAxpyContract(T alpha, const DistMat<T>& A, DistMat<T>& B);
+template <typename T> void Axpy(T alpha, const DistMat<T>& X, DistMat<T>& Y);       // same dist
+template <typename T> void Scale(T alpha, DistMat<T>& A);
+template <typename T> void Zero(DistMat<T>& A);
+
+// ---- BLAS-3 ------------------------------------------------------------------------------------
+template <typename T>
+void LocalGemm(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, T beta, DistMat<T>& C);
+template <typename T>
+void Gemm(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, T beta, DistMat<T>& C, int alg);
+// Which SUMMA variant GEMM_DEFAULT resolves to (reference Gemm/NN.hpp:585-600 and twins).
+int ResolveGemmAlg(int ta, int tb, int64_t m, int64_t n, int64_t k, int alg);
+
+bool implied_align(Dist mine, Dist theirs, int64_t a, const GridShape& g, int64_t* out);
+// Distribution spec B ends up with after `B = A` (dims from A; unconstrained alignments adopt A's).
+DistSpec ResolveCopySpec(const GridShape& g, const DistSpec& A, DistSpec B, bool col_constrained,
+                         bool row_constrained);
+
+// device-op dispatch by element type (thin wrappers over the C ABI; throw on error)
+template <typename T> struct Dev;
+
+}  // namespace elb

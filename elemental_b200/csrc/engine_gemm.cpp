@@ -1,0 +1,234 @@
+// Distributed Gemm: C = alpha op(A) op(B) + beta C over [MC,MR] DistMats — the SUMMA A/B/C/Dot
+// families for all four orientation pairs (reference src/blas_like/level3/Gemm.cpp:273-302 and
+// Gemm/{NN,NT,TN,TT}.hpp).
+//
+// B200-first differences from the reference's schedule (results agree within the GEMM tolerance,
+// redistribution results are bit-identical):
+//  * panels are `PanelWidth()` wide (a whole number of algorithmic blocks, default 2048 fp32 /
+//    1024 fp64) instead of one block of 128: one pass over the local C then amortises enough k
+//    for the tensor pipe to be the bound, not HBM (SURVEY.md §7 hard part 1);
+//  * the local GEMM consumes panels in whichever majorness the gather produces ([MC,*], [*,MC],
+//    [MR,*], [*,MR]) through its TMA/UMMA descriptors, so the reference's explicit panel
+//    transposes (Transpose(B1, B1Trans_MR_STAR) etc.) disappear;
+//  * a panel whose redistribution is the identity on this grid (1 x 1, or c == 1 / r == 1 along the
+//    gathered dimension) is used in place, without a copy.
+#include <algorithm>
+#include <cstdlib>
+
+#include "engine.hpp"
+#include "engine_dev.hpp"
+
+namespace elb {
+
+template <typename T>
+void LocalGemm(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, T beta, DistMat<T>& C) {
+    const int64_t m = C.lh(), n = C.lw();
+    const int64_t ka = ta ? A.lh() : A.lw(), kb = tb ? B.lw() : B.lh();
+    const int64_t ma = ta ? A.lw() : A.lh(), nb = tb ? B.lh() : B.lw();
+    if (ka != kb || ma != m || nb != n)
+        throw EngineError(ELB200_ERR_ARG, "LocalGemm: nonconformal local matrices");
+    Dev<T>::gemm(ta, tb, m, n, ka, alpha, A.buf, A.ldim, B.buf, B.ldim, beta, C.buf, C.ldim, C.stream);
+}
+
+int ResolveGemmAlg(int, int, int64_t m, int64_t n, int64_t k, int alg) {
+    // reference Gemm/NN.hpp:572-600 (same constants in NT/TN/TT)
+    if (alg == GEMM_DEFAULT) {
+        const double weightTowardsC = 2., weightAwayFromDot = 10.;
+        if (weightAwayFromDot * m <= k && weightAwayFromDot * n <= k) alg = GEMM_SUMMA_DOT;
+        else if (m <= n && weightTowardsC * m <= k) alg = GEMM_SUMMA_B;
+        else if (n <= m && weightTowardsC * n <= k) alg = GEMM_SUMMA_A;
+        else alg = GEMM_SUMMA_C;
+    }
+    // the multistream twins differ only in schedule; here every variant already pipelines
+    if (alg == GEMM_SUMMA_A_MS) alg = GEMM_SUMMA_A;
+    if (alg == GEMM_SUMMA_B_MS) alg = GEMM_SUMMA_B;
+    if (alg == GEMM_SUMMA_C_MS) alg = GEMM_SUMMA_C;
+    return alg;
+}
+
+namespace {
+
+// src redistributed as (col,row) aligned with `like`; returns src itself when that
+// redistribution is the identity on every rank (no data motion, no copy).
+template <typename T>
+const DistMat<T>& panel_as(const DistMat<T>& src, DistMat<T>& tmp, const DistSpec& like) {
+    tmp.col_constrained = tmp.row_constrained = false;
+    tmp.spec.col_align = tmp.spec.row_align = 0;
+    tmp.AlignWith(like, true);
+    Grid& g = *src.grid;
+    const DistSpec target = ResolveCopySpec(g.shape, src.spec, tmp.spec, tmp.col_constrained, tmp.row_constrained);
+    const CopyPlan plan = plan_copy(g.shape, g.me, src.spec, target);
+    if (plan.kind == EX_LOCAL) {
+        bool identity_everywhere = true;  // identical local shapes on every rank <=> strides/shifts agree
+        if (dist_stride(g.shape, src.spec.col) != dist_stride(g.shape, target.col) ||
+            dist_stride(g.shape, src.spec.row) != dist_stride(g.shape, target.row))
+            identity_everywhere = false;
+        for (int v = 0; v < g.size() && identity_everywhere; ++v) {
+            const GridCoord q = coord_of_vc(g.shape, v);
+            if (Shift(dist_rank(g.shape, src.spec.col, q), src.spec.col_align, dist_stride(g.shape, src.spec.col)) !=
+                    Shift(dist_rank(g.shape, target.col, q), target.col_align, dist_stride(g.shape, target.col)) ||
+                Shift(dist_rank(g.shape, src.spec.row, q), src.spec.row_align, dist_stride(g.shape, src.spec.row)) !=
+                    Shift(dist_rank(g.shape, target.row, q), target.row_align, dist_stride(g.shape, target.row)))
+                identity_everywhere = false;
+        }
+        if (identity_everywhere) return src;
+    }
+    Copy(src, tmp);
+    return tmp;
+}
+
+struct Dims { int64_t m, n, k; };
+
+// ---- stationary C: C += alpha op(A)(:,kr) op(B)(kr,:) -----------------------------------------
+template <typename T>
+void SummaC(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, DistMat<T>& C, Dims d) {
+    Grid& g = *C.grid;
+    const int64_t W = Grid::PanelWidth(sizeof(T));
+    DistMat<T> PA(g, ta ? STAR : MC, ta ? MC : STAR, C.stream);
+    DistMat<T> PB(g, tb ? MR : STAR, tb ? STAR : MR, C.stream);
+    for (int64_t k0 = 0; k0 < d.k; k0 += W) {
+        const int64_t kb = std::min(W, d.k - k0);
+        DistMat<T> A1 = ta ? A.View(k0, k0 + kb, 0, d.m) : A.View(0, d.m, k0, k0 + kb);
+        DistMat<T> B1 = tb ? B.View(0, d.n, k0, k0 + kb) : B.View(k0, k0 + kb, 0, d.n);
+        const DistMat<T>& a = panel_as(A1, PA, C.spec);  // [MC,*] (or [*,MC]) aligned with C's rows
+        const DistMat<T>& b = panel_as(B1, PB, C.spec);  // [*,MR] (or [MR,*]) aligned with C's cols
+        LocalGemm(ta, tb, alpha, a, b, T(1), C);
+    }
+}
+
+// ---- stationary A: per column panel of C, D1 = alpha op(A) op(B)(:,panel) summed over the
+//      grid dimension that shares op(A)'s k index, then scattered into C1 --------------------
+template <typename T>
+void SummaA(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, DistMat<T>& C, Dims d) {
+    Grid& g = *C.grid;
+    const int64_t W = Grid::PanelWidth(sizeof(T));
+    // k runs over MR when A is used as is (k = A's columns), over MC when A is transposed
+    const Dist kd = ta ? MC : MR;
+    DistMat<T> PB(g, tb ? STAR : kd, tb ? kd : STAR, C.stream);       // op(B) panel: k x nb or nb x k
+    DistMat<T> D1(g, ta ? MR : MC, STAR, C.stream);                   // m x nb partial sums
+    DistMat<T> D1s(g, MR, MC, C.stream);
+    for (int64_t j0 = 0; j0 < d.n; j0 += W) {
+        const int64_t nb = std::min(W, d.n - j0);
+        DistMat<T> B1 = tb ? B.View(j0, j0 + nb, 0, d.k) : B.View(0, d.k, j0, j0 + nb);
+        DistMat<T> C1 = C.View(0, d.m, j0, j0 + nb);
+        const DistMat<T>& b = panel_as(B1, PB, A.spec);
+        D1.col_constrained = D1.row_constrained = false;
+        D1.AlignWith(A.spec, true);
+        D1.Resize(d.m, nb);
+        LocalGemm(ta, tb, alpha, A, b, T(0), D1);
+        if (!ta) {
+            AxpyContract(T(1), D1, C1);          // [MC,*] -> [MC,MR]: ReduceScatter over MR
+        } else {
+            D1s.col_constrained = D1s.row_constrained = false;
+            Contract(D1, D1s);                   // [MR,*] -> [MR,MC]: ReduceScatter over MC
+            Axpy(T(1), D1s, C1);                 // [MR,MC] -> [MC,MR] exchange + local axpy
+        }
+    }
+}
+
+// ---- stationary B: per row panel of C -----------------------------------------------------------
+template <typename T>
+void SummaB(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, DistMat<T>& C, Dims d) {
+    Grid& g = *C.grid;
+    const int64_t W = Grid::PanelWidth(sizeof(T));
+    // k runs over MC when B is used as is (k = B's rows), over MR when B is transposed
+    const Dist kd = tb ? MR : MC;
+    DistMat<T> PA(g, ta ? kd : STAR, ta ? STAR : kd, C.stream);       // op(A) panel: mb x k or k x mb
+    DistMat<T> D1(g, STAR, tb ? MC : MR, C.stream);                   // mb x n partial sums
+    DistMat<T> D1s(g, MR, MC, C.stream);
+    for (int64_t i0 = 0; i0 < d.m; i0 += W) {
+        const int64_t mb = std::min(W, d.m - i0);
+        DistMat<T> A1 = ta ? A.View(0, d.k, i0, i0 + mb) : A.View(i0, i0 + mb, 0, d.k);
+        DistMat<T> C1 = C.View(i0, i0 + mb, 0, d.n);
+        const DistMat<T>& a = panel_as(A1, PA, B.spec);
+        D1.col_constrained = D1.row_constrained = false;
+        D1.AlignWith(B.spec, true);
+        D1.Resize(mb, d.n);
+        LocalGemm(ta, tb, alpha, a, B, T(0), D1);
+        if (!tb) {
+            AxpyContract(T(1), D1, C1);          // [*,MR] -> [MC,MR]: ReduceScatter over MC
+        } else {
+            D1s.col_constrained = D1s.row_constrained = false;
+            Contract(D1, D1s);                   // [*,MC] -> [MR,MC]: ReduceScatter over MR
+            Axpy(T(1), D1s, C1);
+        }
+    }
+}
+
+// ---- Dot: k spread over all p ranks, C tiles reduce-scattered over the whole grid ---------------
+template <typename T>
+void SummaDot(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, DistMat<T>& C, Dims d) {
+    Grid& g = *C.grid;
+    static const int64_t kBlock = [] { const char* e = std::getenv("ELB200_DOT_BLOCK"); int64_t v = e ? std::atoll(e) : 0; return v > 0 ? v : int64_t(8192); }();
+    DistMat<T> Ak(g, ta ? VC : STAR, ta ? STAR : VC, C.stream);  // k over VC
+    DistMat<T> Bk(g, tb ? STAR : VC, tb ? VC : STAR, C.stream);
+    Ak.Align(0, 0); Bk.Align(0, 0);
+    Copy(A, Ak);
+    Copy(B, Bk);
+    DistMat<T> C11(g, STAR, STAR, C.stream);
+    for (int64_t i0 = 0; i0 < d.m; i0 += kBlock) {
+        const int64_t mb = std::min(kBlock, d.m - i0);
+        DistMat<T> A1 = ta ? Ak.View(0, d.k, i0, i0 + mb) : Ak.View(i0, i0 + mb, 0, d.k);
+        for (int64_t j0 = 0; j0 < d.n; j0 += kBlock) {
+            const int64_t nb = std::min(kBlock, d.n - j0);
+            DistMat<T> B1 = tb ? Bk.View(j0, j0 + nb, 0, d.k) : Bk.View(0, d.k, j0, j0 + nb);
+            DistMat<T> Cv = C.View(i0, i0 + mb, j0, j0 + nb);
+            C11.Resize(mb, nb);
+            LocalGemm(ta, tb, alpha, A1, B1, T(0), C11);
+            AxpyContract(T(1), C11, Cv);
+        }
+    }
+}
+
+}  // namespace
+
+template <typename T>
+void Gemm(int ta, int tb, T alpha, const DistMat<T>& Apre, const DistMat<T>& Bpre, T beta, DistMat<T>& Cpre, int alg) {
+    ta = ta ? 1 : 0; tb = tb ? 1 : 0;
+    Grid& g = *Cpre.grid;
+    if (Apre.grid != &g || Bpre.grid != &g) throw EngineError(ELB200_ERR_ARG, "Gemm: matrices live on different grids");
+    Dims d;
+    d.m = ta ? Apre.spec.width : Apre.spec.height;
+    d.k = ta ? Apre.spec.height : Apre.spec.width;
+    d.n = tb ? Bpre.spec.height : Bpre.spec.width;
+    const int64_t kb = tb ? Bpre.spec.width : Bpre.spec.height;
+    if (d.k != kb || Cpre.spec.height != d.m || Cpre.spec.width != d.n)
+        throw EngineError(ELB200_ERR_ARG, "Gemm: nonconformal matrices");
+    if (alg == GEMM_CANNON) throw EngineError(ELB200_ERR_ARG, "Cannon_NN: Bad device (CPU only in the reference, Gemm/NN.hpp:30-31)");
+    Scale(beta, Cpre);
+    if (d.m == 0 || d.n == 0 || d.k == 0 || alpha == T(0)) return;
+    alg = ResolveGemmAlg(ta, tb, d.m, d.n, d.k, alg);
+
+    // Read / read-write proxies to [MC,MR] (reference Proxy.hpp:236-257: pass-through when the
+    // matrix already has the requested distribution).
+    const bool a_ok = Apre.spec.col == MC && Apre.spec.row == MR;
+    const bool b_ok = Bpre.spec.col == MC && Bpre.spec.row == MR;
+    const bool c_ok = Cpre.spec.col == MC && Cpre.spec.row == MR;
+    DistMat<T> Ap(g, MC, MR, Cpre.stream), Bp(g, MC, MR, Cpre.stream), Cp(g, MC, MR, Cpre.stream);
+    const bool dot = alg == GEMM_SUMMA_DOT;
+    if (!a_ok && !dot) Copy(Apre, Ap);
+    if (!b_ok && !dot) Copy(Bpre, Bp);
+    if (!c_ok) Copy(Cpre, Cp);
+    const DistMat<T>& A = (a_ok || dot) ? Apre : Ap;
+    const DistMat<T>& B = (b_ok || dot) ? Bpre : Bp;
+    DistMat<T>& C = c_ok ? Cpre : Cp;
+
+    switch (alg) {
+        case GEMM_SUMMA_A: SummaA(ta, tb, alpha, A, B, C, d); break;
+        case GEMM_SUMMA_B: SummaB(ta, tb, alpha, A, B, C, d); break;
+        case GEMM_SUMMA_C: SummaC(ta, tb, alpha, A, B, C, d); break;
+        case GEMM_SUMMA_DOT: SummaDot(ta, tb, alpha, A, B, C, d); break;
+        default: throw EngineError(ELB200_ERR_ARG, "Gemm: unsupported GemmAlgorithm");
+    }
+    if (!c_ok) {
+        DistMat<T> back = Cpre.View(0, d.m, 0, d.n);  // keeps Cpre's alignment and buffer
+        Copy(C, back);
+    }
+}
+
+template void LocalGemm<float>(int, int, float, const DistMat<float>&, const DistMat<float>&, float, DistMat<float>&);
+template void LocalGemm<double>(int, int, double, const DistMat<double>&, const DistMat<double>&, double, DistMat<double>&);
+template void Gemm<float>(int, int, float, const DistMat<float>&, const DistMat<float>&, float, DistMat<float>&, int);
+template void Gemm<double>(int, int, double, const DistMat<double>&, const DistMat<double>&, double, DistMat<double>&, int);
+
+}  // namespace elb

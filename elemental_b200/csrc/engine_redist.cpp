@@ -1,0 +1,221 @@
+// Distributed BLAS-1 of the Gemm path: Copy (any (U,V)->(U',V')), TransposeCopy, AxpyContract,
+// Contract, TransposeAxpyContract, Axpy, Scale, Zero. One generic lattice-exchange engine
+// (plan.hpp) replaces the reference's per-pair routines; AllGather and ReduceScatter shapes run
+// on the matching NCCL collective over the grid's MC / MR / VC communicator.
+#include <algorithm>
+
+#include "engine.hpp"
+#include "engine_dev.hpp"
+
+namespace elb {
+namespace {
+
+template <typename T>
+void run_lattice(int mode, const std::vector<Message>& msgs, T* M, int64_t ldm, T* buf, T alpha,
+                 cudaStream_t s) {
+    elb200_segment segs[ELB200_MAX_SEGMENTS];
+    int n = 0;
+    for (const Message& m : msgs) {
+        if (m.count() == 0) continue;
+        segs[n++] = m.seg;
+        if (n == ELB200_MAX_SEGMENTS) { Dev<T>::lattice(mode, n, segs, M, ldm, buf, alpha, s); n = 0; }
+    }
+    if (n) Dev<T>::lattice(mode, n, segs, M, ldm, buf, alpha, s);
+}
+
+// dst lattice <- src lattice, both on this rank (same number of rows/cols by construction)
+template <typename T>
+void lattice_to_lattice(const elb200_segment& a, const T* A, int64_t lda, const elb200_segment& b, T* B,
+                        int64_t ldb, cudaStream_t s) {
+    Dev<T>::copy2d(a.rows, a.cols, A + a.row0 + a.col0 * lda, a.row_step, a.col_step * lda,
+                   B + b.row0 + b.col0 * ldb, b.row_step, b.col_step * ldb, s);
+}
+
+// Unconstrained alignments of B follow A where the distributions relate (reference: the
+// AlignColsAndResize / AlignAndResize calls at the top of every copy:: routine).
+template <typename T>
+void adopt_alignment(const DistMat<T>& A, DistMat<T>& B) {
+    const DistSpec t = ResolveCopySpec(A.grid->shape, A.spec, B.spec, B.col_constrained, B.row_constrained);
+    B.spec.col_align = t.col_align;
+    B.spec.row_align = t.row_align;
+}
+
+}  // namespace
+
+template <typename T>
+void Copy(const DistMat<T>& A, DistMat<T>& B) {
+    if (A.grid != B.grid) throw EngineError(ELB200_ERR_ARG, "Copy: matrices live on different grids");
+    Grid& g = *A.grid;
+    adopt_alignment(A, B);
+    B.Resize(A.spec.height, A.spec.width);
+    if (A.spec.height == 0 || A.spec.width == 0) return;
+    cudaStream_t s = B.stream;
+    const CopyPlan plan = plan_copy(g.shape, g.me, A.spec, B.spec);
+    T* Abuf = const_cast<T*>(A.buf);
+
+    if (plan.kind == EX_LOCAL) {
+        if (plan.has_self)
+            lattice_to_lattice<T>(plan.self_send.seg, A.buf, A.ldim, plan.self_recv.seg, B.buf, B.ldim, s);
+        return;
+    }
+    if (plan.kind == EX_ALLGATHER) {
+        ncclComm_t comm = g.comm_for(plan.comm_dist);
+        if (!comm) throw EngineError(ELB200_ERR_STATE, "Copy: grid has no NCCL communicator");
+        const int gsz = int(plan.recvs.size());
+        const int64_t mine = plan.sends[0].count();
+        // ship straight out of A's local matrix when it is one contiguous full-size block
+        const bool direct = mine == plan.portion && (A.ldim == plan.sends[0].seg.rows || plan.sends[0].seg.cols <= 1);
+        Scratch<T> stage((gsz + (direct ? 0 : 1)) * plan.portion, s);
+        T* recv = stage.p;
+        const T* send = A.buf;
+        if (!direct) {
+            T* slot = stage.p + int64_t(gsz) * plan.portion;
+            if (mine > 0) {
+                std::vector<Message> one{plan.sends[0]};
+                run_lattice<T>(ELB200_PACK, one, Abuf, A.ldim, slot, T(0), s);
+            }
+            send = slot;
+        }
+        nccl_check(ncclAllGather(send, recv, size_t(plan.portion), Dev<T>::nccl, comm, s), "ncclAllGather");
+        run_lattice<T>(ELB200_UNPACK, plan.recvs, B.buf, B.ldim, recv, T(0), s);
+        return;
+    }
+    // general exchange: pack -> grouped send/recv over the world communicator -> unpack
+    if (!g.world) throw EngineError(ELB200_ERR_STATE, "Copy: grid has no NCCL communicator");
+    Scratch<T> sbuf(plan.send_elems, s), rbuf(plan.recv_elems, s);
+    run_lattice<T>(ELB200_PACK, plan.sends, Abuf, A.ldim, sbuf.p, T(0), s);
+    nccl_check(ncclGroupStart(), "ncclGroupStart");
+    for (const Message& m : plan.sends)
+        nccl_check(ncclSend(sbuf.p + m.seg.buf_offset, size_t(m.count()), Dev<T>::nccl, m.peer, g.world, s), "ncclSend");
+    for (const Message& m : plan.recvs)
+        nccl_check(ncclRecv(rbuf.p + m.seg.buf_offset, size_t(m.count()), Dev<T>::nccl, m.peer, g.world, s), "ncclRecv");
+    nccl_check(ncclGroupEnd(), "ncclGroupEnd");
+    run_lattice<T>(ELB200_UNPACK, plan.recvs, B.buf, B.ldim, rbuf.p, T(0), s);
+    if (plan.has_self)
+        lattice_to_lattice<T>(plan.self_send.seg, A.buf, A.ldim, plan.self_recv.seg, B.buf, B.ldim, s);
+}
+
+// B = A^T. The transpose of A[U,V] is a [V,U] matrix whose local matrix is the transpose of A's
+// (reference Transpose(ElementalMatrix), level1/Transpose.hpp:200-250: local transpose into a
+// [V,U] temporary, then Copy).
+template <typename T>
+void TransposeCopy(const DistMat<T>& A, DistMat<T>& B) {
+    Grid& g = *A.grid;
+    cudaStream_t s = B.stream;
+    const bool same = B.spec.col == A.spec.row && B.spec.row == A.spec.col &&
+                      (!B.col_constrained || B.spec.col_align == A.spec.row_align) &&
+                      (!B.row_constrained || B.spec.row_align == A.spec.col_align);
+    if (same) {
+        B.spec.col_align = A.spec.row_align;
+        B.spec.row_align = A.spec.col_align;
+        B.Resize(A.spec.width, A.spec.height);
+        Dev<T>::transpose(A.lh(), A.lw(), A.buf, A.ldim, B.buf, B.ldim, s);
+        return;
+    }
+    DistMat<T> At(g, A.spec.row, A.spec.col, s);
+    At.Align(A.spec.row_align, A.spec.col_align);
+    At.Resize(A.spec.width, A.spec.height);
+    Dev<T>::transpose(A.lh(), A.lw(), A.buf, A.ldim, At.buf, At.ldim, s);
+    Copy(At, B);
+}
+
+template <typename T>
+void Axpy(T alpha, const DistMat<T>& X, DistMat<T>& Y) {
+    if (X.spec.height != Y.spec.height || X.spec.width != Y.spec.width)
+        throw EngineError(ELB200_ERR_ARG, "Axpy: nonconformal dimensions");
+    if (X.spec.col == Y.spec.col && X.spec.row == Y.spec.row && X.spec.col_align == Y.spec.col_align &&
+        X.spec.row_align == Y.spec.row_align) {
+        Dev<T>::axpy2d(Y.lh(), Y.lw(), alpha, X.buf, 1, X.ldim, Y.buf, 1, Y.ldim, Y.stream);
+        return;
+    }
+    // different distribution or alignment: redistribute X like Y first (reference Axpy on
+    // ElementalMatrix, level1/Axpy.hpp:120-175, does the same through a temporary copy)
+    DistMat<T> X2(*Y.grid, Y.spec.col, Y.spec.row, Y.stream);
+    X2.Align(Y.spec.col_align, Y.spec.row_align);
+    Copy(X, X2);
+    Dev<T>::axpy2d(Y.lh(), Y.lw(), alpha, X2.buf, 1, X2.ldim, Y.buf, 1, Y.ldim, Y.stream);
+}
+
+template <typename T>
+void Scale(T alpha, DistMat<T>& A) { Dev<T>::scale2d(A.lh(), A.lw(), alpha, A.buf, A.ldim, A.stream); }
+template <typename T>
+void Zero(DistMat<T>& A) { Dev<T>::fill2d(A.lh(), A.lw(), T(0), A.buf, A.ldim, A.stream); }
+
+// B += alpha * (sum over A's replicas)  (reference AxpyContract, level1/AxpyContract.hpp:483-509)
+template <typename T>
+void AxpyContract(T alpha, const DistMat<T>& A, DistMat<T>& B) {
+    Grid& g = *A.grid;
+    cudaStream_t s = B.stream;
+    if (A.spec.height != B.spec.height || A.spec.width != B.spec.width)
+        throw EngineError(ELB200_ERR_ARG, "AxpyContract: nonconformal dimensions");
+    ContractPlan plan = plan_contract(g.shape, g.me, A.spec, B.spec);
+    if (!plan.valid) {
+        // Same distributions but different alignment: realign every partial-sum layer first
+        // (the reference's unaligned branches do this with a SendRecv, AxpyContract.hpp:219-261).
+        const bool col_ok = A.spec.col == B.spec.col || A.spec.col == STAR;
+        const bool row_ok = A.spec.row == B.spec.row || A.spec.row == STAR;
+        if (!col_ok || !row_ok) throw EngineError(ELB200_ERR_ARG, "AxpyContract: incompatible distributions");
+        DistMat<T> A2(g, A.spec.col, A.spec.row, s);
+        A2.Align(A.spec.col == B.spec.col ? B.spec.col_align : 0, A.spec.row == B.spec.row ? B.spec.row_align : 0);
+        Copy(A, A2);
+        plan = plan_contract(g.shape, g.me, A2.spec, B.spec);
+        if (!plan.valid) throw EngineError(ELB200_ERR_ARG, "AxpyContract: realignment failed");
+        AxpyContract(alpha, A2, B);
+        return;
+    }
+    if (A.spec.height == 0 || A.spec.width == 0) return;
+    T* Abuf = const_cast<T*>(A.buf);
+    if (plan.group == 1) {
+        const elb200_segment& a = plan.packs[0].seg;
+        Dev<T>::axpy2d(a.rows, a.cols, alpha, A.buf + a.row0 + a.col0 * A.ldim, a.row_step, a.col_step * A.ldim,
+                       B.buf, 1, B.ldim, s);
+        return;
+    }
+    ncclComm_t comm = g.comm_for(plan.comm_dist);
+    if (!comm) throw EngineError(ELB200_ERR_STATE, "AxpyContract: grid has no NCCL communicator");
+    Scratch<T> stage(int64_t(plan.group + 1) * plan.portion, s);
+    run_lattice<T>(ELB200_PACK, plan.packs, Abuf, A.ldim, stage.p, T(0), s);
+    T* recv = stage.p + int64_t(plan.group) * plan.portion;
+    nccl_check(ncclReduceScatter(stage.p, recv, size_t(plan.portion), Dev<T>::nccl, ncclSum, comm, s), "ncclReduceScatter");
+    elb200_segment u = plan.unpack;
+    u.buf_offset = int64_t(plan.group) * plan.portion;
+    if (u.rows > 0 && u.cols > 0) Dev<T>::lattice(ELB200_UNPACK_AXPY, 1, &u, B.buf, B.ldim, stage.p, alpha, s);
+}
+
+// B = sum over A's replicas (reference Contract, level1/Contract.hpp:14-99)
+template <typename T>
+void Contract(const DistMat<T>& A, DistMat<T>& B) {
+    if (A.spec.col == B.spec.col && !B.col_constrained) B.spec.col_align = A.spec.col_align;
+    if (A.spec.row == B.spec.row && !B.row_constrained) B.spec.row_align = A.spec.row_align;
+    B.Resize(A.spec.height, A.spec.width);
+    Zero(B);
+    AxpyContract(T(1), A, B);
+}
+
+// B += alpha * (sum over A's replicas)^T (reference TransposeAxpyContract.hpp:14-47)
+template <typename T>
+void TransposeAxpyContract(T alpha, const DistMat<T>& A, DistMat<T>& B) {
+    Grid& g = *A.grid;
+    cudaStream_t s = B.stream;
+    DistMat<T> sum(g, B.spec.row, B.spec.col, s);
+    sum.Align(B.spec.row_align, B.spec.col_align);
+    if (A.spec.col == sum.spec.col && A.spec.row == sum.spec.row) Copy(A, sum);
+    else Contract(A, sum);
+    // B(rows x cols) += alpha * sum(cols x rows)^T on the local matrices
+    Dev<T>::axpy2d_transpose(B.lh(), B.lw(), alpha, sum.buf, sum.ldim, B.buf, B.ldim, s);
+}
+
+#define ELB_INST(T)                                                          \
+    template void Copy<T>(const DistMat<T>&, DistMat<T>&);                   \
+    template void TransposeCopy<T>(const DistMat<T>&, DistMat<T>&);          \
+    template void AxpyContract<T>(T, const DistMat<T>&, DistMat<T>&);        \
+    template void Contract<T>(const DistMat<T>&, DistMat<T>&);               \
+    template void TransposeAxpyContract<T>(T, const DistMat<T>&, DistMat<T>&); \
+    template void Axpy<T>(T, const DistMat<T>&, DistMat<T>&);                \
+    template void Scale<T>(T, DistMat<T>&);                                  \
+    template void Zero<T>(DistMat<T>&);
+ELB_INST(float)
+ELB_INST(double)
+#undef ELB_INST
+
+}  // namespace elb

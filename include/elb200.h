@@ -159,6 +159,125 @@ int elb200_lattice_f32(int mode, int nseg, const elb200_segment* segs, float* M,
 int elb200_lattice_f64(int mode, int nseg, const elb200_segment* segs, double* M, int64_t ldm,
                        double* buf, double alpha, void* stream);
 
+
+/* ------------------------------------------------------------------------------------------
+ * Redistribution planner (pure host code; callable without a GPU).
+ * For an r x c grid (COLUMN_MAJOR: VC rank = mc + r*mr, reference src/core/Grid.cpp:147-148) and
+ * two element-cyclic distribution specs, returns what THIS rank packs, sends, receives and
+ * unpacks for B = A (elb200_plan_copy) or B += sum-over-replicas(A) (elb200_plan_contract).
+ * Distributions: 0=MC 1=MR 2=VC 3=VR 4=STAR (reference El::Dist, include/El/core/types.hpp).
+ * ---------------------------------------------------------------------------------------- */
+typedef struct elb200_dist_spec {
+    int col_dist, row_dist;
+    int64_t col_align, row_align;
+    int64_t height, width;
+} elb200_dist_spec;
+
+typedef struct elb200_message {
+    int peer;   /* VC rank of the other side */
+    int valid;  /* 0: slot unused */
+    elb200_segment seg;
+} elb200_message;
+
+typedef struct elb200_copy_plan {
+    int kind;       /* 0 local, 1 allgather, 2 grouped send/recv */
+    int comm_dist;  /* allgather: communicator (0=MC column comm, 1=MR row comm, 2=VC world) */
+    int64_t portion;
+    int nsend, nrecv, has_self;
+    int64_t send_elems, recv_elems;
+    elb200_message self_send, self_recv;
+    elb200_message sends[ELB200_MAX_SEGMENTS], recvs[ELB200_MAX_SEGMENTS];
+} elb200_copy_plan;
+
+typedef struct elb200_contract_plan {
+    int valid, comm_dist, group, my_index;
+    int64_t portion;
+    int npack;
+    elb200_message packs[ELB200_MAX_SEGMENTS];
+    elb200_segment unpack;
+} elb200_contract_plan;
+
+int elb200_plan_copy(int grid_height, int grid_width, int vc_rank, const elb200_dist_spec* A,
+                     const elb200_dist_spec* B, elb200_copy_plan* out);
+int elb200_plan_contract(int grid_height, int grid_width, int vc_rank, const elb200_dist_spec* A,
+                         const elb200_dist_spec* B, elb200_contract_plan* out);
+/* Shift_/Length_/MaxLength_ (include/El/core/indexing/impl.hpp:33-66,244-245) and
+ * Grid::DefaultHeight (src/core/Grid.cpp:57-63), exported for the parity tests. */
+int64_t elb200_shift(int64_t rank, int64_t align, int64_t stride);
+int64_t elb200_length(int64_t n, int64_t shift, int64_t stride);
+int64_t elb200_max_length(int64_t n, int64_t stride);
+int elb200_default_grid_height(int grid_size);
+/* GEMM_DEFAULT heuristic (src/blas_like/level3/Gemm/NN.hpp:572-600); returns a GemmAlgorithm. */
+int elb200_gemm_resolve_alg(int transA, int transB, int64_t m, int64_t n, int64_t k, int alg);
+
+/* ------------------------------------------------------------------------------------------
+ * Handle API over the host engine: what the C++ facade (include/El.hpp) and the Python mirror
+ * (elemental_b200/el.py) bind. One process per GPU; every rank of a grid calls collectively and
+ * in the same order (same contract as the reference, SURVEY.md 8(b) "Threading").
+ *   elb200_grid_t  <-> El::Grid        (include/El/core/Grid.hpp:15-140, src/core/Grid.cpp:74-223)
+ *   elb200_dm_t    <-> El::DistMatrix<T,U,V,ELEMENT,Device::GPU>
+ *                      (include/El/core/DistMatrix/ElementMatrix.hpp, AbstractDistMatrix.hpp)
+ * ---------------------------------------------------------------------------------------- */
+typedef struct elb200_grid_s* elb200_grid_t;
+typedef struct elb200_dm_s* elb200_dm_t;
+enum { ELB200_F32 = 0, ELB200_F64 = 1 };
+#define ELB200_UNIQUE_ID_BYTES 128
+
+/* NCCL bootstrap: rank 0 calls elb200_unique_id and ships the 128 bytes to the other ranks by any
+ * side channel (the reference gets its communicator from MPI, src/core/imports/mpi.cpp:80-91). */
+int elb200_unique_id(void* out128);
+/* height x width grid, this process is VC rank `vc_rank` and drives CUDA device `device`.
+ * id128 may be NULL when height*width == 1. */
+int elb200_grid_create(int height, int width, int vc_rank, const void* id128, int device,
+                       elb200_grid_t* out);
+int elb200_grid_destroy(elb200_grid_t g);
+int elb200_grid_info(elb200_grid_t g, int* height, int* width, int* vc_rank, int* mc_rank,
+                     int* mr_rank);
+void* elb200_grid_stream(elb200_grid_t g); /* the grid's compute stream (cudaStream_t) */
+int elb200_grid_sync(elb200_grid_t g);     /* cudaStreamSynchronize on it */
+
+/* El::Blocksize / SetBlocksize / PushBlocksizeStack / PopBlocksizeStack
+ * (src/blas_like/blocksizes.cpp:35-67). */
+int elb200_blocksize(void);
+void elb200_set_blocksize(int nb);
+void elb200_push_blocksize(int nb);
+void elb200_pop_blocksize(void);
+
+typedef struct elb200_dm_info_t {
+    int dtype, col_dist, row_dist, is_view;
+    int64_t height, width, col_align, row_align, col_shift, row_shift;
+    int64_t col_stride, row_stride, local_height, local_width, ldim;
+    void* buffer; /* device pointer to the local column-major matrix */
+} elb200_dm_info_t;
+
+int elb200_dm_create(elb200_grid_t g, int dtype, int col_dist, int row_dist, elb200_dm_t* out);
+int elb200_dm_destroy(elb200_dm_t a);
+int elb200_dm_info(elb200_dm_t a, elb200_dm_info_t* out);
+int elb200_dm_align(elb200_dm_t a, int64_t col_align, int64_t row_align);
+int elb200_dm_align_with(elb200_dm_t a, elb200_dm_t other);
+int elb200_dm_resize(elb200_dm_t a, int64_t height, int64_t width);
+int elb200_dm_attach(elb200_dm_t a, int64_t height, int64_t width, int64_t col_align,
+                     int64_t row_align, void* device_buffer, int64_t ldim);
+int elb200_dm_view(elb200_dm_t a, int64_t i0, int64_t i1, int64_t j0, int64_t j1,
+                   elb200_dm_t* out);
+/* B = A for any pair of the 11 distributions (DistMatrix::operator=). */
+int elb200_dm_copy(elb200_dm_t A, elb200_dm_t B);
+int elb200_dm_transpose(elb200_dm_t A, elb200_dm_t B); /* B = A^T (El::Transpose) */
+int elb200_dm_axpy(double alpha, elb200_dm_t X, elb200_dm_t Y);
+int elb200_dm_scale(double alpha, elb200_dm_t A);
+int elb200_dm_zero(elb200_dm_t A);
+int elb200_dm_axpy_contract(double alpha, elb200_dm_t A, elb200_dm_t B);
+int elb200_dm_contract(elb200_dm_t A, elb200_dm_t B);
+int elb200_dm_transpose_axpy_contract(double alpha, elb200_dm_t A, elb200_dm_t B);
+/* El::LocalGemm (src/blas_like/level3/Gemm.cpp:318-426) */
+int elb200_dm_local_gemm(int transA, int transB, double alpha, elb200_dm_t A, elb200_dm_t B,
+                         double beta, elb200_dm_t C);
+/* El::Gemm(orientA, orientB, alpha, A, B, beta, C, alg) (src/blas_like/level3/Gemm.cpp:273-302).
+ * alg: El::GemmAlgorithm 0=DEFAULT 1=SUMMA_A 2=SUMMA_B 3=SUMMA_C 4=SUMMA_DOT 5=CANNON
+ *      6..8 = the _MS twins (include/El/blas_like/level3.hpp:22-35). */
+int elb200_dist_gemm(int transA, int transB, double alpha, elb200_dm_t A, elb200_dm_t B,
+                     double beta, elb200_dm_t C, int alg);
+
 #ifdef __cplusplus
 } /* extern "C" */
 #endif

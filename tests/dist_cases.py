@@ -1,0 +1,193 @@
+"""Shared distributed parity cases, run by every rank of a grid (1 x 1 inside pytest, r x c under
+torchrun via tests/dist_worker.py). Each case builds the same seeded GLOBAL matrices on every rank,
+loads this rank's entries, runs the CUDA path through the C ABI handle API, and compares this
+rank's local result with the oracle's (oracle.dist / oracle.gemm over virtual ranks).
+
+The procedure mirrors the reference's own tests:
+  * tests/core/DistMatrix.cpp:12-76  — every (U,V) <- (U',V') assignment must equal the [*,*]
+    gather exactly (bit-exact here too);
+  * tests/blas_like/BasicGemm.cpp:134-235 — GPU Gemm vs CPU recomputation (alpha=2, beta=3);
+  * tests/blas_like/Gemm.cpp:52-231 — orientations x GemmAlgorithm x alignments.
+"""
+from __future__ import annotations
+
+import itertools
+
+import numpy as np
+import torch
+
+from elemental_b200 import el
+from oracle import dist as OD
+from oracle import gemm as OG
+
+NPDT = {torch.float32: np.float32, torch.float64: np.float64}
+
+
+def _grid_oracle(grid) -> OD.Grid:
+    return OD.Grid(grid.Height(), grid.Width())
+
+
+def check_redistributions(grid, dtype=torch.float64, m=23, n=17, pairs=None, seed=0) -> int:
+    """B = A for (U,V) -> (U',V') with random alignments; exact equality of local matrices."""
+    og = _grid_oracle(grid)
+    rng = np.random.default_rng(seed)  # same stream on every rank
+    npdt = NPDT[dtype]
+    G = np.asfortranarray(rng.uniform(-1, 1, (m, n)).astype(npdt))
+    count = 0
+    for (U, V), (U2, V2) in (pairs or itertools.product(OD.PAIRS, OD.PAIRS)):
+        ca, ra = int(rng.integers(og.stride(U))), int(rng.integers(og.stride(V)))
+        ca2, ra2 = int(rng.integers(og.stride(U2))), int(rng.integers(og.stride(V2)))
+        A = el.DistMatrix(grid, U, V, dtype).Align(ca, ra).from_global(G)
+        B = el.DistMatrix(grid, U2, V2, dtype).Align(ca2, ra2)
+        el.Copy(A, B)
+        got = B.get_local()
+        spec = OD.Spec(U2, V2, ca2, ra2, m, n)
+        exp = OD.local_of(G, spec, og, grid.Rank())
+        assert got.shape == exp.shape, ((U, V), (U2, V2), got.shape, exp.shape)
+        assert np.array_equal(got, exp), f"Copy [{OD.NAMES[U]},{OD.NAMES[V]}]->[{OD.NAMES[U2]},{OD.NAMES[V2]}] differs"
+        # unconstrained target adopts compatible alignments and must still hold the right entries
+        B2 = el.DistMatrix(grid, U2, V2, dtype)
+        el.Copy(A, B2)
+        spec2 = OD.Spec(U2, V2, B2.ColAlign(), B2.RowAlign(), m, n)
+        assert np.array_equal(B2.get_local(), OD.local_of(G, spec2, og, grid.Rank()))
+        count += 1
+    return count
+
+
+def check_views_and_transpose(grid, dtype=torch.float32) -> None:
+    og = _grid_oracle(grid)
+    npdt = NPDT[dtype]
+    rng = np.random.default_rng(1)
+    G = np.asfortranarray(rng.uniform(-1, 1, (29, 31)).astype(npdt))
+    A = el.DistMatrix(grid, el.MC, el.MR, dtype).Align(1 % og.r, 2 % og.c).from_global(G)
+    V = A.View(3, 20, 5, 29)
+    sub = G[3:20, 5:29]
+    spec = OD.Spec(OD.MC, OD.MR, V.ColAlign(), V.RowAlign(), *sub.shape)
+    assert np.array_equal(V.get_local(), OD.local_of(sub, spec, og, grid.Rank()))
+    for (U2, V2) in OD.PAIRS:
+        B = el.DistMatrix(grid, U2, V2, dtype)
+        el.Transpose(V, B)
+        spec = OD.Spec(U2, V2, B.ColAlign(), B.RowAlign(), sub.shape[1], sub.shape[0])
+        assert np.array_equal(B.get_local(), OD.local_of(np.asfortranarray(sub.T), spec, og, grid.Rank()))
+
+
+def check_contractions(grid, dtype=torch.float64) -> None:
+    """AxpyContract / Contract / TransposeAxpyContract: every rank holds a DIFFERENT partial sum;
+    the result is the oracle's sum over ranks (order-dependent rounding -> tolerance 4 ulp * p)."""
+    og = _grid_oracle(grid)
+    npdt = NPDT[dtype]
+    p, me = og.p, grid.Rank()
+    m, n = 19, 14
+    rng = np.random.default_rng(2)
+    eps = np.finfo(npdt).eps
+    cases = [((OD.MC, OD.STAR), (OD.MC, OD.MR)), ((OD.STAR, OD.MR), (OD.MC, OD.MR)),
+             ((OD.STAR, OD.STAR), (OD.MC, OD.MR)), ((OD.MR, OD.STAR), (OD.MR, OD.MC)),
+             ((OD.STAR, OD.MC), (OD.MR, OD.MC)), ((OD.MC, OD.MR), (OD.MC, OD.MR))]
+    for (UA, VA), (UB, VB) in cases:
+        for aligned in (True, False):
+            caB, raB = int(rng.integers(og.stride(UB))), int(rng.integers(og.stride(VB)))
+            caA = caB if (UA == UB and aligned) else int(rng.integers(og.stride(UA)))
+            raA = raB if (VA == VB and aligned) else int(rng.integers(og.stride(VA)))
+            specA = OD.Spec(UA, VA, caA, raA, m, n)
+            parts = [np.asfortranarray(rng.uniform(-1, 1, specA.local_shape(og, q)).astype(npdt)) for q in range(p)]
+            GB = np.asfortranarray(rng.uniform(-1, 1, (m, n)).astype(npdt))
+            A = el.DistMatrix(grid, UA, VA, dtype).Align(caA, raA).Resize(m, n)
+            A.set_local(parts[me])
+            B = el.DistMatrix(grid, UB, VB, dtype).Align(caB, raB).from_global(GB)
+            el.AxpyContract(0.5, A, B)
+            oA = OD.VDM(og, specA, [x.copy() for x in parts])
+            oB = OD.VDM.from_global(og, GB, UB, VB, caB, raB)
+            OD.axpy_contract(npdt(0.5), oA, oB)
+            assert np.allclose(B.get_local(), oB.loc[me], rtol=0, atol=4 * p * eps), ((UA, VA), (UB, VB), aligned)
+    # Contract and TransposeAxpyContract on the SUMMA_B / SUMMA_A temporaries
+    specA = OD.Spec(OD.MR, OD.STAR, 0, 0, n, m)
+    parts = [np.asfortranarray(rng.uniform(-1, 1, specA.local_shape(og, q)).astype(npdt)) for q in range(p)]
+    A = el.DistMatrix(grid, el.MR, el.STAR, dtype).Align(0, 0).Resize(n, m)
+    A.set_local(parts[me])
+    S = el.DistMatrix(grid, el.MR, el.MC, dtype)
+    el.Contract(A, S)
+    total = OD.VDM(og, specA, parts).contributions()
+    exp = OD.local_of(total, OD.Spec(OD.MR, OD.MC, S.ColAlign(), S.RowAlign(), n, m), og, me)
+    assert np.allclose(S.get_local(), exp, rtol=0, atol=4 * p * eps)
+    GC = np.asfortranarray(rng.uniform(-1, 1, (m, n)).astype(npdt))
+    Cm = el.DistMatrix(grid, el.MC, el.MR, dtype).Align(1 % og.r, 1 % og.c).from_global(GC)
+    el.TransposeAxpyContract(2.0, A, Cm)
+    expC = OD.local_of(GC + npdt(2.0) * total.T, OD.Spec(OD.MC, OD.MR, 1 % og.r, 1 % og.c, m, n), og, me)
+    assert np.allclose(Cm.get_local(), expC, rtol=0, atol=8 * p * eps)
+
+
+def gemm_case(grid, dtype, oa, ob, alg, m, n, k, alpha=2.0, beta=3.0, aligns=None, nb=None, dists=None):
+    """One El::Gemm call vs the oracle; returns the relative Frobenius error of the global result
+    restricted to this rank's entries, and the bound."""
+    og = _grid_oracle(grid)
+    npdt = NPDT[dtype]
+    me = grid.Rank()
+    A = OG.uniform_matrix(*((m, k) if oa == 0 else (k, m)), 101, npdt, 0.0, 1.0)
+    B = OG.uniform_matrix(*((k, n) if ob == 0 else (n, k)), 102, npdt, 0.0, 1.0)
+    C = OG.uniform_matrix(m, n, 103, npdt, 0.0, 1.0)
+    aligns = aligns or ((0, 0), (0, 0), (0, 0))
+    dists = dists or ((el.MC, el.MR),) * 3
+    dA = el.DistMatrix(grid, *dists[0], dtype).Align(aligns[0][0] % og.stride(dists[0][0]), aligns[0][1] % og.stride(dists[0][1])).from_global(A)
+    dB = el.DistMatrix(grid, *dists[1], dtype).Align(aligns[1][0] % og.stride(dists[1][0]), aligns[1][1] % og.stride(dists[1][1])).from_global(B)
+    dC = el.DistMatrix(grid, *dists[2], dtype).Align(aligns[2][0] % og.stride(dists[2][0]), aligns[2][1] % og.stride(dists[2][1])).from_global(C)
+    if nb:
+        el.PushBlocksizeStack(nb)
+    try:
+        el.Gemm(oa, ob, alpha, dA, dB, beta, dC, alg)
+    finally:
+        if nb:
+            el.PopBlocksizeStack()
+    got = dC.get_local()
+    ref = OG.gemm_global(oa, ob, alpha, A, B, beta, C, np.longdouble)
+    spec = OD.Spec(dists[2][0], dists[2][1], dC.ColAlign(), dC.RowAlign(), m, n)
+    ref_loc = OD.local_of(ref, spec, og, me)
+    # error measured against the norm of the whole result (the reference's Frobenius criterion)
+    num = float(np.linalg.norm(got.astype(np.longdouble) - ref_loc))
+    den = float(np.linalg.norm(ref)) / np.sqrt(og.p)
+    return num / max(den, 1e-300), OG.gemm_tolerance(npdt, k)
+
+
+def check_gemm_variants(grid, dtype, shapes=((70, 50, 90),), algs=(1, 2, 3, 4, 0), nb=16) -> int:
+    og = _grid_oracle(grid)
+    cnt = 0
+    for (m, n, k) in shapes:
+        for oa, ob in itertools.product((0, 1), (0, 1)):
+            for alg in algs:
+                for al in (((0, 0), (0, 0), (0, 0)), ((1, 2), (0, 1), (1, 0))):
+                    err, tol = gemm_case(grid, dtype, oa, ob, alg, m, n, k, aligns=al, nb=nb)
+                    assert err <= tol, f"Gemm oa={oa} ob={ob} alg={alg} {m}x{n}x{k} aligns={al}: {err:.3e} > {tol:.3e}"
+                    cnt += 1
+    return cnt
+
+
+def check_gemm_proxies(grid, dtype) -> None:
+    """Inputs that are not [MC,MR] go through the read / read-write proxies (Proxy.hpp:236-320)."""
+    combos = [((el.STAR, el.VC), (el.STAR, el.STAR), (el.MC, el.MR)),
+              ((el.VC, el.STAR), (el.MR, el.MC), (el.STAR, el.VR)),
+              ((el.STAR, el.STAR), (el.MC, el.MR), (el.MR, el.MC))]
+    for d in combos:
+        for alg in (0, 3, 4):
+            err, tol = gemm_case(grid, dtype, 0, 0, alg, 45, 37, 64, dists=d, nb=16)
+            assert err <= tol, (d, alg, err, tol)
+
+
+def run_all(grid, heavy=False) -> dict:
+    out = {}
+    out["redist_f64"] = check_redistributions(grid, torch.float64)
+    out["redist_f32"] = check_redistributions(grid, torch.float32, m=64, n=48, seed=4,
+                                              pairs=[((OD.MC, OD.MR), t) for t in OD.PAIRS] + [(t, (OD.MC, OD.MR)) for t in OD.PAIRS])
+    check_views_and_transpose(grid, torch.float32)
+    check_views_and_transpose(grid, torch.float64)
+    check_contractions(grid, torch.float64)
+    check_contractions(grid, torch.float32)
+    out["gemm_f64"] = check_gemm_variants(grid, torch.float64)
+    out["gemm_f32"] = check_gemm_variants(grid, torch.float32)
+    check_gemm_proxies(grid, torch.float64)
+    check_gemm_proxies(grid, torch.float32)
+    if heavy:
+        # panels wider than one algorithmic block, ragged edges, default blocksize
+        for dt in (torch.float32, torch.float64):
+            for (oa, ob, alg) in ((0, 0, 3), (0, 1, 3), (1, 0, 1), (1, 1, 2), (0, 0, 4)):
+                err, tol = gemm_case(grid, dt, oa, ob, alg, 1100, 900, 2500, alpha=0.5, beta=-0.5)
+                assert err <= tol, (dt, oa, ob, alg, err, tol)
+    return out

@@ -1,0 +1,106 @@
+"""GPU parity of the distributed layer through the handle C ABI (Grid / DistMatrix / Gemm).
+
+Single process = 1 x 1 grid (every redistribution degenerates to local lattice copies, every
+SUMMA variant to local GEMMs + local contractions). With >= 2 visible GPUs the same cases run on
+1x2 / 2x1 / 2x2 ... grids under torchrun (tests/dist_worker.py), one process per GPU over NCCL.
+"""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_redistributions_1x1(grid1):
+    from tests import dist_cases as dc
+    assert dc.check_redistributions(grid1, torch.float64) == 121
+    dc.check_views_and_transpose(grid1, torch.float32)
+    dc.check_views_and_transpose(grid1, torch.float64)
+
+
+def test_contractions_1x1(grid1):
+    from tests import dist_cases as dc
+    dc.check_contractions(grid1, torch.float64)
+    dc.check_contractions(grid1, torch.float32)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+def test_gemm_all_variants_1x1(grid1, dtype):
+    from tests import dist_cases as dc
+    assert dc.check_gemm_variants(grid1, dtype) == 40
+    dc.check_gemm_proxies(grid1, dtype)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+def test_gemm_reference_driver_config(grid1, dtype):
+    """BASELINE config C1 shape class (tests/blas_like/Gemm.cpp defaults: m=n=k=2000 is too slow
+    for the oracle in float128, so 600) with the driver's blocksize 96 and BasicGemm's alpha=2,
+    beta=3, over every orientation and SUMMA variant."""
+    from tests import dist_cases as dc
+    for oa in (0, 1):
+        for ob in (0, 1):
+            for alg in (1, 2, 3, 4):
+                err, tol = dc.gemm_case(grid1, dtype, oa, ob, alg, 600, 500, 700, nb=96)
+                assert err <= tol, (oa, ob, alg, err, tol)
+
+
+def test_gemm_errors(grid1):
+    from elemental_b200 import el
+    from elemental_b200._lib import Elb200Error
+    A = el.DistMatrix(grid1, dtype=torch.float32).Resize(8, 9)
+    B = el.DistMatrix(grid1, dtype=torch.float32).Resize(10, 7)  # nonconformal with A
+    C = el.DistMatrix(grid1, dtype=torch.float32).Resize(8, 7)
+    with pytest.raises(Elb200Error):  # reference: LogicError("Nonconformal matrices"), Gemm/NN.hpp:560-568
+        el.Gemm(0, 0, 1.0, A, B, 0.0, C)
+    B.Resize(9, 7)
+    with pytest.raises(Elb200Error):  # Cannon_NN rejects GPU matrices (Gemm/NN.hpp:30-31)
+        el.Gemm(0, 0, 1.0, A, B, 0.0, C, el.GEMM_CANNON)
+    D = el.DistMatrix(grid1, dtype=torch.float64).Resize(8, 7)
+    with pytest.raises(Elb200Error):
+        el.Gemm(0, 0, 1.0, A, B, 0.0, D)
+
+
+def test_gemm_roundtrip_property_large(grid1):
+    """Size-independent property at a bench-class size (n=4096 fp32): Gemm is linear in alpha and
+    additive over a split of k — C(k) == C(k[:h]) + C(k[h:]) within the fp32 bound."""
+    from elemental_b200 import el
+    from oracle import gemm as OG
+    n, h = 4096, 1536
+    gen = torch.Generator(device="cuda").manual_seed(9)
+    with torch.cuda.stream(grid1.stream):
+        A = el.DistMatrix(grid1, dtype=torch.float32).Resize(n, n)
+        B = el.DistMatrix(grid1, dtype=torch.float32).Resize(n, n)
+        A.Matrix().copy_((torch.rand((n, n), device="cuda", generator=gen) - 0.5) * 0.2)
+        B.Matrix().copy_((torch.rand((n, n), device="cuda", generator=gen) - 0.5) * 0.2)
+    C1 = el.DistMatrix(grid1, dtype=torch.float32).Resize(n, n)
+    C2 = el.DistMatrix(grid1, dtype=torch.float32).Resize(n, n)
+    el.Gemm(0, 0, 0.5, A, B, 0.0, C1, el.GEMM_SUMMA_C)
+    el.Gemm(0, 0, 0.5, A.View(0, n, 0, h), B.View(0, h, 0, n), 0.0, C2, el.GEMM_SUMMA_C)
+    el.Gemm(0, 0, 0.5, A.View(0, n, h, n), B.View(h, n, 0, n), 1.0, C2, el.GEMM_SUMMA_A)
+    grid1.sync()
+    with torch.cuda.stream(grid1.stream):
+        c1, c2 = C1.Matrix().double(), C2.Matrix().double()
+        ref = 0.5 * (A.Matrix().double() @ B.Matrix().double())
+        e12 = float(torch.linalg.norm(c1 - c2) / torch.linalg.norm(ref))
+        e1 = float(torch.linalg.norm(c1 - ref) / torch.linalg.norm(ref))
+    grid1.sync()
+    tol = OG.gemm_tolerance(np.float32, n)
+    assert e1 <= tol and e12 <= 2 * tol, (e1, e12, tol)
+
+
+@pytest.mark.parametrize("nproc,height", [(2, 1), (2, 2), (4, 2), (8, 2)])
+def test_multi_gpu_grids(nproc, height):
+    if torch.cuda.device_count() < nproc:
+        pytest.skip(f"needs {nproc} GPUs")
+    port = 29600 + nproc * 10 + height
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+           "--master-addr", "127.0.0.1", "--master-port", str(port),
+           os.path.join(ROOT, "tests", "dist_worker.py"), "--height", str(height)]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT)
+    assert res.returncode == 0, res.stdout[-4000:] + res.stderr[-4000:]
+    assert "DIST_WORKER_PASS" in res.stdout
