@@ -1,0 +1,349 @@
+#!/usr/bin/env python
+"""bench.py — El::Gemm TFLOP/s, the reference's headline metric (BASELINE.json), on B200.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--dtype f32|f64] [--impl ours|reference]
+  torchrun --nnodes=1 --nproc-per-node N ... bench.py --gpus N --steps K --warmup W
+
+One "step" = one El::Gemm(NORMAL, NORMAL, 0.5, A, B, -0.5, C, GEMM_SUMMA_C) over [MC,MR] DistMatrices
+on the default r x c grid (Grid::DefaultHeight), inputs Uniform(-0.1, 0.1) resident in HBM
+(reference drivers: tests/blas_like/Gemm_Suite.cpp:153-248; TFLOP/s = 2 m n k / t, Gemm.cpp:120).
+N = 1 is BASELINE config[1] (fp32 SUMMA_C n=16384 on one B200). For N > 1 the per-GPU work is held
+fixed (weak scaling): n = 16384 * N^(1/3) rounded to 512, i.e. n = 32768 at 8 GPUs — the metric's size.
+
+The JSON line carries, beside the base contract: `roofline` (the local GEMM kernel timed with CUDA
+events inside the timed region), `cpu_baseline` (the reference's CPU path on this box's host cores,
+bounded sample), `e2e` (same call with host buffers, H2D/D2H inside the timed region), `clocks`,
+`gpu_launches`.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "El::Gemm TFLOP/s"
+UNIT = "TFLOP/s"
+BASE_N = 16384
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--dtype", choices=["f32", "f64"], default="f32")
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--n", type=int, default=0, help="override the matrix size (diagnostics only)")
+    ap.add_argument("--alg", type=int, default=3, help="El::GemmAlgorithm (3 = GEMM_SUMMA_C)")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    return ap.parse_args()
+
+
+def workload_n(n_gpus: int, override: int = 0) -> int:
+    if override:
+        return override
+    return int(round(BASE_N * n_gpus ** (1.0 / 3.0) / 512.0)) * 512
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return {"hbm_gbs": p["hbm_gbs"], "bf16": p["bf16_tflops"], "bf16_sustained": p.get("bf16_tflops_sustained", p["bf16_tflops"]),
+                "source": "measured (MEASURED_PEAKS.json)"}
+    return {"hbm_gbs": 6650.0, "bf16": 1590.0, "bf16_sustained": 1400.0, "source": "fallback (B200_PROFILING.md)"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms DURING the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx, self.proc, self.lines = gpu_index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=3)
+        except Exception:
+            self.proc.kill()
+        sm, mx, pw, reasons = [], [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "power_w_max": max(pw), "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------ CPU reference arm
+def cpu_reference_rate(dtype: str, n_sample: int, reps: int = 1):
+    """The reference's CPU path on this box's host cores, bounded sample. Uses the reference's own
+    code compiled from /root/reference (oracle/_ref/gemm_ref) when that binary exists, else the
+    oracle's restatement of SUMMA_NNC (oracle/gemm.py) over a 1 x 1 grid with nb = 128.
+    Returns (tflops, info dict)."""
+    import numpy as np
+    ref_bin = os.path.join(ROOT, "oracle", "_ref", "gemm_ref")
+    cores = os.cpu_count() or 1
+    if os.path.exists(ref_bin):
+        env = dict(os.environ)
+        libdir = os.path.join(ROOT, "oracle", "_ref")
+        env["LD_LIBRARY_PATH"] = libdir + ":" + env.get("LD_LIBRARY_PATH", "")
+        env.setdefault("OPENBLAS_NUM_THREADS", str(cores))
+        best = None
+        for _ in range(reps):
+            out = subprocess.run([ref_bin, "--bench", dtype, str(n_sample)], capture_output=True, text=True, env=env, timeout=1200)
+            for ln in out.stdout.splitlines():
+                if ln.startswith("REF_GEMM_SECONDS"):
+                    t = float(ln.split()[1])
+                    best = t if best is None else min(best, t)
+        if best:
+            return 2.0 * n_sample ** 3 / best / 1e12, {"kind": "reference", "cores": cores,
+                    "sample": f"reference El::Gemm<{dtype},Device::CPU> SUMMA_C n={n_sample}, 1x1 grid, nb=128, OpenBLAS threads={env['OPENBLAS_NUM_THREADS']}"}
+    from oracle import gemm as OG
+    npdt = np.float32 if dtype == "f32" else np.float64
+    A = OG.uniform_matrix(n_sample, n_sample, 1, npdt)
+    B = OG.uniform_matrix(n_sample, n_sample, 2, npdt)
+    Cm = OG.uniform_matrix(n_sample, n_sample, 3, npdt)
+    best = None
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        OG.summa_nnc_1x1(0.5, A, B, -0.5, Cm, nb=128)
+        t = time.perf_counter() - t0
+        best = t if best is None else min(best, t)
+    return 2.0 * n_sample ** 3 / best / 1e12, {"kind": "port", "cores": cores,
+            "sample": f"oracle restatement of SUMMA_NNC (numpy/OpenBLAS local gemm) n={n_sample}, 1x1 grid, nb=128"}
+
+
+def pick_cpu_sample(dtype: str) -> int:
+    """Largest n in {2048, 4096, 8192} whose sample should stay within ~10-30 s on this host."""
+    import numpy as np
+    npdt = np.float32 if dtype == "f32" else np.float64
+    x = np.ones((1024, 1024), dtype=npdt)
+    t0 = time.perf_counter(); (x @ x); (x @ x); dt = (time.perf_counter() - t0) / 2
+    rate = 2.0 * 1024 ** 3 / max(dt, 1e-6)  # flop/s of this host's BLAS on a small product
+    for n in (8192, 4096, 2048):
+        if 2.0 * n ** 3 / rate * 1.6 < 25.0:
+            return n
+    return 2048
+
+
+def run_reference(args) -> int:
+    """--impl reference: the reference's CPU implementation of the path on the host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    n_full = workload_n(args.gpus, args.n)
+    n_s = pick_cpu_sample(args.dtype)
+    for _ in range(args.warmup if args.warmup < 2 else 1):
+        cpu_reference_rate(args.dtype, min(n_s, 2048))
+    vals, t0 = [], time.perf_counter()
+    info = {}
+    for _ in range(args.steps):
+        v, info = cpu_reference_rate(args.dtype, n_s)
+        vals.append(v)
+        if time.perf_counter() - t0 > 240:
+            break
+    v = statistics.mean(vals)
+    ms = 2.0 * n_s ** 3 / (v * 1e12) * 1e3
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": len(vals),
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": args.dtype, "data": "synthetic",
+            "config": {"workload": f"El::Gemm {args.dtype} SUMMA_C n={n_full} (NN, alpha=0.5, beta=-0.5); each step = bounded sample n={n_s} of it",
+                       "grid": "1x1 (host cores)"},
+            "cpu_baseline": {"value": v, "unit": UNIT, **info},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def run_ours(args) -> int:
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        print("bench.py: no CUDA device — elemental_b200 has no CPU fallback", file=sys.stderr)
+        return 2
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+    from elemental_b200 import el
+    from elemental_b200._lib import lib
+
+    n_gpus = world
+    n = workload_n(n_gpus, args.n)
+    tdt = torch.float32 if args.dtype == "f32" else torch.float64
+    esz = 4 if args.dtype == "f32" else 8
+    grid = el.Grid(device=local)
+    A = el.DistMatrix(grid, el.MC, el.MR, tdt).Resize(n, n)
+    B = el.DistMatrix(grid, el.MC, el.MR, tdt).Resize(n, n)
+    Cm = el.DistMatrix(grid, el.MC, el.MR, tdt).Resize(n, n)
+    gen = torch.Generator(device=f"cuda:{local}").manual_seed(21 + rank)
+    with torch.cuda.stream(grid.stream):
+        for M in (A, B, Cm):
+            v = M.Matrix()
+            v.copy_((torch.rand(v.shape, device=v.device, dtype=tdt, generator=gen) - 0.5) * 0.2)
+    grid.sync()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step():
+        el.Gemm(el.NORMAL, el.NORMAL, 0.5, A, B, -0.5, Cm, args.alg)
+
+    for _ in range(max(args.warmup, 0)):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    lib.elb200_gemm_profile(1)
+    launches0 = lib.elb200_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(grid.stream)
+    for _ in range(args.steps):
+        step()
+    e1.record(grid.stream)
+    barrier()
+    ms = e0.elapsed_time(e1) / args.steps
+    launches = lib.elb200_launch_count() - launches0
+    lib.elb200_gemm_profile(0)
+    k_ms, k_flop, k_n = C.c_double(), C.c_double(), C.c_int()
+    lib.elb200_gemm_profile_collect(C.byref(k_ms), C.byref(k_flop), C.byref(k_n))
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([ms], device=f"cuda:{local}", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    flops = 2.0 * n ** 3
+    value = flops / (ms * 1e-3) / 1e12
+
+    # ---- e2e: same call with HOST buffers; H2D of A,B,C and D2H of C inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        hosts = []
+        for M in (A, B, Cm):
+            v = M.Matrix()
+            hosts.append(torch.empty(v.shape, dtype=tdt).pin_memory())
+        with torch.cuda.stream(grid.stream):
+            for M, h in zip((A, B, Cm), hosts):
+                h.copy_(M.Matrix(), non_blocking=True)
+        out_h = torch.empty(Cm.Matrix().shape, dtype=tdt).pin_memory()
+        grid.sync()
+        e2e_steps = max(1, min(args.steps, 3))
+
+        def e2e_step():
+            with torch.cuda.stream(grid.stream):
+                for M, h in zip((A, B, Cm), hosts):
+                    M.Matrix().copy_(h, non_blocking=True)
+            step()
+            with torch.cuda.stream(grid.stream):
+                out_h.copy_(Cm.Matrix(), non_blocking=True)
+
+        e2e_step()
+        barrier()
+        e0.record(grid.stream)
+        for _ in range(e2e_steps):
+            e2e_step()
+        e1.record(grid.stream)
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1) / e2e_steps], device=f"cuda:{local}", dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        loc = A.LocalHeight() * A.LocalWidth() * esz
+        e2e = {"value": flops / (float(t.item()) * 1e-3) / 1e12, "unit": UNIT, "ms_per_step": float(t.item()),
+               "h2d_bytes_per_step": 3 * loc * n_gpus, "d2h_bytes_per_step": loc * n_gpus, "steps": e2e_steps}
+
+    if rank == 0:
+        peaks = load_peaks()
+        ach = (k_flop.value / (k_ms.value * 1e-3) / 1e12) if k_ms.value > 0 else None
+        if args.dtype == "f32":
+            # 3xTF32: three tf32 UMMAs per useful MAC, tf32 rate = bf16 rate / 2  =>  bf16 / 6
+            peak = peaks["bf16_sustained"] / 6.0
+            basis = f"{peaks['source']}: sustained bf16 {peaks['bf16_sustained']} TF/s / 6 (tf32 = bf16/2, 3 UMMAs per MAC); burst-derived {peaks['bf16'] / 6.0:.1f}"
+        else:
+            peak = 40.0
+            basis = "B200 FP64 (DMMA == FMA rate) nominal 40 TF/s; no measured fp64 peak in MEASURED_PEAKS.json (cublasDgemm on this pool: 35.9 TF/s, profiles/)"
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", f"r01_ncu_gemm_{args.dtype}_traffic.json")
+        if os.path.exists(tp):
+            with open(tp) as f:
+                traffic = json.load(f).get("dram_bytes_per_launch")
+        roof = {"bound": "tensor", "kernel": "gemm_f32_3xtf32_kernel<cta_group::2>" if args.dtype == "f32" else "gemm_f64_dmma_kernel",
+                "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": (ach / peak) if ach else None, "traffic": traffic,
+                "launches_timed": k_n.value, "kernel_ms_per_step": k_ms.value / args.steps, "kernel_share_of_step": (k_ms.value / args.steps) / ms,
+                "peak_basis": basis}
+        cpu = None
+        if not args.no_cpu and n_gpus == 1:
+            n_s = pick_cpu_sample(args.dtype)
+            v, info = cpu_reference_rate(args.dtype, n_s)
+            cpu = {"value": v, "unit": UNIT, **info}
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": args.dtype,
+                "data": "synthetic",
+                "config": {"workload": f"El::Gemm {args.dtype} {['DEFAULT','SUMMA_A','SUMMA_B','SUMMA_C','SUMMA_DOT'][args.alg] if args.alg < 5 else args.alg} n={n} (NN, alpha=0.5, beta=-0.5), [MC,MR] on a {grid.Height()}x{grid.Width()} grid",
+                           "inputs": "Uniform(-0.1,0.1), resident in HBM", "l2": f"inputs {3 * n * n * esz / n_gpus / 2**20:.0f} MiB per GPU > 126 MB L2 (no flush needed)",
+                           "panel_k": "full k on 1x1; ELB200_PANEL_K default 2048 (fp32) / 1024 (fp64) otherwise",
+                           "per_gpu_tflops": value / n_gpus},
+                "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main() -> int:
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -79,6 +79,7 @@ SIGNATURES = {
     "elb200_status_string": (C.c_char_p, [ci]),
     "elb200_last_error": (C.c_char_p, []),
     "elb200_build_info": (C.c_char_p, []),
+    "elb200_launch_count": (C.c_ulonglong, []),
     "elb200_gemm_f32": (ci, [ci, ci, i64, i64, i64, f32, vp, i64, vp, i64, f32, vp, i64, vp]),
     "elb200_gemm_f64": (ci, [ci, ci, i64, i64, i64, f64, vp, i64, vp, i64, f64, vp, i64, vp]),
     "elb200_gemm_f32_ex": (ci, [ci, ci, i64, i64, i64, f32, vp, i64, vp, i64, f32, vp, i64, ci, vp]),
@@ -109,6 +110,8 @@ SIGNATURES = {
     "elb200_grid_info": (ci, [vp] + [C.POINTER(ci)] * 5),
     "elb200_grid_stream": (vp, [vp]),
     "elb200_grid_sync": (ci, [vp]),
+    "elb200_gemm_profile": (None, [ci]),
+    "elb200_gemm_profile_collect": (ci, [C.POINTER(f64), C.POINTER(f64), C.POINTER(ci)]),
     "elb200_blocksize": (ci, []),
     "elb200_set_blocksize": (None, [ci]),
     "elb200_push_blocksize": (None, [ci]),

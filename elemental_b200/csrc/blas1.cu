@@ -105,6 +105,7 @@ int launch_panel(int64_t rows, int64_t cols, const T* src, int64_t lds, T* dst, 
         return ELB200_OK;
     }
     dim3 grid(static_cast<unsigned>(gx), static_cast<unsigned>(gy));
+    count_launch();
     if (vec)
         panel_kernel<T, V, OP><<<grid, block, 0, s>>>(rows_v, cols, reinterpret_cast<const V*>(src),
                                                       lds / N, reinterpret_cast<V*>(dst), ldd / N,
@@ -140,6 +141,7 @@ int launch_strided(int64_t rows, int64_t cols, const T* src, int64_t srs, int64_
     int64_t gy = (cols + by - 1) / by;
     if (gy > 4096) gy = 4096;
     dim3 grid(static_cast<unsigned>((rows + bx - 1) / bx), static_cast<unsigned>(gy));
+    count_launch();
     strided_kernel<T, AXPY><<<grid, dim3(bx, by), 0, s>>>(rows, cols, src, srs, scs, dst, drs, dcs,
                                                           alpha);
     return check_cuda(cudaGetLastError(), "strided_kernel");
@@ -186,6 +188,7 @@ int launch_transpose(int64_t rows, int64_t cols, const T* A, int64_t lda, T* B, 
         }
         return ELB200_OK;
     }
+    count_launch();
     transpose_kernel<T, AXPY><<<dim3(unsigned(gx), unsigned(gy)), dim3(32, 8), 0, s>>>(
         rows, cols, A, lda, B, ldb, alpha);
     return check_cuda(cudaGetLastError(), "transpose_kernel");
@@ -251,6 +254,7 @@ int launch_lattice(int mode, int nseg, const elb200_segment* segs, T* M, int64_t
     if (gy > 1024) gy = 1024;
     dim3 grid(unsigned((rows_v + bx - 1) / bx), unsigned(gy), unsigned(n));
     dim3 block(bx, by);
+    count_launch();
 #define ELB_LAT(MODE_)                                                                  \
     if (vec) lattice_kernel<T, V, MODE_><<<grid, block, 0, s>>>(tab, M, ldm, buf, alpha); \
     else lattice_kernel<T, T, MODE_><<<grid, block, 0, s>>>(tab, M, ldm, buf, alpha);

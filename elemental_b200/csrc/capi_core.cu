@@ -2,12 +2,15 @@
 #include <cuda_runtime.h>
 #include <cstdio>
 #include <cstring>
+#include <atomic>
 
 #include "elb200_internal.h"
 
 namespace elb {
 
 thread_local char g_last_error[512] = "";
+std::atomic<unsigned long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
 void set_last_error(const char* what, const char* detail) {
     std::snprintf(g_last_error, sizeof(g_last_error), "%s: %s", what, detail ? detail : "");
@@ -70,6 +73,7 @@ const char* elb200_status_string(int status) {
 }
 
 const char* elb200_last_error(void) { return g_last_error; }
+unsigned long long elb200_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 const char* elb200_build_info(void) {
     return "libelb200 sm_100a: gemm_f32 tcgen05 3xTF32 (TMA+TMEM, cta_group 1/2), "

@@ -154,6 +154,11 @@ int elb200_grid_sync(elb200_grid_t g) {
     return guarded("elb200_grid_sync", [&] { cuda_check(cudaStreamSynchronize(g->g->stream), "cudaStreamSynchronize"); });
 }
 
+void elb200_gemm_profile(int enable) { GemmProfileEnable(enable != 0); }
+int elb200_gemm_profile_collect(double* total_ms, double* total_flop, int* launches) {
+    return guarded("elb200_gemm_profile_collect", [&] { GemmProfileCollect(total_ms, total_flop, launches); });
+}
+
 int elb200_blocksize(void) { return Grid::Blocksize(); }
 void elb200_set_blocksize(int nb) { Grid::SetBlocksize(nb); }
 void elb200_push_blocksize(int nb) { Grid::PushBlocksize(nb); }

@@ -8,6 +8,8 @@
 namespace elb {
 
 int device_sm_count();
+// every kernel launch of this library bumps a process-wide counter (bench.py's gpu_launches)
+void count_launch();
 
 int gemm_f32_tensor(int transA, int transB, int64_t m, int64_t n, int64_t k, float alpha,
                     const float* A, int64_t lda, const float* B, int64_t ldb, float beta, float* C,

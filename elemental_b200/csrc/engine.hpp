@@ -113,6 +113,8 @@ template <typename T>
 void Gemm(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, T beta, DistMat<T>& C, int alg);
 // Which SUMMA variant GEMM_DEFAULT resolves to (reference Gemm/NN.hpp:585-600 and twins).
 int ResolveGemmAlg(int ta, int tb, int64_t m, int64_t n, int64_t k, int alg);
+void GemmProfileEnable(bool on);
+void GemmProfileCollect(double* ms, double* flop, int* launches);
 
 bool implied_align(Dist mine, Dist theirs, int64_t a, const GridShape& g, int64_t* out);
 // Distribution spec B ends up with after `B = A` (dims from A; unconstrained alignments adopt A's).

@@ -20,6 +20,34 @@
 
 namespace elb {
 
+// Optional per-launch timing of the local GEMM (bench.py's roofline leg): CUDA events on the
+// launching stream around every LocalGemm kernel; durations are read back after the run.
+namespace {
+struct GemmProfile {
+    bool on = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev;
+    double flop = 0;
+} g_prof;
+}  // namespace
+
+void GemmProfileEnable(bool on) { g_prof.on = on; }
+void GemmProfileCollect(double* ms, double* flop, int* launches) {
+    double total = 0;
+    for (auto& e : g_prof.ev) {
+        float t = 0;
+        cudaEventSynchronize(e.second);
+        cudaEventElapsedTime(&t, e.first, e.second);
+        total += t;
+        cudaEventDestroy(e.first);
+        cudaEventDestroy(e.second);
+    }
+    if (ms) *ms = total;
+    if (flop) *flop = g_prof.flop;
+    if (launches) *launches = int(g_prof.ev.size());
+    g_prof.ev.clear();
+    g_prof.flop = 0;
+}
+
 template <typename T>
 void LocalGemm(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, T beta, DistMat<T>& C) {
     const int64_t m = C.lh(), n = C.lw();
@@ -27,7 +55,19 @@ void LocalGemm(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B
     const int64_t ma = ta ? A.lw() : A.lh(), nb = tb ? B.lh() : B.lw();
     if (ka != kb || ma != m || nb != n)
         throw EngineError(ELB200_ERR_ARG, "LocalGemm: nonconformal local matrices");
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    const bool prof = g_prof.on && m > 0 && n > 0 && ka > 0;
+    if (prof) {
+        cuda_check(cudaEventCreate(&e0), "cudaEventCreate");
+        cuda_check(cudaEventCreate(&e1), "cudaEventCreate");
+        cuda_check(cudaEventRecord(e0, C.stream), "cudaEventRecord");
+    }
     Dev<T>::gemm(ta, tb, m, n, ka, alpha, A.buf, A.ldim, B.buf, B.ldim, beta, C.buf, C.ldim, C.stream);
+    if (prof) {
+        cuda_check(cudaEventRecord(e1, C.stream), "cudaEventRecord");
+        g_prof.ev.emplace_back(e0, e1);
+        g_prof.flop += 2.0 * double(m) * double(n) * double(ka);
+    }
 }
 
 int ResolveGemmAlg(int, int, int64_t m, int64_t n, int64_t k, int alg) {
@@ -83,7 +123,8 @@ struct Dims { int64_t m, n, k; };
 template <typename T>
 void SummaC(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, DistMat<T>& C, Dims d) {
     Grid& g = *C.grid;
-    const int64_t W = Grid::PanelWidth(sizeof(T));
+    // on a 1 x 1 grid no panel moves: the whole k range is one local GEMM (C is read once)
+    const int64_t W = g.size() == 1 ? std::max<int64_t>(d.k, 1) : Grid::PanelWidth(sizeof(T));
     DistMat<T> PA(g, ta ? STAR : MC, ta ? MC : STAR, C.stream);
     DistMat<T> PB(g, tb ? MR : STAR, tb ? STAR : MR, C.stream);
     for (int64_t k0 = 0; k0 < d.k; k0 += W) {

@@ -363,6 +363,7 @@ cudaError_t launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const Params&
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
+    count_launch();
     return cudaLaunchKernelEx(&cfg, kern, tmA, tmB, p);
 }
 

@@ -195,6 +195,7 @@ cudaError_t launch(const Params& p, cudaStream_t stream) {
         if (e != cudaSuccess) return e;
         configured = true;
     }
+    count_launch();
     kern<<<dim3(unsigned(p.tiles_m) * unsigned(p.tiles_n)), kThreads, kSmemBytes, stream>>>(p);
     return cudaGetLastError();
 }

@@ -42,6 +42,8 @@ const char* elb200_status_string(int status);
 const char* elb200_last_error(void);
 /* Compile-time facts: "sm_100a", kernel list. */
 const char* elb200_build_info(void);
+/* Number of CUDA kernels this library has launched in this process (all entry points). */
+unsigned long long elb200_launch_count(void);
 
 /* ------------------------------------------------------------------------------------------
  * BLAS-3: local GEMM.  C(m x n) = alpha * op(A) * op(B) + beta * C
@@ -235,6 +237,12 @@ int elb200_grid_info(elb200_grid_t g, int* height, int* width, int* vc_rank, int
                      int* mr_rank);
 void* elb200_grid_stream(elb200_grid_t g); /* the grid's compute stream (cudaStream_t) */
 int elb200_grid_sync(elb200_grid_t g);     /* cudaStreamSynchronize on it */
+
+/* Measurement hook (bench.py roofline leg): when enabled, every LocalGemm kernel launch is
+ * bracketed by CUDA events on its own stream; collect() synchronises and returns the summed device
+ * time (ms), the algorithmic flops (2*m*n*k per launch) and the launch count, then resets. */
+void elb200_gemm_profile(int enable);
+int elb200_gemm_profile_collect(double* total_ms, double* total_flop, int* launches);
 
 /* El::Blocksize / SetBlocksize / PushBlocksizeStack / PopBlocksizeStack
  * (src/blas_like/blocksizes.cpp:35-67). */

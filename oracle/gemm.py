@@ -186,6 +186,22 @@ def dist_gemm(g: Grid, orientA, orientB, alpha, A, B, beta, C, alg=GEMM_DEFAULT,
     return Cd.to_global()
 
 
+def summa_nnc_1x1(alpha, A: np.ndarray, B: np.ndarray, beta, C: np.ndarray, nb: int = 128) -> np.ndarray:
+    """The reference's CPU El::Gemm(NORMAL,NORMAL,...,GEMM_SUMMA_C) on a 1 x 1 grid, without the
+    virtual-rank bookkeeping: Scale(beta,C) (Gemm.cpp:282), then per nb-panel a local copy of A1
+    (RowAllGather.hpp:35-38), a local transpose of B1 (Transpose/ColAllGather.hpp:26-32) and one
+    BLAS rank-nb update (NN.hpp:371-384). Used as the timed CPU port when oracle/_ref is absent."""
+    C = np.array(C, order="F", copy=True)
+    C *= C.dtype.type(beta)
+    k = A.shape[1]
+    al = C.dtype.type(alpha)
+    for k0 in range(0, k, nb):
+        A1 = np.array(A[:, k0:k0 + nb], order="F")          # A1_MC_STAR = A1
+        B1T = np.array(B[k0:k0 + nb, :].T, order="F")       # Transpose(B1, B1Trans_MR_STAR)
+        C += al * (A1 @ B1T.T)                              # LocalGemm(NORMAL, TRANSPOSE, alpha, ., ., 1, C)
+    return C
+
+
 def frobenius_rel_err(X, ref) -> float:
     ref = np.asarray(ref, dtype=np.float64)
     d = np.asarray(X, dtype=np.float64) - ref
