@@ -43,7 +43,7 @@ def parse_args():
     ap.add_argument("--dtype", choices=["f32", "f64"], default="f32")
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--n", type=int, default=0, help="override the matrix size (diagnostics only)")
-    ap.add_argument("--alg", type=int, default=3, help="El::GemmAlgorithm (3 = GEMM_SUMMA_C)")
+    ap.add_argument("--alg", type=int, default=6, help="El::GemmAlgorithm, reference enum values (6 = GEMM_SUMMA_C, 7 = GEMM_SUMMA_DOT)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     return ap.parse_args()
@@ -326,7 +326,7 @@ def run_ours(args) -> int:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": args.dtype,
                 "data": "synthetic",
-                "config": {"workload": f"El::Gemm {args.dtype} {['DEFAULT','SUMMA_A','SUMMA_B','SUMMA_C','SUMMA_DOT'][args.alg] if args.alg < 5 else args.alg} n={n} (NN, alpha=0.5, beta=-0.5), [MC,MR] on a {grid.Height()}x{grid.Width()} grid",
+                "config": {"workload": f"El::Gemm {args.dtype} {['DEFAULT','SUMMA_A_MS','SUMMA_A','SUMMA_B_MS','SUMMA_B','SUMMA_C_MS','SUMMA_C','SUMMA_DOT','CANNON'][args.alg]} n={n} (NN, alpha=0.5, beta=-0.5), [MC,MR] on a {grid.Height()}x{grid.Width()} grid",
                            "inputs": "Uniform(-0.1,0.1), resident in HBM", "l2": f"inputs {3 * n * n * esz / n_gpus / 2**20:.0f} MiB per GPU > 126 MB L2 (no flush needed)",
                            "panel_k": "full k on 1x1; ELB200_PANEL_K default 2048 (fp32) / 1024 (fp64) otherwise",
                            "per_gpu_tflops": value / n_gpus},

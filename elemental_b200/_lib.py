@@ -27,8 +27,9 @@ UNIQUE_ID_BYTES = 128
 F32, F64 = 0, 1
 MC, MR, VC, VR, STAR = 0, 1, 2, 3, 4
 DIST_NAMES = {MC: "MC", MR: "MR", VC: "VC", VR: "VR", STAR: "STAR"}
-GEMM_DEFAULT, GEMM_SUMMA_A, GEMM_SUMMA_B, GEMM_SUMMA_C, GEMM_SUMMA_DOT, GEMM_CANNON = range(6)
-GEMM_SUMMA_A_MS, GEMM_SUMMA_B_MS, GEMM_SUMMA_C_MS = 6, 7, 8
+# El::GemmAlgorithm, values as in the reference enum (include/El/blas_like/level3.hpp:23-33)
+(GEMM_DEFAULT, GEMM_SUMMA_A_MS, GEMM_SUMMA_A, GEMM_SUMMA_B_MS, GEMM_SUMMA_B, GEMM_SUMMA_C_MS, GEMM_SUMMA_C,
+ GEMM_SUMMA_DOT, GEMM_CANNON) = range(9)
 PACK, UNPACK, UNPACK_AXPY = 0, 1, 2
 
 i64 = C.c_int64

@@ -24,10 +24,10 @@ void throw_status(int status, const char* where);
 void cuda_check(cudaError_t e, const char* where);
 void nccl_check(ncclResult_t r, const char* where);
 
-// Mirrors El::GemmAlgorithm (reference include/El/blas_like/level3.hpp:22-35), same order.
+// Mirrors El::GemmAlgorithm (reference include/El/blas_like/level3.hpp:22-35), same order and values.
 enum GemmAlg : int {
-    GEMM_DEFAULT = 0, GEMM_SUMMA_A = 1, GEMM_SUMMA_B = 2, GEMM_SUMMA_C = 3, GEMM_SUMMA_DOT = 4,
-    GEMM_CANNON = 5, GEMM_SUMMA_A_MS = 6, GEMM_SUMMA_B_MS = 7, GEMM_SUMMA_C_MS = 8
+    GEMM_DEFAULT = 0, GEMM_SUMMA_A_MS = 1, GEMM_SUMMA_A = 2, GEMM_SUMMA_B_MS = 3, GEMM_SUMMA_B = 4,
+    GEMM_SUMMA_C_MS = 5, GEMM_SUMMA_C = 6, GEMM_SUMMA_DOT = 7, GEMM_CANNON = 8
 };
 
 class Grid {

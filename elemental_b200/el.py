@@ -19,8 +19,9 @@ from . import _lib
 from ._lib import (F32, F64, MC, MR, STAR, VC, VR, check, lib)  # noqa: F401
 
 NORMAL, TRANSPOSE, ADJOINT = 0, 1, 2  # El::Orientation (include/El/core/types.hpp)
-GEMM_DEFAULT, GEMM_SUMMA_A, GEMM_SUMMA_B, GEMM_SUMMA_C, GEMM_SUMMA_DOT, GEMM_CANNON = range(6)
-GEMM_SUMMA_A_MS, GEMM_SUMMA_B_MS, GEMM_SUMMA_C_MS = 6, 7, 8
+# El::GemmAlgorithm, values as in the reference enum (include/El/blas_like/level3.hpp:23-33)
+(GEMM_DEFAULT, GEMM_SUMMA_A_MS, GEMM_SUMMA_A, GEMM_SUMMA_B_MS, GEMM_SUMMA_B, GEMM_SUMMA_C_MS, GEMM_SUMMA_C,
+ GEMM_SUMMA_DOT, GEMM_CANNON) = range(9)
 
 _DTYPES = {torch.float32: F32, torch.float64: F64, np.dtype("float32"): F32,
            np.dtype("float64"): F64, "float32": F32, "float64": F64, F32: F32, F64: F64}

@@ -281,8 +281,10 @@ int elb200_dm_transpose_axpy_contract(double alpha, elb200_dm_t A, elb200_dm_t B
 int elb200_dm_local_gemm(int transA, int transB, double alpha, elb200_dm_t A, elb200_dm_t B,
                          double beta, elb200_dm_t C);
 /* El::Gemm(orientA, orientB, alpha, A, B, beta, C, alg) (src/blas_like/level3/Gemm.cpp:273-302).
- * alg: El::GemmAlgorithm 0=DEFAULT 1=SUMMA_A 2=SUMMA_B 3=SUMMA_C 4=SUMMA_DOT 5=CANNON
- *      6..8 = the _MS twins (include/El/blas_like/level3.hpp:22-35). */
+ * alg: the reference's El::GemmAlgorithm values (include/El/blas_like/level3.hpp:23-33):
+ *      0=DEFAULT 1=SUMMA_A_MS 2=SUMMA_A 3=SUMMA_B_MS 4=SUMMA_B 5=SUMMA_C_MS 6=SUMMA_C
+ *      7=SUMMA_DOT 8=CANNON (the _MS variants run their plain twins; CANNON errors on GPU
+ *      as in Gemm/NN.hpp:30-31). */
 int elb200_dist_gemm(int transA, int transB, double alpha, elb200_dm_t A, elb200_dm_t B,
                      double beta, elb200_dm_t C, int alg);
 

@@ -11,8 +11,9 @@ import numpy as np
 from .dist import MC, MR, STAR, VC, VR, VDM, Grid, axpy_contract, redistribute, transpose  # noqa: F401
 
 NORMAL, TRANSPOSE, ADJOINT = 0, 1, 2
-(GEMM_DEFAULT, GEMM_SUMMA_A, GEMM_SUMMA_B, GEMM_SUMMA_C, GEMM_SUMMA_DOT, GEMM_CANNON,
- GEMM_SUMMA_A_MS, GEMM_SUMMA_B_MS, GEMM_SUMMA_C_MS) = range(9)
+# values of the reference enum El::GemmAlgorithm (include/El/blas_like/level3.hpp:23-33)
+(GEMM_DEFAULT, GEMM_SUMMA_A_MS, GEMM_SUMMA_A, GEMM_SUMMA_B_MS, GEMM_SUMMA_B, GEMM_SUMMA_C_MS, GEMM_SUMMA_C,
+ GEMM_SUMMA_DOT, GEMM_CANNON) = range(9)
 
 
 def op(X: np.ndarray, orient: int) -> np.ndarray:

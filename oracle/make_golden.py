@@ -1,0 +1,84 @@
+"""TEST INFRASTRUCTURE ONLY. Regenerates tests/golden/ from the REFERENCE ITSELF.
+
+Runs oracle/_ref/gemm_ref (the reference's own CPU El::Gemm, compiled by oracle/ref_build/Makefile
+from /root/reference where it lies; single rank) with --golden, and packs what it wrote into
+
+  tests/golden/ref_gemm_1x1.npz   per case: orientations, GemmAlgorithm, m n k, blocksize, alpha,
+                                  beta, the inputs A B C0 and the reference's C (f32 and f64)
+  tests/golden/ref_indexing.npz   tables of El::Shift / El::Length / El::MaxLength
+                                  (include/El/core/indexing/impl.hpp) and Grid::DefaultHeight
+                                  (src/core/Grid.cpp) as the reference evaluates them
+
+Usage (in the build container, where /root/reference exists):
+    make -C oracle/ref_build && python oracle/make_golden.py
+The fixtures travel to the GPU box; the reference tree and this script's inputs do not need to.
+"""
+from __future__ import annotations
+
+import os
+import subprocess
+import sys
+import tempfile
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF_BIN = os.path.join(ROOT, "oracle", "_ref", "gemm_ref")
+OUT = os.path.join(ROOT, "tests", "golden")
+
+
+def lcg_matrix(h: int, w: int, seed: int, dtype) -> np.ndarray:
+    """The input generator of oracle/ref_build/gemm_ref.cpp (fill_lcg), column-major fill order."""
+    mask = (1 << 64) - 1
+    s = (0x9E3779B97F4A7C15 * (seed + 1)) & mask
+    out = np.empty((h, w), dtype=np.float64)
+    for j in range(w):
+        for i in range(h):
+            s = (s * 6364136223846793005 + 1442695040888963407) & mask
+            out[i, j] = 2.0 * (((s >> 11) & ((1 << 53) - 1)) / float(1 << 53)) - 1.0
+    return out.astype(dtype)
+
+
+def main() -> int:
+    if not os.path.exists(REF_BIN):
+        print("oracle/_ref/gemm_ref is missing: run `make -C oracle/ref_build` first", file=sys.stderr)
+        return 1
+    os.makedirs(OUT, exist_ok=True)
+    with tempfile.TemporaryDirectory() as tmp:
+        subprocess.run([REF_BIN, "--golden", tmp], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        arrays = {}
+        meta = []
+        for ln in open(os.path.join(tmp, "index.txt")):
+            t, cid, oa, ob, alg, m, n, k, nb, alpha, beta = ln.split()
+            cid, oa, ob, alg, m, n, k, nb = map(int, (cid, oa, ob, alg, m, n, k, nb))
+            dt = np.float32 if t == "f32" else np.float64
+            shapes = {"A": (k, m) if oa else (m, k), "B": (n, k) if ob else (k, n), "C0": (m, n), "C": (m, n)}
+            for name, (h, w) in shapes.items():
+                raw = np.fromfile(os.path.join(tmp, f"{t}_{cid}_{name}.bin"), dtype=dt)
+                assert raw.size == h * w, (ln, name, raw.size)
+                mat = raw.reshape(w, h).T.copy()  # files are column-major
+                # Inputs come from a fixed LCG (gemm_ref.cpp fill_lcg, restated as lcg_matrix below), so
+                # only the reference's OUTPUT is stored, plus the inputs of case 0; every other input is
+                # checked here, at generation time, to equal the restated generator bit for bit.
+                if name == "C" or cid == 0:
+                    arrays[f"{t}_{cid}_{name}"] = mat
+                else:
+                    seed = 3 * cid + {"A": 0, "B": 1, "C0": 2}[name]
+                    assert np.array_equal(mat, lcg_matrix(h, w, seed, dt)), (ln, name)
+            meta.append((0 if t == "f32" else 1, cid, oa, ob, alg, m, n, k, nb, float(alpha), float(beta)))
+        arrays["meta"] = np.array(meta, dtype=np.float64)
+        np.savez_compressed(os.path.join(OUT, "ref_gemm_1x1.npz"), **arrays)
+
+        L, H = [], []
+        for ln in open(os.path.join(tmp, "indexing.txt")):
+            f = ln.split()
+            (L if f[0] == "L" else H).append([int(x) for x in f[1:]])
+        # L columns: n rank align stride shift length maxlength ; H columns: p height
+        np.savez_compressed(os.path.join(OUT, "ref_indexing.npz"), L=np.array(L, dtype=np.int64),
+                            H=np.array(H, dtype=np.int64))
+    print(f"wrote {len(meta)} Gemm cases, {len(L)} index rows, {len(H)} grid heights to {OUT}")
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

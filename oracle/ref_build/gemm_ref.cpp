@@ -1,0 +1,118 @@
+// ORACLE BUILD ONLY (test infrastructure): a driver over the REFERENCE'S OWN CPU El::Gemm,
+// compiled from /root/reference where it lies, single rank (oracle/ref_build/stub/mpi.h),
+// linked against the OpenBLAS found in the image. Nothing here is on the product path.
+//
+//   gemm_ref --bench f32|f64 n         time El::Gemm(NORMAL,NORMAL,0.5,A,B,-0.5,C,GEMM_SUMMA_C), nb=128
+//   gemm_ref --golden <dir>            write inputs + reference outputs of a fixed list of small
+//                                      cases (all orientations x GemmAlgorithm, ragged sizes) and
+//                                      tables of the index functions, as raw little-endian files
+#include <El.hpp>
+
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <string>
+#include <vector>
+
+using namespace El;
+
+template <typename T>
+static void fill_lcg(Matrix<T>& M, unsigned seed) {
+    // deterministic, implementation-independent input generator (also restated in tests)
+    unsigned long long s = 0x9E3779B97F4A7C15ull * (seed + 1);
+    for (Int j = 0; j < M.Width(); ++j)
+        for (Int i = 0; i < M.Height(); ++i) {
+            s = s * 6364136223846793005ull + 1442695040888963407ull;
+            const double u = double((s >> 11) & ((1ull << 53) - 1)) / double(1ull << 53);
+            M.Set(i, j, T(2.0 * u - 1.0));
+        }
+}
+
+template <typename T>
+static void dump(const std::string& path, const Matrix<T>& M) {
+    std::ofstream f(path, std::ios::binary);
+    for (Int j = 0; j < M.Width(); ++j)
+        f.write(reinterpret_cast<const char*>(M.LockedBuffer(0, j)), sizeof(T) * M.Height());
+}
+
+template <typename T>
+static double bench(Int n) {
+    const Grid& g = Grid::Default();
+    DistMatrix<T> A(g), B(g), C(g);
+    Uniform(A, n, n, T(0), T(0.1));
+    Uniform(B, n, n, T(0), T(0.1));
+    Uniform(C, n, n, T(0), T(0.1));
+    SetBlocksize(128);
+    {  // warm the BLAS threads
+        DistMatrix<T> a(g), b(g), c(g);
+        Uniform(a, 512, 512); Uniform(b, 512, 512); Uniform(c, 512, 512);
+        Gemm(NORMAL, NORMAL, T(0.5), a, b, T(-0.5), c, GEMM_SUMMA_C);
+    }
+    auto t0 = std::chrono::steady_clock::now();
+    Gemm(NORMAL, NORMAL, T(0.5), A, B, T(-0.5), C, GEMM_SUMMA_C);
+    auto t1 = std::chrono::steady_clock::now();
+    return std::chrono::duration<double>(t1 - t0).count();
+}
+
+template <typename T>
+static void golden_cases(const std::string& dir, const char* tname, std::ofstream& index) {
+    const Grid& g = Grid::Default();
+    struct Case { Int m, n, k; Int nb; double alpha, beta; };
+    const Case cases[] = {{37, 29, 53, 16, 2.0, 3.0}, {64, 64, 64, 128, 0.5, -0.5}, {5, 130, 41, 32, 1.0, 0.0}};
+    const Orientation os[2] = {NORMAL, TRANSPOSE};
+    const GemmAlgorithm algs[] = {GEMM_DEFAULT, GEMM_SUMMA_A, GEMM_SUMMA_B, GEMM_SUMMA_C, GEMM_SUMMA_DOT};
+    int id = 0;
+    for (const Case& c : cases)
+        for (int ia = 0; ia < 2; ++ia)
+            for (int ib = 0; ib < 2; ++ib)
+                for (GemmAlgorithm alg : algs) {
+                    DistMatrix<T> A(g), B(g), C(g);
+                    A.Resize(ia ? c.k : c.m, ia ? c.m : c.k);
+                    B.Resize(ib ? c.n : c.k, ib ? c.k : c.n);
+                    C.Resize(c.m, c.n);
+                    fill_lcg(A.Matrix(), 3 * id + 0);
+                    fill_lcg(B.Matrix(), 3 * id + 1);
+                    fill_lcg(C.Matrix(), 3 * id + 2);
+                    const std::string base = dir + "/" + tname + "_" + std::to_string(id);
+                    dump(base + "_A.bin", A.LockedMatrix());
+                    dump(base + "_B.bin", B.LockedMatrix());
+                    dump(base + "_C0.bin", C.LockedMatrix());
+                    SetBlocksize(c.nb);
+                    Gemm(os[ia], os[ib], T(c.alpha), A, B, T(c.beta), C, alg);
+                    dump(base + "_C.bin", C.LockedMatrix());
+                    index << tname << " " << id << " " << ia << " " << ib << " " << int(alg) << " " << c.m << " "
+                          << c.n << " " << c.k << " " << c.nb << " " << c.alpha << " " << c.beta << "\n";
+                    ++id;
+                }
+}
+
+int main(int argc, char* argv[]) {
+    Environment env(argc, argv);
+    if (argc >= 4 && !std::strcmp(argv[1], "--bench")) {
+        const Int n = std::atoi(argv[3]);
+        const double t = !std::strcmp(argv[2], "f32") ? bench<float>(n) : bench<double>(n);
+        std::printf("REF_GEMM_SECONDS %.6f n=%d dtype=%s\n", t, int(n), argv[2]);
+        return 0;
+    }
+    if (argc >= 3 && !std::strcmp(argv[1], "--golden")) {
+        const std::string dir = argv[2];
+        std::ofstream index(dir + "/index.txt");
+        golden_cases<float>(dir, "f32", index);
+        golden_cases<double>(dir, "f64", index);
+        // index-function tables (include/El/core/indexing/impl.hpp) and Grid::DefaultHeight
+        std::ofstream tab(dir + "/indexing.txt");
+        for (Int stride = 1; stride <= 8; ++stride)
+            for (Int align = 0; align < stride; ++align)
+                for (Int rank = 0; rank < stride; ++rank)
+                    for (Int n : {0, 1, 7, 64, 1000}) {
+                        const Int shift = Shift(rank, align, stride);
+                        tab << "L " << n << " " << rank << " " << align << " " << stride << " " << shift << " "
+                            << Length(n, shift, stride) << " " << MaxLength(n, stride) << "\n";
+                    }
+        for (int p = 1; p <= 64; ++p) tab << "H " << p << " " << Grid::DefaultHeight(p) << "\n";
+        return 0;
+    }
+    std::printf("usage: gemm_ref --bench f32|f64 n | --golden dir\n");
+    return 64;
+}

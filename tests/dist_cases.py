@@ -147,7 +147,8 @@ def gemm_case(grid, dtype, oa, ob, alg, m, n, k, alpha=2.0, beta=3.0, aligns=Non
     return num / max(den, 1e-300), OG.gemm_tolerance(npdt, k)
 
 
-def check_gemm_variants(grid, dtype, shapes=((70, 50, 90),), algs=(1, 2, 3, 4, 0), nb=16) -> int:
+def check_gemm_variants(grid, dtype, shapes=((70, 50, 90),), algs=(el.GEMM_SUMMA_A, el.GEMM_SUMMA_B, el.GEMM_SUMMA_C, el.GEMM_SUMMA_DOT, el.GEMM_DEFAULT),
+                        nb=16) -> int:
     og = _grid_oracle(grid)
     cnt = 0
     for (m, n, k) in shapes:
@@ -166,7 +167,7 @@ def check_gemm_proxies(grid, dtype) -> None:
               ((el.VC, el.STAR), (el.MR, el.MC), (el.STAR, el.VR)),
               ((el.STAR, el.STAR), (el.MC, el.MR), (el.MR, el.MC))]
     for d in combos:
-        for alg in (0, 3, 4):
+        for alg in (el.GEMM_DEFAULT, el.GEMM_SUMMA_C, el.GEMM_SUMMA_DOT):
             err, tol = gemm_case(grid, dtype, 0, 0, alg, 45, 37, 64, dists=d, nb=16)
             assert err <= tol, (d, alg, err, tol)
 

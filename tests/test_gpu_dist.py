@@ -44,7 +44,7 @@ def test_gemm_reference_driver_config(grid1, dtype):
     from tests import dist_cases as dc
     for oa in (0, 1):
         for ob in (0, 1):
-            for alg in (1, 2, 3, 4):
+            for alg in (el.GEMM_SUMMA_A, el.GEMM_SUMMA_B, el.GEMM_SUMMA_C, el.GEMM_SUMMA_DOT):
                 err, tol = dc.gemm_case(grid1, dtype, oa, ob, alg, 600, 500, 700, nb=96)
                 assert err <= tol, (oa, ob, alg, err, tol)
 
