@@ -1,0 +1,153 @@
+"""CPU tests that PIN the oracle: tests/golden/ holds outputs of the reference itself (its own CPU
+El::Gemm compiled by oracle/ref_build, see oracle/make_golden.py); the numpy restatement under
+oracle/ has to reproduce them, and has to agree with itself across grid shapes."""
+import itertools
+import os
+
+import numpy as np
+import pytest
+
+from oracle import dist as OD
+from oracle import gemm as OG
+from oracle.make_golden import lcg_matrix
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+@pytest.fixture(scope="module")
+def gold_gemm():
+    return np.load(os.path.join(GOLD, "ref_gemm_1x1.npz"))
+
+
+@pytest.fixture(scope="module")
+def gold_index():
+    return np.load(os.path.join(GOLD, "ref_indexing.npz"))
+
+
+def test_index_functions_match_reference(gold_index):
+    """El::Shift / Length / MaxLength exactly as the reference evaluates them (indexing/impl.hpp)."""
+    for n, rank, align, stride, shift, length, maxlen in gold_index["L"]:
+        assert OD.Shift(int(rank), int(align), int(stride)) == shift
+        assert OD.Length(int(n), int(shift), int(stride)) == length
+        assert OD.MaxLength(int(n), int(stride)) == maxlen
+
+
+def test_default_grid_height_matches_reference(gold_index):
+    for p, h in gold_index["H"]:
+        assert OD.DefaultHeight(int(p)) == h, (p, h)
+
+
+def test_lcg_generator_matches_reference_inputs(gold_gemm):
+    """Case 0's stored inputs are what the reference driver fed El::Gemm; lcg_matrix restates them."""
+    for t, dt in (("f32", np.float32), ("f64", np.float64)):
+        for i, name in enumerate(("A", "B", "C0")):
+            ref = gold_gemm[f"{t}_0_{name}"]
+            assert np.array_equal(lcg_matrix(ref.shape[0], ref.shape[1], i, dt), ref)
+
+
+def _cases(gold):
+    for row in gold["meta"]:
+        ti, cid, oa, ob, alg, m, n, k, nb = (int(x) for x in row[:9])
+        yield ("f32", np.float32) if ti == 0 else ("f64", np.float64), cid, oa, ob, alg, m, n, k, nb, row[9], row[10]
+
+
+def test_oracle_gemm_reproduces_reference_outputs(gold_gemm):
+    """All 120 reference runs (3 shapes x 4 orientations x {DEFAULT, SUMMA_A, B, C, DOT} x 2 dtypes,
+    ragged sizes, several blocksizes): the oracle on a 1 x 1 grid gives the reference's C within the
+    north_star bound; in fp64 the two differ only by summation order inside the BLAS."""
+    worst = {"f32": 0.0, "f64": 0.0}
+    count = 0
+    for (t, dt), cid, oa, ob, alg, m, n, k, nb, alpha, beta in _cases(gold_gemm):
+        A = lcg_matrix(*((k, m) if oa else (m, k)), 3 * cid + 0, dt)
+        B = lcg_matrix(*((n, k) if ob else (k, n)), 3 * cid + 1, dt)
+        C0 = lcg_matrix(m, n, 3 * cid + 2, dt)
+        got = OG.dist_gemm(OD.Grid(1, 1), oa, ob, alpha, A.astype(np.float64), B.astype(np.float64), beta,
+                           C0.astype(np.float64), alg, nb=nb)
+        err = OG.frobenius_rel_err(gold_gemm[f"{t}_{cid}_C"], got)
+        assert err <= OG.gemm_tolerance(dt, k), (t, cid, oa, ob, alg, err)
+        worst[t] = max(worst[t], err)
+        count += 1
+    assert count == 120
+    assert worst["f64"] < 1e-14  # far inside the bound: same algorithm, same arithmetic
+    assert worst["f32"] < 1e-6
+
+
+def test_reference_outputs_are_grid_independent(gold_gemm):
+    """The same reference outputs are reproduced when the oracle runs the SUMMA loops over 2x2,
+    2x3 and 3x1 virtual grids with non-zero alignments: ties the multi-rank restatement to the
+    single-rank reference runs."""
+    rows = [c for c in _cases(gold_gemm) if c[0][0] == "f64" and c[1] < 20]
+    for g in (OD.Grid(2, 2), OD.Grid(2, 3), OD.Grid(3, 1)):
+        for (t, dt), cid, oa, ob, alg, m, n, k, nb, alpha, beta in rows:
+            A = lcg_matrix(*((k, m) if oa else (m, k)), 3 * cid + 0, dt)
+            B = lcg_matrix(*((n, k) if ob else (k, n)), 3 * cid + 1, dt)
+            C0 = lcg_matrix(m, n, 3 * cid + 2, dt)
+            got = OG.dist_gemm(g, oa, ob, alpha, A, B, beta, C0, alg, nb=nb,
+                               aligns=((1 % g.r, 1 % g.c), (0, 2 % g.c), (1 % g.r, 0)))
+            assert OG.frobenius_rel_err(gold_gemm[f"{t}_{cid}_C"], got) <= OG.gemm_tolerance(dt, k)
+
+
+def test_resolve_alg_heuristic():
+    """GEMM_DEFAULT choice (Gemm/NN.hpp:572-600)."""
+    assert OG.resolve_alg(10, 10, 100) == OG.GEMM_SUMMA_DOT
+    assert OG.resolve_alg(10, 50, 20) == OG.GEMM_SUMMA_B
+    assert OG.resolve_alg(50, 10, 20) == OG.GEMM_SUMMA_A
+    assert OG.resolve_alg(100, 100, 100) == OG.GEMM_SUMMA_C
+    assert OG.resolve_alg(100, 100, 100, OG.GEMM_SUMMA_A_MS) == OG.GEMM_SUMMA_A
+
+
+@pytest.mark.parametrize("shape", [(1, 1), (2, 2), (2, 3), (4, 1), (1, 3)])
+def test_redistribute_all_pairs_is_exact(shape):
+    """Every (U,V) -> (U',V') redistribution among the 11 legal element-cyclic pairs moves the same
+    global matrix (bit-exact), including ragged sizes and non-zero alignments."""
+    g = OD.Grid(*shape)
+    pairs = [(OD.MC, OD.MR), (OD.MR, OD.MC), (OD.MC, OD.STAR), (OD.STAR, OD.MC), (OD.MR, OD.STAR), (OD.STAR, OD.MR),
+             (OD.VC, OD.STAR), (OD.STAR, OD.VC), (OD.VR, OD.STAR), (OD.STAR, OD.VR), (OD.STAR, OD.STAR)]
+    G = np.arange(13 * 11, dtype=np.float64).reshape(13, 11)
+    for (U, V), (U2, V2) in itertools.product(pairs, pairs):
+        ca, ra = 1 % g.stride(U), 2 % g.stride(V)
+        A = OD.VDM.from_global(g, G, U, V, ca, ra)
+        assert np.array_equal(A.to_global(), G)
+        B = OD.redistribute(A, U2, V2, 1 % g.stride(U2), 0)
+        assert np.array_equal(B.to_global(), G)
+        for q in range(g.p):
+            assert B.loc[q].shape == B.spec.local_shape(g, q)
+
+
+def test_empty_and_degenerate_shapes():
+    g = OD.Grid(2, 2)
+    for h, w in ((0, 5), (5, 0), (0, 0), (1, 1)):
+        A = OD.VDM.from_global(g, np.zeros((h, w)), OD.MC, OD.MR)
+        assert A.to_global().shape == (h, w)
+    C = OG.dist_gemm(g, 0, 0, 2.0, np.zeros((4, 0)), np.zeros((0, 3)), 3.0, np.ones((4, 3)))
+    assert np.array_equal(C, 3.0 * np.ones((4, 3)))  # k = 0: only Scale(beta, C) happens
+    C = OG.dist_gemm(g, 0, 0, 2.0, np.ones((4, 2)), np.ones((2, 3)), 0.0, np.full((4, 3), np.nan))
+    assert np.array_equal(C, 4.0 * np.ones((4, 3)))  # beta = 0 overwrites, NaNs do not propagate
+
+
+def test_summa_variants_agree_across_grids():
+    rng = np.random.default_rng(5)
+    m, n, k = 23, 31, 47
+    for oa, ob in itertools.product((0, 1), (0, 1)):
+        A = rng.standard_normal((k, m) if oa else (m, k))
+        B = rng.standard_normal((n, k) if ob else (k, n))
+        C0 = rng.standard_normal((m, n))
+        ref = OG.gemm_global(oa, ob, 0.5, A, B, -0.5, C0)
+        for g in (OD.Grid(1, 1), OD.Grid(2, 2), OD.Grid(3, 2)):
+            for alg in (OG.GEMM_SUMMA_A, OG.GEMM_SUMMA_B, OG.GEMM_SUMMA_C, OG.GEMM_SUMMA_DOT):
+                got = OG.dist_gemm(g, oa, ob, 0.5, A, B, -0.5, C0, alg, nb=8)
+                assert OG.frobenius_rel_err(got, ref) < 1e-14, (oa, ob, g, alg)
+
+
+def test_axpy_contract_sums_contributions():
+    """AxpyContract (level1/AxpyContract.hpp): [MC,STAR] partial sums reduce-scattered into [MC,MR]."""
+    g = OD.Grid(2, 3)
+    rng = np.random.default_rng(1)
+    parts = OD.VDM.zeros(g, OD.MC, OD.STAR, 0, 0, 9, 7, np.float64)
+    for q in range(g.p):
+        parts.loc[q][...] = rng.standard_normal(parts.loc[q].shape)
+    total = parts.contributions()
+    B0 = rng.standard_normal((9, 7))
+    Bd = OD.VDM.from_global(g, B0, OD.MC, OD.MR)
+    OD.axpy_contract(2.0, parts, Bd)
+    assert np.allclose(Bd.to_global(), B0 + 2.0 * total, rtol=0, atol=1e-13)
