@@ -313,7 +313,10 @@ def run_ours(args) -> int:
         tp = os.path.join(ROOT, "profiles", f"r01_ncu_gemm_{args.dtype}_traffic.json")
         if os.path.exists(tp):
             with open(tp) as f:
-                traffic = json.load(f).get("dram_bytes_per_launch")
+                tj = json.load(f)
+            # one ncu --set full capture of this kernel at this size (per launch, like `achieved`)
+            if tj.get("n") == n and n_gpus == 1:
+                traffic = tj.get("dram_bytes_per_launch")
         roof = {"bound": "tensor", "kernel": "gemm_f32_3xtf32_kernel<cta_group::2>" if args.dtype == "f32" else "gemm_f64_dmma_kernel",
                 "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": (ach / peak) if ach else None, "traffic": traffic,
                 "launches_timed": k_n.value, "kernel_ms_per_step": k_ms.value / args.steps, "kernel_share_of_step": (k_ms.value / args.steps) / ms,

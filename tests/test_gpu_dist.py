@@ -41,6 +41,7 @@ def test_gemm_reference_driver_config(grid1, dtype):
     """BASELINE config C1 shape class (tests/blas_like/Gemm.cpp defaults: m=n=k=2000 is too slow
     for the oracle in float128, so 600) with the driver's blocksize 96 and BasicGemm's alpha=2,
     beta=3, over every orientation and SUMMA variant."""
+    from elemental_b200 import el
     from tests import dist_cases as dc
     for oa in (0, 1):
         for ob in (0, 1):
