@@ -8,11 +8,11 @@ LIBDIR    := elemental_b200/lib
 CU_SRCS   := $(wildcard $(CSRC)/*.cu)
 CPP_SRCS  := $(wildcard $(CSRC)/*.cpp)
 OBJS      := $(patsubst $(CSRC)/%.cu,build/%.o,$(CU_SRCS)) $(patsubst $(CSRC)/%.cpp,build/%.cpp.o,$(CPP_SRCS))
-HDRS      := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh $(CSRC)/*.hpp include/*.h include/El/*.hpp include/*.hpp)
+HDRS      := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh $(CSRC)/*.hpp include/*.h)
 NCCL_INC  ?= /usr/include
 NCCL_LIB  ?= $(shell python -c "import nvidia.nccl, os; print(os.path.join(list(nvidia.nccl.__path__)[0], 'lib'))" 2>/dev/null)
 
-all: $(LIBDIR)/libelb200.so tools/gemm_check
+all: $(LIBDIR)/libelb200.so tools/gemm_check tools/el_gemm_driver
 
 build/%.o: $(CSRC)/%.cu $(HDRS)
 	@mkdir -p build
@@ -29,7 +29,11 @@ $(LIBDIR)/libelb200.so: $(OBJS)
 tools/gemm_check: tools/gemm_check.cu $(LIBDIR)/libelb200.so include/elb200.h
 	$(NVCC) $(NVFLAGS) -o $@ $< -L$(LIBDIR) -lelb200 -lcublas -Xlinker -rpath,'$$ORIGIN/../$(LIBDIR)'
 
+# counterpart of the reference's tests/blas_like/Gemm.cpp over the C++ facade (include/El.hpp)
+tools/el_gemm_driver: tools/el_gemm_driver.cpp include/El.hpp include/elb200.h $(LIBDIR)/libelb200.so
+	$(NVCC) -std=c++17 -O2 -Xcompiler -Wall -Iinclude -o $@ $< -L$(LIBDIR) -lelb200 -lcudart -Xlinker -rpath,'$$ORIGIN/../$(LIBDIR)'
+
 clean:
-	rm -rf build $(LIBDIR)/libelb200.so tools/gemm_check
+	rm -rf build $(LIBDIR)/libelb200.so tools/gemm_check tools/el_gemm_driver
 
 .PHONY: all clean
