@@ -12,6 +12,7 @@
 #include <string>
 #include <vector>
 
+#include "peer.hpp"
 #include "plan.hpp"
 
 namespace elb {
@@ -45,6 +46,13 @@ public:
     cudaStream_t stream = nullptr;       // compute stream (the reference's SyncInfo of C)
     cudaStream_t comm_stream = nullptr;  // panel prefetch stream (overlap with the local GEMM)
     ncclComm_t world = nullptr, mc_comm = nullptr, mr_comm = nullptr;
+    // NVLink peer-memory staging (zero-SM AllGather); nullptr -> NCCL is used instead.
+    PeerArena* arena = nullptr;
+    // VC ranks of the MC (grid column) / MR (grid row) / VC (world) communicator this rank belongs
+    // to, in communicator order, and this rank's index in it.
+    std::vector<int> comm_members(Dist d) const;
+    int comm_index(Dist d) const { return d == MC ? me.mc : d == MR ? me.mr : vc_rank; }
+    static int arena_channel(Dist d) { return d == MC ? 0 : d == MR ? 1 : 2; }
 
     int size() const { return shape.size(); }
     ncclComm_t comm_for(Dist d) const { return d == MC ? mc_comm : d == MR ? mr_comm : world; }

@@ -69,12 +69,24 @@ Grid::Grid(int height, int width, int vc, const ncclUniqueId* id, int dev) {
         } else {
             mr_comm = world;  // one grid row: MR == world
         }
+        if (dev >= 0) arena = PeerArena::Create(world, vc, shape.size(), stream);
     } else if (shape.size() > 1 && dev >= 0) {
         throw EngineError(ELB200_ERR_STATE, "Grid: p > 1 requires an NCCL unique id");
     }
 }
 
+std::vector<int> Grid::comm_members(Dist d) const {
+    std::vector<int> v;
+    if (d == MC) for (int i = 0; i < shape.r; ++i) v.push_back(vc_of(shape, GridCoord{i, me.mr}));
+    else if (d == MR) for (int j = 0; j < shape.c; ++j) v.push_back(vc_of(shape, GridCoord{me.mc, j}));
+    else for (int q = 0; q < shape.size(); ++q) v.push_back(q);
+    return v;
+}
+
 Grid::~Grid() {
+    if (stream) cudaStreamSynchronize(stream);
+    if (comm_stream) cudaStreamSynchronize(comm_stream);
+    delete arena;
     if (mc_comm && mc_comm != world) ncclCommDestroy(mc_comm);
     if (mr_comm && mr_comm != world) ncclCommDestroy(mr_comm);
     if (world) ncclCommDestroy(world);

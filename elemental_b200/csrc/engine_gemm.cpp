@@ -121,20 +121,65 @@ struct Dims { int64_t m, n, k; };
 
 // ---- stationary C: C += alpha op(A)(:,kr) op(B)(kr,:) -----------------------------------------
 template <typename T>
-void SummaC(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, DistMat<T>& C, Dims d) {
+void SummaC(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, T beta, DistMat<T>& C, Dims d) {
+    // `beta` is applied by the FIRST panel's GEMM (C = alpha*a*b + beta*C), later panels accumulate:
+    // the separate Scale(beta, C) pass of the reference (Gemm.cpp:282) — one more read and write of
+    // the whole local C — is folded into the kernel epilogue.  beta == 0 never reads C.
     Grid& g = *C.grid;
     // on a 1 x 1 grid no panel moves: the whole k range is one local GEMM (C is read once)
     const int64_t W = g.size() == 1 ? std::max<int64_t>(d.k, 1) : Grid::PanelWidth(sizeof(T));
-    DistMat<T> PA(g, ta ? STAR : MC, ta ? MC : STAR, C.stream);
-    DistMat<T> PB(g, tb ? MR : STAR, tb ? STAR : MR, C.stream);
-    for (int64_t k0 = 0; k0 < d.k; k0 += W) {
-        const int64_t kb = std::min(W, d.k - k0);
+    static const bool overlap_on = [] { const char* e = std::getenv("ELB200_OVERLAP"); return !(e && std::atoi(e) == 0); }();
+    // An SM-resident NCCL gather fights the persistent GEMM for SMs (measured: slower than no
+    // overlap at all), so the pipeline is used only with the copy-engine peer arena.
+    if (g.size() == 1 || !g.comm_stream || !g.arena || !overlap_on) {
+        DistMat<T> PA(g, ta ? STAR : MC, ta ? MC : STAR, C.stream);
+        DistMat<T> PB(g, tb ? MR : STAR, tb ? STAR : MR, C.stream);
+        for (int64_t k0 = 0; k0 < d.k; k0 += W) {
+            const int64_t kb = std::min(W, d.k - k0);
+            DistMat<T> A1 = ta ? A.View(k0, k0 + kb, 0, d.m) : A.View(0, d.m, k0, k0 + kb);
+            DistMat<T> B1 = tb ? B.View(0, d.n, k0, k0 + kb) : B.View(k0, k0 + kb, 0, d.n);
+            const DistMat<T>& a = panel_as(A1, PA, C.spec);  // [MC,*] (or [*,MC]) aligned with C's rows
+            const DistMat<T>& b = panel_as(B1, PB, C.spec);  // [*,MR] (or [MR,*]) aligned with C's cols
+            LocalGemm(ta, tb, alpha, a, b, k0 == 0 ? beta : T(1), C);
+        }
+        return;
+    }
+    // Software pipeline over two panel slots: the gathers of panel p+1 run on the comm stream
+    // (copy engines + small unpack kernels) while the local GEMM of panel p owns the SMs.
+    //   ready[s]: panel in slot s is complete        (comm stream -> compute stream)
+    //   freed[s]: the GEMM that read slot s is done   (compute stream -> comm stream)
+    cudaStream_t cs = g.comm_stream;
+    DistMat<T> PA[2] = {DistMat<T>(g, ta ? STAR : MC, ta ? MC : STAR, cs), DistMat<T>(g, ta ? STAR : MC, ta ? MC : STAR, cs)};
+    DistMat<T> PB[2] = {DistMat<T>(g, tb ? MR : STAR, tb ? STAR : MR, cs), DistMat<T>(g, tb ? MR : STAR, tb ? STAR : MR, cs)};
+    cudaEvent_t ready[2], freed[2], start;
+    for (int i = 0; i < 2; ++i) {
+        cuda_check(cudaEventCreateWithFlags(&ready[i], cudaEventDisableTiming), "cudaEventCreate");
+        cuda_check(cudaEventCreateWithFlags(&freed[i], cudaEventDisableTiming), "cudaEventCreate");
+    }
+    cuda_check(cudaEventCreateWithFlags(&start, cudaEventDisableTiming), "cudaEventCreate");
+    cuda_check(cudaEventRecord(start, C.stream), "cudaEventRecord");   // A, B, C are ready in C.stream order
+    cuda_check(cudaStreamWaitEvent(cs, start, 0), "cudaStreamWaitEvent");
+    // ramp: the first gather cannot hide behind a GEMM, so the first two panels are narrower
+    const int64_t nbk = Grid::Blocksize();
+    auto width = [&](int64_t p) { return p >= 2 ? W : std::max(nbk, (W >> (2 - p)) / nbk * nbk); };
+    int64_t p = 0;
+    for (int64_t k0 = 0, kb = 0; k0 < d.k; k0 += kb, ++p) {
+        const int s = int(p & 1);
+        kb = std::min(width(p), d.k - k0);
+        if (p >= 2) cuda_check(cudaStreamWaitEvent(cs, freed[s], 0), "cudaStreamWaitEvent");
         DistMat<T> A1 = ta ? A.View(k0, k0 + kb, 0, d.m) : A.View(0, d.m, k0, k0 + kb);
         DistMat<T> B1 = tb ? B.View(0, d.n, k0, k0 + kb) : B.View(k0, k0 + kb, 0, d.n);
-        const DistMat<T>& a = panel_as(A1, PA, C.spec);  // [MC,*] (or [*,MC]) aligned with C's rows
-        const DistMat<T>& b = panel_as(B1, PB, C.spec);  // [*,MR] (or [MR,*]) aligned with C's cols
-        LocalGemm(ta, tb, alpha, a, b, T(1), C);
+        const DistMat<T>& a = panel_as(A1, PA[s], C.spec);
+        const DistMat<T>& b = panel_as(B1, PB[s], C.spec);
+        cuda_check(cudaEventRecord(ready[s], cs), "cudaEventRecord");
+        cuda_check(cudaStreamWaitEvent(C.stream, ready[s], 0), "cudaStreamWaitEvent");
+        LocalGemm(ta, tb, alpha, a, b, p == 0 ? beta : T(1), C);
+        cuda_check(cudaEventRecord(freed[s], C.stream), "cudaEventRecord");
     }
+    // the panels are freed in comm-stream order: not before the last GEMMs have read them
+    for (int i = 0; i < 2 && i < p; ++i) cuda_check(cudaStreamWaitEvent(cs, freed[i], 0), "cudaStreamWaitEvent");
+    for (int i = 0; i < 2; ++i) { cudaEventDestroy(ready[i]); cudaEventDestroy(freed[i]); }
+    cudaEventDestroy(start);
 }
 
 // ---- stationary A: per column panel of C, D1 = alpha op(A) op(B)(:,panel) summed over the
@@ -236,9 +281,12 @@ void Gemm(int ta, int tb, T alpha, const DistMat<T>& Apre, const DistMat<T>& Bpr
     if (d.k != kb || Cpre.spec.height != d.m || Cpre.spec.width != d.n)
         throw EngineError(ELB200_ERR_ARG, "Gemm: nonconformal matrices");
     if (alg == GEMM_CANNON) throw EngineError(ELB200_ERR_ARG, "Cannon_NN: Bad device (CPU only in the reference, Gemm/NN.hpp:30-31)");
-    Scale(beta, Cpre);
-    if (d.m == 0 || d.n == 0 || d.k == 0 || alpha == T(0)) return;
+    if (d.m == 0 || d.n == 0 || d.k == 0 || alpha == T(0)) { Scale(beta, Cpre); return; }
     alg = ResolveGemmAlg(ta, tb, d.m, d.n, d.k, alg);
+    // Stationary-C on a [MC,MR] C applies beta inside its first local GEMM; every other variant
+    // accumulates into C through AxpyContract, so C is scaled up front as in Gemm.cpp:282.
+    const bool fold_beta = alg == GEMM_SUMMA_C && Cpre.spec.col == MC && Cpre.spec.row == MR;
+    if (!fold_beta) Scale(beta, Cpre);
 
     // Read / read-write proxies to [MC,MR] (reference Proxy.hpp:236-257: pass-through when the
     // matrix already has the requested distribution).
@@ -257,7 +305,7 @@ void Gemm(int ta, int tb, T alpha, const DistMat<T>& Apre, const DistMat<T>& Bpr
     switch (alg) {
         case GEMM_SUMMA_A: SummaA(ta, tb, alpha, A, B, C, d); break;
         case GEMM_SUMMA_B: SummaB(ta, tb, alpha, A, B, C, d); break;
-        case GEMM_SUMMA_C: SummaC(ta, tb, alpha, A, B, C, d); break;
+        case GEMM_SUMMA_C: SummaC(ta, tb, alpha, A, B, fold_beta ? beta : T(1), C, d); break;
         case GEMM_SUMMA_DOT: SummaDot(ta, tb, alpha, A, B, C, d); break;
         default: throw EngineError(ELB200_ERR_ARG, "Gemm: unsupported GemmAlgorithm");
     }

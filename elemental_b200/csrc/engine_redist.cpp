@@ -64,6 +64,27 @@ void Copy(const DistMat<T>& A, DistMat<T>& B) {
         const int gsz = int(plan.recvs.size());
         const int64_t mine = plan.sends[0].count();
         // ship straight out of A's local matrix when it is one contiguous full-size block
+        const auto& s0 = plan.sends[0].seg;
+        const bool contiguous = s0.row_step == 1 && s0.col_step == 1 && (A.ldim == s0.rows || s0.cols <= 1);
+        if (g.arena && size_t(gsz) * plan.portion * sizeof(T) <= g.arena->slot_bytes()) {
+            // NVLink peer-memory gather (peer.hpp): copy engines + stream memops, no SM involved,
+            // so it runs underneath the persistent GEMM of the previous panel.
+            const std::vector<int> members = g.comm_members(plan.comm_dist);
+            const int idx = g.comm_index(plan.comm_dist);
+            Scratch<T> slot(contiguous ? 0 : mine, s);
+            const T* send = A.buf + s0.row0 + s0.col0 * A.ldim;
+            if (!contiguous && mine > 0) {
+                Message one = plan.sends[0];
+                one.seg.buf_offset = 0;
+                run_lattice<T>(ELB200_PACK, std::vector<Message>{one}, Abuf, A.ldim, slot.p, T(0), s);
+                send = slot.p;
+            }
+            PeerArena::Ticket t = g.arena->AllGather(Grid::arena_channel(plan.comm_dist), members, idx, send,
+                                                     size_t(mine) * sizeof(T), size_t(plan.portion) * sizeof(T), s);
+            run_lattice<T>(ELB200_UNPACK, plan.recvs, B.buf, B.ldim, static_cast<T*>(t.data), T(0), s);
+            g.arena->Release(t, members, idx, s);
+            return;
+        }
         const bool direct = mine == plan.portion && (A.ldim == plan.sends[0].seg.rows || plan.sends[0].seg.cols <= 1);
         Scratch<T> stage((gsz + (direct ? 0 : 1)) * plan.portion, s);
         T* recv = stage.p;

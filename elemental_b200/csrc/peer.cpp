@@ -1,0 +1,193 @@
+// PeerArena implementation: CUDA IPC mapping of every rank's staging arena, copy-engine
+// transfers, stream memory operations for the cross-GPU handshake. See peer.hpp.
+#include "peer.hpp"
+
+#include <cuda.h>
+#include <unistd.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+
+#include "engine.hpp"
+
+namespace elb {
+namespace {
+
+enum { ARRIVE = 0, ACK = 1 };
+constexpr size_t kFlagWords = size_t(2) * PeerArena::kChannels * PeerArena::kSlots * PeerArena::kMaxRanks;
+constexpr uint32_t kSeqMask = 0xFFFFu;
+
+typedef CUresult (*WaitValue32Fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+
+WaitValue32Fn wait_value_fn() {
+    static WaitValue32Fn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<WaitValue32Fn>(ptr);
+    });
+    return fn;
+}
+
+struct Hello {
+    cudaIpcMemHandle_t arena, flags;
+    unsigned long long host;  // hash of the hostname: IPC only works inside one node
+    int ok;
+    int pad;
+};
+
+unsigned long long host_hash() {
+    char name[256] = {0};
+    gethostname(name, sizeof(name) - 1);
+    unsigned long long h = 1469598103934665603ull;
+    for (const char* p = name; *p; ++p) h = (h ^ (unsigned char)*p) * 1099511628211ull;
+    return h;
+}
+
+}  // namespace
+
+uint32_t* PeerArena::flag(int rank, int kind, int channel, int slot, int src) const {
+    return flags_[rank] + ((size_t(kind) * kChannels + channel) * kSlots + slot) * kMaxRanks + src;
+}
+char* PeerArena::slot_base(int rank, int channel, int slot) const {
+    return arena_[rank] + (size_t(channel) * kSlots + slot) * slot_bytes_;
+}
+
+PeerArena* PeerArena::Create(ncclComm_t world, int rank, int size, cudaStream_t s) {
+    const char* off = std::getenv("ELB200_P2P");
+    if ((off && std::atoi(off) == 0) || size < 2 || size > kMaxRanks || !world) return nullptr;
+    const char* mb = std::getenv("ELB200_ARENA_MB");
+    const size_t slot_bytes = size_t(mb && std::atoll(mb) > 0 ? std::atoll(mb) : 256) << 20;
+
+    PeerArena* pa = new PeerArena();
+    pa->rank_ = rank; pa->size_ = size; pa->slot_bytes_ = slot_bytes;
+    pa->arena_.assign(size, nullptr);
+    pa->flags_.assign(size, nullptr);
+
+    Hello mine;
+    std::memset(&mine, 0, sizeof(mine));
+    mine.host = host_hash();
+    char* arena = nullptr;
+    uint32_t* flags = nullptr;
+    bool ok = wait_value_fn() != nullptr;
+    ok = ok && cudaMalloc(&arena, size_t(kChannels) * kSlots * slot_bytes) == cudaSuccess;
+    ok = ok && cudaMalloc(&flags, kFlagWords * sizeof(uint32_t)) == cudaSuccess;
+    ok = ok && cudaMalloc(&pa->consts_, (kSeqMask + 1) * sizeof(uint32_t)) == cudaSuccess;
+    if (ok) {
+        std::vector<uint32_t> iota(kSeqMask + 1);
+        for (uint32_t i = 0; i <= kSeqMask; ++i) iota[i] = i;
+        ok = cudaMemcpy(pa->consts_, iota.data(), iota.size() * sizeof(uint32_t), cudaMemcpyHostToDevice) == cudaSuccess;
+        ok = ok && cudaMemset(flags, 0, kFlagWords * sizeof(uint32_t)) == cudaSuccess;
+        ok = ok && cudaIpcGetMemHandle(&mine.arena, arena) == cudaSuccess;
+        ok = ok && cudaIpcGetMemHandle(&mine.flags, flags) == cudaSuccess;
+        ok = ok && cudaDeviceSynchronize() == cudaSuccess;
+    }
+    cudaGetLastError();
+    mine.ok = ok ? 1 : 0;
+    pa->arena_[rank] = arena;
+    pa->flags_[rank] = flags;
+
+    // exchange the handles (device-side AllGather of a few hundred bytes over the world comm)
+    std::vector<Hello> all(size);
+    Hello* dev = nullptr;
+    cuda_check(cudaMalloc(&dev, sizeof(Hello) * (size + 1)), "PeerArena hello");
+    cuda_check(cudaMemcpyAsync(dev + size, &mine, sizeof(Hello), cudaMemcpyHostToDevice, s), "PeerArena hello");
+    nccl_check(ncclAllGather(dev + size, dev, sizeof(Hello), ncclChar, world, s), "PeerArena hello");
+    cuda_check(cudaMemcpyAsync(all.data(), dev, sizeof(Hello) * size, cudaMemcpyDeviceToHost, s), "PeerArena hello");
+    cuda_check(cudaStreamSynchronize(s), "PeerArena hello");
+
+    int good = 1;
+    for (int r = 0; r < size; ++r) good = good && all[r].ok && all[r].host == mine.host;
+    if (good) {
+        for (int r = 0; r < size && good; ++r) {
+            if (r == rank) continue;
+            void *pa_ptr = nullptr, *pf_ptr = nullptr;
+            if (cudaIpcOpenMemHandle(&pa_ptr, all[r].arena, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess ||
+                cudaIpcOpenMemHandle(&pf_ptr, all[r].flags, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess)
+                good = 0;
+            pa->arena_[r] = static_cast<char*>(pa_ptr);
+            pa->flags_[r] = static_cast<uint32_t*>(pf_ptr);
+        }
+        cudaGetLastError();
+    }
+    // every rank must take the same decision: min-reduce the local verdicts
+    int* verdict = reinterpret_cast<int*>(dev);
+    cuda_check(cudaMemcpyAsync(verdict, &good, sizeof(int), cudaMemcpyHostToDevice, s), "PeerArena verdict");
+    nccl_check(ncclAllReduce(verdict, verdict, 1, ncclInt, ncclMin, world, s), "PeerArena verdict");
+    cuda_check(cudaMemcpyAsync(&good, verdict, sizeof(int), cudaMemcpyDeviceToHost, s), "PeerArena verdict");
+    cuda_check(cudaStreamSynchronize(s), "PeerArena verdict");
+    cudaFree(dev);
+    if (!good) {
+        if (rank == 0 && std::getenv("ELB200_VERBOSE"))
+            std::fprintf(stderr, "[elb200] peer arena unavailable (IPC mapping failed); redistributions use NCCL\n");
+        delete pa;
+        return nullptr;
+    }
+    return pa;
+}
+
+PeerArena::~PeerArena() {
+    for (int r = 0; r < size_; ++r) {
+        if (r == rank_) continue;
+        if (arena_[r]) cudaIpcCloseMemHandle(arena_[r]);
+        if (flags_[r]) cudaIpcCloseMemHandle(flags_[r]);
+    }
+    if (!arena_.empty() && arena_[rank_]) cudaFree(arena_[rank_]);
+    if (!flags_.empty() && flags_[rank_]) cudaFree(flags_[rank_]);
+    if (consts_) cudaFree(consts_);
+    cudaGetLastError();
+}
+
+void PeerArena::write_flag(uint32_t* dst, uint32_t seq, cudaStream_t s) {
+    // a 4-byte copy-engine write on the same stream as the payload copies: it starts after they
+    // completed, so a peer that sees the flag sees the data
+    cuda_check(cudaMemcpyAsync(dst, consts_ + (seq & kSeqMask), sizeof(uint32_t), cudaMemcpyDeviceToDevice, s),
+               "PeerArena flag write");
+}
+
+void PeerArena::wait_flag(uint32_t* local, uint32_t seq, cudaStream_t s) {
+    // Equality is exact here: a flag advances to seq+1 only after this rank acknowledged seq.
+    const CUresult r = wait_value_fn()(reinterpret_cast<CUstream>(s), reinterpret_cast<CUdeviceptr>(local),
+                                       seq & kSeqMask, CU_STREAM_WAIT_VALUE_EQ);
+    if (r != CUDA_SUCCESS) throw EngineError(ELB200_ERR_CUDA, "cuStreamWaitValue32 failed");
+}
+
+PeerArena::Ticket PeerArena::AllGather(int channel, const std::vector<int>& members, int my_index, const void* send,
+                                       size_t send_bytes, size_t portion_bytes, cudaStream_t s) {
+    const int g = int(members.size());
+    if (portion_bytes * size_t(g) > slot_bytes_ || send_bytes > portion_bytes)
+        throw EngineError(ELB200_ERR_ARG, "PeerArena::AllGather: message larger than an arena slot");
+    const uint64_t n = uses_[channel]++;
+    Ticket t;
+    t.channel = channel;
+    t.slot = int(n & 1);
+    t.seq = uint32_t(n / 2 + 1);
+    // 1. my previous block in each member's slot must have been consumed
+    for (int i = 0; i < g; ++i)
+        if (i != my_index) wait_flag(flag(rank_, ACK, channel, t.slot, members[i]), t.seq - 1, s);
+    // 2. my block into every member's slot (mine included)
+    if (send_bytes)
+        for (int i = 0; i < g; ++i)
+            cuda_check(cudaMemcpyAsync(slot_base(members[i], channel, t.slot) + size_t(my_index) * portion_bytes, send,
+                                       send_bytes, cudaMemcpyDeviceToDevice, s), "PeerArena copy");
+    // 3. tell them, 4. wait for theirs
+    for (int i = 0; i < g; ++i)
+        if (i != my_index) write_flag(flag(members[i], ARRIVE, channel, t.slot, rank_), t.seq, s);
+    for (int i = 0; i < g; ++i)
+        if (i != my_index) wait_flag(flag(rank_, ARRIVE, channel, t.slot, members[i]), t.seq, s);
+    t.data = slot_base(rank_, channel, t.slot);
+    return t;
+}
+
+void PeerArena::Release(const Ticket& t, const std::vector<int>& members, int my_index, cudaStream_t s) {
+    const int g = int(members.size());
+    for (int i = 0; i < g; ++i)
+        if (i != my_index) write_flag(flag(members[i], ACK, t.channel, t.slot, rank_), t.seq, s);
+}
+
+}  // namespace elb

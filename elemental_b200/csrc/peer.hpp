@@ -1,0 +1,60 @@
+// PeerArena: AllGather over NVLink peer memory with ZERO SMs.
+//
+// The reference gathers SUMMA panels with an NCCL (Aluminum) AllGather kernel
+// (src/core/imports/mpi/AllGather.hpp:8-21 <- Copy/RowAllGather.hpp:58-75, ColAllGather.hpp).
+// An SM-resident collective cannot overlap a persistent GEMM that owns every SM, so here each
+// rank owns a symmetric staging arena in HBM, maps every peer's arena through CUDA IPC, and a
+// gather is
+//     copy engine: my block -> slot[my index] in EVERY member's arena   (cudaMemcpyAsync, NVLink)
+//     copy engine: arrival flag -> every member                         (4-byte write, same stream)
+//     stream memop: wait until every member's flag shows this sequence  (cuStreamWaitValue32)
+// and, once the consumer (one unpack kernel) has run, an ack flag the other way so a slot is never
+// overwritten before it was read.  Nothing spins on an SM and no kernel is launched for the
+// transfer; the waits are stream memory operations, so only the calling stream blocks.
+#pragma once
+#include <cuda_runtime.h>
+#include <nccl.h>
+
+#include <cstdint>
+#include <vector>
+
+namespace elb {
+
+class PeerArena {
+public:
+    enum { kChannels = 3, kSlots = 2, kMaxRanks = 64 };  // channel: 0 = MC comm, 1 = MR comm, 2 = VC (world)
+    struct Ticket {
+        void* data = nullptr;  // local gathered buffer: member i's block at i * portion_bytes
+        int channel = 0, slot = 0;
+        uint32_t seq = 0;
+    };
+
+    // Collective over all `size` ranks of `world` (one process per GPU, same node). Returns nullptr
+    // — on every rank alike — when peer mapping is not possible; callers then use NCCL.
+    static PeerArena* Create(ncclComm_t world, int rank, int size, cudaStream_t s);
+    ~PeerArena();
+
+    size_t slot_bytes() const { return slot_bytes_; }
+    // Collective over `members` (VC ranks in communicator order; members[my_index] == this rank).
+    // All members pass the same channel and portion_bytes; send_bytes <= portion_bytes may differ.
+    Ticket AllGather(int channel, const std::vector<int>& members, int my_index, const void* send,
+                     size_t send_bytes, size_t portion_bytes, cudaStream_t s);
+    // Call after the last read of ticket.data has been enqueued on `s`.
+    void Release(const Ticket& t, const std::vector<int>& members, int my_index, cudaStream_t s);
+
+private:
+    PeerArena() = default;
+    uint32_t* flag(int rank, int kind, int channel, int slot, int src) const;
+    char* slot_base(int rank, int channel, int slot) const;
+    void write_flag(uint32_t* dst, uint32_t seq, cudaStream_t s);
+    void wait_flag(uint32_t* local, uint32_t seq, cudaStream_t s);
+
+    int rank_ = 0, size_ = 1;
+    size_t slot_bytes_ = 0;
+    std::vector<char*> arena_;       // per rank: base of its arena as mapped in THIS process
+    std::vector<uint32_t*> flags_;   // per rank: base of its flag block
+    uint32_t* consts_ = nullptr;     // consts_[i] == i, source of the 4-byte flag writes
+    uint64_t uses_[kChannels] = {0, 0, 0};
+};
+
+}  // namespace elb
