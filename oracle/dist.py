@@ -5,11 +5,13 @@ Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl refere
 this package.  Every function cites the reference file:line it restates (paths relative to the
 reference tree).  p "virtual ranks" live in one process: a collective is a loop over ranks.
 
-Parity status: the reference stores no golden vectors for this path; these
-restatements are pinned (a) against fixtures produced by the reference's own CPU code compiled
-here (oracle/_ref, tests/golden/, see oracle/README.md) for the single-rank cases it can run, and
-(b) against the exact-equality procedure of the reference's tests/core/DistMatrix.cpp:12-76
-(every redistribution must reproduce the [*,*] gather bit for bit).
+Parity status: PINNED.  The reference stores no golden vectors for this path, so
+the fixtures under tests/golden/ were produced by the reference's own CPU code compiled here
+(oracle/ref_build -> oracle/_ref, see oracle/README.md): single-rank El::Gemm outputs and index
+tables, and MULTI-RANK runs (1x2, 2x1, 2x2, 2x3, 3x2, 2x4 grids over a small multi-process MPI
+stub) giving the per-rank local matrices after all 121 redistributions and after El::Gemm.
+tests/test_oracle.py checks this restatement against them: redistributions bit for bit on every
+rank, Gemm within the north-star tolerance.
 """
 from __future__ import annotations
 

@@ -77,7 +77,57 @@ def main() -> int:
         np.savez_compressed(os.path.join(OUT, "ref_indexing.npz"), L=np.array(L, dtype=np.int64),
                             H=np.array(H, dtype=np.int64))
     print(f"wrote {len(meta)} Gemm cases, {len(L)} index rows, {len(H)} grid heights to {OUT}")
+    make_dist_golden()
     return 0
+
+
+DIST_GRIDS = [(2, 1), (2, 2), (4, 2), (6, 2), (6, 3), (8, 2)]  # (processes, grid height)
+
+
+def make_dist_golden() -> None:
+    """The reference run MULTI-RANK (oracle/ref_build/stub/mpi_stub.cpp: one process per rank over a
+    shared-memory file): per-rank local matrices after each of the 121 (U,V)->(U2,V2)
+    redistributions and after 20 El::Gemm runs, on 1x2, 2x1, 2x2, 2x3, 3x2 and 2x4 grids.
+    tests/golden/ref_dist.npz, per grid tag g = f"r{r}c{c}" and rank q:
+      {g}_q{q}_I    [rank, height, width, row, col, vcRank, vrRank]
+      {g}_q{q}_R    rows [U V U2 V2 caA raA caB raB colShiftB rowShiftB lh lw offset]   (El::Dist enum values)
+      {g}_q{q}_G    rows [id oa ob alg m n k nb caC raC colShift rowShift lh lw offset]
+      {g}_q{q}_bin  float64 blob the offsets index into (column-major local matrices)"""
+    arrays = {}
+    for (nproc, height) in DIST_GRIDS:
+        tag = f"r{height}c{nproc // height}"
+        with tempfile.TemporaryDirectory() as tmp:
+            shm = f"/dev/shm/elb_stub_{os.getpid()}_{tag}"
+            if os.path.exists(shm):
+                os.remove(shm)
+            procs = []
+            for q in range(nproc):
+                env = dict(os.environ, ELB_STUB_NP=str(nproc), ELB_STUB_RANK=str(q), ELB_STUB_SHM=shm,
+                           OPENBLAS_NUM_THREADS="1")
+                procs.append(subprocess.Popen([REF_BIN, "--dist-golden", tmp, str(height)], env=env,
+                                              stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True))
+            try:
+                for q, pr in enumerate(procs):
+                    _, err = pr.communicate(timeout=300)
+                    assert pr.returncode == 0, f"{tag} rank {q}: {err[-2000:]}"
+            finally:
+                for pr in procs:
+                    if pr.poll() is None:
+                        pr.kill()
+                if os.path.exists(shm):
+                    os.remove(shm)
+            for q in range(nproc):
+                recs = {"I": [], "R": [], "G": []}
+                for ln in open(os.path.join(tmp, f"rank{q}.txt")):
+                    f = ln.split()
+                    recs[f[0]].append([int(x) for x in f[1:]])
+                assert len(recs["R"]) == 121 and len(recs["G"]) == 20, (tag, q)
+                arrays[f"{tag}_q{q}_I"] = np.array(recs["I"][0], dtype=np.int64)
+                arrays[f"{tag}_q{q}_R"] = np.array(recs["R"], dtype=np.int64)
+                arrays[f"{tag}_q{q}_G"] = np.array(recs["G"], dtype=np.int64)
+                arrays[f"{tag}_q{q}_bin"] = np.fromfile(os.path.join(tmp, f"rank{q}.bin"), dtype=np.float64)
+    np.savez_compressed(os.path.join(OUT, "ref_dist.npz"), **arrays)
+    print(f"wrote multi-rank reference runs for grids {[f'{h}x{n // h}' for n, h in DIST_GRIDS]}")
 
 
 if __name__ == "__main__":

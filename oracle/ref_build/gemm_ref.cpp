@@ -3,6 +3,8 @@
 // linked against the OpenBLAS found in the image. Nothing here is on the product path.
 //
 //   gemm_ref --bench f32|f64 n         time El::Gemm(NORMAL,NORMAL,0.5,A,B,-0.5,C,GEMM_SUMMA_C), nb=128
+//   gemm_ref --dist-golden <dir> <r>   multi-rank (ELB_STUB_NP processes): per-rank local matrices after all
+//                                      121 redistributions and 20 El::Gemm runs on an r x (NP/r) grid
 //   gemm_ref --golden <dir>            write inputs + reference outputs of a fixed list of small
 //                                      cases (all orientations x GemmAlgorithm, ragged sizes) and
 //                                      tables of the index functions, as raw little-endian files
@@ -87,8 +89,102 @@ static void golden_cases(const std::string& dir, const char* tname, std::ofstrea
                 }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Multi-rank golden run (ELB_STUB_NP processes over stub/mpi_stub.cpp): what the REFERENCE puts
+// on every rank after each (U,V) -> (U2,V2) redistribution and after El::Gemm on an r x c grid.
+// Every rank appends to <dir>/rank<q>.txt (records) and <dir>/rank<q>.bin (column-major doubles).
+// ---------------------------------------------------------------------------------------------
+struct DistOut {
+    std::ofstream txt, bin;
+    long offset = 0;
+    void blob(const Matrix<double>& M) {
+        for (Int j = 0; j < M.Width(); ++j)
+            bin.write(reinterpret_cast<const char*>(M.LockedBuffer(0, j)), sizeof(double) * M.Height());
+        offset += long(M.Height()) * M.Width();
+    }
+};
+
+static double entry(Int i, Int j, Int w) { return 1.0 + double(i) * w + j; }
+
+template <Dist U, Dist V, Dist U2, Dist V2>
+static void redist_case(const Grid& g, DistOut& out) {
+    const Int h = 13, w = 11;
+    DistMatrix<double, U, V> A(g);
+    A.Align(1 % A.ColStride(), 2 % A.RowStride());
+    A.Resize(h, w);
+    for (Int j = 0; j < A.LocalWidth(); ++j)
+        for (Int i = 0; i < A.LocalHeight(); ++i) A.SetLocal(i, j, entry(A.GlobalRow(i), A.GlobalCol(j), w));
+    DistMatrix<double, U2, V2> B(g);
+    B.Align(3 % B.ColStride(), 1 % B.RowStride());
+    B = A;
+    out.txt << "R " << int(U) << " " << int(V) << " " << int(U2) << " " << int(V2) << " " << A.ColAlign() << " "
+            << A.RowAlign() << " " << B.ColAlign() << " " << B.RowAlign() << " " << B.ColShift() << " " << B.RowShift()
+            << " " << B.LocalHeight() << " " << B.LocalWidth() << " " << out.offset << "\n";
+    out.blob(B.LockedMatrix());
+}
+template <Dist U, Dist V>
+static void redist_from(const Grid& g, DistOut& out) {
+    redist_case<U, V, MC, MR>(g, out);   redist_case<U, V, MR, MC>(g, out);
+    redist_case<U, V, MC, STAR>(g, out); redist_case<U, V, STAR, MC>(g, out);
+    redist_case<U, V, MR, STAR>(g, out); redist_case<U, V, STAR, MR>(g, out);
+    redist_case<U, V, VC, STAR>(g, out); redist_case<U, V, STAR, VC>(g, out);
+    redist_case<U, V, VR, STAR>(g, out); redist_case<U, V, STAR, VR>(g, out);
+    redist_case<U, V, STAR, STAR>(g, out);
+}
+
+static void fill_global_lcg(DistMatrix<double>& A, Int h, Int w, unsigned seed) {
+    Matrix<double> G(h, w);
+    fill_lcg(G, seed);  // every rank generates the same global matrix and keeps its own entries
+    A.Resize(h, w);
+    for (Int j = 0; j < A.LocalWidth(); ++j)
+        for (Int i = 0; i < A.LocalHeight(); ++i) A.SetLocal(i, j, G.Get(A.GlobalRow(i), A.GlobalCol(j)));
+}
+
+static void dist_golden(const std::string& dir, int gridHeight) {
+    const int rank = mpi::Rank(mpi::COMM_WORLD);
+    const Grid g(mpi::NewWorldComm(), gridHeight);
+    DistOut out;
+    out.txt.open(dir + "/rank" + std::to_string(rank) + ".txt");
+    out.bin.open(dir + "/rank" + std::to_string(rank) + ".bin", std::ios::binary);
+    out.txt << "I " << rank << " " << g.Height() << " " << g.Width() << " " << g.Row() << " " << g.Col() << " "
+            << g.VCRank() << " " << g.VRRank() << "\n";
+    redist_from<MC, MR>(g, out);   redist_from<MR, MC>(g, out);
+    redist_from<MC, STAR>(g, out); redist_from<STAR, MC>(g, out);
+    redist_from<MR, STAR>(g, out); redist_from<STAR, MR>(g, out);
+    redist_from<VC, STAR>(g, out); redist_from<STAR, VC>(g, out);
+    redist_from<VR, STAR>(g, out); redist_from<STAR, VR>(g, out);
+    redist_from<STAR, STAR>(g, out);
+
+    const Int m = 37, n = 29, k = 53, nb = 16;
+    const Orientation os[2] = {NORMAL, TRANSPOSE};
+    const GemmAlgorithm algs[] = {GEMM_DEFAULT, GEMM_SUMMA_A, GEMM_SUMMA_B, GEMM_SUMMA_C, GEMM_SUMMA_DOT};
+    int id = 0;
+    for (int ia = 0; ia < 2; ++ia)
+        for (int ib = 0; ib < 2; ++ib)
+            for (GemmAlgorithm alg : algs) {
+                DistMatrix<double> A(g), B(g), C(g);
+                A.Align(1 % g.Height(), 2 % g.Width());
+                B.Align(0, 1 % g.Width());
+                C.Align(1 % g.Height(), 0);
+                fill_global_lcg(A, ia ? k : m, ia ? m : k, 3 * id + 0);
+                fill_global_lcg(B, ib ? n : k, ib ? k : n, 3 * id + 1);
+                fill_global_lcg(C, m, n, 3 * id + 2);
+                SetBlocksize(nb);
+                Gemm(os[ia], os[ib], 2.0, A, B, 3.0, C, alg);
+                out.txt << "G " << id << " " << ia << " " << ib << " " << int(alg) << " " << m << " " << n << " " << k << " "
+                        << nb << " " << C.ColAlign() << " " << C.RowAlign() << " " << C.ColShift() << " " << C.RowShift()
+                        << " " << C.LocalHeight() << " " << C.LocalWidth() << " " << out.offset << "\n";
+                out.blob(C.LockedMatrix());
+                ++id;
+            }
+}
+
 int main(int argc, char* argv[]) {
     Environment env(argc, argv);
+    if (argc >= 4 && !std::strcmp(argv[1], "--dist-golden")) {
+        dist_golden(argv[2], std::atoi(argv[3]));
+        return 0;
+    }
     if (argc >= 4 && !std::strcmp(argv[1], "--bench")) {
         const Int n = std::atoi(argv[3]);
         const double t = !std::strcmp(argv[2], "f32") ? bench<float>(n) : bench<double>(n);
@@ -113,6 +209,6 @@ int main(int argc, char* argv[]) {
         for (int p = 1; p <= 64; ++p) tab << "H " << p << " " << Grid::DefaultHeight(p) << "\n";
         return 0;
     }
-    std::printf("usage: gemm_ref --bench f32|f64 n | --golden dir\n");
+    std::printf("usage: gemm_ref --bench f32|f64 n | --golden dir | --dist-golden dir gridHeight (under ELB_STUB_NP)\n");
     return 64;
 }

@@ -151,3 +151,78 @@ def test_axpy_contract_sums_contributions():
     Bd = OD.VDM.from_global(g, B0, OD.MC, OD.MR)
     OD.axpy_contract(2.0, parts, Bd)
     assert np.allclose(Bd.to_global(), B0 + 2.0 * total, rtol=0, atol=1e-13)
+
+
+# ---------------------------------------------------------------------------------------------
+# Multi-rank pinning: tests/golden/ref_dist.npz holds what the REFERENCE ITSELF placed on every
+# rank (run multi-process over oracle/ref_build/stub/mpi_stub.cpp, see oracle/make_golden.py).
+# ---------------------------------------------------------------------------------------------
+EL_DIST = {0: OD.MC, 2: OD.MR, 3: OD.VC, 4: OD.VR, 5: OD.STAR}  # El::Dist enum value -> oracle constant
+DIST_TAGS = ["r1c2", "r2c1", "r2c2", "r2c3", "r3c2", "r2c4"]
+
+
+@pytest.fixture(scope="module")
+def gold_dist():
+    return np.load(os.path.join(GOLD, "ref_dist.npz"))
+
+
+def _ranks(gold, tag):
+    r, c = int(tag[1]), int(tag[3])
+    return OD.Grid(r, c), [q for q in range(r * c)]
+
+
+@pytest.mark.parametrize("tag", DIST_TAGS)
+def test_grid_rank_maps_match_reference(gold_dist, tag):
+    """Row / Col / VCRank / VRRank of every process as El::Grid computes them (Grid.cpp:143-148)."""
+    g, ranks = _ranks(gold_dist, tag)
+    for q in ranks:
+        rank, h, w, row, col, vc, vr = (int(x) for x in gold_dist[f"{tag}_q{q}_I"])
+        assert (h, w) == (g.r, g.c)
+        assert g.coords(vc) == (row, col)
+        assert g.vc(row, col) == vc and g.vr(row, col) == vr
+
+
+@pytest.mark.parametrize("tag", DIST_TAGS)
+def test_redistribution_placement_matches_reference(gold_dist, tag):
+    """All 121 (U,V)->(U2,V2) pairs with non-zero alignments: the oracle's per-rank local matrices,
+    shifts and local shapes equal the reference's, bit for bit, on every rank."""
+    g, ranks = _ranks(gold_dist, tag)
+    G = np.arange(13 * 11, dtype=np.float64).reshape(13, 11) + 1.0
+    checked = 0
+    for q in ranks:
+        vc = int(gold_dist[f"{tag}_q{q}_I"][5])
+        blob = gold_dist[f"{tag}_q{q}_bin"]
+        for (U, V, U2, V2, caA, raA, caB, raB, csB, rsB, lh, lw, off) in gold_dist[f"{tag}_q{q}_R"]:
+            A = OD.VDM.from_global(g, G, EL_DIST[int(U)], EL_DIST[int(V)], int(caA), int(raA))
+            B = OD.redistribute(A, EL_DIST[int(U2)], EL_DIST[int(V2)], int(caB), int(raB))
+            assert (B.spec.col_shift(g, vc), B.spec.row_shift(g, vc)) == (csB, rsB)
+            assert B.loc[vc].shape == (lh, lw)
+            ref = blob[off:off + lh * lw].reshape((lh, lw), order="F")
+            assert np.array_equal(B.loc[vc], ref), (tag, q, U, V, U2, V2)
+            checked += 1
+    assert checked == 121 * g.p
+
+
+@pytest.mark.parametrize("tag", DIST_TAGS)
+def test_distributed_gemm_matches_reference_per_rank(gold_dist, tag):
+    """20 El::Gemm runs of the reference per grid (NN/NT/TN/TT x {DEFAULT, SUMMA_A, B, C, DOT},
+    aligned A, B, C, nb = 16): the oracle's SUMMA restatement gives the same local C on each rank
+    within the fp64 bound (summation order differs inside BLAS and the reductions)."""
+    g, ranks = _ranks(gold_dist, tag)
+    aligns = ((1 % g.r, 2 % g.c), (0, 1 % g.c), (1 % g.r, 0))
+    cache = {}
+    for q in ranks:
+        vc = int(gold_dist[f"{tag}_q{q}_I"][5])
+        blob = gold_dist[f"{tag}_q{q}_bin"]
+        for (cid, oa, ob, alg, m, n, k, nb, caC, raC, cs, rs, lh, lw, off) in (tuple(int(x) for x in r) for r in gold_dist[f"{tag}_q{q}_G"]):
+            if cid not in cache:
+                A = lcg_matrix(*((k, m) if oa else (m, k)), 3 * cid + 0, np.float64)
+                B = lcg_matrix(*((n, k) if ob else (k, n)), 3 * cid + 1, np.float64)
+                C0 = lcg_matrix(m, n, 3 * cid + 2, np.float64)
+                cache[cid] = OG.dist_gemm(g, oa, ob, 2.0, A, B, 3.0, C0, alg, nb=nb, aligns=aligns)
+            spec = OD.Spec(OD.MC, OD.MR, caC, raC, m, n)
+            assert (caC, raC) == aligns[2]
+            mine = OD.local_of(cache[cid], spec, g, vc)
+            ref = blob[off:off + lh * lw].reshape((lh, lw), order="F")
+            assert mine.shape == ref.shape
+            assert OG.frobenius_rel_err(mine, ref) <= OG.gemm_tolerance(np.float64, k), (tag, q, cid)
