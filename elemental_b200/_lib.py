@@ -98,6 +98,8 @@ SIGNATURES = {
     "elb200_fill2d_f64": (ci, [i64, i64, f64, vp, i64, vp]),
     "elb200_lattice_f32": (ci, [ci, ci, C.POINTER(Segment), vp, i64, vp, f32, vp]),
     "elb200_lattice_f64": (ci, [ci, ci, C.POINTER(Segment), vp, i64, vp, f64, vp]),
+    "elb200_peer_reduce_axpy_f32": (ci, [ci, C.POINTER(vp), i64, C.POINTER(Segment), vp, i64, f32, vp]),
+    "elb200_peer_reduce_axpy_f64": (ci, [ci, C.POINTER(vp), i64, C.POINTER(Segment), vp, i64, f64, vp]),
     "elb200_plan_copy": (ci, [ci, ci, ci, C.POINTER(DistSpec), C.POINTER(DistSpec), C.POINTER(CopyPlan)]),
     "elb200_plan_contract": (ci, [ci, ci, ci, C.POINTER(DistSpec), C.POINTER(DistSpec), C.POINTER(ContractPlan)]),
     "elb200_shift": (i64, [i64, i64, i64]),
@@ -135,6 +137,8 @@ SIGNATURES = {
     "elb200_dm_transpose_axpy_contract": (ci, [f64, vp, vp]),
     "elb200_dm_local_gemm": (ci, [ci, ci, f64, vp, vp, f64, vp]),
     "elb200_dist_gemm": (ci, [ci, ci, f64, vp, vp, f64, vp, ci]),
+    "elb200_dist_gemm_host_f32": (ci, [vp, ci, ci, i64, i64, i64, f32, vp, i64, vp, i64, f32, vp, i64]),
+    "elb200_dist_gemm_host_f64": (ci, [vp, ci, ci, i64, i64, i64, f64, vp, i64, vp, i64, f64, vp, i64]),
 }
 
 for _name, (_res, _args) in SIGNATURES.items():

@@ -207,18 +207,18 @@ lattice_kernel(const __grid_constant__ SegTable tab, T* M, int64_t ldm, T* buf, 
     constexpr int N = sizeof(V) / sizeof(T);
     const elb200_segment sg = tab.seg[blockIdx.z];
     const int64_t rows_v = sg.rows / N;
-    const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-    if (i >= rows_v) return;
-    const int64_t row_off = (N == 1) ? sg.row0 + i * sg.row_step : sg.row0 + i * N;
-    for (int64_t j = int64_t(blockIdx.y) * blockDim.y + threadIdx.y; j < sg.cols;
-         j += int64_t(gridDim.y) * blockDim.y) {
-        V* mp = reinterpret_cast<V*>(M + row_off + (sg.col0 + j * sg.col_step) * ldm);
-        V* bp = reinterpret_cast<V*>(buf + sg.buf_offset + i * N + j * sg.rows);
-        if constexpr (MODE == ELB200_PACK) *bp = *mp;
-        else if constexpr (MODE == ELB200_UNPACK) *mp = *bp;
-        else {
-            if constexpr (N == 1) *mp = fma(alpha, *bp, *mp);
-            else *mp = vaxpy(alpha, *bp, *mp);
+    for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < rows_v; i += int64_t(gridDim.x) * blockDim.x) {
+        const int64_t row_off = (N == 1) ? sg.row0 + i * sg.row_step : sg.row0 + i * N;
+        for (int64_t j = int64_t(blockIdx.y) * blockDim.y + threadIdx.y; j < sg.cols;
+             j += int64_t(gridDim.y) * blockDim.y) {
+            V* mp = reinterpret_cast<V*>(M + row_off + (sg.col0 + j * sg.col_step) * ldm);
+            V* bp = reinterpret_cast<V*>(buf + sg.buf_offset + i * N + j * sg.rows);
+            if constexpr (MODE == ELB200_PACK) *bp = *mp;
+            else if constexpr (MODE == ELB200_UNPACK) *mp = *bp;
+            else {
+                if constexpr (N == 1) *mp = fma(alpha, *bp, *mp);
+                else *mp = vaxpy(alpha, *bp, *mp);
+            }
         }
     }
 }
@@ -250,9 +250,18 @@ int launch_lattice(int mode, int nseg, const elb200_segment* segs, T* M, int64_t
     int bx = 32;
     while (bx < 256 && bx < rows_v) bx <<= 1;
     const int by = 256 / bx;
+    int64_t gx = (rows_v + bx - 1) / bx;
     int64_t gy = (max_cols + by - 1) / by;
     if (gy > 1024) gy = 1024;
-    dim3 grid(unsigned((rows_v + bx - 1) / bx), unsigned(gy), unsigned(n));
+    // Background mode (set by the engine while a redistribution runs underneath a local GEMM):
+    // a handful of CTAs that grid-stride over the lattice, so the copy touches few SMs.
+    const int cap = lattice_cta_limit();
+    if (cap > 0) {
+        const int64_t per_seg = std::max<int64_t>(1, cap / n);
+        if (gx > per_seg) gx = per_seg;
+        if (gx * gy > per_seg) gy = std::max<int64_t>(1, per_seg / gx);
+    }
+    dim3 grid(static_cast<unsigned>(gx), static_cast<unsigned>(gy), static_cast<unsigned>(n));
     dim3 block(bx, by);
     count_launch();
 #define ELB_LAT(MODE_)                                                                  \
@@ -263,6 +272,45 @@ int launch_lattice(int mode, int nseg, const elb200_segment* segs, T* M, int64_t
     else { ELB_LAT(ELB200_UNPACK_AXPY) }
 #undef ELB_LAT
     return check_cuda(cudaGetLastError(), "lattice_kernel");
+}
+
+// B-lattice += alpha * sum over sources of their packed block: the ReduceScatter of AxpyContract
+// done by the RECEIVER with loads over NVLink peer mappings, fused with the axpy-unpack.
+// Sources are summed in communicator order on every rank (deterministic).
+template <typename T>
+struct PeerSources {
+    const T* p[ELB200_MAX_SEGMENTS];
+    int n;
+};
+template <typename T>
+__global__ void __launch_bounds__(256)
+peer_reduce_axpy_kernel(const __grid_constant__ PeerSources<T> src, int64_t off, const elb200_segment sg, T* M,
+                        int64_t ldm, T alpha) {
+    for (int64_t j = blockIdx.y; j < sg.cols; j += gridDim.y)
+        for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < sg.rows; i += int64_t(gridDim.x) * blockDim.x) {
+            const int64_t e = off + i + j * sg.rows;
+            T sum = T(0);
+            for (int s = 0; s < src.n; ++s) sum += src.p[s][e];
+            T* mp = M + sg.row0 + i * sg.row_step + (sg.col0 + j * sg.col_step) * ldm;
+            *mp = fma(alpha, sum, *mp);
+        }
+}
+template <typename T>
+int peer_reduce_axpy(int nsrc, const T* const* srcs, int64_t off, const elb200_segment* seg, T* M, int64_t ldm, T alpha,
+                     void* stream) {
+    if (nsrc < 1 || nsrc > ELB200_MAX_SEGMENTS || !srcs || !seg || seg->rows < 0 || seg->cols < 0 || seg->row_step < 1 ||
+        seg->col_step < 1)
+        return ELB200_ERR_ARG;
+    if (seg->rows == 0 || seg->cols == 0) return ELB200_OK;
+    PeerSources<T> ps;
+    ps.n = nsrc;
+    for (int i = 0; i < nsrc; ++i) ps.p[i] = srcs[i];
+    const int64_t gx = std::min<int64_t>((seg->rows + 255) / 256, 64);
+    const int64_t gy = std::min<int64_t>(seg->cols, std::max<int64_t>(1, 4 * device_sm_count() / gx));
+    count_launch();
+    peer_reduce_axpy_kernel<T><<<dim3(static_cast<unsigned>(gx), static_cast<unsigned>(gy)), 256, 0,
+                                 static_cast<cudaStream_t>(stream)>>>(ps, off, *seg, M, ldm, alpha);
+    return check_cuda(cudaGetLastError(), "peer_reduce_axpy_kernel");
 }
 
 template <typename T>
@@ -299,6 +347,14 @@ using namespace elb;
 
 extern "C" {
 
+int elb200_peer_reduce_axpy_f32(int nsrc, const float* const* srcs, int64_t src_offset, const elb200_segment* seg,
+                                float* M, int64_t ldm, float alpha, void* stream) {
+    return peer_reduce_axpy<float>(nsrc, srcs, src_offset, seg, M, ldm, alpha, stream);
+}
+int elb200_peer_reduce_axpy_f64(int nsrc, const double* const* srcs, int64_t src_offset, const elb200_segment* seg,
+                                double* M, int64_t ldm, double alpha, void* stream) {
+    return peer_reduce_axpy<double>(nsrc, srcs, src_offset, seg, M, ldm, alpha, stream);
+}
 int elb200_copy2d_f32(int64_t rows, int64_t cols, const float* src, int64_t srs, int64_t scs,
                       float* dst, int64_t drs, int64_t dcs, void* stream) {
     return copy2d<float>(rows, cols, src, srs, scs, dst, drs, dcs, stream);

@@ -12,10 +12,13 @@ void set_last_error(const char* what, const char* detail);
 using namespace elb;
 
 struct elb200_grid_s {
-    std::unique_ptr<Grid> g;
+    std::shared_ptr<Grid> g;
 };
 struct elb200_dm_s {
     int dtype;
+    // keeps the Grid (its streams) alive until the matrix is gone, whatever order the caller
+    // destroys handles in; declared before f/d so that it is released after them
+    std::shared_ptr<Grid> keep;
     std::unique_ptr<DistMat<float>> f;
     std::unique_ptr<DistMat<double>> d;
     Grid* grid() const { return dtype == ELB200_F32 ? f->grid : d->grid; }
@@ -131,13 +134,15 @@ int elb200_grid_create(int height, int width, int vc, const void* id128, int dev
         ncclUniqueId id;
         if (id128) std::memcpy(&id, id128, sizeof(id));
         auto h = std::make_unique<elb200_grid_s>();
-        h->g = std::make_unique<Grid>(height, width, vc, id128 ? &id : nullptr, device);
+        h->g = std::make_shared<Grid>(height, width, vc, id128 ? &id : nullptr, device);
         *out = h.release();
     });
 }
 int elb200_grid_destroy(elb200_grid_t g) {
     if (!g) return ELB200_OK;
-    return guarded("elb200_grid_destroy", [&] { delete g; });
+    // Collective part now (peer arena unmap + barrier, NCCL communicators); the streams live on
+    // until the last DistMatrix handle of this grid is destroyed.
+    return guarded("elb200_grid_destroy", [&] { g->g->Shutdown(); delete g; });
 }
 int elb200_grid_info(elb200_grid_t g, int* h, int* w, int* vc, int* mc, int* mr) {
     if (!g) return ELB200_ERR_ARG;
@@ -170,6 +175,7 @@ int elb200_dm_create(elb200_grid_t g, int dtype, int col, int row, elb200_dm_t* 
     return guarded("elb200_dm_create", [&] {
         auto h = std::make_unique<elb200_dm_s>();
         h->dtype = dtype;
+        h->keep = g->g;
         if (dtype == ELB200_F32) h->f = std::make_unique<DistMat<float>>(*g->g, Dist(col), Dist(row));
         else h->d = std::make_unique<DistMat<double>>(*g->g, Dist(col), Dist(row));
         *out = h.release();
@@ -223,6 +229,7 @@ int elb200_dm_view(elb200_dm_t a, int64_t i0, int64_t i1, int64_t j0, int64_t j1
     return guarded("elb200_dm_view", [&] {
         auto h = std::make_unique<elb200_dm_s>();
         h->dtype = a->dtype;
+        h->keep = a->keep;
         if (a->dtype == ELB200_F32) h->f = std::make_unique<DistMat<float>>(a->f->View(i0, i1, j0, j1));
         else h->d = std::make_unique<DistMat<double>>(a->d->View(i0, i1, j0, j1));
         *out = h.release();
@@ -262,6 +269,19 @@ int elb200_dist_gemm(int ta, int tb, double alpha, elb200_dm_t A, elb200_dm_t B,
         if (A->dtype == ELB200_F32) Gemm(ta, tb, float(alpha), *A->f, *B->f, float(beta), *C->f, alg);
         else Gemm(ta, tb, alpha, *A->d, *B->d, beta, *C->d, alg);
     });
+}
+
+int elb200_dist_gemm_host_f32(elb200_grid_t g, int ta, int tb, int64_t m, int64_t n, int64_t k, float alpha,
+                              const float* A, int64_t lda, const float* B, int64_t ldb, float beta, float* C,
+                              int64_t ldc) {
+    if (!g || ta < 0 || ta > 2 || tb < 0 || tb > 2) return ELB200_ERR_ARG;
+    return guarded("elb200_dist_gemm_host_f32", [&] { GemmHost<float>(*g->g, ta, tb, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc); });
+}
+int elb200_dist_gemm_host_f64(elb200_grid_t g, int ta, int tb, int64_t m, int64_t n, int64_t k, double alpha,
+                              const double* A, int64_t lda, const double* B, int64_t ldb, double beta, double* C,
+                              int64_t ldc) {
+    if (!g || ta < 0 || ta > 2 || tb < 0 || tb > 2) return ELB200_ERR_ARG;
+    return guarded("elb200_dist_gemm_host_f64", [&] { GemmHost<double>(*g->g, ta, tb, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc); });
 }
 
 }  // extern "C"

@@ -36,6 +36,9 @@ public:
     // nccl_id == nullptr: a grid without communicators (p must be 1, or plan-only use).
     Grid(int height, int width, int vc_rank, const ncclUniqueId* nccl_id, int device);
     ~Grid();
+    // Collective teardown (peer arena, NCCL communicators); idempotent. The streams stay usable,
+    // so matrices of this grid can still be destroyed afterwards.
+    void Shutdown();
     Grid(const Grid&) = delete;
     Grid& operator=(const Grid&) = delete;
 
@@ -45,6 +48,7 @@ public:
     int device = 0;
     cudaStream_t stream = nullptr;       // compute stream (the reference's SyncInfo of C)
     cudaStream_t comm_stream = nullptr;  // panel prefetch stream (overlap with the local GEMM)
+    cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;  // host-operand streaming (GemmHost)
     ncclComm_t world = nullptr, mc_comm = nullptr, mr_comm = nullptr;
     // NVLink peer-memory staging (zero-SM AllGather); nullptr -> NCCL is used instead.
     PeerArena* arena = nullptr;
@@ -119,6 +123,13 @@ template <typename T>
 void LocalGemm(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, T beta, DistMat<T>& C);
 template <typename T>
 void Gemm(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, T beta, DistMat<T>& C, int alg);
+// C = alpha op(A) op(B) + beta C with every operand in HOST memory: the local parts of zero-aligned
+// [MC,MR] matrices (column-major, leading dimensions lda/ldb/ldc) stream through the GPU — A stays
+// resident, column blocks of B and C are uploaded, gathered, multiplied and downloaded in a
+// pipeline over four streams. Returns when C is complete in host memory.
+template <typename T>
+void GemmHost(Grid& g, int ta, int tb, int64_t m, int64_t n, int64_t k, T alpha, const T* A, int64_t lda,
+              const T* B, int64_t ldb, T beta, T* C, int64_t ldc);
 // Which SUMMA variant GEMM_DEFAULT resolves to (reference Gemm/NN.hpp:585-600 and twins).
 int ResolveGemmAlg(int ta, int tb, int64_t m, int64_t n, int64_t k, int alg);
 void GemmProfileEnable(bool on);

@@ -56,6 +56,8 @@ Grid::Grid(int height, int width, int vc, const ncclUniqueId* id, int dev) {
         cuda_check(cudaSetDevice(dev), "cudaSetDevice");
         cuda_check(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking), "cudaStreamCreate");
         cuda_check(cudaStreamCreateWithFlags(&comm_stream, cudaStreamNonBlocking), "cudaStreamCreate");
+        cuda_check(cudaStreamCreateWithFlags(&h2d_stream, cudaStreamNonBlocking), "cudaStreamCreate");
+        cuda_check(cudaStreamCreateWithFlags(&d2h_stream, cudaStreamNonBlocking), "cudaStreamCreate");
     }
     if (id && shape.size() > 1) {
         nccl_check(ncclCommInitRank(&world, shape.size(), *id, vc), "ncclCommInitRank");
@@ -83,15 +85,35 @@ std::vector<int> Grid::comm_members(Dist d) const {
     return v;
 }
 
-Grid::~Grid() {
+void Grid::Shutdown() {
     if (stream) cudaStreamSynchronize(stream);
     if (comm_stream) cudaStreamSynchronize(comm_stream);
-    delete arena;
+    if (arena) {
+        // grid destruction is collective (like the reference's Grid::~Grid freeing its communicators):
+        // unmap the peers, wait until everybody has, then release the local arena
+        arena->Detach();
+        int* token = nullptr;
+        if (world && cudaMalloc(&token, sizeof(int)) == cudaSuccess) {
+            cudaMemsetAsync(token, 0, sizeof(int), stream);
+            if (ncclAllReduce(token, token, 1, ncclInt, ncclSum, world, stream) == ncclSuccess) cudaStreamSynchronize(stream);
+            cudaFree(token);
+        }
+        cudaGetLastError();
+        delete arena;
+        arena = nullptr;
+    }
     if (mc_comm && mc_comm != world) ncclCommDestroy(mc_comm);
     if (mr_comm && mr_comm != world) ncclCommDestroy(mr_comm);
     if (world) ncclCommDestroy(world);
+    mc_comm = mr_comm = world = nullptr;
+}
+
+Grid::~Grid() {
+    Shutdown();
     if (stream) cudaStreamDestroy(stream);
     if (comm_stream) cudaStreamDestroy(comm_stream);
+    if (h2d_stream) cudaStreamDestroy(h2d_stream);
+    if (d2h_stream) cudaStreamDestroy(d2h_stream);
 }
 
 // ------------------------------------------------------------------ DistMat

@@ -7,6 +7,9 @@
 
 namespace elb {
 
+void set_lattice_cta_limit(int ctas);  // capi_core.cu
+
+
 template <> struct Dev<float> {
     static constexpr ncclDataType_t nccl = ncclFloat;
     static void gemm(int ta, int tb, int64_t m, int64_t n, int64_t k, float al, const float* A, int64_t lda,
@@ -37,6 +40,10 @@ template <> struct Dev<float> {
     static void lattice(int mode, int nseg, const elb200_segment* segs, float* M, int64_t ldm, float* buf,
                         float al, cudaStream_t s) {
         throw_status(elb200_lattice_f32(mode, nseg, segs, M, ldm, buf, al, s), "elb200_lattice_f32");
+    }
+    static void peer_reduce_axpy(int nsrc, const float* const* srcs, int64_t off, const elb200_segment* seg, float* M,
+                                 int64_t ldm, float al, cudaStream_t s) {
+        throw_status(elb200_peer_reduce_axpy_f32(nsrc, srcs, off, seg, M, ldm, al, s), "elb200_peer_reduce_axpy_f32");
     }
 };
 
@@ -70,6 +77,10 @@ template <> struct Dev<double> {
     static void lattice(int mode, int nseg, const elb200_segment* segs, double* M, int64_t ldm, double* buf,
                         double al, cudaStream_t s) {
         throw_status(elb200_lattice_f64(mode, nseg, segs, M, ldm, buf, al, s), "elb200_lattice_f64");
+    }
+    static void peer_reduce_axpy(int nsrc, const double* const* srcs, int64_t off, const elb200_segment* seg, double* M,
+                                 int64_t ldm, double al, cudaStream_t s) {
+        throw_status(elb200_peer_reduce_axpy_f64(nsrc, srcs, off, seg, M, ldm, al, s), "elb200_peer_reduce_axpy_f64");
     }
 };
 

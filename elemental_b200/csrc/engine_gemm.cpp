@@ -169,8 +169,13 @@ void SummaC(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, T
         if (p >= 2) cuda_check(cudaStreamWaitEvent(cs, freed[s], 0), "cudaStreamWaitEvent");
         DistMat<T> A1 = ta ? A.View(k0, k0 + kb, 0, d.m) : A.View(0, d.m, k0, k0 + kb);
         DistMat<T> B1 = tb ? B.View(0, d.n, k0, k0 + kb) : B.View(k0, k0 + kb, 0, d.n);
+        // optional cap on the CTAs of unpack kernels that run underneath a GEMM (ELB200_BG_CTAS; off by
+        // default: measured, a short full-width unpack disturbs the GEMM less than a long narrow one)
+        static const int bg_ctas = [] { const char* e = std::getenv("ELB200_BG_CTAS"); return e ? std::atoi(e) : 0; }();
+        set_lattice_cta_limit(p >= 1 ? bg_ctas : 0);
         const DistMat<T>& a = panel_as(A1, PA[s], C.spec);
         const DistMat<T>& b = panel_as(B1, PB[s], C.spec);
+        set_lattice_cta_limit(0);
         cuda_check(cudaEventRecord(ready[s], cs), "cudaEventRecord");
         cuda_check(cudaStreamWaitEvent(C.stream, ready[s], 0), "cudaStreamWaitEvent");
         LocalGemm(ta, tb, alpha, a, b, p == 0 ? beta : T(1), C);
@@ -315,9 +320,134 @@ void Gemm(int ta, int tb, T alpha, const DistMat<T>& Apre, const DistMat<T>& Bpr
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Host-operand Gemm: C-block-major stationary-C with the whole k range per block.
+//   h2d stream : A (once), then per column block of C its slices of B and C
+//   comm stream: gather op(A) -> [MC,*] once, each B block -> [*,MR]   (peer arena / NCCL)
+//   compute    : one full-k local GEMM per block (beta applied in the epilogue)
+//   d2h stream : the finished C block
+// Two block slots keep PCIe (both directions), NVLink and the tensor pipe busy at the same time.
+// ---------------------------------------------------------------------------------------------
+namespace {
+struct Ev {
+    cudaEvent_t e = nullptr;
+    Ev() { cuda_check(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), "cudaEventCreate"); }
+    ~Ev() { if (e) cudaEventDestroy(e); }
+    Ev(const Ev&) = delete;
+    Ev& operator=(const Ev&) = delete;
+    void record(cudaStream_t s) { cuda_check(cudaEventRecord(e, s), "cudaEventRecord"); }
+    void block(cudaStream_t s) { cuda_check(cudaStreamWaitEvent(s, e, 0), "cudaStreamWaitEvent"); }
+};
+template <typename T>
+void copy_rect(T* dst, int64_t ldd, const T* src, int64_t lds, int64_t rows, int64_t cols, cudaMemcpyKind kind, cudaStream_t s) {
+    if (rows <= 0 || cols <= 0) return;
+    cuda_check(cudaMemcpy2DAsync(dst, size_t(ldd) * sizeof(T), src, size_t(lds) * sizeof(T), size_t(rows) * sizeof(T),
+                                 size_t(cols), kind, s), "cudaMemcpy2DAsync");
+}
+int64_t lcm64(int64_t a, int64_t b) { int64_t x = a, y = b; while (y) { int64_t t = x % y; x = y; y = t; } return a / x * b; }
+}  // namespace
+
+template <typename T>
+void GemmHost(Grid& g, int ta, int tb, int64_t m, int64_t n, int64_t k, T alpha, const T* Ah, int64_t lda,
+              const T* Bh, int64_t ldb, T beta, T* Ch, int64_t ldc) {
+    ta = ta ? 1 : 0; tb = tb ? 1 : 0;
+    if (m < 0 || n < 0 || k < 0) throw EngineError(ELB200_ERR_ARG, "GemmHost: negative dimension");
+    if (m == 0 || n == 0) return;
+    if (!Ch || (k > 0 && alpha != T(0) && (!Ah || !Bh))) throw EngineError(ELB200_ERR_ARG, "GemmHost: null operand");
+    const GridShape gs = g.shape;
+    const int64_t r = gs.r, c = gs.c;
+    auto loc = [](int64_t n_, int64_t rank, int64_t stride) { return Length(n_, Shift(rank, 0, stride), stride); };
+    const int64_t hA = ta ? k : m, wA = ta ? m : k, hB = tb ? n : k, wB = tb ? k : n;
+    const int64_t lhA = loc(hA, g.me.mc, r), lwA = loc(wA, g.me.mr, c);
+    const int64_t lhB = loc(hB, g.me.mc, r), lwB = loc(wB, g.me.mr, c);
+    const int64_t lhC = loc(m, g.me.mc, r);
+    if (lda < std::max<int64_t>(lhA, 1) || ldb < std::max<int64_t>(lhB, 1) || ldc < std::max<int64_t>(lhC, 1))
+        throw EngineError(ELB200_ERR_ARG, "GemmHost: leading dimension smaller than the local height");
+    const bool product = k > 0 && alpha != T(0);
+    cudaStream_t s = g.stream, cs = g.comm_stream, hs = g.h2d_stream, ds = g.d2h_stream;
+
+    // global column blocks of C: multiples of lcm(r,c)*256 so every block view keeps alignment 0
+    const int64_t unit = lcm64(r, c) * 256;
+    int64_t Wg = (n / 8 + unit - 1) / unit * unit;
+    if (Wg < unit) Wg = unit;
+    const int64_t nblocks = (n + Wg - 1) / Wg;
+
+    DistMat<T> A(g, MC, MR, s);
+    DistMat<T> PA(g, ta ? STAR : MC, ta ? MC : STAR, cs);
+    DistMat<T> Bblk[2] = {DistMat<T>(g, MC, MR, s), DistMat<T>(g, MC, MR, s)};
+    DistMat<T> Cblk[2] = {DistMat<T>(g, MC, MR, s), DistMat<T>(g, MC, MR, s)};
+    DistMat<T> PB[2] = {DistMat<T>(g, tb ? MR : STAR, tb ? STAR : MR, cs), DistMat<T>(g, tb ? MR : STAR, tb ? STAR : MR, cs)};
+    const int64_t w0 = std::min(Wg, n);
+    if (product) A.Resize(hA, wA);
+    for (int i = 0; i < 2 && i < nblocks; ++i) {
+        if (product) Bblk[i].Resize(tb ? w0 : k, tb ? k : w0);
+        Cblk[i].Resize(m, w0);
+    }
+    Ev alloc, a_up, a_ready, up[2], ready[2], done[2], out[2];
+    alloc.record(s);
+    alloc.block(hs);
+    alloc.block(cs);
+    alloc.block(ds);
+
+    const DistMat<T>* a = nullptr;
+    if (product) {
+        copy_rect(A.buf, A.ldim, Ah, lda, lhA, lwA, cudaMemcpyHostToDevice, hs);
+        a_up.record(hs);
+        a_up.block(cs);
+        DistSpec like;  // C's distribution: [MC,MR], alignment 0
+        like.col = MC; like.row = MR; like.height = m; like.width = n;
+        a = &panel_as(A, PA, like);
+        a_ready.record(cs);
+    }
+
+    for (int64_t j = 0; j < nblocks; ++j) {
+        const int sl = int(j & 1);
+        const int64_t J0 = j * Wg, J1 = std::min(n, J0 + Wg), wj = J1 - J0;
+        if (j >= 2) out[sl].block(hs);  // the slot's previous block has been multiplied and downloaded
+        // local index ranges of the block: C columns and (B not transposed) B columns run over MR,
+        // (B transposed) B rows run over MC
+        const int64_t cc0 = loc(J0, g.me.mr, c), ccn = loc(J1, g.me.mr, c) - cc0;
+        Cblk[sl].Resize(m, wj);
+        copy_rect(Cblk[sl].buf, Cblk[sl].ldim, Ch + cc0 * ldc, ldc, lhC, ccn, cudaMemcpyHostToDevice, hs);
+        if (product) {
+            if (!tb) {
+                Bblk[sl].Resize(k, wj);
+                copy_rect(Bblk[sl].buf, Bblk[sl].ldim, Bh + cc0 * ldb, ldb, lhB, ccn, cudaMemcpyHostToDevice, hs);
+            } else {
+                const int64_t br0 = loc(J0, g.me.mc, r), brn = loc(J1, g.me.mc, r) - br0;
+                Bblk[sl].Resize(wj, k);
+                copy_rect(Bblk[sl].buf, Bblk[sl].ldim, Bh + br0, ldb, brn, lwB, cudaMemcpyHostToDevice, hs);
+            }
+        }
+        up[sl].record(hs);
+        if (product) {
+            up[sl].block(cs);
+            const DistMat<T>& b = panel_as(Bblk[sl], PB[sl], Cblk[sl].spec);
+            ready[sl].record(cs);
+            ready[sl].block(s);
+            if (j == 0) a_ready.block(s);
+            LocalGemm(ta, tb, alpha, *a, b, beta, Cblk[sl]);
+        } else {
+            up[sl].block(s);
+            Scale(beta, Cblk[sl]);
+        }
+        done[sl].record(s);
+        done[sl].block(ds);
+        copy_rect(Ch + cc0 * ldc, ldc, Cblk[sl].buf, Cblk[sl].ldim, lhC, ccn, cudaMemcpyDeviceToHost, ds);
+        out[sl].record(ds);
+    }
+    // join: the temporaries are freed in the order of their own streams, after their last readers
+    for (int i = 0; i < 2 && i < nblocks; ++i) { out[i].block(s); done[i].block(cs); }
+    cuda_check(cudaStreamSynchronize(ds), "GemmHost: d2h");
+    cuda_check(cudaStreamSynchronize(s), "GemmHost: compute");
+    cuda_check(cudaStreamSynchronize(cs), "GemmHost: comm");
+}
+
 template void LocalGemm<float>(int, int, float, const DistMat<float>&, const DistMat<float>&, float, DistMat<float>&);
 template void LocalGemm<double>(int, int, double, const DistMat<double>&, const DistMat<double>&, double, DistMat<double>&);
 template void Gemm<float>(int, int, float, const DistMat<float>&, const DistMat<float>&, float, DistMat<float>&, int);
 template void Gemm<double>(int, int, double, const DistMat<double>&, const DistMat<double>&, double, DistMat<double>&, int);
+template void GemmHost<float>(Grid&, int, int, int64_t, int64_t, int64_t, float, const float*, int64_t, const float*, int64_t, float, float*, int64_t);
+template void GemmHost<double>(Grid&, int, int, int64_t, int64_t, int64_t, double, const double*, int64_t, const double*, int64_t, double, double*, int64_t);
 
 }  // namespace elb

@@ -192,6 +192,22 @@ void AxpyContract(T alpha, const DistMat<T>& A, DistMat<T>& B) {
                        B.buf, 1, B.ldim, s);
         return;
     }
+    if (g.arena && size_t(plan.group) * plan.portion * sizeof(T) <= g.arena->slot_bytes() && plan.group <= ELB200_MAX_SEGMENTS) {
+        // ReduceScatter by the receiver over NVLink peer memory (peer.hpp pull mode): every member
+        // packs its partial sums into its own arena slot, then ONE kernel per rank loads its portion
+        // from all members' slots, sums them in communicator order and applies the axpy-unpack.
+        const std::vector<int> members = g.comm_members(plan.comm_dist);
+        const int idx = g.comm_index(plan.comm_dist);
+        PeerArena::Ticket t = g.arena->Publish(Grid::arena_channel(plan.comm_dist), members, idx,
+                                               size_t(plan.group) * plan.portion * sizeof(T), s);
+        run_lattice<T>(ELB200_PACK, plan.packs, Abuf, A.ldim, static_cast<T*>(t.data), T(0), s);
+        g.arena->Signal(t, members, idx, s);
+        const T* srcs[ELB200_MAX_SEGMENTS];
+        for (int i = 0; i < plan.group; ++i) srcs[i] = static_cast<const T*>(g.arena->PeerSlot(members[i], t));
+        Dev<T>::peer_reduce_axpy(plan.group, srcs, int64_t(plan.my_index) * plan.portion, &plan.unpack, B.buf, B.ldim, alpha, s);
+        g.arena->Release(t, members, idx, s);
+        return;
+    }
     ncclComm_t comm = g.comm_for(plan.comm_dist);
     if (!comm) throw EngineError(ELB200_ERR_STATE, "AxpyContract: grid has no NCCL communicator");
     Scratch<T> stage(int64_t(plan.group + 1) * plan.portion, s);

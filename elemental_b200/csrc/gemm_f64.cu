@@ -21,9 +21,15 @@
 namespace elb {
 namespace {
 
-constexpr int BM = 128, BN = 128, BK = 16;
+#ifndef ELB_F64_BK
+#define ELB_F64_BK 32
+#endif
+#ifndef ELB_F64_STAGES
+#define ELB_F64_STAGES 3
+#endif
+constexpr int BM = 128, BN = 128, BK = ELB_F64_BK;
 constexpr int kThreads = 256;
-constexpr int kStages = 4;
+constexpr int kStages = ELB_F64_STAGES;
 constexpr int kPitchMN = BM + 4;  // smem tile [k][mn]: pitch % 16 == 4 -> conflict-free fragment reads
 constexpr int kPitchK = BK + 4;   // smem tile [mn][k]
 constexpr int kOperandDoubles = (BK * kPitchMN > BM * kPitchK) ? BK * kPitchMN : BM * kPitchK;

@@ -131,12 +131,19 @@ PeerArena* PeerArena::Create(ncclComm_t world, int rank, int size, cudaStream_t 
     return pa;
 }
 
-PeerArena::~PeerArena() {
-    for (int r = 0; r < size_; ++r) {
+void PeerArena::Detach() {
+    for (int r = 0; r < size_ && r < int(arena_.size()); ++r) {
         if (r == rank_) continue;
         if (arena_[r]) cudaIpcCloseMemHandle(arena_[r]);
         if (flags_[r]) cudaIpcCloseMemHandle(flags_[r]);
+        arena_[r] = nullptr;
+        flags_[r] = nullptr;
     }
+    cudaGetLastError();
+}
+
+PeerArena::~PeerArena() {
+    Detach();
     if (!arena_.empty() && arena_[rank_]) cudaFree(arena_[rank_]);
     if (!flags_.empty() && flags_[rank_]) cudaFree(flags_[rank_]);
     if (consts_) cudaFree(consts_);
@@ -182,6 +189,31 @@ PeerArena::Ticket PeerArena::AllGather(int channel, const std::vector<int>& memb
         if (i != my_index) wait_flag(flag(rank_, ARRIVE, channel, t.slot, members[i]), t.seq, s);
     t.data = slot_base(rank_, channel, t.slot);
     return t;
+}
+
+PeerArena::Ticket PeerArena::Publish(int channel, const std::vector<int>& members, int my_index, size_t bytes,
+                                     cudaStream_t s) {
+    if (bytes > slot_bytes_) throw EngineError(ELB200_ERR_ARG, "PeerArena::Publish: buffer larger than an arena slot");
+    const int g = int(members.size());
+    const uint64_t n = uses_[channel]++;
+    Ticket t;
+    t.channel = channel;
+    t.slot = int(n & 1);
+    t.seq = uint32_t(n / 2 + 1);
+    // every member must be done with the previous contents of this slot generation (an ack means
+    // "I have finished reading all members' slots", so all acks == nobody reads mine any more)
+    for (int i = 0; i < g; ++i)
+        if (i != my_index) wait_flag(flag(rank_, ACK, channel, t.slot, members[i]), t.seq - 1, s);
+    t.data = slot_base(rank_, channel, t.slot);
+    return t;
+}
+
+void PeerArena::Signal(const Ticket& t, const std::vector<int>& members, int my_index, cudaStream_t s) {
+    const int g = int(members.size());
+    for (int i = 0; i < g; ++i)
+        if (i != my_index) write_flag(flag(members[i], ARRIVE, t.channel, t.slot, rank_), t.seq, s);
+    for (int i = 0; i < g; ++i)
+        if (i != my_index) wait_flag(flag(rank_, ARRIVE, t.channel, t.slot, members[i]), t.seq, s);
 }
 
 void PeerArena::Release(const Ticket& t, const std::vector<int>& members, int my_index, cudaStream_t s) {

@@ -33,6 +33,9 @@ public:
     // — on every rank alike — when peer mapping is not possible; callers then use NCCL.
     static PeerArena* Create(ncclComm_t world, int rank, int size, cudaStream_t s);
     ~PeerArena();
+    // Unmap every peer's arena (idempotent). The owner may free its memory only after all
+    // importers have done this, so Grid teardown runs Detach -> barrier -> delete.
+    void Detach();
 
     size_t slot_bytes() const { return slot_bytes_; }
     // Collective over `members` (VC ranks in communicator order; members[my_index] == this rank).
@@ -41,6 +44,13 @@ public:
                      size_t send_bytes, size_t portion_bytes, cudaStream_t s);
     // Call after the last read of ticket.data has been enqueued on `s`.
     void Release(const Ticket& t, const std::vector<int>& members, int my_index, cudaStream_t s);
+
+    // Pull mode (reductions): every member fills ITS OWN slot (t.data, `bytes` long) after Publish,
+    // then Signal; afterwards each member reads all members' slots through the peer mapping
+    // (PeerSlot) from a kernel — NVLink loads — and finally calls Release.
+    Ticket Publish(int channel, const std::vector<int>& members, int my_index, size_t bytes, cudaStream_t s);
+    void Signal(const Ticket& t, const std::vector<int>& members, int my_index, cudaStream_t s);
+    const void* PeerSlot(int rank, const Ticket& t) const { return slot_base(rank, t.channel, t.slot); }
 
 private:
     PeerArena() = default;

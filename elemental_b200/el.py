@@ -262,6 +262,21 @@ def Gemm(orientA, orientB, alpha, A: DistMatrix, B: DistMatrix, beta, C_: DistMa
     check(lib.elb200_dist_gemm(orientA, orientB, alpha, A._h, B._h, beta, C_._h, alg), "Gemm")
 
 
+def GemmHost(grid: "Grid", orientA, orientB, m: int, n: int, k: int, alpha, A: torch.Tensor, lda: int,
+             B: torch.Tensor, ldb: int, beta, C_: torch.Tensor, ldc: int) -> None:
+    """El::Gemm on HOST operands: A, B, C_ are CPU tensors (pinned recommended) holding this rank's
+    column-major local parts of zero-aligned [MC,MR] matrices; they stream through the GPU in a
+    H2D | gather | GEMM | D2H pipeline and C_ is complete on return (elb200_dist_gemm_host_*)."""
+    for t in (A, B, C_):
+        if t.is_cuda:
+            raise ValueError("GemmHost takes host tensors; use Gemm for device-resident DistMatrices")
+    if not (A.dtype == B.dtype == C_.dtype) or C_.dtype not in (torch.float32, torch.float64):
+        raise TypeError("GemmHost: float32 or float64 operands of one dtype")
+    fn = lib.elb200_dist_gemm_host_f32 if C_.dtype == torch.float32 else lib.elb200_dist_gemm_host_f64
+    check(fn(grid._h, orientA, orientB, m, n, k, alpha, A.data_ptr(), lda, B.data_ptr(), ldb, beta,
+             C_.data_ptr(), ldc), "GemmHost")
+
+
 def gemm_local(orientA, orientB, alpha, A: torch.Tensor, lda, B: torch.Tensor, ldb, beta,
                C_: torch.Tensor, ldc, m, n, k, stream: int = 0, cta_group: int = 0) -> None:
     """gpu_blas::Gemm replacement on raw column-major device buffers (GPU_BLAS_impl.hpp:417-444)."""

@@ -161,6 +161,20 @@ int elb200_lattice_f32(int mode, int nseg, const elb200_segment* segs, float* M,
 int elb200_lattice_f64(int mode, int nseg, const elb200_segment* segs, double* M, int64_t ldm,
                        double* buf, double alpha, void* stream);
 
+/* M lattice += alpha * (srcs[0][off + e] + srcs[1][off + e] + ... ), e running over the packed
+ * rows x cols block of `seg`: the receiver side of a ReduceScatter, fused with the axpy-unpack.
+ * srcs are device pointers this GPU can load from — its own staging buffer and its peers' buffers
+ * mapped over NVLink (CUDA IPC / peer access); the sum runs in array order on every caller.
+ * Replaces mpi::ReduceScatter<GPU> + the update loop in axpy_contract::{RowScatter,ColScatter,
+ * Scatter} (include/El/blas_like/level1/AxpyContract.hpp:318-337, 196-216, 455-476;
+ * src/core/imports/mpi/ReduceScatter.hpp:36-52). nsrc <= ELB200_MAX_SEGMENTS. */
+int elb200_peer_reduce_axpy_f32(int nsrc, const float* const* srcs, int64_t src_offset,
+                                const elb200_segment* seg, float* M, int64_t ldm, float alpha,
+                                void* stream);
+int elb200_peer_reduce_axpy_f64(int nsrc, const double* const* srcs, int64_t src_offset,
+                                const elb200_segment* seg, double* M, int64_t ldm, double alpha,
+                                void* stream);
+
 
 /* ------------------------------------------------------------------------------------------
  * Redistribution planner (pure host code; callable without a GPU).
@@ -287,6 +301,20 @@ int elb200_dm_local_gemm(int transA, int transB, double alpha, elb200_dm_t A, el
  *      as in Gemm/NN.hpp:30-31). */
 int elb200_dist_gemm(int transA, int transB, double alpha, elb200_dm_t A, elb200_dm_t B,
                      double beta, elb200_dm_t C, int alg);
+
+/* El::Gemm with every operand in HOST memory (the reference reaches this case through its
+ * CPU<->GPU proxies, include/El/core/ProxyDevice.hpp + Matrix<T,GPU> = Matrix<T,CPU> copies,
+ * include/El/core/Matrix/impl_gpu.hpp, which upload everything, compute, download).
+ * A, B, C are this rank's LOCAL parts of zero-aligned [MC,MR] matrices of global size
+ * op(A) m x k, op(B) k x n, C m x n (column-major, ld in elements; pinned memory recommended).
+ * A stays resident on the device, column blocks of B and C stream through a four-stream
+ * pipeline (H2D | gather | GEMM | D2H). Synchronous: C is complete in host memory on return. */
+int elb200_dist_gemm_host_f32(elb200_grid_t g, int transA, int transB, int64_t m, int64_t n, int64_t k,
+                              float alpha, const float* A, int64_t lda, const float* B, int64_t ldb,
+                              float beta, float* C, int64_t ldc);
+int elb200_dist_gemm_host_f64(elb200_grid_t g, int transA, int transB, int64_t m, int64_t n, int64_t k,
+                              double alpha, const double* A, int64_t lda, const double* B, int64_t ldb,
+                              double beta, double* C, int64_t ldc);
 
 #ifdef __cplusplus
 } /* extern "C" */

@@ -172,6 +172,48 @@ def check_gemm_proxies(grid, dtype) -> None:
             assert err <= tol, (d, alg, err, tol)
 
 
+def check_gemm_host(grid, dtype) -> int:
+    """el.GemmHost (elb200_dist_gemm_host_*): operands in HOST memory, streamed in column blocks.
+    Sizes give three blocks on this grid (ragged last one), all orientations, beta = 0 with NaNs in
+    C (must not propagate), k = 0 (pure scaling), padded leading dimensions."""
+    import math
+    og = _grid_oracle(grid)
+    npdt = NPDT[dtype]
+    me = grid.Rank()
+    unit = (og.r * og.c // math.gcd(og.r, og.c)) * 256
+    m, n, k = 300, 2 * unit + 77, 200
+    zero = lambda h, w: OD.Spec(OD.MC, OD.MR, 0, 0, h, w)  # noqa: E731
+    cnt = 0
+    for oa, ob in itertools.product((0, 1), (0, 1)):
+        for (alpha, beta, kk) in ((2.0, 3.0, k), (0.5, 0.0, k), (1.0, -0.5, 0)):
+            A = OG.uniform_matrix(*((m, kk) if oa == 0 else (kk, m)), 201, npdt, 0.0, 1.0)
+            B = OG.uniform_matrix(*((kk, n) if ob == 0 else (n, kk)), 202, npdt, 0.0, 1.0)
+            C0 = OG.uniform_matrix(m, n, 203, npdt, 0.0, 1.0)
+            ref = OG.gemm_global(oa, ob, alpha, A, B, beta, C0, np.longdouble)
+
+            def host(G, pad):
+                loc = OD.local_of(G, zero(*G.shape), og, me)
+                ld = max(loc.shape[0], 1) + pad
+                buf = torch.zeros((max(loc.shape[1], 1), ld), dtype=dtype).pin_memory()
+                view = buf.t()[:loc.shape[0], :loc.shape[1]]  # column-major window, leading dimension ld
+                view.copy_(torch.from_numpy(np.ascontiguousarray(loc)))
+                return buf, view, ld
+            bA, _, lda = host(A, 3)
+            bB, _, ldb = host(B, 0)
+            bC, vC, ldc = host(C0, 5)
+            if beta == 0.0:
+                vC.fill_(float("nan"))
+            el.GemmHost(grid, oa, ob, m, n, kk, alpha, bA, lda, bB, ldb, beta, bC, ldc)
+            got = vC.numpy()
+            ref_loc = OD.local_of(ref, zero(m, n), og, me)
+            num = float(np.linalg.norm(got.astype(np.longdouble) - ref_loc))
+            den = float(np.linalg.norm(ref)) / np.sqrt(og.p)
+            assert np.isfinite(got).all(), (oa, ob, alpha, beta, kk)
+            assert num / max(den, 1e-300) <= OG.gemm_tolerance(npdt, max(kk, 1)), (oa, ob, alpha, beta, kk, num / den)
+            cnt += 1
+    return cnt
+
+
 def run_all(grid, heavy=False) -> dict:
     out = {}
     out["redist_f64"] = check_redistributions(grid, torch.float64)
@@ -185,10 +227,12 @@ def run_all(grid, heavy=False) -> dict:
     out["gemm_f32"] = check_gemm_variants(grid, torch.float32)
     check_gemm_proxies(grid, torch.float64)
     check_gemm_proxies(grid, torch.float32)
+    out["gemm_host"] = check_gemm_host(grid, torch.float32) + check_gemm_host(grid, torch.float64)
     if heavy:
         # panels wider than one algorithmic block, ragged edges, default blocksize
         for dt in (torch.float32, torch.float64):
-            for (oa, ob, alg) in ((0, 0, 3), (0, 1, 3), (1, 0, 1), (1, 1, 2), (0, 0, 4)):
+            for (oa, ob, alg) in ((0, 0, el.GEMM_SUMMA_C), (0, 1, el.GEMM_SUMMA_C), (1, 0, el.GEMM_SUMMA_A), (1, 1, el.GEMM_SUMMA_B),
+                                   (0, 0, el.GEMM_SUMMA_DOT)):
                 err, tol = gemm_case(grid, dt, oa, ob, alg, 1100, 900, 2500, alpha=0.5, beta=-0.5)
                 assert err <= tol, (dt, oa, ob, alg, err, tol)
     return out

@@ -50,6 +50,13 @@ def test_gemm_reference_driver_config(grid1, dtype):
                 assert err <= tol, (oa, ob, alg, err, tol)
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+def test_gemm_host_operands_1x1(grid1, dtype):
+    """Host-operand Gemm (H2D | GEMM | D2H pipeline over column blocks) against the oracle."""
+    from tests import dist_cases as dc
+    assert dc.check_gemm_host(grid1, dtype) == 12
+
+
 def test_gemm_errors(grid1):
     from elemental_b200 import el
     from elemental_b200._lib import Elb200Error

@@ -186,6 +186,37 @@ def test_lattice_pack_unpack(L, dtype, aligned):
         assert np.array_equal(m3.cpu().numpy()[:, :H].T, ref.astype(dtype))
 
 
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_peer_reduce_axpy(L, dtype):
+    """Receiver-side ReduceScatter fused with the axpy-unpack (AxpyContract.hpp:318-337): the
+    lattice of M gets alpha * (sum over sources of their packed block at the same offset).  On one
+    GPU the sources are plain device buffers; on a grid they are peer mappings of the arena slots."""
+    import ctypes as C
+    sfx = SUF[dtype]
+    fn = getattr(L.lib, f"elb200_peer_reduce_axpy_{sfx}")
+    rng = np.random.default_rng(3)
+    H, W, ld = 37, 29, 40
+    for (seg, nsrc) in (((1, 2, 18, 3, 4, 6, 0), 3), ((0, 1, 37, 0, 1, 29, 0), 4), ((5, 3, 1, 2, 1, 1, 0), 2)):
+        r0, rs, nr, c0, cs, nc, _ = seg
+        off = 7
+        total = off + nr * nc + 3
+        srcs = [rng.integers(-8, 9, total).astype(dtype) for _ in range(nsrc)]  # small ints: exact sums
+        M = np.zeros((W, ld), dtype=dtype); M[:, :H] = rng.integers(-8, 9, (W, H)).astype(dtype)
+        dsrc = [dev(x) for x in srcs]
+        ptrs = (C.c_void_p * nsrc)(*[d.data_ptr() for d in dsrc])
+        dM = dev(M)
+        sg = L.Segment(*seg)
+        assert fn(nsrc, ptrs, off, C.byref(sg), dM.data_ptr(), ld, dtype(2.0), None) == 0
+        ref = M[:, :H].T.copy()
+        blk = sum(x[off:off + nr * nc] for x in srcs).reshape((nr, nc), order="F")
+        ref[r0:r0 + rs * nr:rs, c0:c0 + cs * nc:cs] += dtype(2.0) * blk
+        got = dM.cpu().numpy()
+        assert np.array_equal(got[:, :H].T, ref)
+        assert np.array_equal(got[:, H:], M[:, H:])  # padding rows untouched
+    bad = L.Segment(0, 0, 1, 0, 1, 1, 0)
+    assert fn(1, (C.c_void_p * 1)(0), 0, C.byref(bad), 0, 1, dtype(1), None) != 0  # row_step < 1
+
+
 GEMM_SHAPES = [(128, 128, 32), (256, 512, 96), (300, 200, 100), (129, 257, 33), (1000, 1000, 1000),
                (64, 40, 500), (4, 4, 4), (513, 1, 77), (2000, 2000, 64)]
 
