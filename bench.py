@@ -360,7 +360,7 @@ def _measure(args, grid, el, lib, torch, dist, world, rank, local, n_gpus, n, td
                 "data": "synthetic",
                 "config": {"workload": f"El::Gemm {args.dtype} {['DEFAULT','SUMMA_A_MS','SUMMA_A','SUMMA_B_MS','SUMMA_B','SUMMA_C_MS','SUMMA_C','SUMMA_DOT','CANNON'][args.alg]} n={n} (NN, alpha=0.5, beta=-0.5), [MC,MR] on a {grid.Height()}x{grid.Width()} grid",
                            "inputs": "Uniform(-0.1,0.1), resident in HBM", "l2": f"inputs {3 * n * n * esz / n_gpus / 2**20:.0f} MiB per GPU > 126 MB L2 (no flush needed)",
-                           "panel_k": "full k on 1x1; ELB200_PANEL_K default 2048 (fp32) / 1024 (fp64) otherwise",
+                           "panel_k": "full k on 1x1; ELB200_PANEL_K (default 4096 fp32 / 2048 fp64) otherwise",
                            "per_gpu_tflops": value / n_gpus},
                 "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
         return line

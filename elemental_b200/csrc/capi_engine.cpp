@@ -116,6 +116,24 @@ int elb200_plan_contract(int r, int c, int vc, const elb200_dist_spec* A, const 
     return ELB200_OK;
 }
 
+int elb200_plan_direct_panel(int r, int c, int vc, int64_t kb, int64_t a_row_align, int64_t b_col_align,
+                             int64_t* row_off, int64_t* a_cols, int* nclasses, int64_t* b_row0, int64_t* b_rows) {
+    if (r < 1 || c < 1 || vc < 0 || vc >= r * c || kb < 0 || !row_off || !a_cols || !nclasses || !b_row0 || !b_rows)
+        return ELB200_ERR_ARG;
+    if (r > ELB200_MAX_SEGMENTS) return ELB200_ERR_ARG;
+    GridShape g; g.r = r; g.c = c;
+    const DirectPanelPlan p = plan_direct_panel(g, coord_of_vc(g, vc), kb, Mod(a_row_align, c), Mod(b_col_align, r));
+    for (size_t i = 0; i < p.row_off.size(); ++i) row_off[i] = p.row_off[i];
+    *nclasses = int(p.a_cols.size());
+    for (size_t i = 0; i < p.a_cols.size(); ++i) {
+        const PanelCols& pc = p.a_cols[i];
+        int64_t* o = a_cols + 5 * i;
+        o[0] = pc.dst_col0; o[1] = pc.dst_step; o[2] = pc.src_col0; o[3] = pc.src_step; o[4] = pc.count;
+    }
+    *b_row0 = p.b_row0; *b_rows = p.b_rows;
+    return ELB200_OK;
+}
+
 int elb200_unique_id(void* out128) {
     if (!out128) return ELB200_ERR_ARG;
     static_assert(sizeof(ncclUniqueId) <= ELB200_UNIQUE_ID_BYTES, "unique id size");

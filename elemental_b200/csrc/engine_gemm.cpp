@@ -48,6 +48,25 @@ void GemmProfileCollect(double* ms, double* flop, int* launches) {
     g_prof.flop = 0;
 }
 
+// one local GEMM launch on `s`, bracketed by events when the measurement hook is on
+template <typename T>
+void gemm_profiled(int ta, int tb, int64_t m, int64_t n, int64_t k, T alpha, const T* A, int64_t lda, const T* B,
+                   int64_t ldb, T beta, T* C, int64_t ldc, cudaStream_t s) {
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    const bool prof = g_prof.on && m > 0 && n > 0 && k > 0;
+    if (prof) {
+        cuda_check(cudaEventCreate(&e0), "cudaEventCreate");
+        cuda_check(cudaEventCreate(&e1), "cudaEventCreate");
+        cuda_check(cudaEventRecord(e0, s), "cudaEventRecord");
+    }
+    Dev<T>::gemm(ta, tb, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, s);
+    if (prof) {
+        cuda_check(cudaEventRecord(e1, s), "cudaEventRecord");
+        g_prof.ev.emplace_back(e0, e1);
+        g_prof.flop += 2.0 * double(m) * double(n) * double(k);
+    }
+}
+
 template <typename T>
 void LocalGemm(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, T beta, DistMat<T>& C) {
     const int64_t m = C.lh(), n = C.lw();
@@ -55,19 +74,7 @@ void LocalGemm(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B
     const int64_t ma = ta ? A.lw() : A.lh(), nb = tb ? B.lh() : B.lw();
     if (ka != kb || ma != m || nb != n)
         throw EngineError(ELB200_ERR_ARG, "LocalGemm: nonconformal local matrices");
-    cudaEvent_t e0 = nullptr, e1 = nullptr;
-    const bool prof = g_prof.on && m > 0 && n > 0 && ka > 0;
-    if (prof) {
-        cuda_check(cudaEventCreate(&e0), "cudaEventCreate");
-        cuda_check(cudaEventCreate(&e1), "cudaEventCreate");
-        cuda_check(cudaEventRecord(e0, C.stream), "cudaEventRecord");
-    }
-    Dev<T>::gemm(ta, tb, m, n, ka, alpha, A.buf, A.ldim, B.buf, B.ldim, beta, C.buf, C.ldim, C.stream);
-    if (prof) {
-        cuda_check(cudaEventRecord(e1, C.stream), "cudaEventRecord");
-        g_prof.ev.emplace_back(e0, e1);
-        g_prof.flop += 2.0 * double(m) * double(n) * double(ka);
-    }
+    gemm_profiled<T>(ta, tb, m, n, ka, alpha, A.buf, A.ldim, B.buf, B.ldim, beta, C.buf, C.ldim, C.stream);
 }
 
 int ResolveGemmAlg(int, int, int64_t m, int64_t n, int64_t k, int alg) {
@@ -87,6 +94,17 @@ int ResolveGemmAlg(int, int, int64_t m, int64_t n, int64_t k, int alg) {
 }
 
 namespace {
+
+// RAII event: record on one stream, make another wait
+struct Ev {
+    cudaEvent_t e = nullptr;
+    Ev() { cuda_check(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), "cudaEventCreate"); }
+    ~Ev() { if (e) cudaEventDestroy(e); }
+    Ev(const Ev&) = delete;
+    Ev& operator=(const Ev&) = delete;
+    void record(cudaStream_t s) { cuda_check(cudaEventRecord(e, s), "cudaEventRecord"); }
+    void block(cudaStream_t s) { cuda_check(cudaStreamWaitEvent(s, e, 0), "cudaStreamWaitEvent"); }
+};
 
 // src redistributed as (col,row) aligned with `like`; returns src itself when that
 // redistribution is the identity on every rank (no data motion, no copy).
@@ -119,6 +137,82 @@ const DistMat<T>& panel_as(const DistMat<T>& src, DistMat<T>& tmp, const DistSpe
 
 struct Dims { int64_t m, n, k; };
 
+// ---- stationary C, NN, aligned operands: zero-copy panels over NVLink ----------------------------
+// Both panels of a k-range are AllGathers (A1 -> [MC,*] over the row communicator, B1 -> [*,MR] over
+// the column communicator, Gemm/NN.hpp:363-377).  A sum over k does not care about the order of k,
+// so the panel is laid out with the k indices PERMUTED such that every member's contribution is a
+// pitched block: rows of the B panel are grouped by owner (member q's local rows are contiguous),
+// and the columns of the A panel follow the same order.  Then each contribution is a handful of
+// cudaMemcpy2DAsync transfers (copy engines) straight from the owner's local matrix into the
+// panel inside every member's peer-mapped arena slot: no staging buffer, no pack or unpack kernel,
+// no SM touched while the previous panel's GEMM runs.
+template <typename T>
+void SummaCDirectNN(T alpha, const DistMat<T>& A, const DistMat<T>& B, T beta, DistMat<T>& C, Dims d, int64_t W) {
+    Grid& g = *C.grid;
+    PeerArena& ar = *g.arena;
+    const int64_t sz = int64_t(sizeof(T)), vec = 16 / sz;
+    cudaStream_t cs = g.comm_stream;
+    const std::vector<int> rowm = g.comm_members(MR), colm = g.comm_members(MC);
+    const int ridx = g.me.mr, cidx = g.me.mc;
+    const int64_t mloc = C.lh(), nloc = C.lw();
+    const int64_t ldpa = std::max(vec, (mloc + vec - 1) / vec * vec);
+    Ev ready[2], freed[2], start;
+    PeerArena::Ticket ticketA[2], ticketB[2];
+    bool live[2] = {false, false};
+    start.record(C.stream);
+    start.block(cs);
+    const int64_t nbk = Grid::Blocksize();
+    auto width = [&](int64_t p) { return p >= 2 ? W : std::max(nbk, (W >> (2 - p)) / nbk * nbk); };
+    int64_t p = 0;
+    for (int64_t k0 = 0, kb = 0; k0 < d.k; k0 += kb, ++p) {
+        const int s = int(p & 1);
+        kb = std::min(width(p), d.k - k0);
+        if (live[s]) {  // the GEMM that read this slot two panels ago is done: hand the slot back
+            freed[s].block(cs);
+            ar.Release(ticketA[s], rowm, ridx, cs);
+            ar.Release(ticketB[s], colm, cidx, cs);
+            live[s] = false;
+        }
+        const DistMat<T> A1 = A.View(0, d.m, k0, k0 + kb);
+        const DistMat<T> B1 = B.View(k0, k0 + kb, 0, d.n);
+        const int64_t ldpb = std::max(vec, (kb + vec - 1) / vec * vec);
+        const DirectPanelPlan plan = plan_direct_panel(g.shape, g.me, kb, A1.spec.row_align, B1.spec.col_align);
+        std::vector<PeerArena::Copy2D> ca;
+        for (const PanelCols& pc : plan.a_cols) {
+            PeerArena::Copy2D cp;
+            cp.dst_offset = size_t(pc.dst_col0 * ldpa * sz);
+            cp.dpitch = size_t(pc.dst_step * ldpa * sz);
+            cp.src = A1.buf + pc.src_col0 * A1.ldim;
+            cp.spitch = size_t(pc.src_step * A1.ldim * sz);
+            cp.width = size_t(mloc * sz);
+            cp.height = size_t(pc.count);
+            ca.push_back(cp);
+        }
+        ticketA[s] = ar.GatherDirect(Grid::arena_channel(MR), rowm, ridx, ca, cs);
+        // my rows of the B panel: one block at row offset off[my mc]
+        std::vector<PeerArena::Copy2D> cb(1);
+        cb[0].dst_offset = size_t(plan.b_row0 * sz);
+        cb[0].dpitch = size_t(ldpb * sz);
+        cb[0].src = B1.buf;
+        cb[0].spitch = size_t(B1.ldim * sz);
+        cb[0].width = size_t(plan.b_rows * sz);
+        cb[0].height = size_t(nloc);
+        ticketB[s] = ar.GatherDirect(Grid::arena_channel(MC), colm, cidx, cb, cs);
+        live[s] = true;
+        ready[s].record(cs);
+        ready[s].block(C.stream);
+        gemm_profiled<T>(0, 0, mloc, nloc, kb, alpha, static_cast<const T*>(ticketA[s].data), ldpa,
+                         static_cast<const T*>(ticketB[s].data), ldpb, p == 0 ? beta : T(1), C.buf, C.ldim, C.stream);
+        freed[s].record(C.stream);
+    }
+    for (int s = 0; s < 2; ++s)
+        if (live[s]) {
+            freed[s].block(cs);
+            ar.Release(ticketA[s], rowm, ridx, cs);
+            ar.Release(ticketB[s], colm, cidx, cs);
+        }
+}
+
 // ---- stationary C: C += alpha op(A)(:,kr) op(B)(kr,:) -----------------------------------------
 template <typename T>
 void SummaC(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, T beta, DistMat<T>& C, Dims d) {
@@ -129,6 +223,18 @@ void SummaC(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, T
     // on a 1 x 1 grid no panel moves: the whole k range is one local GEMM (C is read once)
     const int64_t W = g.size() == 1 ? std::max<int64_t>(d.k, 1) : Grid::PanelWidth(sizeof(T));
     static const bool overlap_on = [] { const char* e = std::getenv("ELB200_OVERLAP"); return !(e && std::atoi(e) == 0); }();
+    if (g.size() > 1 && g.comm_stream && g.arena && overlap_on && !ta && !tb) {
+        static const bool direct_on = [] { const char* e = std::getenv("ELB200_DIRECT"); return !(e && std::atoi(e) == 0); }();
+        // the two panels live in arena slots: shrink the panel width until they fit
+        const int64_t vec = 16 / int64_t(sizeof(T)), nbk = Grid::Blocksize();
+        const int64_t per_k = std::max(C.lh() + vec, C.lw()) * int64_t(sizeof(T));
+        int64_t Wd = std::min<int64_t>(W, (int64_t(g.arena->slot_bytes()) / per_k - vec) / nbk * nbk);
+        if (direct_on && Wd >= std::max<int64_t>(nbk, 512) && A.spec.col_align == C.spec.col_align &&
+            B.spec.row_align == C.spec.row_align) {
+            SummaCDirectNN(alpha, A, B, beta, C, d, Wd);
+            return;
+        }
+    }
     // An SM-resident NCCL gather fights the persistent GEMM for SMs (measured: slower than no
     // overlap at all), so the pipeline is used only with the copy-engine peer arena.
     if (g.size() == 1 || !g.comm_stream || !g.arena || !overlap_on) {
@@ -329,15 +435,6 @@ void Gemm(int ta, int tb, T alpha, const DistMat<T>& Apre, const DistMat<T>& Bpr
 // Two block slots keep PCIe (both directions), NVLink and the tensor pipe busy at the same time.
 // ---------------------------------------------------------------------------------------------
 namespace {
-struct Ev {
-    cudaEvent_t e = nullptr;
-    Ev() { cuda_check(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), "cudaEventCreate"); }
-    ~Ev() { if (e) cudaEventDestroy(e); }
-    Ev(const Ev&) = delete;
-    Ev& operator=(const Ev&) = delete;
-    void record(cudaStream_t s) { cuda_check(cudaEventRecord(e, s), "cudaEventRecord"); }
-    void block(cudaStream_t s) { cuda_check(cudaStreamWaitEvent(s, e, 0), "cudaStreamWaitEvent"); }
-};
 template <typename T>
 void copy_rect(T* dst, int64_t ldd, const T* src, int64_t lds, int64_t rows, int64_t cols, cudaMemcpyKind kind, cudaStream_t s) {
     if (rows <= 0 || cols <= 0) return;

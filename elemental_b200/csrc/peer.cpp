@@ -62,7 +62,7 @@ PeerArena* PeerArena::Create(ncclComm_t world, int rank, int size, cudaStream_t 
     const char* off = std::getenv("ELB200_P2P");
     if ((off && std::atoi(off) == 0) || size < 2 || size > kMaxRanks || !world) return nullptr;
     const char* mb = std::getenv("ELB200_ARENA_MB");
-    const size_t slot_bytes = size_t(mb && std::atoll(mb) > 0 ? std::atoll(mb) : 256) << 20;
+    const size_t slot_bytes = size_t(mb && std::atoll(mb) > 0 ? std::atoll(mb) : 512) << 20;
 
     PeerArena* pa = new PeerArena();
     pa->rank_ = rank; pa->size_ = size; pa->slot_bytes_ = slot_bytes;
@@ -183,6 +183,32 @@ PeerArena::Ticket PeerArena::AllGather(int channel, const std::vector<int>& memb
             cuda_check(cudaMemcpyAsync(slot_base(members[i], channel, t.slot) + size_t(my_index) * portion_bytes, send,
                                        send_bytes, cudaMemcpyDeviceToDevice, s), "PeerArena copy");
     // 3. tell them, 4. wait for theirs
+    for (int i = 0; i < g; ++i)
+        if (i != my_index) write_flag(flag(members[i], ARRIVE, channel, t.slot, rank_), t.seq, s);
+    for (int i = 0; i < g; ++i)
+        if (i != my_index) wait_flag(flag(rank_, ARRIVE, channel, t.slot, members[i]), t.seq, s);
+    t.data = slot_base(rank_, channel, t.slot);
+    return t;
+}
+
+PeerArena::Ticket PeerArena::GatherDirect(int channel, const std::vector<int>& members, int my_index,
+                                          const std::vector<Copy2D>& copies, cudaStream_t s) {
+    const int g = int(members.size());
+    const uint64_t n = uses_[channel]++;
+    Ticket t;
+    t.channel = channel;
+    t.slot = int(n & 1);
+    t.seq = uint32_t(n / 2 + 1);
+    for (int i = 0; i < g; ++i)
+        if (i != my_index) wait_flag(flag(rank_, ACK, channel, t.slot, members[i]), t.seq - 1, s);
+    for (int i = 0; i < g; ++i)
+        for (const Copy2D& c : copies) {
+            if (c.width == 0 || c.height == 0) continue;
+            if (c.dst_offset + (c.height - 1) * c.dpitch + c.width > slot_bytes_)
+                throw EngineError(ELB200_ERR_ARG, "PeerArena::GatherDirect: transfer leaves the slot");
+            cuda_check(cudaMemcpy2DAsync(slot_base(members[i], channel, t.slot) + c.dst_offset, c.dpitch, c.src, c.spitch,
+                                         c.width, c.height, cudaMemcpyDeviceToDevice, s), "PeerArena direct copy");
+        }
     for (int i = 0; i < g; ++i)
         if (i != my_index) write_flag(flag(members[i], ARRIVE, channel, t.slot, rank_), t.seq, s);
     for (int i = 0; i < g; ++i)

@@ -45,6 +45,21 @@ public:
     // Call after the last read of ticket.data has been enqueued on `s`.
     void Release(const Ticket& t, const std::vector<int>& members, int my_index, cudaStream_t s);
 
+    // Direct mode (SUMMA panels): every member's contribution goes with pitched 2-D copy-engine
+    // transfers straight to its final place inside each member's slot, which IS the panel the GEMM
+    // reads — no staging, no pack, no unpack kernel. `copies` is the same for every destination
+    // (all members lay the panel out identically). Release only after the panel has been consumed.
+    struct Copy2D {
+        size_t dst_offset;  // bytes from the slot base
+        size_t dpitch;      // bytes
+        const void* src;
+        size_t spitch;      // bytes
+        size_t width;       // bytes per row of the transfer
+        size_t height;      // rows of the transfer
+    };
+    Ticket GatherDirect(int channel, const std::vector<int>& members, int my_index, const std::vector<Copy2D>& copies,
+                        cudaStream_t s);
+
     // Pull mode (reductions): every member fills ITS OWN slot (t.data, `bytes` long) after Publish,
     // then Signal; afterwards each member reads all members' slots through the peer mapping
     // (PeerSlot) from a kernel — NVLink loads — and finally calls Release.

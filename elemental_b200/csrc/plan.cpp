@@ -253,4 +253,31 @@ ContractPlan plan_contract(const GridShape& g, GridCoord me, const DistSpec& A, 
     return plan;
 }
 
+DirectPanelPlan plan_direct_panel(const GridShape& g, GridCoord me, int64_t kb, int64_t a_row_align,
+                                  int64_t b_col_align) {
+    DirectPanelPlan p;
+    const int64_t r = g.r, c = g.c;
+    int64_t gcd = r, t = c;
+    while (t) { const int64_t x = gcd % t; gcd = t; t = x; }
+    const int64_t P = r / gcd, L = P * c;  // classes per source, lcm(r, c)
+    p.row_off.assign(size_t(r) + 1, 0);
+    for (int64_t q = 0; q < r; ++q) p.row_off[size_t(q) + 1] = p.row_off[size_t(q)] + Length(kb, Shift(q, b_col_align, r), r);
+    p.b_row0 = p.row_off[size_t(me.mc)];
+    p.b_rows = p.row_off[size_t(me.mc) + 1] - p.b_row0;
+    const int64_t shA = Shift(me.mr, a_row_align, c), cntA = Length(kb, shA, c);
+    for (int64_t u = 0; u < P && u < cntA; ++u) {
+        const int64_t t0 = shA + u * c;                       // panel-relative k of local column u
+        const int64_t q = Mod(t0 + b_col_align, r);           // its owner among the B rows
+        const int64_t i0 = (t0 - Shift(q, b_col_align, r)) / r;
+        PanelCols pc;
+        pc.dst_col0 = p.row_off[size_t(q)] + i0;
+        pc.dst_step = L / r;
+        pc.src_col0 = u;
+        pc.src_step = P;
+        pc.count = (cntA - u + P - 1) / P;
+        p.a_cols.push_back(pc);
+    }
+    return p;
+}
+
 }  // namespace elb

@@ -98,4 +98,22 @@ struct ContractPlan {
 };
 ContractPlan plan_contract(const GridShape& g, GridCoord me, const DistSpec& A, const DistSpec& B);
 
+// Zero-copy SUMMA-C panels (NN): layout of a kb-wide k-panel whose k indices are permuted so that
+// every owner's contribution is a strided block (engine_gemm.cpp SummaCDirectNN).
+//   B panel (kb x nloc): rows grouped by their owner in the column communicator; member q's local
+//     rows of B1 are rows [row_off[q], row_off[q+1]) of the panel.
+//   A panel (mloc x kb): column for panel-relative index t sits where row t of the B panel sits.
+//     This rank's local columns of A1 split into classes; class u maps local columns
+//     src_col0 + v*src_step to panel columns dst_col0 + v*dst_step, v = 0..count-1.
+struct PanelCols { int64_t dst_col0, dst_step, src_col0, src_step, count; };
+struct DirectPanelPlan {
+    std::vector<int64_t> row_off;   // r + 1 entries
+    std::vector<PanelCols> a_cols;  // this rank's contribution to the A panel
+    int64_t b_row0 = 0, b_rows = 0; // this rank's contribution to the B panel
+};
+// a_row_align: row alignment of the A1 view (k over MR); b_col_align: column alignment of the B1
+// view (k over MC).
+DirectPanelPlan plan_direct_panel(const GridShape& g, GridCoord me, int64_t kb, int64_t a_row_align,
+                                  int64_t b_col_align);
+
 }  // namespace elb

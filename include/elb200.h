@@ -217,6 +217,14 @@ int elb200_plan_copy(int grid_height, int grid_width, int vc_rank, const elb200_
                      const elb200_dist_spec* B, elb200_copy_plan* out);
 int elb200_plan_contract(int grid_height, int grid_width, int vc_rank, const elb200_dist_spec* A,
                          const elb200_dist_spec* B, elb200_contract_plan* out);
+/* Layout of a zero-copy SUMMA-C panel (NN) for an r x c grid, seen from VC rank `vc_rank`: the k
+ * indices of a kb-wide panel are permuted so that every owner's block is strided (see DESIGN.md
+ * 3.5). row_off[r+1]: member q's B rows occupy panel rows [row_off[q], row_off[q+1]);
+ * a_cols[5*i..]: {dst_col0, dst_step, src_col0, src_step, count} for this rank's i-th class of A1
+ * columns (at most r classes); b_row0/b_rows: this rank's rows of the B panel. Host-only. */
+int elb200_plan_direct_panel(int grid_height, int grid_width, int vc_rank, int64_t kb,
+                             int64_t a_row_align, int64_t b_col_align, int64_t* row_off,
+                             int64_t* a_cols, int* nclasses, int64_t* b_row0, int64_t* b_rows);
 /* Shift_/Length_/MaxLength_ (include/El/core/indexing/impl.hpp:33-66,244-245) and
  * Grid::DefaultHeight (src/core/Grid.cpp:57-63), exported for the parity tests. */
 int64_t elb200_shift(int64_t rank, int64_t align, int64_t stride);

@@ -182,3 +182,51 @@ def test_planner_reproduces_reference_placement(tag):
             ref = blob[off:off + lh * lw].reshape((lh, lw), order="F")
             assert np.array_equal(done[key].loc[vc], ref), (tag, q, key)
     assert len(done) == 121
+
+
+@pytest.mark.parametrize("shape", [(1, 2), (2, 1), (2, 2), (2, 4), (4, 2), (2, 3), (3, 2), (3, 3), (4, 6)])
+def test_direct_panel_layout(shape):
+    """Zero-copy SUMMA-C panels (elb200_plan_direct_panel): every rank's strided contributions,
+    applied for all members of its row / column communicator, build an A panel and a B panel whose
+    product equals A1 * B1 restricted to that rank — for ragged panel widths, panel offsets that
+    shift the alignments, and grids where r does not divide c."""
+    import ctypes as C
+    g = OD.Grid(*shape)
+    r, c = shape
+    rng = np.random.default_rng(13)
+    m, n = 9, 7
+    for (k0, kb, caA, raA, caB, raB) in ((0, 16, 0, 0, 0, 0), (5, 13, 1, 2, 3, 1), (3, 1, 0, 1, 1, 0), (7, r * c + 3, 1, 1, 0, 2)):
+        K = k0 + kb + 2
+        A = rng.integers(-4, 5, (m, K)).astype(np.float64)
+        B = rng.integers(-4, 5, (K, n)).astype(np.float64)
+        Ad = OD.VDM.from_global(g, A, OD.MC, OD.MR, caA, raA)
+        Bd = OD.VDM.from_global(g, B, OD.MC, OD.MR, caB, raB)
+        A1, B1 = Ad.view(0, m, k0, k0 + kb), Bd.view(k0, k0 + kb, 0, n)
+        ref = A[:, k0:k0 + kb] @ B[k0:k0 + kb, :]
+        plans = {}
+        for q in range(g.p):
+            row_off = (C.c_int64 * (r + 1))()
+            a_cols = (C.c_int64 * (5 * 64))()
+            ncls, b0, bn = C.c_int(), C.c_int64(), C.c_int64()
+            assert L.lib.elb200_plan_direct_panel(r, c, q, kb, A1.spec.row_align, B1.spec.col_align, row_off, a_cols,
+                                                  C.byref(ncls), C.byref(b0), C.byref(bn)) == 0
+            plans[q] = (list(row_off), [tuple(a_cols[5 * i:5 * i + 5]) for i in range(ncls.value)], b0.value, bn.value)
+            assert row_off[r] == kb and bn.value == B1.loc[q].shape[0]
+        for q in range(g.p):
+            mc, mr = g.coords(q)
+            PA = np.full((A1.loc[q].shape[0], kb), np.nan)
+            PB = np.full((kb, B1.loc[q].shape[1]), np.nan)
+            for j in range(c):  # row communicator: everybody with my mc contributes columns of A1
+                src = g.vc(mc, j)
+                for (d0, ds, s0, ss, cnt) in plans[src][1]:
+                    for v in range(cnt):
+                        assert np.isnan(PA[:, d0 + v * ds]).all(), "two columns landed on the same place"
+                        PA[:, d0 + v * ds] = A1.loc[src][:, s0 + v * ss]
+            for i in range(r):  # column communicator: everybody with my mr contributes rows of B1
+                src = g.vc(i, mr)
+                _, _, b0, bn = plans[src]
+                assert np.isnan(PB[b0:b0 + bn, :]).all()
+                PB[b0:b0 + bn, :] = B1.loc[src]
+            assert not np.isnan(PA).any() and not np.isnan(PB).any(), (shape, k0, kb, q)
+            cspec = OD.Spec(OD.MC, OD.MR, caA, raB, m, n)  # C aligned with A's rows and B's columns
+            assert np.array_equal(PA @ PB, OD.local_of(ref, cspec, g, q)), (shape, k0, kb, q)
