@@ -174,10 +174,55 @@ transpose_kernel(int64_t rows, int64_t cols, const T* __restrict__ A, int64_t ld
     }
 }
 
+// 64 x 64 tile, 16-byte global accesses on both sides (4 fp32 / 2 fp64 per thread and access):
+// enough bytes in flight per SM to reach the HBM roof also for 4-byte elements.
+template <typename T, bool AXPY>
+__global__ void __launch_bounds__(256)
+transpose_vec_kernel(int64_t rows, int64_t cols, const T* __restrict__ A, int64_t lda, T* B, int64_t ldb, T alpha) {
+    using V = typename VecOf<T>::type;
+    constexpr int N = VecOf<T>::N, TS = 64, TX = TS / N, TY = 256 / TX;
+    __shared__ T tile[TS][TS + 1];
+    const int64_t r0 = int64_t(blockIdx.x) * TS, c0 = int64_t(blockIdx.y) * TS;
+    const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
+#pragma unroll
+    for (int cc = ty; cc < TS; cc += TY) {
+        const int64_t r = r0 + tx * N, c = c0 + cc;
+        if (r < rows && c < cols) {
+            T e[N];
+            *reinterpret_cast<V*>(e) = *reinterpret_cast<const V*>(A + r + c * lda);
+#pragma unroll
+            for (int i = 0; i < N; ++i) tile[cc][tx * N + i] = e[i];
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int rr = ty; rr < TS; rr += TY) {
+        const int64_t c = c0 + tx * N, r = r0 + rr;  // B(c, r) = A(r, c)
+        if (r < rows && c < cols) {
+            T e[N];
+#pragma unroll
+            for (int i = 0; i < N; ++i) e[i] = tile[tx * N + i][rr];
+            V* d = reinterpret_cast<V*>(B + c + r * ldb);
+            if constexpr (AXPY) *d = vaxpy(alpha, *reinterpret_cast<V*>(e), *d);
+            else *d = *reinterpret_cast<V*>(e);
+        }
+    }
+}
+
 template <typename T, bool AXPY>
 int launch_transpose(int64_t rows, int64_t cols, const T* A, int64_t lda, T* B, int64_t ldb,
                      T alpha, cudaStream_t s) {
     if (rows <= 0 || cols <= 0) return ELB200_OK;
+    constexpr int NV = VecOf<T>::N;
+    // (fp64 already reaches the HBM roof with the 32 x 32 tile below: measured 6633 vs 5401 GB/s)
+    if (sizeof(T) == 4 && rows % NV == 0 && cols % NV == 0 && lda % NV == 0 && ldb % NV == 0 &&
+        (reinterpret_cast<uintptr_t>(A) & 15u) == 0 && (reinterpret_cast<uintptr_t>(B) & 15u) == 0 &&
+        (cols + 63) / 64 <= 65535) {
+        count_launch();
+        transpose_vec_kernel<T, AXPY><<<dim3(unsigned((rows + 63) / 64), unsigned((cols + 63) / 64)), 256, 0, s>>>(
+            rows, cols, A, lda, B, ldb, alpha);
+        return check_cuda(cudaGetLastError(), "transpose_vec_kernel");
+    }
     const int64_t gx = (rows + 31) / 32, gy = (cols + 31) / 32;
     if (gy > 65535) {
         const int64_t slab = int64_t(65535) * 32;
@@ -223,11 +268,99 @@ lattice_kernel(const __grid_constant__ SegTable tab, T* M, int64_t ldm, T* buf, 
     }
 }
 
+// Row-interleaved portions (ColStridedPack / ColStridedUnpack, Copy/util.hpp:167-230): segment q
+// owns the rows I of the matrix with I mod S == residue_q.  Walking each segment on its own touches
+// one element per S of every 32-byte sector; walking the MATRIX rows instead (thread <-> row I,
+// segment looked up from I mod S) makes the matrix side fully coalesced and the staging side S
+// interleaved streams of consecutive elements, so every sector moved is fully used.
+struct InterleaveTable {
+    int64_t buf_offset[ELB200_MAX_SEGMENTS];  // by residue; -1: nobody owns that residue
+    int64_t seg_rows[ELB200_MAX_SEGMENTS];
+    int64_t first_row[ELB200_MAX_SEGMENTS];
+    int64_t S, col0, col_step, cols, rows_total;
+};
+template <typename T, int MODE>
+__global__ void __launch_bounds__(256)
+interleave_kernel(const __grid_constant__ InterleaveTable tab, T* M, int64_t ldm, T* buf, T alpha) {
+    for (int64_t I = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; I < tab.rows_total; I += int64_t(gridDim.x) * blockDim.x) {
+        const int res = int(I % tab.S);
+        const int64_t off = tab.buf_offset[res];
+        if (off < 0 || I < tab.first_row[res]) continue;
+        const int64_t i = (I - tab.first_row[res]) / tab.S, nr = tab.seg_rows[res];
+        if (i >= nr) continue;
+        // four columns per trip: four independent loads in flight before the first store
+        constexpr int U = 4;
+        for (int64_t j0 = int64_t(blockIdx.y) * U; j0 < tab.cols; j0 += int64_t(gridDim.y) * U) {
+            T v[U], w[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int64_t j = j0 + u;
+                if (j < tab.cols) {
+                    const T* mp = M + I + (tab.col0 + j * tab.col_step) * ldm;
+                    const T* bp = buf + off + i + j * nr;
+                    if constexpr (MODE == ELB200_PACK) v[u] = *mp;
+                    else v[u] = *bp;
+                    if constexpr (MODE == ELB200_UNPACK_AXPY) w[u] = *mp;
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int64_t j = j0 + u;
+                if (j < tab.cols) {
+                    T* mp = M + I + (tab.col0 + j * tab.col_step) * ldm;
+                    T* bp = buf + off + i + j * nr;
+                    if constexpr (MODE == ELB200_PACK) *bp = v[u];
+                    else if constexpr (MODE == ELB200_UNPACK) *mp = v[u];
+                    else *mp = fma(alpha, v[u], w[u]);
+                }
+            }
+        }
+    }
+}
+// true (and the launch done) when the segment set is a row interleave
+template <typename T>
+bool try_interleave(int mode, int nseg, const elb200_segment* segs, T* M, int64_t ldm, T* buf, T alpha, cudaStream_t s,
+                    int* status) {
+    if (nseg < 2) return false;
+    const int64_t S = segs[0].row_step;
+    if (S < 2 || S > ELB200_MAX_SEGMENTS) return false;
+    InterleaveTable tab;
+    for (int q = 0; q < ELB200_MAX_SEGMENTS; ++q) { tab.buf_offset[q] = -1; tab.seg_rows[q] = 0; tab.first_row[q] = 0; }
+    tab.S = S; tab.col0 = segs[0].col0; tab.col_step = segs[0].col_step; tab.cols = segs[0].cols; tab.rows_total = 0;
+    int live = 0;
+    for (int k = 0; k < nseg; ++k) {
+        const elb200_segment& g = segs[k];
+        if (g.rows == 0 || g.cols == 0) continue;
+        if (g.row_step != S || g.col0 != tab.col0 || g.col_step != tab.col_step || g.cols != tab.cols) return false;
+        const int res = int(g.row0 % S);
+        if (tab.buf_offset[res] >= 0) return false;  // two segments on one residue: not an interleave
+        tab.buf_offset[res] = g.buf_offset; tab.seg_rows[res] = g.rows; tab.first_row[res] = g.row0;
+        tab.rows_total = std::max(tab.rows_total, g.row0 + (g.rows - 1) * S + 1);
+        ++live;
+    }
+    if (live < 2 || tab.cols <= 0) return false;
+    const int64_t gx = std::min<int64_t>((tab.rows_total + 255) / 256, 1024);
+    const int64_t gy = std::min<int64_t>((tab.cols + 3) / 4, std::max<int64_t>(1, 16 * device_sm_count() / gx));
+    dim3 grid(static_cast<unsigned>(gx), static_cast<unsigned>(gy));
+    count_launch();
+    if (mode == ELB200_PACK) interleave_kernel<T, ELB200_PACK><<<grid, 256, 0, s>>>(tab, M, ldm, buf, alpha);
+    else if (mode == ELB200_UNPACK) interleave_kernel<T, ELB200_UNPACK><<<grid, 256, 0, s>>>(tab, M, ldm, buf, alpha);
+    else interleave_kernel<T, ELB200_UNPACK_AXPY><<<grid, 256, 0, s>>>(tab, M, ldm, buf, alpha);
+    *status = check_cuda(cudaGetLastError(), "interleave_kernel");
+    return true;
+}
+
 template <typename T>
 int launch_lattice(int mode, int nseg, const elb200_segment* segs, T* M, int64_t ldm, T* buf,
                    T alpha, cudaStream_t s) {
     if (nseg < 0 || nseg > ELB200_MAX_SEGMENTS || (nseg > 0 && !segs)) return ELB200_ERR_ARG;
     if (mode < 0 || mode > 2) return ELB200_ERR_ARG;
+    for (int k = 0; k < nseg; ++k)
+        if (segs[k].rows < 0 || segs[k].cols < 0 || segs[k].row_step < 1 || segs[k].col_step < 1) return ELB200_ERR_ARG;
+    if (lattice_cta_limit() == 0) {
+        int st = ELB200_OK;
+        if (try_interleave<T>(mode, nseg, segs, M, ldm, buf, alpha, s, &st)) return st;
+    }
     using V = typename VecOf<T>::type;
     constexpr int N = VecOf<T>::N;
     SegTable tab;
@@ -296,6 +429,30 @@ peer_reduce_axpy_kernel(const __grid_constant__ PeerSources<T> src, int64_t off,
         }
 }
 template <typename T>
+__global__ void __launch_bounds__(256)
+peer_reduce_axpy_vec_kernel(const __grid_constant__ PeerSources<T> src, int64_t off, const elb200_segment sg, T* M,
+                            int64_t ldm, T alpha) {
+    using V = typename VecOf<T>::type;
+    constexpr int N = VecOf<T>::N;
+    const int64_t rows_v = sg.rows / N;
+    for (int64_t j = blockIdx.y; j < sg.cols; j += gridDim.y)
+        for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < rows_v; i += int64_t(gridDim.x) * blockDim.x) {
+            const int64_t e = off + i * N + j * sg.rows;
+            T acc[N];
+#pragma unroll
+            for (int t = 0; t < N; ++t) acc[t] = T(0);
+            for (int s = 0; s < src.n; ++s) {
+                T v[N];
+                *reinterpret_cast<V*>(v) = *reinterpret_cast<const V*>(src.p[s] + e);
+#pragma unroll
+                for (int t = 0; t < N; ++t) acc[t] += v[t];
+            }
+            V* mp = reinterpret_cast<V*>(M + sg.row0 + i * N + (sg.col0 + j * sg.col_step) * ldm);
+            *mp = vaxpy(alpha, *reinterpret_cast<V*>(acc), *mp);
+        }
+}
+
+template <typename T>
 int peer_reduce_axpy(int nsrc, const T* const* srcs, int64_t off, const elb200_segment* seg, T* M, int64_t ldm, T alpha,
                      void* stream) {
     if (nsrc < 1 || nsrc > ELB200_MAX_SEGMENTS || !srcs || !seg || seg->rows < 0 || seg->cols < 0 || seg->row_step < 1 ||
@@ -305,8 +462,21 @@ int peer_reduce_axpy(int nsrc, const T* const* srcs, int64_t off, const elb200_s
     PeerSources<T> ps;
     ps.n = nsrc;
     for (int i = 0; i < nsrc; ++i) ps.p[i] = srcs[i];
+    constexpr int NV = VecOf<T>::N;
+    bool vec = seg->row_step == 1 && seg->rows % NV == 0 && seg->row0 % NV == 0 && off % NV == 0 && ldm % NV == 0 &&
+               (reinterpret_cast<uintptr_t>(M) & 15u) == 0;
+    for (int i = 0; i < nsrc; ++i) vec = vec && (reinterpret_cast<uintptr_t>(srcs[i]) & 15u) == 0;
+    if (vec) {
+        const int64_t rows_v = seg->rows / NV;
+        const int64_t vx = std::min<int64_t>((rows_v + 255) / 256, 64);
+        const int64_t vy = std::min<int64_t>(seg->cols, std::max<int64_t>(1, 16 * device_sm_count() / vx));
+        count_launch();
+        peer_reduce_axpy_vec_kernel<T><<<dim3(static_cast<unsigned>(vx), static_cast<unsigned>(vy)), 256, 0,
+                                         static_cast<cudaStream_t>(stream)>>>(ps, off, *seg, M, ldm, alpha);
+        return check_cuda(cudaGetLastError(), "peer_reduce_axpy_vec_kernel");
+    }
     const int64_t gx = std::min<int64_t>((seg->rows + 255) / 256, 64);
-    const int64_t gy = std::min<int64_t>(seg->cols, std::max<int64_t>(1, 4 * device_sm_count() / gx));
+    const int64_t gy = std::min<int64_t>(seg->cols, std::max<int64_t>(1, 16 * device_sm_count() / gx));
     count_launch();
     peer_reduce_axpy_kernel<T><<<dim3(static_cast<unsigned>(gx), static_cast<unsigned>(gy)), 256, 0,
                                  static_cast<cudaStream_t>(stream)>>>(ps, off, *seg, M, ldm, alpha);

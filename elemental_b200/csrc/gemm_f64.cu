@@ -3,14 +3,15 @@
 // Replaces the cublasDgemm call of the reference's LocalGemm
 // (reference: src/hydrogen/device/cuBLAS_API.cpp:282-300 via src/blas_like/level3/Gemm.cpp:163-186).
 // tcgen05 has no f64 kind, so FP64 tensor math is the warp-level mma.sync.m8n8k4.f64 (SASS DMMA)
-// fed by a 4-stage cp.async (LDGSTS) pipeline.
+// fed by a 3-stage cp.async (LDGSTS) pipeline of 128 x 32 operand tiles (ELB_F64_BK / ELB_F64_STAGES;
+// measured on B200: BK 32 x 3 stages 32.7 TF/s, BK 16 x 4 stages 31.5 TF/s at n = 16384).
 //
 // The kernel computes C^T = op(B)^T * op(A)^T so that each thread's accumulator pair is two
 // CONSECUTIVE rows of one column of C: 16-byte loads/stores into the column-major C.
 //   mma A-role (8x4, row): op(B)(k,n)  with n = lane/4, k = lane%4
 //   mma B-role (4x8, col): op(A)(m,k)  with m = lane/4, k = lane%4
 //   D (8x8): thread holds C(m = 2*(lane%4)+{0,1}, n = lane/4)
-// CTA tile 128(m) x 128(n) x 16(k); 8 warps as 2(m) x 4(n), each 64 x 32: 32 DMMAs per k4 step
+// CTA tile 128(m) x 128(n) x BK(k); 8 warps as 2(m) x 4(n), each 64 x 32: 32 DMMAs per k4 step
 // against 12 conflict-free LDS.64.
 #include <cuda_runtime.h>
 #include <cstdint>
@@ -47,7 +48,7 @@ __device__ __forceinline__ void tile_coords(int t, int tiles_m, int tiles_n, int
     tm = r / gsize;
 }
 
-// Copy one operand tile (128 mn x 16 k) global -> smem with zero fill outside the matrix.
+// Copy one operand tile (128 mn x BK k) global -> smem with zero fill outside the matrix.
 //  MN_CONTIG: X(mn,k) at X[k*ld + mn]  -> smem [k][mn] pitch kPitchMN
 //  else     : X(mn,k) at X[mn*ld + k]  -> smem [mn][k] pitch kPitchK
 template <bool MN_CONTIG, int VEC>

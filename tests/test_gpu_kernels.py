@@ -141,6 +141,28 @@ def test_transpose(L, dtype, rows, cols):
 
 
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("rows,cols", [(132, 200), (64, 64), (4, 516)])
+def test_transpose_vector_path(L, dtype, rows, cols):
+    """16-byte-aligned operands take the 64 x 64 vectorised kernel (tiles with ragged edges)."""
+    sfx = SUF[dtype]
+    lda, ldb = rows + 4, cols + 8
+    A = colmajor(rows, cols, lda, dtype, 15)
+    B0 = np.full((rows, ldb), 9.0, dtype=dtype)
+    d = dev(B0)
+    assert getattr(L.lib, f"elb200_transpose_{sfx}")(rows, cols, dev(A).data_ptr(), lda, d.data_ptr(), ldb, None) == 0
+    exp = B0.copy(); exp[:, :cols] = A[:, :rows].T
+    assert np.array_equal(d.cpu().numpy(), exp)
+    A2 = colmajor(cols, rows, cols + 4, dtype, 16)
+    Bt = colmajor(rows, cols, rows + 4, dtype, 17, fill=1.0)
+    d = dev(Bt)
+    a = dtype(0.5)
+    assert getattr(L.lib, f"elb200_axpy2d_transpose_{sfx}")(rows, cols, a, dev(A2).data_ptr(), cols + 4, d.data_ptr(), rows + 4, None) == 0
+    exp = Bt.copy()
+    exp[:, :rows] = (np.longdouble(a) * A2[:, :cols].T.astype(np.longdouble) + Bt[:, :rows].astype(np.longdouble)).astype(dtype)
+    assert np.array_equal(d.cpu().numpy(), exp)
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
 @pytest.mark.parametrize("aligned", [True, False])
 def test_lattice_pack_unpack(L, dtype, aligned):
     """One launch moves every portion: RowStridedUnpack / ColStridedPack / StridedPack shapes
@@ -196,9 +218,9 @@ def test_peer_reduce_axpy(L, dtype):
     fn = getattr(L.lib, f"elb200_peer_reduce_axpy_{sfx}")
     rng = np.random.default_rng(3)
     H, W, ld = 37, 29, 40
-    for (seg, nsrc) in (((1, 2, 18, 3, 4, 6, 0), 3), ((0, 1, 37, 0, 1, 29, 0), 4), ((5, 3, 1, 2, 1, 1, 0), 2)):
+    for (seg, nsrc, off) in (((1, 2, 18, 3, 4, 6, 0), 3, 7), ((0, 1, 37, 0, 1, 29, 0), 4, 7), ((5, 3, 1, 2, 1, 1, 0), 2, 7),
+                             ((4, 1, 32, 1, 2, 9, 0), 3, 8), ((0, 1, 36, 0, 1, 29, 0), 5, 0)):  # last two: 16-byte vector path
         r0, rs, nr, c0, cs, nc, _ = seg
-        off = 7
         total = off + nr * nc + 3
         srcs = [rng.integers(-8, 9, total).astype(dtype) for _ in range(nsrc)]  # small ints: exact sums
         M = np.zeros((W, ld), dtype=dtype); M[:, :H] = rng.integers(-8, 9, (W, H)).astype(dtype)
