@@ -60,6 +60,17 @@ Grid::Grid(int height, int width, int vc, const ncclUniqueId* id, int dev) {
         cuda_check(cudaStreamCreateWithFlags(&comm_stream, cudaStreamNonBlocking), "cudaStreamCreate");
         cuda_check(cudaStreamCreateWithFlags(&h2d_stream, cudaStreamNonBlocking), "cudaStreamCreate");
         cuda_check(cudaStreamCreateWithFlags(&d2h_stream, cudaStreamNonBlocking), "cudaStreamCreate");
+        // Every temporary (panels, staging, proxies) comes from the device's stream-ordered pool.
+        // Its default release threshold is 0, i.e. all cached memory goes back to the driver at the
+        // next synchronisation and a Gemm with multi-GiB temporaries pays the mapping cost again
+        // on every call; keep it cached like the reference's CUB pool does (src/core/imports/cub.cpp).
+        // ELB200_POOL_KEEP_MB bounds what is kept (default: unbounded).
+        cudaMemPool_t pool = nullptr;
+        if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess && pool) {
+            const char* e = std::getenv("ELB200_POOL_KEEP_MB");
+            uint64_t keep = e && std::atoll(e) >= 0 ? uint64_t(std::atoll(e)) << 20 : UINT64_MAX;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        }
     }
     if (id && shape.size() > 1) {
         nccl_check(ncclCommInitRank(&world, shape.size(), *id, vc), "ncclCommInitRank");

@@ -357,6 +357,12 @@ template <typename T>
 void SummaDot(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, DistMat<T>& C, Dims d) {
     Grid& g = *C.grid;
     static const int64_t kBlock = [] { const char* e = std::getenv("ELB200_DOT_BLOCK"); int64_t v = e ? std::atoll(e) : 0; return v > 0 ? v : int64_t(8192); }();
+    if (g.size() == 1) {
+        // one rank: every distribution is the whole matrix, the k-split and the reduction are
+        // identities — multiply straight into C (beta was applied by the caller)
+        gemm_profiled<T>(ta, tb, d.m, d.n, d.k, alpha, A.buf, A.ldim, B.buf, B.ldim, T(1), C.buf, C.ldim, C.stream);
+        return;
+    }
     DistMat<T> Ak(g, ta ? VC : STAR, ta ? STAR : VC, C.stream);  // k over VC
     DistMat<T> Bk(g, tb ? STAR : VC, tb ? VC : STAR, C.stream);
     Ak.Align(0, 0); Bk.Align(0, 0);

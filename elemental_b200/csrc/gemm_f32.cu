@@ -21,6 +21,7 @@
 #include <cuda.h>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <mutex>
 
 #include "ptx.cuh"
@@ -374,6 +375,23 @@ int gemm_f32_tensor(int transA, int transB, int64_t m, int64_t n, int64_t k, flo
                     const float* A, int64_t lda, const float* B, int64_t ldb, float beta, float* C,
                     int64_t ldc, int cta_group, cudaStream_t stream) {
     if (cta_group == 0) cta_group = 2;
+    // The TMEM accumulator truncates, so the error of one launch grows linearly with the length of
+    // its accumulation chain (~5e-9 per k step, measured). Very long k is therefore cut into
+    // chunks that accumulate through the epilogue's rounded fp32 FMA (beta = 1 after the first):
+    // k = 262144 (BASELINE C5) then stays near 1e-4 instead of 1e-3 for < 1% more time. The bench
+    // shape (k = 16384) is one launch.
+    static const int64_t kchunk = [] { const char* e = std::getenv("ELB200_F32_KCHUNK"); int64_t v = e ? std::atoll(e) : 0; return v >= 256 ? v / 32 * 32 : int64_t(16384); }();
+    if (k > kchunk + kchunk / 2) {
+        for (int64_t k0 = 0; k0 < k; k0 += kchunk) {
+            const int64_t kc = (k - k0 < kchunk + kchunk / 2) ? k - k0 : kchunk;
+            const float* Ac = transA == 0 ? A + k0 * lda : A + k0;
+            const float* Bc = transB == 0 ? B + k0 : B + k0 * ldb;
+            const int st = gemm_f32_tensor(transA, transB, m, n, kc, alpha, Ac, lda, Bc, ldb, k0 == 0 ? beta : 1.0f, C, ldc, cta_group, stream);
+            if (st != ELB200_OK) return st;
+            if (kc != kchunk) break;
+        }
+        return ELB200_OK;
+    }
     // A is (m x k) if N else (k x m), column-major. 'N' -> m contiguous -> MN-major.
     const bool a_mn = (transA == 0);
     // B is (k x n) if N else (n x k). 'N' -> k contiguous -> K-major; 'T' -> n contiguous -> MN-major.

@@ -101,6 +101,47 @@ def test_gemm_roundtrip_property_large(grid1):
     assert e1 <= tol and e12 <= 2 * tol, (e1, e12, tol)
 
 
+@pytest.mark.parametrize("dtype,alg", [(torch.float32, 6), (torch.float64, 6), (torch.float32, 7)])
+def test_gemm_full_size_properties(grid1, dtype, alg):
+    """BASELINE configs at FULL size (C2: fp32 n = 16384 SUMMA_C; the per-GPU shape of C3 in fp64;
+    SUMMA_Dot on the same operands) checked through size-independent properties, since no CPU
+    oracle finishes n = 16384 in seconds:
+      * checksum of checksums: C 1 == alpha A (B 1) + beta C0 1 (fp64 matrix-vector products),
+      * 96 sampled rows of C against the fp64 product of those rows of A with B,
+    both within the north-star bound (1e-5 sqrt(k) fp32, 1e-13 sqrt(k) fp64, relative Frobenius)."""
+    from elemental_b200 import el
+    from oracle import gemm as OG
+    n, alpha, beta = 16384, 0.5, -0.5
+    gen = torch.Generator(device="cuda").manual_seed(21)
+    mats = []
+    with torch.cuda.stream(grid1.stream):
+        for _ in range(3):
+            M = el.DistMatrix(grid1, dtype=dtype).Resize(n, n)
+            M.Matrix().copy_((torch.rand((n, n), device="cuda", dtype=dtype, generator=gen) - 0.5) * 0.2)
+            mats.append(M)
+        A, B, Cm = mats
+        a, b, c = A.Matrix(), B.Matrix(), Cm.Matrix()   # local == global on 1 x 1
+        ones = torch.ones(n, device="cuda", dtype=torch.float64)
+        rows = torch.randperm(n, device="cuda", generator=gen)[:96]
+        c0_sum = c.double() @ ones
+        c0_rows = c[rows].double()
+    grid1.sync()
+    el.Gemm(el.NORMAL, el.NORMAL, alpha, A, B, beta, Cm, alg)
+    grid1.sync()
+    with torch.cuda.stream(grid1.stream):
+        want_sum = alpha * (a.double() @ (b.double() @ ones)) + beta * c0_sum
+        got_sum = c.double() @ ones
+        want_rows = alpha * (a[rows].double() @ b.double()) + beta * c0_rows
+        got_rows = c[rows].double()
+        e_sum = float(torch.linalg.norm(got_sum - want_sum) / torch.linalg.norm(want_sum))
+        e_rows = float(torch.linalg.norm(got_rows - want_rows) / torch.linalg.norm(want_rows))
+    grid1.sync()
+    tol = OG.gemm_tolerance(np.float32 if dtype == torch.float32 else np.float64, n)
+    assert e_rows <= tol and e_sum <= tol, (e_rows, e_sum, tol)
+    for M in mats:
+        M.destroy()
+
+
 @pytest.mark.parametrize("nproc,height", [(2, 1), (2, 2), (4, 2), (8, 2)])
 def test_multi_gpu_grids(nproc, height):
     if torch.cuda.device_count() < nproc:

@@ -271,6 +271,29 @@ def test_local_gemm_matches_oracle(L, dtype, ta, tb):
                 assert np.all(out[:, m:] == 5.0)  # padding rows of C untouched
 
 
+@pytest.mark.parametrize("ta,tb", list(itertools.product([0, 1], [0, 1])))
+def test_gemm_f32_long_k_chunks(L, ta, tb):
+    """k beyond 1.5 x 16384 is accumulated in chunks (bounded TMEM accumulation chains, BASELINE C5
+    shape class k >> m, n): every orientation must address its chunks correctly, keep the beta
+    semantics of the first chunk only, and stay well inside the fp32 bound (checked at a quarter of it)."""
+    m, n, k = 200, 136, 70000
+    g = torch.Generator(device="cuda").manual_seed(3)
+    ar, ac = (k, m) if ta else (m, k)
+    br, bc = (n, k) if tb else (k, n)
+    A = (torch.rand((ac, ar), device="cuda", generator=g) - 0.5) * 0.2   # column-major ar x ac
+    B = (torch.rand((bc, br), device="cuda", generator=g) - 0.5) * 0.2
+    C0 = torch.rand((n, m), device="cuda", generator=g) * 0.1
+    c = C0.clone()
+    assert L.lib.elb200_gemm_f32(ta, tb, m, n, k, 2.0, A.data_ptr(), ar, B.data_ptr(), br, 3.0, c.data_ptr(), m, None) == 0
+    torch.cuda.synchronize()
+    # a (cols, rows) row-major tensor X is the column-major matrix X.t()
+    opA = A.double() if ta else A.double().t()      # m x k
+    opB = B.double() if tb else B.double().t()      # k x n
+    ref = 2.0 * (opA @ opB) + 3.0 * C0.double().t()
+    err = float(torch.linalg.norm(c.double().t() - ref) / torch.linalg.norm(ref))
+    assert err <= 0.25 * OG.gemm_tolerance(np.float32, k), err
+
+
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
 def test_gemm_degenerate_and_errors(L, dtype):
     sfx = SUF[dtype]
