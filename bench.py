@@ -66,7 +66,7 @@ def load_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms DURING the timed region."""
+    """nvidia-smi clocks / throttle reasons sampled every 50 ms DURING the timed region."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
@@ -76,7 +76,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "200", "-i", str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                                          "-lms", "50", "-i", str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._pump, daemon=True)
             self.t.start()
         except Exception:
@@ -152,8 +152,11 @@ def cpu_reference_rate(dtype: str, n_sample: int, reps: int = 1):
             "sample": f"oracle restatement of SUMMA_NNC (numpy/OpenBLAS local gemm) n={n_sample}, 1x1 grid, nb=128"}
 
 
-def pick_cpu_sample(dtype: str) -> int:
-    """Largest n in {2048, 4096, 8192} whose sample should stay within ~10-30 s on this host."""
+def pick_cpu_sample(dtype: str, n_override: int = 0) -> int:
+    """Largest n in {2048, 4096, 8192} whose sample should stay within ~10-30 s on this host.
+    A small --n (e.g. BASELINE C1: --dtype f64 --n 2000) is run on the CPU at exactly that size."""
+    if 0 < n_override <= 8192:
+        return n_override
     import numpy as np
     npdt = np.float32 if dtype == "f32" else np.float64
     x = np.ones((1024, 1024), dtype=npdt)
@@ -171,7 +174,7 @@ def run_reference(args) -> int:
     if rank != 0:
         return 0
     n_full = workload_n(args.gpus, args.n)
-    n_s = pick_cpu_sample(args.dtype)
+    n_s = pick_cpu_sample(args.dtype, args.n)
     for _ in range(args.warmup if args.warmup < 2 else 1):
         cpu_reference_rate(args.dtype, min(n_s, 2048))
     vals, t0 = [], time.perf_counter()
@@ -191,7 +194,7 @@ def run_reference(args) -> int:
             "cpu_baseline": {"value": v, "unit": UNIT, **info},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -227,7 +230,7 @@ def run_ours(args) -> int:
         torch.cuda.synchronize()
         grid.close()  # collective: unmaps the peer arenas and frees the NCCL communicators
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -352,14 +355,15 @@ def _measure(args, grid, el, lib, torch, dist, world, rank, local, n_gpus, n, td
                 "peak_basis": basis}
         cpu = None
         if not args.no_cpu and n_gpus == 1:
-            n_s = pick_cpu_sample(args.dtype)
+            n_s = pick_cpu_sample(args.dtype, args.n)
             v, info = cpu_reference_rate(args.dtype, n_s)
             cpu = {"value": v, "unit": UNIT, **info}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": args.dtype,
                 "data": "synthetic",
                 "config": {"workload": f"El::Gemm {args.dtype} {['DEFAULT','SUMMA_A_MS','SUMMA_A','SUMMA_B_MS','SUMMA_B','SUMMA_C_MS','SUMMA_C','SUMMA_DOT','CANNON'][args.alg]} n={n} (NN, alpha=0.5, beta=-0.5), [MC,MR] on a {grid.Height()}x{grid.Width()} grid",
-                           "inputs": "Uniform(-0.1,0.1), resident in HBM", "l2": f"inputs {3 * n * n * esz / n_gpus / 2**20:.0f} MiB per GPU > 126 MB L2 (no flush needed)",
+                           "inputs": "Uniform(-0.1,0.1), resident in HBM", "l2": (f"inputs {3 * n * n * esz / n_gpus / 2**20:.0f} MiB per GPU > 126 MB L2 (no flush needed)" if 3 * n * n * esz / n_gpus > 2 * 126e6
+                                  else f"inputs {3 * n * n * esz / n_gpus / 2**20:.0f} MiB per GPU fit the 126 MB L2: --n diagnostic line, not a bench value"),
                            "panel_k": "full k on 1x1; ELB200_PANEL_K (default 4096 fp32 / 2048 fp64) otherwise",
                            "per_gpu_tflops": value / n_gpus},
                 "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
@@ -369,9 +373,28 @@ def _measure(args, grid, el, lib, torch, dist, world, rank, local, n_gpus, n, td
 
 def main() -> int:
     args = parse_args()
+    # The contract is ONE JSON line on stdout. Libraries below us write there too (torch prints
+    # "NCCL version ..." on rank 0 when the first communicator comes up), so everything but the
+    # final line is sent to stderr: fd 1 is pointed at fd 2 for the run and restored for the print.
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         return run_reference(args)
     return run_ours(args)
+
+
+_RESULT_FD = None
+
+
+def emit(line: dict) -> None:
+    data = (json.dumps(line) + "\n").encode()
+    sys.stdout.flush()
+    if _RESULT_FD is None:
+        os.write(1, data)
+    else:
+        os.write(_RESULT_FD, data)
 
 
 if __name__ == "__main__":
