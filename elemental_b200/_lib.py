@@ -25,8 +25,8 @@ lib = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
 MAX_SEGMENTS = 64
 UNIQUE_ID_BYTES = 128
 F32, F64 = 0, 1
-MC, MR, VC, VR, STAR = 0, 1, 2, 3, 4
-DIST_NAMES = {MC: "MC", MR: "MR", VC: "VC", VR: "VR", STAR: "STAR"}
+MC, MR, VC, VR, STAR, CIRC = 0, 1, 2, 3, 4, 5
+DIST_NAMES = {MC: "MC", MR: "MR", VC: "VC", VR: "VR", STAR: "STAR", CIRC: "CIRC"}
 # El::GemmAlgorithm, values as in the reference enum (include/El/blas_like/level3.hpp:23-33)
 (GEMM_DEFAULT, GEMM_SUMMA_A_MS, GEMM_SUMMA_A, GEMM_SUMMA_B_MS, GEMM_SUMMA_B, GEMM_SUMMA_C_MS, GEMM_SUMMA_C,
  GEMM_SUMMA_DOT, GEMM_CANNON) = range(9)
@@ -42,7 +42,7 @@ class Segment(C.Structure):
 
 class DistSpec(C.Structure):
     _fields_ = [("col_dist", C.c_int), ("row_dist", C.c_int), ("col_align", i64),
-                ("row_align", i64), ("height", i64), ("width", i64)]
+                ("row_align", i64), ("height", i64), ("width", i64), ("root", C.c_int)]
 
 
 class Message(C.Structure):
@@ -68,7 +68,7 @@ class DmInfo(C.Structure):
                 ("is_view", C.c_int), ("height", i64), ("width", i64), ("col_align", i64),
                 ("row_align", i64), ("col_shift", i64), ("row_shift", i64), ("col_stride", i64),
                 ("row_stride", i64), ("local_height", i64), ("local_width", i64), ("ldim", i64),
-                ("buffer", C.c_void_p)]
+                ("buffer", C.c_void_p), ("root", C.c_int)]
 
 
 vp = C.c_void_p
@@ -127,6 +127,9 @@ SIGNATURES = {
     "elb200_dm_align": (ci, [vp, i64, i64]),
     "elb200_dm_align_with": (ci, [vp, vp]),
     "elb200_dm_resize": (ci, [vp, i64, i64]),
+    "elb200_dm_set_root": (ci, [vp, ci]),
+    "elb200_dm_write_local": (ci, [vp, vp, i64]),
+    "elb200_dm_read_local": (ci, [vp, vp, i64]),
     "elb200_dm_attach": (ci, [vp, i64, i64, i64, i64, vp, i64]),
     "elb200_dm_view": (ci, [vp, i64, i64, i64, i64, C.POINTER(vp)]),
     "elb200_dm_copy": (ci, [vp, vp]),

@@ -47,6 +47,7 @@ DistSpec to_spec(const elb200_dist_spec& s) {
     d.col = Dist(s.col_dist); d.row = Dist(s.row_dist);
     d.col_align = s.col_align; d.row_align = s.row_align;
     d.height = s.height; d.width = s.width;
+    d.root = s.root;
     return d;
 }
 elb200_message to_msg(const Message& m) {
@@ -57,6 +58,7 @@ elb200_message to_msg(const Message& m) {
 bool spec_ok(const GridShape& g, const elb200_dist_spec& s) {
     if (!valid_pair(Dist(s.col_dist), Dist(s.row_dist))) return false;
     if (s.height < 0 || s.width < 0) return false;
+    if (Dist(s.col_dist) == CIRC ? (s.root < 0 || s.root >= g.size()) : s.root != 0) return false;
     if (s.col_align < 0 || s.col_align >= dist_stride(g, Dist(s.col_dist))) return false;
     if (s.row_align < 0 || s.row_align >= dist_stride(g, Dist(s.row_dist))) return false;
     return true;
@@ -216,6 +218,7 @@ int elb200_dm_info(elb200_dm_t a, elb200_dm_info_t* o) {
         o->col_stride = M.col_stride(); o->row_stride = M.row_stride();
         o->local_height = M.lh(); o->local_width = M.lw(); o->ldim = M.ldim;
         o->buffer = M.buf;
+        o->root = M.spec.root;
     };
     ELB_ON(a, fill(M), fill(M));
     return ELB200_OK;
@@ -230,6 +233,18 @@ int elb200_dm_align_with(elb200_dm_t a, elb200_dm_t o) {
         const DistSpec s = o->dtype == ELB200_F32 ? o->f->spec : o->d->spec;
         ELB_ON(a, M.AlignWith(s), M.AlignWith(s));
     });
+}
+int elb200_dm_set_root(elb200_dm_t a, int root) {
+    if (!a) return ELB200_ERR_ARG;
+    return guarded("elb200_dm_set_root", [&] { ELB_ON(a, M.SetRoot(root), M.SetRoot(root)); });
+}
+int elb200_dm_write_local(elb200_dm_t a, const void* src, int64_t ld) {
+    if (!a) return ELB200_ERR_ARG;
+    return guarded("elb200_dm_write_local", [&] { ELB_ON(a, M.WriteLocal(static_cast<const float*>(src), ld), M.WriteLocal(static_cast<const double*>(src), ld)); });
+}
+int elb200_dm_read_local(elb200_dm_t a, void* dst, int64_t ld) {
+    if (!a) return ELB200_ERR_ARG;
+    return guarded("elb200_dm_read_local", [&] { ELB_ON(a, M.ReadLocal(static_cast<float*>(dst), ld), M.ReadLocal(static_cast<double*>(dst), ld)); });
 }
 int elb200_dm_resize(elb200_dm_t a, int64_t h, int64_t w) {
     if (!a) return ELB200_ERR_ARG;

@@ -103,6 +103,12 @@ public:
     // (reference ElementalMatrix::AlignWith, src/core/DistMatrix/ElementMatrix.cpp).
     void AlignWith(const DistSpec& other, bool constrain = true);
     void Resize(int64_t height, int64_t width);
+    // [CIRC,CIRC]: which VC rank holds the matrix (reference SetRoot); keeps the contents only if
+    // the root does not change.
+    void SetRoot(int root);
+    // local matrix <-> host memory (column-major, ld >= local height), async on `stream`
+    void WriteLocal(const T* host, int64_t ld);
+    void ReadLocal(T* host, int64_t ld) const;
     void Attach(int64_t height, int64_t width, int64_t col_align, int64_t row_align, T* buffer, int64_t ld);
     // Zero-copy view of rows [i0,i1) x cols [j0,j1) (reference View/LockedView + operator()(IR,IR)).
     DistMat View(int64_t i0, int64_t i1, int64_t j0, int64_t j1) const;

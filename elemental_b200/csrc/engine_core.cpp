@@ -220,6 +220,36 @@ void DistMat<T>::Resize(int64_t h, int64_t w) {
 }
 
 template <typename T>
+void DistMat<T>::SetRoot(int root) {
+    if (root < 0 || root >= grid->size()) throw EngineError(ELB200_ERR_ARG, "SetRoot: root outside the grid");
+    if (spec.col != CIRC) {
+        if (root != 0) throw EngineError(ELB200_ERR_ARG, "SetRoot: only [CIRC,CIRC] matrices have a root");
+        return;
+    }
+    if (root == spec.root) return;
+    if (!owner) throw EngineError(ELB200_ERR_ARG, "SetRoot: cannot move the root of a view");
+    spec.root = root;
+    Resize(spec.height, spec.width);  // local extent changes from everything to nothing or back
+}
+
+template <typename T>
+void DistMat<T>::WriteLocal(const T* host, int64_t ld) {
+    const int64_t h = lh(), w = lw();
+    if (h == 0 || w == 0) return;
+    if (!host || ld < h) throw EngineError(ELB200_ERR_ARG, "WriteLocal: null buffer or ld < local height");
+    cuda_check(cudaMemcpy2DAsync(buf, size_t(ldim) * sizeof(T), host, size_t(ld) * sizeof(T), size_t(h) * sizeof(T), size_t(w),
+                                 cudaMemcpyHostToDevice, stream), "cudaMemcpy2DAsync(H2D)");
+}
+template <typename T>
+void DistMat<T>::ReadLocal(T* host, int64_t ld) const {
+    const int64_t h = lh(), w = lw();
+    if (h == 0 || w == 0) return;
+    if (!host || ld < h) throw EngineError(ELB200_ERR_ARG, "ReadLocal: null buffer or ld < local height");
+    cuda_check(cudaMemcpy2DAsync(host, size_t(ld) * sizeof(T), buf, size_t(ldim) * sizeof(T), size_t(h) * sizeof(T), size_t(w),
+                                 cudaMemcpyDeviceToHost, stream), "cudaMemcpy2DAsync(D2H)");
+}
+
+template <typename T>
 void DistMat<T>::Attach(int64_t h, int64_t w, int64_t ca, int64_t ra, T* buffer, int64_t ld) {
     if (owner && buf) cuda_check(cudaFreeAsync(buf, stream), "cudaFreeAsync");
     owner = false; capacity = 0;
@@ -239,10 +269,11 @@ DistMat<T> DistMat<T>::View(int64_t i0, int64_t i1, int64_t j0, int64_t j1) cons
     v.spec.height = i1 - i0; v.spec.width = j1 - j0;
     v.spec.col_align = Mod(spec.col_align + i0, col_stride());
     v.spec.row_align = Mod(spec.row_align + j0, row_stride());
+    v.spec.root = spec.root;
     v.col_constrained = v.row_constrained = true;
     const int64_t lr0 = Length(i0, col_shift(), col_stride());
     const int64_t lc0 = Length(j0, row_shift(), row_stride());
-    v.buf = buf ? buf + lr0 + lc0 * ldim : nullptr;
+    v.buf = buf && owns_data(grid->shape, spec, grid->me) ? buf + lr0 + lc0 * ldim : buf;
     v.ldim = ldim;
     return v;
 }

@@ -123,7 +123,7 @@ template <typename T>
 void TransposeCopy(const DistMat<T>& A, DistMat<T>& B) {
     Grid& g = *A.grid;
     cudaStream_t s = B.stream;
-    const bool same = B.spec.col == A.spec.row && B.spec.row == A.spec.col &&
+    const bool same = B.spec.col == A.spec.row && B.spec.row == A.spec.col && B.spec.root == A.spec.root &&
                       (!B.col_constrained || B.spec.col_align == A.spec.row_align) &&
                       (!B.row_constrained || B.spec.row_align == A.spec.col_align);
     if (same) {
@@ -134,6 +134,7 @@ void TransposeCopy(const DistMat<T>& A, DistMat<T>& B) {
         return;
     }
     DistMat<T> At(g, A.spec.row, A.spec.col, s);
+    At.spec.root = A.spec.root;
     At.Align(A.spec.row_align, A.spec.col_align);
     At.Resize(A.spec.width, A.spec.height);
     Dev<T>::transpose(A.lh(), A.lw(), A.buf, A.ldim, At.buf, At.ldim, s);

@@ -32,21 +32,25 @@ static int constrains(Dist d) {
         case MC: return 1;
         case MR: return 2;
         case VC:
-        case VR: return 3;
+        case VR:
+        case CIRC: return 3;  // ownership depends on both coordinates (one rank holds everything)
         default: return 0;
     }
 }
 
 bool valid_pair(Dist u, Dist v) {
+    if (u == CIRC || v == CIRC) return u == CIRC && v == CIRC;
     if (u < MC || u > STAR || v < MC || v > STAR) return false;
     return (constrains(u) & constrains(v)) == 0;
 }
 
 int64_t local_height(const GridShape& g, const DistSpec& d, GridCoord q) {
+    if (!owns_data(g, d, q)) return 0;
     const int s = dist_stride(g, d.col);
     return Length(d.height, Shift(dist_rank(g, d.col, q), d.col_align, s), s);
 }
 int64_t local_width(const GridShape& g, const DistSpec& d, GridCoord q) {
+    if (!owns_data(g, d, q)) return 0;
     const int s = dist_stride(g, d.row);
     return Length(d.width, Shift(dist_rank(g, d.row, q), d.row_align, s), s);
 }
@@ -94,6 +98,8 @@ Side side_of(const GridShape& g, const DistSpec& d, GridCoord q) {
 // local matrix on that rank.
 elb200_segment pair_lattice(const GridShape& g, const DistSpec& A, GridCoord src, const DistSpec& B,
                             GridCoord dst, bool of_a) {
+    elb200_segment none{};
+    if (!owns_data(g, A, src) || !owns_data(g, B, dst)) return none;  // [CIRC,CIRC]: only the root holds entries
     const Side sa = side_of(g, A, src), sb = side_of(g, B, dst);
     const Lattice1D rows = intersect(A.height, sa.row_shift, sa.row_stride, sb.row_shift, sb.row_stride);
     const Lattice1D cols = intersect(A.width, sa.col_shift, sa.col_stride, sb.col_shift, sb.col_stride);
@@ -134,7 +140,10 @@ CopyPlan plan_copy(const GridShape& g, GridCoord me, const DistSpec& A, const Di
     // alignment (reference: copy::RowAllGather / copy::ColAllGather aligned branches,
     // Copy/RowAllGather.hpp:30-76, Copy/ColAllGather.hpp:45-100).
     Dist gathered = STAR;
-    if (A.col == B.col && A.col_align == B.col_align && B.row == STAR && A.row != STAR)
+    if (A.col == CIRC || B.col == CIRC) {
+        // Gather to / Scatter from the root (reference copy::Gather, copy::Scatter,
+        // Copy/Gather.hpp, Copy/Scatter.hpp): point-to-point lattices through the general exchange
+    } else if (A.col == B.col && A.col_align == B.col_align && B.row == STAR && A.row != STAR)
         gathered = A.row;
     else if (A.row == B.row && A.row_align == B.row_align && B.col == STAR && A.col != STAR)
         gathered = A.col;
@@ -209,6 +218,7 @@ CopyPlan plan_copy(const GridShape& g, GridCoord me, const DistSpec& A, const Di
 ContractPlan plan_contract(const GridShape& g, GridCoord me, const DistSpec& A, const DistSpec& B) {
     ContractPlan plan;
     if (A.height != B.height || A.width != B.width) return plan;
+    if (A.col == CIRC || B.col == CIRC) return plan;  // no partial-sum form of [CIRC,CIRC]
     const bool col_same = A.col == B.col, row_same = A.row == B.row;
     const bool col_collect = !col_same && A.col == STAR, row_collect = !row_same && A.row == STAR;
     if (!(col_same || col_collect) || !(row_same || row_collect)) return plan;

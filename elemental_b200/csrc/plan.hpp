@@ -20,7 +20,9 @@
 
 namespace elb {
 
-enum Dist : int { MC = 0, MR = 1, VC = 2, VR = 3, STAR = 4 };
+// CIRC: the whole matrix on one rank (`root`, a VC rank); only valid as [CIRC,CIRC]
+// (reference DistMatrix<T,CIRC,CIRC>, src/core/DistMatrix/ElementMatrix/CIRC_CIRC.cpp).
+enum Dist : int { MC = 0, MR = 1, VC = 2, VR = 3, STAR = 4, CIRC = 5 };
 
 inline int64_t Mod(int64_t a, int64_t b) { int64_t r = a % b; return r < 0 ? r + b : r; }
 inline int64_t Shift(int64_t rank, int64_t align, int64_t stride) { return Mod(rank - align, stride); }
@@ -42,7 +44,7 @@ inline int vr_of(const GridShape& g, GridCoord q) { return q.mr + g.c * q.mc; }
 
 int dist_stride(const GridShape& g, Dist d);
 int dist_rank(const GridShape& g, Dist d, GridCoord q);
-bool valid_pair(Dist u, Dist v);  // the 11 ELEMENT-wrap pairs reachable from [MC,MR] Gemm
+bool valid_pair(Dist u, Dist v);  // the 11 ELEMENT-wrap pairs reachable from [MC,MR] Gemm + [CIRC,CIRC]
 
 // Distribution metadata of one DistMatrix (the reference's DistData + dims,
 // include/El/core/DistMatrix/AbstractDistMatrix.hpp).
@@ -50,7 +52,11 @@ struct DistSpec {
     Dist col = MC, row = MR;
     int64_t col_align = 0, row_align = 0;
     int64_t height = 0, width = 0;
+    int root = 0;  // [CIRC,CIRC] only: VC rank that owns the matrix (reference Root(), CrossComm = VCComm)
 };
+inline bool owns_data(const GridShape& g, const DistSpec& d, GridCoord q) {
+    return d.col != CIRC || vc_of(g, q) == d.root;
+}
 int64_t local_height(const GridShape& g, const DistSpec& d, GridCoord q);
 int64_t local_width(const GridShape& g, const DistSpec& d, GridCoord q);
 

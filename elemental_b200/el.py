@@ -16,7 +16,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import (F32, F64, MC, MR, STAR, VC, VR, check, lib)  # noqa: F401
+from ._lib import (CIRC, F32, F64, MC, MR, STAR, VC, VR, check, lib)  # noqa: F401
 
 NORMAL, TRANSPOSE, ADJOINT = 0, 1, 2  # El::Orientation (include/El/core/types.hpp)
 # El::GemmAlgorithm, values as in the reference enum (include/El/blas_like/level3.hpp:23-33)
@@ -160,6 +160,25 @@ class DistMatrix:
     def AlignWith(self, other: "DistMatrix"):
         check(lib.elb200_dm_align_with(self._h, other._h), "AlignWith"); return self
 
+    def Root(self): return self._info().root
+
+    def SetRoot(self, root: int):
+        """AbstractDistMatrix::SetRoot — the VC rank holding a [CIRC,CIRC] matrix."""
+        check(lib.elb200_dm_set_root(self._h, root), "SetRoot")
+        return self
+
+    def write_local_from_host(self, host: torch.Tensor) -> None:
+        """Local matrix <- host tensor laid out column-major as (LocalWidth, ld) rows (ld >= LocalHeight):
+        the CPU -> GPU DistMatrix copy of the reference (ProxyDevice.hpp). Async on the grid stream."""
+        if host.dim() != 2 or host.stride(1) != 1 or host.dtype != _TORCH[self.dtype] or host.is_cuda:
+            raise ValueError("host tensor must be a contiguous-row CPU tensor of the matrix dtype")
+        check(lib.elb200_dm_write_local(self._h, host.data_ptr(), host.stride(0) if host.shape[0] > 1 else max(host.shape[1], 1)), "write_local")
+
+    def read_local_to_host(self, host: torch.Tensor) -> None:
+        if host.dim() != 2 or host.stride(1) != 1 or host.dtype != _TORCH[self.dtype] or host.is_cuda:
+            raise ValueError("host tensor must be a contiguous-row CPU tensor of the matrix dtype")
+        check(lib.elb200_dm_read_local(self._h, host.data_ptr(), host.stride(0) if host.shape[0] > 1 else max(host.shape[1], 1)), "read_local")
+
     def Resize(self, height: int, width: int):
         check(lib.elb200_dm_resize(self._h, height, width), "Resize"); return self
 
@@ -201,6 +220,8 @@ class DistMatrix:
         """Resize to G's shape and load this rank's entries of the global matrix G."""
         self.Resize(G.shape[0], G.shape[1])
         inf = self._info()
+        if inf.local_height == 0 or inf.local_width == 0:
+            return self  # e.g. a [CIRC,CIRC] matrix away from its root
         self.set_local(np.ascontiguousarray(G[inf.col_shift::inf.col_stride, inf.row_shift::inf.row_stride]))
         return self
 

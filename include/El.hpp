@@ -49,7 +49,8 @@ inline int ToEngineDist(Dist d) {
         case VC: return 2;
         case VR: return 3;
         case STAR: return 4;
-        default: throw std::logic_error("El::Dist MD/CIRC are outside the Gemm path");
+        case CIRC: return 5;
+        default: throw std::logic_error("El::Dist MD is outside the Gemm path");
     }
 }
 template <typename T> struct TypeCode;
@@ -158,6 +159,9 @@ public:
     template <Dist U2, Dist V2>
     void AlignWith(const DistMatrix<T, U2, V2>& A) { detail::Check(elb200_dm_align_with(h_, A.Handle()), "AlignWith"); }
     void Resize(Int height, Int width) { detail::Check(elb200_dm_resize(h_, height, width), "Resize"); }
+    // [CIRC,CIRC] only: the VC rank that holds the matrix (AbstractDistMatrix.hpp:58,113)
+    void SetRoot(int root) { detail::Check(elb200_dm_set_root(h_, root), "SetRoot"); }
+    int Root() const { return Info().root; }
     // Attach(height, width, grid, colAlign, rowAlign, buffer, ldim): borrow device memory
     void Attach(Int height, Int width, Int colAlign, Int rowAlign, T* deviceBuffer, Int ldim) {
         detail::Check(elb200_dm_attach(h_, height, width, colAlign, rowAlign, deviceBuffer, ldim), "Attach");

@@ -181,12 +181,15 @@ int elb200_peer_reduce_axpy_f64(int nsrc, const double* const* srcs, int64_t src
  * For an r x c grid (COLUMN_MAJOR: VC rank = mc + r*mr, reference src/core/Grid.cpp:147-148) and
  * two element-cyclic distribution specs, returns what THIS rank packs, sends, receives and
  * unpacks for B = A (elb200_plan_copy) or B += sum-over-replicas(A) (elb200_plan_contract).
- * Distributions: 0=MC 1=MR 2=VC 3=VR 4=STAR (reference El::Dist, include/El/core/types.hpp).
+ * Distributions: 0=MC 1=MR 2=VC 3=VR 4=STAR 5=CIRC (reference El::Dist, include/El/core/types.hpp).
+ * CIRC is valid only as [CIRC,CIRC]: the whole matrix on VC rank `root`
+ * (src/core/DistMatrix/ElementMatrix/CIRC_CIRC.cpp; copy::Gather / copy::Scatter).
  * ---------------------------------------------------------------------------------------- */
 typedef struct elb200_dist_spec {
     int col_dist, row_dist;
     int64_t col_align, row_align;
     int64_t height, width;
+    int root; /* [CIRC,CIRC] only; 0 otherwise */
 } elb200_dist_spec;
 
 typedef struct elb200_message {
@@ -278,6 +281,7 @@ typedef struct elb200_dm_info_t {
     int64_t height, width, col_align, row_align, col_shift, row_shift;
     int64_t col_stride, row_stride, local_height, local_width, ldim;
     void* buffer; /* device pointer to the local column-major matrix */
+    int root;     /* owning VC rank of a [CIRC,CIRC] matrix (AbstractDistMatrix::Root) */
 } elb200_dm_info_t;
 
 int elb200_dm_create(elb200_grid_t g, int dtype, int col_dist, int row_dist, elb200_dm_t* out);
@@ -285,12 +289,21 @@ int elb200_dm_destroy(elb200_dm_t a);
 int elb200_dm_info(elb200_dm_t a, elb200_dm_info_t* out);
 int elb200_dm_align(elb200_dm_t a, int64_t col_align, int64_t row_align);
 int elb200_dm_align_with(elb200_dm_t a, elb200_dm_t other);
+/* AbstractDistMatrix::SetRoot (include/El/core/DistMatrix/AbstractDistMatrix.hpp:58): the VC rank
+ * that holds a [CIRC,CIRC] matrix. Collective metadata; every rank passes the same root. */
+int elb200_dm_set_root(elb200_dm_t a, int root);
 int elb200_dm_resize(elb200_dm_t a, int64_t height, int64_t width);
+/* Local matrix <-> HOST memory (column-major, leading dimension ld >= local height), the data
+ * movement of the reference's CPU <-> GPU DistMatrix copies (include/El/core/ProxyDevice.hpp,
+ * Matrix<T,Device::GPU>(Matrix<T,Device::CPU> const&)). Asynchronous on the matrix's stream; pinned
+ * host memory makes it a true overlap-able DMA. */
+int elb200_dm_write_local(elb200_dm_t a, const void* host_src, int64_t ld);
+int elb200_dm_read_local(elb200_dm_t a, void* host_dst, int64_t ld);
 int elb200_dm_attach(elb200_dm_t a, int64_t height, int64_t width, int64_t col_align,
                      int64_t row_align, void* device_buffer, int64_t ldim);
 int elb200_dm_view(elb200_dm_t a, int64_t i0, int64_t i1, int64_t j0, int64_t j1,
                    elb200_dm_t* out);
-/* B = A for any pair of the 11 distributions (DistMatrix::operator=). */
+/* B = A for any pair of the 11 distributions and [CIRC,CIRC] (DistMatrix::operator=). */
 int elb200_dm_copy(elb200_dm_t A, elb200_dm_t B);
 int elb200_dm_transpose(elb200_dm_t A, elb200_dm_t B); /* B = A^T (El::Transpose) */
 int elb200_dm_axpy(double alpha, elb200_dm_t X, elb200_dm_t Y);

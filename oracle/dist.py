@@ -9,7 +9,8 @@ Parity status: PINNED.  The reference stores no golden vectors for this path (SU
 the fixtures under tests/golden/ were produced by the reference's own CPU code compiled here
 (oracle/ref_build -> oracle/_ref, see oracle/README.md): single-rank El::Gemm outputs and index
 tables, and MULTI-RANK runs (1x2, 2x1, 2x2, 2x3, 3x2, 2x4 grids over a small multi-process MPI
-stub) giving the per-rank local matrices after all 121 redistributions and after El::Gemm.
+stub) giving the per-rank local matrices after all 121 redistributions, after the 23 [CIRC,CIRC]
+gather / scatter cases, and after El::Gemm.
 tests/test_oracle.py checks this restatement against them: redistributions bit for bit on every
 rank, Gemm within the north-star tolerance.
 """
@@ -20,11 +21,14 @@ from typing import Dict, List, Tuple
 
 import numpy as np
 
-MC, MR, VC, VR, STAR = 0, 1, 2, 3, 4
-NAMES = {MC: "MC", MR: "MR", VC: "VC", VR: "VR", STAR: "STAR"}
+MC, MR, VC, VR, STAR, CIRC = 0, 1, 2, 3, 4, 5
+NAMES = {MC: "MC", MR: "MR", VC: "VC", VR: "VR", STAR: "STAR", CIRC: "CIRC"}
 # the 11 ELEMENT-wrap pairs reachable from [MC,MR] Gemm
 PAIRS = [(MC, MR), (MC, STAR), (STAR, MC), (MR, STAR), (STAR, MR), (MR, MC), (VC, STAR),
          (STAR, VC), (VR, STAR), (STAR, VR), (STAR, STAR)]
+# + [CIRC,CIRC]: the whole matrix on one VC rank `root` (src/core/DistMatrix/ElementMatrix/CIRC_CIRC.cpp;
+# filled and emptied by copy::Gather / copy::Scatter, Copy/Gather.hpp, Copy/Scatter.hpp)
+PAIRS_WITH_CIRC = PAIRS + [(CIRC, CIRC)]
 
 
 # --------------------------------------------------------------------------- indexing
@@ -75,11 +79,11 @@ class Grid:
         return mr + self.c * mc  # Grid.cpp:148
 
     def stride(self, d: int) -> int:
-        return {MC: self.r, MR: self.c, VC: self.p, VR: self.p, STAR: 1}[d]
+        return {MC: self.r, MR: self.c, VC: self.p, VR: self.p, STAR: 1, CIRC: 1}[d]
 
     def rank(self, d: int, vc: int) -> int:
         mc, mr = self.coords(vc)
-        return {MC: mc, MR: mr, VC: vc, VR: self.vr(mc, mr), STAR: 0}[d]
+        return {MC: mc, MR: mr, VC: vc, VR: self.vr(mc, mr), STAR: 0, CIRC: 0}[d]
 
 
 @dataclass(frozen=True)
@@ -91,6 +95,10 @@ class Spec:
     row_align: int = 0
     height: int = 0
     width: int = 0
+    root: int = 0  # [CIRC,CIRC] only: the owning VC rank (AbstractDistMatrix::Root, CrossComm = VCComm)
+
+    def owns(self, vc: int) -> bool:
+        return self.U != CIRC or vc == self.root
 
     def col_shift(self, g: Grid, vc: int) -> int:
         return Shift(g.rank(self.U, vc), self.col_align, g.stride(self.U))
@@ -99,6 +107,8 @@ class Spec:
         return Shift(g.rank(self.V, vc), self.row_align, g.stride(self.V))
 
     def local_shape(self, g: Grid, vc: int) -> Tuple[int, int]:
+        if not self.owns(vc):
+            return (0, 0)
         return (Length(self.height, self.col_shift(g, vc), g.stride(self.U)),
                 Length(self.width, self.row_shift(g, vc), g.stride(self.V)))
 
@@ -106,6 +116,8 @@ class Spec:
 def local_of(G: np.ndarray, spec: Spec, g: Grid, vc: int) -> np.ndarray:
     """Entries of the global matrix G that rank vc stores: local(iLoc,jLoc) = G(colShift +
     iLoc*colStride, rowShift + jLoc*rowStride) (GlobalIndex, indexing/impl.hpp:68-69)."""
+    if not spec.owns(vc):
+        return np.zeros((0, 0), dtype=G.dtype, order="F")
     return np.array(G[spec.col_shift(g, vc)::g.stride(spec.U), spec.row_shift(g, vc)::g.stride(spec.V)],
                     order="F")
 
@@ -117,13 +129,15 @@ class VDM:
         self.g, self.spec, self.loc = g, spec, locals_
 
     @staticmethod
-    def from_global(g: Grid, G: np.ndarray, U: int, V: int, col_align: int = 0, row_align: int = 0) -> "VDM":
-        spec = Spec(U, V, col_align % g.stride(U), row_align % g.stride(V), G.shape[0], G.shape[1])
+    def from_global(g: Grid, G: np.ndarray, U: int, V: int, col_align: int = 0, row_align: int = 0,
+                    root: int = 0) -> "VDM":
+        spec = Spec(U, V, col_align % g.stride(U), row_align % g.stride(V), G.shape[0], G.shape[1],
+                    root if U == CIRC else 0)
         return VDM(g, spec, [local_of(G, spec, g, q) for q in range(g.p)])
 
     @staticmethod
-    def zeros(g: Grid, U, V, col_align, row_align, h, w, dtype) -> "VDM":
-        spec = Spec(U, V, col_align % g.stride(U), row_align % g.stride(V), h, w)
+    def zeros(g: Grid, U, V, col_align, row_align, h, w, dtype, root: int = 0) -> "VDM":
+        spec = Spec(U, V, col_align % g.stride(U), row_align % g.stride(V), h, w, root if U == CIRC else 0)
         return VDM(g, spec, [np.zeros(spec.local_shape(g, q), dtype=dtype, order="F") for q in range(g.p)])
 
     def to_global(self) -> np.ndarray:
@@ -132,6 +146,8 @@ class VDM:
         s, g = self.spec, self.g
         G = np.zeros((s.height, s.width), dtype=self.loc[0].dtype, order="F")
         for q in range(g.p):
+            if not s.owns(q):
+                continue
             G[s.col_shift(g, q)::g.stride(s.U), s.row_shift(g, q)::g.stride(s.V)] = self.loc[q]
         return G
 
@@ -141,6 +157,8 @@ class VDM:
         s, g = self.spec, self.g
         G = np.zeros((s.height, s.width), dtype=self.loc[0].dtype, order="F")
         for q in range(g.p):
+            if not s.owns(q):
+                continue
             G[s.col_shift(g, q)::g.stride(s.U), s.row_shift(g, q)::g.stride(s.V)] += self.loc[q]
         return G
 
@@ -149,7 +167,7 @@ class VDM:
         (include/El/core/View.hpp; AbstractDistMatrix::operator())."""
         s, g = self.spec, self.g
         nspec = Spec(s.U, s.V, (s.col_align + i0) % g.stride(s.U), (s.row_align + j0) % g.stride(s.V),
-                     i1 - i0, j1 - j0)
+                     i1 - i0, j1 - j0, s.root)
         out = []
         for q in range(g.p):
             r0 = Length(i0, s.col_shift(g, q), g.stride(s.U))
@@ -159,10 +177,10 @@ class VDM:
         return VDM(g, nspec, out)
 
 
-def redistribute(A: VDM, U: int, V: int, col_align: int = 0, row_align: int = 0) -> VDM:
+def redistribute(A: VDM, U: int, V: int, col_align: int = 0, row_align: int = 0, root: int = 0) -> VDM:
     """B = A for any (U,V)->(U',V'): the RESULT every copy:: routine must produce (exactly the
     entries of the global matrix each rank owns under the target distribution)."""
-    return VDM.from_global(A.g, A.to_global(), U, V, col_align, row_align)
+    return VDM.from_global(A.g, A.to_global(), U, V, col_align, row_align, root)
 
 
 # --------------------------------------------------------------------------- pipelines, step by step
@@ -197,7 +215,8 @@ def row_all_gather(A: VDM) -> VDM:
 
 def _same_free(g: Grid, s: Spec, t: int, q: int) -> bool:
     """t and q agree on the grid coordinates that neither U nor V depends on."""
-    dep = {MC: (True, False), MR: (False, True), VC: (True, True), VR: (True, True), STAR: (False, False)}
+    dep = {MC: (True, False), MR: (False, True), VC: (True, True), VR: (True, True), STAR: (False, False),
+           CIRC: (True, True)}
     du, dv = dep[s.U], dep[s.V]
     (tmc, tmr), (qmc, qmr) = g.coords(t), g.coords(q)
     ok = True

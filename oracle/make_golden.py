@@ -91,6 +91,7 @@ def make_dist_golden() -> None:
     tests/golden/ref_dist.npz, per grid tag g = f"r{r}c{c}" and rank q:
       {g}_q{q}_I    [rank, height, width, row, col, vcRank, vrRank]
       {g}_q{q}_R    rows [U V U2 V2 caA raA caB raB colShiftB rowShiftB lh lw offset]   (El::Dist enum values)
+      {g}_q{q}_Q    the 23 [CIRC,CIRC] cases (gather to / scatter from a root): R's columns + [rootA rootB]
       {g}_q{q}_G    rows [id oa ob alg m n k nb caC raC colShift rowShift lh lw offset]
       {g}_q{q}_bin  float64 blob the offsets index into (column-major local matrices)"""
     arrays = {}
@@ -117,14 +118,15 @@ def make_dist_golden() -> None:
                 if os.path.exists(shm):
                     os.remove(shm)
             for q in range(nproc):
-                recs = {"I": [], "R": [], "G": []}
+                recs = {"I": [], "R": [], "G": [], "Q": []}
                 for ln in open(os.path.join(tmp, f"rank{q}.txt")):
                     f = ln.split()
                     recs[f[0]].append([int(x) for x in f[1:]])
-                assert len(recs["R"]) == 121 and len(recs["G"]) == 20, (tag, q)
+                assert len(recs["R"]) == 121 and len(recs["G"]) == 20 and len(recs["Q"]) == 23, (tag, q)
                 arrays[f"{tag}_q{q}_I"] = np.array(recs["I"][0], dtype=np.int64)
                 arrays[f"{tag}_q{q}_R"] = np.array(recs["R"], dtype=np.int64)
                 arrays[f"{tag}_q{q}_G"] = np.array(recs["G"], dtype=np.int64)
+                arrays[f"{tag}_q{q}_Q"] = np.array(recs["Q"], dtype=np.int64)
                 arrays[f"{tag}_q{q}_bin"] = np.fromfile(os.path.join(tmp, f"rank{q}.bin"), dtype=np.float64)
     np.savez_compressed(os.path.join(OUT, "ref_dist.npz"), **arrays)
     print(f"wrote multi-rank reference runs for grids {[f'{h}x{n // h}' for n, h in DIST_GRIDS]}")

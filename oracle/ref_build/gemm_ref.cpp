@@ -109,17 +109,22 @@ static double entry(Int i, Int j, Int w) { return 1.0 + double(i) * w + j; }
 template <Dist U, Dist V, Dist U2, Dist V2>
 static void redist_case(const Grid& g, DistOut& out) {
     const Int h = 13, w = 11;
+    constexpr bool circ = U == CIRC || U2 == CIRC;  // Gather / Scatter cases: "Q" records with the two roots
     DistMatrix<double, U, V> A(g);
+    if (U == CIRC) A.SetRoot(2 % g.Size());
     A.Align(1 % A.ColStride(), 2 % A.RowStride());
     A.Resize(h, w);
     for (Int j = 0; j < A.LocalWidth(); ++j)
         for (Int i = 0; i < A.LocalHeight(); ++i) A.SetLocal(i, j, entry(A.GlobalRow(i), A.GlobalCol(j), w));
     DistMatrix<double, U2, V2> B(g);
+    if (U2 == CIRC) B.SetRoot(1 % g.Size());
     B.Align(3 % B.ColStride(), 1 % B.RowStride());
     B = A;
-    out.txt << "R " << int(U) << " " << int(V) << " " << int(U2) << " " << int(V2) << " " << A.ColAlign() << " "
+    out.txt << (circ ? "Q " : "R ") << int(U) << " " << int(V) << " " << int(U2) << " " << int(V2) << " " << A.ColAlign() << " "
             << A.RowAlign() << " " << B.ColAlign() << " " << B.RowAlign() << " " << B.ColShift() << " " << B.RowShift()
-            << " " << B.LocalHeight() << " " << B.LocalWidth() << " " << out.offset << "\n";
+            << " " << B.LocalHeight() << " " << B.LocalWidth() << " " << out.offset;
+    if (circ) out.txt << " " << A.Root() << " " << B.Root();
+    out.txt << "\n";
     out.blob(B.LockedMatrix());
 }
 template <Dist U, Dist V>
@@ -154,6 +159,16 @@ static void dist_golden(const std::string& dir, int gridHeight) {
     redist_from<VC, STAR>(g, out); redist_from<STAR, VC>(g, out);
     redist_from<VR, STAR>(g, out); redist_from<STAR, VR>(g, out);
     redist_from<STAR, STAR>(g, out);
+    // [CIRC,CIRC] (copy::Gather / copy::Scatter): every distribution to the root, the root to every
+    // distribution, and root to root
+    redist_case<MC, MR, CIRC, CIRC>(g, out);   redist_case<MR, MC, CIRC, CIRC>(g, out);
+    redist_case<MC, STAR, CIRC, CIRC>(g, out); redist_case<STAR, MC, CIRC, CIRC>(g, out);
+    redist_case<MR, STAR, CIRC, CIRC>(g, out); redist_case<STAR, MR, CIRC, CIRC>(g, out);
+    redist_case<VC, STAR, CIRC, CIRC>(g, out); redist_case<STAR, VC, CIRC, CIRC>(g, out);
+    redist_case<VR, STAR, CIRC, CIRC>(g, out); redist_case<STAR, VR, CIRC, CIRC>(g, out);
+    redist_case<STAR, STAR, CIRC, CIRC>(g, out);
+    redist_from<CIRC, CIRC>(g, out);
+    redist_case<CIRC, CIRC, CIRC, CIRC>(g, out);
 
     const Int m = 37, n = 29, k = 53, nb = 16;
     const Orientation os[2] = {NORMAL, TRANSPOSE};

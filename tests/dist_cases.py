@@ -54,6 +54,74 @@ def check_redistributions(grid, dtype=torch.float64, m=23, n=17, pairs=None, see
     return count
 
 
+def check_circ(grid, dtype=torch.float64, m=23, n=17) -> int:
+    """[CIRC,CIRC] (copy::Gather / copy::Scatter, Copy/Gather.hpp, Copy/Scatter.hpp): gather every
+    distribution to a root, scatter it back with other alignments, move the root, transpose through
+    it, and round-trip the local matrix through host memory — all bit-exact."""
+    og = _grid_oracle(grid)
+    p, me = og.p, grid.Rank()
+    rng = np.random.default_rng(7)
+    npdt = NPDT[dtype]
+    G = np.asfortranarray(rng.uniform(-1, 1, (m, n)).astype(npdt))
+    count = 0
+    for (U, V) in OD.PAIRS:
+        ca, ra = int(rng.integers(og.stride(U))), int(rng.integers(og.stride(V)))
+        root = int(rng.integers(p))
+        A = el.DistMatrix(grid, U, V, dtype).Align(ca, ra).from_global(G)
+        R = el.DistMatrix(grid, el.CIRC, el.CIRC, dtype).SetRoot(root)
+        el.Copy(A, R)
+        assert R.Root() == root and (R.LocalHeight(), R.LocalWidth()) == ((m, n) if me == root else (0, 0))
+        if me == root:
+            assert np.array_equal(R.get_local(), G), f"gather [{OD.NAMES[U]},{OD.NAMES[V]}] -> root {root}"
+        ca2, ra2 = int(rng.integers(og.stride(U))), int(rng.integers(og.stride(V)))
+        B = el.DistMatrix(grid, U, V, dtype).Align(ca2, ra2)
+        el.Copy(R, B)
+        exp = OD.local_of(G, OD.Spec(U, V, ca2, ra2, m, n), og, me)
+        assert np.array_equal(B.get_local(), exp), f"scatter root {root} -> [{OD.NAMES[U]},{OD.NAMES[V]}]"
+        count += 2
+    # root -> another root, and a view of the rooted matrix scattered out
+    R = el.DistMatrix(grid, el.CIRC, el.CIRC, dtype).SetRoot(0).from_global(G)
+    R2 = el.DistMatrix(grid, el.CIRC, el.CIRC, dtype).SetRoot(p - 1)
+    el.Copy(R, R2)
+    if me == p - 1:
+        assert np.array_equal(R2.get_local(), G)
+    else:
+        assert R2.LocalHeight() == 0
+    V_ = R2.View(2, m - 3, 1, n - 2)
+    B = el.DistMatrix(grid, el.MC, el.MR, dtype)
+    el.Copy(V_, B)
+    sub = np.asfortranarray(G[2:m - 3, 1:n - 2])
+    assert np.array_equal(B.get_local(), OD.local_of(sub, OD.Spec(OD.MC, OD.MR, B.ColAlign(), B.RowAlign(), *sub.shape), og, me))
+    T = el.DistMatrix(grid, el.VR, el.STAR, dtype)
+    el.Transpose(R2, T)
+    assert np.array_equal(T.get_local(), OD.local_of(np.asfortranarray(G.T), OD.Spec(OD.VR, OD.STAR, T.ColAlign(), T.RowAlign(), n, m), og, me))
+    # CPU <-> GPU copy of the local matrix (ProxyDevice.hpp): pinned host tensors, ld > local height
+    A = el.DistMatrix(grid, el.MC, el.MR, dtype).Align(1 % og.r, 0).from_global(G)
+    lh, lw = A.LocalHeight(), A.LocalWidth()
+    host = torch.full((max(lw, 1), lh + 3), -7.0, dtype=dtype).pin_memory()
+    A.read_local_to_host(host)
+    grid.sync()
+    loc = OD.local_of(G, OD.Spec(OD.MC, OD.MR, 1 % og.r, 0, m, n), og, me)
+    if lh and lw:
+        assert np.array_equal(host[:lw, :lh].numpy().T, loc) and bool((host[:, lh:] == -7.0).all())
+    host[:lw, :lh] *= 2
+    A.write_local_from_host(host)
+    grid.sync()
+    assert np.array_equal(A.get_local(), 2 * loc)
+    # Gemm with rooted operands goes through the [MC,MR] proxies (Proxy.hpp:236-257)
+    k = 11
+    Ga = np.asfortranarray(rng.uniform(-1, 1, (m, k)).astype(npdt))
+    Gb = np.asfortranarray(rng.uniform(-1, 1, (k, n)).astype(npdt))
+    Ar = el.DistMatrix(grid, el.CIRC, el.CIRC, dtype).SetRoot(p - 1).from_global(Ga)
+    Bm = el.DistMatrix(grid, el.MC, el.MR, dtype).from_global(Gb)
+    Cr = el.DistMatrix(grid, el.CIRC, el.CIRC, dtype).SetRoot(0).from_global(G)
+    el.Gemm(el.NORMAL, el.NORMAL, 2.0, Ar, Bm, 3.0, Cr, el.GEMM_SUMMA_C)
+    if me == 0:
+        ref = OG.gemm_global(0, 0, 2.0, Ga, Gb, 3.0, G, np.longdouble)
+        assert OG.frobenius_rel_err(Cr.get_local(), ref) <= OG.gemm_tolerance(npdt, k)
+    return count + 5
+
+
 def check_views_and_transpose(grid, dtype=torch.float32) -> None:
     og = _grid_oracle(grid)
     npdt = NPDT[dtype]
@@ -219,6 +287,7 @@ def run_all(grid, heavy=False) -> dict:
     out["redist_f64"] = check_redistributions(grid, torch.float64)
     out["redist_f32"] = check_redistributions(grid, torch.float32, m=64, n=48, seed=4,
                                               pairs=[((OD.MC, OD.MR), t) for t in OD.PAIRS] + [(t, (OD.MC, OD.MR)) for t in OD.PAIRS])
+    out["circ"] = check_circ(grid, torch.float64) + check_circ(grid, torch.float32)
     check_views_and_transpose(grid, torch.float32)
     check_views_and_transpose(grid, torch.float64)
     check_contractions(grid, torch.float64)

@@ -45,7 +45,7 @@ class Comms:
 
 
 def local_spec(spec: OD.Spec) -> L.DistSpec:
-    return PS.spec_c(spec.U, spec.V, spec.col_align, spec.row_align, spec.height, spec.width)
+    return PS.spec_c(spec.U, spec.V, spec.col_align, spec.row_align, spec.height, spec.width, spec.root)
 
 
 def copy(cm: Comms, a_loc: np.ndarray, sa: OD.Spec, sb: OD.Spec) -> np.ndarray:
@@ -132,6 +132,20 @@ def main() -> int:
         got = copy(cm, OD.local_of(G, sa, g, rank), sa, sb)
         assert np.array_equal(got, OD.local_of(G, sb, g, rank)), (U, V, U2, V2)
         checks += 1
+
+    # 1b. [CIRC,CIRC]: gather to a root, scatter from it, move the root (Copy/Gather.hpp, Scatter.hpp)
+    for (U, V) in pairs:
+        sa = OD.Spec(U, V, 1 % g.stride(U), 2 % g.stride(V), 13, 11)
+        sr = OD.Spec(L.CIRC, L.CIRC, 0, 0, 13, 11, (world - 1))
+        sr2 = OD.Spec(L.CIRC, L.CIRC, 0, 0, 13, 11, 0)
+        rooted = copy(cm, OD.local_of(G, sa, g, rank), sa, sr)
+        assert rooted.shape == ((13, 11) if rank == world - 1 else (0, 0))
+        assert np.array_equal(rooted, OD.local_of(G, sr, g, rank))
+        moved = copy(cm, rooted, sr, sr2)
+        assert np.array_equal(moved, OD.local_of(G, sr2, g, rank))
+        sb = OD.Spec(U, V, 3 % g.stride(U), 1 % g.stride(V), 13, 11)
+        assert np.array_equal(copy(cm, moved, sr2, sb), OD.local_of(G, sb, g, rank)), (U, V)
+        checks += 3
 
     # 2. SUMMA-C (NN.hpp:330-387): AllGather panels, local product
     rng = np.random.default_rng(11)  # same stream on every rank

@@ -17,8 +17,8 @@ from oracle import dist as OD
 EX_LOCAL, EX_ALLGATHER, EX_SENDRECV = 0, 1, 2
 
 
-def spec_c(U, V, ca, ra, h, w) -> L.DistSpec:
-    return L.DistSpec(U, V, ca, ra, h, w)
+def spec_c(U, V, ca, ra, h, w, root=0) -> L.DistSpec:
+    return L.DistSpec(U, V, ca, ra, h, w, root)
 
 
 def seg_tuple(s: L.Segment):
@@ -53,12 +53,12 @@ def comm_members(g: OD.Grid, comm_dist: int, vc: int) -> List[int]:
     return list(range(g.p))
 
 
-def run_copy(g: OD.Grid, A: OD.VDM, U2, V2, ca2, ra2) -> OD.VDM:
+def run_copy(g: OD.Grid, A: OD.VDM, U2, V2, ca2, ra2, root2=0) -> OD.VDM:
     """B[U2,V2] = A executed from the plans of all g.p ranks."""
     h, w = A.spec.height, A.spec.width
-    sa = spec_c(A.spec.U, A.spec.V, A.spec.col_align, A.spec.row_align, h, w)
-    sb = spec_c(U2, V2, ca2, ra2, h, w)
-    B = OD.VDM.zeros(g, U2, V2, ca2, ra2, h, w, A.loc[0].dtype)
+    sa = spec_c(A.spec.U, A.spec.V, A.spec.col_align, A.spec.row_align, h, w, A.spec.root)
+    sb = spec_c(U2, V2, ca2, ra2, h, w, root2)
+    B = OD.VDM.zeros(g, U2, V2, ca2, ra2, h, w, A.loc[0].dtype, root2)
     for q in range(g.p):
         B.loc[q][...] = np.nan
     plans = [copy_plan(g.r, g.c, q, sa, sb) for q in range(g.p)]

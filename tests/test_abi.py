@@ -61,7 +61,7 @@ def test_ctypes_table_matches_header():
 def test_struct_layouts_match_header_sizes():
     """Plain-C structs crossing the boundary: sizes implied by the header's field lists."""
     assert C.sizeof(L.Segment) == 7 * 8
-    assert C.sizeof(L.DistSpec) == 2 * 4 + 4 * 8
+    assert C.sizeof(L.DistSpec) == 2 * 4 + 4 * 8 + 8  # + int root, padded to the 8-byte alignment
     assert C.sizeof(L.Message) == 8 + C.sizeof(L.Segment)
     assert L.MAX_SEGMENTS == int(re.search(r"#define ELB200_MAX_SEGMENTS (\d+)", open(HEADER).read()).group(1))
 

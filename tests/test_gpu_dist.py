@@ -23,6 +23,12 @@ def test_redistributions_1x1(grid1):
     dc.check_views_and_transpose(grid1, torch.float64)
 
 
+def test_circ_gather_scatter_1x1(grid1):
+    from tests import dist_cases as dc
+    assert dc.check_circ(grid1, torch.float64) == 27
+    assert dc.check_circ(grid1, torch.float32) == 27
+
+
 def test_contractions_1x1(grid1):
     from tests import dist_cases as dc
     dc.check_contractions(grid1, torch.float64)

@@ -204,6 +204,31 @@ def test_redistribution_placement_matches_reference(gold_dist, tag):
 
 
 @pytest.mark.parametrize("tag", DIST_TAGS)
+def test_circ_gather_scatter_matches_reference(gold_dist, tag):
+    """[CIRC,CIRC] (copy::Gather / copy::Scatter): every distribution gathered to a root, the root
+    scattered to every distribution, and root-to-root — 23 cases per grid with roots 2 mod p
+    (source) and 1 mod p (target); per-rank local matrices equal the reference's bit for bit,
+    and non-root ranks hold 0 x 0."""
+    g, ranks = _ranks(gold_dist, tag)
+    G = np.arange(13 * 11, dtype=np.float64).reshape(13, 11) + 1.0
+    el = dict(EL_DIST); el[6] = OD.CIRC
+    checked = 0
+    for q in ranks:
+        vc = int(gold_dist[f"{tag}_q{q}_I"][5])
+        blob = gold_dist[f"{tag}_q{q}_bin"]
+        for (U, V, U2, V2, caA, raA, caB, raB, csB, rsB, lh, lw, off, rootA, rootB) in gold_dist[f"{tag}_q{q}_Q"]:
+            A = OD.VDM.from_global(g, G, el[int(U)], el[int(V)], int(caA), int(raA), int(rootA))
+            B = OD.redistribute(A, el[int(U2)], el[int(V2)], int(caB), int(raB), int(rootB))
+            assert B.loc[vc].shape == (lh, lw), (tag, q, U, U2)
+            if int(U2) == 6:
+                assert (lh, lw) == ((13, 11) if vc == int(rootB) else (0, 0))
+            ref = blob[off:off + lh * lw].reshape((lh, lw), order="F")
+            assert np.array_equal(B.loc[vc], ref), (tag, q, U, V, U2, V2)
+            checked += 1
+    assert checked == 23 * g.p
+
+
+@pytest.mark.parametrize("tag", DIST_TAGS)
 def test_distributed_gemm_matches_reference_per_rank(gold_dist, tag):
     """20 El::Gemm runs of the reference per grid (NN/NT/TN/TT x {DEFAULT, SUMMA_A, B, C, DOT},
     aligned A, B, C, nb = 16): the oracle's SUMMA restatement gives the same local C on each rank

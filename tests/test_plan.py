@@ -182,6 +182,21 @@ def test_planner_reproduces_reference_placement(tag):
             ref = blob[off:off + lh * lw].reshape((lh, lw), order="F")
             assert np.array_equal(done[key].loc[vc], ref), (tag, q, key)
     assert len(done) == 121
+    # [CIRC,CIRC]: gather to / scatter from a root, root to root (23 cases per grid)
+    el = dict(EL_DIST); el[6] = L.CIRC
+    done = {}
+    for q in range(g.p):
+        vc = int(gold[f"{tag}_q{q}_I"][5])
+        blob = gold[f"{tag}_q{q}_bin"]
+        for (U, V, U2, V2, caA, raA, caB, raB, _cs, _rs, lh, lw, off, rootA, rootB) in (tuple(int(x) for x in r) for r in gold[f"{tag}_q{q}_Q"]):
+            key = (U, V, U2, V2)
+            if key not in done:
+                A = OD.VDM.from_global(g, G, el[U], el[V], caA, raA, rootA)
+                done[key] = PS.run_copy(g, A, el[U2], el[V2], caB, raB, rootB)
+            ref = blob[off:off + lh * lw].reshape((lh, lw), order="F")
+            assert done[key].loc[vc].shape == (lh, lw), (tag, q, key)
+            assert np.array_equal(done[key].loc[vc], ref), (tag, q, key)
+    assert len(done) == 23
 
 
 @pytest.mark.parametrize("shape", [(1, 2), (2, 1), (2, 2), (2, 4), (4, 2), (2, 3), (3, 2), (3, 3), (4, 6)])
