@@ -102,6 +102,7 @@ SIGNATURES = {
     "elb200_peer_reduce_axpy_f64": (ci, [ci, C.POINTER(vp), i64, C.POINTER(Segment), vp, i64, f64, vp]),
     "elb200_plan_copy": (ci, [ci, ci, ci, C.POINTER(DistSpec), C.POINTER(DistSpec), C.POINTER(CopyPlan)]),
     "elb200_plan_contract": (ci, [ci, ci, ci, C.POINTER(DistSpec), C.POINTER(DistSpec), C.POINTER(ContractPlan)]),
+    "elb200_plan_send_offset": (i64, [ci, ci, ci, C.POINTER(DistSpec), C.POINTER(DistSpec), ci]),
     "elb200_plan_direct_panel": (ci, [ci, ci, ci, i64, i64, i64, C.POINTER(i64), C.POINTER(i64), C.POINTER(ci),
                                       C.POINTER(i64), C.POINTER(i64)]),
     "elb200_shift": (i64, [i64, i64, i64]),

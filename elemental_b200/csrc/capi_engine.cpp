@@ -118,6 +118,13 @@ int elb200_plan_contract(int r, int c, int vc, const elb200_dist_spec* A, const 
     return ELB200_OK;
 }
 
+int64_t elb200_plan_send_offset(int r, int c, int sender, const elb200_dist_spec* A, const elb200_dist_spec* B, int dest) {
+    if (!A || !B || r < 1 || c < 1 || sender < 0 || sender >= r * c || dest < 0 || dest >= r * c) return -1;
+    GridShape g; g.r = r; g.c = c;
+    if (!spec_ok(g, *A) || !spec_ok(g, *B)) return -1;
+    return plan_send_offset(g, coord_of_vc(g, sender), to_spec(*A), to_spec(*B), dest);
+}
+
 int elb200_plan_direct_panel(int r, int c, int vc, int64_t kb, int64_t a_row_align, int64_t b_col_align,
                              int64_t* row_off, int64_t* a_cols, int* nclasses, int64_t* b_row0, int64_t* b_rows) {
     if (r < 1 || c < 1 || vc < 0 || vc >= r * c || kb < 0 || !row_off || !a_cols || !nclasses || !b_row0 || !b_rows)

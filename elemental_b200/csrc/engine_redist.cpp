@@ -101,8 +101,34 @@ void Copy(const DistMat<T>& A, DistMat<T>& B) {
         run_lattice<T>(ELB200_UNPACK, plan.recvs, B.buf, B.ldim, recv, T(0), s);
         return;
     }
-    // general exchange: pack -> grouped send/recv over the world communicator -> unpack
+    // general exchange: pack -> point-to-point -> unpack
     if (!g.world) throw EngineError(ELB200_ERR_STATE, "Copy: grid has no NCCL communicator");
+    // NVLink pull (peer.hpp): every rank packs ITS sends straight into its own arena slot, signals,
+    // and the receivers fetch their messages from the senders' slots with the copy engines — no
+    // NCCL kernels, no SMs during the transfer. Taken when the largest possible send staging
+    // (a whole local matrix of A) fits a slot, a bound every rank evaluates identically.
+    static const bool pull = [] { const char* e = std::getenv("ELB200_A2A_PULL"); return !e || std::atoi(e) != 0; }();
+    const size_t max_local_a = size_t(MaxLength(A.spec.height, dist_stride(g.shape, A.spec.col))) *
+                               size_t(MaxLength(A.spec.width, dist_stride(g.shape, A.spec.row))) * sizeof(T);
+    if (pull && g.arena && max_local_a <= g.arena->slot_bytes()) {
+        const std::vector<int> members = g.comm_members(VC);
+        const int idx = g.vc_rank;
+        PeerArena::Ticket t = g.arena->Publish(Grid::arena_channel(VC), members, idx, size_t(plan.send_elems) * sizeof(T), s);
+        run_lattice<T>(ELB200_PACK, plan.sends, Abuf, A.ldim, static_cast<T*>(t.data), T(0), s);
+        g.arena->Signal(t, members, idx, s);
+        Scratch<T> rbuf(plan.recv_elems, s);
+        for (const Message& m : plan.recvs) {
+            // where the sender packed the message for me inside its slot
+            const int64_t off = plan_send_offset(g.shape, coord_of_vc(g.shape, m.peer), A.spec, B.spec, g.vc_rank);
+            cuda_check(cudaMemcpyAsync(rbuf.p + m.seg.buf_offset, static_cast<const T*>(g.arena->PeerSlot(m.peer, t)) + off,
+                                       size_t(m.count()) * sizeof(T), cudaMemcpyDeviceToDevice, s), "peer pull");
+        }
+        g.arena->Release(t, members, idx, s);  // stream order: the acks leave after my pulls completed
+        run_lattice<T>(ELB200_UNPACK, plan.recvs, B.buf, B.ldim, rbuf.p, T(0), s);
+        if (plan.has_self)
+            lattice_to_lattice<T>(plan.self_send.seg, A.buf, A.ldim, plan.self_recv.seg, B.buf, B.ldim, s);
+        return;
+    }
     Scratch<T> sbuf(plan.send_elems, s), rbuf(plan.recv_elems, s);
     run_lattice<T>(ELB200_PACK, plan.sends, Abuf, A.ldim, sbuf.p, T(0), s);
     nccl_check(ncclGroupStart(), "ncclGroupStart");

@@ -125,6 +125,21 @@ Dist comm_for_mask(int mask) { return mask == 1 ? MC : mask == 2 ? MR : mask == 
 
 }  // namespace
 
+int64_t plan_send_offset(const GridShape& g, GridCoord sender, const DistSpec& A, const DistSpec& B, int dest_vc) {
+    // mirrors the send loop of plan_copy: messages are laid out in increasing VC rank of the receiver
+    const int free_a = 3 & ~(constrains(A.col) | constrains(A.row));
+    const int sender_vc = vc_of(g, sender);
+    int64_t off = 0;
+    for (int v = 0; v < dest_vc; ++v) {
+        if (v == sender_vc) continue;
+        const GridCoord q = coord_of_vc(g, v);
+        if (((free_a & 1) && sender.mc != q.mc) || ((free_a & 2) && sender.mr != q.mr)) continue;
+        const elb200_segment sg = pair_lattice(g, A, sender, B, q, true);
+        off += sg.rows * sg.cols;
+    }
+    return off;
+}
+
 CopyPlan plan_copy(const GridShape& g, GridCoord me, const DistSpec& A, const DistSpec& B) {
     CopyPlan plan;
     const int p = g.size();

@@ -89,6 +89,11 @@ struct CopyPlan {
 // src/core/DistMatrix/ElementMatrix/*.cpp operator= tables).
 CopyPlan plan_copy(const GridShape& g, GridCoord me, const DistSpec& A, const DistSpec& B);
 
+// Offset (elements) inside rank `sender`'s packed send staging of its message to VC rank
+// `dest_vc`, for the EX_SENDRECV plan of B = A: what a receiver needs to fetch its message from the
+// sender's staging without asking (peer-memory pull, engine_redist.cpp).
+int64_t plan_send_offset(const GridShape& g, GridCoord sender, const DistSpec& A, const DistSpec& B, int dest_vc);
+
 // Plan of B += alpha * (sum over the replicas of A) for the partial-sum distributions of the
 // reference's axpy_contract::{RowScatter,ColScatter,Scatter}
 // (include/El/blas_like/level1/AxpyContract.hpp:146-479). A's col/row dist must each equal B's or

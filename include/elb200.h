@@ -220,6 +220,12 @@ int elb200_plan_copy(int grid_height, int grid_width, int vc_rank, const elb200_
                      const elb200_dist_spec* B, elb200_copy_plan* out);
 int elb200_plan_contract(int grid_height, int grid_width, int vc_rank, const elb200_dist_spec* A,
                          const elb200_dist_spec* B, elb200_contract_plan* out);
+/* Offset (elements) of the message rank `sender_vc` addresses to rank `dest_vc` inside the sender's
+ * packed send staging of the general exchange of B = A (== sends[i].seg.buf_offset of the sender's
+ * plan); lets a receiver pull its message out of the sender's peer-mapped staging. -1 on bad
+ * arguments. Host-only. */
+int64_t elb200_plan_send_offset(int grid_height, int grid_width, int sender_vc, const elb200_dist_spec* A,
+                                const elb200_dist_spec* B, int dest_vc);
 /* Layout of a zero-copy SUMMA-C panel (NN) for an r x c grid, seen from VC rank `vc_rank`: the k
  * indices of a kb-wide panel are permuted so that every owner's block is strided (see DESIGN.md
  * 3.5). row_off[r+1]: member q's B rows occupy panel rows [row_off[q], row_off[q+1]);

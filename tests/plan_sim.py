@@ -92,6 +92,9 @@ def run_copy(g: OD.Grid, A: OD.VDM, U2, V2, ca2, ra2, root2=0) -> OD.VDM:
     # grouped point-to-point: match every send with the receive posted for it
     sent = {}
     for q, p in enumerate(plans):
+        # a receiver can locate its message inside the sender's staging on its own (peer-memory pull)
+        for i in range(p.nsend):
+            assert L.lib.elb200_plan_send_offset(g.r, g.c, q, C.byref(sa), C.byref(sb), p.sends[i].peer) == p.sends[i].seg.buf_offset
         segs = [seg_tuple(p.sends[i].seg) for i in range(p.nsend)]
         buf = OD.apply_segments_pack(A.loc[q], segs, p.send_elems)
         for i in range(p.nsend):
