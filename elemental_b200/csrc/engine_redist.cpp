@@ -117,12 +117,13 @@ void Copy(const DistMat<T>& A, DistMat<T>& B) {
         run_lattice<T>(ELB200_PACK, plan.sends, Abuf, A.ldim, static_cast<T*>(t.data), T(0), s);
         g.arena->Signal(t, members, idx, s);
         Scratch<T> rbuf(plan.recv_elems, s);
+        std::vector<PeerArena::PullOp> pulls;
         for (const Message& m : plan.recvs) {
             // where the sender packed the message for me inside its slot
             const int64_t off = plan_send_offset(g.shape, coord_of_vc(g.shape, m.peer), A.spec, B.spec, g.vc_rank);
-            cuda_check(cudaMemcpyAsync(rbuf.p + m.seg.buf_offset, static_cast<const T*>(g.arena->PeerSlot(m.peer, t)) + off,
-                                       size_t(m.count()) * sizeof(T), cudaMemcpyDeviceToDevice, s), "peer pull");
+            pulls.push_back({m.peer, size_t(off) * sizeof(T), rbuf.p + m.seg.buf_offset, size_t(m.count()) * sizeof(T)});
         }
+        g.arena->Pull(t, pulls, s);
         g.arena->Release(t, members, idx, s);  // stream order: the acks leave after my pulls completed
         run_lattice<T>(ELB200_UNPACK, plan.recvs, B.buf, B.ldim, rbuf.p, T(0), s);
         if (plan.has_self)

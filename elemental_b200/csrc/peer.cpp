@@ -128,7 +128,53 @@ PeerArena* PeerArena::Create(ncclComm_t world, int rank, int size, cudaStream_t 
         delete pa;
         return nullptr;
     }
+    // auxiliary lanes for concurrent peer transfers (ELB200_FANOUT=0 keeps everything on one stream)
+    const char* fo = std::getenv("ELB200_FANOUT");
+    pa->lanes_ = (fo && std::atoi(fo) == 0) || size < 3 ? 0 : kLanes;
+    for (int i = 0; i < pa->lanes_; ++i) {
+        cuda_check(cudaStreamCreateWithFlags(&pa->lane_[i], cudaStreamNonBlocking), "PeerArena lane");
+        cuda_check(cudaEventCreateWithFlags(&pa->lane_done_[i], cudaEventDisableTiming), "PeerArena lane event");
+    }
+    if (pa->lanes_) cuda_check(cudaEventCreateWithFlags(&pa->fork_ev_, cudaEventDisableTiming), "PeerArena fork event");
     return pa;
+}
+
+cudaStream_t PeerArena::fork(int item, cudaStream_t s) {
+    if (!lanes_) return s;
+    if (!forked_) {
+        cuda_check(cudaEventRecord(fork_ev_, s), "PeerArena fork");
+        forked_ = true;
+    }
+    const int l = item % lanes_;
+    if (!lane_used_[l]) {
+        cuda_check(cudaStreamWaitEvent(lane_[l], fork_ev_, 0), "PeerArena fork wait");
+        lane_used_[l] = true;
+    }
+    return lane_[l];
+}
+
+void PeerArena::join(cudaStream_t s) {
+    for (int l = 0; l < lanes_; ++l) {
+        if (!lane_used_[l]) continue;
+        cuda_check(cudaEventRecord(lane_done_[l], lane_[l]), "PeerArena join");
+        cuda_check(cudaStreamWaitEvent(s, lane_done_[l], 0), "PeerArena join wait");
+        lane_used_[l] = false;
+    }
+    forked_ = false;
+}
+
+void PeerArena::Pull(const Ticket& t, const std::vector<PullOp>& ops, cudaStream_t s) {
+    for (const PullOp& op : ops)
+        if (op.bytes && op.src_offset + op.bytes > slot_bytes_)
+            throw EngineError(ELB200_ERR_ARG, "PeerArena::Pull: read leaves the slot");
+    int item = 0;
+    for (const PullOp& op : ops) {
+        if (!op.bytes) continue;
+        cudaStream_t ls = fork(item++, s);  // one lane per source: the peers are read concurrently
+        cuda_check(cudaMemcpyAsync(op.dst, slot_base(op.rank, t.channel, t.slot) + op.src_offset, op.bytes,
+                                   cudaMemcpyDeviceToDevice, ls), "PeerArena pull");
+    }
+    join(s);
 }
 
 void PeerArena::Detach() {
@@ -144,6 +190,11 @@ void PeerArena::Detach() {
 
 PeerArena::~PeerArena() {
     Detach();
+    for (int i = 0; i < kLanes; ++i) {
+        if (lane_[i]) cudaStreamDestroy(lane_[i]);
+        if (lane_done_[i]) cudaEventDestroy(lane_done_[i]);
+    }
+    if (fork_ev_) cudaEventDestroy(fork_ev_);
     if (!arena_.empty() && arena_[rank_]) cudaFree(arena_[rank_]);
     if (!flags_.empty() && flags_[rank_]) cudaFree(flags_[rank_]);
     if (consts_) cudaFree(consts_);
@@ -177,14 +228,17 @@ PeerArena::Ticket PeerArena::AllGather(int channel, const std::vector<int>& memb
     // 1. my previous block in each member's slot must have been consumed
     for (int i = 0; i < g; ++i)
         if (i != my_index) wait_flag(flag(rank_, ACK, channel, t.slot, members[i]), t.seq - 1, s);
-    // 2. my block into every member's slot (mine included)
-    if (send_bytes)
-        for (int i = 0; i < g; ++i)
+    // 2. my block into every member's slot (mine included), 3. tell them: payload and flag for one
+    // member stay on one lane (ordered), different members go out concurrently
+    for (int i = 0; i < g; ++i) {
+        cudaStream_t ls = fork(i, s);
+        if (send_bytes)
             cuda_check(cudaMemcpyAsync(slot_base(members[i], channel, t.slot) + size_t(my_index) * portion_bytes, send,
-                                       send_bytes, cudaMemcpyDeviceToDevice, s), "PeerArena copy");
-    // 3. tell them, 4. wait for theirs
-    for (int i = 0; i < g; ++i)
-        if (i != my_index) write_flag(flag(members[i], ARRIVE, channel, t.slot, rank_), t.seq, s);
+                                       send_bytes, cudaMemcpyDeviceToDevice, ls), "PeerArena copy");
+        if (i != my_index) write_flag(flag(members[i], ARRIVE, channel, t.slot, rank_), t.seq, ls);
+    }
+    join(s);
+    // 4. wait for theirs
     for (int i = 0; i < g; ++i)
         if (i != my_index) wait_flag(flag(rank_, ARRIVE, channel, t.slot, members[i]), t.seq, s);
     t.data = slot_base(rank_, channel, t.slot);
@@ -201,16 +255,19 @@ PeerArena::Ticket PeerArena::GatherDirect(int channel, const std::vector<int>& m
     t.seq = uint32_t(n / 2 + 1);
     for (int i = 0; i < g; ++i)
         if (i != my_index) wait_flag(flag(rank_, ACK, channel, t.slot, members[i]), t.seq - 1, s);
-    for (int i = 0; i < g; ++i)
+    for (const Copy2D& c : copies)
+        if (c.width && c.height && c.dst_offset + (c.height - 1) * c.dpitch + c.width > slot_bytes_)
+            throw EngineError(ELB200_ERR_ARG, "PeerArena::GatherDirect: transfer leaves the slot");
+    for (int i = 0; i < g; ++i) {
+        cudaStream_t ls = fork(i, s);  // one lane per destination; its arrival flag follows its payload
         for (const Copy2D& c : copies) {
             if (c.width == 0 || c.height == 0) continue;
-            if (c.dst_offset + (c.height - 1) * c.dpitch + c.width > slot_bytes_)
-                throw EngineError(ELB200_ERR_ARG, "PeerArena::GatherDirect: transfer leaves the slot");
             cuda_check(cudaMemcpy2DAsync(slot_base(members[i], channel, t.slot) + c.dst_offset, c.dpitch, c.src, c.spitch,
-                                         c.width, c.height, cudaMemcpyDeviceToDevice, s), "PeerArena direct copy");
+                                         c.width, c.height, cudaMemcpyDeviceToDevice, ls), "PeerArena direct copy");
         }
-    for (int i = 0; i < g; ++i)
-        if (i != my_index) write_flag(flag(members[i], ARRIVE, channel, t.slot, rank_), t.seq, s);
+        if (i != my_index) write_flag(flag(members[i], ARRIVE, channel, t.slot, rank_), t.seq, ls);
+    }
+    join(s);
     for (int i = 0; i < g; ++i)
         if (i != my_index) wait_flag(flag(rank_, ARRIVE, channel, t.slot, members[i]), t.seq, s);
     t.data = slot_base(rank_, channel, t.slot);

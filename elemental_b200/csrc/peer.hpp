@@ -66,6 +66,16 @@ public:
     Ticket Publish(int channel, const std::vector<int>& members, int my_index, size_t bytes, cudaStream_t s);
     void Signal(const Ticket& t, const std::vector<int>& members, int my_index, cudaStream_t s);
     const void* PeerSlot(int rank, const Ticket& t) const { return slot_base(rank, t.channel, t.slot); }
+    // Fetch pieces of the members' published slots into local memory with the copy engines, the
+    // transfers from different peers running concurrently (general exchange of Copy). Call between
+    // Signal and Release.
+    struct PullOp {
+        int rank;           // VC rank whose slot is read
+        size_t src_offset;  // bytes from its slot base
+        void* dst;          // local device memory
+        size_t bytes;
+    };
+    void Pull(const Ticket& t, const std::vector<PullOp>& ops, cudaStream_t s);
 
 private:
     PeerArena() = default;
@@ -73,6 +83,11 @@ private:
     char* slot_base(int rank, int channel, int slot) const;
     void write_flag(uint32_t* dst, uint32_t seq, cudaStream_t s);
     void wait_flag(uint32_t* local, uint32_t seq, cudaStream_t s);
+    // Transfers to / from different peers are independent: they are spread over `lanes_` auxiliary
+    // streams forked from the caller's stream and joined back into it, so several copy engines
+    // and NVLink paths work at once instead of one peer after the other.
+    cudaStream_t fork(int item, cudaStream_t s);  // stream for item i of the current fan-out
+    void join(cudaStream_t s);                    // caller's stream waits for every lane used
 
     int rank_ = 0, size_ = 1;
     size_t slot_bytes_ = 0;
@@ -80,6 +95,13 @@ private:
     std::vector<uint32_t*> flags_;   // per rank: base of its flag block
     uint32_t* consts_ = nullptr;     // consts_[i] == i, source of the 4-byte flag writes
     uint64_t uses_[kChannels] = {0, 0, 0};
+    enum { kLanes = 4 };
+    int lanes_ = 0;  // 0: no fan-out, everything on the caller's stream
+    cudaStream_t lane_[kLanes] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t lane_done_[kLanes] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t fork_ev_ = nullptr;
+    bool lane_used_[kLanes] = {false, false, false, false};
+    bool forked_ = false;
 };
 
 }  // namespace elb
