@@ -12,7 +12,7 @@ HDRS      := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh $(CSRC)/*.hpp include/*.h)
 NCCL_INC  ?= /usr/include
 NCCL_LIB  ?= $(shell python -c "import nvidia.nccl, os; print(os.path.join(list(nvidia.nccl.__path__)[0], 'lib'))" 2>/dev/null)
 
-all: $(LIBDIR)/libelb200.so tools/gemm_check tools/el_gemm_driver
+all: $(LIBDIR)/libelb200.so tools/gemm_check tools/el_gemm_driver tools/el_api_check
 
 build/%.o: $(CSRC)/%.cu $(HDRS)
 	@mkdir -p build
@@ -33,7 +33,11 @@ tools/gemm_check: tools/gemm_check.cu $(LIBDIR)/libelb200.so include/elb200.h
 tools/el_gemm_driver: tools/el_gemm_driver.cpp include/El.hpp include/elb200.h $(LIBDIR)/libelb200.so
 	$(NVCC) -std=c++17 -O2 -Xcompiler -Wall -Iinclude -o $@ $< -L$(LIBDIR) -lelb200 -lcudart -Xlinker -rpath,'$$ORIGIN/../$(LIBDIR)'
 
+# every name of the facade, written the way a Hydrogen caller writes it (compile + link = the CPU-side check)
+tools/el_api_check: tools/el_api_check.cpp include/El.hpp include/elb200.h $(LIBDIR)/libelb200.so
+	$(NVCC) -std=c++17 -O1 -Xcompiler -Wall -Iinclude -o $@ $< -L$(LIBDIR) -lelb200 -lcudart -Xlinker -rpath,'$$ORIGIN/../$(LIBDIR)'
+
 clean:
-	rm -rf build $(LIBDIR)/libelb200.so tools/gemm_check tools/el_gemm_driver
+	rm -rf build $(LIBDIR)/libelb200.so tools/gemm_check tools/el_gemm_driver tools/el_api_check
 
 .PHONY: all clean

@@ -26,12 +26,56 @@ typedef int Int;  // reference default (no EL_USE_64BIT_INTS)
 
 // Values as in the reference (include/El/core/types.hpp:208-217, :464-469; level3.hpp:23-33).
 enum Dist { MC, MD, MR, VC, VR, STAR, CIRC };
+enum DistWrap { ELEMENT, BLOCK };
 enum Orientation { NORMAL, TRANSPOSE, ADJOINT };
 enum GridOrder { ROW_MAJOR, COLUMN_MAJOR };
+// hydrogen::Device (include/hydrogen/Device.hpp): only GPU exists here — there is no CPU path
+enum class Device : unsigned char { CPU, GPU };
 enum GemmAlgorithm {
     GEMM_DEFAULT, GEMM_SUMMA_A_MS, GEMM_SUMMA_A, GEMM_SUMMA_B_MS, GEMM_SUMMA_B, GEMM_SUMMA_C_MS, GEMM_SUMMA_C,
     GEMM_SUMMA_DOT, GEMM_CANNON
 };
+
+// El::Initialize / Finalize / Environment (src/core/environment.cpp:215-372). The reference brings up
+// MPI, the GPU and the blocksize stack; here there is no MPI (the NCCL bootstrap happens in Grid),
+// so these only make sure a device is usable and keep the call sites compiling.
+inline void Initialize(int& /*argc*/, char**& /*argv*/) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n < 1)
+        throw std::runtime_error("El::Initialize: no CUDA device (there is no CPU path)");
+}
+inline void Initialize() { int c = 0; char** v = nullptr; Initialize(c, v); }
+inline void Finalize() {}
+struct Environment {
+    Environment() { Initialize(); }
+    Environment(int& argc, char**& argv) { Initialize(argc, argv); }
+    ~Environment() { Finalize(); }
+};
+
+// SyncInfo<Device::GPU> (include/hydrogen/device/gpu/cuda/SyncInfo.hpp:14-84): a (stream, event)
+// handle. Every device entry of libelb200 takes the stream explicitly; the event is for callers
+// that order their own streams against it the way MultiSync does.
+template <Device D> struct SyncInfo;
+template <> struct SyncInfo<Device::GPU> {
+    SyncInfo() = default;
+    SyncInfo(cudaStream_t s, cudaEvent_t e) : stream_(s), event_(e) {}
+    cudaStream_t Stream() const { return stream_; }
+    cudaEvent_t Event() const { return event_; }
+    cudaStream_t stream_ = nullptr;
+    cudaEvent_t event_ = nullptr;
+};
+inline void Synchronize(const SyncInfo<Device::GPU>& si) {
+    if (cudaStreamSynchronize(si.Stream()) != cudaSuccess) throw std::runtime_error("El::Synchronize failed");
+}
+inline void AddSynchronizationPoint(const SyncInfo<Device::GPU>& si) {
+    if (si.Event() && cudaEventRecord(si.Event(), si.Stream()) != cudaSuccess) throw std::runtime_error("cudaEventRecord failed");
+}
+// `b` waits for everything enqueued on `a` so far (hydrogen/SyncInfoBase.hpp AddSynchronizationPoint(a, b))
+inline void AddSynchronizationPoint(const SyncInfo<Device::GPU>& a, const SyncInfo<Device::GPU>& b) {
+    if (!a.Event()) throw std::logic_error("AddSynchronizationPoint: the master SyncInfo has no event");
+    if (cudaEventRecord(a.Event(), a.Stream()) != cudaSuccess || cudaStreamWaitEvent(b.Stream(), a.Event(), 0) != cudaSuccess)
+        throw std::runtime_error("AddSynchronizationPoint failed");
+}
 
 namespace detail {
 inline void Check(int st, const char* where) {
@@ -64,6 +108,157 @@ struct Range {
 };
 inline Range IR(Int a, Int b) { return Range{a, b}; }
 static const Range ALL{0, -1};
+
+// ---------------------------------------------------------------------------------------------
+// El::Matrix<T, Device::GPU> (include/El/core/Matrix/decl.hpp:299-520): column-major device
+// matrix, owner or view, carrying the stream its operations run on (SyncInfo).
+// ---------------------------------------------------------------------------------------------
+template <typename T, Device D = Device::GPU>
+class Matrix {
+    static_assert(D == Device::GPU, "elemental_b200 has no CPU path: Matrix<T, Device::GPU> only");
+    static_assert(std::is_same<T, float>::value || std::is_same<T, double>::value, "float and double only");
+
+public:
+    Matrix() = default;
+    Matrix(Int height, Int width, Int ldim = 0) { Resize(height, width, ldim); }
+    ~Matrix() { Release(); }
+    Matrix(const Matrix&) = delete;  // copies are explicit (El::Copy), like every GPU transfer here
+    Matrix& operator=(const Matrix&) = delete;
+    Matrix(Matrix&& o) noexcept { *this = std::move(o); }
+    Matrix& operator=(Matrix&& o) noexcept {
+        if (this != &o) {
+            Release();
+            buf_ = o.buf_; h_ = o.h_; w_ = o.w_; ld_ = o.ld_; own_ = o.own_; cap_ = o.cap_; sync_ = o.sync_;
+            o.buf_ = nullptr; o.own_ = false; o.cap_ = 0;
+        }
+        return *this;
+    }
+    Int Height() const { return h_; }
+    Int Width() const { return w_; }
+    Int LDim() const { return ld_; }
+    bool Viewing() const { return !own_ && buf_ != nullptr; }
+    bool IsEmpty() const { return h_ == 0 || w_ == 0; }
+    Device GetDevice() const { return Device::GPU; }
+    T* Buffer() { return buf_; }
+    T* Buffer(Int i, Int j) { return buf_ + size_t(i) + size_t(j) * size_t(ld_); }
+    const T* LockedBuffer() const { return buf_; }
+    const T* LockedBuffer(Int i, Int j) const { return buf_ + size_t(i) + size_t(j) * size_t(ld_); }
+    void Resize(Int height, Int width, Int ldim = 0) {
+        if (height < 0 || width < 0) throw std::logic_error("Matrix::Resize: negative dimension");
+        const Int ld = ldim > 0 ? ldim : (height > 0 ? (height + 3) / 4 * 4 : 4);  // 16-byte column pitch
+        if (ld < height) throw std::logic_error("Matrix::Resize: ldim < height");
+        if (!own_ && buf_) {
+            if (height != h_ || width != w_) throw std::logic_error("Matrix::Resize: cannot resize a view");
+            return;
+        }
+        const size_t need = size_t(ld) * size_t(width > 0 ? width : 1);
+        if (need > cap_) {
+            Release();
+            if (cudaMallocAsync(reinterpret_cast<void**>(&buf_), need * sizeof(T), sync_.Stream()) != cudaSuccess)
+                throw std::runtime_error("Matrix::Resize: device allocation failed");
+            cap_ = need; own_ = true;
+        }
+        h_ = height; w_ = width; ld_ = ld;
+    }
+    // Attach / LockedAttach: borrow device memory (Matrix/decl.hpp Attach)
+    void Attach(Int height, Int width, T* buffer, Int ldim) {
+        Release();
+        buf_ = buffer; h_ = height; w_ = width; ld_ = ldim > 0 ? ldim : 1; own_ = false; cap_ = 0;
+    }
+    void LockedAttach(Int height, Int width, const T* buffer, Int ldim) { Attach(height, width, const_cast<T*>(buffer), ldim); }
+    // A(IR(i0,i1), IR(j0,j1)): zero-copy view
+    Matrix operator()(Range I, Range J) const;
+    SyncInfo<Device::GPU> GetSyncInfo() const { return sync_; }
+    void SetSyncInfo(const SyncInfo<Device::GPU>& si) { sync_ = si; }
+
+private:
+    void Release() {
+        if (own_ && buf_) cudaFreeAsync(buf_, sync_.Stream());
+        buf_ = nullptr; own_ = false; cap_ = 0;
+    }
+    T* buf_ = nullptr;
+    Int h_ = 0, w_ = 0, ld_ = 1;
+    bool own_ = false;
+    size_t cap_ = 0;
+    SyncInfo<Device::GPU> sync_;
+};
+template <typename T, Device D>
+Matrix<T, D> Matrix<T, D>::operator()(Range I, Range J) const {
+    const Int i1 = I.end < 0 ? h_ : I.end, j1 = J.end < 0 ? w_ : J.end;
+    if (I.beg < 0 || J.beg < 0 || i1 > h_ || j1 > w_ || I.beg > i1 || J.beg > j1) throw std::logic_error("Matrix view out of bounds");
+    Matrix v;
+    v.Attach(i1 - I.beg, j1 - J.beg, const_cast<T*>(LockedBuffer(I.beg, J.beg)), ld_);
+    v.SetSyncInfo(sync_);
+    return v;
+}
+template <typename T>
+SyncInfo<Device::GPU> SyncInfoFromMatrix(const Matrix<T, Device::GPU>& A) { return A.GetSyncInfo(); }
+template <typename T>
+void SetSyncInfo(Matrix<T, Device::GPU>& A, const SyncInfo<Device::GPU>& si) { A.SetSyncInfo(si); }
+
+namespace detail {
+template <typename T> struct LocalOps;
+template <> struct LocalOps<float> {
+    static int gemm(int ta, int tb, long m, long n, long k, float al, const float* A, long lda, const float* B, long ldb, float be, float* C, long ldc, void* s) { return elb200_gemm_f32(ta, tb, m, n, k, al, A, lda, B, ldb, be, C, ldc, s); }
+    static int copy(long r, long c, const float* X, long xr, long xc, float* Y, long yr, long yc, void* s) { return elb200_copy2d_f32(r, c, X, xr, xc, Y, yr, yc, s); }
+    static int transpose(long r, long c, const float* A, long lda, float* B, long ldb, void* s) { return elb200_transpose_f32(r, c, A, lda, B, ldb, s); }
+    static int axpy(long r, long c, float al, const float* X, long xr, long xc, float* Y, long yr, long yc, void* s) { return elb200_axpy2d_f32(r, c, al, X, xr, xc, Y, yr, yc, s); }
+    static int scale(long r, long c, float al, float* A, long lda, void* s) { return elb200_scale2d_f32(r, c, al, A, lda, s); }
+    static int fill(long r, long c, float v, float* A, long lda, void* s) { return elb200_fill2d_f32(r, c, v, A, lda, s); }
+};
+template <> struct LocalOps<double> {
+    static int gemm(int ta, int tb, long m, long n, long k, double al, const double* A, long lda, const double* B, long ldb, double be, double* C, long ldc, void* s) { return elb200_gemm_f64(ta, tb, m, n, k, al, A, lda, B, ldb, be, C, ldc, s); }
+    static int copy(long r, long c, const double* X, long xr, long xc, double* Y, long yr, long yc, void* s) { return elb200_copy2d_f64(r, c, X, xr, xc, Y, yr, yc, s); }
+    static int transpose(long r, long c, const double* A, long lda, double* B, long ldb, void* s) { return elb200_transpose_f64(r, c, A, lda, B, ldb, s); }
+    static int axpy(long r, long c, double al, const double* X, long xr, long xc, double* Y, long yr, long yc, void* s) { return elb200_axpy2d_f64(r, c, al, X, xr, xc, Y, yr, yc, s); }
+    static int scale(long r, long c, double al, double* A, long lda, void* s) { return elb200_scale2d_f64(r, c, al, A, lda, s); }
+    static int fill(long r, long c, double v, double* A, long lda, void* s) { return elb200_fill2d_f64(r, c, v, A, lda, s); }
+};
+}  // namespace detail
+
+// Local (sequential) BLAS on Matrix<T,GPU>: the reference's Gemm(Matrix) -> gpu_blas::Gemm
+// (Gemm.cpp:141-271) and the level-1 routines around it, asynchronous on C's / B's stream.
+template <typename T>
+void Gemm(Orientation orientA, Orientation orientB, T alpha, const Matrix<T>& A, const Matrix<T>& B, T beta, Matrix<T>& C) {
+    const Int m = orientA == NORMAL ? A.Height() : A.Width(), ka = orientA == NORMAL ? A.Width() : A.Height();
+    const Int n = orientB == NORMAL ? B.Width() : B.Height(), kb = orientB == NORMAL ? B.Height() : B.Width();
+    if (ka != kb || C.Height() != m || C.Width() != n) throw std::logic_error("Gemm: nonconformal matrices");  // Gemm.cpp:199-238
+    detail::Check(detail::LocalOps<T>::gemm(orientA != NORMAL, orientB != NORMAL, m, n, ka, alpha, A.LockedBuffer(), A.LDim(),
+                                            B.LockedBuffer(), B.LDim(), beta, C.Buffer(), C.LDim(), C.GetSyncInfo().Stream()), "Gemm");
+}
+template <typename T>
+void Gemm(Orientation orientA, Orientation orientB, T alpha, const Matrix<T>& A, const Matrix<T>& B, Matrix<T>& C) {
+    C.Resize(orientA == NORMAL ? A.Height() : A.Width(), orientB == NORMAL ? B.Width() : B.Height());
+    Gemm(orientA, orientB, alpha, A, B, T(0), C);
+}
+template <typename T>
+void Copy(const Matrix<T>& A, Matrix<T>& B) {
+    B.Resize(A.Height(), A.Width());
+    detail::Check(detail::LocalOps<T>::copy(A.Height(), A.Width(), A.LockedBuffer(), 1, A.LDim(), B.Buffer(), 1, B.LDim(),
+                                            B.GetSyncInfo().Stream()), "Copy");
+}
+template <typename T>
+void Transpose(const Matrix<T>& A, Matrix<T>& B) {
+    B.Resize(A.Width(), A.Height());
+    detail::Check(detail::LocalOps<T>::transpose(A.Height(), A.Width(), A.LockedBuffer(), A.LDim(), B.Buffer(), B.LDim(),
+                                                 B.GetSyncInfo().Stream()), "Transpose");
+}
+template <typename T>
+void Axpy(T alpha, const Matrix<T>& X, Matrix<T>& Y) {
+    if (X.Height() != Y.Height() || X.Width() != Y.Width()) throw std::logic_error("Axpy: nonconformal matrices");
+    detail::Check(detail::LocalOps<T>::axpy(X.Height(), X.Width(), alpha, X.LockedBuffer(), 1, X.LDim(), Y.Buffer(), 1, Y.LDim(),
+                                            Y.GetSyncInfo().Stream()), "Axpy");
+}
+template <typename T>
+void Scale(T alpha, Matrix<T>& A) {
+    detail::Check(detail::LocalOps<T>::scale(A.Height(), A.Width(), alpha, A.Buffer(), A.LDim(), A.GetSyncInfo().Stream()), "Scale");
+}
+template <typename T>
+void Fill(Matrix<T>& A, T value) {
+    detail::Check(detail::LocalOps<T>::fill(A.Height(), A.Width(), value, A.Buffer(), A.LDim(), A.GetSyncInfo().Stream()), "Fill");
+}
+template <typename T>
+void Zero(Matrix<T>& A) { Fill(A, T(0)); }
 
 // ---------------------------------------------------------------------------------------------
 // El::Grid — r x c process grid, COLUMN_MAJOR (VC rank = row + r*col), one process per GPU.
@@ -127,9 +322,11 @@ inline void PopBlocksizeStack() { elb200_pop_blocksize(); }
 // ---------------------------------------------------------------------------------------------
 // El::DistMatrix<T,U,V> (ELEMENT wrap, Device::GPU).  Owns its local matrix unless it is a view.
 // ---------------------------------------------------------------------------------------------
-template <typename T, Dist U = MC, Dist V = MR>
+template <typename T, Dist U = MC, Dist V = MR, DistWrap W = ELEMENT, Device D = Device::GPU>
 class DistMatrix {
     static_assert(std::is_same<T, float>::value || std::is_same<T, double>::value, "float and double only");
+    static_assert(W == ELEMENT, "BLOCK-wrapped distributions are outside the Gemm path");
+    static_assert(D == Device::GPU, "elemental_b200 has no CPU path: Device::GPU only");
 
 public:
     explicit DistMatrix(const El::Grid& g) : grid_(&g) {
@@ -145,7 +342,7 @@ public:
     }
     // B = A across distributions (the operator= tables of src/core/DistMatrix/ElementMatrix/*.cpp)
     template <Dist U2, Dist V2>
-    DistMatrix& operator=(const DistMatrix<T, U2, V2>& A) {
+    DistMatrix& operator=(const DistMatrix<T, U2, V2, W, D>& A) {
         detail::Check(elb200_dm_copy(A.Handle(), h_), "DistMatrix::operator=");
         return *this;
     }
@@ -157,7 +354,7 @@ public:
 
     void Align(Int colAlign, Int rowAlign) { detail::Check(elb200_dm_align(h_, colAlign, rowAlign), "Align"); }
     template <Dist U2, Dist V2>
-    void AlignWith(const DistMatrix<T, U2, V2>& A) { detail::Check(elb200_dm_align_with(h_, A.Handle()), "AlignWith"); }
+    void AlignWith(const DistMatrix<T, U2, V2, W, D>& A) { detail::Check(elb200_dm_align_with(h_, A.Handle()), "AlignWith"); }
     void Resize(Int height, Int width) { detail::Check(elb200_dm_resize(h_, height, width), "Resize"); }
     // [CIRC,CIRC] only: the VC rank that holds the matrix (AbstractDistMatrix.hpp:58,113)
     void SetRoot(int root) { detail::Check(elb200_dm_set_root(h_, root), "SetRoot"); }
@@ -195,6 +392,42 @@ public:
     T* Buffer() { return static_cast<T*>(Info().buffer); }              // DEVICE pointer
     const T* LockedBuffer() const { return static_cast<const T*>(Info().buffer); }
     elb200_dm_t Handle() const { return h_; }
+    Device GetLocalDevice() const { return Device::GPU; }
+    DistWrap Wrap() const { return W; }
+    bool Participating() const { return true; }  // every process of the grid takes part (no viewing-comm subsets)
+    // local <-> global index maps (include/El/core/DistMatrix/AbstractDistMatrix.hpp)
+    bool IsLocalRow(Int i) const { const auto d = Info(); return d.local_height > 0 && (i - d.col_shift) % d.col_stride == 0 && i >= d.col_shift; }
+    bool IsLocalCol(Int j) const { const auto d = Info(); return d.local_width > 0 && (j - d.row_shift) % d.row_stride == 0 && j >= d.row_shift; }
+    bool IsLocal(Int i, Int j) const { return IsLocalRow(i) && IsLocalCol(j); }
+    Int LocalRow(Int i) const { const auto d = Info(); return Int((i - d.col_shift) / d.col_stride); }
+    Int LocalCol(Int j) const { const auto d = Info(); return Int((j - d.row_shift) / d.row_stride); }
+    // The local matrix as a zero-copy El::Matrix view on the grid's stream (Matrix() / LockedMatrix()).
+    El::Matrix<T, Device::GPU> Matrix() {
+        const auto d = Info();
+        El::Matrix<T, Device::GPU> m;
+        m.Attach(Int(d.local_height), Int(d.local_width), static_cast<T*>(d.buffer), Int(d.ldim));
+        m.SetSyncInfo(SyncInfo<Device::GPU>(grid_->Stream(), nullptr));
+        return m;
+    }
+    El::Matrix<T, Device::GPU> LockedMatrix() const { return const_cast<DistMatrix*>(this)->Matrix(); }
+    // Single local entries through the host: synchronous, for tests and setup code only
+    // (the reference's GetLocal / SetLocal on a GPU matrix are the same blocking copies).
+    T GetLocal(Int iLoc, Int jLoc) const {
+        const auto d = Info();
+        if (iLoc < 0 || jLoc < 0 || iLoc >= d.local_height || jLoc >= d.local_width) throw std::logic_error("GetLocal: index out of range");
+        T v;
+        CudaCheck(cudaMemcpyAsync(&v, static_cast<const T*>(d.buffer) + size_t(iLoc) + size_t(jLoc) * size_t(d.ldim), sizeof(T),
+                                  cudaMemcpyDeviceToHost, grid_->Stream()));
+        grid_->Synchronize();
+        return v;
+    }
+    void SetLocal(Int iLoc, Int jLoc, T v) {
+        const auto d = Info();
+        if (iLoc < 0 || jLoc < 0 || iLoc >= d.local_height || jLoc >= d.local_width) throw std::logic_error("SetLocal: index out of range");
+        CudaCheck(cudaMemcpyAsync(static_cast<T*>(d.buffer) + size_t(iLoc) + size_t(jLoc) * size_t(d.ldim), &v, sizeof(T),
+                                  cudaMemcpyHostToDevice, grid_->Stream()));
+        grid_->Synchronize();
+    }
 
     // Host <-> local device matrix, column-major with leading dimension LocalHeight() on the host
     // side (the reference's CPU<->GPU Matrix copies, include/El/core/Matrix/impl_gpu.hpp).

@@ -1,0 +1,96 @@
+// el_api_check — compile-and-link check of the El.hpp facade against libelb200: a translation unit
+// written the way a Hydrogen / LBANN caller writes it (SURVEY.md 8(b) "Source API"), touching every
+// name of the facade for float and double.  `make tools/el_api_check` building it is the test on a
+// machine without a GPU; run on a GPU box it executes a small end-to-end pass and prints PASS.
+#include <El.hpp>
+
+#include <cstdio>
+#include <vector>
+
+using namespace El;
+
+template <typename T>
+static int exercise(const Grid& g) {
+    int bad = 0;
+    const Int m = 96, n = 80, k = 112;
+    DistMatrix<T, MC, MR, ELEMENT, Device::GPU> A(g), B(g), C(g);
+    Uniform(A, m, k, T(0), T(1), 1);
+    Uniform(B, k, n, T(0), T(1), 2);
+    Uniform(C, m, n, T(0), T(1), 3);
+    DistMatrix<T> C0(C);                                    // copy constructor
+    PushBlocksizeStack(32);
+    Gemm(NORMAL, NORMAL, T(2), A, B, T(3), C, GEMM_SUMMA_C);
+    PopBlocksizeStack();
+    // the same product out of redistributed panels + LocalGemm (what SUMMA_C does internally)
+    DistMatrix<T, MC, STAR> A_MC_STAR(g);
+    DistMatrix<T, STAR, MR> B_STAR_MR(g);
+    A_MC_STAR.AlignWith(C0);
+    B_STAR_MR.AlignWith(C0);
+    A_MC_STAR = A;
+    B_STAR_MR = B;
+    DistMatrix<T> D(C0);
+    LocalGemm(NORMAL, NORMAL, T(2), A_MC_STAR, B_STAR_MR, T(3), D);
+    Axpy(T(-1), C, D);
+    if (FrobeniusNorm(D) > 1e-3 * FrobeniusNorm(C)) ++bad;
+    // local matrices, views, SyncInfo
+    auto Cloc = C.Matrix();
+    const auto Aloc = A.LockedMatrix();
+    SyncInfo<Device::GPU> si = SyncInfoFromMatrix(Cloc);
+    Matrix<T> L1(Cloc.Height(), Cloc.Width()), L2;
+    SetSyncInfo(L1, si);
+    SetSyncInfo(L2, si);
+    Copy(Cloc, L1);
+    Transpose(L1, L2);
+    Scale(T(0.5), L1);
+    Axpy(T(1), Cloc, L1);
+    Zero(L2);
+    Fill(L2, T(1));
+    auto V = L1(IR(0, L1.Height() / 2), ALL);
+    if (V.Height() != L1.Height() / 2 || !V.Viewing() || Aloc.GetDevice() != Device::GPU) ++bad;
+    Matrix<T> P;
+    SetSyncInfo(P, si);
+    if (Aloc.Width() > 0 && Aloc.Height() > 0) {
+        Matrix<T> At;
+        SetSyncInfo(At, si);
+        Transpose(Aloc, At);
+        Gemm(NORMAL, NORMAL, T(1), At, Aloc, P);           // local Gemm(Matrix) with resize
+        if (P.Height() != Aloc.Width()) ++bad;
+    }
+    Synchronize(si);
+    // views, index maps, single entries, contractions, transposes, rooted matrices
+    auto Cv = C(IR(8, m), IR(4, n));
+    if (Cv.Height() != m - 8 || !Cv.Viewing() || Cv.ColAlign() != (C.ColAlign() + 8) % C.ColStride()) ++bad;
+    if (C.LocalHeight() > 0 && C.LocalWidth() > 0) {
+        const T v = C.GetLocal(0, 0);
+        C.SetLocal(0, 0, v);
+        if (!C.IsLocal(C.GlobalRow(0), C.GlobalCol(0)) || C.LocalRow(C.GlobalRow(0)) != 0) ++bad;
+    }
+    DistMatrix<T, MR, MC> Ct(g);
+    Transpose(C, Ct);
+    DistMatrix<T, STAR, STAR> Full(g);
+    Copy(C, Full);
+    DistMatrix<T> Acc(g);
+    Acc.Resize(m, n);
+    Zero(Acc);
+    AxpyContract(T(1), Full, Acc);                          // sums p replicas
+    Contract(Full, Acc);
+    DistMatrix<T, CIRC, CIRC> Root(g);
+    Root.SetRoot(g.Size() - 1);
+    Root = C;
+    if (Root.Root() != g.Size() - 1 || (g.Rank() == g.Size() - 1 ? Root.LocalHeight() != m : Root.LocalHeight() != 0)) ++bad;
+    DistMatrix<T, VC, STAR> Rows(g);
+    Rows = Root;
+    Gemm(TRANSPOSE, NORMAL, T(1), A, C0, Acc);              // resize overload
+    if (Acc.Height() != k || Acc.Width() != n) ++bad;
+    g.Synchronize();
+    return bad;
+}
+
+int main(int argc, char** argv) {
+    Environment env(argc, argv);
+    Grid g;  // 1 x 1 on the current device
+    int bad = exercise<float>(g) + exercise<double>(g);
+    if (Blocksize() != 128 || Grid::DefaultHeight(8) != 2) ++bad;
+    std::printf(bad ? "EL_API_CHECK_FAIL %d\n" : "EL_API_CHECK_PASS\n", bad);
+    return bad ? 1 : 0;
+}
