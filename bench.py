@@ -340,7 +340,8 @@ def _measure(args, grid, el, lib, torch, dist, world, rank, local, n_gpus, n, td
             basis = f"{peaks['source']}: sustained bf16 {peaks['bf16_sustained']} TF/s / 6 (tf32 = bf16/2, 3 UMMAs per MAC); burst-derived {peaks['bf16'] / 6.0:.1f}"
         else:
             peak = 40.0
-            basis = "B200 FP64 (DMMA == FMA rate) nominal 40 TF/s; no measured fp64 peak in MEASURED_PEAKS.json (cublasDgemm on this pool: 35.9 TF/s, profiles/)"
+            basis = ("B200 FP64 (DMMA == FMA rate) nominal 40 TF/s; no measured fp64 peak in MEASURED_PEAKS.json. ncu reports the pipe's "
+                     "peak_sustained as 128 flop/clk/SM = 37.2 TF/s at 1965 MHz; cublasDgemm on this pool: 35.9 TF/s (profiles/)")
         traffic = None
         tp = os.path.join(ROOT, "profiles", f"r01_ncu_gemm_{args.dtype}_traffic.json")
         if os.path.exists(tp):
