@@ -25,7 +25,11 @@ void nccl_check(ncclResult_t r, const char* where) {
 namespace {
 std::mutex g_bs_mutex;
 std::vector<int>& bs_stack() {
+#ifdef ELB200_HOSTSIM  // tests/hostsim runs the ranks of a grid as threads of one process: one stack per rank
+    static thread_local std::vector<int> s{128};
+#else
     static std::vector<int> s{128};
+#endif
     return s;
 }
 }  // namespace

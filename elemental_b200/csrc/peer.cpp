@@ -62,7 +62,9 @@ PeerArena* PeerArena::Create(ncclComm_t world, int rank, int size, cudaStream_t 
     const char* off = std::getenv("ELB200_P2P");
     if ((off && std::atoi(off) == 0) || size < 2 || size > kMaxRanks || !world) return nullptr;
     const char* mb = std::getenv("ELB200_ARENA_MB");
-    const size_t slot_bytes = size_t(mb && std::atoll(mb) > 0 ? std::atoll(mb) : 1024) << 20;
+    const char* kb = std::getenv("ELB200_ARENA_KB");  // finer unit, for tests of the does-not-fit fallbacks
+    const size_t slot_bytes = kb && std::atoll(kb) > 0 ? size_t(std::atoll(kb)) << 10
+                                                       : size_t(mb && std::atoll(mb) > 0 ? std::atoll(mb) : 1024) << 20;
 
     PeerArena* pa = new PeerArena();
     pa->rank_ = rank; pa->size_ = size; pa->slot_bytes_ = slot_bytes;

@@ -23,6 +23,17 @@ from oracle import gemm as OG
 NPDT = {torch.float32: np.float32, torch.float64: np.float64}
 
 
+def use_backend(module) -> None:
+    """Swap the `el` interface the cases drive: elemental_b200.el (the CUDA library, default) or
+    tests/hostsim/sim_el.py (the same ENGINE sources over host test doubles, for machines without a GPU)."""
+    global el
+    el = module
+
+
+def _pin(t: torch.Tensor) -> torch.Tensor:
+    return t.pin_memory() if torch.cuda.is_available() else t
+
+
 def _grid_oracle(grid) -> OD.Grid:
     return OD.Grid(grid.Height(), grid.Width())
 
@@ -98,7 +109,7 @@ def check_circ(grid, dtype=torch.float64, m=23, n=17) -> int:
     # CPU <-> GPU copy of the local matrix (ProxyDevice.hpp): pinned host tensors, ld > local height
     A = el.DistMatrix(grid, el.MC, el.MR, dtype).Align(1 % og.r, 0).from_global(G)
     lh, lw = A.LocalHeight(), A.LocalWidth()
-    host = torch.full((max(lw, 1), lh + 3), -7.0, dtype=dtype).pin_memory()
+    host = _pin(torch.full((max(lw, 1), lh + 3), -7.0, dtype=dtype))
     A.read_local_to_host(host)
     grid.sync()
     loc = OD.local_of(G, OD.Spec(OD.MC, OD.MR, 1 % og.r, 0, m, n), og, me)
@@ -262,7 +273,7 @@ def check_gemm_host(grid, dtype) -> int:
             def host(G, pad):
                 loc = OD.local_of(G, zero(*G.shape), og, me)
                 ld = max(loc.shape[0], 1) + pad
-                buf = torch.zeros((max(loc.shape[1], 1), ld), dtype=dtype).pin_memory()
+                buf = _pin(torch.zeros((max(loc.shape[1], 1), ld), dtype=dtype))
                 view = buf.t()[:loc.shape[0], :loc.shape[1]]  # column-major window, leading dimension ld
                 view.copy_(torch.from_numpy(np.ascontiguousarray(loc)))
                 return buf, view, ld
@@ -282,6 +293,27 @@ def check_gemm_host(grid, dtype) -> int:
     return cnt
 
 
+def check_gemm_pipeline(grid, dtype=torch.float64) -> int:
+    """SUMMA with MANY panels per call (k = 1300 is several panels once ELB200_PANEL_K is 512 or less;
+    with the default width it is one): exercises the two-slot gather / GEMM pipeline, the ramp widths,
+    slot hand-back and the zero-copy direct panels (NN, aligned) as well as the staged ones
+    (misaligned / transposed), and the multi-panel loops of SUMMA A / B."""
+    og = _grid_oracle(grid)
+    cnt = 0
+    mis = ((1, 2), (0, 1), (1, 0))
+    for (oa, ob, alg, al) in ((0, 0, el.GEMM_SUMMA_C, None), (0, 0, el.GEMM_SUMMA_C, mis), (1, 0, el.GEMM_SUMMA_C, None),
+                              (0, 1, el.GEMM_SUMMA_C, mis), (1, 1, el.GEMM_SUMMA_C, None)):
+        err, tol = gemm_case(grid, dtype, oa, ob, alg, 150, 130, 1300, alpha=0.5, beta=-0.5, aligns=al)
+        assert err <= tol, (oa, ob, alg, al, err, tol)
+        cnt += 1
+    for (oa, ob, alg) in ((0, 0, el.GEMM_SUMMA_A), (1, 0, el.GEMM_SUMMA_A), (0, 1, el.GEMM_SUMMA_B), (1, 1, el.GEMM_SUMMA_B)):
+        m, n, k = (90, 1300, 110) if alg == el.GEMM_SUMMA_A else (1300, 90, 110)
+        err, tol = gemm_case(grid, dtype, oa, ob, alg, m, n, k, alpha=0.5, beta=-0.5, aligns=mis)
+        assert err <= tol, (oa, ob, alg, err, tol)
+        cnt += 1
+    return cnt
+
+
 def run_all(grid, heavy=False) -> dict:
     out = {}
     out["redist_f64"] = check_redistributions(grid, torch.float64)
@@ -297,6 +329,7 @@ def run_all(grid, heavy=False) -> dict:
     check_gemm_proxies(grid, torch.float64)
     check_gemm_proxies(grid, torch.float32)
     out["gemm_host"] = check_gemm_host(grid, torch.float32) + check_gemm_host(grid, torch.float64)
+    out["gemm_pipeline"] = check_gemm_pipeline(grid, torch.float64) + check_gemm_pipeline(grid, torch.float32)
     if heavy:
         # panels wider than one algorithmic block, ragged edges, default blocksize
         for dt in (torch.float32, torch.float64):

@@ -1,0 +1,268 @@
+// hostsim: test doubles of libelb200's DEVICE entry points (the kernels of blas1.cu, gemm_f32.cu,
+// gemm_f64.cu and the glue of capi_core.cu), same C signatures and argument checks, executed as
+// stream-ordered host closures (see sim.hpp). They exist so that the host ENGINE can be run without
+// a GPU in tests; they say nothing about the CUDA kernels, which are checked on a B200 by the
+// `-m gpu` tests. Every access is bounds-checked against the simulated device allocations.
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+#include "../../include/elb200.h"
+#include "sim.hpp"
+
+namespace elb {
+
+thread_local char g_last_error[512] = "";
+std::atomic<unsigned long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+thread_local int g_lattice_cta_limit = 0;
+int lattice_cta_limit() { return g_lattice_cta_limit; }
+void set_lattice_cta_limit(int ctas) { g_lattice_cta_limit = ctas > 0 ? ctas : 0; }
+void set_last_error(const char* what, const char* detail) {
+    std::snprintf(g_last_error, sizeof(g_last_error), "%s: %s", what, detail ? detail : "");
+}
+int device_sm_count() { return 148; }
+
+}  // namespace elb
+
+namespace {
+
+using elb::count_launch;
+
+cudaStream_t st(void* s) { return static_cast<cudaStream_t>(s); }
+
+// byte span touched by a rows x cols lattice with element strides (rs, cs) starting at p
+template <typename T>
+void check_lattice(const T* p, int64_t rows, int64_t cols, int64_t rs, int64_t cs, const char* what) {
+    if (rows <= 0 || cols <= 0) return;
+    if (rs < 0 || cs < 0) sim::fail("%s: negative stride", what);
+    const int64_t last = (rows - 1) * rs + (cols - 1) * cs;
+    sim::check_device_range(p, size_t(last + 1) * sizeof(T), what);
+}
+
+template <typename T>
+int copy2d(int64_t rows, int64_t cols, const T* src, int64_t srs, int64_t scs, T* dst, int64_t drs, int64_t dcs, void* s) {
+    if (rows < 0 || cols < 0) return ELB200_ERR_ARG;
+    if (rows == 0 || cols == 0) return ELB200_OK;
+    count_launch();
+    sim::enqueue(st(s), [=] {
+        check_lattice(src, rows, cols, srs, scs, "copy2d src");
+        check_lattice(dst, rows, cols, drs, dcs, "copy2d dst");
+        for (int64_t j = 0; j < cols; ++j)
+            for (int64_t i = 0; i < rows; ++i) dst[i * drs + j * dcs] = src[i * srs + j * scs];
+    });
+    return ELB200_OK;
+}
+
+template <typename T>
+int axpy2d(int64_t rows, int64_t cols, T alpha, const T* X, int64_t xrs, int64_t xcs, T* Y, int64_t yrs, int64_t ycs, void* s) {
+    if (rows < 0 || cols < 0) return ELB200_ERR_ARG;
+    if (rows == 0 || cols == 0) return ELB200_OK;
+    count_launch();
+    sim::enqueue(st(s), [=] {
+        check_lattice(X, rows, cols, xrs, xcs, "axpy2d X");
+        check_lattice(Y, rows, cols, yrs, ycs, "axpy2d Y");
+        for (int64_t j = 0; j < cols; ++j)
+            for (int64_t i = 0; i < rows; ++i) Y[i * yrs + j * ycs] += alpha * X[i * xrs + j * xcs];
+    });
+    return ELB200_OK;
+}
+
+// B(cols x rows, ldb) = A(rows x cols, lda)^T, or B += alpha * A^T
+template <typename T, bool AXPY>
+int transpose(int64_t rows, int64_t cols, const T* A, int64_t lda, T* B, int64_t ldb, T alpha, void* s) {
+    if (rows < 0 || cols < 0 || lda < (rows > 1 ? rows : 1) || ldb < (cols > 1 ? cols : 1)) return ELB200_ERR_ARG;
+    if (rows == 0 || cols == 0) return ELB200_OK;
+    count_launch();
+    sim::enqueue(st(s), [=] {
+        check_lattice(A, rows, cols, 1, lda, "transpose A");
+        check_lattice(B, cols, rows, 1, ldb, "transpose B");
+        for (int64_t j = 0; j < cols; ++j)
+            for (int64_t i = 0; i < rows; ++i) {
+                if (AXPY) B[j + i * ldb] += alpha * A[i + j * lda];
+                else B[j + i * ldb] = A[i + j * lda];
+            }
+    });
+    return ELB200_OK;
+}
+
+template <typename T>
+int fill2d(int64_t rows, int64_t cols, T v, T* A, int64_t lda, void* s) {
+    if (rows < 0 || cols < 0) return ELB200_ERR_ARG;
+    if (rows == 0 || cols == 0) return ELB200_OK;
+    count_launch();
+    sim::enqueue(st(s), [=] {
+        check_lattice(A, rows, cols, 1, lda, "fill2d");
+        for (int64_t j = 0; j < cols; ++j)
+            for (int64_t i = 0; i < rows; ++i) A[i + j * lda] = v;
+    });
+    return ELB200_OK;
+}
+
+template <typename T>
+int scale2d(int64_t rows, int64_t cols, T alpha, T* A, int64_t lda, void* s) {
+    if (rows < 0 || cols < 0) return ELB200_ERR_ARG;
+    if (alpha == T(1)) return ELB200_OK;
+    if (alpha == T(0)) return fill2d<T>(rows, cols, T(0), A, lda, s);
+    if (rows == 0 || cols == 0) return ELB200_OK;
+    count_launch();
+    sim::enqueue(st(s), [=] {
+        check_lattice(A, rows, cols, 1, lda, "scale2d");
+        for (int64_t j = 0; j < cols; ++j)
+            for (int64_t i = 0; i < rows; ++i) A[i + j * lda] *= alpha;
+    });
+    return ELB200_OK;
+}
+
+template <typename T>
+int lattice(int mode, int nseg, const elb200_segment* segs, T* M, int64_t ldm, T* buf, T alpha, void* s) {
+    if (mode < ELB200_PACK || mode > ELB200_UNPACK_AXPY || nseg < 0 || nseg > ELB200_MAX_SEGMENTS || (nseg > 0 && !segs))
+        return ELB200_ERR_ARG;
+    std::vector<elb200_segment> tab;
+    for (int i = 0; i < nseg; ++i) {
+        const elb200_segment& g = segs[i];
+        if (g.rows < 0 || g.cols < 0 || g.row_step < 1 || g.col_step < 1 || g.row0 < 0 || g.col0 < 0 || g.buf_offset < 0)
+            return ELB200_ERR_ARG;
+        if (g.rows > 0 && g.cols > 0) tab.push_back(g);
+    }
+    if (tab.empty()) return ELB200_OK;
+    if (!M || !buf || ldm < 1) return ELB200_ERR_ARG;
+    count_launch();
+    sim::enqueue(st(s), [=] {
+        for (const elb200_segment& g : tab) {
+            check_lattice(M + g.row0 + g.col0 * ldm, g.rows, g.cols, g.row_step, g.col_step * ldm, "lattice M");
+            sim::check_device_range(buf + g.buf_offset, size_t(g.rows) * size_t(g.cols) * sizeof(T), "lattice staging");
+            for (int64_t j = 0; j < g.cols; ++j)
+                for (int64_t i = 0; i < g.rows; ++i) {
+                    T* mp = M + g.row0 + i * g.row_step + (g.col0 + j * g.col_step) * ldm;
+                    T* bp = buf + g.buf_offset + i + j * g.rows;
+                    if (mode == ELB200_PACK) *bp = *mp;
+                    else if (mode == ELB200_UNPACK) *mp = *bp;
+                    else *mp += alpha * *bp;
+                }
+        }
+    });
+    return ELB200_OK;
+}
+
+template <typename T>
+int peer_reduce_axpy(int nsrc, const T* const* srcs, int64_t off, const elb200_segment* seg, T* M, int64_t ldm, T alpha, void* s) {
+    if (nsrc < 1 || nsrc > ELB200_MAX_SEGMENTS || !srcs || !seg || seg->rows < 0 || seg->cols < 0 || seg->row_step < 1 ||
+        seg->col_step < 1)
+        return ELB200_ERR_ARG;
+    if (seg->rows == 0 || seg->cols == 0) return ELB200_OK;
+    std::vector<const T*> src(srcs, srcs + nsrc);
+    const elb200_segment g = *seg;
+    count_launch();
+    sim::enqueue(st(s), [=] {
+        check_lattice(M + g.row0 + g.col0 * ldm, g.rows, g.cols, g.row_step, g.col_step * ldm, "peer_reduce_axpy M");
+        for (const T* p : src) sim::check_device_range(p + off, size_t(g.rows) * size_t(g.cols) * sizeof(T), "peer_reduce_axpy source");
+        for (int64_t j = 0; j < g.cols; ++j)
+            for (int64_t i = 0; i < g.rows; ++i) {
+                const int64_t e = off + i + j * g.rows;
+                T sum = T(0);
+                for (const T* p : src) sum += p[e];
+                T* mp = M + g.row0 + i * g.row_step + (g.col0 + j * g.col_step) * ldm;
+                *mp += alpha * sum;
+            }
+    });
+    return ELB200_OK;
+}
+
+int check_gemm_args(int transA, int transB, int64_t m, int64_t n, int64_t k, const void* A, int64_t lda, const void* B,
+                    int64_t ldb, const void* C, int64_t ldc) {
+    if (transA < 0 || transA > 2 || transB < 0 || transB > 2) return ELB200_ERR_ARG;
+    if (m < 0 || n < 0 || k < 0) return ELB200_ERR_ARG;
+    const int64_t a_rows = transA ? k : m, b_rows = transB ? n : k;
+    if (lda < (a_rows > 1 ? a_rows : 1) || ldb < (b_rows > 1 ? b_rows : 1) || ldc < (m > 1 ? m : 1)) return ELB200_ERR_ARG;
+    if (m > 0 && n > 0 && !C) return ELB200_ERR_ARG;
+    if (m > 0 && n > 0 && k > 0 && (!A || !B)) return ELB200_ERR_ARG;
+    return ELB200_OK;
+}
+
+// plain triple loop in double precision (axpy form over packed column-major op(A))
+template <typename T>
+int gemm(int ta, int tb, int64_t m, int64_t n, int64_t k, T alpha, const T* A, int64_t lda, const T* B, int64_t ldb, T beta,
+         T* C, int64_t ldc, void* s) {
+    int stt = check_gemm_args(ta, tb, m, n, k, A, lda, B, ldb, C, ldc);
+    if (stt != ELB200_OK) return stt;
+    if (m == 0 || n == 0) return ELB200_OK;
+    if (k == 0 || alpha == T(0)) return scale2d<T>(m, n, beta, C, ldc, s);
+    count_launch();
+    sim::enqueue(st(s), [=] {
+        check_lattice(A, ta ? k : m, ta ? m : k, 1, lda, "gemm A");
+        check_lattice(B, tb ? n : k, tb ? k : n, 1, ldb, "gemm B");
+        check_lattice(C, m, n, 1, ldc, "gemm C");
+        std::vector<double> a(static_cast<size_t>(m * k));
+        std::vector<double> acc(static_cast<size_t>(m), 0.0);
+        for (int64_t l = 0; l < k; ++l)
+            for (int64_t i = 0; i < m; ++i) a[size_t(i) + size_t(l) * m] = double(ta ? A[l + i * lda] : A[i + l * lda]);
+        for (int64_t j = 0; j < n; ++j) {
+            std::fill(acc.begin(), acc.end(), 0.0);
+            for (int64_t l = 0; l < k; ++l) {
+                const double b = double(tb ? B[j + l * ldb] : B[l + j * ldb]);
+                const double* col = a.data() + size_t(l) * m;
+                for (int64_t i = 0; i < m; ++i) acc[i] += col[i] * b;
+            }
+            for (int64_t i = 0; i < m; ++i) {
+                T* c = C + i + j * ldc;
+                *c = beta == T(0) ? T(double(alpha) * acc[i]) : T(double(alpha) * acc[i] + double(beta) * double(*c));
+            }
+        }
+    });
+    return ELB200_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* elb200_status_string(int status) {
+    switch (status) {
+        case ELB200_OK: return "ok";
+        case ELB200_ERR_CUDA: return "CUDA error";
+        case ELB200_ERR_ARG: return "invalid argument";
+        case ELB200_ERR_TENSORMAP: return "tensor map encode failed";
+        case ELB200_ERR_NCCL: return "NCCL error";
+        case ELB200_ERR_STATE: return "library not initialised";
+        default: return "unknown status";
+    }
+}
+const char* elb200_last_error(void) { return elb::g_last_error; }
+unsigned long long elb200_launch_count(void) { return elb::g_launches.load(std::memory_order_relaxed); }
+const char* elb200_build_info(void) { return "hostsim: host test double of libelb200's device layer (tests only, no GPU code)"; }
+
+int elb200_gemm_f32(int ta, int tb, int64_t m, int64_t n, int64_t k, float al, const float* A, int64_t lda, const float* B,
+                    int64_t ldb, float be, float* C, int64_t ldc, void* s) {
+    return gemm<float>(ta, tb, m, n, k, al, A, lda, B, ldb, be, C, ldc, s);
+}
+int elb200_gemm_f32_ex(int ta, int tb, int64_t m, int64_t n, int64_t k, float al, const float* A, int64_t lda, const float* B,
+                       int64_t ldb, float be, float* C, int64_t ldc, int, void* s) {
+    return gemm<float>(ta, tb, m, n, k, al, A, lda, B, ldb, be, C, ldc, s);
+}
+int elb200_gemm_f64(int ta, int tb, int64_t m, int64_t n, int64_t k, double al, const double* A, int64_t lda, const double* B,
+                    int64_t ldb, double be, double* C, int64_t ldc, void* s) {
+    return gemm<double>(ta, tb, m, n, k, al, A, lda, B, ldb, be, C, ldc, s);
+}
+
+#define SIM_BLAS1(SUF, T)                                                                                                       \
+    int elb200_copy2d_##SUF(int64_t r, int64_t c, const T* src, int64_t srs, int64_t scs, T* dst, int64_t drs, int64_t dcs,     \
+                            void* s) { return copy2d<T>(r, c, src, srs, scs, dst, drs, dcs, s); }                              \
+    int elb200_transpose_##SUF(int64_t r, int64_t c, const T* A, int64_t lda, T* B, int64_t ldb, void* s) {                     \
+        return transpose<T, false>(r, c, A, lda, B, ldb, T(0), s); }                                                            \
+    int elb200_axpy2d_##SUF(int64_t r, int64_t c, T al, const T* X, int64_t xrs, int64_t xcs, T* Y, int64_t yrs, int64_t ycs,   \
+                            void* s) { return axpy2d<T>(r, c, al, X, xrs, xcs, Y, yrs, ycs, s); }                              \
+    int elb200_axpy2d_transpose_##SUF(int64_t r, int64_t c, T al, const T* A, int64_t lda, T* B, int64_t ldb, void* s) {        \
+        return transpose<T, true>(c, r, A, lda, B, ldb, al, s); }                                                               \
+    int elb200_scale2d_##SUF(int64_t r, int64_t c, T al, T* A, int64_t lda, void* s) { return scale2d<T>(r, c, al, A, lda, s); } \
+    int elb200_fill2d_##SUF(int64_t r, int64_t c, T v, T* A, int64_t lda, void* s) { return fill2d<T>(r, c, v, A, lda, s); }    \
+    int elb200_lattice_##SUF(int mode, int nseg, const elb200_segment* segs, T* M, int64_t ldm, T* buf, T al, void* s) {        \
+        return lattice<T>(mode, nseg, segs, M, ldm, buf, al, s); }                                                              \
+    int elb200_peer_reduce_axpy_##SUF(int nsrc, const T* const* srcs, int64_t off, const elb200_segment* seg, T* M,             \
+                                      int64_t ldm, T al, void* s) { return peer_reduce_axpy<T>(nsrc, srcs, off, seg, M, ldm, al, s); }
+SIM_BLAS1(f32, float)
+SIM_BLAS1(f64, double)
+#undef SIM_BLAS1
+
+}  // extern "C"

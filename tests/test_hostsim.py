@@ -1,0 +1,92 @@
+"""The host ENGINE of libelb200 executed WITHOUT a GPU (N > 1 on CPU).
+
+tests/hostsim links the engine sources of elemental_b200/csrc (Grid, DistMat, the redistribution
+exchanges, the peer-arena handshake, the SUMMA A / B / C / Dot schedules with their stream / event
+pipelines, the host-operand Gemm, the handle C ABI) against test doubles of the CUDA runtime (streams
+are FIFO worker threads, events carry generations, device memory is bounds-checked and poisoned on
+free), of NCCL (ranks are threads of one process) and of the device kernels.  The distributed parity
+cases of tests/dist_cases.py — the same functions the `-m gpu` tests run on B200s — then run on
+1 x 1 ... 2 x 4 grids against the oracle: every redistribution bit-exact, every Gemm variant within
+the north-star bound.  This checks the HOST logic only; the CUDA kernels are checked on the GPU.
+Nothing of hostsim is linked into or loaded by the product library (tests/hostsim/sim.hpp).
+"""
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+WORKER = os.path.join(ROOT, "tests", "hostsim", "worker.py")
+
+
+@pytest.fixture(scope="module")
+def simlib():
+    sys.path.insert(0, ROOT)
+    from tests.hostsim import build
+    return build.build()
+
+
+def _run(grid, *args, env=None, timeout=900):
+    e = dict(os.environ, HOSTSIM_TIMEOUT="90", ELB200_ARENA_MB="8", OMP_NUM_THREADS="1")
+    e.update(env or {})
+    r = subprocess.run([sys.executable, WORKER, grid, *args], capture_output=True, text=True, timeout=timeout, cwd=ROOT, env=e)
+    assert r.returncode == 0 and "HOSTSIM_PASS" in r.stdout, (r.stdout[-3000:] + r.stderr[-6000:])
+    return r.stdout
+
+
+def test_engine_1x1_all_cases(simlib):
+    out = _run("1x1")
+    assert "'redist_f64': 121" in out and "'gemm_f64': 40" in out and "'gemm_host': 24" in out
+
+
+def test_engine_2x2_peer_arena_all_cases(simlib):
+    """Every case on a 2 x 2 grid with the NVLink peer-arena paths (copy-engine AllGather, pull
+    exchange, receiver-side reduce) — the paths the multi-GPU bench runs."""
+    out = _run("2x2")
+    assert "'redist_f64': 121" in out and "'circ': 54" in out and "'gemm_f32': 40" in out
+
+
+def test_engine_2x4_bench_grid(simlib):
+    """The 8-GPU grid shape of BASELINE C3 (2 x 4): redistributions, contractions, all Gemm variants."""
+    _run("2x4", "--only", "check_redistributions,check_contractions,check_gemm_variants_f64,check_gemm_proxies_f32")
+
+
+def test_engine_3x2_nccl_fallback(simlib):
+    """Peer arena disabled (ELB200_P2P=0): the NCCL AllGather / ReduceScatter / grouped send-recv
+    paths on a non-square grid with r > c."""
+    _run("3x2", "--only", "check_redistributions,check_contractions,check_gemm_variants_f32", env={"ELB200_P2P": "0"})
+
+
+@pytest.mark.parametrize("grid,env", [("2x2", {}), ("2x4", {}), ("1x2", {}), ("2x3", {"ELB200_P2P": "0"}),
+                                       ("2x2", {"ELB200_DIRECT": "0"}), ("2x2", {"ELB200_OVERLAP": "0"})])
+def test_engine_multi_panel_pipeline(simlib, grid, env):
+    """Narrow panels (ELB200_PANEL_K=512, k = 1300): several panels per Gemm through the two-slot
+    gather | GEMM pipeline, zero-copy direct panels, staged panels, and with the pipeline off."""
+    e = {"ELB200_PANEL_K": "512"}
+    e.update(env)
+    _run(grid, "--only", "check_gemm_pipeline,check_gemm_pipeline_f32", env=e)
+
+
+def test_engine_tiny_arena_falls_back(simlib):
+    """Arena slots of 4 KiB: some messages fit, most do not — every size check must route the rest to
+    NCCL (and every rank must take the same branch)."""
+    _run("2x2", "--only", "check_redistributions,check_contractions,check_gemm_pipeline", env={"ELB200_ARENA_KB": "4"})
+
+
+def test_cxx_facade_on_hostsim(simlib):
+    """include/El.hpp exercised for real on CPU: tools/el_api_check.cpp and tools/el_gemm_driver.cpp
+    (the counterpart of the reference's tests/blas_like/Gemm.cpp) linked against the hostsim engine."""
+    out_dir = os.path.dirname(simlib)
+    for tool, args in (("el_api_check", []), ("el_gemm_driver", ["--m", "150", "--n", "120", "--k", "130", "--reps", "1"]),
+                       ("el_gemm_driver", ["--m", "150", "--n", "120", "--k", "130", "--reps", "1", "--f64"])):
+        exe = os.path.join(out_dir, tool)
+        src = os.path.join(ROOT, "tools", tool + ".cpp")
+        deps = [src, simlib, os.path.join(ROOT, "include", "El.hpp"), os.path.join(ROOT, "include", "elb200.h")]
+        if not os.path.exists(exe) or any(os.path.getmtime(d) > os.path.getmtime(exe) for d in deps):
+            cuda_inc = os.environ.get("CUDA_HOME", "/usr/local/cuda") + "/include"
+            r = subprocess.run(["g++", "-std=c++17", "-O1", "-I" + os.path.join(ROOT, "include"), "-I" + cuda_inc, "-o", exe, src,
+                                simlib, "-Wl,-rpath," + out_dir, "-pthread"], capture_output=True, text=True)
+            assert r.returncode == 0, r.stderr[-3000:]
+        r = subprocess.run([exe] + args, capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0 and "_PASS" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
