@@ -31,6 +31,9 @@ DIST_NAMES = {MC: "MC", MR: "MR", VC: "VC", VR: "VR", STAR: "STAR", CIRC: "CIRC"
 (GEMM_DEFAULT, GEMM_SUMMA_A_MS, GEMM_SUMMA_A, GEMM_SUMMA_B_MS, GEMM_SUMMA_B, GEMM_SUMMA_C_MS, GEMM_SUMMA_C,
  GEMM_SUMMA_DOT, GEMM_CANNON) = range(9)
 PACK, UNPACK, UNPACK_AXPY = 0, 1, 2
+LOWER, UPPER = 0, 1  # El::UpperOrLower
+LEFT, RIGHT = 0, 1   # El::LeftOrRight
+TRAP_SCALE, TRAP_AXPY, TRAP_MAKE = 0, 1, 2
 
 i64 = C.c_int64
 
@@ -100,6 +103,8 @@ SIGNATURES = {
     "elb200_lattice_f64": (ci, [ci, ci, C.POINTER(Segment), vp, i64, vp, f64, vp]),
     "elb200_peer_reduce_axpy_f32": (ci, [ci, C.POINTER(vp), i64, C.POINTER(Segment), vp, i64, f32, vp]),
     "elb200_peer_reduce_axpy_f64": (ci, [ci, C.POINTER(vp), i64, C.POINTER(Segment), vp, i64, f64, vp]),
+    "elb200_trapezoid_f32": (ci, [ci, ci, i64, i64, i64, i64, i64, i64, i64, f32, vp, i64, vp, i64, vp]),
+    "elb200_trapezoid_f64": (ci, [ci, ci, i64, i64, i64, i64, i64, i64, i64, f64, vp, i64, vp, i64, vp]),
     "elb200_plan_copy": (ci, [ci, ci, ci, C.POINTER(DistSpec), C.POINTER(DistSpec), C.POINTER(CopyPlan)]),
     "elb200_plan_contract": (ci, [ci, ci, ci, C.POINTER(DistSpec), C.POINTER(DistSpec), C.POINTER(ContractPlan)]),
     "elb200_plan_send_offset": (i64, [ci, ci, ci, C.POINTER(DistSpec), C.POINTER(DistSpec), ci]),
@@ -143,6 +148,16 @@ SIGNATURES = {
     "elb200_dm_transpose_axpy_contract": (ci, [f64, vp, vp]),
     "elb200_dm_local_gemm": (ci, [ci, ci, f64, vp, vp, f64, vp]),
     "elb200_dist_gemm": (ci, [ci, ci, f64, vp, vp, f64, vp, ci]),
+    "elb200_local_trrk_blocksize": (i64, []),
+    "elb200_set_local_trrk_blocksize": (None, [i64]),
+    "elb200_dm_scale_trapezoid": (ci, [f64, ci, vp, i64]),
+    "elb200_dm_axpy_trapezoid": (ci, [ci, f64, vp, vp, i64]),
+    "elb200_dm_make_trapezoidal": (ci, [ci, vp, i64]),
+    "elb200_dm_make_symmetric": (ci, [ci, vp]),
+    "elb200_dm_local_trrk": (ci, [ci, ci, ci, f64, vp, vp, f64, vp]),
+    "elb200_dist_trrk": (ci, [ci, ci, ci, f64, vp, vp, f64, vp]),
+    "elb200_dist_syrk": (ci, [ci, ci, f64, vp, f64, vp]),
+    "elb200_dist_symm": (ci, [ci, ci, f64, vp, vp, f64, vp]),
     "elb200_dist_gemm_host_f32": (ci, [vp, ci, ci, i64, i64, i64, f32, vp, i64, vp, i64, f32, vp, i64]),
     "elb200_dist_gemm_host_f64": (ci, [vp, ci, ci, i64, i64, i64, f64, vp, i64, vp, i64, f64, vp, i64]),
 }

@@ -7,6 +7,7 @@
 //   src/hydrogen/blas/gpu/{Copy,Axpy,Scale,Fill,Transpose}.cu and the cublas?geam calls in
 //   include/hydrogen/blas/GPU_BLAS_impl.hpp:110-198,254-273.
 #include <cuda_runtime.h>
+#include <algorithm>
 #include <cstdint>
 #include <type_traits>
 
@@ -483,6 +484,65 @@ int peer_reduce_axpy(int nsrc, const T* const* srcs, int64_t off, const elb200_s
     return check_cuda(cudaGetLastError(), "peer_reduce_axpy_kernel");
 }
 
+// Trapezoid-masked entrywise ops on the LOCAL part of an element-cyclic matrix: local (i,j) is global
+// (row0 + i*row_step, col0 + j*col_step); the op touches the entries inside (SCALE, AXPY) or outside
+// (MAKE: zero them) the trapezoid  LOWER: gi >= gj - offset,  UPPER: gi <= gj - offset.
+// Replaces the host loops of ScaleTrapezoid / AxpyTrapezoid / LocalAxpyTrapezoid / MakeTrapezoidal
+// (include/El/blas_like/level1/{ScaleTrapezoid,AxpyTrapezoid,MakeTrapezoidal}.hpp), which the
+// reference runs per column on the CPU.  Threads run down the columns (coalesced); entries on the
+// other side of the boundary are neither read nor written.
+enum : int { TRAP_SCALE = 0, TRAP_AXPY = 1, TRAP_MAKE = 2 };
+template <typename T, int OP>
+__global__ void __launch_bounds__(256)
+trapezoid_kernel(int64_t rows, int64_t cols, int upper, int64_t offset, int64_t row0, int64_t row_step, int64_t col0,
+                 int64_t col_step, T alpha, const T* __restrict__ X, int64_t ldx, T* Y, int64_t ldy) {
+    const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= rows) return;
+    const int64_t gi = row0 + i * row_step;
+    for (int64_t j = int64_t(blockIdx.y) * blockDim.y + threadIdx.y; j < cols; j += int64_t(gridDim.y) * blockDim.y) {
+        const int64_t gj = col0 + j * col_step;
+        const bool inside = upper ? (gi <= gj - offset) : (gi >= gj - offset);
+        T* y = Y + i + j * ldy;
+        if constexpr (OP == TRAP_SCALE) {
+            if (inside) *y = alpha == T(0) ? T(0) : alpha * *y;
+        } else if constexpr (OP == TRAP_AXPY) {
+            if (inside) *y = fma(alpha, X[i + j * ldx], *y);
+        } else {
+            if (!inside) *y = T(0);
+        }
+    }
+}
+
+template <typename T>
+int launch_trapezoid(int op, int uplo, int64_t offset, int64_t rows, int64_t cols, int64_t row0, int64_t row_step,
+                     int64_t col0, int64_t col_step, T alpha, const T* X, int64_t ldx, T* Y, int64_t ldy, void* stream) {
+    if (op < TRAP_SCALE || op > TRAP_MAKE || uplo < 0 || uplo > 1 || rows < 0 || cols < 0 || row_step < 1 || col_step < 1 ||
+        row0 < 0 || col0 < 0)
+        return ELB200_ERR_ARG;
+    if (rows == 0 || cols == 0) return ELB200_OK;
+    if (!Y || ldy < rows || (op == TRAP_AXPY && (!X || ldx < rows))) return ELB200_ERR_ARG;
+    if (op == TRAP_SCALE && alpha == T(1)) return ELB200_OK;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    int bx = 32;
+    while (bx < 256 && bx < rows) bx <<= 1;
+    const int by = 256 / bx;
+    const int64_t gx = (rows + bx - 1) / bx;
+    int64_t gy = (cols + by - 1) / by;
+    const int64_t want = std::max<int64_t>(1, 32 * int64_t(device_sm_count()) / gx);  // enough CTAs to fill the SMs, grid-stride beyond
+    if (gy > want) gy = want;
+    if (gy > 65535) gy = 65535;
+    const dim3 grid(static_cast<unsigned>(gx), static_cast<unsigned>(gy)), block(bx, by);
+    const int upper = uplo == 1;
+    count_launch();
+    if (op == TRAP_SCALE)
+        trapezoid_kernel<T, TRAP_SCALE><<<grid, block, 0, s>>>(rows, cols, upper, offset, row0, row_step, col0, col_step, alpha, X, ldx, Y, ldy);
+    else if (op == TRAP_AXPY)
+        trapezoid_kernel<T, TRAP_AXPY><<<grid, block, 0, s>>>(rows, cols, upper, offset, row0, row_step, col0, col_step, alpha, X, ldx, Y, ldy);
+    else
+        trapezoid_kernel<T, TRAP_MAKE><<<grid, block, 0, s>>>(rows, cols, upper, offset, row0, row_step, col0, col_step, alpha, X, ldx, Y, ldy);
+    return check_cuda(cudaGetLastError(), "trapezoid_kernel");
+}
+
 template <typename T>
 int copy2d(int64_t rows, int64_t cols, const T* src, int64_t srs, int64_t scs, T* dst, int64_t drs,
            int64_t dcs, void* stream) {
@@ -591,6 +651,17 @@ int elb200_lattice_f64(int mode, int nseg, const elb200_segment* segs, double* M
                        double* buf, double alpha, void* stream) {
     return launch_lattice<double>(mode, nseg, segs, M, ldm, buf, alpha,
                                   static_cast<cudaStream_t>(stream));
+}
+
+int elb200_trapezoid_f32(int op, int uplo, int64_t offset, int64_t rows, int64_t cols, int64_t row0, int64_t row_step,
+                         int64_t col0, int64_t col_step, float alpha, const float* X, int64_t ldx, float* Y, int64_t ldy,
+                         void* stream) {
+    return launch_trapezoid<float>(op, uplo, offset, rows, cols, row0, row_step, col0, col_step, alpha, X, ldx, Y, ldy, stream);
+}
+int elb200_trapezoid_f64(int op, int uplo, int64_t offset, int64_t rows, int64_t cols, int64_t row0, int64_t row_step,
+                         int64_t col0, int64_t col_step, double alpha, const double* X, int64_t ldx, double* Y, int64_t ldy,
+                         void* stream) {
+    return launch_trapezoid<double>(op, uplo, offset, rows, cols, row0, row_step, col0, col_step, alpha, X, ldx, Y, ldy, stream);
 }
 
 }  // extern "C"

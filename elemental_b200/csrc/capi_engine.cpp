@@ -195,6 +195,8 @@ int elb200_blocksize(void) { return Grid::Blocksize(); }
 void elb200_set_blocksize(int nb) { Grid::SetBlocksize(nb); }
 void elb200_push_blocksize(int nb) { Grid::PushBlocksize(nb); }
 void elb200_pop_blocksize(void) { Grid::PopBlocksize(); }
+int64_t elb200_local_trrk_blocksize(void) { return Grid::LocalTrrkBlocksize(); }
+void elb200_set_local_trrk_blocksize(int64_t nb) { Grid::SetLocalTrrkBlocksize(nb); }
 
 int elb200_dm_create(elb200_grid_t g, int dtype, int col, int row, elb200_dm_t* out) {
     if (!g || !out || (dtype != ELB200_F32 && dtype != ELB200_F64)) return ELB200_ERR_ARG;
@@ -322,6 +324,51 @@ int elb200_dist_gemm_host_f64(elb200_grid_t g, int ta, int tb, int64_t m, int64_
                               int64_t ldc) {
     if (!g || ta < 0 || ta > 2 || tb < 0 || tb > 2) return ELB200_ERR_ARG;
     return guarded("elb200_dist_gemm_host_f64", [&] { GemmHost<double>(*g->g, ta, tb, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc); });
+}
+
+// ---- triangular rank-k family (engine_level3.cpp) ---------------------------------------------------
+int elb200_dm_scale_trapezoid(double alpha, int uplo, elb200_dm_t A, int64_t offset) {
+    if (!A) return ELB200_ERR_ARG;
+    return guarded("elb200_dm_scale_trapezoid", [&] { ELB_ON(A, ScaleTrapezoid(float(alpha), uplo, M, offset), ScaleTrapezoid(alpha, uplo, M, offset)); });
+}
+int elb200_dm_make_trapezoidal(int uplo, elb200_dm_t A, int64_t offset) {
+    if (!A) return ELB200_ERR_ARG;
+    return guarded("elb200_dm_make_trapezoidal", [&] { ELB_ON(A, MakeTrapezoidal(uplo, M, offset), MakeTrapezoidal(uplo, M, offset)); });
+}
+int elb200_dm_make_symmetric(int uplo, elb200_dm_t A) {
+    if (!A) return ELB200_ERR_ARG;
+    return guarded("elb200_dm_make_symmetric", [&] { ELB_ON(A, MakeSymmetric(uplo, M), MakeSymmetric(uplo, M)); });
+}
+int elb200_dm_axpy_trapezoid(int uplo, double alpha, elb200_dm_t A, elb200_dm_t B, int64_t offset) {
+    ELB_BINARY("elb200_dm_axpy_trapezoid", AxpyTrapezoid(uplo, float(alpha), *A->f, *B->f, offset), AxpyTrapezoid(uplo, alpha, *A->d, *B->d, offset))
+}
+int elb200_dm_local_trrk(int uplo, int ta, int tb, double alpha, elb200_dm_t A, elb200_dm_t B, double beta, elb200_dm_t C) {
+    if (!same_dtype(A, B) || !same_dtype(A, C) || ta < 0 || ta > 2 || tb < 0 || tb > 2) return ELB200_ERR_ARG;
+    return guarded("elb200_dm_local_trrk", [&] {
+        if (A->dtype == ELB200_F32) LocalTrrk(uplo, ta, tb, float(alpha), *A->f, *B->f, float(beta), *C->f);
+        else LocalTrrk(uplo, ta, tb, alpha, *A->d, *B->d, beta, *C->d);
+    });
+}
+int elb200_dist_trrk(int uplo, int ta, int tb, double alpha, elb200_dm_t A, elb200_dm_t B, double beta, elb200_dm_t C) {
+    if (!same_dtype(A, B) || !same_dtype(A, C) || ta < 0 || ta > 2 || tb < 0 || tb > 2) return ELB200_ERR_ARG;
+    return guarded("elb200_dist_trrk", [&] {
+        if (A->dtype == ELB200_F32) Trrk(uplo, ta, tb, float(alpha), *A->f, *B->f, float(beta), *C->f);
+        else Trrk(uplo, ta, tb, alpha, *A->d, *B->d, beta, *C->d);
+    });
+}
+int elb200_dist_syrk(int uplo, int trans, double alpha, elb200_dm_t A, double beta, elb200_dm_t C) {
+    if (!same_dtype(A, C) || trans < 0 || trans > 2) return ELB200_ERR_ARG;
+    return guarded("elb200_dist_syrk", [&] {
+        if (A->dtype == ELB200_F32) Syrk(uplo, trans, float(alpha), *A->f, float(beta), *C->f);
+        else Syrk(uplo, trans, alpha, *A->d, beta, *C->d);
+    });
+}
+int elb200_dist_symm(int side, int uplo, double alpha, elb200_dm_t A, elb200_dm_t B, double beta, elb200_dm_t C) {
+    if (!same_dtype(A, B) || !same_dtype(A, C)) return ELB200_ERR_ARG;
+    return guarded("elb200_dist_symm", [&] {
+        if (A->dtype == ELB200_F32) Symm(side, uplo, float(alpha), *A->f, *B->f, float(beta), *C->f);
+        else Symm(side, uplo, alpha, *A->d, *B->d, beta, *C->d);
+    });
 }
 
 }  // extern "C"

@@ -66,6 +66,10 @@ public:
     static void SetBlocksize(int nb);
     static void PushBlocksize(int nb);
     static void PopBlocksize();
+    // LocalTrrk recursion cut-off (reference LocalTrrkBlocksize<T> / SetLocalTrrkBlocksize<T>,
+    // src/blas_like/blocksizes.cpp:82-87); default 2048 here, see engine_level3.cpp.
+    static int64_t LocalTrrkBlocksize();
+    static void SetLocalTrrkBlocksize(int64_t nb);
     // Internal SUMMA_C/A/B panel width: several algorithmic blocks are moved and multiplied per
     // step so that one pass over the local C amortises >= this many k.
     static int64_t PanelWidth(int elem_bytes);
@@ -136,6 +140,22 @@ void Gemm(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, T b
 template <typename T>
 void GemmHost(Grid& g, int ta, int tb, int64_t m, int64_t n, int64_t k, T alpha, const T* A, int64_t lda,
               const T* B, int64_t ldb, T beta, T* C, int64_t ldc);
+// ---- triangular rank-k family (reference src/blas_like/level3/{Trrk,Syrk,Herk,Symm,Hemm}.cpp) -----
+// uplo: 0 = LOWER, 1 = UPPER (El::UpperOrLower); side: 0 = LEFT, 1 = RIGHT (El::LeftOrRight).
+template <typename T> void ScaleTrapezoid(T alpha, int uplo, DistMat<T>& A, int64_t offset);
+template <typename T> void AxpyTrapezoid(int uplo, T alpha, const DistMat<T>& X, DistMat<T>& Y, int64_t offset);
+template <typename T> void MakeTrapezoidal(int uplo, DistMat<T>& A, int64_t offset);
+template <typename T> void MakeSymmetric(int uplo, DistMat<T>& A);
+template <typename T>
+void LocalTrrk(int uplo, int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, T beta, DistMat<T>& C);
+template <typename T>
+void Trrk(int uplo, int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, T beta, DistMat<T>& C);
+template <typename T> void Syrk(int uplo, int trans, T alpha, const DistMat<T>& A, T beta, DistMat<T>& C);
+template <typename T>
+void Symm(int side, int uplo, T alpha, const DistMat<T>& A, const DistMat<T>& B, T beta, DistMat<T>& C);
+// src redistributed like tmp's distribution, aligned with `like`; returns src itself when that
+// redistribution is the identity on every rank (engine_gemm.cpp).
+template <typename T> const DistMat<T>& PanelAs(const DistMat<T>& src, DistMat<T>& tmp, const DistSpec& like);
 // Which SUMMA variant GEMM_DEFAULT resolves to (reference Gemm/NN.hpp:585-600 and twins).
 int ResolveGemmAlg(int ta, int tb, int64_t m, int64_t n, int64_t k, int alg);
 void GemmProfileEnable(bool on);

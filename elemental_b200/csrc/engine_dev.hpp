@@ -45,6 +45,10 @@ template <> struct Dev<float> {
                                  int64_t ldm, float al, cudaStream_t s) {
         throw_status(elb200_peer_reduce_axpy_f32(nsrc, srcs, off, seg, M, ldm, al, s), "elb200_peer_reduce_axpy_f32");
     }
+    static void trapezoid(int op, int uplo, int64_t offset, int64_t r, int64_t c, int64_t row0, int64_t rstep, int64_t col0,
+                          int64_t cstep, float al, const float* X, int64_t ldx, float* Y, int64_t ldy, cudaStream_t s) {
+        throw_status(elb200_trapezoid_f32(op, uplo, offset, r, c, row0, rstep, col0, cstep, al, X, ldx, Y, ldy, s), "elb200_trapezoid_f32");
+    }
 };
 
 template <> struct Dev<double> {
@@ -81,6 +85,10 @@ template <> struct Dev<double> {
     static void peer_reduce_axpy(int nsrc, const double* const* srcs, int64_t off, const elb200_segment* seg, double* M,
                                  int64_t ldm, double al, cudaStream_t s) {
         throw_status(elb200_peer_reduce_axpy_f64(nsrc, srcs, off, seg, M, ldm, al, s), "elb200_peer_reduce_axpy_f64");
+    }
+    static void trapezoid(int op, int uplo, int64_t offset, int64_t r, int64_t c, int64_t row0, int64_t rstep, int64_t col0,
+                          int64_t cstep, double al, const double* X, int64_t ldx, double* Y, int64_t ldy, cudaStream_t s) {
+        throw_status(elb200_trapezoid_f64(op, uplo, offset, r, c, row0, rstep, col0, cstep, al, X, ldx, Y, ldy, s), "elb200_trapezoid_f64");
     }
 };
 

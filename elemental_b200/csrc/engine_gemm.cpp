@@ -546,6 +546,11 @@ void GemmHost(Grid& g, int ta, int tb, int64_t m, int64_t n, int64_t k, T alpha,
     cuda_check(cudaStreamSynchronize(cs), "GemmHost: comm");
 }
 
+template <typename T>
+const DistMat<T>& PanelAs(const DistMat<T>& src, DistMat<T>& tmp, const DistSpec& like) { return panel_as(src, tmp, like); }
+template const DistMat<float>& PanelAs<float>(const DistMat<float>&, DistMat<float>&, const DistSpec&);
+template const DistMat<double>& PanelAs<double>(const DistMat<double>&, DistMat<double>&, const DistSpec&);
+
 template void LocalGemm<float>(int, int, float, const DistMat<float>&, const DistMat<float>&, float, DistMat<float>&);
 template void LocalGemm<double>(int, int, double, const DistMat<double>&, const DistMat<double>&, double, DistMat<double>&);
 template void Gemm<float>(int, int, float, const DistMat<float>&, const DistMat<float>&, float, DistMat<float>&, int);

@@ -105,11 +105,15 @@ void Copy(const DistMat<T>& A, DistMat<T>& B) {
     if (!g.world) throw EngineError(ELB200_ERR_STATE, "Copy: grid has no NCCL communicator");
     // NVLink pull (peer.hpp): every rank packs ITS sends straight into its own arena slot, signals,
     // and the receivers fetch their messages from the senders' slots with the copy engines — no
-    // NCCL kernels, no SMs during the transfer. Taken when the largest possible send staging
-    // (a whole local matrix of A) fits a slot, a bound every rank evaluates identically.
+    // NCCL kernels, no SMs during the transfer. Taken when the largest possible send staging fits a
+    // slot, by a bound every rank evaluates identically: a whole local matrix of A ...
     static const bool pull = [] { const char* e = std::getenv("ELB200_A2A_PULL"); return !e || std::atoi(e) != 0; }();
+    // ... times the number of ranks that hold a copy of each entry under B's distribution: a sender packs one
+    // message per destination, so towards a replicated target (e.g. [MC,MR] -> [MR,*]) its staging is that many
+    // times its local matrix.
+    const size_t copies = B.spec.col == CIRC ? 1 : size_t(g.size()) / (size_t(dist_stride(g.shape, B.spec.col)) * size_t(dist_stride(g.shape, B.spec.row)));
     const size_t max_local_a = size_t(MaxLength(A.spec.height, dist_stride(g.shape, A.spec.col))) *
-                               size_t(MaxLength(A.spec.width, dist_stride(g.shape, A.spec.row))) * sizeof(T);
+                               size_t(MaxLength(A.spec.width, dist_stride(g.shape, A.spec.row))) * sizeof(T) * std::max<size_t>(copies, 1);
     if (pull && g.arena && max_local_a <= g.arena->slot_bytes()) {
         const std::vector<int> members = g.comm_members(VC);
         const int idx = g.vc_rank;

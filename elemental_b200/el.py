@@ -283,6 +283,67 @@ def Gemm(orientA, orientB, alpha, A: DistMatrix, B: DistMatrix, beta, C_: DistMa
     check(lib.elb200_dist_gemm(orientA, orientB, alpha, A._h, B._h, beta, C_._h, alg), "Gemm")
 
 
+# ---- triangular rank-k family (include/El/blas_like/level3.hpp:92-126,239-252,292-313,499-536) ----
+LOWER, UPPER = 0, 1  # El::UpperOrLower (include/El/core/types.hpp:511-515)
+LEFT, RIGHT = 0, 1   # El::LeftOrRight  (types.hpp:418-422)
+
+
+def LocalTrrkBlocksize() -> int:
+    """El::LocalTrrkBlocksize<T> (src/blas_like/blocksizes.cpp:86-87); one value for both types here."""
+    return lib.elb200_local_trrk_blocksize()
+
+
+def SetLocalTrrkBlocksize(nb: int) -> None:
+    lib.elb200_set_local_trrk_blocksize(int(nb))
+
+
+def ScaleTrapezoid(alpha: float, uplo: int, A, offset: int = 0) -> None:
+    """include/El/blas_like/level1/ScaleTrapezoid.hpp:49-96."""
+    check(lib.elb200_dm_scale_trapezoid(alpha, uplo, A._h, offset), "ScaleTrapezoid")
+
+
+def AxpyTrapezoid(uplo: int, alpha: float, X, Y, offset: int = 0) -> None:
+    check(lib.elb200_dm_axpy_trapezoid(uplo, alpha, X._h, Y._h, offset), "AxpyTrapezoid")
+
+
+def MakeTrapezoidal(uplo: int, A, offset: int = 0) -> None:
+    check(lib.elb200_dm_make_trapezoidal(uplo, A._h, offset), "MakeTrapezoidal")
+
+
+def MakeSymmetric(uplo: int, A) -> None:
+    """level1/MakeSymmetric.hpp:56-73 (real types: MakeHermitian is the same)."""
+    check(lib.elb200_dm_make_symmetric(uplo, A._h), "MakeSymmetric")
+
+
+MakeHermitian = MakeSymmetric
+
+
+def LocalTrrk(uplo: int, orientA: int, orientB: int, alpha, A, B, beta, C_) -> None:
+    """Trrk/Local.hpp:688-890: triangle of C[MC,MR] = alpha op(A) op(B) + beta C on aligned panels."""
+    check(lib.elb200_dm_local_trrk(uplo, orientA, orientB, alpha, A._h, B._h, beta, C_._h), "LocalTrrk")
+
+
+def Trrk(uplo: int, orientA: int, orientB: int, alpha, A, B, beta, C_) -> None:
+    """src/blas_like/level3/Trrk.cpp:100-118."""
+    check(lib.elb200_dist_trrk(uplo, orientA, orientB, alpha, A._h, B._h, beta, C_._h), "Trrk")
+
+
+def Syrk(uplo: int, orientation: int, alpha, A, beta, C_) -> None:
+    """src/blas_like/level3/Syrk.cpp:172-190."""
+    check(lib.elb200_dist_syrk(uplo, orientation, alpha, A._h, beta, C_._h), "Syrk")
+
+
+Herk = Syrk  # real types (src/blas_like/level3/Herk.cpp: Syrk with conjugate = true)
+
+
+def Symm(side: int, uplo: int, alpha, A, B, beta, C_) -> None:
+    """src/blas_like/level3/Symm.cpp:56-80."""
+    check(lib.elb200_dist_symm(side, uplo, alpha, A._h, B._h, beta, C_._h), "Symm")
+
+
+Hemm = Symm
+
+
 def GemmHost(grid: "Grid", orientA, orientB, m: int, n: int, k: int, alpha, A: torch.Tensor, lda: int,
              B: torch.Tensor, ldb: int, beta, C_: torch.Tensor, ldc: int) -> None:
     """El::Gemm on HOST operands: A, B, C_ are CPU tensors (pinned recommended) holding this rank's

@@ -29,6 +29,8 @@ enum Dist { MC, MD, MR, VC, VR, STAR, CIRC };
 enum DistWrap { ELEMENT, BLOCK };
 enum Orientation { NORMAL, TRANSPOSE, ADJOINT };
 enum GridOrder { ROW_MAJOR, COLUMN_MAJOR };
+enum UpperOrLower { LOWER, UPPER };   // include/El/core/types.hpp:511-515
+enum LeftOrRight { LEFT, RIGHT };     // types.hpp:418-422
 // hydrogen::Device (include/hydrogen/Device.hpp): only GPU exists here — there is no CPU path
 enum class Device : unsigned char { CPU, GPU };
 enum GemmAlgorithm {
@@ -518,6 +520,98 @@ void LocalGemm(Orientation orientA, Orientation orientB, T alpha, const DistMatr
                const DistMatrix<T, UB, VB>& B, T beta, DistMatrix<T, UC, VC_>& C) {
     detail::Check(elb200_dm_local_gemm(int(orientA), int(orientB), double(alpha), A.Handle(), B.Handle(), double(beta),
                                        C.Handle()), "LocalGemm");
+}
+
+// ---------------------------------------------------------------------------------------------
+// Triangular rank-k family (include/El/blas_like/level3.hpp:92-126,239-252,292-313,499-536 and the
+// level-1 trapezoid routines).  conjugate / ADJOINT equal the plain forms for the real types here.
+// ---------------------------------------------------------------------------------------------
+template <typename T> Int LocalTrrkBlocksize() { return Int(elb200_local_trrk_blocksize()); }
+template <typename T> void SetLocalTrrkBlocksize(Int blocksize) { elb200_set_local_trrk_blocksize(blocksize); }
+
+template <typename T, typename S, Dist U, Dist V>
+void ScaleTrapezoid(S alpha, UpperOrLower uplo, DistMatrix<T, U, V>& A, Int offset = 0) {
+    detail::Check(elb200_dm_scale_trapezoid(double(alpha), int(uplo), A.Handle(), offset), "ScaleTrapezoid");
+}
+template <typename T, typename S, Dist U, Dist V, Dist U2, Dist V2>
+void AxpyTrapezoid(UpperOrLower uplo, S alpha, const DistMatrix<T, U, V>& X, DistMatrix<T, U2, V2>& Y, Int offset = 0) {
+    detail::Check(elb200_dm_axpy_trapezoid(int(uplo), double(alpha), X.Handle(), Y.Handle(), offset), "AxpyTrapezoid");
+}
+template <typename T, Dist U, Dist V>
+void MakeTrapezoidal(UpperOrLower uplo, DistMatrix<T, U, V>& A, Int offset = 0) {
+    detail::Check(elb200_dm_make_trapezoidal(int(uplo), A.Handle(), offset), "MakeTrapezoidal");
+}
+template <typename T, Dist U, Dist V>
+void MakeSymmetric(UpperOrLower uplo, DistMatrix<T, U, V>& A, bool /*conjugate*/ = false) {
+    detail::Check(elb200_dm_make_symmetric(int(uplo), A.Handle()), "MakeSymmetric");
+}
+template <typename T, Dist U, Dist V>
+void MakeHermitian(UpperOrLower uplo, DistMatrix<T, U, V>& A) { MakeSymmetric(uplo, A, true); }
+
+// triangle of C := alpha op(A) op(B) + beta C  (Trrk.cpp:100-118)
+template <typename T, Dist UA, Dist VA, Dist UB, Dist VB, Dist UC, Dist VC_>
+void Trrk(UpperOrLower uplo, Orientation orientA, Orientation orientB, T alpha, const DistMatrix<T, UA, VA>& A,
+          const DistMatrix<T, UB, VB>& B, T beta, DistMatrix<T, UC, VC_>& C) {
+    detail::Check(elb200_dist_trrk(int(uplo), int(orientA), int(orientB), double(alpha), A.Handle(), B.Handle(), double(beta),
+                                   C.Handle()), "Trrk");
+}
+// The four LocalTrrk overloads (level3.hpp:513-536; Trrk/Local.hpp:688-890): panels aligned with C.
+template <typename T>
+void LocalTrrk(UpperOrLower uplo, T alpha, const DistMatrix<T, MC, STAR>& A, const DistMatrix<T, STAR, MR>& B, T beta,
+               DistMatrix<T, MC, MR>& C) {
+    detail::Check(elb200_dm_local_trrk(int(uplo), 0, 0, double(alpha), A.Handle(), B.Handle(), double(beta), C.Handle()), "LocalTrrk");
+}
+template <typename T>
+void LocalTrrk(UpperOrLower uplo, Orientation orientB, T alpha, const DistMatrix<T, MC, STAR>& A,
+               const DistMatrix<T, MR, STAR>& B, T beta, DistMatrix<T, MC, MR>& C) {
+    if (orientB == NORMAL) throw std::logic_error("LocalTrrk: B must be (Conjugate)Transpose'd");  // Local.hpp:74-75
+    detail::Check(elb200_dm_local_trrk(int(uplo), 0, 1, double(alpha), A.Handle(), B.Handle(), double(beta), C.Handle()), "LocalTrrk");
+}
+template <typename T>
+void LocalTrrk(UpperOrLower uplo, Orientation orientA, T alpha, const DistMatrix<T, STAR, MC>& A,
+               const DistMatrix<T, STAR, MR>& B, T beta, DistMatrix<T, MC, MR>& C) {
+    if (orientA == NORMAL) throw std::logic_error("LocalTrrk: A must be (Conjugate)Transpose'd");  // Local.hpp:89-90
+    detail::Check(elb200_dm_local_trrk(int(uplo), 1, 0, double(alpha), A.Handle(), B.Handle(), double(beta), C.Handle()), "LocalTrrk");
+}
+template <typename T>
+void LocalTrrk(UpperOrLower uplo, Orientation orientA, Orientation orientB, T alpha, const DistMatrix<T, STAR, MC>& A,
+               const DistMatrix<T, MR, STAR>& B, T beta, DistMatrix<T, MC, MR>& C) {
+    if (orientA == NORMAL || orientB == NORMAL) throw std::logic_error("LocalTrrk: A and B must be (Conjugate)Transpose'd");
+    detail::Check(elb200_dm_local_trrk(int(uplo), 1, 1, double(alpha), A.Handle(), B.Handle(), double(beta), C.Handle()), "LocalTrrk");
+}
+// triangle of C := alpha A A^T + beta C (NORMAL) or alpha A^T A + beta C  (Syrk.cpp:172-190)
+template <typename T, Dist UA, Dist VA, Dist UC, Dist VC_>
+void Syrk(UpperOrLower uplo, Orientation orientation, T alpha, const DistMatrix<T, UA, VA>& A, T beta,
+          DistMatrix<T, UC, VC_>& C, bool /*conjugate*/ = false) {
+    detail::Check(elb200_dist_syrk(int(uplo), int(orientation), double(alpha), A.Handle(), double(beta), C.Handle()), "Syrk");
+}
+// C resized to n x n and zeroed first (Syrk.cpp:192-203)
+template <typename T, Dist UA, Dist VA, Dist UC, Dist VC_>
+void Syrk(UpperOrLower uplo, Orientation orientation, T alpha, const DistMatrix<T, UA, VA>& A, DistMatrix<T, UC, VC_>& C,
+          bool conjugate = false) {
+    const Int n = orientation == NORMAL ? A.Height() : A.Width();
+    C.Resize(n, n);
+    Zero(C);
+    Syrk(uplo, orientation, alpha, A, T(0), C, conjugate);
+}
+template <typename T, Dist UA, Dist VA, Dist UC, Dist VC_>
+void Herk(UpperOrLower uplo, Orientation orientation, T alpha, const DistMatrix<T, UA, VA>& A, T beta, DistMatrix<T, UC, VC_>& C) {
+    Syrk(uplo, orientation, alpha, A, beta, C, true);
+}
+template <typename T, Dist UA, Dist VA, Dist UC, Dist VC_>
+void Herk(UpperOrLower uplo, Orientation orientation, T alpha, const DistMatrix<T, UA, VA>& A, DistMatrix<T, UC, VC_>& C) {
+    Syrk(uplo, orientation, alpha, A, C, true);
+}
+// C := alpha A B + beta C (LEFT) or alpha B A + beta C (RIGHT), A symmetric, `uplo` triangle referenced (Symm.cpp:56-80)
+template <typename T, Dist UA, Dist VA, Dist UB, Dist VB, Dist UC, Dist VC_>
+void Symm(LeftOrRight side, UpperOrLower uplo, T alpha, const DistMatrix<T, UA, VA>& A, const DistMatrix<T, UB, VB>& B, T beta,
+          DistMatrix<T, UC, VC_>& C, bool /*conjugate*/ = false) {
+    detail::Check(elb200_dist_symm(int(side), int(uplo), double(alpha), A.Handle(), B.Handle(), double(beta), C.Handle()), "Symm");
+}
+template <typename T, Dist UA, Dist VA, Dist UB, Dist VB, Dist UC, Dist VC_>
+void Hemm(LeftOrRight side, UpperOrLower uplo, T alpha, const DistMatrix<T, UA, VA>& A, const DistMatrix<T, UB, VB>& B, T beta,
+          DistMatrix<T, UC, VC_>& C) {
+    Symm(side, uplo, alpha, A, B, beta, C, true);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -176,6 +176,28 @@ int elb200_peer_reduce_axpy_f64(int nsrc, const double* const* srcs, int64_t src
                                 void* stream);
 
 
+/* Trapezoid-masked entrywise ops on the LOCAL part of an element-cyclic matrix. Local entry (i,j) of
+ * the rows x cols column-major block Y is global entry (row0 + i*row_step, col0 + j*col_step); with
+ * uplo = ELB200_LOWER the trapezoid is { gi >= gj - offset }, with ELB200_UPPER { gi <= gj - offset }
+ * (the reference's convention: offset 0 includes the diagonal, UPPER with offset 1 / LOWER with
+ * offset -1 are the strict triangles).
+ *   op ELB200_TRAP_SCALE: Y *= alpha inside the trapezoid (alpha == 0 writes exact zeros)
+ *   op ELB200_TRAP_AXPY : Y += alpha * X inside the trapezoid (X: same local shape, ldx)
+ *   op ELB200_TRAP_MAKE : Y = 0 OUTSIDE the trapezoid
+ * Replaces the per-column host loops of ScaleTrapezoid, AxpyTrapezoid / LocalAxpyTrapezoid and
+ * MakeTrapezoidal (include/El/blas_like/level1/ScaleTrapezoid.hpp:49-96, AxpyTrapezoid.hpp,
+ * MakeTrapezoidal.hpp:45-86) as used by LocalTrrk (src/blas_like/level3/Trrk/Local.hpp:350-396),
+ * Syrk (src/blas_like/level3/Syrk.cpp:172-190) and MakeSymmetric (level1/MakeSymmetric.hpp:56-73). */
+typedef enum elb200_uplo { ELB200_LOWER = 0, ELB200_UPPER = 1 } elb200_uplo;   /* El::UpperOrLower */
+typedef enum elb200_side { ELB200_LEFT = 0, ELB200_RIGHT = 1 } elb200_side;    /* El::LeftOrRight  */
+typedef enum elb200_trap_op { ELB200_TRAP_SCALE = 0, ELB200_TRAP_AXPY = 1, ELB200_TRAP_MAKE = 2 } elb200_trap_op;
+int elb200_trapezoid_f32(int op, int uplo, int64_t offset, int64_t rows, int64_t cols, int64_t row0,
+                         int64_t row_step, int64_t col0, int64_t col_step, float alpha, const float* X,
+                         int64_t ldx, float* Y, int64_t ldy, void* stream);
+int elb200_trapezoid_f64(int op, int uplo, int64_t offset, int64_t rows, int64_t cols, int64_t row0,
+                         int64_t row_step, int64_t col0, int64_t col_step, double alpha, const double* X,
+                         int64_t ldx, double* Y, int64_t ldy, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Redistribution planner (pure host code; callable without a GPU).
  * For an r x c grid (COLUMN_MAJOR: VC rank = mc + r*mr, reference src/core/Grid.cpp:147-148) and
@@ -328,6 +350,37 @@ int elb200_dm_local_gemm(int transA, int transB, double alpha, elb200_dm_t A, el
  *      as in Gemm/NN.hpp:30-31). */
 int elb200_dist_gemm(int transA, int transB, double alpha, elb200_dm_t A, elb200_dm_t B,
                      double beta, elb200_dm_t C, int alg);
+
+/* ------------------------------------------------------------------------------------------
+ * Triangular rank-k family built from the same blocks: panel AllGathers, LocalGemm
+ * and the trapezoid kernels above. uplo / side are El::UpperOrLower / El::LeftOrRight values.
+ *   ScaleTrapezoid / AxpyTrapezoid / MakeTrapezoidal / MakeSymmetric
+ *       (include/El/blas_like/level1/{ScaleTrapezoid,AxpyTrapezoid,MakeTrapezoidal,MakeSymmetric}.hpp)
+ *   LocalTrrk: triangle of C[MC,MR] += alpha op(A) op(B), A = [MC,*] (N) or [*,MC] (T), B = [*,MR] (N)
+ *       or [MR,*] (T), aligned with C (src/blas_like/level3/Trrk/Local.hpp:688-890; the GPU
+ *       instantiation Trrk.cpp:117-176 is the (T,N) case)
+ *   Trrk : triangle of C = alpha op(A) op(B) + beta C        (src/blas_like/level3/Trrk.cpp:100-118)
+ *   Syrk / Herk (real): triangle of C = alpha A A^T + beta C (N) or alpha A^T A + beta C (T)
+ *       (src/blas_like/level3/Syrk.cpp:172-190, Herk.cpp)
+ *   Symm / Hemm (real): C = alpha A B + beta C (LEFT) or alpha B A + beta C (RIGHT), A symmetric with
+ *       only its `uplo` triangle referenced (src/blas_like/level3/Symm.cpp:56-80, Hemm.cpp)
+ * Entries of C outside the triangle are never read or written by Trrk / Syrk.
+ * ---------------------------------------------------------------------------------------- */
+/* El::LocalTrrkBlocksize<T> / SetLocalTrrkBlocksize<T> (src/blas_like/blocksizes.cpp:82-87): LocalTrrk
+ * recurses while C.Height() > gridWidth * blocksize. One value for both types; default 2048. */
+int64_t elb200_local_trrk_blocksize(void);
+void elb200_set_local_trrk_blocksize(int64_t nb);
+int elb200_dm_scale_trapezoid(double alpha, int uplo, elb200_dm_t A, int64_t offset);
+int elb200_dm_axpy_trapezoid(int uplo, double alpha, elb200_dm_t X, elb200_dm_t Y, int64_t offset);
+int elb200_dm_make_trapezoidal(int uplo, elb200_dm_t A, int64_t offset);
+int elb200_dm_make_symmetric(int uplo, elb200_dm_t A);
+int elb200_dm_local_trrk(int uplo, int transA, int transB, double alpha, elb200_dm_t A, elb200_dm_t B,
+                         double beta, elb200_dm_t C);
+int elb200_dist_trrk(int uplo, int transA, int transB, double alpha, elb200_dm_t A, elb200_dm_t B,
+                     double beta, elb200_dm_t C);
+int elb200_dist_syrk(int uplo, int trans, double alpha, elb200_dm_t A, double beta, elb200_dm_t C);
+int elb200_dist_symm(int side, int uplo, double alpha, elb200_dm_t A, elb200_dm_t B, double beta,
+                     elb200_dm_t C);
 
 /* El::Gemm with every operand in HOST memory (the reference reaches this case through its
  * CPU<->GPU proxies, include/El/core/ProxyDevice.hpp + Matrix<T,GPU> = Matrix<T,CPU> copies,

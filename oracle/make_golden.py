@@ -78,6 +78,7 @@ def main() -> int:
                             H=np.array(H, dtype=np.int64))
     print(f"wrote {len(meta)} Gemm cases, {len(L)} index rows, {len(H)} grid heights to {OUT}")
     make_dist_golden()
+    make_level3_golden()
     return 0
 
 
@@ -132,5 +133,56 @@ def make_dist_golden() -> None:
     print(f"wrote multi-rank reference runs for grids {[f'{h}x{n // h}' for n, h in DIST_GRIDS]}")
 
 
+def _run_ranks(args, nproc: int, tag: str):
+    """Start `nproc` processes of gemm_ref over the shared-memory MPI stub and wait for them."""
+    shm = f"/dev/shm/elb_stub_{os.getpid()}_{tag}"
+    if os.path.exists(shm):
+        os.remove(shm)
+    procs = []
+    for q in range(nproc):
+        env = dict(os.environ, ELB_STUB_NP=str(nproc), ELB_STUB_RANK=str(q), ELB_STUB_SHM=shm, OPENBLAS_NUM_THREADS="1")
+        procs.append(subprocess.Popen([REF_BIN] + args, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True))
+    try:
+        for q, pr in enumerate(procs):
+            _, err = pr.communicate(timeout=300)
+            assert pr.returncode == 0, f"{tag} rank {q}: {err[-2000:]}"
+    finally:
+        for pr in procs:
+            if pr.poll() is None:
+                pr.kill()
+        if os.path.exists(shm):
+            os.remove(shm)
+
+
+LEVEL3_GRIDS = [(1, 1)] + DIST_GRIDS
+
+
+def make_level3_golden() -> None:
+    """The reference's triangular rank-k family run multi-rank (gemm_ref --level3-golden): ScaleTrapezoid,
+    MakeTrapezoidal, AxpyTrapezoid, MakeSymmetric, the four LocalTrrk overloads, Trrk, Syrk, Symm.
+    tests/golden/ref_level3.npz, per grid tag g and rank q:
+      {g}_q{q}_L    rows [kind uplo p1 p2 colAlign rowAlign colShift rowShift lh lw offset]
+                    kind 0 ScaleTrapezoid(-0.5) 1 MakeTrapezoidal 2 AxpyTrapezoid(2.0) (p1 = offset); 3 MakeSymmetric;
+                    4 LocalTrrk 5 Trrk (p1, p2 = orientation of A, B); 6 Syrk (p1 = orientation); 7 Symm (p1 = side)
+      {g}_q{q}_bin  float64 blob (column-major local results)
+    Inputs are LCG matrices (lcg_matrix) with seeds 7001 (A), 7002 (B), 7003 (C), 7004 (X); sizes and
+    scalars as in oracle/ref_build/gemm_ref.cpp::level3_golden."""
+    arrays = {}
+    for (nproc, height) in LEVEL3_GRIDS:
+        tag = f"r{height}c{nproc // height}"
+        with tempfile.TemporaryDirectory() as tmp:
+            _run_ranks(["--level3-golden", tmp, str(height)], nproc, "l3" + tag)
+            for q in range(nproc):
+                recs = [[int(x) for x in ln.split()[1:]] for ln in open(os.path.join(tmp, f"l3rank{q}.txt"))]
+                assert len(recs) == 12 + 6 + 2 + 8 + 8 + 4 + 4, (tag, q, len(recs))
+                arrays[f"{tag}_q{q}_L"] = np.array(recs, dtype=np.int64)
+                arrays[f"{tag}_q{q}_bin"] = np.fromfile(os.path.join(tmp, f"l3rank{q}.bin"), dtype=np.float64)
+    np.savez_compressed(os.path.join(OUT, "ref_level3.npz"), **arrays)
+    print(f"wrote level-3 reference runs for grids {[f'{h}x{n // h}' for n, h in LEVEL3_GRIDS]}")
+
+
 if __name__ == "__main__":
+    if "--level3-only" in sys.argv:
+        make_level3_golden()
+        sys.exit(0)
     sys.exit(main())

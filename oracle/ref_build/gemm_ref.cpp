@@ -5,6 +5,7 @@
 //   gemm_ref --bench f32|f64 n         time El::Gemm(NORMAL,NORMAL,0.5,A,B,-0.5,C,GEMM_SUMMA_C), nb=128
 //   gemm_ref --dist-golden <dir> <r>   multi-rank (ELB_STUB_NP processes): per-rank local matrices after all
 //                                      121 redistributions and 20 El::Gemm runs on an r x (NP/r) grid
+//   gemm_ref --level3-golden <dir> <r> multi-rank: per-rank outputs of the trapezoid routines, LocalTrrk, Trrk, Syrk, Symm
 //   gemm_ref --golden <dir>            write inputs + reference outputs of a fixed list of small
 //                                      cases (all orientations x GemmAlgorithm, ragged sizes) and
 //                                      tables of the index functions, as raw little-endian files
@@ -194,10 +195,148 @@ static void dist_golden(const std::string& dir, int gridHeight) {
             }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Triangular rank-k family, multi-rank like dist_golden: per-rank local outputs of
+// the reference's ScaleTrapezoid / MakeTrapezoidal / AxpyTrapezoid / MakeSymmetric, the four
+// LocalTrrk overloads, Trrk, Syrk and Symm.  Records "L kind uplo p1 p2 colAlign rowAlign colShift
+// rowShift lh lw offset" in <dir>/l3rank<q>.txt, blobs in <dir>/l3rank<q>.bin.
+// ---------------------------------------------------------------------------------------------
+template <typename DM>
+static void fill_dm_lcg(DM& A, Int h, Int w, unsigned seed) {
+    Matrix<double> G(h, w);
+    fill_lcg(G, seed);
+    A.Resize(h, w);
+    for (Int j = 0; j < A.LocalWidth(); ++j)
+        for (Int i = 0; i < A.LocalHeight(); ++i) A.SetLocal(i, j, G.Get(A.GlobalRow(i), A.GlobalCol(j)));
+}
+
+template <typename DM>
+static void l3_record(DistOut& out, int kind, int uplo, int p1, int p2, const DM& C) {
+    out.txt << "L " << kind << " " << uplo << " " << p1 << " " << p2 << " " << C.ColAlign() << " " << C.RowAlign() << " "
+            << C.ColShift() << " " << C.RowShift() << " " << C.LocalHeight() << " " << C.LocalWidth() << " " << out.offset << "\n";
+    out.blob(C.LockedMatrix());
+}
+
+static void level3_golden(const std::string& dir, int gridHeight) {
+    const int rank = mpi::Rank(mpi::COMM_WORLD);
+    const Grid g(mpi::NewWorldComm(), gridHeight);
+    DistOut out;
+    out.txt.open(dir + "/l3rank" + std::to_string(rank) + ".txt");
+    out.bin.open(dir + "/l3rank" + std::to_string(rank) + ".bin", std::ios::binary);
+    const UpperOrLower uplos[2] = {LOWER, UPPER};
+    const Orientation os[2] = {NORMAL, TRANSPOSE};
+    const Int ca = 1 % g.Height(), ra = 2 % g.Width();
+    // kinds 0-2: trapezoid level-1 routines on a 13 x 11 [MC,MR] matrix, offsets 0, 1, -2
+    const int offsets[3] = {0, 1, -2};
+    for (int u = 0; u < 2; ++u)
+        for (int oi = 0; oi < 3; ++oi) {
+            DistMatrix<double> A(g), X(g);
+            A.Align(ca, ra); X.Align(ca, ra);
+            fill_dm_lcg(A, 13, 11, 7001);
+            ScaleTrapezoid(-0.5, uplos[u], A, offsets[oi]);
+            l3_record(out, 0, u, offsets[oi], 0, A);
+            fill_dm_lcg(A, 13, 11, 7001);
+            MakeTrapezoidal(uplos[u], A, offsets[oi]);
+            l3_record(out, 1, u, offsets[oi], 0, A);
+        }
+    for (int u = 0; u < 2; ++u)
+        for (int oi = 0; oi < 3; ++oi) {
+            DistMatrix<double> A(g), X(g);
+            A.Align(ca, ra); X.Align(ca, ra);
+            fill_dm_lcg(A, 13, 13, 7001);
+            fill_dm_lcg(X, 13, 13, 7004);
+            // UPPER with a negative offset is skipped (+2 instead of -2): the reference's LocalAxpyTrapezoid does not
+            // clamp j+1-offset to the height (AxpyTrapezoid.hpp:78, unlike ScaleTrapezoid.hpp:74-75) and runs past
+            // the end of the local columns there — an upstream defect, not behaviour to reproduce
+            const int off = (u == 1 && offsets[oi] < 0) ? -offsets[oi] : offsets[oi];
+            AxpyTrapezoid(uplos[u], 2.0, X, A, off);
+            l3_record(out, 2, u, off, 0, A);
+        }
+    // kind 3: MakeSymmetric
+    for (int u = 0; u < 2; ++u) {
+        DistMatrix<double> A(g);
+        A.Align(ca, ra);
+        fill_dm_lcg(A, 13, 13, 7001);
+        MakeSymmetric(uplos[u], A);
+        l3_record(out, 3, u, 0, 0, A);
+    }
+    // kind 4: the four LocalTrrk overloads (Trrk/Local.hpp:688-890), alpha 2, beta 3, n 37, k 23
+    const Int n = 37, k = 23;
+    SetBlocksize(16);
+    SetLocalTrrkBlocksize<double>(4);
+    for (int u = 0; u < 2; ++u) {
+        {
+            DistMatrix<double> C(g); C.Align(ca, ra); fill_dm_lcg(C, n, n, 7003);
+            DistMatrix<double, MC, STAR> A(g); A.AlignWith(C); fill_dm_lcg(A, n, k, 7001);
+            DistMatrix<double, STAR, MR> B(g); B.AlignWith(C); fill_dm_lcg(B, k, n, 7002);
+            LocalTrrk(uplos[u], 2.0, A, B, 3.0, C);
+            l3_record(out, 4, u, 0, 0, C);
+        }
+        {
+            DistMatrix<double> C(g); C.Align(ca, ra); fill_dm_lcg(C, n, n, 7003);
+            DistMatrix<double, MC, STAR> A(g); A.AlignWith(C); fill_dm_lcg(A, n, k, 7001);
+            DistMatrix<double, MR, STAR> B(g); B.AlignWith(C); fill_dm_lcg(B, n, k, 7002);
+            LocalTrrk(uplos[u], TRANSPOSE, 2.0, A, B, 3.0, C);
+            l3_record(out, 4, u, 0, 1, C);
+        }
+        {
+            DistMatrix<double> C(g); C.Align(ca, ra); fill_dm_lcg(C, n, n, 7003);
+            DistMatrix<double, STAR, MC> A(g); A.AlignWith(C); fill_dm_lcg(A, k, n, 7001);
+            DistMatrix<double, STAR, MR> B(g); B.AlignWith(C); fill_dm_lcg(B, k, n, 7002);
+            LocalTrrk(uplos[u], TRANSPOSE, 2.0, A, B, 3.0, C);
+            l3_record(out, 4, u, 1, 0, C);
+        }
+        {
+            DistMatrix<double> C(g); C.Align(ca, ra); fill_dm_lcg(C, n, n, 7003);
+            DistMatrix<double, STAR, MC> A(g); A.AlignWith(C); fill_dm_lcg(A, k, n, 7001);
+            DistMatrix<double, MR, STAR> B(g); B.AlignWith(C); fill_dm_lcg(B, n, k, 7002);
+            LocalTrrk(uplos[u], TRANSPOSE, TRANSPOSE, 2.0, A, B, 3.0, C);
+            l3_record(out, 4, u, 1, 1, C);
+        }
+    }
+    // kind 5: Trrk, all orientations; kind 6: Syrk; kind 7: Symm.  [MC,MR] operands with alignments.
+    for (int u = 0; u < 2; ++u)
+        for (int ia = 0; ia < 2; ++ia)
+            for (int ib = 0; ib < 2; ++ib) {
+                DistMatrix<double> A(g), B(g), C(g);
+                A.Align(ca, 0); B.Align(0, ra); C.Align(ca, ra);
+                fill_dm_lcg(A, ia ? k : n, ia ? n : k, 7001);
+                fill_dm_lcg(B, ib ? n : k, ib ? k : n, 7002);
+                fill_dm_lcg(C, n, n, 7003);
+                Trrk(uplos[u], os[ia], os[ib], 2.0, A, B, 3.0, C);
+                l3_record(out, 5, u, ia, ib, C);
+            }
+    for (int u = 0; u < 2; ++u)
+        for (int it = 0; it < 2; ++it) {
+            DistMatrix<double> A(g), C(g);
+            A.Align(ca, 0); C.Align(0, ra);
+            fill_dm_lcg(A, it ? k : n, it ? n : k, 7001);
+            fill_dm_lcg(C, n, n, 7003);
+            Syrk(uplos[u], os[it], 2.0, A, 3.0, C);
+            l3_record(out, 6, u, it, 0, C);
+        }
+    const Int m2 = 29;
+    const LeftOrRight sides[2] = {LEFT, RIGHT};
+    for (int sd = 0; sd < 2; ++sd)
+        for (int u = 0; u < 2; ++u) {
+            DistMatrix<double> A(g), B(g), C(g);
+            A.Align(ca, ra); C.Align(0, ra);
+            fill_dm_lcg(A, n, n, 7001);
+            fill_dm_lcg(B, sd ? m2 : n, sd ? n : m2, 7002);
+            fill_dm_lcg(C, sd ? m2 : n, sd ? n : m2, 7003);
+            Symm(sides[sd], uplos[u], 2.0, A, B, 3.0, C);
+            l3_record(out, 7, u, sd, 0, C);
+        }
+}
+
 int main(int argc, char* argv[]) {
     Environment env(argc, argv);
     if (argc >= 4 && !std::strcmp(argv[1], "--dist-golden")) {
         dist_golden(argv[2], std::atoi(argv[3]));
+        return 0;
+    }
+    if (argc >= 4 && !std::strcmp(argv[1], "--level3-golden")) {
+        level3_golden(argv[2], std::atoi(argv[3]));
         return 0;
     }
     if (argc >= 4 && !std::strcmp(argv[1], "--bench")) {

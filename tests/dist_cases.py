@@ -19,6 +19,7 @@ import torch
 from elemental_b200 import el
 from oracle import dist as OD
 from oracle import gemm as OG
+from oracle import level3 as O3
 
 NPDT = {torch.float32: np.float32, torch.float64: np.float64}
 
@@ -312,6 +313,291 @@ def check_gemm_pipeline(grid, dtype=torch.float64) -> int:
         assert err <= tol, (oa, ob, alg, err, tol)
         cnt += 1
     return cnt
+
+
+def check_trapezoids(grid, dtype=torch.float64) -> int:
+    """ScaleTrapezoid / MakeTrapezoidal / AxpyTrapezoid / MakeSymmetric (level-1 trapezoid headers) on
+    several distributions, alignments and offsets: data movement and exact products only (alpha is a
+    power of two), so every result must equal the oracle's bit for bit."""
+    og = _grid_oracle(grid)
+    npdt = NPDT[dtype]
+    me = grid.Rank()
+    rng = np.random.default_rng(11)
+    cnt = 0
+    for (U, V), (h, w) in (((OD.MC, OD.MR), (23, 23)), ((OD.MC, OD.MR), (17, 29)), ((OD.VC, OD.STAR), (21, 13)),
+                           ((OD.STAR, OD.VR), (14, 26)), ((OD.MR, OD.MC), (19, 19)), ((OD.STAR, OD.STAR), (9, 12))):
+        for uplo in (el.LOWER, el.UPPER):
+            for offset in (0, 1, -2, 5):
+                ca, ra = int(rng.integers(og.stride(U))), int(rng.integers(og.stride(V)))
+                G = np.asfortranarray(rng.uniform(-1, 1, (h, w)).astype(npdt))
+                X = np.asfortranarray(rng.uniform(-1, 1, (h, w)).astype(npdt))
+                mask = O3.trapezoid_mask(h, w, uplo, offset)
+                spec = OD.Spec(U, V, ca, ra, h, w)
+                A = el.DistMatrix(grid, U, V, dtype).Align(ca, ra).from_global(G)
+                el.ScaleTrapezoid(-0.5, uplo, A, offset)
+                exp = np.where(mask, npdt(-0.5) * G, G)
+                assert np.array_equal(A.get_local(), OD.local_of(exp, spec, og, me)), ("ScaleTrapezoid", U, V, uplo, offset)
+                el.ScaleTrapezoid(0.0, uplo, A, offset)
+                exp = np.where(mask, npdt(0), G)
+                assert np.array_equal(A.get_local(), OD.local_of(exp, spec, og, me)), ("ScaleTrapezoid 0", U, V, uplo, offset)
+                A.from_global(G)
+                el.MakeTrapezoidal(uplo, A, offset)
+                assert np.array_equal(A.get_local(), OD.local_of(np.where(mask, G, npdt(0)), spec, og, me)), ("MakeTrapezoidal", U, V, uplo, offset)
+                # AxpyTrapezoid with X in the same layout, then in another distribution / alignment
+                A.from_global(G)
+                Xd = el.DistMatrix(grid, U, V, dtype).Align(ca, ra).from_global(X)
+                el.AxpyTrapezoid(uplo, 2.0, Xd, A, offset)
+                exp = np.where(mask, G + npdt(2.0) * X, G)
+                assert np.array_equal(A.get_local(), OD.local_of(exp, spec, og, me)), ("AxpyTrapezoid", U, V, uplo, offset)
+                A.from_global(G)
+                Xo = el.DistMatrix(grid, OD.MC, OD.MR, dtype).Align(1 % og.r, 1 % og.c).from_global(X)
+                el.AxpyTrapezoid(uplo, 2.0, Xo, A, offset)
+                assert np.array_equal(A.get_local(), OD.local_of(exp, spec, og, me)), ("AxpyTrapezoid redistributed", U, V, uplo, offset)
+                cnt += 5
+    for (U, V) in ((OD.MC, OD.MR), (OD.MR, OD.MC), (OD.VC, OD.STAR), (OD.STAR, OD.STAR)):
+        for uplo in (el.LOWER, el.UPPER):
+            n = 27
+            ca, ra = int(rng.integers(og.stride(U))), int(rng.integers(og.stride(V)))
+            G = np.asfortranarray(rng.uniform(-1, 1, (n, n)).astype(npdt))
+            A = el.DistMatrix(grid, U, V, dtype).Align(ca, ra).from_global(G)
+            el.MakeSymmetric(uplo, A)
+            tri = np.where(O3.trapezoid_mask(n, n, uplo, 0), G, npdt(0))
+            strict = np.where(O3.trapezoid_mask(n, n, uplo, -1 if uplo == el.LOWER else 1), G, npdt(0))
+            exp = np.asfortranarray(tri + strict.T)
+            assert np.array_equal(A.get_local(), OD.local_of(exp, OD.Spec(U, V, ca, ra, n, n), og, me)), ("MakeSymmetric", U, V, uplo)
+            cnt += 1
+    return cnt
+
+
+def _tri_err(got_loc, ref, spec, og, me, npdt, k):
+    ref_loc = OD.local_of(ref, spec, og, me)
+    num = float(np.linalg.norm(got_loc.astype(np.longdouble) - ref_loc))
+    den = float(np.linalg.norm(ref)) / np.sqrt(og.p)
+    return num / max(den, 1e-300), OG.gemm_tolerance(npdt, max(k, 1))
+
+
+def check_level3(grid, dtype=torch.float64, trrk_blocksize=8) -> int:
+    """LocalTrrk / Trrk / Syrk / Herk / Symm / Hemm against the global definition (oracle.level3) within the
+    Gemm bound; the triangle of C that the routine must not touch has to come back bit-identical.
+    LocalTrrkBlocksize is lowered so the recursion of LocalTrrk (Trrk/Local.hpp:782-830) runs several
+    levels at these sizes; nb = 16 gives several k panels only where the engine's panel width allows
+    (ELB200_PANEL_K)."""
+    og = _grid_oracle(grid)
+    npdt = NPDT[dtype]
+    me = grid.Rank()
+    cnt = 0
+    old_bs = el.LocalTrrkBlocksize()
+    el.SetLocalTrrkBlocksize(trrk_blocksize)
+    try:
+        n, k = 67, 45
+        C0 = OG.uniform_matrix(n, n, 303, npdt, 0.0, 1.0)
+        # LocalTrrk on explicitly built panels, aligned with a misaligned C
+        for uplo in (el.LOWER, el.UPPER):
+            for ta, tb in itertools.product((0, 1), (0, 1)):
+                ca, ra = 1 % og.r, 2 % og.c
+                A = OG.uniform_matrix(*((k, n) if ta else (n, k)), 301, npdt, 0.0, 1.0)
+                B = OG.uniform_matrix(*((n, k) if tb else (k, n)), 302, npdt, 0.0, 1.0)
+                dA = (el.DistMatrix(grid, el.STAR, el.MC, dtype).Align(0, ca) if ta else el.DistMatrix(grid, el.MC, el.STAR, dtype).Align(ca, 0)).from_global(A)
+                dB = (el.DistMatrix(grid, el.MR, el.STAR, dtype).Align(ra, 0) if tb else el.DistMatrix(grid, el.STAR, el.MR, dtype).Align(0, ra)).from_global(B)
+                dC = el.DistMatrix(grid, el.MC, el.MR, dtype).Align(ca, ra).from_global(C0)
+                el.LocalTrrk(uplo, ta, tb, 2.0, dA, dB, 3.0, dC)
+                ref = O3.trrk_global(uplo, ta, tb, 2.0, A, B, 3.0, C0)
+                spec = OD.Spec(OD.MC, OD.MR, ca, ra, n, n)
+                got = dC.get_local()
+                err, tol = _tri_err(got, ref, spec, og, me, npdt, k)
+                assert err <= tol, ("LocalTrrk", uplo, ta, tb, err, tol)
+                keep = ~OD.local_of(np.asfortranarray(O3.trapezoid_mask(n, n, uplo, 0)), spec, og, me).astype(bool)
+                assert np.array_equal(got[keep], OD.local_of(C0, spec, og, me)[keep]), ("LocalTrrk touched the other triangle", uplo, ta, tb)
+                cnt += 1
+        # Trrk: all orientations, aligned / misaligned [MC,MR] operands, and operands that need proxies
+        layouts = [(((el.MC, el.MR),) * 3, ((0, 0), (0, 0), (0, 0))), (((el.MC, el.MR),) * 3, ((1, 2), (0, 1), (1, 0))),
+                   (((el.VC, el.STAR), (el.STAR, el.VR), (el.MR, el.MC)), ((1, 0), (0, 1), (0, 1)))]
+        for uplo in (el.LOWER, el.UPPER):
+            for ta, tb in itertools.product((0, 1), (0, 1)):
+                for dists, aligns in layouts:
+                    A = OG.uniform_matrix(*((k, n) if ta else (n, k)), 311, npdt, 0.0, 1.0)
+                    B = OG.uniform_matrix(*((n, k) if tb else (k, n)), 312, npdt, 0.0, 1.0)
+                    mk = lambda d, al, G: el.DistMatrix(grid, d[0], d[1], dtype).Align(al[0] % og.stride(d[0]), al[1] % og.stride(d[1])).from_global(G)  # noqa: E731
+                    dA, dB, dC = mk(dists[0], aligns[0], A), mk(dists[1], aligns[1], B), mk(dists[2], aligns[2], C0)
+                    el.PushBlocksizeStack(16)
+                    try:
+                        el.Trrk(uplo, ta, tb, 0.5, dA, dB, -0.5, dC)
+                    finally:
+                        el.PopBlocksizeStack()
+                    ref = O3.trrk_global(uplo, ta, tb, 0.5, A, B, -0.5, C0)
+                    spec = OD.Spec(dists[2][0], dists[2][1], dC.ColAlign(), dC.RowAlign(), n, n)
+                    got = dC.get_local()
+                    err, tol = _tri_err(got, ref, spec, og, me, npdt, k)
+                    assert err <= tol, ("Trrk", uplo, ta, tb, dists, err, tol)
+                    keep = ~OD.local_of(np.asfortranarray(O3.trapezoid_mask(n, n, uplo, 0)), spec, og, me).astype(bool)
+                    assert np.array_equal(got[keep], OD.local_of(C0, spec, og, me)[keep]), ("Trrk touched the other triangle", uplo, ta, tb)
+                    cnt += 1
+        # Syrk / Herk: C = alpha A A^T + beta C (NORMAL) or alpha A^T A + beta C (TRANSPOSE)
+        for uplo in (el.LOWER, el.UPPER):
+            for trans in (0, 1):
+                for fn in (el.Syrk, el.Herk):
+                    A = OG.uniform_matrix(*((k, n) if trans else (n, k)), 321, npdt, 0.0, 1.0)
+                    dA = el.DistMatrix(grid, el.MC, el.MR, dtype).Align(1 % og.r, 0).from_global(A)
+                    dC = el.DistMatrix(grid, el.MC, el.MR, dtype).Align(0, 1 % og.c).from_global(C0)
+                    fn(uplo, trans, 2.0, dA, 3.0, dC)
+                    ref = O3.syrk_global(uplo, trans, 2.0, A, 3.0, C0)
+                    spec = OD.Spec(OD.MC, OD.MR, 0, 1 % og.c, n, n)
+                    err, tol = _tri_err(dC.get_local(), ref, spec, og, me, npdt, k)
+                    assert err <= tol, ("Syrk", uplo, trans, err, tol)
+                    cnt += 1
+        # Symm / Hemm: only the `uplo` triangle of A may be referenced -> poison the other one
+        m2 = 41
+        for side in (el.LEFT, el.RIGHT):
+            for uplo in (el.LOWER, el.UPPER):
+                A = OG.uniform_matrix(n, n, 331, npdt, 0.0, 1.0)
+                Apoison = np.where(O3.trapezoid_mask(n, n, uplo, 0), A, npdt(np.nan))
+                Bm = OG.uniform_matrix(*((n, m2) if side == el.LEFT else (m2, n)), 332, npdt, 0.0, 1.0)
+                Cm = OG.uniform_matrix(*Bm.shape, 333, npdt, 0.0, 1.0)
+                dA = el.DistMatrix(grid, el.MC, el.MR, dtype).Align(1 % og.r, 1 % og.c).from_global(np.asfortranarray(Apoison))
+                dB = el.DistMatrix(grid, el.MC, el.MR, dtype).from_global(Bm)
+                dC = el.DistMatrix(grid, el.MC, el.MR, dtype).Align(0, 1 % og.c).from_global(Cm)
+                (el.Symm if uplo == el.LOWER else el.Hemm)(side, uplo, 2.0, dA, dB, 3.0, dC)
+                ref = O3.symm_global(side, uplo, 2.0, A, Bm, 3.0, Cm)
+                spec = OD.Spec(OD.MC, OD.MR, 0, 1 % og.c, *Cm.shape)
+                got = dC.get_local()
+                assert np.isfinite(got).all(), ("Symm read the unreferenced triangle", side, uplo)
+                err, tol = _tri_err(got, ref, spec, og, me, npdt, n)
+                assert err <= tol, ("Symm", side, uplo, err, tol)
+                cnt += 1
+    finally:
+        el.SetLocalTrrkBlocksize(old_bs)
+    return cnt
+
+
+def check_level3_golden(grid, dtype=torch.float64) -> int:
+    """The REFERENCE'S OWN per-rank outputs (tests/golden/ref_level3.npz: its CPU build run multi-rank on
+    this grid shape) against this library: trapezoid routines and MakeSymmetric bit for bit, LocalTrrk /
+    Trrk / Syrk / Symm within the fp64 Gemm bound.  Grids the reference was not run on return 0."""
+    import os
+    from oracle.make_golden import lcg_matrix
+    assert dtype == torch.float64
+    og = _grid_oracle(grid)
+    gold = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_level3.npz"))
+    tag = f"r{og.r}c{og.c}"
+    me = grid.Rank()
+    if f"{tag}_q{me}_L" not in gold:
+        return 0
+    blob = gold[f"{tag}_q{me}_bin"]
+    ca, ra = 1 % og.r, 2 % og.c
+    n, k, m2 = 37, 23, 29
+    f64 = np.float64
+    DM = lambda U, V, a, b, G: el.DistMatrix(grid, U, V, dtype).Align(a, b).from_global(np.asfortranarray(G))  # noqa: E731
+    old_bs = el.LocalTrrkBlocksize()
+    el.SetLocalTrrkBlocksize(4)
+    el.PushBlocksizeStack(16)
+    cnt = 0
+    try:
+        for (kind, uplo, p1, p2, caC, raC, cs, rs, lh, lw, off) in (tuple(int(x) for x in r) for r in gold[f"{tag}_q{me}_L"]):
+            if kind in (0, 1):
+                R = DM(el.MC, el.MR, ca, ra, lcg_matrix(13, 11, 7001, f64))
+                (el.ScaleTrapezoid(-0.5, uplo, R, p1) if kind == 0 else el.MakeTrapezoidal(uplo, R, p1))
+            elif kind == 2:
+                R = DM(el.MC, el.MR, ca, ra, lcg_matrix(13, 13, 7001, f64))
+                el.AxpyTrapezoid(uplo, 2.0, DM(el.MC, el.MR, ca, ra, lcg_matrix(13, 13, 7004, f64)), R, p1)
+            elif kind == 3:
+                R = DM(el.MC, el.MR, ca, ra, lcg_matrix(13, 13, 7001, f64))
+                el.MakeSymmetric(uplo, R)
+            elif kind == 4:
+                R = DM(el.MC, el.MR, ca, ra, lcg_matrix(n, n, 7003, f64))
+                A = DM(el.STAR, el.MC, 0, ca, lcg_matrix(k, n, 7001, f64)) if p1 else DM(el.MC, el.STAR, ca, 0, lcg_matrix(n, k, 7001, f64))
+                B = DM(el.MR, el.STAR, ra, 0, lcg_matrix(n, k, 7002, f64)) if p2 else DM(el.STAR, el.MR, 0, ra, lcg_matrix(k, n, 7002, f64))
+                el.LocalTrrk(uplo, p1, p2, 2.0, A, B, 3.0, R)
+            elif kind == 5:
+                A = DM(el.MC, el.MR, ca, 0, lcg_matrix(*((k, n) if p1 else (n, k)), 7001, f64))
+                B = DM(el.MC, el.MR, 0, ra, lcg_matrix(*((n, k) if p2 else (k, n)), 7002, f64))
+                R = DM(el.MC, el.MR, ca, ra, lcg_matrix(n, n, 7003, f64))
+                el.Trrk(uplo, p1, p2, 2.0, A, B, 3.0, R)
+            elif kind == 6:
+                A = DM(el.MC, el.MR, ca, 0, lcg_matrix(*((k, n) if p1 else (n, k)), 7001, f64))
+                R = DM(el.MC, el.MR, 0, ra, lcg_matrix(n, n, 7003, f64))
+                el.Syrk(uplo, p1, 2.0, A, 3.0, R)
+            else:
+                shape = (m2, n) if p1 else (n, m2)
+                A = DM(el.MC, el.MR, ca, ra, lcg_matrix(n, n, 7001, f64))
+                B = DM(el.MC, el.MR, 0, 0, lcg_matrix(*shape, 7002, f64))
+                R = DM(el.MC, el.MR, 0, ra, lcg_matrix(*shape, 7003, f64))
+                el.Symm(p1, uplo, 2.0, A, B, 3.0, R)
+            assert (R.ColAlign(), R.RowAlign(), R.ColShift(), R.RowShift()) == (caC, raC, cs, rs), (tag, kind, uplo, p1, p2)
+            got = R.get_local()
+            ref = blob[off:off + lh * lw].reshape((lh, lw), order="F")
+            assert got.shape == ref.shape, (tag, kind, uplo, p1, p2)
+            if kind <= 3:
+                assert np.array_equal(got, ref), (tag, me, kind, uplo, p1, p2)
+            else:
+                assert OG.frobenius_rel_err(got, ref) <= OG.gemm_tolerance(f64, k), (tag, me, kind, uplo, p1, p2)
+            cnt += 1
+    finally:
+        el.PopBlocksizeStack()
+        el.SetLocalTrrkBlocksize(old_bs)
+    return cnt
+
+
+def check_dist_golden(grid, dtype=torch.float64) -> int:
+    """The REFERENCE'S OWN per-rank outputs of tests/golden/ref_dist.npz (its CPU build run multi-rank on
+    this grid shape: 121 (U,V)->(U2,V2) redistributions, 23 [CIRC,CIRC] gather / scatter cases, 20 El::Gemm
+    runs) against this library, rank by rank: redistributions bit for bit, Gemm within the fp64 bound."""
+    import os
+    from oracle.make_golden import lcg_matrix
+    assert dtype == torch.float64
+    og = _grid_oracle(grid)
+    gold = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_dist.npz"))
+    tag = f"r{og.r}c{og.c}"
+    me = grid.Rank()
+    if f"{tag}_q{me}_R" not in gold:
+        return 0
+    blob = gold[f"{tag}_q{me}_bin"]
+    ELD = {0: el.MC, 2: el.MR, 3: el.VC, 4: el.VR, 5: el.STAR, 6: el.CIRC}  # El::Dist enum value -> ours
+    G = np.asfortranarray(np.arange(13 * 11, dtype=np.float64).reshape(13, 11) + 1.0)
+    cnt = 0
+    recs = [tuple(int(x) for x in r) + (0, 0) for r in gold[f"{tag}_q{me}_R"]] + [tuple(int(x) for x in r) for r in gold[f"{tag}_q{me}_Q"]]
+    for (U, V, U2, V2, caA, raA, caB, raB, csB, rsB, lh, lw, off, rootA, rootB) in recs:
+        A = el.DistMatrix(grid, ELD[U], ELD[V], dtype)
+        if U == 6:
+            A.SetRoot(rootA)
+        A.Align(caA, raA).from_global(G)
+        B = el.DistMatrix(grid, ELD[U2], ELD[V2], dtype)
+        if U2 == 6:
+            B.SetRoot(rootB)
+        B.Align(caB, raB)
+        el.Copy(A, B)
+        got = B.get_local()
+        assert got.shape == (lh, lw), (tag, me, U, V, U2, V2, got.shape, (lh, lw))
+        if lh and lw:
+            assert (B.ColShift(), B.RowShift()) == (csB, rsB)
+        assert np.array_equal(got, blob[off:off + lh * lw].reshape((lh, lw), order="F")), (tag, me, U, V, U2, V2)
+        cnt += 1
+    aligns = ((1 % og.r, 2 % og.c), (0, 1 % og.c), (1 % og.r, 0))
+    for (cid, oa, ob, alg, m, n, k, nb, caC, raC, cs, rs, lh, lw, off) in (tuple(int(x) for x in r) for r in gold[f"{tag}_q{me}_G"]):
+        mk = lambda al, M: el.DistMatrix(grid, el.MC, el.MR, dtype).Align(*al).from_global(np.asfortranarray(M))  # noqa: E731
+        dA = mk(aligns[0], lcg_matrix(*((k, m) if oa else (m, k)), 3 * cid + 0, np.float64))
+        dB = mk(aligns[1], lcg_matrix(*((n, k) if ob else (k, n)), 3 * cid + 1, np.float64))
+        dC = mk(aligns[2], lcg_matrix(m, n, 3 * cid + 2, np.float64))
+        el.PushBlocksizeStack(nb)
+        try:
+            el.Gemm(oa, ob, 2.0, dA, dB, 3.0, dC, alg)
+        finally:
+            el.PopBlocksizeStack()
+        got = dC.get_local()
+        ref = blob[off:off + lh * lw].reshape((lh, lw), order="F")
+        assert got.shape == ref.shape and (dC.ColShift(), dC.RowShift()) == (cs, rs)
+        assert OG.frobenius_rel_err(got, ref) <= OG.gemm_tolerance(np.float64, k), (tag, me, cid)
+        cnt += 1
+    return cnt
+
+
+def run_level3(grid) -> dict:
+    """The triangular rank-k family and the comparisons with the reference's own per-rank outputs."""
+    out = {}
+    out["trapezoids"] = check_trapezoids(grid, torch.float64) + check_trapezoids(grid, torch.float32)
+    out["level3"] = check_level3(grid, torch.float64) + check_level3(grid, torch.float32)
+    out["level3_ref_golden"] = check_level3_golden(grid)
+    out["dist_ref_golden"] = check_dist_golden(grid)
+    return out
 
 
 def run_all(grid, heavy=False) -> dict:

@@ -19,6 +19,7 @@ def main() -> int:
     ap = argparse.ArgumentParser()
     ap.add_argument("--height", type=int, default=0)
     ap.add_argument("--heavy", action="store_true")
+    ap.add_argument("--level3", action="store_true", help="run dist_cases.run_level3 instead of run_all")
     args = ap.parse_args()
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
@@ -28,7 +29,7 @@ def main() -> int:
     ok = 1
     try:
         grid = el.Grid(height=args.height or None, device=local)
-        out = dc.run_all(grid, heavy=args.heavy)
+        out = dc.run_level3(grid) if args.level3 else dc.run_all(grid, heavy=args.heavy)
         grid.sync()
         if grid.Rank() == 0:
             print(f"grid {grid.Height()}x{grid.Width()}: {out}", flush=True)

@@ -170,6 +170,32 @@ int peer_reduce_axpy(int nsrc, const T* const* srcs, int64_t off, const elb200_s
     return ELB200_OK;
 }
 
+template <typename T>
+int trapezoid(int op, int uplo, int64_t offset, int64_t rows, int64_t cols, int64_t row0, int64_t row_step, int64_t col0,
+              int64_t col_step, T alpha, const T* X, int64_t ldx, T* Y, int64_t ldy, void* s) {
+    if (op < ELB200_TRAP_SCALE || op > ELB200_TRAP_MAKE || uplo < 0 || uplo > 1 || rows < 0 || cols < 0 || row_step < 1 ||
+        col_step < 1 || row0 < 0 || col0 < 0)
+        return ELB200_ERR_ARG;
+    if (rows == 0 || cols == 0) return ELB200_OK;
+    if (!Y || ldy < rows || (op == ELB200_TRAP_AXPY && (!X || ldx < rows))) return ELB200_ERR_ARG;
+    if (op == ELB200_TRAP_SCALE && alpha == T(1)) return ELB200_OK;
+    count_launch();
+    sim::enqueue(st(s), [=] {
+        check_lattice(Y, rows, cols, 1, ldy, "trapezoid Y");
+        if (op == ELB200_TRAP_AXPY) check_lattice(X, rows, cols, 1, ldx, "trapezoid X");
+        for (int64_t j = 0; j < cols; ++j)
+            for (int64_t i = 0; i < rows; ++i) {
+                const int64_t gi = row0 + i * row_step, gj = col0 + j * col_step;
+                const bool inside = uplo == ELB200_UPPER ? gi <= gj - offset : gi >= gj - offset;
+                T* y = Y + i + j * ldy;
+                if (op == ELB200_TRAP_SCALE) { if (inside) *y = alpha == T(0) ? T(0) : alpha * *y; }
+                else if (op == ELB200_TRAP_AXPY) { if (inside) *y += alpha * X[i + j * ldx]; }
+                else if (!inside) *y = T(0);
+            }
+    });
+    return ELB200_OK;
+}
+
 int check_gemm_args(int transA, int transB, int64_t m, int64_t n, int64_t k, const void* A, int64_t lda, const void* B,
                     int64_t ldb, const void* C, int64_t ldc) {
     if (transA < 0 || transA > 2 || transB < 0 || transB > 2) return ELB200_ERR_ARG;
@@ -261,6 +287,14 @@ int elb200_gemm_f64(int ta, int tb, int64_t m, int64_t n, int64_t k, double al, 
         return lattice<T>(mode, nseg, segs, M, ldm, buf, al, s); }                                                              \
     int elb200_peer_reduce_axpy_##SUF(int nsrc, const T* const* srcs, int64_t off, const elb200_segment* seg, T* M,             \
                                       int64_t ldm, T al, void* s) { return peer_reduce_axpy<T>(nsrc, srcs, off, seg, M, ldm, al, s); }
+int elb200_trapezoid_f32(int op, int uplo, int64_t off, int64_t r, int64_t c, int64_t r0, int64_t rs, int64_t c0, int64_t cs, float al,
+                         const float* X, int64_t ldx, float* Y, int64_t ldy, void* s) {
+    return trapezoid<float>(op, uplo, off, r, c, r0, rs, c0, cs, al, X, ldx, Y, ldy, s);
+}
+int elb200_trapezoid_f64(int op, int uplo, int64_t off, int64_t r, int64_t c, int64_t r0, int64_t rs, int64_t c0, int64_t cs, double al,
+                         const double* X, int64_t ldx, double* Y, int64_t ldy, void* s) {
+    return trapezoid<double>(op, uplo, off, r, c, r0, rs, c0, cs, al, X, ldx, Y, ldy, s);
+}
 SIM_BLAS1(f32, float)
 SIM_BLAS1(f64, double)
 #undef SIM_BLAS1

@@ -14,6 +14,7 @@ def main() -> int:
     ap.add_argument("grid")
     ap.add_argument("--heavy", action="store_true")
     ap.add_argument("--only", default="")
+    ap.add_argument("--level3", action="store_true", help="run dist_cases.run_level3 instead of run_all")
     args = ap.parse_args()
     r, c = (int(x) for x in args.grid.lower().split("x"))
     from tests.hostsim import sim_el
@@ -22,6 +23,8 @@ def main() -> int:
     only = [x for x in args.only.split(",") if x]
 
     def body(grid):
+        if args.level3:
+            return dc.run_level3(grid)
         if not only:
             return dc.run_all(grid, heavy=args.heavy)
         out = {}

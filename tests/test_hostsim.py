@@ -36,49 +36,58 @@ def _run(grid, *args, env=None, timeout=900):
 
 
 def test_engine_1x1_all_cases(simlib):
-    out = _run("1x1")
-    assert "'redist_f64': 121" in out and "'gemm_f64': 40" in out and "'gemm_host': 24" in out
+    out = _run("1x1", "--only", "run_all,run_level3")
+    assert "'redist_f64': 121" in out and "'gemm_f64': 40" in out and "'gemm_host': 24" in out and "'level3_ref_golden': 44" in out
 
 
 def test_engine_2x2_peer_arena_all_cases(simlib):
     """Every case on a 2 x 2 grid with the NVLink peer-arena paths (copy-engine AllGather, pull
-    exchange, receiver-side reduce) — the paths the multi-GPU bench runs."""
-    out = _run("2x2")
+    exchange, receiver-side reduce) — the paths the multi-GPU bench runs — plus the engine against the
+    REFERENCE'S OWN per-rank outputs on this grid shape (run_level3: tests/golden/ref_dist.npz, 121
+    redistributions + 23 [CIRC,CIRC] cases + 20 Gemm runs; ref_level3.npz, 44 level-3 records)."""
+    out = _run("2x2", "--only", "run_all,run_level3")
     assert "'redist_f64': 121" in out and "'circ': 54" in out and "'gemm_f32': 40" in out
+    assert "'level3_ref_golden': 44" in out and "'dist_ref_golden': 164" in out
 
 
 def test_engine_2x4_bench_grid(simlib):
-    """The 8-GPU grid shape of BASELINE C3 (2 x 4): redistributions, contractions, all Gemm variants."""
-    _run("2x4", "--only", "check_redistributions,check_contractions,check_gemm_variants_f64,check_gemm_proxies_f32")
+    """The 8-GPU grid shape of BASELINE C3 (2 x 4): redistributions, contractions, all Gemm variants, the
+    level-3 family, and the reference's own per-rank outputs."""
+    out = _run("2x4", "--only", "check_redistributions,check_contractions,check_gemm_variants_f64,check_gemm_proxies_f32,run_level3")
+    assert "'level3_ref_golden': 44" in out and "'dist_ref_golden': 164" in out
 
 
 def test_engine_3x2_nccl_fallback(simlib):
     """Peer arena disabled (ELB200_P2P=0): the NCCL AllGather / ReduceScatter / grouped send-recv
     paths on a non-square grid with r > c."""
-    _run("3x2", "--only", "check_redistributions,check_contractions,check_gemm_variants_f32", env={"ELB200_P2P": "0"})
+    out = _run("3x2", "--only", "check_redistributions,check_contractions,check_gemm_variants_f32,run_level3", env={"ELB200_P2P": "0"})
+    assert "'dist_ref_golden': 164" in out
 
 
-@pytest.mark.parametrize("grid,env", [("2x2", {}), ("2x4", {}), ("1x2", {}), ("2x3", {"ELB200_P2P": "0"}),
-                                       ("2x2", {"ELB200_DIRECT": "0"}), ("2x2", {"ELB200_OVERLAP": "0"})])
-def test_engine_multi_panel_pipeline(simlib, grid, env):
+@pytest.mark.parametrize("grid,env,extra", [("2x2", {}, ""), ("2x4", {}, ""), ("1x2", {}, ",run_level3"), ("2x1", {}, ",run_level3"),
+                                             ("2x3", {"ELB200_P2P": "0"}, ",run_level3"), ("2x2", {"ELB200_DIRECT": "0"}, ""),
+                                             ("2x2", {"ELB200_OVERLAP": "0"}, "")])
+def test_engine_multi_panel_pipeline(simlib, grid, env, extra):
     """Narrow panels (ELB200_PANEL_K=512, k = 1300): several panels per Gemm through the two-slot
-    gather | GEMM pipeline, zero-copy direct panels, staged panels, and with the pipeline off."""
+    gather | GEMM pipeline, zero-copy direct panels, staged panels, and with the pipeline off; on the
+    grid shapes not covered above also the level-3 family and the reference's own per-rank outputs."""
     e = {"ELB200_PANEL_K": "512"}
     e.update(env)
-    _run(grid, "--only", "check_gemm_pipeline,check_gemm_pipeline_f32", env=e)
+    out = _run(grid, "--only", "check_gemm_pipeline,check_gemm_pipeline_f32" + extra, env=e)
+    assert not extra or "'dist_ref_golden': 164" in out
 
 
 def test_engine_tiny_arena_falls_back(simlib):
     """Arena slots of 4 KiB: some messages fit, most do not — every size check must route the rest to
-    NCCL (and every rank must take the same branch)."""
-    _run("2x2", "--only", "check_redistributions,check_contractions,check_gemm_pipeline", env={"ELB200_ARENA_KB": "4"})
+    NCCL (and every rank must take the same branch). Panels 16 wide: Trrk / Syrk walk several k panels."""
+    _run("2x2", "--only", "check_redistributions,check_contractions,check_gemm_pipeline,check_level3", env={"ELB200_ARENA_KB": "4", "ELB200_PANEL_K": "16"})
 
 
 def test_cxx_facade_on_hostsim(simlib):
     """include/El.hpp exercised for real on CPU: tools/el_api_check.cpp and tools/el_gemm_driver.cpp
     (the counterpart of the reference's tests/blas_like/Gemm.cpp) linked against the hostsim engine."""
     out_dir = os.path.dirname(simlib)
-    for tool, args in (("el_api_check", []), ("el_gemm_driver", ["--m", "150", "--n", "120", "--k", "130", "--reps", "1"]),
+    for tool, args in (("el_api_check", []), ("el_level3_check", []), ("el_gemm_driver", ["--m", "150", "--n", "120", "--k", "130", "--reps", "1"]),
                        ("el_gemm_driver", ["--m", "150", "--n", "120", "--k", "130", "--reps", "1", "--f64"])):
         exe = os.path.join(out_dir, tool)
         src = os.path.join(ROOT, "tools", tool + ".cpp")

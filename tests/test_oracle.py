@@ -9,6 +9,7 @@ import pytest
 
 from oracle import dist as OD
 from oracle import gemm as OG
+from oracle import level3 as O3
 from oracle.make_golden import lcg_matrix
 
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
@@ -251,3 +252,105 @@ def test_distributed_gemm_matches_reference_per_rank(gold_dist, tag):
             ref = blob[off:off + lh * lw].reshape((lh, lw), order="F")
             assert mine.shape == ref.shape
             assert OG.frobenius_rel_err(mine, ref) <= OG.gemm_tolerance(np.float64, k), (tag, q, cid)
+
+
+# ---------------------------------------------------------------------------------------------
+# Triangular rank-k family: tests/golden/ref_level3.npz holds per-rank outputs of
+# the reference's ScaleTrapezoid / MakeTrapezoidal / AxpyTrapezoid / MakeSymmetric, the four
+# LocalTrrk overloads, Trrk, Syrk and Symm (oracle/ref_build/gemm_ref.cpp::level3_golden).
+# ---------------------------------------------------------------------------------------------
+L3_TAGS = ["r1c1"] + DIST_TAGS
+L3_N, L3_K, L3_M2 = 37, 23, 29
+
+
+def level3_oracle_case(g, kind, uplo, p1, p2):
+    """Re-run one record of ref_level3.npz through the oracle restatement; returns the result VDM."""
+    ca, ra = 1 % g.r, 2 % g.c
+    n, k, m2 = L3_N, L3_K, L3_M2
+    f64 = np.float64
+    if kind in (0, 1):
+        A = OD.VDM.from_global(g, lcg_matrix(13, 11, 7001, f64), OD.MC, OD.MR, ca, ra)
+        (O3.scale_trapezoid(-0.5, uplo, A, p1) if kind == 0 else O3.make_trapezoidal(uplo, A, p1))
+        return A
+    if kind == 2:
+        A = OD.VDM.from_global(g, lcg_matrix(13, 13, 7001, f64), OD.MC, OD.MR, ca, ra)
+        X = OD.VDM.from_global(g, lcg_matrix(13, 13, 7004, f64), OD.MC, OD.MR, ca, ra)
+        O3.axpy_trapezoid(uplo, 2.0, X, A, p1)
+        return A
+    if kind == 3:
+        A = OD.VDM.from_global(g, lcg_matrix(13, 13, 7001, f64), OD.MC, OD.MR, ca, ra)
+        O3.make_symmetric(uplo, A)
+        return A
+    if kind == 4:
+        C = OD.VDM.from_global(g, lcg_matrix(n, n, 7003, f64), OD.MC, OD.MR, ca, ra)
+        A = (OD.VDM.from_global(g, lcg_matrix(k, n, 7001, f64), OD.STAR, OD.MC, 0, ca) if p1 else
+             OD.VDM.from_global(g, lcg_matrix(n, k, 7001, f64), OD.MC, OD.STAR, ca, 0))
+        B = (OD.VDM.from_global(g, lcg_matrix(n, k, 7002, f64), OD.MR, OD.STAR, ra, 0) if p2 else
+             OD.VDM.from_global(g, lcg_matrix(k, n, 7002, f64), OD.STAR, OD.MR, 0, ra))
+        O3.local_trrk(uplo, p1, p2, 2.0, A, B, 3.0, C, blocksize=4)
+        return C
+    if kind == 5:
+        A = OD.VDM.from_global(g, lcg_matrix(*((k, n) if p1 else (n, k)), 7001, f64), OD.MC, OD.MR, ca, 0)
+        B = OD.VDM.from_global(g, lcg_matrix(*((n, k) if p2 else (k, n)), 7002, f64), OD.MC, OD.MR, 0, ra)
+        C = OD.VDM.from_global(g, lcg_matrix(n, n, 7003, f64), OD.MC, OD.MR, ca, ra)
+        O3.trrk(uplo, p1, p2, 2.0, A, B, 3.0, C, nb=16)
+        return C
+    if kind == 6:
+        A = OD.VDM.from_global(g, lcg_matrix(*((k, n) if p1 else (n, k)), 7001, f64), OD.MC, OD.MR, ca, 0)
+        C = OD.VDM.from_global(g, lcg_matrix(n, n, 7003, f64), OD.MC, OD.MR, 0, ra)
+        O3.syrk(uplo, p1, 2.0, A, 3.0, C, nb=16)
+        return C
+    if kind == 7:
+        shape = (m2, n) if p1 else (n, m2)
+        A = OD.VDM.from_global(g, lcg_matrix(n, n, 7001, f64), OD.MC, OD.MR, ca, ra)
+        B = OD.VDM.from_global(g, lcg_matrix(*shape, 7002, f64), OD.MC, OD.MR, 0, 0)
+        C = OD.VDM.from_global(g, lcg_matrix(*shape, 7003, f64), OD.MC, OD.MR, 0, ra)
+        O3.symm(p1, uplo, 2.0, A, B, 3.0, C)
+        return C
+    raise ValueError(kind)
+
+
+@pytest.mark.parametrize("tag", L3_TAGS)
+def test_level3_matches_reference_per_rank(tag):
+    """Every record of the reference's level-3 run: the oracle's per-rank local result equals the
+    reference's — bit for bit for the trapezoid routines and MakeSymmetric (kinds 0-3), within the fp64
+    Gemm bound for LocalTrrk / Trrk / Syrk / Symm (BLAS summation order)."""
+    gold = np.load(os.path.join(GOLD, "ref_level3.npz"))
+    g = OD.Grid(int(tag[1]), int(tag[3]))
+    cache = {}
+    checked = 0
+    for q in range(g.p):
+        blob = gold[f"{tag}_q{q}_bin"]
+        for (kind, uplo, p1, p2, caC, raC, cs, rs, lh, lw, off) in (tuple(int(x) for x in r) for r in gold[f"{tag}_q{q}_L"]):
+            key = (kind, uplo, p1, p2)
+            if key not in cache:
+                cache[key] = level3_oracle_case(g, kind, uplo, p1, p2)
+            R = cache[key]
+            assert (R.spec.col_align, R.spec.row_align) == (caC, raC), (tag, key)
+            assert (R.spec.col_shift(g, q), R.spec.row_shift(g, q)) == (cs, rs)
+            ref = blob[off:off + lh * lw].reshape((lh, lw), order="F")
+            assert R.loc[q].shape == ref.shape, (tag, q, key)
+            if kind <= 3:
+                assert np.array_equal(R.loc[q], ref), (tag, q, key)
+            else:
+                assert OG.frobenius_rel_err(R.loc[q], ref) <= OG.gemm_tolerance(np.float64, L3_K), (tag, q, key)
+            checked += 1
+    assert checked == 44 * g.p
+
+
+def test_level3_restatement_equals_global_definition():
+    """LocalTrrk's recursion / Trrk's panel loop / Syrk (oracle.level3) against the plain global
+    definitions on grids the reference was not run on, several blocksizes."""
+    rng = np.random.default_rng(3)
+    n, k = 41, 19
+    for g in (OD.Grid(1, 3), OD.Grid(3, 3), OD.Grid(4, 2)):
+        for uplo in (O3.LOWER, O3.UPPER):
+            for oa, ob in itertools.product((0, 1), (0, 1)):
+                A = rng.standard_normal((k, n) if oa else (n, k))
+                B = rng.standard_normal((n, k) if ob else (k, n))
+                C0 = rng.standard_normal((n, n))
+                C = OD.VDM.from_global(g, C0, OD.MC, OD.MR, 1 % g.r, 1 % g.c)
+                O3.trrk(uplo, oa, ob, 0.5, OD.VDM.from_global(g, A, OD.MC, OD.MR), OD.VDM.from_global(g, B, OD.MC, OD.MR, 0, 1 % g.c),
+                        -0.5, C, nb=8)
+                ref = O3.trrk_global(uplo, oa, ob, 0.5, A, B, -0.5, C0, np.float64)
+                assert OG.frobenius_rel_err(C.to_global(), ref) < 1e-14, (g.r, g.c, uplo, oa, ob)
