@@ -10,13 +10,18 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 CSRC = os.path.join(ROOT, "elemental_b200", "csrc")
-OUT = os.path.join(HERE, "_build")
+# HOSTSIM_SANITIZE=address|thread|undefined builds an instrumented copy into _build_<name>/ (run the python
+# worker under LD_PRELOAD of the matching runtime, e.g. $(gcc -print-file-name=libtsan.so))
+SAN = os.environ.get("HOSTSIM_SANITIZE", "")
+OUT = os.path.join(HERE, "_build" + ("_" + SAN if SAN else ""))
 LIB = os.path.join(OUT, "libelb200_hostsim.so")
 ENGINE = ["engine_core.cpp", "engine_gemm.cpp", "engine_redist.cpp", "engine_level3.cpp", "peer.cpp", "plan.cpp", "capi_engine.cpp"]
 DOUBLES = ["sim_cuda.cpp", "sim_nccl.cpp", "sim_ops.cpp"]
 CUDA_INC = os.environ.get("CUDA_HOME", "/usr/local/cuda") + "/include"
 FLAGS = ["-std=c++17", "-O2", "-g", "-fPIC", "-pthread", "-Wall", "-Wno-unused-function", "-DELB200_HOSTSIM",
          "-I" + CUDA_INC, "-I/usr/include", "-I" + HERE]
+if SAN:
+    FLAGS += ["-fsanitize=" + SAN, "-fno-omit-frame-pointer", "-O1"]
 
 
 def _newer(src: str, deps, obj: str) -> bool:
@@ -46,7 +51,7 @@ def build(verbose: bool = False) -> str:
     if jobs or not os.path.exists(LIB):
         # -Bsymbolic: the engine's calls to cudaMalloc / ncclAllGather / elb200_gemm_f32 ... bind to the doubles
         # inside this library even if the real libcudart / libnccl / libelb200 are loaded in the process
-        cmd = ["g++", "-shared", "-pthread", "-Wl,-Bsymbolic", "-o", LIB] + objs
+        cmd = ["g++", "-shared", "-pthread", "-Wl,-Bsymbolic", "-o", LIB] + objs + (["-fsanitize=" + SAN] if SAN else [])
         r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"hostsim: link failed:\n{r.stdout[-6000:]}")

@@ -64,12 +64,13 @@ def test_engine_3x2_nccl_fallback(simlib):
     assert "'dist_ref_golden': 164" in out
 
 
-@pytest.mark.parametrize("grid,env,extra", [("2x2", {}, ""), ("2x4", {}, ""), ("1x2", {}, ",run_level3"), ("2x1", {}, ",run_level3"),
+@pytest.mark.parametrize("grid,env,extra", [("1x2", {}, ",run_level3"), ("2x1", {}, ",run_level3"),
                                              ("2x3", {"ELB200_P2P": "0"}, ",run_level3"), ("2x2", {"ELB200_DIRECT": "0"}, ""),
                                              ("2x2", {"ELB200_OVERLAP": "0"}, "")])
 def test_engine_multi_panel_pipeline(simlib, grid, env, extra):
     """Narrow panels (ELB200_PANEL_K=512, k = 1300): several panels per Gemm through the two-slot
-    gather | GEMM pipeline, zero-copy direct panels, staged panels, and with the pipeline off; on the
+    gather | GEMM pipeline, zero-copy direct panels, staged panels, and with the pipeline off (2 x 2 and 2 x 4
+    with the default settings run under ThreadSanitizer below); on the
     grid shapes not covered above also the level-3 family and the reference's own per-rank outputs."""
     e = {"ELB200_PANEL_K": "512"}
     e.update(env)
@@ -99,3 +100,58 @@ def test_cxx_facade_on_hostsim(simlib):
             assert r.returncode == 0, r.stderr[-3000:]
         r = subprocess.run([exe] + args, capture_output=True, text=True, timeout=300)
         assert r.returncode == 0 and "_PASS" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+# ---------------------------------------------------------------------------------------------
+# Race detection: the engine on the ThreadSanitizer build of hostsim.  Streams are threads and
+# device memory is ordinary memory there, so two "kernels" / copies touching the same bytes from
+# different streams without an event (or flag) between them are a data race ThreadSanitizer reports.
+# ---------------------------------------------------------------------------------------------
+def _tsan_runtime():
+    r = subprocess.run(["gcc", "-print-file-name=libtsan.so"], capture_output=True, text=True)
+    path = r.stdout.strip()
+    return path if r.returncode == 0 and os.path.isabs(path) and os.path.exists(path) else None
+
+
+@pytest.fixture(scope="module")
+def tsanlib():
+    rt = _tsan_runtime()
+    if rt is None:
+        pytest.skip("no ThreadSanitizer runtime (libtsan.so) next to gcc")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "hostsim", "build.py")], capture_output=True, text=True,
+                       env=dict(os.environ, HOSTSIM_SANITIZE="thread"), cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    return r.stdout.strip().splitlines()[-1], rt
+
+
+def test_race_detector_selftest(tsanlib):
+    """A consumer stream that does not wait for the producer's event must be reported, the ordered version
+    must not (tests/hostsim/race_selftest.cpp) — i.e. the detector can see what the next test relies on."""
+    lib, _ = tsanlib
+    out_dir = os.path.dirname(lib)
+    exe = os.path.join(out_dir, "race_selftest")
+    cuda_inc = os.environ.get("CUDA_HOME", "/usr/local/cuda") + "/include"
+    r = subprocess.run(["g++", "-std=c++17", "-O1", "-g", "-fsanitize=thread", "-I" + cuda_inc, "-o", exe,
+                        os.path.join(ROOT, "tests", "hostsim", "race_selftest.cpp"), lib, "-Wl,-rpath," + out_dir, "-pthread"],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]
+    env = dict(os.environ, TSAN_OPTIONS="exitcode=66")
+    ok = subprocess.run([exe], capture_output=True, text=True, env=env, timeout=120)
+    assert ok.returncode == 0 and "RACE_SELFTEST_DONE ordered" in ok.stdout and "ThreadSanitizer" not in ok.stderr, ok.stderr[-2000:]
+    bad = subprocess.run([exe, "race"], capture_output=True, text=True, env=env, timeout=120)
+    assert bad.returncode == 66 and "WARNING: ThreadSanitizer: data race" in bad.stderr, bad.stdout + bad.stderr[-2000:]
+
+
+@pytest.mark.parametrize("grid,only", [("2x2", "check_gemm_pipeline,check_contractions,check_level3"),
+                                        ("2x4", "check_gemm_pipeline")])
+def test_engine_is_race_free_under_tsan(tsanlib, grid, only):
+    """The multi-panel SUMMA pipeline (zero-copy direct panels, slot hand-back), the peer-arena reductions and
+    exchanges and the level-3 family under ThreadSanitizer: no report.  (The remaining cases — run_all, run_level3,
+    the four-stream host-operand Gemm — were run the same way by hand and are clean too; they are left out of the
+    default suite for time.)"""
+    _, rt = tsanlib
+    e = dict(os.environ, HOSTSIM_SANITIZE="thread", HOSTSIM_TIMEOUT="300", ELB200_ARENA_MB="8", ELB200_PANEL_K="512",
+             OMP_NUM_THREADS="1", LD_PRELOAD=rt, TSAN_OPTIONS="report_signal_unsafe=0 history_size=4 exitcode=66")
+    r = subprocess.run([sys.executable, WORKER, grid, "--only", only], capture_output=True, text=True, timeout=1500, cwd=ROOT, env=e)
+    assert "WARNING: ThreadSanitizer" not in r.stderr, r.stderr[-6000:]
+    assert r.returncode == 0 and "HOSTSIM_PASS" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
