@@ -34,6 +34,7 @@ PACK, UNPACK, UNPACK_AXPY = 0, 1, 2
 LOWER, UPPER = 0, 1  # El::UpperOrLower
 LEFT, RIGHT = 0, 1   # El::LeftOrRight
 TRAP_SCALE, TRAP_AXPY, TRAP_MAKE = 0, 1, 2
+NON_UNIT, UNIT = 0, 1  # El::UnitOrNonUnit
 
 i64 = C.c_int64
 
@@ -105,6 +106,8 @@ SIGNATURES = {
     "elb200_peer_reduce_axpy_f64": (ci, [ci, C.POINTER(vp), i64, C.POINTER(Segment), vp, i64, f64, vp]),
     "elb200_trapezoid_f32": (ci, [ci, ci, i64, i64, i64, i64, i64, i64, i64, f32, vp, i64, vp, i64, vp]),
     "elb200_trapezoid_f64": (ci, [ci, ci, i64, i64, i64, i64, i64, i64, i64, f64, vp, i64, vp, i64, vp]),
+    "elb200_trsm_f32": (ci, [ci, ci, ci, ci, i64, i64, f32, vp, i64, vp, i64, vp]),
+    "elb200_trsm_f64": (ci, [ci, ci, ci, ci, i64, i64, f64, vp, i64, vp, i64, vp]),
     "elb200_plan_copy": (ci, [ci, ci, ci, C.POINTER(DistSpec), C.POINTER(DistSpec), C.POINTER(CopyPlan)]),
     "elb200_plan_contract": (ci, [ci, ci, ci, C.POINTER(DistSpec), C.POINTER(DistSpec), C.POINTER(ContractPlan)]),
     "elb200_plan_send_offset": (i64, [ci, ci, ci, C.POINTER(DistSpec), C.POINTER(DistSpec), ci]),
@@ -158,6 +161,8 @@ SIGNATURES = {
     "elb200_dist_trrk": (ci, [ci, ci, ci, f64, vp, vp, f64, vp]),
     "elb200_dist_syrk": (ci, [ci, ci, f64, vp, f64, vp]),
     "elb200_dist_symm": (ci, [ci, ci, f64, vp, vp, f64, vp]),
+    "elb200_dm_local_trsm": (ci, [ci, ci, ci, ci, f64, vp, vp]),
+    "elb200_dist_trsm": (ci, [ci, ci, ci, ci, f64, vp, vp, ci]),
     "elb200_dist_gemm_host_f32": (ci, [vp, ci, ci, i64, i64, i64, f32, vp, i64, vp, i64, f32, vp, i64]),
     "elb200_dist_gemm_host_f64": (ci, [vp, ci, ci, i64, i64, i64, f64, vp, i64, vp, i64, f64, vp, i64]),
 }

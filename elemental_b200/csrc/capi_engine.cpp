@@ -371,4 +371,13 @@ int elb200_dist_symm(int side, int uplo, double alpha, elb200_dm_t A, elb200_dm_
     });
 }
 
+int elb200_dm_local_trsm(int side, int uplo, int trans, int diag, double alpha, elb200_dm_t A, elb200_dm_t B) {
+    if (trans < 0 || trans > 2) return ELB200_ERR_ARG;
+    ELB_BINARY("elb200_dm_local_trsm", LocalTrsm(side, uplo, trans, diag, float(alpha), *A->f, *B->f), LocalTrsm(side, uplo, trans, diag, alpha, *A->d, *B->d))
+}
+int elb200_dist_trsm(int side, int uplo, int trans, int diag, double alpha, elb200_dm_t A, elb200_dm_t B, int alg) {
+    if (trans < 0 || trans > 2 || alg < 0 || alg > 3) return ELB200_ERR_ARG;
+    ELB_BINARY("elb200_dist_trsm", Trsm(side, uplo, trans, diag, float(alpha), *A->f, *B->f), Trsm(side, uplo, trans, diag, alpha, *A->d, *B->d))
+}
+
 }  // extern "C"

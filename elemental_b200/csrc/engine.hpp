@@ -153,6 +153,10 @@ void Trrk(int uplo, int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<
 template <typename T> void Syrk(int uplo, int trans, T alpha, const DistMat<T>& A, T beta, DistMat<T>& C);
 template <typename T>
 void Symm(int side, int uplo, T alpha, const DistMat<T>& A, const DistMat<T>& B, T beta, DistMat<T>& C);
+// B := alpha op(A)^-1 B (side LEFT) or alpha B op(A)^-1 (RIGHT); diag: 0 = NON_UNIT, 1 = UNIT
+// (reference src/blas_like/level3/Trsm.cpp:129-440, 501-526).
+template <typename T> void LocalTrsm(int side, int uplo, int trans, int diag, T alpha, const DistMat<T>& A, DistMat<T>& X);
+template <typename T> void Trsm(int side, int uplo, int trans, int diag, T alpha, const DistMat<T>& A, DistMat<T>& B);
 // src redistributed like tmp's distribution, aligned with `like`; returns src itself when that
 // redistribution is the identity on every rank (engine_gemm.cpp).
 template <typename T> const DistMat<T>& PanelAs(const DistMat<T>& src, DistMat<T>& tmp, const DistSpec& like);

@@ -49,6 +49,10 @@ template <> struct Dev<float> {
                           int64_t cstep, float al, const float* X, int64_t ldx, float* Y, int64_t ldy, cudaStream_t s) {
         throw_status(elb200_trapezoid_f32(op, uplo, offset, r, c, row0, rstep, col0, cstep, al, X, ldx, Y, ldy, s), "elb200_trapezoid_f32");
     }
+    static void trsm(int side, int uplo, int trans, int diag, int64_t m, int64_t n, float al, const float* A, int64_t lda, float* B,
+                     int64_t ldb, cudaStream_t s) {
+        throw_status(elb200_trsm_f32(side, uplo, trans, diag, m, n, al, A, lda, B, ldb, s), "elb200_trsm_f32");
+    }
 };
 
 template <> struct Dev<double> {
@@ -89,6 +93,10 @@ template <> struct Dev<double> {
     static void trapezoid(int op, int uplo, int64_t offset, int64_t r, int64_t c, int64_t row0, int64_t rstep, int64_t col0,
                           int64_t cstep, double al, const double* X, int64_t ldx, double* Y, int64_t ldy, cudaStream_t s) {
         throw_status(elb200_trapezoid_f64(op, uplo, offset, r, c, row0, rstep, col0, cstep, al, X, ldx, Y, ldy, s), "elb200_trapezoid_f64");
+    }
+    static void trsm(int side, int uplo, int trans, int diag, int64_t m, int64_t n, double al, const double* A, int64_t lda, double* B,
+                     int64_t ldb, cudaStream_t s) {
+        throw_status(elb200_trsm_f64(side, uplo, trans, diag, m, n, al, A, lda, B, ldb, s), "elb200_trsm_f64");
     }
 };
 

@@ -237,6 +237,96 @@ void Symm(int side, int uplo, T alpha, const DistMat<T>& A, const DistMat<T>& B,
     else Gemm(0, 0, alpha, B, Afull, beta, C, GEMM_DEFAULT);
 }
 
+// ---- Trsm -------------------------------------------------------------------------------------------
+// LocalTrsm (Trsm.cpp:501-526): A replicated ([*,*]), X distributed over the dimension that is NOT solved
+// ([*,V] for LEFT, [U,*] for RIGHT): every rank solves its own right-hand sides, no communication.
+template <typename T>
+void LocalTrsm(int side, int uplo, int trans, int diag, T alpha, const DistMat<T>& A, DistMat<T>& X) {
+    check_uplo(uplo, "LocalTrsm");
+    if ((side != 0 && side != 1) || (diag != 0 && diag != 1)) throw EngineError(ELB200_ERR_ARG, "LocalTrsm: bad side / diag");
+    if (A.grid != X.grid) throw EngineError(ELB200_ERR_ARG, "LocalTrsm: matrices live on different grids");
+    if (A.spec.col != STAR || A.spec.row != STAR || A.spec.height != A.spec.width)
+        throw EngineError(ELB200_ERR_ARG, "LocalTrsm: A must be a square [*,*] matrix");
+    if ((side == 0 && X.spec.col != STAR) || (side == 1 && X.spec.row != STAR))
+        throw EngineError(ELB200_ERR_ARG, "LocalTrsm: Dist of RHS must conform with that of triangle");  // Trsm.cpp:513-517
+    if (A.spec.height != (side == 0 ? X.spec.height : X.spec.width)) throw EngineError(ELB200_ERR_ARG, "LocalTrsm: nonconformal matrices");
+    Dev<T>::trsm(side, uplo, trans ? 1 : 0, diag, X.lh(), X.lw(), alpha, A.buf, A.ldim, X.buf, X.ldim, X.stream);
+}
+
+// Trsm (Trsm.cpp:129-440): the many-right-hand-sides schedule of trsm::{LLN,LLT,LUN,LUT}Large and
+// trsm::{RLN,RLT,RUN,RUT} for every side / uplo / orientation, written once: walk the diagonal blocks in
+// the direction of the substitution; per block  A11 -> [*,*],  X1 -> [*,VR] (LEFT) / [VC,*] (RIGHT),
+// LocalTrsm,  X1 -> [*,MR] / [MC,*] and back into X,  then ONE LocalGemm updates all remaining rows
+// (columns) of X with the panel of op(A) next to the block (LLN.hpp:37-68).  Blocks are 8 algorithmic
+// blocksizes wide (1024 by default) instead of one: the update GEMM gets a k deep enough for the tensor
+// pipe and X2 is re-read 8 x less often; the wider diagonal solve is itself recursive GEMMs (trsm.cu).
+template <typename T>
+void Trsm(int side, int uplo, int trans, int diag, T alpha, const DistMat<T>& Apre, DistMat<T>& Bpre) {
+    check_uplo(uplo, "Trsm");
+    if ((side != 0 && side != 1) || (diag != 0 && diag != 1)) throw EngineError(ELB200_ERR_ARG, "Trsm: bad side / diag");
+    trans = trans ? 1 : 0;
+    Grid& g = *Bpre.grid;
+    if (Apre.grid != &g) throw EngineError(ELB200_ERR_ARG, "Trsm: matrices live on different grids");
+    const int64_t na = Apre.spec.height;
+    if (Apre.spec.width != na) throw EngineError(ELB200_ERR_ARG, "Trsm: A must be square");             // Trsm.cpp:146-147
+    if (na != (side == 0 ? Bpre.spec.height : Bpre.spec.width)) throw EngineError(ELB200_ERR_ARG, "Trsm: nonconformal Trsm");
+    Scale(alpha, Bpre);                                                                                   // Trsm.cpp:158
+    if (Bpre.spec.height == 0 || Bpre.spec.width == 0 || alpha == T(0)) return;
+
+    const bool a_ok = Apre.spec.col == MC && Apre.spec.row == MR, b_ok = Bpre.spec.col == MC && Bpre.spec.row == MR;
+    DistMat<T> Ap(g, MC, MR, Bpre.stream), Bp(g, MC, MR, Bpre.stream);
+    if (!a_ok) Copy(Apre, Ap);
+    if (!b_ok) Copy(Bpre, Bp);
+    const DistMat<T>& A = a_ok ? Apre : Ap;
+    DistMat<T>& X = b_ok ? Bpre : Bp;
+    const int64_t m = X.spec.height, n = X.spec.width;
+
+    const int64_t W = 8 * int64_t(Grid::Blocksize());
+    const bool eff_lower = (uplo == LOWER) != (trans != 0);       // op(A) is lower triangular
+    const bool forward = side == 0 ? eff_lower : !eff_lower;      // LEFT: lower -> top down; RIGHT: upper -> left to right
+    cudaStream_t s = X.stream;
+    DistMat<T> A11s(g, STAR, STAR, s);
+    DistMat<T> X1v(g, side == 0 ? STAR : VC, side == 0 ? VR : STAR, s);   // every rank solves its share of the right-hand sides
+    DistMat<T> X1p(g, side == 0 ? STAR : MC, side == 0 ? MR : STAR, s);   // the solved block as a GEMM panel
+    DistMat<T> PA(g, side == 0 ? (trans ? STAR : MC) : (trans ? MR : STAR), side == 0 ? (trans ? MC : STAR) : (trans ? STAR : MR), s);
+    const int64_t nblocks = (na + W - 1) / W;
+    for (int64_t b = 0; b < nblocks; ++b) {
+        const int64_t blk = forward ? b : nblocks - 1 - b;
+        const int64_t k0 = blk * W, k1 = std::min(na, k0 + W);
+        const int64_t r0 = forward ? k1 : 0, r1 = forward ? na : k0;     // what is still to be updated
+        const DistMat<T> A11 = A.View(k0, k1, k0, k1);
+        A11s.col_constrained = A11s.row_constrained = false;
+        Copy(A11, A11s);
+        DistMat<T> X1 = side == 0 ? X.View(k0, k1, 0, n) : X.View(0, m, k0, k1);
+        X1v.col_constrained = X1v.row_constrained = false;
+        Copy(X1, X1v);
+        LocalTrsm(side, uplo, trans, diag, T(1), A11s, X1v);
+        X1p.col_constrained = X1p.row_constrained = false;
+        X1p.spec.col_align = X1p.spec.row_align = 0;
+        X1p.AlignWith(X.spec, true);
+        Copy(X1v, X1p);
+        Copy(X1p, X1);
+        if (r1 <= r0) continue;
+        if (side == 0) {
+            DistMat<T> X2 = X.View(r0, r1, 0, n);
+            // op(A)(rest, block): A(rest, block) as [MC,*], or (transposed) A(block, rest) as [*,MC]
+            const DistMat<T> Ap1 = trans ? A.View(k0, k1, r0, r1) : A.View(r0, r1, k0, k1);
+            const DistMat<T>& a = PanelAs(Ap1, PA, X2.spec);
+            LocalGemm(trans, 0, T(-1), a, X1p, T(1), X2);
+        } else {
+            DistMat<T> X2 = X.View(0, m, r0, r1);
+            // op(A)(block, rest): A(block, rest) as [*,MR], or (transposed) A(rest, block) as [MR,*]
+            const DistMat<T> Ap1 = trans ? A.View(r0, r1, k0, k1) : A.View(k0, k1, r0, r1);
+            const DistMat<T>& a = PanelAs(Ap1, PA, X2.spec);
+            LocalGemm(0, trans, T(-1), X1p, a, T(1), X2);
+        }
+    }
+    if (!b_ok) {
+        DistMat<T> back = Bpre.View(0, m, 0, n);
+        Copy(X, back);
+    }
+}
+
 #define ELB_INST3(T)                                                                                          \
     template void ScaleTrapezoid<T>(T, int, DistMat<T>&, int64_t);                                            \
     template void AxpyTrapezoid<T>(int, T, const DistMat<T>&, DistMat<T>&, int64_t);                          \
@@ -245,7 +335,9 @@ void Symm(int side, int uplo, T alpha, const DistMat<T>& A, const DistMat<T>& B,
     template void LocalTrrk<T>(int, int, int, T, const DistMat<T>&, const DistMat<T>&, T, DistMat<T>&);       \
     template void Trrk<T>(int, int, int, T, const DistMat<T>&, const DistMat<T>&, T, DistMat<T>&);            \
     template void Syrk<T>(int, int, T, const DistMat<T>&, T, DistMat<T>&);                                    \
-    template void Symm<T>(int, int, T, const DistMat<T>&, const DistMat<T>&, T, DistMat<T>&);
+    template void Symm<T>(int, int, T, const DistMat<T>&, const DistMat<T>&, T, DistMat<T>&);                 \
+    template void LocalTrsm<T>(int, int, int, int, T, const DistMat<T>&, DistMat<T>&);                         \
+    template void Trsm<T>(int, int, int, int, T, const DistMat<T>&, DistMat<T>&);
 ELB_INST3(float)
 ELB_INST3(double)
 #undef ELB_INST3

@@ -344,6 +344,21 @@ def Symm(side: int, uplo: int, alpha, A, B, beta, C_) -> None:
 Hemm = Symm
 
 
+NON_UNIT, UNIT = 0, 1  # El::UnitOrNonUnit (include/El/core/types.hpp:489-493)
+TRSM_DEFAULT, TRSM_LARGE, TRSM_MEDIUM, TRSM_SMALL = range(4)  # El::TrsmAlgorithm (level3.hpp:394-401)
+
+
+def LocalTrsm(side: int, uplo: int, orientation: int, diag: int, alpha, A, X, checkIfSingular: bool = False) -> None:
+    """src/blas_like/level3/Trsm.cpp:501-526: A is [*,*], X is [*,V] (LEFT) or [U,*] (RIGHT)."""
+    check(lib.elb200_dm_local_trsm(side, uplo, orientation, diag, alpha, A._h, X._h), "LocalTrsm")
+
+
+def Trsm(side: int, uplo: int, orientation: int, diag: int, alpha, A, B, checkIfSingular: bool = False,
+         alg: int = TRSM_DEFAULT) -> None:
+    """src/blas_like/level3/Trsm.cpp:474-499: B := alpha op(A)^-1 B (LEFT) or alpha B op(A)^-1 (RIGHT)."""
+    check(lib.elb200_dist_trsm(side, uplo, orientation, diag, alpha, A._h, B._h, alg), "Trsm")
+
+
 def GemmHost(grid: "Grid", orientA, orientB, m: int, n: int, k: int, alpha, A: torch.Tensor, lda: int,
              B: torch.Tensor, ldb: int, beta, C_: torch.Tensor, ldc: int) -> None:
     """El::Gemm on HOST operands: A, B, C_ are CPU tensors (pinned recommended) holding this rank's

@@ -31,6 +31,8 @@ enum Orientation { NORMAL, TRANSPOSE, ADJOINT };
 enum GridOrder { ROW_MAJOR, COLUMN_MAJOR };
 enum UpperOrLower { LOWER, UPPER };   // include/El/core/types.hpp:511-515
 enum LeftOrRight { LEFT, RIGHT };     // types.hpp:418-422
+enum UnitOrNonUnit { NON_UNIT, UNIT };  // types.hpp:489-493
+enum TrsmAlgorithm { TRSM_DEFAULT, TRSM_LARGE, TRSM_MEDIUM, TRSM_SMALL };  // level3.hpp:394-401
 // hydrogen::Device (include/hydrogen/Device.hpp): only GPU exists here — there is no CPU path
 enum class Device : unsigned char { CPU, GPU };
 enum GemmAlgorithm {
@@ -612,6 +614,21 @@ template <typename T, Dist UA, Dist VA, Dist UB, Dist VB, Dist UC, Dist VC_>
 void Hemm(LeftOrRight side, UpperOrLower uplo, T alpha, const DistMatrix<T, UA, VA>& A, const DistMatrix<T, UB, VB>& B, T beta,
           DistMatrix<T, UC, VC_>& C) {
     Symm(side, uplo, alpha, A, B, beta, C, true);
+}
+
+// B := alpha op(A)^-1 B (LEFT) or alpha B op(A)^-1 (RIGHT)  (Trsm.cpp:474-499). checkIfSingular is accepted and not
+// evaluated (the reference's GPU path, cuBLAS trsm, does not evaluate it either); every TrsmAlgorithm value runs the
+// many-right-hand-sides schedule.
+template <typename F, Dist UA, Dist VA, Dist UB, Dist VB>
+void Trsm(LeftOrRight side, UpperOrLower uplo, Orientation orientation, UnitOrNonUnit diag, F alpha, const DistMatrix<F, UA, VA>& A,
+          DistMatrix<F, UB, VB>& B, bool /*checkIfSingular*/ = false, TrsmAlgorithm alg = TRSM_DEFAULT) {
+    detail::Check(elb200_dist_trsm(int(side), int(uplo), int(orientation), int(diag), double(alpha), A.Handle(), B.Handle(), int(alg)), "Trsm");
+}
+// A replicated, X distributed over the dimension that is not solved (Trsm.cpp:501-526)
+template <typename F, Dist UX, Dist VX>
+void LocalTrsm(LeftOrRight side, UpperOrLower uplo, Orientation orientation, UnitOrNonUnit diag, F alpha,
+               const DistMatrix<F, STAR, STAR>& A, DistMatrix<F, UX, VX>& X, bool /*checkIfSingular*/ = false) {
+    detail::Check(elb200_dm_local_trsm(int(side), int(uplo), int(orientation), int(diag), double(alpha), A.Handle(), X.Handle()), "LocalTrsm");
 }
 
 // ---------------------------------------------------------------------------------------------

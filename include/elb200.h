@@ -198,6 +198,19 @@ int elb200_trapezoid_f64(int op, int uplo, int64_t offset, int64_t rows, int64_t
                          int64_t row_step, int64_t col0, int64_t col_step, double alpha, const double* X,
                          int64_t ldx, double* Y, int64_t ldy, void* stream);
 
+/* Local triangular solve with many right-hand sides, in place:
+ *   side ELB200_LEFT : op(A) X = alpha B, A is m x m      side ELB200_RIGHT: X op(A) = alpha B, A is n x n
+ * B (m x n, column-major) is overwritten with X; only the `uplo` triangle of A is referenced; diag = 1
+ * (El::UNIT) takes the diagonal as ones without reading it.  Replaces gpu_blas::Trsm -> cublas{S,D}trsm
+ * (include/hydrogen/blas/GPU_BLAS_impl.hpp; src/blas_like/level3/Trsm.cpp:26-50), reached from
+ * Trsm(Matrix<F,GPU>) and LocalTrsm (Trsm.cpp:501-526).  Recursive blocking: off-diagonal updates are
+ * elb200_gemm_* calls, 32 x 32 diagonal blocks are solved by trsm_base_kernel. */
+typedef enum elb200_diag { ELB200_NON_UNIT = 0, ELB200_UNIT = 1 } elb200_diag;  /* El::UnitOrNonUnit */
+int elb200_trsm_f32(int side, int uplo, int trans, int diag, int64_t m, int64_t n, float alpha,
+                    const float* A, int64_t lda, float* B, int64_t ldb, void* stream);
+int elb200_trsm_f64(int side, int uplo, int trans, int diag, int64_t m, int64_t n, double alpha,
+                    const double* A, int64_t lda, double* B, int64_t ldb, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Redistribution planner (pure host code; callable without a GPU).
  * For an r x c grid (COLUMN_MAJOR: VC rank = mc + r*mr, reference src/core/Grid.cpp:147-148) and
@@ -381,6 +394,14 @@ int elb200_dist_trrk(int uplo, int transA, int transB, double alpha, elb200_dm_t
 int elb200_dist_syrk(int uplo, int trans, double alpha, elb200_dm_t A, double beta, elb200_dm_t C);
 int elb200_dist_symm(int side, int uplo, double alpha, elb200_dm_t A, elb200_dm_t B, double beta,
                      elb200_dm_t C);
+/* El::Trsm(side, uplo, orientation, diag, alpha, A, B, checkIfSingular, alg) on DistMatrices
+ * (src/blas_like/level3/Trsm.cpp:129-440, Trsm/{LLN,LLT,LUN,LUT,RLN,RLT,RUN,RUT}.hpp): B := alpha op(A)^-1 B
+ * (LEFT) or alpha B op(A)^-1 (RIGHT).  alg: El::TrsmAlgorithm values (0 DEFAULT, 1 LARGE, 2 MEDIUM, 3 SMALL);
+ * every value runs the many-right-hand-sides schedule (the *Large variants).  checkIfSingular is not
+ * evaluated (the reference's GPU path does not evaluate it either: cuBLAS trsm has no such check).
+ * El::LocalTrsm (Trsm.cpp:501-526): A is [*,*], X is [*,V] (LEFT) or [U,*] (RIGHT); purely local. */
+int elb200_dm_local_trsm(int side, int uplo, int trans, int diag, double alpha, elb200_dm_t A, elb200_dm_t X);
+int elb200_dist_trsm(int side, int uplo, int trans, int diag, double alpha, elb200_dm_t A, elb200_dm_t B, int alg);
 
 /* El::Gemm with every operand in HOST memory (the reference reaches this case through its
  * CPU<->GPU proxies, include/El/core/ProxyDevice.hpp + Matrix<T,GPU> = Matrix<T,CPU> copies,

@@ -192,3 +192,89 @@ def symm_global(side, uplo, alpha, A, B, beta, C, acc=np.longdouble) -> np.ndarr
     S = np.where(trapezoid_mask(*Aa.shape, uplo, 0), Aa, 0) + np.where(trapezoid_mask(*Aa.shape, uplo, -1 if uplo == LOWER else 1), Aa, 0).T
     Ba, Ca = np.asarray(B, dtype=acc), np.asarray(C, dtype=acc)
     return acc(alpha) * (S @ Ba if side == LEFT else Ba @ S) + acc(beta) * Ca
+
+
+# ----------------------------------------------------------------------------- Trsm
+NON_UNIT, UNIT = 0, 1  # El::UnitOrNonUnit (types.hpp:489-493)
+
+
+def _tri_solve(side, uplo, orient, diag, A, B):
+    """op(A) X = B (LEFT) or X op(A) = B (RIGHT) by substitution in the operands' dtype (longdouble allowed);
+    only the `uplo` triangle of A is read. What BLAS trsm computes (src/core/imports/blas/Trsm.hpp)."""
+    A = np.asarray(A)
+    E = np.tril(A) if uplo == LOWER else np.triu(A)
+    e_lower = (uplo == LOWER) != bool(orient)      # op(A) is lower triangular
+    if orient != NORMAL:
+        E = E.T
+    if side == RIGHT:                               # X E = B  <=>  E^T X^T = B^T
+        return _tri_solve(LEFT, UPPER if e_lower else LOWER, NORMAL, diag, E.T, np.asarray(B).T).T
+    n = E.shape[0]
+    X = np.array(B, dtype=np.result_type(E.dtype, np.asarray(B).dtype), copy=True)
+    for i in (range(n) if e_lower else range(n - 1, -1, -1)):
+        if e_lower:
+            X[i, :] -= E[i, :i] @ X[:i, :]
+        else:
+            X[i, :] -= E[i, i + 1:] @ X[i + 1:, :]
+        if diag != UNIT:
+            X[i, :] /= E[i, i]
+    return X
+
+
+def trsm_global(side, uplo, orient, diag, alpha, A, B, acc=np.longdouble) -> np.ndarray:
+    """B := alpha op(A)^-1 B (LEFT) or alpha B op(A)^-1 (RIGHT), computed in `acc`."""
+    Aa = np.asarray(A, dtype=acc)
+    if diag == UNIT:
+        Aa = Aa.copy()
+        np.fill_diagonal(Aa, 1)
+    return _tri_solve(side, uplo, orient, NON_UNIT, Aa, acc(alpha) * np.asarray(B, dtype=acc))
+
+
+def trsm(side, uplo, orient, diag, alpha, A: VDM, B: VDM, nb: int = 128) -> None:
+    """Trsm on [MC,MR] operands (Trsm.cpp:129-440): B *= alpha, then the block loop of trsm::LLNLarge
+    (Trsm/LLN.hpp:37-68) and its LLT / LUN / LUT / RLN / RLT / RUN / RUT twins: per nb block in the direction
+    of the substitution  A11 -> [*,*],  X1 -> [*,VR] (LEFT) / [VC,*] (RIGHT),  LocalTrsm on every rank's share,
+    X1 -> [*,MR] / [MC,*] and back into X,  LocalGemm update of the remaining rows / columns."""
+    from .dist import VC, VR
+    g = B.g
+    t = 1 if orient else 0
+    dt = B.loc[0].dtype
+    for q in range(g.p):
+        B.loc[q] *= dt.type(alpha)
+    na = A.spec.height
+    m, n = B.spec.height, B.spec.width
+    eff_lower = (uplo == LOWER) != bool(t)
+    forward = eff_lower if side == LEFT else not eff_lower
+    starts = list(range(0, na, nb))
+    for k0 in (starts if forward else reversed(starts)):
+        k1 = min(na, k0 + nb)
+        r0, r1 = (k1, na) if forward else (0, k0)
+        A11 = redistribute(A.view(k0, k1, k0, k1), STAR, STAR)
+        X1 = B.view(k0, k1, 0, n) if side == LEFT else B.view(0, m, k0, k1)
+        X1v = redistribute(X1, STAR, VR, 0, X1.spec.row_align) if side == LEFT else redistribute(X1, VC, STAR, X1.spec.col_align, 0)
+        for q in range(g.p):
+            if X1v.loc[q].size:
+                X1v.loc[q][...] = _tri_solve(side, uplo, t, diag, _unit(A11.loc[q], diag), X1v.loc[q]).astype(dt)
+        X1p = (redistribute(X1v, STAR, MR, 0, B.spec.row_align) if side == LEFT else redistribute(X1v, MC, STAR, B.spec.col_align, 0))
+        back = redistribute(X1p, MC, MR, X1.spec.col_align, X1.spec.row_align)
+        for q in range(g.p):
+            X1.loc[q][...] = back.loc[q]
+        if r1 <= r0:
+            continue
+        if side == LEFT:
+            X2 = B.view(r0, r1, 0, n)
+            Ap = A.view(k0, k1, r0, r1) if t else A.view(r0, r1, k0, k1)
+            a = redistribute(Ap, STAR, MC, 0, X2.spec.col_align) if t else redistribute(Ap, MC, STAR, X2.spec.col_align, 0)
+            _local_gemm(t, 0, -1, a, X1p, 1, X2)
+        else:
+            X2 = B.view(0, m, r0, r1)
+            Ap = A.view(r0, r1, k0, k1) if t else A.view(k0, k1, r0, r1)
+            a = redistribute(Ap, MR, STAR, X2.spec.row_align, 0) if t else redistribute(Ap, STAR, MR, 0, X2.spec.row_align)
+            _local_gemm(0, t, -1, X1p, a, 1, X2)
+
+
+def _unit(A11: np.ndarray, diag: int) -> np.ndarray:
+    if diag != UNIT:
+        return A11
+    out = A11.copy()
+    np.fill_diagonal(out, 1)
+    return out

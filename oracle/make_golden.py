@@ -163,7 +163,8 @@ def make_level3_golden() -> None:
     tests/golden/ref_level3.npz, per grid tag g and rank q:
       {g}_q{q}_L    rows [kind uplo p1 p2 colAlign rowAlign colShift rowShift lh lw offset]
                     kind 0 ScaleTrapezoid(-0.5) 1 MakeTrapezoidal 2 AxpyTrapezoid(2.0) (p1 = offset); 3 MakeSymmetric;
-                    4 LocalTrrk 5 Trrk (p1, p2 = orientation of A, B); 6 Syrk (p1 = orientation); 7 Symm (p1 = side)
+                    4 LocalTrrk 5 Trrk (p1, p2 = orientation of A, B); 6 Syrk (p1 = orientation); 7 Symm (p1 = side);
+                    8 Trsm (p1 = side, p2 = 2*orientation + diag; alpha 2, A = LCG + n on the diagonal, or LCG / n for UNIT)
       {g}_q{q}_bin  float64 blob (column-major local results)
     Inputs are LCG matrices (lcg_matrix) with seeds 7001 (A), 7002 (B), 7003 (C), 7004 (X); sizes and
     scalars as in oracle/ref_build/gemm_ref.cpp::level3_golden."""
@@ -174,7 +175,7 @@ def make_level3_golden() -> None:
             _run_ranks(["--level3-golden", tmp, str(height)], nproc, "l3" + tag)
             for q in range(nproc):
                 recs = [[int(x) for x in ln.split()[1:]] for ln in open(os.path.join(tmp, f"l3rank{q}.txt"))]
-                assert len(recs) == 12 + 6 + 2 + 8 + 8 + 4 + 4, (tag, q, len(recs))
+                assert len(recs) == 12 + 6 + 2 + 8 + 8 + 4 + 4 + 16, (tag, q, len(recs))
                 arrays[f"{tag}_q{q}_L"] = np.array(recs, dtype=np.int64)
                 arrays[f"{tag}_q{q}_bin"] = np.fromfile(os.path.join(tmp, f"l3rank{q}.bin"), dtype=np.float64)
     np.savez_compressed(os.path.join(OUT, "ref_level3.npz"), **arrays)

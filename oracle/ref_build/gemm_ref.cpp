@@ -327,6 +327,21 @@ static void level3_golden(const std::string& dir, int gridHeight) {
             Symm(sides[sd], uplos[u], 2.0, A, B, 3.0, C);
             l3_record(out, 7, u, sd, 0, C);
         }
+    // kind 8: Trsm, every side / uplo / orientation / diag (p1 = side, p2 = 2*orientation + diag); A = LCG + n on the
+    // diagonal (well conditioned; for UNIT the strict triangle is scaled by 1/n instead), blocksize 16
+    for (int sd = 0; sd < 2; ++sd)
+        for (int u = 0; u < 2; ++u)
+            for (int it = 0; it < 2; ++it)
+                for (int dg = 0; dg < 2; ++dg) {
+                    DistMatrix<double> A(g), B(g);
+                    A.Align(ca, 0); B.Align(0, ra);
+                    fill_dm_lcg(A, n, n, 7001);
+                    if (dg) Scale(1.0 / double(n), A);
+                    else ShiftDiagonal(A, double(n));
+                    fill_dm_lcg(B, sd ? m2 : n, sd ? n : m2, 7002);
+                    Trsm(sides[sd], uplos[u], os[it], dg ? UNIT : NON_UNIT, 2.0, A, B);
+                    l3_record(out, 8, u, sd, 2 * it + dg, B);
+                }
 }
 
 int main(int argc, char* argv[]) {

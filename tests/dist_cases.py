@@ -472,7 +472,7 @@ def check_level3(grid, dtype=torch.float64, trrk_blocksize=8) -> int:
 def check_level3_golden(grid, dtype=torch.float64) -> int:
     """The REFERENCE'S OWN per-rank outputs (tests/golden/ref_level3.npz: its CPU build run multi-rank on
     this grid shape) against this library: trapezoid routines and MakeSymmetric bit for bit, LocalTrrk /
-    Trrk / Syrk / Symm within the fp64 Gemm bound.  Grids the reference was not run on return 0."""
+    Trrk / Syrk / Symm / Trsm within the fp64 Gemm bound.  Grids the reference was not run on return 0."""
     import os
     from oracle.make_golden import lcg_matrix
     assert dtype == torch.float64
@@ -516,12 +516,19 @@ def check_level3_golden(grid, dtype=torch.float64) -> int:
                 A = DM(el.MC, el.MR, ca, 0, lcg_matrix(*((k, n) if p1 else (n, k)), 7001, f64))
                 R = DM(el.MC, el.MR, 0, ra, lcg_matrix(n, n, 7003, f64))
                 el.Syrk(uplo, p1, 2.0, A, 3.0, R)
-            else:
+            elif kind == 7:
                 shape = (m2, n) if p1 else (n, m2)
                 A = DM(el.MC, el.MR, ca, ra, lcg_matrix(n, n, 7001, f64))
                 B = DM(el.MC, el.MR, 0, 0, lcg_matrix(*shape, 7002, f64))
                 R = DM(el.MC, el.MR, 0, ra, lcg_matrix(*shape, 7003, f64))
                 el.Symm(p1, uplo, 2.0, A, B, 3.0, R)
+            else:
+                side, orient, diag = p1, p2 // 2, p2 % 2
+                Ag = lcg_matrix(n, n, 7001, f64)
+                Ag = Ag * (1.0 / float(n)) if diag else Ag + float(n) * np.eye(n)
+                A = DM(el.MC, el.MR, ca, 0, Ag)
+                R = DM(el.MC, el.MR, 0, ra, lcg_matrix(*((m2, n) if side else (n, m2)), 7002, f64))
+                el.Trsm(side, uplo, orient, diag, 2.0, A, R)
             assert (R.ColAlign(), R.RowAlign(), R.ColShift(), R.RowShift()) == (caC, raC, cs, rs), (tag, kind, uplo, p1, p2)
             got = R.get_local()
             ref = blob[off:off + lh * lw].reshape((lh, lw), order="F")
@@ -590,11 +597,64 @@ def check_dist_golden(grid, dtype=torch.float64) -> int:
     return cnt
 
 
+def check_trsm(grid, dtype=torch.float64) -> int:
+    """LocalTrsm and Trsm for every side / uplo / orientation / diag against the substitution in long double
+    (oracle.level3.trsm_global). A is well conditioned (unit-scale entries + n on the diagonal), the triangle
+    that must not be referenced is poisoned with NaN. Blocksize 8 -> blocks of 64: several diagonal blocks and
+    update GEMMs at n = 150; m2 = 45 right-hand sides; B misaligned; one case with operands that need proxies."""
+    og = _grid_oracle(grid)
+    npdt = NPDT[dtype]
+    me = grid.Rank()
+    n, m2 = 150, 45
+    cnt = 0
+    A0 = OG.uniform_matrix(n, n, 401, npdt, 0.0, 1.0) + npdt(n) * np.eye(n, dtype=npdt)
+    el.PushBlocksizeStack(8)
+    try:
+        for side, uplo, t, diag in itertools.product((el.LEFT, el.RIGHT), (el.LOWER, el.UPPER), (0, 1), (el.NON_UNIT, el.UNIT)):
+            keep = O3.trapezoid_mask(n, n, uplo, 0)
+            Apoison = np.asfortranarray(np.where(keep, A0, npdt(np.nan)))
+            if diag == el.UNIT:   # the diagonal must not be read either
+                Apoison[np.arange(n), np.arange(n)] = np.nan
+            # UNIT makes the off-diagonal part dominant unless it is scaled down
+            Ause = np.asfortranarray(np.where(np.eye(n, dtype=bool), Apoison, Apoison / npdt(n))) if diag == el.UNIT else Apoison
+            Aref = np.where(keep, A0 / (npdt(n) if diag == el.UNIT else npdt(1)), 0)
+            B0 = OG.uniform_matrix(*((n, m2) if side == el.LEFT else (m2, n)), 402, npdt, 0.0, 1.0)
+            ref = O3.trsm_global(side, uplo, t, diag, 2.0, Aref, B0)
+            proxies = (side == el.LEFT and uplo == el.UPPER and t == 1)
+            dA = el.DistMatrix(grid, *((el.VC, el.STAR) if proxies else (el.MC, el.MR)), dtype).Align(1 % og.r if not proxies else 1 % og.p, 0).from_global(Ause)
+            dB = el.DistMatrix(grid, *((el.STAR, el.VR) if proxies else (el.MC, el.MR)), dtype).Align(0, 2 % (og.p if proxies else og.c)).from_global(B0)
+            el.Trsm(side, uplo, t, diag, 2.0, dA, dB)
+            spec = OD.Spec(OD.STAR if proxies else OD.MC, OD.VR if proxies else OD.MR, dB.ColAlign(), dB.RowAlign(), *B0.shape)
+            got = dB.get_local()
+            assert np.isfinite(got).all(), ("Trsm read the unreferenced triangle / diagonal", side, uplo, t, diag)
+            err, tol = _tri_err(got, ref, spec, og, me, npdt, n)
+            assert err <= 4 * tol, ("Trsm", side, uplo, t, diag, err, tol)
+            cnt += 1
+            # LocalTrsm: A replicated, every rank solves its own right-hand sides
+            for nl in ((40, 150) if (t == 0 or diag == el.NON_UNIT) else ()):   # 150: three levels of the local recursion
+                Al = np.asfortranarray(Ause[:nl, :nl])
+                Bl0 = OG.uniform_matrix(*((nl, m2) if side == el.LEFT else (m2, nl)), 403, npdt, 0.0, 1.0)
+                dAl = el.DistMatrix(grid, el.STAR, el.STAR, dtype).from_global(Al)
+                dX = el.DistMatrix(grid, *((el.STAR, el.VR) if side == el.LEFT else (el.VC, el.STAR)), dtype).from_global(Bl0)
+                el.LocalTrsm(side, uplo, t, diag, 0.5, dAl, dX)
+                refl = O3.trsm_global(side, uplo, t, diag, 0.5, Aref[:nl, :nl], Bl0)
+                specl = OD.Spec(OD.STAR if side == el.LEFT else OD.VC, OD.VR if side == el.LEFT else OD.STAR, 0, 0, *Bl0.shape)
+                got = dX.get_local()
+                assert np.isfinite(got).all(), ("LocalTrsm read the unreferenced triangle / diagonal", side, uplo, t, diag, nl)
+                errl, toll = _tri_err(got, refl, specl, og, me, npdt, nl)
+                assert errl <= 4 * toll, ("LocalTrsm", side, uplo, t, diag, nl, errl, toll)
+                cnt += 1
+    finally:
+        el.PopBlocksizeStack()
+    return cnt
+
+
 def run_level3(grid) -> dict:
     """The triangular rank-k family and the comparisons with the reference's own per-rank outputs."""
     out = {}
     out["trapezoids"] = check_trapezoids(grid, torch.float64) + check_trapezoids(grid, torch.float32)
     out["level3"] = check_level3(grid, torch.float64) + check_level3(grid, torch.float32)
+    out["trsm"] = check_trsm(grid, torch.float64) + check_trsm(grid, torch.float32)
     out["level3_ref_golden"] = check_level3_golden(grid)
     out["dist_ref_golden"] = check_dist_golden(grid)
     return out

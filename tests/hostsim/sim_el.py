@@ -267,6 +267,21 @@ def Symm(side: int, uplo: int, alpha, A, B, beta, C_) -> None:
 Hemm = Symm
 
 
+NON_UNIT, UNIT = 0, 1  # El::UnitOrNonUnit (include/El/core/types.hpp:489-493)
+TRSM_DEFAULT, TRSM_LARGE, TRSM_MEDIUM, TRSM_SMALL = range(4)  # El::TrsmAlgorithm (level3.hpp:394-401)
+
+
+def LocalTrsm(side: int, uplo: int, orientation: int, diag: int, alpha, A, X, checkIfSingular: bool = False) -> None:
+    """src/blas_like/level3/Trsm.cpp:501-526: A is [*,*], X is [*,V] (LEFT) or [U,*] (RIGHT)."""
+    check(lib.elb200_dm_local_trsm(side, uplo, orientation, diag, alpha, A._h, X._h), "LocalTrsm")
+
+
+def Trsm(side: int, uplo: int, orientation: int, diag: int, alpha, A, B, checkIfSingular: bool = False,
+         alg: int = TRSM_DEFAULT) -> None:
+    """src/blas_like/level3/Trsm.cpp:474-499: B := alpha op(A)^-1 B (LEFT) or alpha B op(A)^-1 (RIGHT)."""
+    check(lib.elb200_dist_trsm(side, uplo, orientation, diag, alpha, A._h, B._h, alg), "Trsm")
+
+
 def GemmHost(grid, orientA, orientB, m, n, k, alpha, A: torch.Tensor, lda, B: torch.Tensor, ldb, beta, C_: torch.Tensor, ldc):
     fn = lib.elb200_dist_gemm_host_f32 if C_.dtype == torch.float32 else lib.elb200_dist_gemm_host_f64
     check(fn(grid._h, orientA, orientB, m, n, k, alpha, A.data_ptr(), lda, B.data_ptr(), ldb, beta, C_.data_ptr(), ldc), "GemmHost")

@@ -9,6 +9,7 @@
 #include <vector>
 
 #include "../../include/elb200.h"
+#include "../../elemental_b200/csrc/trsm_rec.hpp"
 #include "sim.hpp"
 
 namespace elb {
@@ -196,6 +197,67 @@ int trapezoid(int op, int uplo, int64_t offset, int64_t rows, int64_t cols, int6
     return ELB200_OK;
 }
 
+// Base-case solve (triangle <= kTrsmBase): straightforward substitution in double precision, one right-hand
+// side at a time, enqueued like a kernel. alpha has been applied by the caller.
+template <typename T>
+int trsm_base(bool left, bool lower, bool tr, bool unit, int64_t m, int64_t n, const T* A, int64_t lda, T* B, int64_t ldb, void* s) {
+    const int64_t na = left ? m : n;
+    if (na > elb::kTrsmBase) sim::fail("trsm base case called with a %lld x %lld triangle", (long long)na, (long long)na);
+    count_launch();
+    sim::enqueue(st(s), [=] {
+        check_lattice(A, na, na, 1, lda, "trsm A");
+        check_lattice(B, m, n, 1, ldb, "trsm B");
+        const bool eff_lower = lower != tr;
+        // E(i,j) = op(A)(i,j), read only inside the stored triangle (and never on a UNIT diagonal)
+        auto E = [&](int64_t i, int64_t j) { return double(tr ? A[j + i * lda] : A[i + j * lda]); };
+        std::vector<double> x(static_cast<size_t>(na));
+        const int64_t nrhs = left ? n : m;
+        // LEFT: E x = b. RIGHT: x^T E = b^T  <=>  E^T x = b, i.e. the same substitution with E transposed.
+        const bool fwd = left ? eff_lower : !eff_lower;
+        for (int64_t r = 0; r < nrhs; ++r) {
+            auto b = [&](int64_t i) -> T& { return left ? B[i + r * ldb] : B[r + i * ldb]; };
+            for (int64_t t = 0; t < na; ++t) {
+                const int64_t i = fwd ? t : na - 1 - t;
+                double sum = double(b(i));
+                if (fwd) for (int64_t j = 0; j < i; ++j) sum -= (left ? E(i, j) : E(j, i)) * x[j];
+                else for (int64_t j = i + 1; j < na; ++j) sum -= (left ? E(i, j) : E(j, i)) * x[j];
+                x[i] = unit ? sum : sum / E(i, i);
+            }
+            for (int64_t i = 0; i < na; ++i) b(i) = T(x[i]);
+        }
+    });
+    return ELB200_OK;
+}
+
+template <typename T>
+int gemm(int ta, int tb, int64_t m, int64_t n, int64_t k, T alpha, const T* A, int64_t lda, const T* B, int64_t ldb, T beta,
+         T* C, int64_t ldc, void* s);
+
+// The REAL recursion of the product (elemental_b200/csrc/trsm_rec.hpp) over the doubles above.
+template <typename T>
+struct SimBackend {
+    void* s;
+    int gemm(int ta, int tb, int64_t m, int64_t n, int64_t k, T al, const T* A, int64_t lda, const T* B, int64_t ldb, T be, T* C,
+             int64_t ldc) { return ::gemm<T>(ta, tb, m, n, k, al, A, lda, B, ldb, be, C, ldc, s); }
+    int base(bool left, bool lower, bool trans, bool unit, int64_t m, int64_t n, const T* A, int64_t lda, T* B, int64_t ldb) {
+        return trsm_base<T>(left, lower, trans, unit, m, n, A, lda, B, ldb, s);
+    }
+};
+
+template <typename T>
+int trsm(int side, int uplo, int trans, int diag, int64_t m, int64_t n, T alpha, const T* A, int64_t lda, T* B, int64_t ldb, void* s) {
+    if (side < 0 || side > 1 || uplo < 0 || uplo > 1 || trans < 0 || trans > 2 || diag < 0 || diag > 1 || m < 0 || n < 0)
+        return ELB200_ERR_ARG;
+    const int64_t na = side == 0 ? m : n;
+    if (lda < (na > 1 ? na : 1) || ldb < (m > 1 ? m : 1)) return ELB200_ERR_ARG;
+    if (m == 0 || n == 0) return ELB200_OK;
+    if (!A || !B) return ELB200_ERR_ARG;
+    int stt = scale2d<T>(m, n, alpha, B, ldb, s);
+    if (stt != ELB200_OK || alpha == T(0)) return stt;
+    SimBackend<T> be{s};
+    return elb::trsm_recursive<T>(be, side == 0, uplo == ELB200_LOWER, trans != 0, diag == ELB200_UNIT, m, n, A, lda, B, ldb);
+}
+
 int check_gemm_args(int transA, int transB, int64_t m, int64_t n, int64_t k, const void* A, int64_t lda, const void* B,
                     int64_t ldb, const void* C, int64_t ldc) {
     if (transA < 0 || transA > 2 || transB < 0 || transB > 2) return ELB200_ERR_ARG;
@@ -295,6 +357,10 @@ int elb200_trapezoid_f64(int op, int uplo, int64_t off, int64_t r, int64_t c, in
                          const double* X, int64_t ldx, double* Y, int64_t ldy, void* s) {
     return trapezoid<double>(op, uplo, off, r, c, r0, rs, c0, cs, al, X, ldx, Y, ldy, s);
 }
+int elb200_trsm_f32(int side, int uplo, int trans, int diag, int64_t m, int64_t n, float al, const float* A, int64_t lda, float* B,
+                    int64_t ldb, void* s) { return trsm<float>(side, uplo, trans, diag, m, n, al, A, lda, B, ldb, s); }
+int elb200_trsm_f64(int side, int uplo, int trans, int diag, int64_t m, int64_t n, double al, const double* A, int64_t lda, double* B,
+                    int64_t ldb, void* s) { return trsm<double>(side, uplo, trans, diag, m, n, al, A, lda, B, ldb, s); }
 SIM_BLAS1(f32, float)
 SIM_BLAS1(f64, double)
 #undef SIM_BLAS1

@@ -1,6 +1,6 @@
 """GPU parity of the triangular rank-k family: the trapezoid kernel through the device
 C ABI, then ScaleTrapezoid / AxpyTrapezoid / MakeTrapezoidal / MakeSymmetric, LocalTrrk, Trrk, Syrk /
-Herk, Symm / Hemm through the handle ABI on a 1 x 1 grid (and on r x c grids under torchrun when
+Herk, Symm / Hemm, Trsm / LocalTrsm through the handle ABI on a 1 x 1 grid (and on r x c grids under torchrun when
 several GPUs are visible) — against the oracle (oracle/level3.py) and against the REFERENCE'S OWN
 outputs (tests/golden/ref_level3.npz, ref_dist.npz).  Sorted after the Gemm-path test files on purpose.
 """
@@ -78,12 +78,6 @@ def test_level3_1x1(grid1, dtype):
     assert dc.check_level3(grid1, dtype) == 44
 
 
-def test_level3_matches_reference_outputs_1x1(grid1):
-    """This library against the reference's own outputs for the same inputs (its CPU build, 1 x 1)."""
-    from tests import dist_cases as dc
-    assert dc.check_level3_golden(grid1) == 44
-
-
 @pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
 def test_syrk_symm_large_properties(grid1, dtype):
     """Bench-class size (n = 4096, k = 2048; several LocalTrrk recursion levels with the default blocksize)
@@ -136,6 +130,57 @@ def test_syrk_symm_large_properties(grid1, dtype):
         finite = bool(torch.isfinite(C1.Matrix()).all())
     grid1.sync()
     assert finite and e2 <= 2 * OG.gemm_tolerance(npdt, n), (finite, e2)
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_trsm_kernel(L, dtype):
+    """elb200_trsm_*: every side / uplo / orientation / diag at sizes that stop in the base kernel (<= 32), split
+    once, and recurse several levels (1000), ragged, padded leading dimensions; the triangle (and UNIT diagonal)
+    that must not be referenced holds NaN. Against the long-double substitution within 4x the Gemm bound."""
+    import itertools
+    fn = getattr(L.lib, f"elb200_trsm_{SUF[dtype]}")
+    rng = np.random.default_rng(17)
+    for (na, nrhs) in ((1, 5), (32, 130), (47, 300), (200, 333), (1000, 257)):
+        combos = list(itertools.product((L.LEFT, L.RIGHT), (L.LOWER, L.UPPER), (0, 1), (L.NON_UNIT, L.UNIT)))
+        if na == 1000:
+            combos = combos[::3]
+        A0 = rng.uniform(-1, 1, (na, na))
+        for side, uplo, t, diag in combos:
+            keep = O3.trapezoid_mask(na, na, uplo, 0)
+            Aref = np.where(keep, A0 / na if diag == L.UNIT else A0 + na * np.eye(na), 0.0)
+            Adev = np.where(keep, Aref, np.nan)
+            if diag == L.UNIT:
+                Adev[np.arange(na), np.arange(na)] = np.nan
+            m, n = (na, nrhs) if side == L.LEFT else (nrhs, na)
+            B0 = rng.uniform(-1, 1, (m, n)).astype(dtype)
+            lda, ldb = na + 3, m + 5
+            abuf = np.full((na, lda), np.nan, dtype=dtype); abuf[:, :na] = Adev.T.astype(dtype)   # abuf[j, i] = A(i, j)
+            bbuf = np.full((n, ldb), np.nan, dtype=dtype); bbuf[:, :m] = B0.T
+            a, b = torch.from_numpy(abuf).cuda(), torch.from_numpy(bbuf).cuda()
+            L.check(fn(side, uplo, t, diag, m, n, 2.0, a.data_ptr(), lda, b.data_ptr(), ldb, 0), "trsm")
+            torch.cuda.synchronize()
+            got = b.cpu().numpy()
+            assert np.isnan(got[:, m:]).all(), "padding rows of B were written"
+            X = got[:, :m].T
+            assert np.isfinite(X).all(), ("read the unreferenced triangle / diagonal", na, side, uplo, t, diag)
+            ref = O3.trsm_global(side, uplo, t, diag, 2.0, Aref.astype(dtype), B0)
+            err = OG.frobenius_rel_err(X, ref)
+            assert err <= 4 * OG.gemm_tolerance(dtype, na), (na, nrhs, side, uplo, t, diag, err)
+    x = torch.zeros(16, dtype=torch.float32 if dtype == np.float32 else torch.float64, device="cuda")
+    assert fn(2, 0, 0, 0, 4, 4, 1.0, x.data_ptr(), 4, x.data_ptr(), 4, 0) == 2      # bad side
+    assert fn(0, 0, 0, 0, 4, 4, 1.0, x.data_ptr(), 3, x.data_ptr(), 4, 0) == 2      # lda < m
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+def test_trsm_1x1(grid1, dtype):
+    from tests import dist_cases as dc
+    assert dc.check_trsm(grid1, dtype) == 40
+
+
+def test_level3_matches_reference_outputs_1x1(grid1):
+    """This library against the reference's own outputs for the same inputs (its CPU build, 1 x 1)."""
+    from tests import dist_cases as dc
+    assert dc.check_level3_golden(grid1) == 60
 
 
 def test_el_level3_check_facade():

@@ -37,24 +37,24 @@ def _run(grid, *args, env=None, timeout=900):
 
 def test_engine_1x1_all_cases(simlib):
     out = _run("1x1", "--only", "run_all,run_level3")
-    assert "'redist_f64': 121" in out and "'gemm_f64': 40" in out and "'gemm_host': 24" in out and "'level3_ref_golden': 44" in out
+    assert "'redist_f64': 121" in out and "'gemm_f64': 40" in out and "'gemm_host': 24" in out and "'level3_ref_golden': 60" in out
 
 
 def test_engine_2x2_peer_arena_all_cases(simlib):
     """Every case on a 2 x 2 grid with the NVLink peer-arena paths (copy-engine AllGather, pull
     exchange, receiver-side reduce) — the paths the multi-GPU bench runs — plus the engine against the
     REFERENCE'S OWN per-rank outputs on this grid shape (run_level3: tests/golden/ref_dist.npz, 121
-    redistributions + 23 [CIRC,CIRC] cases + 20 Gemm runs; ref_level3.npz, 44 level-3 records)."""
+    redistributions + 23 [CIRC,CIRC] cases + 20 Gemm runs; ref_level3.npz, 60 level-3 records)."""
     out = _run("2x2", "--only", "run_all,run_level3")
     assert "'redist_f64': 121" in out and "'circ': 54" in out and "'gemm_f32': 40" in out
-    assert "'level3_ref_golden': 44" in out and "'dist_ref_golden': 164" in out
+    assert "'level3_ref_golden': 60" in out and "'dist_ref_golden': 164" in out
 
 
 def test_engine_2x4_bench_grid(simlib):
     """The 8-GPU grid shape of BASELINE C3 (2 x 4): redistributions, contractions, all Gemm variants, the
     level-3 family, and the reference's own per-rank outputs."""
     out = _run("2x4", "--only", "check_redistributions,check_contractions,check_gemm_variants_f64,check_gemm_proxies_f32,run_level3")
-    assert "'level3_ref_golden': 44" in out and "'dist_ref_golden': 164" in out
+    assert "'level3_ref_golden': 60" in out and "'dist_ref_golden': 164" in out
 
 
 def test_engine_3x2_nccl_fallback(simlib):

@@ -257,7 +257,7 @@ def test_distributed_gemm_matches_reference_per_rank(gold_dist, tag):
 # ---------------------------------------------------------------------------------------------
 # Triangular rank-k family: tests/golden/ref_level3.npz holds per-rank outputs of
 # the reference's ScaleTrapezoid / MakeTrapezoidal / AxpyTrapezoid / MakeSymmetric, the four
-# LocalTrrk overloads, Trrk, Syrk and Symm (oracle/ref_build/gemm_ref.cpp::level3_golden).
+# LocalTrrk overloads, Trrk, Syrk, Symm and Trsm (oracle/ref_build/gemm_ref.cpp::level3_golden).
 # ---------------------------------------------------------------------------------------------
 L3_TAGS = ["r1c1"] + DIST_TAGS
 L3_N, L3_K, L3_M2 = 37, 23, 29
@@ -307,6 +307,14 @@ def level3_oracle_case(g, kind, uplo, p1, p2):
         C = OD.VDM.from_global(g, lcg_matrix(*shape, 7003, f64), OD.MC, OD.MR, 0, ra)
         O3.symm(p1, uplo, 2.0, A, B, 3.0, C)
         return C
+    if kind == 8:
+        side, orient, diag = p1, p2 // 2, p2 % 2
+        Ag = lcg_matrix(n, n, 7001, f64)
+        Ag = Ag * (1.0 / float(n)) if diag else Ag + float(n) * np.eye(n)
+        A = OD.VDM.from_global(g, np.asfortranarray(Ag), OD.MC, OD.MR, ca, 0)
+        B = OD.VDM.from_global(g, lcg_matrix(*((m2, n) if side else (n, m2)), 7002, f64), OD.MC, OD.MR, 0, ra)
+        O3.trsm(side, uplo, orient, diag, 2.0, A, B, nb=16)
+        return B
     raise ValueError(kind)
 
 
@@ -314,7 +322,7 @@ def level3_oracle_case(g, kind, uplo, p1, p2):
 def test_level3_matches_reference_per_rank(tag):
     """Every record of the reference's level-3 run: the oracle's per-rank local result equals the
     reference's — bit for bit for the trapezoid routines and MakeSymmetric (kinds 0-3), within the fp64
-    Gemm bound for LocalTrrk / Trrk / Syrk / Symm (BLAS summation order)."""
+    Gemm bound for LocalTrrk / Trrk / Syrk / Symm / Trsm (BLAS summation order)."""
     gold = np.load(os.path.join(GOLD, "ref_level3.npz"))
     g = OD.Grid(int(tag[1]), int(tag[3]))
     cache = {}
@@ -335,7 +343,7 @@ def test_level3_matches_reference_per_rank(tag):
             else:
                 assert OG.frobenius_rel_err(R.loc[q], ref) <= OG.gemm_tolerance(np.float64, L3_K), (tag, q, key)
             checked += 1
-    assert checked == 44 * g.p
+    assert checked == 60 * g.p
 
 
 def test_level3_restatement_equals_global_definition():

@@ -1,6 +1,6 @@
 // el_level3_check — the triangular rank-k family of the El.hpp facade written the way a Hydrogen
 // caller writes it (include/El/blas_like/level3.hpp:92-126,239-252,292-313,499-536): Syrk / Herk /
-// Trrk / LocalTrrk / Symm / Hemm and the trapezoid level-1 routines, float and double, each checked
+// Trrk / LocalTrrk / Symm / Hemm / Trsm / LocalTrsm and the trapezoid level-1 routines, float and double, each checked
 // against El::Gemm on the same operands (Syrk = triangle of A A^T, Symm = Gemm with the symmetrised
 // A, ...).  Compiled by `make`; run on a GPU box (tests/test_gpu_level3.py) and, linked against the
 // hostsim engine, on CPU (tests/test_hostsim.py).
@@ -85,6 +85,45 @@ static int exercise(const Grid& g) {
         AxpyTrapezoid(uplo, T(-1), C, Z, 1);
         Axpy(T(-1), C, Z);
         if (FrobeniusNorm(Z) != 0) ++bad;
+    }
+    // Trsm: B := alpha op(T)^-1 B and back again with Gemm on the explicit triangle: residual check
+    {
+        DistMatrix<T> Tm(g), Bx(g), B0(g), R(g);
+        Uniform(Tm, n, n, T(0), T(1), 21);
+        DistMatrix<T> Shift(g);
+        Shift.Resize(n, n);
+        Zero(Shift);
+        for (Int j = 0; j < Shift.LocalWidth(); ++j)
+            for (Int i = 0; i < Shift.LocalHeight(); ++i)
+                if (Shift.GlobalRow(i) == Shift.GlobalCol(j)) Shift.SetLocal(i, j, T(n));
+        Axpy(T(1), Shift, Tm);                              // well conditioned: n on the diagonal
+        for (LeftOrRight side : {LEFT, RIGHT})
+            for (UpperOrLower uplo : {LOWER, UPPER})
+                for (Orientation o : {NORMAL, TRANSPOSE}) {
+                    const Int bh = side == LEFT ? n : m2, bw = side == LEFT ? m2 : n;
+                    Uniform(B0, bh, bw, T(0), T(1), 22);
+                    Bx = B0;
+                    Trsm(side, uplo, o, NON_UNIT, T(2), Tm, Bx);
+                    DistMatrix<T> Tri(Tm);
+                    MakeTrapezoidal(uplo, Tri);
+                    R = B0;                                 // R = op(Tri) X - 2 B0  (or X op(Tri) - 2 B0)
+                    if (side == LEFT) Gemm(o, NORMAL, T(1), Tri, Bx, T(-2), R);
+                    else Gemm(NORMAL, o, T(1), Bx, Tri, T(-2), R);
+                    if (FrobeniusNorm(R) > 50 * tol * FrobeniusNorm(B0)) ++bad;
+                }
+        // LocalTrsm on a replicated triangle and [*,VR] right-hand sides equals Trsm
+        DistMatrix<T, STAR, STAR> Ts(g);
+        Ts = Tm;
+        DistMatrix<T, STAR, VR> Xv(g);
+        Uniform(B0, n, m2, T(0), T(1), 23);
+        Xv = B0;
+        LocalTrsm(LEFT, LOWER, NORMAL, UNIT, T(1), Ts, Xv);
+        Bx = B0;
+        Trsm(LEFT, LOWER, NORMAL, UNIT, T(1), Tm, Bx, false, TRSM_LARGE);
+        DistMatrix<T> Xm(g);
+        Xm = Xv;
+        Axpy(T(-1), Bx, Xm);
+        if (!(FrobeniusNorm(Xm) <= 50 * tol * FrobeniusNorm(Bx))) ++bad;
     }
     // errors: non-square C, NORMAL where a transposed panel is required
     try {
