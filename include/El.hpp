@@ -433,6 +433,26 @@ public:
         grid_->Synchronize();
     }
 
+    // Single GLOBAL entries (AbstractDistMatrix::Get / Set / Update, src/core/DistMatrix/ElementMatrix.cpp). Get is
+    // collective: every process of the grid calls it and receives the entry (a one-entry view gathered to [*,*]);
+    // Set / Update are carried out by the owning process(es) and are no-ops elsewhere, as in the reference.
+    T Get(Int i, Int j) const {
+        if (i < 0 || j < 0 || i >= Height() || j >= Width()) throw std::logic_error("Get: index out of range");
+        DistMatrix<T, STAR, STAR, W, D> one(*grid_);
+        elb200_dm_t v = nullptr;
+        detail::Check(elb200_dm_view(h_, i, i + 1, j, j + 1, &v), "Get");
+        const int st = elb200_dm_copy(v, one.Handle());
+        elb200_dm_destroy(v);
+        detail::Check(st, "Get");
+        return one.GetLocal(0, 0);
+    }
+    void Set(Int i, Int j, T v) {
+        if (IsLocal(i, j)) SetLocal(LocalRow(i), LocalCol(j), v);
+    }
+    void Update(Int i, Int j, T v) {
+        if (IsLocal(i, j)) SetLocal(LocalRow(i), LocalCol(j), GetLocal(LocalRow(i), LocalCol(j)) + v);
+    }
+
     // Host <-> local device matrix, column-major with leading dimension LocalHeight() on the host
     // side (the reference's CPU<->GPU Matrix copies, include/El/core/Matrix/impl_gpu.hpp).
     void SetLocalFromHost(const T* host) {
@@ -522,6 +542,14 @@ void LocalGemm(Orientation orientA, Orientation orientB, T alpha, const DistMatr
                const DistMatrix<T, UB, VB>& B, T beta, DistMatrix<T, UC, VC_>& C) {
     detail::Check(elb200_dm_local_gemm(int(orientA), int(orientB), double(alpha), A.Handle(), B.Handle(), double(beta),
                                        C.Handle()), "LocalGemm");
+}
+
+// C resized to fit, then C := alpha op(A) op(B) locally (Gemm.cpp:428-440)
+template <typename T, Dist UA, Dist VA, Dist UB, Dist VB, Dist UC, Dist VC_>
+void LocalGemm(Orientation orientA, Orientation orientB, T alpha, const DistMatrix<T, UA, VA>& A,
+               const DistMatrix<T, UB, VB>& B, DistMatrix<T, UC, VC_>& C) {
+    C.Resize(orientA == NORMAL ? A.Height() : A.Width(), orientB == NORMAL ? B.Width() : B.Height());
+    LocalGemm(orientA, orientB, alpha, A, B, T(0), C);
 }
 
 // ---------------------------------------------------------------------------------------------

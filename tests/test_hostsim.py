@@ -100,6 +100,16 @@ def test_cxx_facade_on_hostsim(simlib):
             assert r.returncode == 0, r.stderr[-3000:]
         r = subprocess.run([exe] + args, capture_output=True, text=True, timeout=300)
         assert r.returncode == 0 and "_PASS" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+    # the level-3 facade checks again on 2 x 2 and 2 x 3 grids whose ranks are threads (tests/hostsim/facade_ranks.cpp)
+    exe = os.path.join(out_dir, "facade_ranks")
+    src = os.path.join(ROOT, "tests", "hostsim", "facade_ranks.cpp")
+    cuda_inc = os.environ.get("CUDA_HOME", "/usr/local/cuda") + "/include"
+    r = subprocess.run(["g++", "-std=c++17", "-O1", "-I" + os.path.join(ROOT, "include"), "-I" + cuda_inc, "-o", exe, src, simlib,
+                        "-Wl,-rpath," + out_dir, "-pthread"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]
+    for shape in (("2", "2"), ("2", "3")):
+        r = subprocess.run([exe, *shape], capture_output=True, text=True, timeout=300, env=dict(os.environ, ELB200_ARENA_MB="8", HOSTSIM_TIMEOUT="90"))
+        assert r.returncode == 0 and "FACADE_RANKS_PASS" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
 
 
 # ---------------------------------------------------------------------------------------------

@@ -125,6 +125,26 @@ static int exercise(const Grid& g) {
         Axpy(T(-1), Bx, Xm);
         if (!(FrobeniusNorm(Xm) <= 50 * tol * FrobeniusNorm(Bx))) ++bad;
     }
+    // collective single-entry Get / Set / Update, and the resizing LocalGemm overload
+    {
+        DistMatrix<T> G(C);
+        const T before = G.Get(7, 5);
+        G.Set(7, 5, T(3));
+        G.Update(7, 5, T(0.5));
+        if (G.Get(7, 5) != T(3.5) || C.Get(7, 5) != before) ++bad;
+        DistMatrix<T, MC, STAR> Am(g);
+        DistMatrix<T, STAR, MR> Bm(g);
+        Am = A;                                             // n x k
+        DistMatrix<T> At(g);
+        Transpose(A, At);                                   // k x n
+        Bm = At;
+        DistMatrix<T> P(g), Q(g);
+        LocalGemm(NORMAL, NORMAL, T(1), Am, Bm, P);         // resized to n x n: A A^T
+        Gemm(NORMAL, TRANSPOSE, T(1), A, A, Q);
+        if (P.Height() != n || P.Width() != n) ++bad;
+        Axpy(T(-1), Q, P);
+        if (FrobeniusNorm(P) > tol * FrobeniusNorm(Q)) ++bad;
+    }
     // errors: non-square C, NORMAL where a transposed panel is required
     try {
         DistMatrix<T> Bad(g);
