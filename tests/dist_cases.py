@@ -649,6 +649,76 @@ def check_trsm(grid, dtype=torch.float64) -> int:
     return cnt
 
 
+def check_fuzz(grid, dtype=torch.float64, iters=None, seed=None) -> int:
+    """Randomised sweep (same random stream on every rank): Gemm with random sizes — including 0, 1 and sizes
+    smaller than the grid —, orientations, algorithms, alignments, blocksizes and operand distributions;
+    redistributions of random shapes between random pairs; Trrk / Syrk / Trsm with random shapes."""
+    import os
+    iters = int(os.environ.get("ELB_FUZZ_ITERS", "40")) if iters is None else iters
+    seed = int(os.environ.get("ELB_FUZZ_SEED", "1234")) if seed is None else seed
+    og = _grid_oracle(grid)
+    npdt = NPDT[dtype]
+    me = grid.Rank()
+    rng = np.random.default_rng(seed)
+    dims = [0, 1, 2, 3, 5, 8, 13, 31, 64, 77]
+    algs = (el.GEMM_DEFAULT, el.GEMM_SUMMA_A, el.GEMM_SUMMA_B, el.GEMM_SUMMA_C, el.GEMM_SUMMA_DOT, el.GEMM_SUMMA_C_MS)
+    cnt = 0
+    for it in range(iters):
+        m, n, k = (int(rng.choice(dims)) for _ in range(3))
+        oa, ob = int(rng.integers(2)), int(rng.integers(2))
+        alg = algs[int(rng.integers(len(algs)))]
+        nb = int(rng.choice([1, 4, 16, 128]))
+        dists = tuple(OD.PAIRS[int(rng.integers(len(OD.PAIRS)))] if rng.random() < 0.3 else (el.MC, el.MR) for _ in range(3))
+        aligns = tuple((int(rng.integers(8)), int(rng.integers(8))) for _ in range(3))
+        alpha, beta = float(rng.choice([0.0, 1.0, -0.5, 2.0])), float(rng.choice([0.0, 1.0, 3.0]))
+        err, tol = gemm_case(grid, dtype, oa, ob, alg, m, n, k, alpha=alpha, beta=beta, aligns=aligns, nb=nb, dists=dists)
+        assert err <= tol, ("fuzz Gemm", it, (m, n, k), oa, ob, alg, nb, dists, aligns, alpha, beta, err, tol)
+        # a random redistribution of a random shape
+        h, w = int(rng.choice(dims)), int(rng.choice(dims))
+        (U, V), (U2, V2) = OD.PAIRS[int(rng.integers(len(OD.PAIRS)))], OD.PAIRS[int(rng.integers(len(OD.PAIRS)))]
+        ca, ra = int(rng.integers(og.stride(U))), int(rng.integers(og.stride(V)))
+        ca2, ra2 = int(rng.integers(og.stride(U2))), int(rng.integers(og.stride(V2)))
+        G = np.asfortranarray(rng.uniform(-1, 1, (h, w)).astype(npdt))
+        A = el.DistMatrix(grid, U, V, dtype).Align(ca, ra).from_global(G)
+        B = el.DistMatrix(grid, U2, V2, dtype).Align(ca2, ra2)
+        el.Copy(A, B)
+        assert np.array_equal(B.get_local(), OD.local_of(G, OD.Spec(U2, V2, ca2, ra2, h, w), og, me)), ("fuzz Copy", it, (h, w), (U, V), (U2, V2))
+        # triangular family on a random size
+        nn, kk = int(rng.choice(dims)), int(rng.choice(dims))
+        uplo, t = int(rng.integers(2)), int(rng.integers(2))
+        A2 = OG.uniform_matrix(*((kk, nn) if t else (nn, kk)), 900 + it, npdt, 0.0, 1.0)
+        C2 = OG.uniform_matrix(nn, nn, 950 + it, npdt, 0.0, 1.0)
+        dA = el.DistMatrix(grid, el.MC, el.MR, dtype).Align(aligns[0][0] % og.r, aligns[0][1] % og.c).from_global(A2)
+        dC = el.DistMatrix(grid, el.MC, el.MR, dtype).Align(aligns[2][0] % og.r, aligns[2][1] % og.c).from_global(C2)
+        el.PushBlocksizeStack(nb)
+        old_bs = el.LocalTrrkBlocksize()
+        el.SetLocalTrrkBlocksize(int(rng.choice([1, 4, 2048])))
+        try:
+            el.Syrk(uplo, t, alpha, dA, beta, dC)
+            ref = O3.syrk_global(uplo, t, alpha, A2, beta, C2)
+            spec = OD.Spec(OD.MC, OD.MR, dC.ColAlign(), dC.RowAlign(), nn, nn)
+            if nn:
+                e2, t2 = _tri_err(dC.get_local(), ref, spec, og, me, npdt, kk)
+                assert e2 <= t2, ("fuzz Syrk", it, nn, kk, uplo, t, nb, e2, t2)
+            side, diag = int(rng.integers(2)), int(rng.integers(2))
+            T0 = OG.uniform_matrix(nn, nn, 970 + it, npdt, 0.0, 1.0)
+            T0 = T0 / npdt(max(nn, 1)) if diag else T0 + npdt(nn) * np.eye(nn, dtype=npdt)
+            Bs = OG.uniform_matrix(*((nn, kk) if side == el.LEFT else (kk, nn)), 980 + it, npdt, 0.0, 1.0)
+            dT = el.DistMatrix(grid, el.MC, el.MR, dtype).Align(aligns[1][0] % og.r, aligns[1][1] % og.c).from_global(np.asfortranarray(T0))
+            dB = el.DistMatrix(grid, el.MC, el.MR, dtype).Align(aligns[2][0] % og.r, aligns[2][1] % og.c).from_global(Bs)
+            el.Trsm(side, uplo, t, diag, 2.0, dT, dB)
+            if nn and kk:
+                ref = O3.trsm_global(side, uplo, t, diag, 2.0, T0, Bs)
+                spec = OD.Spec(OD.MC, OD.MR, dB.ColAlign(), dB.RowAlign(), *Bs.shape)
+                e3, t3 = _tri_err(dB.get_local(), ref, spec, og, me, npdt, nn)
+                assert e3 <= 4 * t3, ("fuzz Trsm", it, nn, kk, side, uplo, t, diag, nb, e3, t3)
+        finally:
+            el.SetLocalTrrkBlocksize(old_bs)
+            el.PopBlocksizeStack()
+        cnt += 1
+    return cnt
+
+
 def run_level3(grid) -> dict:
     """The triangular rank-k family and the comparisons with the reference's own per-rank outputs."""
     out = {}
@@ -657,6 +727,7 @@ def run_level3(grid) -> dict:
     out["trsm"] = check_trsm(grid, torch.float64) + check_trsm(grid, torch.float32)
     out["level3_ref_golden"] = check_level3_golden(grid)
     out["dist_ref_golden"] = check_dist_golden(grid)
+    out["fuzz"] = check_fuzz(grid, torch.float64, iters=30) + check_fuzz(grid, torch.float32, iters=30)
     return out
 
 

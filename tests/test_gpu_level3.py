@@ -193,6 +193,14 @@ def test_el_level3_check_facade():
     assert r.returncode == 0 and "EL_LEVEL3_CHECK_PASS" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
 
 
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+def test_randomised_sweep_1x1(grid1, dtype):
+    """Random sizes (0, 1, ragged), orientations, algorithms, alignments, blocksizes, operand distributions for Gemm,
+    Copy, Syrk and Trsm — the edge cases of every kernel entry (empty and one-element operands, k = 0, beta = 0)."""
+    from tests import dist_cases as dc
+    assert dc.check_fuzz(grid1, dtype, iters=60, seed=4321) == 60
+
+
 @pytest.mark.parametrize("nproc,height", [(2, 1), (4, 2), (8, 2)])
 def test_multi_gpu_level3_and_reference_goldens(nproc, height):
     """r x c grids, one process per GPU: the level-3 cases plus this library against the reference's own

@@ -53,14 +53,14 @@ def test_engine_2x2_peer_arena_all_cases(simlib):
 def test_engine_2x4_bench_grid(simlib):
     """The 8-GPU grid shape of BASELINE C3 (2 x 4): redistributions, contractions, all Gemm variants, the
     level-3 family, and the reference's own per-rank outputs."""
-    out = _run("2x4", "--only", "check_redistributions,check_contractions,check_gemm_variants_f64,check_gemm_proxies_f32,run_level3")
+    out = _run("2x4", "--only", "check_redistributions,check_contractions,check_gemm_variants_f64,check_gemm_proxies_f32,run_level3,check_fuzz")
     assert "'level3_ref_golden': 60" in out and "'dist_ref_golden': 164" in out
 
 
 def test_engine_3x2_nccl_fallback(simlib):
     """Peer arena disabled (ELB200_P2P=0): the NCCL AllGather / ReduceScatter / grouped send-recv
     paths on a non-square grid with r > c."""
-    out = _run("3x2", "--only", "check_redistributions,check_contractions,check_gemm_variants_f32,run_level3", env={"ELB200_P2P": "0"})
+    out = _run("3x2", "--only", "check_redistributions,check_contractions,check_gemm_variants_f32,run_level3,check_fuzz", env={"ELB200_P2P": "0"})
     assert "'dist_ref_golden': 164" in out
 
 
@@ -81,7 +81,8 @@ def test_engine_multi_panel_pipeline(simlib, grid, env, extra):
 def test_engine_tiny_arena_falls_back(simlib):
     """Arena slots of 4 KiB: some messages fit, most do not — every size check must route the rest to
     NCCL (and every rank must take the same branch). Panels 16 wide: Trrk / Syrk walk several k panels."""
-    _run("2x2", "--only", "check_redistributions,check_contractions,check_gemm_pipeline,check_level3", env={"ELB200_ARENA_KB": "4", "ELB200_PANEL_K": "16"})
+    _run("2x2", "--only", "check_redistributions,check_contractions,check_gemm_pipeline,check_level3,check_trsm,check_fuzz,check_fuzz_f32",
+         env={"ELB200_ARENA_KB": "4", "ELB200_PANEL_K": "16"})
 
 
 def test_cxx_facade_on_hostsim(simlib):
