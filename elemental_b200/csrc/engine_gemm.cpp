@@ -363,6 +363,46 @@ void SummaDot(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B,
         gemm_profiled<T>(ta, tb, d.m, d.n, d.k, alpha, A.buf, A.ldim, B.buf, B.ldim, T(1), C.buf, C.ldim, C.stream);
         return;
     }
+    // Tall-skinny regime proper (one C tile): the up-front all-to-all of A and B is cut into k ranges and
+    // pipelined against the local GEMM over two slots, like the SUMMA-C panels — the exchange of range c+1
+    // (comm stream: pack, copy-engine pulls, unpack) runs under the GEMM of range c, and the tile accumulates
+    // in C11 across ranges before its single reduce-scatter. ELB200_DOT_CHUNK = local k per range (default
+    // 4096 fp32 / 2048 fp64), ELB200_DOT_PIPELINE=0 restores the one-shot exchange.
+    static const bool pipe_on = [] { const char* e = std::getenv("ELB200_DOT_PIPELINE"); return !(e && std::atoi(e) == 0); }();
+    static const int64_t chunk_env = [] { const char* e = std::getenv("ELB200_DOT_CHUNK"); return e ? std::atoll(e) : 0ll; }();
+    const int64_t chunk_local = chunk_env > 0 ? chunk_env : (sizeof(T) == 4 ? 4096 : 2048);
+    const int64_t chunk = chunk_local * g.size();  // global k per range
+    if (pipe_on && g.comm_stream && d.m <= kBlock && d.n <= kBlock && d.k >= 2 * chunk) {
+        cudaStream_t cs = g.comm_stream;
+        DistMat<T> Aks[2] = {DistMat<T>(g, ta ? VC : STAR, ta ? STAR : VC, cs), DistMat<T>(g, ta ? VC : STAR, ta ? STAR : VC, cs)};
+        DistMat<T> Bks[2] = {DistMat<T>(g, tb ? STAR : VC, tb ? VC : STAR, cs), DistMat<T>(g, tb ? STAR : VC, tb ? VC : STAR, cs)};
+        DistMat<T> C11p(g, STAR, STAR, C.stream);
+        C11p.Resize(d.m, d.n);
+        Ev ready[2], freed[2], start;
+        start.record(C.stream);  // A, B (and the freshly allocated C11) are ready in C.stream order
+        start.block(cs);
+        int64_t p = 0;
+        for (int64_t k0 = 0; k0 < d.k; k0 += chunk, ++p) {
+            const int sl = int(p & 1);
+            const int64_t k1 = std::min(d.k, k0 + chunk);
+            if (p >= 2) freed[sl].block(cs);  // the GEMM that read this slot two ranges ago is done
+            const DistMat<T> A1 = ta ? A.View(k0, k1, 0, d.m) : A.View(0, d.m, k0, k1);
+            const DistMat<T> B1 = tb ? B.View(0, d.n, k0, k1) : B.View(k0, k1, 0, d.n);
+            Aks[sl].col_constrained = Aks[sl].row_constrained = false;
+            Bks[sl].col_constrained = Bks[sl].row_constrained = false;
+            Aks[sl].Align(0, 0); Bks[sl].Align(0, 0);
+            Copy(A1, Aks[sl]);
+            Copy(B1, Bks[sl]);
+            ready[sl].record(cs);
+            ready[sl].block(C.stream);
+            LocalGemm(ta, tb, alpha, Aks[sl], Bks[sl], p == 0 ? T(0) : T(1), C11p);
+            freed[sl].record(C.stream);
+        }
+        // the slots are freed in comm-stream order: not before the last GEMMs have read them
+        for (int i = 0; i < 2 && i < p; ++i) freed[i].block(cs);
+        AxpyContract(T(1), C11p, C);
+        return;
+    }
     DistMat<T> Ak(g, ta ? VC : STAR, ta ? STAR : VC, C.stream);  // k over VC
     DistMat<T> Bk(g, tb ? STAR : VC, tb ? VC : STAR, C.stream);
     Ak.Align(0, 0); Bk.Align(0, 0);

@@ -731,6 +731,21 @@ def run_level3(grid) -> dict:
     return out
 
 
+def check_gemm_dot_pipeline(grid, dtype=torch.float64) -> int:
+    """SUMMA_Dot in its tall-skinny regime (m, n << k): with ELB200_DOT_CHUNK small enough (hostsim tests set 4;
+    the default is 4096 / 2048 local k per range) the up-front all-to-all of A and B runs in k ranges pipelined
+    against the local GEMM; all orientations, aligned and misaligned operands, ragged last range."""
+    cnt = 0
+    mis = ((1, 2), (0, 1), (1, 0))
+    for oa, ob in itertools.product((0, 1), (0, 1)):
+        for al in (None, mis):
+            for alg in (el.GEMM_SUMMA_DOT, el.GEMM_DEFAULT):   # DEFAULT resolves to DOT here (10 m <= k, 10 n <= k)
+                err, tol = gemm_case(grid, dtype, oa, ob, alg, 33, 27, 1111, alpha=0.5, beta=-0.5, aligns=al, nb=16)
+                assert err <= tol, (oa, ob, alg, al, err, tol)
+                cnt += 1
+    return cnt
+
+
 def run_all(grid, heavy=False) -> dict:
     out = {}
     out["redist_f64"] = check_redistributions(grid, torch.float64)
@@ -747,6 +762,7 @@ def run_all(grid, heavy=False) -> dict:
     check_gemm_proxies(grid, torch.float32)
     out["gemm_host"] = check_gemm_host(grid, torch.float32) + check_gemm_host(grid, torch.float64)
     out["gemm_pipeline"] = check_gemm_pipeline(grid, torch.float64) + check_gemm_pipeline(grid, torch.float32)
+    out["gemm_dot_pipeline"] = check_gemm_dot_pipeline(grid, torch.float64) + check_gemm_dot_pipeline(grid, torch.float32)
     if heavy:
         # panels wider than one algorithmic block, ragged edges, default blocksize
         for dt in (torch.float32, torch.float64):

@@ -72,9 +72,9 @@ def test_engine_multi_panel_pipeline(simlib, grid, env, extra):
     gather | GEMM pipeline, zero-copy direct panels, staged panels, and with the pipeline off (2 x 2 and 2 x 4
     with the default settings run under ThreadSanitizer below); on the
     grid shapes not covered above also the level-3 family and the reference's own per-rank outputs."""
-    e = {"ELB200_PANEL_K": "512"}
+    e = {"ELB200_PANEL_K": "512", "ELB200_DOT_CHUNK": "4"}
     e.update(env)
-    out = _run(grid, "--only", "check_gemm_pipeline,check_gemm_pipeline_f32" + extra, env=e)
+    out = _run(grid, "--only", "check_gemm_pipeline,check_gemm_pipeline_f32,check_gemm_dot_pipeline,check_gemm_dot_pipeline_f32" + extra, env=e)
     assert not extra or "'dist_ref_golden': 164" in out
 
 
@@ -153,15 +153,16 @@ def test_race_detector_selftest(tsanlib):
     assert bad.returncode == 66 and "WARNING: ThreadSanitizer: data race" in bad.stderr, bad.stdout + bad.stderr[-2000:]
 
 
-@pytest.mark.parametrize("grid,only", [("2x2", "check_gemm_pipeline,check_contractions,check_level3"),
-                                        ("2x4", "check_gemm_pipeline")])
+@pytest.mark.parametrize("grid,only", [("2x2", "check_gemm_pipeline,check_contractions,check_level3,check_gemm_dot_pipeline"),
+                                        ("2x4", "check_gemm_pipeline,check_gemm_dot_pipeline")])
 def test_engine_is_race_free_under_tsan(tsanlib, grid, only):
-    """The multi-panel SUMMA pipeline (zero-copy direct panels, slot hand-back), the peer-arena reductions and
+    """The multi-panel SUMMA-C pipeline (zero-copy direct panels, slot hand-back), the k-range pipeline of SUMMA-Dot
+    (exchange on the comm stream under the GEMM), the peer-arena reductions and
     exchanges and the level-3 family under ThreadSanitizer: no report.  (The remaining cases — run_all, run_level3,
     the four-stream host-operand Gemm — were run the same way by hand and are clean too; they are left out of the
     default suite for time.)"""
     _, rt = tsanlib
-    e = dict(os.environ, HOSTSIM_SANITIZE="thread", HOSTSIM_TIMEOUT="300", ELB200_ARENA_MB="8", ELB200_PANEL_K="512",
+    e = dict(os.environ, HOSTSIM_SANITIZE="thread", HOSTSIM_TIMEOUT="300", ELB200_ARENA_MB="8", ELB200_PANEL_K="512", ELB200_DOT_CHUNK="4",
              OMP_NUM_THREADS="1", LD_PRELOAD=rt, TSAN_OPTIONS="report_signal_unsafe=0 history_size=4 exitcode=66")
     r = subprocess.run([sys.executable, WORKER, grid, "--only", only], capture_output=True, text=True, timeout=1500, cwd=ROOT, env=e)
     assert "WARNING: ThreadSanitizer" not in r.stderr, r.stderr[-6000:]
