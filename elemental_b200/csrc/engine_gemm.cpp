@@ -478,7 +478,7 @@ void Gemm(int ta, int tb, T alpha, const DistMat<T>& Apre, const DistMat<T>& Bpr
 //   comm stream: gather op(A) -> [MC,*] once, each B block -> [*,MR]   (peer arena / NCCL)
 //   compute    : one full-k local GEMM per block (beta applied in the epilogue)
 //   d2h stream : the finished C block
-// Two block slots keep PCIe (both directions), NVLink and the tensor pipe busy at the same time.
+// Four block slots keep PCIe (both directions), NVLink and the tensor pipe busy at the same time.
 // ---------------------------------------------------------------------------------------------
 namespace {
 template <typename T>
@@ -515,18 +515,25 @@ void GemmHost(Grid& g, int ta, int tb, int64_t m, int64_t n, int64_t k, T alpha,
     if (Wg < unit) Wg = unit;
     const int64_t nblocks = (n + Wg - 1) / Wg;
 
+    // Block slots. With two, the upload of block j had to wait for the download of block j-2, i.e. for a
+    // whole GEMM + D2H, and the H2D stream — the bottleneck: 3 of the 4 bytes moved go up — idled between
+    // blocks (timeline in DESIGN.md 3.6); four slots keep it busy back to back.
+    constexpr int kSlots = 4;
     DistMat<T> A(g, MC, MR, s);
     DistMat<T> PA(g, ta ? STAR : MC, ta ? MC : STAR, cs);
-    DistMat<T> Bblk[2] = {DistMat<T>(g, MC, MR, s), DistMat<T>(g, MC, MR, s)};
-    DistMat<T> Cblk[2] = {DistMat<T>(g, MC, MR, s), DistMat<T>(g, MC, MR, s)};
-    DistMat<T> PB[2] = {DistMat<T>(g, tb ? MR : STAR, tb ? STAR : MR, cs), DistMat<T>(g, tb ? MR : STAR, tb ? STAR : MR, cs)};
+    std::vector<DistMat<T>> Bblk, Cblk, PB;
+    for (int i = 0; i < kSlots; ++i) {
+        Bblk.emplace_back(g, MC, MR, s);
+        Cblk.emplace_back(g, MC, MR, s);
+        PB.emplace_back(g, tb ? MR : STAR, tb ? STAR : MR, cs);
+    }
     const int64_t w0 = std::min(Wg, n);
     if (product) A.Resize(hA, wA);
-    for (int i = 0; i < 2 && i < nblocks; ++i) {
+    for (int i = 0; i < kSlots && i < nblocks; ++i) {
         if (product) Bblk[i].Resize(tb ? w0 : k, tb ? k : w0);
         Cblk[i].Resize(m, w0);
     }
-    Ev alloc, a_up, a_ready, up[2], ready[2], done[2], out[2];
+    Ev alloc, a_up, a_ready, up[kSlots], ready[kSlots], done[kSlots], out[kSlots];
     alloc.record(s);
     alloc.block(hs);
     alloc.block(cs);
@@ -544,9 +551,9 @@ void GemmHost(Grid& g, int ta, int tb, int64_t m, int64_t n, int64_t k, T alpha,
     }
 
     for (int64_t j = 0; j < nblocks; ++j) {
-        const int sl = int(j & 1);
+        const int sl = int(j % kSlots);
         const int64_t J0 = j * Wg, J1 = std::min(n, J0 + Wg), wj = J1 - J0;
-        if (j >= 2) out[sl].block(hs);  // the slot's previous block has been multiplied and downloaded
+        if (j >= kSlots) out[sl].block(hs);  // the slot's previous block has been multiplied and downloaded
         // local index ranges of the block: C columns and (B not transposed) B columns run over MR,
         // (B transposed) B rows run over MC
         const int64_t cc0 = loc(J0, g.me.mr, c), ccn = loc(J1, g.me.mr, c) - cc0;
@@ -580,7 +587,7 @@ void GemmHost(Grid& g, int ta, int tb, int64_t m, int64_t n, int64_t k, T alpha,
         out[sl].record(ds);
     }
     // join: the temporaries are freed in the order of their own streams, after their last readers
-    for (int i = 0; i < 2 && i < nblocks; ++i) { out[i].block(s); done[i].block(cs); }
+    for (int i = 0; i < kSlots && i < nblocks; ++i) { out[i].block(s); done[i].block(cs); }
     cuda_check(cudaStreamSynchronize(ds), "GemmHost: d2h");
     cuda_check(cudaStreamSynchronize(s), "GemmHost: compute");
     cuda_check(cudaStreamSynchronize(cs), "GemmHost: comm");
