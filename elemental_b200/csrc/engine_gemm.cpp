@@ -533,22 +533,30 @@ void GemmHost(Grid& g, int ta, int tb, int64_t m, int64_t n, int64_t k, T alpha,
         if (product) Bblk[i].Resize(tb ? w0 : k, tb ? k : w0);
         Cblk[i].Resize(m, w0);
     }
-    Ev alloc, a_up, a_ready, up[kSlots], ready[kSlots], done[kSlots], out[kSlots];
+    Ev alloc, up[kSlots], ready[kSlots], done[kSlots], out[kSlots];
     alloc.record(s);
     alloc.block(hs);
     alloc.block(cs);
     alloc.block(ds);
 
-    const DistMat<T>* a = nullptr;
-    if (product) {
-        copy_rect(A.buf, A.ldim, Ah, lda, lhA, lwA, cudaMemcpyHostToDevice, hs);
-        a_up.record(hs);
-        a_up.block(cs);
-        DistSpec like;  // C's distribution: [MC,MR], alignment 0
-        like.col = MC; like.row = MR; like.height = m; like.width = n;
-        a = &panel_as(A, PA, like);
-        a_ready.record(cs);
+    // op(A) as a panel aligned with C: [MC,*] (or [*,MC]); on a 1 x 1 grid A itself. A is NOT uploaded up front:
+    // block 0's B and C slices go first and A follows in k ranges, each multiplied into block 0 as soon as it has
+    // landed (and been gathered) — the first GEMM starts after ~1/8 of A instead of after all of it.
+    DistSpec like;  // C's distribution: [MC,MR], alignment 0
+    like.col = MC; like.row = MR; like.height = m; like.width = n;
+    const bool single = g.size() == 1;
+    if (product && !single) {
+        PA.col_constrained = PA.row_constrained = false;
+        PA.spec.col_align = PA.spec.row_align = 0;
+        PA.AlignWith(like, true);
+        PA.Resize(hA, wA);
     }
+    const DistMat<T>& afull = single ? A : PA;
+    constexpr int kMaxRanges = 8;
+    static const int64_t min_range = [] { const char* e = std::getenv("ELB200_HOST_KRANGE"); const int64_t v = e ? std::atoll(e) : 0; return v > 0 ? v : int64_t(512); }();
+    const int nranges = product ? int(std::min<int64_t>(kMaxRanges, std::max<int64_t>(1, k / min_range))) : 0;
+    const int64_t Kc = nranges ? (k + nranges - 1) / nranges : 0;
+    Ev a_up[kMaxRanges], a_ready[kMaxRanges];
 
     for (int64_t j = 0; j < nblocks; ++j) {
         const int sl = int(j % kSlots);
@@ -575,8 +583,34 @@ void GemmHost(Grid& g, int ta, int tb, int64_t m, int64_t n, int64_t k, T alpha,
             const DistMat<T>& b = panel_as(Bblk[sl], PB[sl], Cblk[sl].spec);
             ready[sl].record(cs);
             ready[sl].block(s);
-            if (j == 0) a_ready.block(s);
-            LocalGemm(ta, tb, alpha, *a, b, beta, Cblk[sl]);
+            if (j == 0) {
+                for (int q = 0; q < nranges; ++q) {
+                    const int64_t k0 = std::min(k, q * Kc), k1 = std::min(k, k0 + Kc);
+                    if (k1 <= k0) break;
+                    // this rank's part of A(:, k0:k1) (or A(k0:k1, :) when transposed): k runs over MR / MC
+                    if (!ta) {
+                        const int64_t c0 = loc(k0, g.me.mr, c), cn = loc(k1, g.me.mr, c) - c0;
+                        copy_rect(A.buf + c0 * A.ldim, A.ldim, Ah + c0 * lda, lda, lhA, cn, cudaMemcpyHostToDevice, hs);
+                    } else {
+                        const int64_t r0 = loc(k0, g.me.mc, r), rn = loc(k1, g.me.mc, r) - r0;
+                        copy_rect(A.buf + r0, A.ldim, Ah + r0, lda, rn, lwA, cudaMemcpyHostToDevice, hs);
+                    }
+                    a_up[q].record(hs);
+                    a_up[q].block(cs);
+                    if (!single) {
+                        const DistMat<T> Asrc = ta ? A.View(k0, k1, 0, m) : A.View(0, m, k0, k1);
+                        DistMat<T> Adst = ta ? PA.View(k0, k1, 0, m) : PA.View(0, m, k0, k1);
+                        Copy(Asrc, Adst);
+                    }
+                    a_ready[q].record(cs);
+                    a_ready[q].block(s);
+                    const DistMat<T> av = ta ? afull.View(k0, k1, 0, m) : afull.View(0, m, k0, k1);
+                    const DistMat<T> bv = tb ? b.View(0, wj, k0, k1) : b.View(k0, k1, 0, wj);
+                    LocalGemm(ta, tb, alpha, av, bv, q == 0 ? beta : T(1), Cblk[sl]);
+                }
+            } else {
+                LocalGemm(ta, tb, alpha, afull, b, beta, Cblk[sl]);
+            }
         } else {
             up[sl].block(s);
             Scale(beta, Cblk[sl]);

@@ -28,7 +28,8 @@ def simlib():
 
 
 def _run(grid, *args, env=None, timeout=900):
-    e = dict(os.environ, HOSTSIM_TIMEOUT="90", ELB200_ARENA_MB="8", OMP_NUM_THREADS="1")
+    # ELB200_HOST_KRANGE=16: the host-operand Gemm streams A in several k ranges at the small k of the cases
+    e = dict(os.environ, HOSTSIM_TIMEOUT="90", ELB200_ARENA_MB="8", OMP_NUM_THREADS="1", ELB200_HOST_KRANGE="16")
     e.update(env or {})
     r = subprocess.run([sys.executable, WORKER, grid, *args], capture_output=True, text=True, timeout=timeout, cwd=ROOT, env=e)
     assert r.returncode == 0 and "HOSTSIM_PASS" in r.stdout, (r.stdout[-3000:] + r.stderr[-6000:])
