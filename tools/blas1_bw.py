@@ -60,6 +60,13 @@ def main():
              lambda: getattr(lib, f"elb200_lattice_{sfx}")(L.UNPACK_AXPY, stride, segs, Y.data_ptr(), n, buf.data_ptr(), ct(0.5), None)),
             ("peer_reduce_axpy, 2 sources (local)", 4,
              lambda: getattr(lib, f"elb200_peer_reduce_axpy_{sfx}")(2, srcs, 0, C.byref(one), Y.data_ptr(), n, ct(0.5), None)),
+            # trapezoid kernel: algorithmic bytes count the entries INSIDE the lower triangle
+            # (n(n+1)/2) for SCALE (2 passes) and AXPY (3), the entries OUTSIDE it (n(n-1)/2) for MAKE (1)
+            ("trapezoid SCALE lower", 2, lambda: getattr(lib, f"elb200_trapezoid_{sfx}")(L.TRAP_SCALE, L.LOWER, 0, n, n, 0, 1, 0, 1, ct(1.0001), None, n, Y.data_ptr(), n, None)),
+            ("trapezoid AXPY lower", 3, lambda: getattr(lib, f"elb200_trapezoid_{sfx}")(L.TRAP_AXPY, L.LOWER, 0, n, n, 0, 1, 0, 1, ct(0.5), X.data_ptr(), n, Y.data_ptr(), n, None)),
+            ("trapezoid AXPY lower, element-cyclic 2x4 index map", 3,
+             lambda: getattr(lib, f"elb200_trapezoid_{sfx}")(L.TRAP_AXPY, L.LOWER, 0, n, n, 1, 2, 3, 4, ct(0.5), X.data_ptr(), n, Y.data_ptr(), n, None)),
+            ("trapezoid MAKE lower", 1, lambda: getattr(lib, f"elb200_trapezoid_{sfx}")(L.TRAP_MAKE, L.LOWER, 0, n, n, 0, 1, 0, 1, ct(0), None, n, Y.data_ptr(), n, None)),
         ]
         for name, passes, fn in cases:
             for _ in range(3):
@@ -74,6 +81,13 @@ def main():
             torch.cuda.synchronize()
             ms = e0.elapsed_time(e1) / reps
             elems = (n // 2) * n if "row-strided dst" in name else n * n
+            if name.startswith("trapezoid"):
+                if "index map" in name:   # global (1 + 2i, 3 + 4j): inside when 1 + 2i >= 3 + 4j
+                    elems = sum(max(0, n - max(0, (2 + 4 * j + 1) // 2)) for j in range(n))
+                else:
+                    elems = n * (n + 1) // 2
+                if "MAKE" in name:
+                    elems = n * n - elems
             gbs = passes * elems * s / (ms * 1e-3) / 1e9
             rows.append({"kernel": name, "dtype": sfx, "n": n, "ms": ms, "algorithmic_GBps": gbs, "frac_of_measured_hbm": gbs / peak})
             print(f"{sfx} {name:58s} {ms:8.3f} ms  {gbs:8.1f} GB/s  {gbs / peak:5.2f} of {peak:.0f}")
