@@ -15,6 +15,7 @@
 // against 12 conflict-free LDS.64.
 #include <cuda_runtime.h>
 #include <cstdint>
+#include <cstdlib>
 
 #include "ptx.cuh"
 #include "elb200_internal.h"
@@ -207,6 +208,185 @@ cudaError_t launch(const Params& p, cudaStream_t stream) {
     return cudaGetLastError();
 }
 
+// ---------------------------------------------------------------------------------------------
+// Warp-specialised variant (ELB200_F64_WS=1; off by default until it has been measured on a B200).
+// The ncu capture of the kernel above charges 6.4 % of the warp time to the CTA-wide barrier per
+// k-tile and 6.2 % to the fragment loads right behind it (profiles/).  Here two
+// producer warps issue every cp.async and eight consumer warps only do LDS + DMMA: a stage is
+// handed over through a pair of mbarriers (full: cp.async.mbarrier.arrive of the 64 producer
+// threads; empty: one arrive per consumer warp), so no warp ever waits for the slowest of the CTA,
+// and the consumers prefetch the fragments of k4+4 while the DMMAs of k4 issue.
+// Same tile, same shared-memory layout (conflict-free pitches), same epilogue as the kernel above.
+// ---------------------------------------------------------------------------------------------
+constexpr int kProducerThreads = 64;
+constexpr int kThreadsWS = kThreads + kProducerThreads;
+
+template <bool MN_CONTIG, int VEC>
+__device__ __forceinline__ void load_tile_ws(const double* __restrict__ X, int64_t ld, int mn0, int k0, int mn_extent,
+                                             int k_extent, uint32_t smem_tile, int ptid) {
+    constexpr int kChunks = (BM * BK) / VEC;
+    constexpr int kPerThread = kChunks / kProducerThreads;
+#pragma unroll 4
+    for (int i = 0; i < kPerThread; ++i) {
+        const int c = ptid + i * kProducerThreads;
+        int mn, kk;
+        uint32_t dst;
+        if constexpr (MN_CONTIG) {
+            constexpr int kPerRow = BM / VEC;
+            kk = c / kPerRow;
+            mn = (c % kPerRow) * VEC;
+            dst = smem_tile + uint32_t(kk * kPitchMN + mn) * 8u;
+        } else {
+            constexpr int kPerRow = BK / VEC;
+            mn = c / kPerRow;
+            kk = (c % kPerRow) * VEC;
+            dst = smem_tile + uint32_t(mn * kPitchK + kk) * 8u;
+        }
+        const int gmn = mn0 + mn, gk = k0 + kk;
+        int valid;
+        if constexpr (MN_CONTIG) valid = (gk < k_extent) ? min(max(mn_extent - gmn, 0), VEC) : 0;
+        else valid = (gmn < mn_extent) ? min(max(k_extent - gk, 0), VEC) : 0;
+        const double* src = X;
+        if (valid > 0) src = MN_CONTIG ? X + int64_t(gk) * ld + gmn : X + int64_t(gmn) * ld + gk;
+        cp_async_zfill<VEC * 8>(dst, src, valid * 8);
+    }
+}
+
+// all cp.async issued so far by this thread arrive on `bar` when they have landed (count not incremented)
+__device__ __forceinline__ void cp_async_arrive_noinc(uint32_t bar) {
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+template <bool TA, bool TB, int VEC>
+__global__ void __launch_bounds__(kThreadsWS, 1) gemm_f64_dmma_ws_kernel(const Params p) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t bars[2 * kStages];  // full[0..kStages), empty[kStages..2*kStages)
+    const uint32_t smem_base = smem_u32(smem_raw);
+    const double* smem_d = reinterpret_cast<const double*>(smem_raw);
+    const uint32_t bar_base = smem_u32(bars);
+    auto full = [&](int s) { return bar_base + uint32_t(s) * 8u; };
+    auto empty = [&](int s) { return bar_base + uint32_t(kStages + s) * 8u; };
+
+    int tm, tn;
+    tile_coords(blockIdx.x, p.tiles_m, p.tiles_n, tm, tn);
+    const int m0 = tm * BM, n0 = tn * BN;
+    const int num_kt = (p.k + BK - 1) / BK;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(full(s), kProducerThreads);
+            mbar_init(empty(s), kThreads / 32);
+        }
+        fence_mbar_init();
+    }
+    __syncthreads();
+
+    if (threadIdx.x >= kThreads) {
+        // ---- producers
+        const int ptid = threadIdx.x - kThreads;
+        for (int kt = 0; kt < num_kt; ++kt) {
+            const int s = kt % kStages;
+            if (kt >= kStages) mbar_wait(empty(s), uint32_t((kt / kStages - 1) & 1));
+            const uint32_t sa = smem_base + uint32_t(s * kStageDoubles) * 8u;
+            const uint32_t sb = sa + uint32_t(kOperandDoubles) * 8u;
+            load_tile_ws<!TA, VEC>(p.A, p.lda, m0, kt * BK, p.m, p.k, sa, ptid);
+            load_tile_ws<TB, VEC>(p.B, p.ldb, n0, kt * BK, p.n, p.k, sb, ptid);
+            cp_async_arrive_noinc(full(s));
+        }
+        cp_async_wait<0>();
+        return;
+    }
+
+    // ---- consumers
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int wm = (warp & 1) * 64;
+    const int wn = (warp >> 1) * 32;
+    const int lr = lane >> 2, lk = lane & 3;
+
+    double acc[4][8][2];
+#pragma unroll
+    for (int ni = 0; ni < 4; ++ni)
+#pragma unroll
+        for (int mi = 0; mi < 8; ++mi) acc[ni][mi][0] = acc[ni][mi][1] = 0.0;
+
+    auto load_frags = [&](const double* sa, const double* sb, int k4, double (&bf)[8], double (&af)[4]) {
+#pragma unroll
+        for (int mi = 0; mi < 8; ++mi) {
+            const int mm = wm + mi * 8 + lr, kk = k4 + lk;
+            bf[mi] = TA ? sa[mm * kPitchK + kk] : sa[kk * kPitchMN + mm];
+        }
+#pragma unroll
+        for (int ni = 0; ni < 4; ++ni) {
+            const int nn = wn + ni * 8 + lr, kk = k4 + lk;
+            af[ni] = TB ? sb[kk * kPitchMN + nn] : sb[nn * kPitchK + kk];
+        }
+    };
+
+    for (int kt = 0; kt < num_kt; ++kt) {
+        const int s = kt % kStages;
+        mbar_wait(full(s), uint32_t((kt / kStages) & 1));
+        const double* sa = smem_d + s * kStageDoubles;
+        const double* sb = sa + kOperandDoubles;
+        double bf[2][8], af[2][4];
+        load_frags(sa, sb, 0, bf[0], af[0]);
+#pragma unroll
+        for (int k4 = 0; k4 < BK; k4 += 4) {
+            const int cur = (k4 >> 2) & 1;
+            if (k4 + 4 < BK) load_frags(sa, sb, k4 + 4, bf[cur ^ 1], af[cur ^ 1]);
+#pragma unroll
+            for (int ni = 0; ni < 4; ++ni)
+#pragma unroll
+                for (int mi = 0; mi < 8; ++mi) dmma_m8n8k4(acc[ni][mi], af[cur][ni], bf[cur][mi]);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty(s));  // this warp is done with the stage
+    }
+
+    const bool vec_ok = ((p.ldc & 1) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15u) == 0);
+#pragma unroll
+    for (int ni = 0; ni < 4; ++ni) {
+        const int n = n0 + wn + ni * 8 + lr;
+        if (n >= p.n) continue;
+        double* ccol = p.C + int64_t(n) * p.ldc;
+#pragma unroll
+        for (int mi = 0; mi < 8; ++mi) {
+            const int m = m0 + wm + mi * 8 + 2 * lk;
+            if (m >= p.m) continue;
+            double o0 = p.alpha * acc[ni][mi][0], o1 = p.alpha * acc[ni][mi][1];
+            if (vec_ok && m + 1 < p.m) {
+                double2* ptr = reinterpret_cast<double2*>(ccol + m);
+                if (p.beta != 0.0) {
+                    const double2 c = *ptr;
+                    o0 = fma(p.beta, c.x, o0);
+                    o1 = fma(p.beta, c.y, o1);
+                }
+                *ptr = make_double2(o0, o1);
+            } else {
+                if (p.beta != 0.0) o0 = fma(p.beta, ccol[m], o0);
+                ccol[m] = o0;
+                if (m + 1 < p.m) {
+                    if (p.beta != 0.0) o1 = fma(p.beta, ccol[m + 1], o1);
+                    ccol[m + 1] = o1;
+                }
+            }
+        }
+    }
+}
+
+template <bool TA, bool TB, int VEC>
+cudaError_t launch_ws(const Params& p, cudaStream_t stream) {
+    auto kern = gemm_f64_dmma_ws_kernel<TA, TB, VEC>;
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+        if (e != cudaSuccess) return e;
+        configured = true;
+    }
+    count_launch();
+    kern<<<dim3(unsigned(p.tiles_m) * unsigned(p.tiles_n)), kThreadsWS, kSmemBytes, stream>>>(p);
+    return cudaGetLastError();
+}
+
 }  // namespace
 
 int gemm_f64_dmma(int transA, int transB, int64_t m, int64_t n, int64_t k, double alpha,
@@ -228,6 +408,17 @@ int gemm_f64_dmma(int transA, int transB, int64_t m, int64_t n, int64_t k, doubl
     else if (!ta && tb) e = launch<false, true, V>(p, stream);        \
     else if (ta && !tb) e = launch<true, false, V>(p, stream);        \
     else e = launch<true, true, V>(p, stream);
+    static const bool ws = [] { const char* v = std::getenv("ELB200_F64_WS"); return v && std::atoi(v) != 0; }();
+    if (ws) {
+#define ELB_DISPATCH_WS(V)                                                \
+    if (!ta && !tb) e = launch_ws<false, false, V>(p, stream);           \
+    else if (!ta && tb) e = launch_ws<false, true, V>(p, stream);        \
+    else if (ta && !tb) e = launch_ws<true, false, V>(p, stream);        \
+    else e = launch_ws<true, true, V>(p, stream);
+        if (aligned) { ELB_DISPATCH_WS(2) } else { ELB_DISPATCH_WS(1) }
+#undef ELB_DISPATCH_WS
+        return e == cudaSuccess ? ELB200_OK : ELB200_ERR_CUDA;
+    }
     if (aligned) { ELB_DISPATCH(2) } else { ELB_DISPATCH(1) }
 #undef ELB_DISPATCH
     return e == cudaSuccess ? ELB200_OK : ELB200_ERR_CUDA;
