@@ -3,6 +3,7 @@
 // (plan.hpp) replaces the reference's per-pair routines; AllGather and ReduceScatter shapes run
 // on the matching NCCL collective over the grid's MC / MR / VC communicator.
 #include <algorithm>
+#include <cstdlib>
 
 #include "engine.hpp"
 #include "engine_dev.hpp"
@@ -78,6 +79,25 @@ void Copy(const DistMat<T>& A, DistMat<T>& B) {
                 one.seg.buf_offset = 0;
                 run_lattice<T>(ELB200_PACK, std::vector<Message>{one}, Abuf, A.ldim, slot.p, T(0), s);
                 send = slot.p;
+            }
+            // Large blocks: do not wait for the whole gather. My own block goes straight from A into B (no copy
+            // into my own slot) while the peers' blocks are in flight, and each peer's block is unpacked as soon
+            // as ITS arrival flag is up — transfers from the other peers continue underneath. Small messages are
+            // latency-bound and keep the one-wait, one-launch form. (ELB200_AG_SPLIT_MB, default 4; 0 disables.)
+            static const int64_t split_mb = [] { const char* e = std::getenv("ELB200_AG_SPLIT_MB"); return e ? std::atoll(e) : 4ll; }();
+            static const int64_t split_b = [] { const char* e = std::getenv("ELB200_AG_SPLIT_BYTES"); return e ? std::atoll(e) : 0ll; }();
+            const int64_t split_bytes = split_b > 0 ? split_b : split_mb << 20;
+            if (split_bytes > 0 && plan.portion * int64_t(sizeof(T)) >= split_bytes && plan.recvs[size_t(idx)].peer == g.vc_rank) {
+                PeerArena::Ticket t = g.arena->AllGatherBegin(Grid::arena_channel(plan.comm_dist), members, idx, send,
+                                                              size_t(mine) * sizeof(T), size_t(plan.portion) * sizeof(T), true, s);
+                if (mine > 0) lattice_to_lattice<T>(s0, A.buf, A.ldim, plan.recvs[size_t(idx)].seg, B.buf, B.ldim, s);
+                for (int i = 0; i < gsz; ++i) {
+                    if (i == idx) continue;
+                    g.arena->WaitMember(t, members, idx, i, s);
+                    run_lattice<T>(ELB200_UNPACK, std::vector<Message>{plan.recvs[size_t(i)]}, B.buf, B.ldim, static_cast<T*>(t.data), T(0), s);
+                }
+                g.arena->Release(t, members, idx, s);
+                return;
             }
             PeerArena::Ticket t = g.arena->AllGather(Grid::arena_channel(plan.comm_dist), members, idx, send,
                                                      size_t(mine) * sizeof(T), size_t(plan.portion) * sizeof(T), s);

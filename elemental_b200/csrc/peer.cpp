@@ -217,8 +217,8 @@ void PeerArena::wait_flag(uint32_t* local, uint32_t seq, cudaStream_t s) {
     if (r != CUDA_SUCCESS) throw EngineError(ELB200_ERR_CUDA, "cuStreamWaitValue32 failed");
 }
 
-PeerArena::Ticket PeerArena::AllGather(int channel, const std::vector<int>& members, int my_index, const void* send,
-                                       size_t send_bytes, size_t portion_bytes, cudaStream_t s) {
+PeerArena::Ticket PeerArena::AllGatherBegin(int channel, const std::vector<int>& members, int my_index, const void* send,
+                                            size_t send_bytes, size_t portion_bytes, bool skip_self, cudaStream_t s) {
     const int g = int(members.size());
     if (portion_bytes * size_t(g) > slot_bytes_ || send_bytes > portion_bytes)
         throw EngineError(ELB200_ERR_ARG, "PeerArena::AllGather: message larger than an arena slot");
@@ -230,9 +230,10 @@ PeerArena::Ticket PeerArena::AllGather(int channel, const std::vector<int>& memb
     // 1. my previous block in each member's slot must have been consumed
     for (int i = 0; i < g; ++i)
         if (i != my_index) wait_flag(flag(rank_, ACK, channel, t.slot, members[i]), t.seq - 1, s);
-    // 2. my block into every member's slot (mine included), 3. tell them: payload and flag for one
-    // member stay on one lane (ordered), different members go out concurrently
+    // 2. my block into every member's slot (mine included unless skip_self), 3. tell them: payload and flag
+    // for one member stay on one lane (ordered), different members go out concurrently
     for (int i = 0; i < g; ++i) {
+        if (i == my_index && skip_self) continue;
         cudaStream_t ls = fork(i, s);
         if (send_bytes)
             cuda_check(cudaMemcpyAsync(slot_base(members[i], channel, t.slot) + size_t(my_index) * portion_bytes, send,
@@ -240,10 +241,19 @@ PeerArena::Ticket PeerArena::AllGather(int channel, const std::vector<int>& memb
         if (i != my_index) write_flag(flag(members[i], ARRIVE, channel, t.slot, rank_), t.seq, ls);
     }
     join(s);
-    // 4. wait for theirs
-    for (int i = 0; i < g; ++i)
-        if (i != my_index) wait_flag(flag(rank_, ARRIVE, channel, t.slot, members[i]), t.seq, s);
     t.data = slot_base(rank_, channel, t.slot);
+    return t;
+}
+
+void PeerArena::WaitMember(const Ticket& t, const std::vector<int>& members, int my_index, int i, cudaStream_t s) {
+    if (i != my_index) wait_flag(flag(rank_, ARRIVE, t.channel, t.slot, members[i]), t.seq, s);
+}
+
+PeerArena::Ticket PeerArena::AllGather(int channel, const std::vector<int>& members, int my_index, const void* send,
+                                       size_t send_bytes, size_t portion_bytes, cudaStream_t s) {
+    Ticket t = AllGatherBegin(channel, members, my_index, send, send_bytes, portion_bytes, false, s);
+    // 4. wait for theirs
+    for (int i = 0; i < int(members.size()); ++i) WaitMember(t, members, my_index, i, s);
     return t;
 }
 

@@ -42,6 +42,13 @@ public:
     // All members pass the same channel and portion_bytes; send_bytes <= portion_bytes may differ.
     Ticket AllGather(int channel, const std::vector<int>& members, int my_index, const void* send,
                      size_t send_bytes, size_t portion_bytes, cudaStream_t s);
+    // The same gather in two halves, so that the consumer can start on the blocks that have landed while the
+    // others are still in flight: Begin sends my block to every member (skip_self: not into my own slot — the
+    // caller reads its own block from the source) and returns without waiting; WaitMember blocks `s` until
+    // member i's block has arrived in my slot. AllGather == Begin(skip_self = false) + WaitMember for all.
+    Ticket AllGatherBegin(int channel, const std::vector<int>& members, int my_index, const void* send, size_t send_bytes,
+                          size_t portion_bytes, bool skip_self, cudaStream_t s);
+    void WaitMember(const Ticket& t, const std::vector<int>& members, int my_index, int i, cudaStream_t s);
     // Call after the last read of ticket.data has been enqueued on `s`.
     void Release(const Ticket& t, const std::vector<int>& members, int my_index, cudaStream_t s);
 

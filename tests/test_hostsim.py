@@ -54,7 +54,10 @@ def test_engine_2x2_peer_arena_all_cases(simlib):
 def test_engine_2x4_bench_grid(simlib):
     """The 8-GPU grid shape of BASELINE C3 (2 x 4): redistributions, contractions, all Gemm variants, the
     level-3 family, and the reference's own per-rank outputs."""
-    out = _run("2x4", "--only", "check_redistributions,check_contractions,check_gemm_variants_f64,check_gemm_proxies_f32,run_level3,check_fuzz")
+    # ELB200_AG_SPLIT_BYTES=1: every arena AllGather takes the split form (own block straight from the source,
+    # each peer's block unpacked on ITS arrival); the other runs use the one-wait form at these sizes
+    out = _run("2x4", "--only", "check_redistributions,check_contractions,check_gemm_variants_f64,check_gemm_proxies_f32,run_level3,check_fuzz",
+               env={"ELB200_AG_SPLIT_BYTES": "1"})
     assert "'level3_ref_golden': 60" in out and "'dist_ref_golden': 164" in out
 
 
@@ -66,7 +69,7 @@ def test_engine_3x2_nccl_fallback(simlib):
 
 
 @pytest.mark.parametrize("grid,env,extra", [("1x2", {}, ",run_level3"), ("2x1", {}, ",run_level3"),
-                                             ("2x3", {"ELB200_P2P": "0"}, ",run_level3"), ("2x2", {"ELB200_DIRECT": "0"}, ""),
+                                             ("2x3", {"ELB200_P2P": "0"}, ",run_level3"), ("2x2", {"ELB200_DIRECT": "0", "ELB200_AG_SPLIT_BYTES": "1"}, ""),
                                              ("2x2", {"ELB200_OVERLAP": "0"}, "")])
 def test_engine_multi_panel_pipeline(simlib, grid, env, extra):
     """Narrow panels (ELB200_PANEL_K=512, k = 1300): several panels per Gemm through the two-slot
