@@ -16,7 +16,7 @@ def main() -> int:
     ap.add_argument("--only", default="")
     ap.add_argument("--level3", action="store_true", help="run dist_cases.run_level3 instead of run_all")
     args = ap.parse_args()
-    r, c = (int(x) for x in args.grid.lower().split("x"))
+    grids = [tuple(int(x) for x in gs.lower().split("x")) for gs in args.grid.split(",")]   # "2x2" or "1x2,2x1"
     from tests.hostsim import sim_el
     from tests import dist_cases as dc
     dc.use_backend(sim_el)
@@ -37,9 +37,10 @@ def main() -> int:
                 out[name] = getattr(dc, name)(grid)
         return out
 
-    t0 = time.time()
-    res = sim_el.run_grid(r, c, body)
-    print(f"hostsim grid {r}x{c}: {res[0]} in {time.time() - t0:.1f} s", flush=True)
+    for (r, c) in grids:
+        t0 = time.time()
+        res = sim_el.run_grid(r, c, body)
+        print(f"hostsim grid {r}x{c}: {res[0]} in {time.time() - t0:.1f} s", flush=True)
     print("HOSTSIM_PASS", flush=True)
     return 0
 
