@@ -513,6 +513,51 @@ trapezoid_kernel(int64_t rows, int64_t cols, int upper, int64_t offset, int64_t 
     }
 }
 
+// 128-bit version: a thread owns N consecutive rows (float4 / double2) of a column. The mask is monotone down a
+// column, so the group is uniform (all inside or all outside) unless the boundary cuts through it; only those
+// groups — at most one per column — fall back to per-element work.
+template <typename T, int OP>
+__global__ void __launch_bounds__(256)
+trapezoid_vec_kernel(int64_t rows_v, int64_t cols, int upper, int64_t offset, int64_t row0, int64_t row_step, int64_t col0,
+                     int64_t col_step, T alpha, const T* __restrict__ X, int64_t ldx, T* Y, int64_t ldy) {
+    using V = typename VecOf<T>::type;
+    constexpr int N = VecOf<T>::N;
+    const int64_t iv = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (iv >= rows_v) return;
+    const int64_t i = iv * N;
+    const int64_t g_first = row0 + i * row_step, g_last = row0 + (i + N - 1) * row_step;
+    for (int64_t j = int64_t(blockIdx.y) * blockDim.y + threadIdx.y; j < cols; j += int64_t(gridDim.y) * blockDim.y) {
+        const int64_t lim = col0 + j * col_step - offset;  // inside: upper gi <= lim, lower gi >= lim
+        const bool in_first = upper ? (g_first <= lim) : (g_first >= lim);
+        const bool in_last = upper ? (g_last <= lim) : (g_last >= lim);
+        T* y = Y + i + j * ldy;
+        if (in_first == in_last) {
+            if (OP == TRAP_MAKE ? in_first : !in_first) continue;  // nothing to do for this group
+            V* yv = reinterpret_cast<V*>(y);
+            if constexpr (OP == TRAP_SCALE) {
+                *yv = alpha == T(0) ? vsplat(T(0)) : vscale(alpha, *yv);
+            } else if constexpr (OP == TRAP_AXPY) {
+                *yv = vaxpy(alpha, *reinterpret_cast<const V*>(X + i + j * ldx), *yv);
+            } else {
+                *yv = vsplat(T(0));
+            }
+        } else {
+#pragma unroll
+            for (int e = 0; e < N; ++e) {
+                const int64_t gi = g_first + e * row_step;
+                const bool inside = upper ? (gi <= lim) : (gi >= lim);
+                if constexpr (OP == TRAP_SCALE) {
+                    if (inside) y[e] = alpha == T(0) ? T(0) : alpha * y[e];
+                } else if constexpr (OP == TRAP_AXPY) {
+                    if (inside) y[e] = fma(alpha, X[i + e + j * ldx], y[e]);
+                } else {
+                    if (!inside) y[e] = T(0);
+                }
+            }
+        }
+    }
+}
+
 template <typename T>
 int launch_trapezoid(int op, int uplo, int64_t offset, int64_t rows, int64_t cols, int64_t row0, int64_t row_step,
                      int64_t col0, int64_t col_step, T alpha, const T* X, int64_t ldx, T* Y, int64_t ldy, void* stream) {
@@ -523,10 +568,14 @@ int launch_trapezoid(int op, int uplo, int64_t offset, int64_t rows, int64_t col
     if (!Y || ldy < rows || (op == TRAP_AXPY && (!X || ldx < rows))) return ELB200_ERR_ARG;
     if (op == TRAP_SCALE && alpha == T(1)) return ELB200_OK;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
+    constexpr int NV = VecOf<T>::N;
+    const bool vec = rows % NV == 0 && ldy % NV == 0 && (reinterpret_cast<uintptr_t>(Y) & 15u) == 0 &&
+                     (op != TRAP_AXPY || (ldx % NV == 0 && (reinterpret_cast<uintptr_t>(X) & 15u) == 0));
+    const int64_t rows_t = vec ? rows / NV : rows;  // rows in units of one thread's work
     int bx = 32;
-    while (bx < 256 && bx < rows) bx <<= 1;
+    while (bx < 256 && bx < rows_t) bx <<= 1;
     const int by = 256 / bx;
-    const int64_t gx = (rows + bx - 1) / bx;
+    const int64_t gx = (rows_t + bx - 1) / bx;
     int64_t gy = (cols + by - 1) / by;
     const int64_t want = std::max<int64_t>(1, 32 * int64_t(device_sm_count()) / gx);  // enough CTAs to fill the SMs, grid-stride beyond
     if (gy > want) gy = want;
@@ -534,6 +583,15 @@ int launch_trapezoid(int op, int uplo, int64_t offset, int64_t rows, int64_t col
     const dim3 grid(static_cast<unsigned>(gx), static_cast<unsigned>(gy)), block(bx, by);
     const int upper = uplo == 1;
     count_launch();
+    if (vec) {
+        if (op == TRAP_SCALE)
+            trapezoid_vec_kernel<T, TRAP_SCALE><<<grid, block, 0, s>>>(rows_t, cols, upper, offset, row0, row_step, col0, col_step, alpha, X, ldx, Y, ldy);
+        else if (op == TRAP_AXPY)
+            trapezoid_vec_kernel<T, TRAP_AXPY><<<grid, block, 0, s>>>(rows_t, cols, upper, offset, row0, row_step, col0, col_step, alpha, X, ldx, Y, ldy);
+        else
+            trapezoid_vec_kernel<T, TRAP_MAKE><<<grid, block, 0, s>>>(rows_t, cols, upper, offset, row0, row_step, col0, col_step, alpha, X, ldx, Y, ldy);
+        return check_cuda(cudaGetLastError(), "trapezoid_vec_kernel");
+    }
     if (op == TRAP_SCALE)
         trapezoid_kernel<T, TRAP_SCALE><<<grid, block, 0, s>>>(rows, cols, upper, offset, row0, row_step, col0, col_step, alpha, X, ldx, Y, ldy);
     else if (op == TRAP_AXPY)
