@@ -17,7 +17,8 @@ if [ "$N" = "1" ]; then
   # 2. the bench lines (fp32 = BASELINE C2; fp64); e2e now has four block slots + streamed A
   python bench.py --steps 5 --warmup 3 > $OUT/bench_f32_1gpu.json 2>> $OUT/session.log
   python bench.py --steps 5 --warmup 3 --dtype f64 > $OUT/bench_f64_1gpu.json 2>> $OUT/session.log
-  # 3. fp64 kernel A/B: current vs warp-specialised (ELB200_F64_WS=1), same binary
+  # 3. fp64 kernel A/B: current vs warp-specialised (ELB200_F64_WS=1), same binary; the kernel tests with the variant on
+  ELB200_F64_WS=1 timeout 600 python -m pytest tests/test_gpu_kernels.py -m gpu -x -q -k gemm > $OUT/f64_ws_pytest.log 2>&1; echo "f64 WS pytest exit $?" >> $OUT/session.log
   run tools/gemm_check perf f64 8192 16384
   ELB200_F64_WS=1 tools/gemm_check correctness f64 > $OUT/f64_ws_correctness.log 2>&1; echo "f64 WS correctness exit $?" >> $OUT/session.log
   ELB200_F64_WS=1 tools/gemm_check perf f64 8192 16384 > $OUT/f64_ws_perf.log 2>&1
