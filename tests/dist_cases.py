@@ -719,12 +719,62 @@ def check_fuzz(grid, dtype=torch.float64, iters=None, seed=None) -> int:
     return cnt
 
 
+def check_level3_errors(grid, dtype=torch.float64) -> int:
+    """Argument errors of the level-3 family come back as ELB200_ERR_ARG (the reference throws LogicError:
+    "Nonconformal Syrk" Syrk.cpp:108-117, "A must be square" / "Nonconformal Trsm" Trsm.cpp:146-156, "Dist of RHS must
+    conform with that of triangle" Trsm.cpp:513-517, EnsureConformal Trrk/Local.hpp:20-48, "Cannot make non-square
+    matrix symmetric" MakeSymmetric.hpp:60-61) and leave the operands untouched."""
+    og = _grid_oracle(grid)
+    npdt = NPDT[dtype]
+    me = grid.Rank()
+    G = OG.uniform_matrix(12, 12, 501, npdt, 0.0, 1.0)
+    R = OG.uniform_matrix(12, 9, 502, npdt, 0.0, 1.0)
+    mk = lambda U, V, M: el.DistMatrix(grid, U, V, dtype).from_global(M)  # noqa: E731
+    sq, rect = mk(el.MC, el.MR, G), mk(el.MC, el.MR, R)
+    star = mk(el.STAR, el.STAR, G)
+    cnt = 0
+
+    def must_fail(fn, what):
+        nonlocal cnt
+        try:
+            fn()
+        except Exception as e:  # Elb200Error of whichever binding is active
+            assert getattr(e, "status", None) == 2, (what, e)
+            cnt += 1
+            return
+        raise AssertionError(f"{what}: no error raised")
+
+    must_fail(lambda: el.Syrk(el.LOWER, el.NORMAL, 1.0, rect, 0.0, rect), "Syrk into a non-square C")
+    must_fail(lambda: el.Syrk(el.LOWER, el.TRANSPOSE, 1.0, rect, 0.0, sq), "Syrk with n != C.Height()")
+    must_fail(lambda: el.Syrk(2, el.NORMAL, 1.0, rect, 0.0, sq), "Syrk with a bad uplo")
+    must_fail(lambda: el.Trrk(el.UPPER, el.NORMAL, el.NORMAL, 1.0, rect, rect, 0.0, sq), "Trrk with nonconformal A, B")
+    must_fail(lambda: el.Symm(el.LEFT, el.LOWER, 1.0, rect, rect, 0.0, rect), "Symm with a non-square A")
+    must_fail(lambda: el.Symm(el.RIGHT, el.LOWER, 1.0, sq, rect, 0.0, rect), "Symm RIGHT with A of the wrong size")
+    must_fail(lambda: el.Trsm(el.LEFT, el.LOWER, el.NORMAL, el.NON_UNIT, 1.0, rect, rect), "Trsm with a non-square A")
+    must_fail(lambda: el.Trsm(el.RIGHT, el.LOWER, el.NORMAL, el.NON_UNIT, 1.0, sq, rect), "Trsm RIGHT with A of the wrong size")
+    must_fail(lambda: el.LocalTrsm(el.LEFT, el.LOWER, el.NORMAL, el.NON_UNIT, 1.0, sq, rect), "LocalTrsm with a distributed triangle")
+    must_fail(lambda: el.LocalTrsm(el.LEFT, el.LOWER, el.NORMAL, el.NON_UNIT, 1.0, star, rect), "LocalTrsm LEFT with X distributed over rows")
+    must_fail(lambda: el.MakeSymmetric(el.LOWER, rect), "MakeSymmetric of a non-square matrix")
+    must_fail(lambda: el.AxpyTrapezoid(el.LOWER, 1.0, rect, sq), "AxpyTrapezoid with nonconformal X, Y")
+    a_mc = el.DistMatrix(grid, el.MC, el.STAR, dtype).from_global(R)
+    b_mr = el.DistMatrix(grid, el.STAR, el.MR, dtype).from_global(np.asfortranarray(R.T))
+    must_fail(lambda: el.LocalTrrk(el.LOWER, el.TRANSPOSE, el.NORMAL, 1.0, a_mc, b_mr, 0.0, sq), "LocalTrrk with [MC,*] passed as transposed A")
+    if og.r > 1:
+        c_mis = el.DistMatrix(grid, el.MC, el.MR, dtype).Align(1, 0).from_global(G)
+        must_fail(lambda: el.LocalTrrk(el.LOWER, el.NORMAL, el.NORMAL, 1.0, a_mc, b_mr, 0.0, c_mis), "LocalTrrk with A not aligned with C")
+    # nothing was modified
+    assert np.array_equal(sq.get_local(), OD.local_of(G, OD.Spec(OD.MC, OD.MR, 0, 0, 12, 12), og, me))
+    assert np.array_equal(rect.get_local(), OD.local_of(R, OD.Spec(OD.MC, OD.MR, 0, 0, 12, 9), og, me))
+    return cnt
+
+
 def run_level3(grid) -> dict:
     """The triangular rank-k family and the comparisons with the reference's own per-rank outputs."""
     out = {}
     out["trapezoids"] = check_trapezoids(grid, torch.float64) + check_trapezoids(grid, torch.float32)
     out["level3"] = check_level3(grid, torch.float64) + check_level3(grid, torch.float32)
     out["trsm"] = check_trsm(grid, torch.float64) + check_trsm(grid, torch.float32)
+    out["level3_errors"] = check_level3_errors(grid, torch.float64)
     out["level3_ref_golden"] = check_level3_golden(grid)
     out["dist_ref_golden"] = check_dist_golden(grid)
     out["fuzz"] = check_fuzz(grid, torch.float64, iters=30) + check_fuzz(grid, torch.float32, iters=30)

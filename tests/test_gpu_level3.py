@@ -177,6 +177,11 @@ def test_trsm_1x1(grid1, dtype):
     assert dc.check_trsm(grid1, dtype) == 40
 
 
+def test_level3_errors_1x1(grid1):
+    from tests import dist_cases as dc
+    assert dc.check_level3_errors(grid1, torch.float64) == 13
+
+
 def test_level3_matches_reference_outputs_1x1(grid1):
     """This library against the reference's own outputs for the same inputs (its CPU build, 1 x 1)."""
     from tests import dist_cases as dc
