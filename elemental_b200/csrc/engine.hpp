@@ -58,6 +58,14 @@ public:
     int comm_index(Dist d) const { return d == MC ? me.mc : d == MR ? me.mr : vc_rank; }
     static int arena_channel(Dist d) { return d == MC ? 0 : d == MR ? 1 : 2; }
 
+    // NCCL fallbacks issued from different streams (the pipelines put redistributions on the comm stream) are
+    // serialised in issue order: NCCL does not allow concurrent operations on one communicator, and the
+    // MC / MR / VC communicators may be the same object. Bracket every NCCL call (group) with these.
+    void NcclBegin(cudaStream_t s);
+    void NcclEnd(cudaStream_t s);
+    cudaEvent_t nccl_done = nullptr;
+    bool nccl_recorded = false;
+
     int size() const { return shape.size(); }
     ncclComm_t comm_for(Dist d) const { return d == MC ? mc_comm : d == MR ? mr_comm : world; }
     // Algorithmic blocksize stack (reference src/blas_like/blocksizes.cpp:35-67; default 128,

@@ -94,6 +94,15 @@ Grid::Grid(int height, int width, int vc, const ncclUniqueId* id, int dev) {
     }
 }
 
+void Grid::NcclBegin(cudaStream_t s) {
+    if (nccl_recorded) cuda_check(cudaStreamWaitEvent(s, nccl_done, 0), "cudaStreamWaitEvent(nccl order)");
+}
+void Grid::NcclEnd(cudaStream_t s) {
+    if (!nccl_done) cuda_check(cudaEventCreateWithFlags(&nccl_done, cudaEventDisableTiming), "cudaEventCreate(nccl order)");
+    cuda_check(cudaEventRecord(nccl_done, s), "cudaEventRecord(nccl order)");
+    nccl_recorded = true;
+}
+
 std::vector<int> Grid::comm_members(Dist d) const {
     std::vector<int> v;
     if (d == MC) for (int i = 0; i < shape.r; ++i) v.push_back(vc_of(shape, GridCoord{i, me.mr}));
@@ -131,6 +140,7 @@ Grid::~Grid() {
     if (comm_stream) cudaStreamDestroy(comm_stream);
     if (h2d_stream) cudaStreamDestroy(h2d_stream);
     if (d2h_stream) cudaStreamDestroy(d2h_stream);
+    if (nccl_done) cudaEventDestroy(nccl_done);
 }
 
 // ------------------------------------------------------------------ DistMat

@@ -293,6 +293,35 @@ void SummaC(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, T
     cudaEventDestroy(start);
 }
 
+// Two-slot panel pipeline shared by SUMMA-A / SUMMA-B: the redistribution of panel p+1 runs on the comm stream
+// (copy engines + small pack / unpack kernels) under the local GEMM and the reduce-scatter of panel p.
+//   ready[s]: panel in slot s is complete        (comm stream -> compute stream)
+//   freed[s]: the GEMM that read slot s is done   (compute stream -> comm stream)
+struct PanelPipe {
+    bool on;
+    cudaStream_t cs, ms;  // panel (comm) stream, main (compute) stream
+    Ev ready[2], freed[2], start;
+    int64_t p = 0;
+    PanelPipe(Grid& g, cudaStream_t main_stream) : on(false), cs(main_stream), ms(main_stream) {
+        // Opt-in (ELB200_AB_PIPELINE=1) until it has run on real multi-GPU hardware: unlike the SUMMA-C / Dot / Trrk
+        // pipelines, here BOTH streams run arena operations with flag waits at the same time (the reduce-scatter of
+        // panel p on the compute stream, the exchange of panel p+1 on the comm stream). Correct and race-free on
+        // hostsim; on hardware, streams that share a work queue could couple those waits.
+        static const bool overlap_on = [] { const char* e = std::getenv("ELB200_AB_PIPELINE"); return e && std::atoi(e) != 0; }();
+        on = g.size() > 1 && g.comm_stream && g.arena && overlap_on;
+        if (on) {
+            cs = g.comm_stream;
+            start.record(ms);  // the operands are ready in main-stream order
+            start.block(cs);
+        }
+    }
+    int slot() const { return on ? int(p & 1) : 0; }
+    void before_panel() { if (on && p >= 2) freed[slot()].block(cs); }      // slot reusable?
+    void panel_ready() { if (on) { ready[slot()].record(cs); ready[slot()].block(ms); } }
+    void panel_consumed() { if (on) freed[slot()].record(ms); ++p; }
+    void finish() { if (on) for (int i = 0; i < 2 && i < p; ++i) freed[i].block(cs); }  // panels die in comm-stream order
+};
+
 // ---- stationary A: per column panel of C, D1 = alpha op(A) op(B)(:,panel) summed over the
 //      grid dimension that shares op(A)'s k index, then scattered into C1 --------------------
 template <typename T>
@@ -301,18 +330,22 @@ void SummaA(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, D
     const int64_t W = Grid::PanelWidth(sizeof(T));
     // k runs over MR when A is used as is (k = A's columns), over MC when A is transposed
     const Dist kd = ta ? MC : MR;
-    DistMat<T> PB(g, tb ? STAR : kd, tb ? kd : STAR, C.stream);       // op(B) panel: k x nb or nb x k
+    PanelPipe pipe(g, C.stream);
+    DistMat<T> PB[2] = {DistMat<T>(g, tb ? STAR : kd, tb ? kd : STAR, pipe.cs), DistMat<T>(g, tb ? STAR : kd, tb ? kd : STAR, pipe.cs)};  // op(B) panel: k x nb or nb x k
     DistMat<T> D1(g, ta ? MR : MC, STAR, C.stream);                   // m x nb partial sums
     DistMat<T> D1s(g, MR, MC, C.stream);
     for (int64_t j0 = 0; j0 < d.n; j0 += W) {
         const int64_t nb = std::min(W, d.n - j0);
         DistMat<T> B1 = tb ? B.View(j0, j0 + nb, 0, d.k) : B.View(0, d.k, j0, j0 + nb);
         DistMat<T> C1 = C.View(0, d.m, j0, j0 + nb);
-        const DistMat<T>& b = panel_as(B1, PB, A.spec);
+        pipe.before_panel();
+        const DistMat<T>& b = panel_as(B1, PB[pipe.slot()], A.spec);
+        pipe.panel_ready();
         D1.col_constrained = D1.row_constrained = false;
         D1.AlignWith(A.spec, true);
         D1.Resize(d.m, nb);
         LocalGemm(ta, tb, alpha, A, b, T(0), D1);
+        pipe.panel_consumed();
         if (!ta) {
             AxpyContract(T(1), D1, C1);          // [MC,*] -> [MC,MR]: ReduceScatter over MR
         } else {
@@ -321,6 +354,7 @@ void SummaA(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, D
             Axpy(T(1), D1s, C1);                 // [MR,MC] -> [MC,MR] exchange + local axpy
         }
     }
+    pipe.finish();
 }
 
 // ---- stationary B: per row panel of C -----------------------------------------------------------
@@ -330,18 +364,22 @@ void SummaB(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, D
     const int64_t W = Grid::PanelWidth(sizeof(T));
     // k runs over MC when B is used as is (k = B's rows), over MR when B is transposed
     const Dist kd = tb ? MR : MC;
-    DistMat<T> PA(g, ta ? kd : STAR, ta ? STAR : kd, C.stream);       // op(A) panel: mb x k or k x mb
+    PanelPipe pipe(g, C.stream);
+    DistMat<T> PA[2] = {DistMat<T>(g, ta ? kd : STAR, ta ? STAR : kd, pipe.cs), DistMat<T>(g, ta ? kd : STAR, ta ? STAR : kd, pipe.cs)};  // op(A) panel: mb x k or k x mb
     DistMat<T> D1(g, STAR, tb ? MC : MR, C.stream);                   // mb x n partial sums
     DistMat<T> D1s(g, MR, MC, C.stream);
     for (int64_t i0 = 0; i0 < d.m; i0 += W) {
         const int64_t mb = std::min(W, d.m - i0);
         DistMat<T> A1 = ta ? A.View(0, d.k, i0, i0 + mb) : A.View(i0, i0 + mb, 0, d.k);
         DistMat<T> C1 = C.View(i0, i0 + mb, 0, d.n);
-        const DistMat<T>& a = panel_as(A1, PA, B.spec);
+        pipe.before_panel();
+        const DistMat<T>& a = panel_as(A1, PA[pipe.slot()], B.spec);
+        pipe.panel_ready();
         D1.col_constrained = D1.row_constrained = false;
         D1.AlignWith(B.spec, true);
         D1.Resize(mb, d.n);
         LocalGemm(ta, tb, alpha, a, B, T(0), D1);
+        pipe.panel_consumed();
         if (!tb) {
             AxpyContract(T(1), D1, C1);          // [*,MR] -> [MC,MR]: ReduceScatter over MC
         } else {
@@ -350,6 +388,7 @@ void SummaB(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, D
             Axpy(T(1), D1s, C1);
         }
     }
+    pipe.finish();
 }
 
 // ---- Dot: k spread over all p ranks, C tiles reduce-scattered over the whole grid ---------------

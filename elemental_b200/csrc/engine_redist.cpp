@@ -117,7 +117,9 @@ void Copy(const DistMat<T>& A, DistMat<T>& B) {
             }
             send = slot;
         }
+        g.NcclBegin(s);
         nccl_check(ncclAllGather(send, recv, size_t(plan.portion), Dev<T>::nccl, comm, s), "ncclAllGather");
+        g.NcclEnd(s);
         run_lattice<T>(ELB200_UNPACK, plan.recvs, B.buf, B.ldim, recv, T(0), s);
         return;
     }
@@ -156,12 +158,14 @@ void Copy(const DistMat<T>& A, DistMat<T>& B) {
     }
     Scratch<T> sbuf(plan.send_elems, s), rbuf(plan.recv_elems, s);
     run_lattice<T>(ELB200_PACK, plan.sends, Abuf, A.ldim, sbuf.p, T(0), s);
+    g.NcclBegin(s);
     nccl_check(ncclGroupStart(), "ncclGroupStart");
     for (const Message& m : plan.sends)
         nccl_check(ncclSend(sbuf.p + m.seg.buf_offset, size_t(m.count()), Dev<T>::nccl, m.peer, g.world, s), "ncclSend");
     for (const Message& m : plan.recvs)
         nccl_check(ncclRecv(rbuf.p + m.seg.buf_offset, size_t(m.count()), Dev<T>::nccl, m.peer, g.world, s), "ncclRecv");
     nccl_check(ncclGroupEnd(), "ncclGroupEnd");
+    g.NcclEnd(s);
     run_lattice<T>(ELB200_UNPACK, plan.recvs, B.buf, B.ldim, rbuf.p, T(0), s);
     if (plan.has_self)
         lattice_to_lattice<T>(plan.self_send.seg, A.buf, A.ldim, plan.self_recv.seg, B.buf, B.ldim, s);
@@ -265,7 +269,9 @@ void AxpyContract(T alpha, const DistMat<T>& A, DistMat<T>& B) {
     Scratch<T> stage(int64_t(plan.group + 1) * plan.portion, s);
     run_lattice<T>(ELB200_PACK, plan.packs, Abuf, A.ldim, stage.p, T(0), s);
     T* recv = stage.p + int64_t(plan.group) * plan.portion;
+    g.NcclBegin(s);
     nccl_check(ncclReduceScatter(stage.p, recv, size_t(plan.portion), Dev<T>::nccl, ncclSum, comm, s), "ncclReduceScatter");
+    g.NcclEnd(s);
     elb200_segment u = plan.unpack;
     u.buf_offset = int64_t(plan.group) * plan.portion;
     if (u.rows > 0 && u.cols > 0) Dev<T>::lattice(ELB200_UNPACK_AXPY, 1, &u, B.buf, B.ldim, stage.p, alpha, s);

@@ -1,7 +1,7 @@
 // hostsim: test double of the CUDA runtime entry points the elb engine uses (see sim.hpp).
 // "Device" memory is host memory tracked in a registry (every access by a simulated kernel or
 // copy is bounds-checked against it, freed memory is poisoned); streams are FIFO worker threads;
-// events carry generations; cuStreamWaitValue32 is a stream-ordered spin on a memory word.
+// every event record is its own object (a wait captures the record that was latest when it was issued); cuStreamWaitValue32 is a stream-ordered spin on a memory word.
 #include <cuda.h>
 #include <cuda_runtime.h>
 
@@ -145,20 +145,25 @@ Stream* S(cudaStream_t s) {
 }
 
 // ------------------------------------------------------------------ events
-struct EventState {
+// One cudaEventRecord = one Record object. A wait (cudaStreamWaitEvent, cudaEventSynchronize) captures the
+// record that was the latest when the wait was ISSUED and waits for exactly that one — re-recording the
+// event afterwards, on this or another stream, neither satisfies nor delays it (CUDA semantics; a
+// "highest completed generation" counter would be wrong when one event is recorded on two streams).
+struct Record {
     std::mutex m;
     std::condition_variable cv;
-    uint64_t recorded = 0, completed = 0;
+    bool done = false;
     Clock::time_point when;
 };
 struct Event {
-    std::shared_ptr<EventState> st = std::make_shared<EventState>();
+    std::mutex m;
+    std::shared_ptr<Record> latest;  // null until the first record
 };
 
-void wait_event(const std::shared_ptr<EventState>& st, uint64_t gen, const char* who) {
-    std::unique_lock<std::mutex> l(st->m);
-    if (!st->cv.wait_for(l, std::chrono::duration<double>(wait_timeout_seconds()), [&] { return st->completed >= gen; }))
-        fail("%s: event generation %llu never completed (deadlock?)", who, (unsigned long long)gen);
+void wait_record(const std::shared_ptr<Record>& r, const char* who) {
+    std::unique_lock<std::mutex> l(r->m);
+    if (!r->cv.wait_for(l, std::chrono::duration<double>(wait_timeout_seconds()), [&] { return r->done; }))
+        fail("%s: the recorded work never completed (deadlock?)", who);
 }
 
 void copy_bytes(void* dst, const void* src, size_t n) {
@@ -337,54 +342,50 @@ cudaError_t cudaEventCreateWithFlags(cudaEvent_t* e, unsigned int) {
 }
 cudaError_t cudaEventCreate(cudaEvent_t* e) { return cudaEventCreateWithFlags(e, 0); }
 cudaError_t cudaEventDestroy(cudaEvent_t e) {
-    delete reinterpret_cast<Event*>(e);  // queued records / waits keep the shared state alive
+    delete reinterpret_cast<Event*>(e);  // queued records / waits hold their Record through shared_ptr
     return cudaSuccess;
 }
 cudaError_t cudaEventRecord(cudaEvent_t e, cudaStream_t s) {
     if (!e) return cudaErrorInvalidResourceHandle;
-    std::shared_ptr<EventState> st = reinterpret_cast<Event*>(e)->st;
-    uint64_t gen;
+    Event* ev = reinterpret_cast<Event*>(e);
+    auto rec = std::make_shared<Record>();
     {
-        std::lock_guard<std::mutex> l(st->m);
-        gen = ++st->recorded;
+        std::lock_guard<std::mutex> l(ev->m);
+        ev->latest = rec;
     }
-    enqueue(s, [st, gen] {
+    enqueue(s, [rec] {
         {
-            std::lock_guard<std::mutex> l(st->m);
-            if (gen > st->completed) st->completed = gen;
-            st->when = Clock::now();
+            std::lock_guard<std::mutex> l(rec->m);
+            rec->done = true;
+            rec->when = Clock::now();
         }
-        st->cv.notify_all();
+        rec->cv.notify_all();
     });
     return cudaSuccess;
 }
+static std::shared_ptr<Record> latest_record(cudaEvent_t e) {
+    Event* ev = reinterpret_cast<Event*>(e);
+    std::lock_guard<std::mutex> l(ev->m);
+    return ev->latest;
+}
 cudaError_t cudaStreamWaitEvent(cudaStream_t s, cudaEvent_t e, unsigned int) {
     if (!e) return cudaErrorInvalidResourceHandle;
-    std::shared_ptr<EventState> st = reinterpret_cast<Event*>(e)->st;
-    uint64_t gen;
-    {
-        std::lock_guard<std::mutex> l(st->m);
-        gen = st->recorded;  // the most recent record at the time of THIS call (CUDA semantics)
-    }
-    if (gen == 0) return cudaSuccess;  // never recorded: no-op
-    enqueue(s, [st, gen] { wait_event(st, gen, "cudaStreamWaitEvent"); });
+    std::shared_ptr<Record> rec = latest_record(e);  // the most recent record at the time of THIS call
+    if (!rec) return cudaSuccess;                     // never recorded: no-op
+    enqueue(s, [rec] { wait_record(rec, "cudaStreamWaitEvent"); });
     return cudaSuccess;
 }
 cudaError_t cudaEventSynchronize(cudaEvent_t e) {
     if (!e) return cudaErrorInvalidResourceHandle;
-    std::shared_ptr<EventState> st = reinterpret_cast<Event*>(e)->st;
-    uint64_t gen;
-    {
-        std::lock_guard<std::mutex> l(st->m);
-        gen = st->recorded;
-    }
-    if (gen) wait_event(st, gen, "cudaEventSynchronize");
+    std::shared_ptr<Record> rec = latest_record(e);
+    if (rec) wait_record(rec, "cudaEventSynchronize");
     return cudaSuccess;
 }
 cudaError_t cudaEventElapsedTime(float* ms, cudaEvent_t a, cudaEvent_t b) {
     if (!a || !b) return cudaErrorInvalidResourceHandle;
-    auto sa = reinterpret_cast<Event*>(a)->st, sb = reinterpret_cast<Event*>(b)->st;
-    *ms = std::chrono::duration<float, std::milli>(sb->when - sa->when).count();
+    auto ra = latest_record(a), rb = latest_record(b);
+    if (!ra || !rb) return cudaErrorInvalidResourceHandle;
+    *ms = std::chrono::duration<float, std::milli>(rb->when - ra->when).count();
     return cudaSuccess;
 }
 

@@ -29,7 +29,8 @@ def simlib():
 
 def _run(grid, *args, env=None, timeout=900):
     # ELB200_HOST_KRANGE=16: the host-operand Gemm streams A in several k ranges at the small k of the cases
-    e = dict(os.environ, HOSTSIM_TIMEOUT="90", ELB200_ARENA_MB="8", OMP_NUM_THREADS="1", ELB200_HOST_KRANGE="16")
+    # ELB200_AB_PIPELINE=1: the opt-in SUMMA-A / SUMMA-B panel pipeline is exercised here
+    e = dict(os.environ, HOSTSIM_TIMEOUT="90", ELB200_ARENA_MB="8", OMP_NUM_THREADS="1", ELB200_HOST_KRANGE="16", ELB200_AB_PIPELINE="1")
     e.update(env or {})
     r = subprocess.run([sys.executable, WORKER, grid, *args], capture_output=True, text=True, timeout=timeout, cwd=ROOT, env=e)
     assert r.returncode == 0 and "HOSTSIM_PASS" in r.stdout, (r.stdout[-3000:] + r.stderr[-6000:])
@@ -156,7 +157,7 @@ def test_race_detector_selftest(tsanlib):
     assert bad.returncode == 66 and "WARNING: ThreadSanitizer: data race" in bad.stderr, bad.stdout + bad.stderr[-2000:]
 
 
-@pytest.mark.parametrize("grid,only,panel_k", [("2x2", "check_gemm_pipeline,check_contractions,check_gemm_dot_pipeline", "512"),
+@pytest.mark.parametrize("grid,only,panel_k", [("2x2", "check_gemm_pipeline,check_contractions,check_gemm_dot_pipeline,check_gemm_variants_f64", "512"),
                                                 ("2x4", "check_gemm_pipeline,check_gemm_dot_pipeline", "512"),
                                                 ("2x2", "check_level3,check_trsm", "16")])
 def test_engine_is_race_free_under_tsan(tsanlib, grid, only, panel_k):
@@ -166,7 +167,7 @@ def test_engine_is_race_free_under_tsan(tsanlib, grid, only, panel_k):
     the four-stream host-operand Gemm — were run the same way by hand and are clean too; they are left out of the
     default suite for time.)"""
     _, rt = tsanlib
-    e = dict(os.environ, HOSTSIM_SANITIZE="thread", HOSTSIM_TIMEOUT="300", ELB200_ARENA_MB="8", ELB200_PANEL_K=panel_k, ELB200_DOT_CHUNK="4",
+    e = dict(os.environ, HOSTSIM_SANITIZE="thread", HOSTSIM_TIMEOUT="300", ELB200_ARENA_MB="8", ELB200_PANEL_K=panel_k, ELB200_DOT_CHUNK="4", ELB200_AB_PIPELINE="1",
              OMP_NUM_THREADS="1", LD_PRELOAD=rt, TSAN_OPTIONS="report_signal_unsafe=0 history_size=4 exitcode=66")
     r = subprocess.run([sys.executable, WORKER, grid, "--only", only], capture_output=True, text=True, timeout=1500, cwd=ROOT, env=e)
     assert "WARNING: ThreadSanitizer" not in r.stderr, r.stderr[-6000:]
