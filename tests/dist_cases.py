@@ -252,7 +252,7 @@ def check_gemm_proxies(grid, dtype) -> None:
             assert err <= tol, (d, alg, err, tol)
 
 
-def check_gemm_host(grid, dtype) -> int:
+def check_gemm_host(grid, dtype, m=150, k=100) -> int:
     """el.GemmHost (elb200_dist_gemm_host_*): operands in HOST memory, streamed in column blocks.
     Sizes give six blocks on this grid (ragged last one; four block slots, so slots are reused), all orientations, beta = 0 with NaNs in
     C (must not propagate), k = 0 (pure scaling), padded leading dimensions."""
@@ -261,7 +261,7 @@ def check_gemm_host(grid, dtype) -> int:
     npdt = NPDT[dtype]
     me = grid.Rank()
     unit = (og.r * og.c // math.gcd(og.r, og.c)) * 256
-    m, n, k = 150, 5 * unit + 77, 100   # six column blocks (ragged last one): more blocks than block slots
+    n = 5 * unit + 77   # six column blocks (ragged last one): more blocks than block slots
     zero = lambda h, w: OD.Spec(OD.MC, OD.MR, 0, 0, h, w)  # noqa: E731
     cnt = 0
     for oa, ob in itertools.product((0, 1), (0, 1)):

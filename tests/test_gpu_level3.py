@@ -198,6 +198,14 @@ def test_el_level3_check_facade():
     assert r.returncode == 0 and "EL_LEVEL3_CHECK_PASS" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+def test_gemm_host_streamed_a_ranges_1x1(grid1, dtype):
+    """Host-operand Gemm with k large enough (2100 > 4 x 512) for A to be streamed in several k ranges behind the
+    first block (engine_gemm.cpp::GemmHost), all orientations, beta = 0 with NaNs in C, k = 0."""
+    from tests import dist_cases as dc
+    assert dc.check_gemm_host(grid1, dtype, m=260, k=2100) == 12
+
+
 @pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
 def test_randomised_sweep_1x1(grid1, dtype):
     """Random sizes (0, 1, ragged), orientations, algorithms, alignments, blocksizes, operand distributions for Gemm,
