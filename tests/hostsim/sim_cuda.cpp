@@ -75,14 +75,20 @@ void sim_free(void* p) {
 }
 
 // ------------------------------------------------------------------ streams
-struct Stream {
+// A hardware work queue: one worker thread executing closures in FIFO order. By default every stream has a
+// queue of its own (streams are fully concurrent). HOSTSIM_HWQ=N models CUDA_DEVICE_MAX_CONNECTIONS=N: the
+// streams of a rank ("device") are spread round-robin over N queues, and work of different streams that lands
+// in the same queue runs in ISSUE order — so a stream-ordered wait (an event, a cuStreamWaitValue32 on a peer's
+// flag) at the head of a queue also holds back the other streams behind it, the false dependency real hardware
+// has. A schedule that only works because streams never share a queue deadlocks here (and is reported by the
+// wait timeouts) instead of on an 8-GPU box.
+struct HwQueue {
     std::mutex m;
-    std::condition_variable cv, idle;
+    std::condition_variable cv;
     std::deque<std::function<void()>> q;
-    bool stop = false, busy = false;
-    std::thread::id owner = std::this_thread::get_id();  // the rank (host thread) whose "device" this stream is on
+    bool stop = false;
     std::thread th;
-    Stream() {
+    HwQueue() {
         th = std::thread([this] {
             for (;;) {
                 std::function<void()> fn;
@@ -92,14 +98,8 @@ struct Stream {
                     if (q.empty()) return;
                     fn = std::move(q.front());
                     q.pop_front();
-                    busy = true;
                 }
                 fn();
-                {
-                    std::lock_guard<std::mutex> l(m);
-                    busy = false;
-                    if (q.empty()) idle.notify_all();
-                }
             }
         });
     }
@@ -110,12 +110,7 @@ struct Stream {
         }
         cv.notify_one();
     }
-    void sync() {
-        std::unique_lock<std::mutex> l(m);
-        if (!idle.wait_for(l, std::chrono::duration<double>(wait_timeout_seconds()), [this] { return q.empty() && !busy; }))
-            fail("cudaStreamSynchronize: stream %p did not drain within %.0f s (deadlock?)", (void*)this, wait_timeout_seconds());
-    }
-    ~Stream() {
+    ~HwQueue() {
         {
             std::lock_guard<std::mutex> l(m);
             stop = true;
@@ -125,10 +120,60 @@ struct Stream {
     }
 };
 
+int hwq_count() {
+    static int n = [] { const char* e = std::getenv("HOSTSIM_HWQ"); return e ? std::atoi(e) : 0; }();
+    return n > 0 ? n : 0;
+}
+// the shared queues of the calling rank (host thread); leaked at exit on purpose
+thread_local std::vector<HwQueue*> t_hwq;
+thread_local int t_hwq_next = 0;
+
+struct Stream {
+    std::mutex m;
+    std::condition_variable idle;
+    uint64_t pending = 0;  // closures pushed and not yet finished
+    std::thread::id owner = std::this_thread::get_id();  // the rank (host thread) whose "device" this stream is on
+    HwQueue* hw = nullptr;
+    bool own_hw = false;
+    Stream() {
+        const int n = hwq_count();
+        if (n == 0) {
+            hw = new HwQueue();
+            own_hw = true;
+        } else {
+            if (int(t_hwq.size()) < n) t_hwq.push_back(new HwQueue());
+            hw = t_hwq[size_t(t_hwq_next++ % n) % t_hwq.size()];
+        }
+    }
+    void push(std::function<void()> fn) {
+        {
+            std::lock_guard<std::mutex> l(m);
+            ++pending;
+        }
+        hw->push([this, fn = std::move(fn)] {
+            fn();
+            {
+                std::lock_guard<std::mutex> l(m);
+                --pending;
+                if (pending == 0) idle.notify_all();
+            }
+        });
+    }
+    void sync() {
+        std::unique_lock<std::mutex> l(m);
+        if (!idle.wait_for(l, std::chrono::duration<double>(wait_timeout_seconds()), [this] { return pending == 0; }))
+            fail("cudaStreamSynchronize: stream %p did not drain within %.0f s (deadlock?)", (void*)this, wait_timeout_seconds());
+    }
+    ~Stream() {
+        if (own_hw) delete hw;
+    }
+};
+
 std::mutex g_streams_mutex;
 std::set<Stream*> g_streams;
+// the legacy default stream of the calling rank (one process per GPU in reality: one per host thread here)
 Stream* default_stream() {
-    static Stream* s = [] {
+    thread_local Stream* s = [] {
         Stream* d = new Stream();
         std::lock_guard<std::mutex> l(g_streams_mutex);
         g_streams.insert(d);
