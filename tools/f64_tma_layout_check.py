@@ -47,6 +47,26 @@ def k_contig(rowperm, k40=0):
     return worst
 
 
+def wavefronts128(addrs):
+    """16-byte loads are served per quarter-warp (8 lanes x 16 B = 128 B)"""
+    per_bank = {}
+    for a in addrs:
+        for w in range(a // 4, a // 4 + 4):
+            per_bank.setdefault(w % 32, set()).add(w)
+    return max(len(v) for v in per_bank.values())
+
+
+def k_contig_pairs(rowperm, kpair0=0):
+    """K-contiguous tile read with ONE 16-byte load per lane: lane (lr, lk) loads (k = kpair0 + 2 lk, + 1) of mn
+    row rowperm[lr]; .x feeds the even k4 step, .y the odd one (same k order as the MN-contiguous {0,2,4,6} /
+    {1,3,5,7} scheme, so mixed-majorness products (NN, TT) can use both). Worst quarter-warp."""
+    worst = 0
+    for quarter in range(4):
+        addrs = [phys(rowperm[lr], 8 * (kpair0 + 2 * lk)) for lr in range(2 * quarter, 2 * quarter + 2) for lk in range(4)]
+        worst = max(worst, wavefronts128(addrs))
+    return worst
+
+
 def main():
     print("MN-contiguous tile, natural k order {0,1,2,3}:", mn_contig([0, 1, 2, 3]), "wavefront(s) per half-warp")
     best = [(mn_contig(list(c)), c) for c in itertools.combinations(range(8), 4)]
@@ -61,6 +81,11 @@ def main():
     print("  row permutations with 1 wavefront:", len(good), "e.g.", good[0])
     for k40 in (0, 4, 8, 12):
         assert k_contig(list(good[0]), k40) == 1
+    print("K-contiguous tile, one 16-byte load per lane (k pair), natural rows:", k_contig_pairs(list(range(8))), "wavefront(s) per quarter-warp")
+    good128 = [p for p in itertools.permutations(range(8)) if all(k_contig_pairs(list(p), kp) == 1 for kp in (0, 8))]
+    print("  row permutations with 1 wavefront:", len(good128), "e.g.", good128[0] if good128 else None)
+    print("  => one k order for every orientation: k(step s, lane lk) = 8 (s / 2) + 2 lk + (s & 1);")
+    print("     MN-contiguous operands read row k directly, K-contiguous operands read the pair once per two steps")
     print("padded layout of the current kernel (pitch 132 doubles, MN-contiguous):",
           max(wavefronts([(kk * 132 + mm) * 8 for mm in range(4 * h, 4 * h + 4) for kk in range(4)]) for h in (0, 1)), "wavefront(s)")
 
