@@ -409,6 +409,11 @@ int gemm_f64_dmma(int transA, int transB, int64_t m, int64_t n, int64_t k, doubl
     else if (!ta && tb) e = launch<false, true, V>(p, stream);        \
     else if (ta && !tb) e = launch<true, false, V>(p, stream);        \
     else e = launch<true, true, V>(p, stream);
+    static const bool tma = [] { const char* v = std::getenv("ELB200_F64_TMA"); return v && std::atoi(v) != 0; }();
+    if (tma) {
+        const int st = gemm_f64_dmma_tma(transA, transB, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, stream);
+        if (st >= 0) return st;  // -1: operands not TMA-able (alignment), use the cp.async kernels
+    }
     static const bool ws = [] { const char* v = std::getenv("ELB200_F64_WS"); return v && std::atoi(v) != 0; }();
     if (ws) {
 #define ELB_DISPATCH_WS(V)                                                \

@@ -22,6 +22,9 @@ if [ "$N" = "1" ]; then
   run tools/gemm_check perf f64 8192 16384
   ELB200_F64_WS=1 tools/gemm_check correctness f64 > $OUT/f64_ws_correctness.log 2>&1; echo "f64 WS correctness exit $?" >> $OUT/session.log
   ELB200_F64_WS=1 tools/gemm_check perf f64 8192 16384 > $OUT/f64_ws_perf.log 2>&1
+  # 3b. TMA-fed fp64 kernel (experimental, never run before): correctness first, then time
+  ELB200_F64_TMA=1 timeout 60 tools/native_bench f64 8192 > $OUT/f64_tma_native.log 2>&1; echo "f64 TMA native exit $?" >> $OUT/session.log
+  ELB200_F64_TMA=1 timeout 600 python -m pytest tests/test_gpu_kernels.py -m gpu -x -q -k gemm > $OUT/f64_tma_pytest.log 2>&1; echo "f64 TMA pytest exit $?" >> $OUT/session.log
   # 4. new HBM-bound kernels and the level-3 family
   run python tools/blas1_bw.py --out $OUT/blas1_bandwidth.json
   run python tools/level3_bench.py --n 16384 --out $OUT/level3_1gpu.json
