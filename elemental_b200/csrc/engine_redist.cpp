@@ -88,14 +88,21 @@ void Copy(const DistMat<T>& A, DistMat<T>& B) {
             static const int64_t split_b = [] { const char* e = std::getenv("ELB200_AG_SPLIT_BYTES"); return e ? std::atoll(e) : 0ll; }();
             const int64_t split_bytes = split_b > 0 ? split_b : split_mb << 20;
             if (split_bytes > 0 && plan.portion * int64_t(sizeof(T)) >= split_bytes && plan.recvs[size_t(idx)].peer == g.vc_rank) {
-                PeerArena::Ticket t = g.arena->AllGatherBegin(Grid::arena_channel(plan.comm_dist), members, idx, send,
-                                                              size_t(mine) * sizeof(T), size_t(plan.portion) * sizeof(T), true, s);
+                // Rotation (peer.hpp AllGatherRotate): the sends leave one after the other, so the blocks land staggered
+                // and block d is unpacked while block d + 1 is on the wire; my own block is copied underneath the
+                // sends. ELB200_AG_ROTATE=0 keeps the earlier form (all sends at once, `s` joined before my block).
+                static const bool rotate = [] { const char* e = std::getenv("ELB200_AG_ROTATE"); return !e || std::atoi(e) != 0; }();
+                PeerArena::Ticket t = rotate ? g.arena->AllGatherRotate(Grid::arena_channel(plan.comm_dist), members, idx, send,
+                                                                        size_t(mine) * sizeof(T), size_t(plan.portion) * sizeof(T), s)
+                                             : g.arena->AllGatherBegin(Grid::arena_channel(plan.comm_dist), members, idx, send,
+                                                                       size_t(mine) * sizeof(T), size_t(plan.portion) * sizeof(T), true, s);
                 if (mine > 0) lattice_to_lattice<T>(s0, A.buf, A.ldim, plan.recvs[size_t(idx)].seg, B.buf, B.ldim, s);
-                for (int i = 0; i < gsz; ++i) {
-                    if (i == idx) continue;
+                for (int d = 1; d < gsz; ++d) {
+                    const int i = (idx - d + gsz) % gsz;  // arrival order under the rotation
                     g.arena->WaitMember(t, members, idx, i, s);
                     run_lattice<T>(ELB200_UNPACK, std::vector<Message>{plan.recvs[size_t(i)]}, B.buf, B.ldim, static_cast<T*>(t.data), T(0), s);
                 }
+                if (rotate) g.arena->AllGatherEnd(s);  // my sends are done: `send` (A or the pack scratch) may be reused
                 g.arena->Release(t, members, idx, s);
                 return;
             }

@@ -245,6 +245,30 @@ PeerArena::Ticket PeerArena::AllGatherBegin(int channel, const std::vector<int>&
     return t;
 }
 
+PeerArena::Ticket PeerArena::AllGatherRotate(int channel, const std::vector<int>& members, int my_index, const void* send,
+                                             size_t send_bytes, size_t portion_bytes, cudaStream_t s) {
+    const int g = int(members.size());
+    if (portion_bytes * size_t(g) > slot_bytes_ || send_bytes > portion_bytes)
+        throw EngineError(ELB200_ERR_ARG, "PeerArena::AllGather: message larger than an arena slot");
+    const uint64_t n = uses_[channel]++;
+    Ticket t;
+    t.channel = channel;
+    t.slot = int(n & 1);
+    t.seq = uint32_t(n / 2 + 1);
+    for (int i = 0; i < g; ++i)
+        if (i != my_index) wait_flag(flag(rank_, ACK, channel, t.slot, members[i]), t.seq - 1, s);
+    cudaStream_t ls = fork(0, s);
+    for (int d = 1; d < g; ++d) {
+        const int i = (my_index + d) % g;
+        if (send_bytes)
+            cuda_check(cudaMemcpyAsync(slot_base(members[i], channel, t.slot) + size_t(my_index) * portion_bytes, send,
+                                       send_bytes, cudaMemcpyDeviceToDevice, ls), "PeerArena copy");
+        write_flag(flag(members[i], ARRIVE, channel, t.slot, rank_), t.seq, ls);
+    }
+    t.data = slot_base(rank_, channel, t.slot);
+    return t;
+}
+
 void PeerArena::WaitMember(const Ticket& t, const std::vector<int>& members, int my_index, int i, cudaStream_t s) {
     if (i != my_index) wait_flag(flag(rank_, ARRIVE, t.channel, t.slot, members[i]), t.seq, s);
 }

@@ -49,6 +49,14 @@ public:
     Ticket AllGatherBegin(int channel, const std::vector<int>& members, int my_index, const void* send, size_t send_bytes,
                           size_t portion_bytes, bool skip_self, cudaStream_t s);
     void WaitMember(const Ticket& t, const std::vector<int>& members, int my_index, int i, cudaStream_t s);
+    // Rotation form for large blocks: my block goes to members my_index + 1, my_index + 2, ... one after the other on
+    // ONE copy lane, each at the full link rate (every member's ingress carries exactly one flow at a time), so the
+    // blocks land STAGGERED — member my_index - d's block arrives d-th — and the consumer unpacks block d while
+    // block d + 1 is on the wire. `s` is NOT joined: work the caller enqueues on `s` next (its own block) runs
+    // underneath the sends. AllGatherEnd(s) makes `s` wait for my sends; call it before the send buffer is reused.
+    Ticket AllGatherRotate(int channel, const std::vector<int>& members, int my_index, const void* send, size_t send_bytes,
+                           size_t portion_bytes, cudaStream_t s);
+    void AllGatherEnd(cudaStream_t s) { join(s); }
     // Call after the last read of ticket.data has been enqueued on `s`.
     void Release(const Ticket& t, const std::vector<int>& members, int my_index, cudaStream_t s);
 

@@ -5,6 +5,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
@@ -40,13 +41,68 @@ double wait_timeout_seconds() {
     return t;
 }
 
+bool vtime_on() {
+    static bool v = [] { const char* e = std::getenv("HOSTSIM_VTIME"); return e && std::atoi(e) != 0; }();
+    return v;
+}
+bool dry_run() {
+    static bool v = [] { const char* e = std::getenv("HOSTSIM_DRY"); return e && std::atoi(e) != 0; }();
+    return v;
+}
+
 namespace {
 
 using Clock = std::chrono::steady_clock;
 
+// ------------------------------------------------------------------ virtual time
+std::atomic<int> g_next_dev{0};
+thread_local int t_dev = -1;            // device (rank) id of the calling HOST thread, assigned on first use
+thread_local double t_host_vtime = 0;   // host thread's virtual clock: advanced by synchronising calls
+int host_dev() {
+    if (t_dev < 0) t_dev = g_next_dev.fetch_add(1);
+    return t_dev;
+}
+constexpr int kMaxDev = 64;
+std::mutex g_res_mutex;
+// Busy intervals of one exclusive resource. Worker threads reach the reservation in REAL-time order, which is not
+// virtual-time order, so "free again at" is not enough: an operation takes the earliest gap that fits it.
+struct Busy {
+    std::map<double, double> iv;  // start -> end, disjoint
+    double find(double t, double dur) const {
+        auto it = iv.upper_bound(t);
+        if (it != iv.begin()) {
+            auto prev = std::prev(it);
+            if (prev->second > t) t = prev->second;
+        }
+        while (it != iv.end() && it->first < t + dur - 1e-12) {
+            if (it->second > t) t = it->second;
+            ++it;
+        }
+        return t;
+    }
+    void add(double t, double dur) {
+        auto it = iv.upper_bound(t);
+        if (it != iv.begin()) {
+            auto prev = std::prev(it);
+            if (prev->second >= t - 1e-12) {  // touches the interval before it: extend that one
+                if (prev->second < t + dur) prev->second = t + dur;
+                return;
+            }
+        }
+        iv[t] = t + dur;
+    }
+};
+Busy g_res_busy[kMaxDev][RES_COUNT];         // tensor pipe, HBM kernels, PCIe up / down of a device
+Busy g_nvl_out[kMaxDev], g_nvl_in[kMaxDev];  // NVLink egress / ingress of a device
+std::mutex g_flag_mutex;
+std::map<uintptr_t, double> g_flag_time;       // virtual time of the last 4-byte (flag) write to an address
+struct Stream;
+thread_local Stream* t_cur = nullptr;          // stream whose closure the calling WORKER thread is executing
+
 // ------------------------------------------------------------------ memory registry
 std::mutex g_mem_mutex;
 std::map<uintptr_t, size_t> g_live;  // base -> bytes
+std::map<uintptr_t, int> g_live_dev;  // base -> device (rank) that allocated it
 
 void* sim_alloc(size_t bytes) {
     const size_t n = bytes ? bytes : 1;
@@ -54,9 +110,10 @@ void* sim_alloc(size_t bytes) {
     if (posix_memalign(&p, 256, (n + 255) / 256 * 256) != 0 || !p) return nullptr;
     // fresh device memory holds garbage: signalling pattern (NaN as fp32 and fp64) for small blocks,
     // large arenas are left untouched so that they stay lazily committed
-    if (n <= (size_t(64) << 20)) std::memset(p, 0xFF, n);
+    if (n <= (size_t(64) << 20) && !dry_run()) std::memset(p, 0xFF, n);
     std::lock_guard<std::mutex> l(g_mem_mutex);
     g_live[reinterpret_cast<uintptr_t>(p)] = n;
+    g_live_dev[reinterpret_cast<uintptr_t>(p)] = host_dev();
     return p;
 }
 
@@ -69,8 +126,14 @@ void sim_free(void* p) {
         if (it == g_live.end()) fail("free of a pointer that is not a live device allocation: %p", p);
         n = it->second;
         g_live.erase(it);
+        g_live_dev.erase(reinterpret_cast<uintptr_t>(p));
     }
-    if (n <= (size_t(64) << 20)) std::memset(p, 0xFF, n);  // use-after-free reads NaN
+    if (n <= (size_t(64) << 20) && !dry_run()) std::memset(p, 0xFF, n);  // use-after-free reads NaN
+    if (vtime_on()) {  // flag write times of this allocation die with it (the address may come back)
+        std::lock_guard<std::mutex> l(g_flag_mutex);
+        const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+        g_flag_time.erase(g_flag_time.lower_bound(a), g_flag_time.lower_bound(a + n));
+    }
     std::free(p);
 }
 
@@ -135,6 +198,8 @@ struct Stream {
     std::thread::id owner = std::this_thread::get_id();  // the rank (host thread) whose "device" this stream is on
     HwQueue* hw = nullptr;
     bool own_hw = false;
+    double vtime = 0;       // virtual clock (only touched by the worker executing this stream's closures, and after sync)
+    int dev = host_dev();  // device (rank) this stream belongs to
     Stream() {
         const int n = hwq_count();
         if (n == 0) {
@@ -150,8 +215,12 @@ struct Stream {
             std::lock_guard<std::mutex> l(m);
             ++pending;
         }
-        hw->push([this, fn = std::move(fn)] {
+        const double issued = t_host_vtime;
+        hw->push([this, issued, fn = std::move(fn)] {
+            t_cur = this;
+            if (vtime < issued) vtime = issued;  // work cannot start before the host enqueued it
             fn();
+            t_cur = nullptr;
             {
                 std::lock_guard<std::mutex> l(m);
                 --pending;
@@ -163,6 +232,7 @@ struct Stream {
         std::unique_lock<std::mutex> l(m);
         if (!idle.wait_for(l, std::chrono::duration<double>(wait_timeout_seconds()), [this] { return pending == 0; }))
             fail("cudaStreamSynchronize: stream %p did not drain within %.0f s (deadlock?)", (void*)this, wait_timeout_seconds());
+        if (t_host_vtime < vtime) t_host_vtime = vtime;  // the host has waited for everything on this stream
     }
     ~Stream() {
         if (own_hw) delete hw;
@@ -199,6 +269,7 @@ struct Record {
     std::condition_variable cv;
     bool done = false;
     Clock::time_point when;
+    double vt = 0;  // virtual time of the stream when the record executed
 };
 struct Event {
     std::mutex m;
@@ -211,6 +282,52 @@ void wait_record(const std::shared_ptr<Record>& r, const char* who) {
         fail("%s: the recorded work never completed (deadlock?)", who);
 }
 
+int device_of(const void* p) {  // -1: not device memory (host)
+    const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+    std::lock_guard<std::mutex> l(g_mem_mutex);
+    auto it = g_live.upper_bound(a);
+    if (it == g_live.begin()) return -1;
+    --it;
+    if (a < it->first || a >= it->first + it->second) return -1;
+    return g_live_dev[it->first];
+}
+
+// virtual duration of a copy of n bytes, by where source and destination live
+void account_copy(void* dst, const void* src, size_t n) {
+    if (!vtime_on() || !t_cur) return;
+    if (n <= 64) {  // flags and scalars: a latency, no bandwidth
+        t_cur->vtime += kFlagLatency;
+        if (n == 4) {
+            std::lock_guard<std::mutex> l(g_flag_mutex);
+            g_flag_time[reinterpret_cast<uintptr_t>(dst)] = t_cur->vtime;
+        }
+        return;
+    }
+    const int ds = device_of(src), dd = device_of(dst);
+    if (ds < 0 && dd >= 0) { vt_op(RES_H2D, kLaunch + double(n) / kRatePcie); return; }
+    if (ds >= 0 && dd < 0) { vt_op(RES_D2H, kLaunch + double(n) / kRatePcie); return; }
+    if (ds == dd) {
+        vt_trace("d2d-local", t_cur->vtime, kLaunch + double(n) / kRateLocalCopy, double(n));
+        t_cur->vtime += kLaunch + double(n) / kRateLocalCopy;
+        return;
+    }
+    // peer copy over NVLink: occupies the source's egress and the destination's ingress
+    const double dur = kLaunch + double(n) / kRateNvlink;
+    std::lock_guard<std::mutex> l(g_res_mutex);
+    double start = t_cur->vtime;
+    Busy& out = g_nvl_out[ds % kMaxDev];
+    Busy& in = g_nvl_in[dd % kMaxDev];
+    for (;;) {  // earliest time both the source's egress and the destination's ingress have a gap of `dur`
+        const double a = out.find(start, dur), b = in.find(a, dur);
+        start = b;
+        if (a == b) break;
+    }
+    out.add(start, dur);
+    in.add(start, dur);
+    vt_trace("d2d-peer", start, dur, double(n));
+    t_cur->vtime = start + dur;
+}
+
 void copy_bytes(void* dst, const void* src, size_t n) {
     // 4-byte aligned word copies are the arena's flag writes: make them release stores so that a
     // spinning cuStreamWaitValue32 on another thread sees the payload written before them
@@ -220,6 +337,7 @@ void copy_bytes(void* dst, const void* src, size_t n) {
         __atomic_store_n(static_cast<uint32_t*>(dst), v, __ATOMIC_RELEASE);
         return;
     }
+    if (dry_run() && n > kDryKeep) return;  // payloads are not moved in a dry run; flags, scalars and control records are
     std::memmove(dst, src, n);
 }
 
@@ -234,7 +352,18 @@ CUresult sim_cuStreamWaitValue32(CUstream stream, CUdeviceptr addr, cuuint32_t v
         for (uint64_t spin = 0;; ++spin) {
             const uint32_t v = __atomic_load_n(p, __ATOMIC_ACQUIRE);
             const bool ok = (flags & 3u) == CU_STREAM_WAIT_VALUE_EQ ? v == value : int32_t(v - value) >= 0;
-            if (ok) return;
+            if (ok) {
+                if (vtime_on()) {
+                    double tw = 0;
+                    {
+                        std::lock_guard<std::mutex> l(g_flag_mutex);
+                        auto it = g_flag_time.find(reinterpret_cast<uintptr_t>(p));
+                        if (it != g_flag_time.end()) tw = it->second;
+                    }
+                    vt_at_least(tw);
+                }
+                return;
+            }
             if (spin < 64) std::this_thread::yield();
             else std::this_thread::sleep_for(std::chrono::microseconds(50));
             if ((spin & 1023u) == 1023u &&
@@ -248,6 +377,35 @@ CUresult sim_cuStreamWaitValue32(CUstream stream, CUdeviceptr addr, cuuint32_t v
 }  // namespace
 
 void enqueue(cudaStream_t s, std::function<void()> fn) { S(s)->push(std::move(fn)); }
+
+double vt_now() { return t_cur ? t_cur->vtime : t_host_vtime; }
+void vt_at_least(double t) {
+    if (t_cur) { if (t_cur->vtime < t) t_cur->vtime = t; }
+    else if (t_host_vtime < t) t_host_vtime = t;
+}
+// HOSTSIM_VTRACE=<file>: one line per modelled operation — device, stream, what, start and duration in microseconds
+void vt_trace(const char* what, double start, double seconds, double bytes) {
+    static FILE* f = [] { const char* e = std::getenv("HOSTSIM_VTRACE"); return e && *e ? std::fopen(e, "w") : nullptr; }();
+    if (!f) return;
+    static std::mutex m;
+    std::lock_guard<std::mutex> l(m);
+    std::fprintf(f, "dev %d stream %p %-10s start %12.2f us  dur %10.2f us  bytes %.0f\n", t_cur ? t_cur->dev : -1, (void*)t_cur, what,
+                 start * 1e6, seconds * 1e6, bytes);
+    std::fflush(f);
+}
+void vt_op(Res res, double seconds) {
+    if (!vtime_on() || !t_cur) return;
+    double start = t_cur->vtime;
+    if (res != RES_NONE) {
+        std::lock_guard<std::mutex> l(g_res_mutex);
+        Busy& b = g_res_busy[t_cur->dev % kMaxDev][res];
+        start = b.find(start, seconds);
+        b.add(start, seconds);
+    }
+    static const char* names[RES_COUNT] = {"op", "tensor", "hbm", "h2d", "d2h"};
+    vt_trace(names[res], start, seconds, 0);
+    t_cur->vtime = start + seconds;
+}
 
 void check_device_range(const void* p, size_t bytes, const char* what) {
     if (bytes == 0) return;
@@ -301,6 +459,7 @@ cudaError_t cudaMemcpyAsync(void* dst, const void* src, size_t n, enum cudaMemcp
     enqueue(s, [=] {
         if (dst_is_device(kind)) check_device_range(dst, n, "cudaMemcpyAsync dst");
         if (src_is_device(kind)) check_device_range(src, n, "cudaMemcpyAsync src");
+        account_copy(dst, src, n);
         copy_bytes(dst, src, n);
     });
     return cudaSuccess;
@@ -317,6 +476,8 @@ cudaError_t cudaMemcpy2DAsync(void* dst, size_t dpitch, const void* src, size_t 
     enqueue(s, [=] {
         if (dst_is_device(kind)) check_device_range(dst, (height - 1) * dpitch + width, "cudaMemcpy2DAsync dst");
         if (src_is_device(kind)) check_device_range(src, (height - 1) * spitch + width, "cudaMemcpy2DAsync src");
+        account_copy(dst, src, width * height);
+        if (dry_run()) return;
         for (size_t r = 0; r < height; ++r)
             std::memmove(static_cast<char*>(dst) + r * dpitch, static_cast<const char*>(src) + r * spitch, width);
     });
@@ -326,6 +487,8 @@ cudaError_t cudaMemsetAsync(void* p, int v, size_t n, cudaStream_t s) {
     if (n == 0) return cudaSuccess;
     enqueue(s, [=] {
         check_device_range(p, n, "cudaMemsetAsync");
+        vt_op(RES_HBM, kLaunch + double(n) / kRateHbm);
+        if (dry_run() && n > kDryKeep) return;
         std::memset(p, v, n);
     });
     return cudaSuccess;
@@ -403,6 +566,7 @@ cudaError_t cudaEventRecord(cudaEvent_t e, cudaStream_t s) {
             std::lock_guard<std::mutex> l(rec->m);
             rec->done = true;
             rec->when = Clock::now();
+            rec->vt = vt_now();
         }
         rec->cv.notify_all();
     });
@@ -417,20 +581,21 @@ cudaError_t cudaStreamWaitEvent(cudaStream_t s, cudaEvent_t e, unsigned int) {
     if (!e) return cudaErrorInvalidResourceHandle;
     std::shared_ptr<Record> rec = latest_record(e);  // the most recent record at the time of THIS call
     if (!rec) return cudaSuccess;                     // never recorded: no-op
-    enqueue(s, [rec] { wait_record(rec, "cudaStreamWaitEvent"); });
+    enqueue(s, [rec] { wait_record(rec, "cudaStreamWaitEvent"); vt_at_least(rec->vt); });
     return cudaSuccess;
 }
 cudaError_t cudaEventSynchronize(cudaEvent_t e) {
     if (!e) return cudaErrorInvalidResourceHandle;
     std::shared_ptr<Record> rec = latest_record(e);
-    if (rec) wait_record(rec, "cudaEventSynchronize");
+    if (rec) { wait_record(rec, "cudaEventSynchronize"); vt_at_least(rec->vt); }
     return cudaSuccess;
 }
 cudaError_t cudaEventElapsedTime(float* ms, cudaEvent_t a, cudaEvent_t b) {
     if (!a || !b) return cudaErrorInvalidResourceHandle;
     auto ra = latest_record(a), rb = latest_record(b);
     if (!ra || !rb) return cudaErrorInvalidResourceHandle;
-    *ms = std::chrono::duration<float, std::milli>(rb->when - ra->when).count();
+    if (vtime_on()) *ms = float((rb->vt - ra->vt) * 1e3);  // modelled milliseconds
+    else *ms = std::chrono::duration<float, std::milli>(rb->when - ra->when).count();
     return cudaSuccess;
 }
 

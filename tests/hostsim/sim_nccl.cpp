@@ -24,6 +24,7 @@ struct Msg {
     const void* src;
     size_t bytes;
     bool done = false;
+    double vt = 0;  // sender's virtual time when it posted the message
 };
 
 struct Shared {
@@ -42,6 +43,17 @@ struct Shared {
 
     explicit Shared(int n_) : n(n_), send(n_, nullptr), color(n_, 0), key(n_, 0) {}
 
+    // virtual time: all participants leave a collective at max(arrival times) + its duration
+    std::vector<double> vt;
+    double vt_sync(int rank, double seconds, const char* who) {
+        if (vt.size() != size_t(n)) vt.assign(size_t(n), 0.0);
+        vt[size_t(rank)] = sim::vt_now();
+        barrier(who);
+        double t = 0;
+        for (double x : vt) t = x > t ? x : t;
+        barrier(who);
+        return t + seconds;
+    }
     void barrier(const char* who) {
         std::unique_lock<std::mutex> l(m);
         const uint64_t g = gen;
@@ -117,6 +129,7 @@ void run_p2p(const std::vector<P2P>& ops) {
         auto msg = std::make_shared<Msg>();
         msg->src = o.sbuf;
         msg->bytes = o.bytes;
+        msg->vt = sim::vt_now();
         Shared& sh = *o.comm->sh;
         {
             std::lock_guard<std::mutex> l(sh.m);
@@ -140,7 +153,11 @@ void run_p2p(const std::vector<P2P>& ops) {
         }
         if (msg->bytes != o.bytes)
             sim::fail("ncclRecv: rank %d expects %zu bytes from rank %d, sender posted %zu", o.comm->rank, o.bytes, o.peer, msg->bytes);
-        std::memcpy(o.rbuf, msg->src, o.bytes);
+        if (sim::vtime_on()) {  // a message starts when both ends have posted it
+            sim::vt_at_least(msg->vt);
+            sim::vt_at_least(sim::vt_now() + 10e-6 + double(o.bytes) / 300e9);
+        }
+        if (!(sim::dry_run() && o.bytes > sim::kDryKeep)) std::memcpy(o.rbuf, msg->src, o.bytes);
         {
             std::lock_guard<std::mutex> l(sh.m);
             msg->done = true;
@@ -254,11 +271,13 @@ ncclResult_t ncclAllGather(const void* sendbuf, void* recvbuf, size_t count, ncc
             sim::check_device_range(recvbuf, bytes * sh.n, "ncclAllGather recv");
         }
         sh.send[comm->rank] = sendbuf;
+        if (sim::vtime_on()) sim::vt_at_least(sh.vt_sync(comm->rank, 20e-6 + double(bytes) * double(sh.n - 1) / 300e9, "ncclAllGather"));
         sh.barrier("ncclAllGather");
-        std::vector<char> tmp(bytes * sh.n);
-        for (int q = 0; q < sh.n; ++q) std::memcpy(tmp.data() + size_t(q) * bytes, sh.send[q], bytes);
+        const bool skip = sim::dry_run() && bytes > sim::kDryKeep;
+        std::vector<char> tmp(skip ? 0 : bytes * sh.n);
+        if (!skip) for (int q = 0; q < sh.n; ++q) std::memcpy(tmp.data() + size_t(q) * bytes, sh.send[q], bytes);
         sh.barrier("ncclAllGather");
-        std::memcpy(recvbuf, tmp.data(), tmp.size());
+        if (!skip) std::memcpy(recvbuf, tmp.data(), tmp.size());
         sh.barrier("ncclAllGather");
     });
     return ncclSuccess;
@@ -274,15 +293,17 @@ ncclResult_t ncclReduceScatter(const void* sendbuf, void* recvbuf, size_t recvco
             sim::check_device_range(recvbuf, bytes, "ncclReduceScatter recv");
         }
         sh.send[comm->rank] = sendbuf;
+        if (sim::vtime_on()) sim::vt_at_least(sh.vt_sync(comm->rank, 20e-6 + double(bytes) * double(sh.n - 1) / 300e9, "ncclReduceScatter"));
         sh.barrier("ncclReduceScatter");
-        std::vector<char> acc(bytes);
-        for (int q = 0; q < sh.n; ++q) {
+        const bool skip = sim::dry_run() && bytes > sim::kDryKeep;
+        std::vector<char> acc(skip ? 0 : bytes);
+        for (int q = 0; q < sh.n && !skip; ++q) {
             const char* src = static_cast<const char*>(sh.send[q]) + size_t(comm->rank) * bytes;
             if (q == 0) std::memcpy(acc.data(), src, bytes);
             else reduce_bytes(acc.data(), src, recvcount, dt, op);
         }
         sh.barrier("ncclReduceScatter");
-        std::memcpy(recvbuf, acc.data(), bytes);
+        if (!skip) std::memcpy(recvbuf, acc.data(), bytes);
         sh.barrier("ncclReduceScatter");
     });
     return ncclSuccess;
@@ -298,14 +319,16 @@ ncclResult_t ncclAllReduce(const void* sendbuf, void* recvbuf, size_t count, ncc
             sim::check_device_range(recvbuf, bytes, "ncclAllReduce recv");
         }
         sh.send[comm->rank] = sendbuf;
+        if (sim::vtime_on()) sim::vt_at_least(sh.vt_sync(comm->rank, 20e-6 + 2.0 * double(bytes) / 300e9, "ncclAllReduce"));
         sh.barrier("ncclAllReduce");
-        std::vector<char> acc(bytes);
-        for (int q = 0; q < sh.n; ++q) {
+        const bool skip = sim::dry_run() && bytes > sim::kDryKeep;
+        std::vector<char> acc(skip ? 0 : bytes);
+        for (int q = 0; q < sh.n && !skip; ++q) {
             if (q == 0) std::memcpy(acc.data(), sh.send[q], bytes);
             else reduce_bytes(acc.data(), sh.send[q], count, dt, op);
         }
         sh.barrier("ncclAllReduce");
-        std::memcpy(recvbuf, acc.data(), bytes);
+        if (!skip) std::memcpy(recvbuf, acc.data(), bytes);
         sh.barrier("ncclAllReduce");
     });
     return ncclSuccess;

@@ -50,6 +50,8 @@ int copy2d(int64_t rows, int64_t cols, const T* src, int64_t srs, int64_t scs, T
     sim::enqueue(st(s), [=] {
         check_lattice(src, rows, cols, srs, scs, "copy2d src");
         check_lattice(dst, rows, cols, drs, dcs, "copy2d dst");
+        sim::vt_op(sim::RES_HBM, sim::kLaunch + 2.0 * double(rows) * double(cols) * sizeof(T) / sim::kRateHbm);
+        if (sim::dry_run()) return;
         for (int64_t j = 0; j < cols; ++j)
             for (int64_t i = 0; i < rows; ++i) dst[i * drs + j * dcs] = src[i * srs + j * scs];
     });
@@ -64,6 +66,8 @@ int axpy2d(int64_t rows, int64_t cols, T alpha, const T* X, int64_t xrs, int64_t
     sim::enqueue(st(s), [=] {
         check_lattice(X, rows, cols, xrs, xcs, "axpy2d X");
         check_lattice(Y, rows, cols, yrs, ycs, "axpy2d Y");
+        sim::vt_op(sim::RES_HBM, sim::kLaunch + 3.0 * double(rows) * double(cols) * sizeof(T) / sim::kRateHbm);
+        if (sim::dry_run()) return;
         for (int64_t j = 0; j < cols; ++j)
             for (int64_t i = 0; i < rows; ++i) Y[i * yrs + j * ycs] += alpha * X[i * xrs + j * xcs];
     });
@@ -79,6 +83,8 @@ int transpose(int64_t rows, int64_t cols, const T* A, int64_t lda, T* B, int64_t
     sim::enqueue(st(s), [=] {
         check_lattice(A, rows, cols, 1, lda, "transpose A");
         check_lattice(B, cols, rows, 1, ldb, "transpose B");
+        sim::vt_op(sim::RES_HBM, sim::kLaunch + (AXPY ? 3.0 : 2.0) * double(rows) * double(cols) * sizeof(T) / sim::kRateHbm);
+        if (sim::dry_run()) return;
         for (int64_t j = 0; j < cols; ++j)
             for (int64_t i = 0; i < rows; ++i) {
                 if (AXPY) B[j + i * ldb] += alpha * A[i + j * lda];
@@ -95,6 +101,8 @@ int fill2d(int64_t rows, int64_t cols, T v, T* A, int64_t lda, void* s) {
     count_launch();
     sim::enqueue(st(s), [=] {
         check_lattice(A, rows, cols, 1, lda, "fill2d");
+        sim::vt_op(sim::RES_HBM, sim::kLaunch + 1.0 * double(rows) * double(cols) * sizeof(T) / sim::kRateHbm);
+        if (sim::dry_run()) return;
         for (int64_t j = 0; j < cols; ++j)
             for (int64_t i = 0; i < rows; ++i) A[i + j * lda] = v;
     });
@@ -110,6 +118,8 @@ int scale2d(int64_t rows, int64_t cols, T alpha, T* A, int64_t lda, void* s) {
     count_launch();
     sim::enqueue(st(s), [=] {
         check_lattice(A, rows, cols, 1, lda, "scale2d");
+        sim::vt_op(sim::RES_HBM, sim::kLaunch + 2.0 * double(rows) * double(cols) * sizeof(T) / sim::kRateHbm);
+        if (sim::dry_run()) return;
         for (int64_t j = 0; j < cols; ++j)
             for (int64_t i = 0; i < rows; ++i) A[i + j * lda] *= alpha;
     });
@@ -131,9 +141,13 @@ int lattice(int mode, int nseg, const elb200_segment* segs, T* M, int64_t ldm, T
     if (!M || !buf || ldm < 1) return ELB200_ERR_ARG;
     count_launch();
     sim::enqueue(st(s), [=] {
+        double elems = 0;
+        for (const elb200_segment& g : tab) elems += double(g.rows) * double(g.cols);
+        sim::vt_op(sim::RES_HBM, sim::kLaunch + (mode == ELB200_UNPACK_AXPY ? 3.0 : 2.0) * elems * sizeof(T) / sim::kRateHbm);
         for (const elb200_segment& g : tab) {
             check_lattice(M + g.row0 + g.col0 * ldm, g.rows, g.cols, g.row_step, g.col_step * ldm, "lattice M");
             sim::check_device_range(buf + g.buf_offset, size_t(g.rows) * size_t(g.cols) * sizeof(T), "lattice staging");
+            if (sim::dry_run()) continue;
             for (int64_t j = 0; j < g.cols; ++j)
                 for (int64_t i = 0; i < g.rows; ++i) {
                     T* mp = M + g.row0 + i * g.row_step + (g.col0 + j * g.col_step) * ldm;
@@ -159,6 +173,12 @@ int peer_reduce_axpy(int nsrc, const T* const* srcs, int64_t off, const elb200_s
     sim::enqueue(st(s), [=] {
         check_lattice(M + g.row0 + g.col0 * ldm, g.rows, g.cols, g.row_step, g.col_step * ldm, "peer_reduce_axpy M");
         for (const T* p : src) sim::check_device_range(p + off, size_t(g.rows) * size_t(g.cols) * sizeof(T), "peer_reduce_axpy source");
+        {
+            const double bytes = double(g.rows) * double(g.cols) * sizeof(T);
+            const double t_link = double(src.size() > 1 ? src.size() - 1 : 0) * bytes / sim::kRateNvlink, t_hbm = 3.0 * bytes / sim::kRateHbm;
+            sim::vt_op(sim::RES_HBM, sim::kLaunch + (t_link > t_hbm ? t_link : t_hbm));
+        }
+        if (sim::dry_run()) return;
         for (int64_t j = 0; j < g.cols; ++j)
             for (int64_t i = 0; i < g.rows; ++i) {
                 const int64_t e = off + i + j * g.rows;
@@ -184,6 +204,8 @@ int trapezoid(int op, int uplo, int64_t offset, int64_t rows, int64_t cols, int6
     sim::enqueue(st(s), [=] {
         check_lattice(Y, rows, cols, 1, ldy, "trapezoid Y");
         if (op == ELB200_TRAP_AXPY) check_lattice(X, rows, cols, 1, ldx, "trapezoid X");
+        sim::vt_op(sim::RES_HBM, sim::kLaunch + (op == ELB200_TRAP_AXPY ? 1.5 : op == ELB200_TRAP_SCALE ? 1.0 : 0.5) * double(rows) * double(cols) * sizeof(T) / sim::kRateHbm);
+        if (sim::dry_run()) return;
         for (int64_t j = 0; j < cols; ++j)
             for (int64_t i = 0; i < rows; ++i) {
                 const int64_t gi = row0 + i * row_step, gj = col0 + j * col_step;
@@ -207,6 +229,8 @@ int trsm_base(bool left, bool lower, bool tr, bool unit, int64_t m, int64_t n, c
     sim::enqueue(st(s), [=] {
         check_lattice(A, na, na, 1, lda, "trsm A");
         check_lattice(B, m, n, 1, ldb, "trsm B");
+        sim::vt_op(sim::RES_TENSOR, sim::kLaunch + double(na) * double(na) * double(left ? n : m) / 4e12);  // CUDA-core substitution
+        if (sim::dry_run()) return;
         const bool eff_lower = lower != tr;
         // E(i,j) = op(A)(i,j), read only inside the stored triangle (and never on a UNIT diagonal)
         auto E = [&](int64_t i, int64_t j) { return double(tr ? A[j + i * lda] : A[i + j * lda]); };
@@ -282,6 +306,8 @@ int gemm(int ta, int tb, int64_t m, int64_t n, int64_t k, T alpha, const T* A, i
         check_lattice(A, ta ? k : m, ta ? m : k, 1, lda, "gemm A");
         check_lattice(B, tb ? n : k, tb ? k : n, 1, ldb, "gemm B");
         check_lattice(C, m, n, 1, ldc, "gemm C");
+        sim::vt_op(sim::RES_TENSOR, 2.0 * sim::kLaunch + 2.0 * double(m) * double(n) * double(k) / (sizeof(T) == 4 ? sim::kRateTensorF32 : sim::kRateTensorF64));
+        if (sim::dry_run()) return;
         std::vector<double> a(static_cast<size_t>(m * k));
         std::vector<double> acc(static_cast<size_t>(m), 0.0);
         for (int64_t l = 0; l < k; ++l)

@@ -99,6 +99,34 @@ def test_engine_survives_shared_hardware_queues(simlib, grid, hwq):
          env={"HOSTSIM_HWQ": hwq, "ELB200_PANEL_K": "16", "ELB200_DOT_CHUNK": "4", "ELB200_AG_SPLIT_BYTES": "1"})
 
 
+def test_timeline_model(simlib):
+    """HOSTSIM_VTIME=1 (tests/hostsim/sim.hpp): the virtual clocks must not change any result — the parity cases
+    pass with them on — and the dry-run model of a schedule gives the times the model's own rates imply
+    (tools/model_timeline.py; DESIGN.md 9 holds its calibration against the B200 measurements)."""
+    out = _run("2x2", "--only", "check_gemm_variants_f64,check_redistributions", env={"HOSTSIM_VTIME": "1"})
+    assert "'check_gemm_variants_f64': 40" in out
+    tool = os.path.join(ROOT, "tools", "model_timeline.py")
+
+    def model(*args, **env):
+        r = subprocess.run([sys.executable, tool, *args], capture_output=True, text=True, timeout=600, cwd=ROOT, env=dict(os.environ, **env))
+        line = [ln for ln in r.stdout.splitlines() if ln.startswith("model:")]
+        assert r.returncode == 0 and line, r.stdout[-2000:] + r.stderr[-4000:]
+        return line[-1]
+
+    import re
+    ms = float(re.search(r": ([0-9.]+) ms", model("gemm", "1", "1", "8192", "f32")).group(1))
+    ideal = 2.0 * 8192 ** 3 / 230e12 * 1e3
+    assert ideal <= ms <= 1.05 * ideal, (ms, ideal)
+    # 8 ranks: panel gathers ride under the local products, so the step stays within 10 % of the tensor-pipe time
+    ms8 = float(re.search(r": ([0-9.]+) ms", model("gemm", "2", "4", "16384", "f32")).group(1))
+    ideal8 = 2.0 * 16384 ** 3 / 8 / 230e12 * 1e3
+    assert ideal8 <= ms8 <= 1.10 * ideal8, (ms8, ideal8)
+    # the split + rotated gather may not be slower than the one-piece gather in the model, and is deterministic
+    g_rot = [float(x) for x in re.search(r": ([0-9.]+) / ([0-9.]+) / ([0-9.]+) ms", model("c4", "2", "4")).groups()]
+    g_one = [float(x) for x in re.search(r": ([0-9.]+) / ([0-9.]+) / ([0-9.]+) ms", model("c4", "2", "4", ELB200_AG_SPLIT_MB="0")).groups()]
+    assert g_rot[0] <= g_one[0] and g_rot[1:] == g_one[1:], (g_rot, g_one)
+
+
 def test_cxx_facade_on_hostsim(simlib):
     """include/El.hpp exercised for real on CPU: tools/el_api_check.cpp and tools/el_gemm_driver.cpp
     (the counterpart of the reference's tests/blas_like/Gemm.cpp) linked against the hostsim engine."""
