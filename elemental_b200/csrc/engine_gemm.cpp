@@ -526,6 +526,11 @@ void copy_rect(T* dst, int64_t ldd, const T* src, int64_t lds, int64_t rows, int
     cuda_check(cudaMemcpy2DAsync(dst, size_t(ldd) * sizeof(T), src, size_t(lds) * sizeof(T), size_t(rows) * sizeof(T),
                                  size_t(cols), kind, s), "cudaMemcpy2DAsync");
 }
+// smallest k range worth a GEMM of its own in the host-operand Gemm (A ranges of block 0, B ranges of the split form)
+int64_t host_min_krange() {
+    static const int64_t v = [] { const char* e = std::getenv("ELB200_HOST_KRANGE"); const int64_t x = e ? std::atoll(e) : 0; return x > 0 ? x : int64_t(512); }();
+    return v;
+}
 int64_t lcm64(int64_t a, int64_t b) { int64_t x = a, y = b; while (y) { int64_t t = x % y; x = y; y = t; } return a / x * b; }
 }  // namespace
 
@@ -552,7 +557,25 @@ void GemmHost(Grid& g, int ta, int tb, int64_t m, int64_t n, int64_t k, T alpha,
     const int64_t unit = lcm64(r, c) * 256;
     int64_t Wg = (n / 8 + unit - 1) / unit * unit;
     if (Wg < unit) Wg = unit;
-    const int64_t nblocks = (n + Wg - 1) / Wg;
+    // Blocks of Wg columns, and a TAPERED tail: the last stretch is cut in halves down to one unit (…, Wg/2, Wg/4,
+    // unit, unit). What is left to do after the last byte has gone up — the product and the download of the last
+    // block — is pure latency on top of the PCIe-bound pipeline; with uniform blocks that was 1/8 of the product
+    // plus 1/8 of the download (≈ 7 ms of 66 at n = 16384 fp32), with the taper it is one unit's worth (< 1 ms).
+    // ELB200_HOST_TAPER=0 keeps uniform blocks.
+    static const bool taper = [] { const char* e = std::getenv("ELB200_HOST_TAPER"); return !e || std::atoi(e) != 0; }();
+    std::vector<int64_t> starts;  // block j = columns [starts[j], starts[j+1])
+    {
+        int64_t at = 0;
+        while (n - at > Wg) { starts.push_back(at); at += Wg; }
+        while (taper && n - at > unit) {
+            const int64_t w = std::max(unit, ((n - at) / 2 + unit - 1) / unit * unit);
+            starts.push_back(at);
+            at += w;
+        }
+        if (at < n) starts.push_back(at);
+        starts.push_back(n);
+    }
+    const int64_t nblocks = int64_t(starts.size()) - 1;
 
     // Block slots. With two, the upload of block j had to wait for the download of block j-2, i.e. for a
     // whole GEMM + D2H, and the H2D stream — the bottleneck: 3 of the 4 bytes moved go up — idled between
@@ -560,17 +583,28 @@ void GemmHost(Grid& g, int ta, int tb, int64_t m, int64_t n, int64_t k, T alpha,
     constexpr int kSlots = 4;
     DistMat<T> A(g, MC, MR, s);
     DistMat<T> PA(g, ta ? STAR : MC, ta ? MC : STAR, cs);
-    std::vector<DistMat<T>> Bblk, Cblk, PB;
+    std::vector<DistMat<T>> Bblk, Cblk, Cin, PB;
     for (int i = 0; i < kSlots; ++i) {
         Bblk.emplace_back(g, MC, MR, s);
         Cblk.emplace_back(g, MC, MR, s);
+        Cin.emplace_back(g, MC, MR, s);
         PB.emplace_back(g, tb ? MR : STAR, tb ? STAR : MR, cs);
     }
+    // Opt-in (ELB200_HOST_BRANGES=R > 1; not measured on a GPU yet): blocks 1.. upload their B slice
+    // in R k ranges and multiply each range as it lands, accumulating into the block with beta = 0 on the first;
+    // the C slice goes up AFTER them into a landing block and is folded in by one axpy (C_j = acc + beta * C_j).
+    // The product then trails the upload by one range instead of one block.
+    constexpr int kMaxBRanges = 8;
+    static const int b_ranges_env = [] { const char* e = std::getenv("ELB200_HOST_BRANGES"); return e ? std::atoi(e) : 1; }();
+    const int b_ranges = product ? int(std::min<int64_t>(std::min(kMaxBRanges, std::max(1, b_ranges_env)), std::max<int64_t>(1, k / host_min_krange()))) : 1;
+    const int64_t Kb = (k + b_ranges - 1) / b_ranges;
+    Ev b_up[kSlots][kMaxBRanges], b_ready[kSlots][kMaxBRanges];
     const int64_t w0 = std::min(Wg, n);
     if (product) A.Resize(hA, wA);
     for (int i = 0; i < kSlots && i < nblocks; ++i) {
         if (product) Bblk[i].Resize(tb ? w0 : k, tb ? k : w0);
         Cblk[i].Resize(m, w0);
+        if (b_ranges > 1 && beta != T(0)) Cin[i].Resize(m, w0);
     }
     Ev alloc, up[kSlots], ready[kSlots], done[kSlots], out[kSlots];
     alloc.record(s);
@@ -592,20 +626,67 @@ void GemmHost(Grid& g, int ta, int tb, int64_t m, int64_t n, int64_t k, T alpha,
     }
     const DistMat<T>& afull = single ? A : PA;
     constexpr int kMaxRanges = 8;
-    static const int64_t min_range = [] { const char* e = std::getenv("ELB200_HOST_KRANGE"); const int64_t v = e ? std::atoll(e) : 0; return v > 0 ? v : int64_t(512); }();
+    const int64_t min_range = host_min_krange();
     const int nranges = product ? int(std::min<int64_t>(kMaxRanges, std::max<int64_t>(1, k / min_range))) : 0;
     const int64_t Kc = nranges ? (k + nranges - 1) / nranges : 0;
     Ev a_up[kMaxRanges], a_ready[kMaxRanges];
 
     for (int64_t j = 0; j < nblocks; ++j) {
         const int sl = int(j % kSlots);
-        const int64_t J0 = j * Wg, J1 = std::min(n, J0 + Wg), wj = J1 - J0;
+        const int64_t J0 = starts[size_t(j)], J1 = starts[size_t(j) + 1], wj = J1 - J0;
         if (j >= kSlots) out[sl].block(hs);  // the slot's previous block has been multiplied and downloaded
         // local index ranges of the block: C columns and (B not transposed) B columns run over MR,
         // (B transposed) B rows run over MC
         const int64_t cc0 = loc(J0, g.me.mr, c), ccn = loc(J1, g.me.mr, c) - cc0;
         Cblk[sl].Resize(m, wj);
-        copy_rect(Cblk[sl].buf, Cblk[sl].ldim, Ch + cc0 * ldc, ldc, lhC, ccn, cudaMemcpyHostToDevice, hs);
+        if (b_ranges > 1 && j > 0) {
+            const int64_t br0 = loc(J0, g.me.mc, r), brn = loc(J1, g.me.mc, r) - br0;  // B transposed: block rows over MC
+            Bblk[sl].Resize(tb ? wj : k, tb ? k : wj);
+            if (!single) {
+                PB[sl].col_constrained = PB[sl].row_constrained = false;
+                PB[sl].spec.col_align = PB[sl].spec.row_align = 0;
+                PB[sl].AlignWith(Cblk[sl].spec, true);
+                PB[sl].Resize(tb ? wj : k, tb ? k : wj);
+            }
+            const DistMat<T>& bfull = single ? Bblk[sl] : PB[sl];
+            for (int q = 0; q < b_ranges; ++q) {
+                const int64_t k0 = std::min(k, q * Kb), k1 = std::min(k, k0 + Kb);
+                if (k1 <= k0) break;
+                if (!tb) {  // rows k0:k1 of the slice: k runs over MC
+                    const int64_t r0 = loc(k0, g.me.mc, r), rn = loc(k1, g.me.mc, r) - r0;
+                    copy_rect(Bblk[sl].buf + r0, Bblk[sl].ldim, Bh + cc0 * ldb + r0, ldb, rn, ccn, cudaMemcpyHostToDevice, hs);
+                } else {    // columns k0:k1 of the slice: k runs over MR
+                    const int64_t c0 = loc(k0, g.me.mr, c), cn = loc(k1, g.me.mr, c) - c0;
+                    copy_rect(Bblk[sl].buf + c0 * Bblk[sl].ldim, Bblk[sl].ldim, Bh + br0 + c0 * ldb, ldb, brn, cn, cudaMemcpyHostToDevice, hs);
+                }
+                b_up[sl][q].record(hs);
+                b_up[sl][q].block(cs);
+                if (!single) {
+                    const DistMat<T> Bsrc = tb ? Bblk[sl].View(0, wj, k0, k1) : Bblk[sl].View(k0, k1, 0, wj);
+                    DistMat<T> Bdst = tb ? PB[sl].View(0, wj, k0, k1) : PB[sl].View(k0, k1, 0, wj);
+                    Copy(Bsrc, Bdst);
+                }
+                b_ready[sl][q].record(cs);
+                b_ready[sl][q].block(s);
+                const DistMat<T> av = ta ? afull.View(k0, k1, 0, m) : afull.View(0, m, k0, k1);
+                const DistMat<T> bv = tb ? bfull.View(0, wj, k0, k1) : bfull.View(k0, k1, 0, wj);
+                LocalGemm(ta, tb, alpha, av, bv, q == 0 ? T(0) : T(1), Cblk[sl]);
+            }
+            if (beta != T(0)) {
+                Cin[sl].Resize(m, wj);
+                copy_rect(Cin[sl].buf, Cin[sl].ldim, Ch + cc0 * ldc, ldc, lhC, ccn, cudaMemcpyHostToDevice, hs);
+                up[sl].record(hs);
+                up[sl].block(s);
+                Axpy(beta, Cin[sl], Cblk[sl]);
+            }
+            done[sl].record(s);
+            done[sl].block(ds);
+            copy_rect(Ch + cc0 * ldc, ldc, Cblk[sl].buf, Cblk[sl].ldim, lhC, ccn, cudaMemcpyDeviceToHost, ds);
+            out[sl].record(ds);
+            continue;
+        }
+        // beta == 0: C's old contents are never read (they may hold NaNs) — nothing to upload
+        if (beta != T(0) || !product) copy_rect(Cblk[sl].buf, Cblk[sl].ldim, Ch + cc0 * ldc, ldc, lhC, ccn, cudaMemcpyHostToDevice, hs);
         if (product) {
             if (!tb) {
                 Bblk[sl].Resize(k, wj);

@@ -252,16 +252,17 @@ def check_gemm_proxies(grid, dtype) -> None:
             assert err <= tol, (d, alg, err, tol)
 
 
-def check_gemm_host(grid, dtype, m=150, k=100) -> int:
+def check_gemm_host(grid, dtype, m=60, k=100) -> int:
     """el.GemmHost (elb200_dist_gemm_host_*): operands in HOST memory, streamed in column blocks.
-    Sizes give six blocks on this grid (ragged last one; four block slots, so slots are reused), all orientations, beta = 0 with NaNs in
+    Sizes give eight blocks on this grid (six of two units, a tapered one of one unit, a ragged last one; four block slots, so
+    slots are reused), all orientations, beta = 0 with NaNs in
     C (must not propagate), k = 0 (pure scaling), padded leading dimensions."""
     import math
     og = _grid_oracle(grid)
     npdt = NPDT[dtype]
     me = grid.Rank()
     unit = (og.r * og.c // math.gcd(og.r, og.c)) * 256
-    n = 5 * unit + 77   # six column blocks (ragged last one): more blocks than block slots
+    n = 13 * unit + 77  # 6 blocks of 2 units + the tapered tail (1 unit, then the ragged 77): more blocks than block slots
     zero = lambda h, w: OD.Spec(OD.MC, OD.MR, 0, 0, h, w)  # noqa: E731
     cnt = 0
     for oa, ob in itertools.product((0, 1), (0, 1)):

@@ -94,9 +94,9 @@ def test_engine_survives_shared_hardware_queues(simlib, grid, hwq):
     """HOSTSIM_HWQ=N spreads a rank's streams over N work queues executed in ISSUE order (the false dependencies
     of CUDA_DEVICE_MAX_CONNECTIONS): a stream-ordered wait on a peer's flag then also holds back every stream
     behind it in that queue. With ONE queue per rank and every pipeline on (SUMMA-C panels, SUMMA-Dot ranges,
-    SUMMA-A / B panels, Trrk panels, host-operand Gemm, split AllGather) nothing may deadlock."""
+    SUMMA-A / B panels, Trrk panels, host-operand Gemm with the opt-in B ranges, split AllGather) nothing may deadlock."""
     _run(grid, "--only", "check_gemm_variants_f64,check_gemm_pipeline,check_gemm_dot_pipeline,check_level3,check_trsm,check_circ,check_gemm_host_f32",
-         env={"HOSTSIM_HWQ": hwq, "ELB200_PANEL_K": "16", "ELB200_DOT_CHUNK": "4", "ELB200_AG_SPLIT_BYTES": "1"})
+         env={"HOSTSIM_HWQ": hwq, "ELB200_PANEL_K": "16", "ELB200_DOT_CHUNK": "4", "ELB200_AG_SPLIT_BYTES": "1", "ELB200_HOST_BRANGES": "3"})
 
 
 def test_timeline_model(simlib):

@@ -17,6 +17,11 @@ if [ "$N" = "1" ]; then
   # 2. the bench lines (fp32 = BASELINE C2; fp64); e2e now has four block slots + streamed A
   python bench.py --steps 5 --warmup 3 > $OUT/bench_f32_1gpu.json 2>> $OUT/session.log
   python bench.py --steps 5 --warmup 3 --dtype f64 > $OUT/bench_f64_1gpu.json 2>> $OUT/session.log
+  # 2b. host-operand Gemm A/B: uniform blocks (the measured form), tapered tail (default), taper + B in 4 k ranges
+  for v in "ELB200_HOST_TAPER=0" "ELB200_HOST_TAPER=1" "ELB200_HOST_BRANGES=4" "ELB200_HOST_BRANGES=8"; do
+    echo "=== e2e $v" >> $OUT/e2e_variants.log; env $v timeout 120 tools/native_bench e2e >> $OUT/e2e_variants.log 2>&1
+  done
+  ELB200_HOST_BRANGES=4 timeout 600 python -m pytest tests/test_gpu_dist.py tests/test_gpu_level3.py -m gpu -x -q -k "gemm_host" > $OUT/e2e_branges_pytest.log 2>&1; echo "BRANGES pytest exit $?" >> $OUT/session.log
   # 3. fp64 kernel A/B: current vs warp-specialised (ELB200_F64_WS=1), same binary; the kernel tests with the variant on
   ELB200_F64_WS=1 timeout 600 python -m pytest tests/test_gpu_kernels.py -m gpu -x -q -k gemm > $OUT/f64_ws_pytest.log 2>&1; echo "f64 WS pytest exit $?" >> $OUT/session.log
   run tools/gemm_check perf f64 8192 16384
@@ -39,6 +44,7 @@ else
   # C4 with the split AllGather, and with it off; C5 with the SUMMA-Dot pipeline, and with it off
   run $TR tools/dist_sweep.py --c4 --c5 --out $OUT/dist_sweep_${N}gpu.json
   ELB200_AG_SPLIT_MB=0 ELB200_DOT_PIPELINE=0 $TR tools/dist_sweep.py --c4 --c5 --out $OUT/dist_sweep_${N}gpu_before.json >> $OUT/session.log 2>&1
+  ELB200_AG_ROTATE=0 $TR tools/dist_sweep.py --c4 --out $OUT/dist_sweep_${N}gpu_norotate.json >> $OUT/session.log 2>&1
   run $TR tools/level3_bench.py --n 32768 --dtype f32 --out $OUT/level3_${N}gpu.json
 fi
 tail -5 $OUT/session.log

@@ -135,7 +135,9 @@ def main():
 
     rows = [
         ("C2 fp32 n=16384 1x1", "38.7 ms (227.5 TF/s)", ["gemm", "1", "1", "16384", "f32"], None),
-        ("e2e fp32 n=16384 1x1 (4 slots, A streamed)", "67.8 ms (129.8 TF/s)", ["e2e", "1", "1", "16384", "f32"], None),
+        ("e2e fp32 n=16384 1x1, uniform blocks (as measured)", "67.8 ms (129.8 TF/s)", ["e2e", "1", "1", "16384", "f32"], {"ELB200_HOST_TAPER": "0"}),
+        ("e2e fp32 n=16384 1x1, tapered tail (default)", "not measured yet", ["e2e", "1", "1", "16384", "f32"], None),
+        ("e2e fp32 n=16384 1x1, tapered tail + B in 4 k ranges", "not measured yet", ["e2e", "1", "1", "16384", "f32"], {"ELB200_HOST_BRANGES": "4"}),
         ("fp32 n=32768 2x4", "40.9 ms (1720.9 TF/s)", ["gemm", "2", "4", "32768", "f32"], None),
         ("C3 fp64 n=32768 2x4", "292 ms (240.7 TF/s)", ["gemm", "2", "4", "32768", "f64"], None),
         ("C4 1 GiB 2x2, gather in one piece (as measured)", "0.54 / 0.55 / 0.61 ms", ["c4", "2", "2"], {"ELB200_AG_SPLIT_MB": "0"}),
