@@ -9,7 +9,7 @@ numbers are a model to be CALIBRATED against measurements (see the table it prin
 
   python tools/model_timeline.py                     # the calibration table (known measurements next to the model)
   python tools/model_timeline.py gemm 2 4 32768 f32  # one scenario: El::Gemm SUMMA_C on a 2 x 4 grid
-  python tools/model_timeline.py e2e 1 1 16384 f32 | c4 2 2 | c5 2 4
+  python tools/model_timeline.py e2e 1 1 16384 f32 | c4 2 2 | c5 2 4 | syrk 2 4 32768 f32 | symm ... | trsm ...
 """
 import ctypes as C
 import os
@@ -100,6 +100,22 @@ def scen_c4(r, c, gbytes=1 << 30, dtype="f32"):
     return tuple(max(x[i] for x in res) for i in range(3))
 
 
+def scen_level3(r, c, n, dtype, what):
+    """Syrk (C := a A A^T + b C, LOWER, n x n from n x n) / Symm (LEFT, LOWER) / Trsm (LEFT LOWER NORMAL, n x n right-hand sides)"""
+    dt = torch.float32 if dtype == "f32" else torch.float64
+
+    def body(g):
+        A, B, Cm = dm(g, el.MC, el.MR, dt, n, n), dm(g, el.MC, el.MR, dt, n, n), dm(g, el.MC, el.MR, dt, n, n)
+        if what == "syrk":
+            return timed(g, lambda: el.Syrk(el.LOWER, 0, 0.5, A, -0.5, Cm))
+        if what == "symm":
+            return timed(g, lambda: el.Symm(el.LEFT, el.LOWER, 0.5, A, B, -0.5, Cm))
+        return timed(g, lambda: el.Trsm(el.LEFT, el.LOWER, 0, el.NON_UNIT, 0.5, A, B))
+    ms = max(el.run_grid(r, c, body))
+    flops = {"syrk": 1.0, "symm": 2.0, "trsm": 1.0}[what] * n ** 3
+    return ms, flops / ms / 1e9
+
+
 def main():
     a = sys.argv[1:]
     if a and a[0] == "gemm":
@@ -116,6 +132,11 @@ def main():
         r, c = int(a[1]), int(a[2])
         t = scen_c4(r, c)
         print(f"model: C4 1 GiB fp32 on {r}x{c}: {t[0]:.2f} / {t[1]:.2f} / {t[2]:.2f} ms ([MC,MR]->[MC,*] / ->[*,VR] / AxpyContract)")
+        return
+    if a and a[0] in ("syrk", "symm", "trsm"):
+        r, c, n, dt = int(a[1]), int(a[2]), int(a[3]), a[4]
+        ms, tf = scen_level3(r, c, n, dt, a[0])
+        print(f"model: El::{a[0].capitalize()} {dt} n={n} on {r}x{c}: {ms:.2f} ms ({tf:.1f} useful TF/s)")
         return
     if a and a[0] == "c5":
         r, c = int(a[1]), int(a[2])
