@@ -23,6 +23,18 @@ struct EngineError : std::runtime_error {
 };
 void throw_status(int status, const char* where);
 void cuda_check(cudaError_t e, const char* where);
+
+// RAII event: record on one stream, make another wait. Released on every exit of the schedule that owns it,
+// a throwing redistribution in the middle of a pipeline included.
+struct Ev {
+    cudaEvent_t e = nullptr;
+    Ev() { cuda_check(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), "cudaEventCreate"); }
+    ~Ev() { if (e) cudaEventDestroy(e); }
+    Ev(const Ev&) = delete;
+    Ev& operator=(const Ev&) = delete;
+    void record(cudaStream_t s) { cuda_check(cudaEventRecord(e, s), "cudaEventRecord"); }
+    void block(cudaStream_t s) { cuda_check(cudaStreamWaitEvent(s, e, 0), "cudaStreamWaitEvent"); }
+};
 void nccl_check(ncclResult_t r, const char* where);
 
 // Mirrors El::GemmAlgorithm (reference include/El/blas_like/level3.hpp:22-35), same order and values.

@@ -95,16 +95,6 @@ int ResolveGemmAlg(int, int, int64_t m, int64_t n, int64_t k, int alg) {
 
 namespace {
 
-// RAII event: record on one stream, make another wait
-struct Ev {
-    cudaEvent_t e = nullptr;
-    Ev() { cuda_check(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), "cudaEventCreate"); }
-    ~Ev() { if (e) cudaEventDestroy(e); }
-    Ev(const Ev&) = delete;
-    Ev& operator=(const Ev&) = delete;
-    void record(cudaStream_t s) { cuda_check(cudaEventRecord(e, s), "cudaEventRecord"); }
-    void block(cudaStream_t s) { cuda_check(cudaStreamWaitEvent(s, e, 0), "cudaStreamWaitEvent"); }
-};
 
 // src redistributed as (col,row) aligned with `like`; returns src itself when that
 // redistribution is the identity on every rank (no data motion, no copy).
@@ -257,14 +247,9 @@ void SummaC(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, T
     cudaStream_t cs = g.comm_stream;
     DistMat<T> PA[2] = {DistMat<T>(g, ta ? STAR : MC, ta ? MC : STAR, cs), DistMat<T>(g, ta ? STAR : MC, ta ? MC : STAR, cs)};
     DistMat<T> PB[2] = {DistMat<T>(g, tb ? MR : STAR, tb ? STAR : MR, cs), DistMat<T>(g, tb ? MR : STAR, tb ? STAR : MR, cs)};
-    cudaEvent_t ready[2], freed[2], start;
-    for (int i = 0; i < 2; ++i) {
-        cuda_check(cudaEventCreateWithFlags(&ready[i], cudaEventDisableTiming), "cudaEventCreate");
-        cuda_check(cudaEventCreateWithFlags(&freed[i], cudaEventDisableTiming), "cudaEventCreate");
-    }
-    cuda_check(cudaEventCreateWithFlags(&start, cudaEventDisableTiming), "cudaEventCreate");
-    cuda_check(cudaEventRecord(start, C.stream), "cudaEventRecord");   // A, B, C are ready in C.stream order
-    cuda_check(cudaStreamWaitEvent(cs, start, 0), "cudaStreamWaitEvent");
+    Ev ready[2], freed[2], start;  // RAII: released on every exit, a throwing redistribution included
+    start.record(C.stream);        // A, B, C are ready in C.stream order
+    start.block(cs);
     // ramp: the first gather cannot hide behind a GEMM, so the first two panels are narrower
     const int64_t nbk = Grid::Blocksize();
     auto width = [&](int64_t p) { return p >= 2 ? W : std::max(nbk, (W >> (2 - p)) / nbk * nbk); };
@@ -272,7 +257,7 @@ void SummaC(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, T
     for (int64_t k0 = 0, kb = 0; k0 < d.k; k0 += kb, ++p) {
         const int s = int(p & 1);
         kb = std::min(width(p), d.k - k0);
-        if (p >= 2) cuda_check(cudaStreamWaitEvent(cs, freed[s], 0), "cudaStreamWaitEvent");
+        if (p >= 2) freed[s].block(cs);
         DistMat<T> A1 = ta ? A.View(k0, k0 + kb, 0, d.m) : A.View(0, d.m, k0, k0 + kb);
         DistMat<T> B1 = tb ? B.View(0, d.n, k0, k0 + kb) : B.View(k0, k0 + kb, 0, d.n);
         // optional cap on the CTAs of unpack kernels that run underneath a GEMM (ELB200_BG_CTAS; off by
@@ -282,15 +267,13 @@ void SummaC(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, T
         const DistMat<T>& a = panel_as(A1, PA[s], C.spec);
         const DistMat<T>& b = panel_as(B1, PB[s], C.spec);
         set_lattice_cta_limit(0);
-        cuda_check(cudaEventRecord(ready[s], cs), "cudaEventRecord");
-        cuda_check(cudaStreamWaitEvent(C.stream, ready[s], 0), "cudaStreamWaitEvent");
+        ready[s].record(cs);
+        ready[s].block(C.stream);
         LocalGemm(ta, tb, alpha, a, b, p == 0 ? beta : T(1), C);
-        cuda_check(cudaEventRecord(freed[s], C.stream), "cudaEventRecord");
+        freed[s].record(C.stream);
     }
     // the panels are freed in comm-stream order: not before the last GEMMs have read them
-    for (int i = 0; i < 2 && i < p; ++i) cuda_check(cudaStreamWaitEvent(cs, freed[i], 0), "cudaStreamWaitEvent");
-    for (int i = 0; i < 2; ++i) { cudaEventDestroy(ready[i]); cudaEventDestroy(freed[i]); }
-    cudaEventDestroy(start);
+    for (int i = 0; i < 2 && i < p; ++i) freed[i].block(cs);
 }
 
 // Two-slot panel pipeline shared by SUMMA-A / SUMMA-B: the redistribution of panel p+1 runs on the comm stream

@@ -20,6 +20,7 @@
 #include <algorithm>
 #include <atomic>
 #include <cstdlib>
+#include <memory>
 
 #include "engine.hpp"
 #include "engine_dev.hpp"
@@ -199,40 +200,33 @@ void Trrk(int uplo, int ta, int tb, T alpha, const DistMat<T>& Apre, const DistM
         cudaStream_t ps = pipe ? g.comm_stream : C.stream;
         DistMat<T> PA[2] = {DistMat<T>(g, ta ? STAR : MC, ta ? MC : STAR, ps), DistMat<T>(g, ta ? STAR : MC, ta ? MC : STAR, ps)};
         DistMat<T> PB[2] = {DistMat<T>(g, tb ? MR : STAR, tb ? STAR : MR, ps), DistMat<T>(g, tb ? MR : STAR, tb ? STAR : MR, ps)};
-        cudaEvent_t ready[2] = {nullptr, nullptr}, freed[2] = {nullptr, nullptr}, start = nullptr;
+        std::unique_ptr<Ev[]> ev(pipe ? new Ev[5] : nullptr);  // ready[2], freed[2], start
+        Ev* ready = ev.get();
+        Ev* freed = pipe ? ev.get() + 2 : nullptr;
         if (pipe) {
-            for (int i = 0; i < 2; ++i) {
-                cuda_check(cudaEventCreateWithFlags(&ready[i], cudaEventDisableTiming), "cudaEventCreate");
-                cuda_check(cudaEventCreateWithFlags(&freed[i], cudaEventDisableTiming), "cudaEventCreate");
-            }
-            cuda_check(cudaEventCreateWithFlags(&start, cudaEventDisableTiming), "cudaEventCreate");
-            cuda_check(cudaEventRecord(start, C.stream), "cudaEventRecord");  // A, B, C are ready in C.stream order
-            cuda_check(cudaStreamWaitEvent(ps, start, 0), "cudaStreamWaitEvent");
+            ev[4].record(C.stream);  // A, B, C are ready in C.stream order
+            ev[4].block(ps);
         }
         int64_t p = 0;
         for (int64_t k0 = 0; k0 < k; k0 += W, ++p) {
             const int sl = pipe ? int(p & 1) : 0;
             const int64_t kw = std::min(W, k - k0);
-            if (pipe && p >= 2) cuda_check(cudaStreamWaitEvent(ps, freed[sl], 0), "cudaStreamWaitEvent");
+            if (pipe && p >= 2) freed[sl].block(ps);
             const DistMat<T> A1 = ta ? A.View(k0, k0 + kw, 0, n) : A.View(0, n, k0, k0 + kw);
             const DistMat<T> B1 = tb ? B.View(0, n, k0, k0 + kw) : B.View(k0, k0 + kw, 0, n);
             const DistMat<T>& a = PanelAs(A1, PA[sl], C.spec);
             const DistMat<T>& b = PanelAs(B1, PB[sl], C.spec);
             if (pipe) {
-                cuda_check(cudaEventRecord(ready[sl], ps), "cudaEventRecord");
-                cuda_check(cudaStreamWaitEvent(C.stream, ready[sl], 0), "cudaStreamWaitEvent");
+                ready[sl].record(ps);
+                ready[sl].block(C.stream);
             }
             // a / b may be A1 / B1 themselves when the gather is the identity on this grid (PanelAs), so
             // the recursion is entered directly instead of through LocalTrrk's distribution checks
             local_trrk_rec(uplo, ta, tb, alpha, a, b, C, int64_t(g.shape.c) * Grid::LocalTrrkBlocksize());
-            if (pipe) cuda_check(cudaEventRecord(freed[sl], C.stream), "cudaEventRecord");
+            if (pipe) freed[sl].record(C.stream);
         }
-        if (pipe) {
-            // the panels are freed in comm-stream order: not before the last products have read them
-            for (int i = 0; i < 2 && i < p; ++i) cuda_check(cudaStreamWaitEvent(ps, freed[i], 0), "cudaStreamWaitEvent");
-            for (int i = 0; i < 2; ++i) { cudaEventDestroy(ready[i]); cudaEventDestroy(freed[i]); }
-            cudaEventDestroy(start);
-        }
+        // the panels are freed in comm-stream order: not before the last products have read them
+        for (int i = 0; pipe && i < 2 && i < p; ++i) freed[i].block(ps);
     }
     if (!c_ok) {
         DistMat<T> back = Cpre.View(0, n, 0, n);
