@@ -98,29 +98,36 @@ int elb200_gemm_f32_ex(int transA, int transB, int64_t m, int64_t n, int64_t k, 
     const float* Ause = A; const float* Buse = B;
     int64_t lda_use = lda, ldb_use = ldb;
     float* tmpA = nullptr; float* tmpB = nullptr;
+    auto release = [&]() {  // stream-ordered: safe right after the launches that read them
+        if (tmpA) cudaFreeAsync(tmpA, s);
+        if (tmpB) cudaFreeAsync(tmpB, s);
+        tmpA = tmpB = nullptr;
+    };
     if (!a_ok) {
         const int64_t rows = transA ? k : m, cols = transA ? m : k;
         lda_use = (rows + 3) & ~int64_t(3);
         if (check_cuda(cudaMallocAsync(&tmpA, size_t(lda_use) * cols * 4, s), "cudaMallocAsync"))
             return ELB200_ERR_CUDA;
         st = elb200_copy2d_f32(rows, cols, A, 1, lda, tmpA, 1, lda_use, stream);
-        if (st != ELB200_OK) return st;
+        if (st != ELB200_OK) { release(); return st; }
         Ause = tmpA;
     }
     if (!b_ok) {
         const int64_t rows = transB ? n : k, cols = transB ? k : n;
         ldb_use = (rows + 3) & ~int64_t(3);
-        if (check_cuda(cudaMallocAsync(&tmpB, size_t(ldb_use) * cols * 4, s), "cudaMallocAsync"))
+        if (check_cuda(cudaMallocAsync(&tmpB, size_t(ldb_use) * cols * 4, s), "cudaMallocAsync")) {
+            tmpB = nullptr;
+            release();
             return ELB200_ERR_CUDA;
+        }
         st = elb200_copy2d_f32(rows, cols, B, 1, ldb, tmpB, 1, ldb_use, stream);
-        if (st != ELB200_OK) return st;
+        if (st != ELB200_OK) { release(); return st; }
         Buse = tmpB;
     }
     st = gemm_f32_tensor(transA != 0, transB != 0, m, n, k, alpha, Ause, lda_use, Buse, ldb_use,
                          beta, C, ldc, cta_group, s);
     if (st == ELB200_ERR_CUDA) set_last_error("gemm_f32 launch", cudaGetErrorString(cudaGetLastError()));
-    if (tmpA) cudaFreeAsync(tmpA, s);
-    if (tmpB) cudaFreeAsync(tmpB, s);
+    release();
     return st;
 }
 
