@@ -289,6 +289,7 @@ def _measure(args, grid, el, lib, torch, dist, world, rank, local, n_gpus, n, td
     # elb200_dist_gemm_host_*): A, B, C live in pinned HOST memory, every step uploads them,
     # multiplies and downloads C inside the timed region.
     e2e = None
+    e2e_error = None
     if not args.no_e2e:
         def host_like(M):
             v = M.Matrix()
@@ -316,20 +317,29 @@ def _measure(args, grid, el, lib, torch, dist, world, rank, local, n_gpus, n, td
         # the two paths accumulate k in different chunkings (one full-k GEMM per block here, k-panels
         # there), so they agree to the north-star bound, not bit for bit
         bound = (1e-5 if args.dtype == "f32" else 1e-13) * float(n) ** 0.5
-        if not num <= bound * max(den, 1e-30):
-            raise RuntimeError(f"GemmHost result differs from the device-resident Gemm: rel err {num / max(den, 1e-30):.3e}")
-        barrier()
-        e0.record(grid.stream)
-        for _ in range(e2e_steps):
-            e2e_step()
-        e1.record(grid.stream)
-        barrier()
-        t = torch.tensor([e0.elapsed_time(e1) / e2e_steps], device=f"cuda:{local}", dtype=torch.float64)
+        # a mismatch voids the e2e number only: the device-resident line above stands, the failure is reported in
+        # the line ("e2e": null, "e2e_error") and on stderr; every rank takes the same branch (flag reduced over ranks)
+        rel = num / max(den, 1e-30)
+        bad = torch.tensor([0.0 if num <= bound * max(den, 1e-30) else 1.0], device=f"cuda:{local}", dtype=torch.float64)
         if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        loc = A.LocalHeight() * A.LocalWidth() * esz
-        e2e = {"value": flops / (float(t.item()) * 1e-3) / 1e12, "unit": UNIT, "ms_per_step": float(t.item()),
-               "h2d_bytes_per_step": 3 * loc * n_gpus, "d2h_bytes_per_step": loc * n_gpus, "steps": e2e_steps}
+            dist.all_reduce(bad, op=dist.ReduceOp.MAX)
+        if float(bad.item()) != 0.0:
+            e2e_error = f"GemmHost result differs from the device-resident Gemm on some rank (rank {rank}: rel err {rel:.3e}, bound {bound:.3e})"
+            print("bench.py: " + e2e_error, file=sys.stderr)
+        else:
+            e2e_error = None
+            barrier()
+            e0.record(grid.stream)
+            for _ in range(e2e_steps):
+                e2e_step()
+            e1.record(grid.stream)
+            barrier()
+            t = torch.tensor([e0.elapsed_time(e1) / e2e_steps], device=f"cuda:{local}", dtype=torch.float64)
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            loc = A.LocalHeight() * A.LocalWidth() * esz
+            e2e = {"value": flops / (float(t.item()) * 1e-3) / 1e12, "unit": UNIT, "ms_per_step": float(t.item()),
+                   "h2d_bytes_per_step": 3 * loc * n_gpus, "d2h_bytes_per_step": loc * n_gpus, "steps": e2e_steps}
 
     if rank == 0:
         peaks = load_peaks()
@@ -368,6 +378,8 @@ def _measure(args, grid, el, lib, torch, dist, world, rank, local, n_gpus, n, td
                            "panel_k": "full k on 1x1; ELB200_PANEL_K (default 4096 fp32 / 2048 fp64) otherwise",
                            "per_gpu_tflops": value / n_gpus},
                 "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
+        if e2e_error:
+            line["e2e_error"] = e2e_error
         return line
     return None
 
