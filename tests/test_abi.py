@@ -88,6 +88,22 @@ def test_library_is_built_for_sm_100a_only():
     assert archs == {"100a"}, archs
 
 
+def test_hot_kernels_use_the_blackwell_paths():
+    """Static check of the shipped binary: the fp32 GEMM issues tcgen05.mma (SASS UTCHMMA, both CTA-group
+    forms) fed by TMA (UTMALDG) with mbarriers (SYNCS), the fp64 GEMM runs on the DMMA pipe, and the
+    BLAS-1 / pack kernels use 128-bit global accesses — and nothing fell back to mma.sync-era HMMA or to
+    a library GEMM (libelb200.so must not link cuBLAS)."""
+    cuobjdump = "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(cuobjdump):
+        pytest.skip("cuobjdump not available")
+    sass = subprocess.run([cuobjdump, "-sass", L.LIB_PATH], capture_output=True, text=True).stdout
+    for mnemonic in ("UTCHMMA.2CTA", "UTCHMMA ", "UTMALDG.2D", "SYNCS.PHASECHK", "DMMA.8", "LDG.E.128", "STG.E.128"):
+        assert mnemonic in sass, mnemonic
+    assert not re.search(r"(?<![A-Z])HMMA\.", sass)  # mma.sync / wmma half-precision path (UTCHMMA is tcgen05)
+    needed = subprocess.run(["readelf", "-d", L.LIB_PATH], capture_output=True, text=True).stdout
+    assert "cublas" not in needed.lower(), needed
+
+
 def test_product_does_not_import_the_oracle():
     """oracle/ is test infrastructure: nothing under elemental_b200/ may import or execute it."""
     pkg = os.path.join(ROOT, "elemental_b200")
