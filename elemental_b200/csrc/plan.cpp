@@ -191,7 +191,6 @@ CopyPlan plan_copy(const GridShape& g, GridCoord me, const DistSpec& A, const Di
         }
     }
 
-    bool remote = false;
     for (int v = 0; v < p; ++v) {
         const GridCoord q = coord_of_vc(g, v);
         if (feeds(me, q)) {
@@ -200,7 +199,7 @@ CopyPlan plan_copy(const GridShape& g, GridCoord me, const DistSpec& A, const Di
             m.seg = pair_lattice(g, A, me, B, q, true);
             if (m.count() > 0) {
                 if (v == my_vc) { plan.has_self = true; plan.self_send = m; }
-                else { m.seg.buf_offset = plan.send_elems; plan.send_elems += m.count(); plan.sends.push_back(m); remote = true; }
+                else { m.seg.buf_offset = plan.send_elems; plan.send_elems += m.count(); plan.sends.push_back(m); }
             }
         }
         if (feeds(q, me)) {
@@ -209,14 +208,13 @@ CopyPlan plan_copy(const GridShape& g, GridCoord me, const DistSpec& A, const Di
             m.seg = pair_lattice(g, A, q, B, me, false);
             if (m.count() > 0) {
                 if (v == my_vc) plan.self_recv = m;
-                else { m.seg.buf_offset = plan.recv_elems; plan.recv_elems += m.count(); plan.recvs.push_back(m); remote = true; }
+                else { m.seg.buf_offset = plan.recv_elems; plan.recv_elems += m.count(); plan.recvs.push_back(m); }
             }
         }
     }
     // EX_LOCAL must be agreed on by every rank (it decides whether a collective call is made):
     // it holds exactly when no pair of DISTINCT ranks exchanges anything, which each rank can
     // decide from the specs alone.
-    (void)remote;
     bool any_remote = false;
     for (int vs = 0; vs < p && !any_remote; ++vs)
         for (int vq = 0; vq < p && !any_remote; ++vq) {
