@@ -83,8 +83,10 @@ void Copy(const DistMat<T>& A, DistMat<T>& B) {
             // Large blocks: do not wait for the whole gather. My own block goes straight from A into B (no copy
             // into my own slot) while the peers' blocks are in flight, and each peer's block is unpacked as soon
             // as ITS arrival flag is up — transfers from the other peers continue underneath. Small messages are
-            // latency-bound and keep the one-wait, one-launch form. (ELB200_AG_SPLIT_MB, default 4; 0 disables.)
-            static const int64_t split_mb = [] { const char* e = std::getenv("ELB200_AG_SPLIT_MB"); return e ? std::atoll(e) : 4ll; }();
+            // latency-bound and keep the one-wait, one-launch form. OPT-IN (ELB200_AG_SPLIT_MB=4 is the intended
+            // threshold; default 0 = off) until the form has run on real NVLink hardware: the one-piece gather below
+            // is the one every committed multi-GPU number was measured with.
+            static const int64_t split_mb = [] { const char* e = std::getenv("ELB200_AG_SPLIT_MB"); return e ? std::atoll(e) : 0ll; }();
             static const int64_t split_b = [] { const char* e = std::getenv("ELB200_AG_SPLIT_BYTES"); return e ? std::atoll(e) : 0ll; }();
             const int64_t split_bytes = split_b > 0 ? split_b : split_mb << 20;
             if (split_bytes > 0 && plan.portion * int64_t(sizeof(T)) >= split_bytes && plan.recvs[size_t(idx)].peer == g.vc_rank) {

@@ -42,9 +42,11 @@ else
   $TR bench.py --gpus $N --steps 5 --warmup 3 > $OUT/bench_f32_${N}gpu.json 2>> $OUT/session.log
   $TR bench.py --gpus $N --steps 5 --warmup 3 --dtype f64 > $OUT/bench_f64_${N}gpu.json 2>> $OUT/session.log
   # C4 with the split AllGather, and with it off; C5 with the SUMMA-Dot pipeline, and with it off
-  run $TR tools/dist_sweep.py --c4 --c5 --out $OUT/dist_sweep_${N}gpu.json
-  ELB200_AG_SPLIT_MB=0 ELB200_DOT_PIPELINE=0 $TR tools/dist_sweep.py --c4 --c5 --out $OUT/dist_sweep_${N}gpu_before.json >> $OUT/session.log 2>&1
-  ELB200_AG_ROTATE=0 $TR tools/dist_sweep.py --c4 --out $OUT/dist_sweep_${N}gpu_norotate.json >> $OUT/session.log 2>&1
+  # the split gather is opt-in until it has passed here: parity with it on, then the A/B
+  ELB200_AG_SPLIT_MB=4 timeout 900 $TR tests/dist_worker.py > $OUT/dist_worker_agsplit.log 2>&1; echo "AG split dist_worker exit $?" >> $OUT/session.log
+  ELB200_DOT_PIPELINE=0 $TR tools/dist_sweep.py --c4 --c5 --out $OUT/dist_sweep_${N}gpu_before.json >> $OUT/session.log 2>&1
+  ELB200_AG_SPLIT_MB=4 timeout 900 $TR tools/dist_sweep.py --c4 --c5 --out $OUT/dist_sweep_${N}gpu.json >> $OUT/session.log 2>&1
+  ELB200_AG_SPLIT_MB=4 ELB200_AG_ROTATE=0 timeout 900 $TR tools/dist_sweep.py --c4 --out $OUT/dist_sweep_${N}gpu_norotate.json >> $OUT/session.log 2>&1
   run $TR tools/level3_bench.py --n 32768 --dtype f32 --out $OUT/level3_${N}gpu.json
 fi
 tail -5 $OUT/session.log
