@@ -7,13 +7,22 @@
 One "step" = one El::Gemm(NORMAL, NORMAL, 0.5, A, B, -0.5, C, GEMM_SUMMA_C) over [MC,MR] DistMatrices
 on the default r x c grid (Grid::DefaultHeight), inputs Uniform(-0.1, 0.1) resident in HBM
 (reference drivers: tests/blas_like/Gemm_Suite.cpp:153-248; TFLOP/s = 2 m n k / t, Gemm.cpp:120).
-N = 1 is BASELINE config[1] (fp32 SUMMA_C n=16384 on one B200). For N > 1 the per-GPU work is held
-fixed (weak scaling): n = 16384 * N^(1/3) rounded to 512, i.e. n = 32768 at 8 GPUs — the metric's size.
 
-The JSON line carries, beside the base contract: `roofline` (the local GEMM kernel timed with CUDA
-events inside the timed region), `cpu_baseline` (the reference's CPU path on this box's host cores,
-bounded sample), `e2e` (same call with host buffers, H2D/D2H inside the timed region), `clocks`,
-`gpu_launches`.
+The headline line is fp32 at the size the metric is quoted on, n = 32768, on ONE GPU; for N > 1 the
+per-GPU work is held fixed (weak scaling): n = 32768 * N^(1/3) rounded to 512 (65536 at 8 GPUs).
+The same run adds, as sub-records of the line (each timed the same way, outside the main timed region):
+  `strong_n32768`  fp32 at FIXED n = 32768 on the N-GPU grid (N > 1; at N = 1 it is the headline itself)
+  `fp64`           the fp64 half of the metric at n = 32768 on the N-GPU grid (N = 8: BASELINE config C3,
+                   2 x 4 grid), with its own roofline object and e2e value
+  `parity`         oracle parity of the multi-rank code paths on THIS grid (tests/dist_cases.run_all: 121
+                   redistributions bit-exact, contractions, 40 Gemm variants per dtype, proxies, host-operand
+                   Gemm, pipelines) plus the bench-size accuracy of every timed configuration (a checksum of
+                   checksums in fp64, and sampled rows at N = 1). The oracle is the checker there, never the
+                   thing measured; a parity failure makes the exit code non-zero.
+Beside the base contract the line carries `roofline` (the local GEMM kernel timed with CUDA events inside
+the timed region), `cpu_baseline` (the reference's CPU path on this box's host cores, bounded sample),
+`e2e` (same call with host buffers, H2D/D2H inside the timed region), `clocks`, `gpu_launches`,
+`library_peaks` (cuBLAS Dgemm / TF32 GemmEx through torch.matmul on this very GPU: practical denominators).
 """
 from __future__ import annotations
 
@@ -32,7 +41,9 @@ sys.path.insert(0, ROOT)
 
 METRIC = "El::Gemm TFLOP/s"
 UNIT = "TFLOP/s"
-BASE_N = 16384
+BASE_N = 32768      # the size BASELINE.json quotes the metric on
+FIXED_N = 32768     # strong-scaling / fp64 sub-records
+ALG_NAMES = ['DEFAULT', 'SUMMA_A_MS', 'SUMMA_A', 'SUMMA_B_MS', 'SUMMA_B', 'SUMMA_C_MS', 'SUMMA_C', 'SUMMA_DOT', 'CANNON']
 
 
 def parse_args():
@@ -46,6 +57,9 @@ def parse_args():
     ap.add_argument("--alg", type=int, default=6, help="El::GemmAlgorithm, reference enum values (6 = GEMM_SUMMA_C, 7 = GEMM_SUMMA_DOT)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the oracle parity pass (diagnostics only)")
+    ap.add_argument("--no-sub", action="store_true", help="skip the fp64 / strong-scaling sub-records (diagnostics only)")
+    ap.add_argument("--sub-steps", type=int, default=3, help="timed steps of each sub-record")
     return ap.parse_args()
 
 
@@ -53,6 +67,15 @@ def workload_n(n_gpus: int, override: int = 0) -> int:
     if override:
         return override
     return int(round(BASE_N * n_gpus ** (1.0 / 3.0) / 512.0)) * 512
+
+
+def make_config(args, n_gpus: int, n: int) -> dict:
+    """`config` of the JSON line — built the same way by both arms so the two lines name one workload."""
+    return {"workload": f"El::Gemm {args.dtype} {ALG_NAMES[args.alg]} n={n} (NN, alpha=0.5, beta=-0.5) over [MC,MR] DistMatrices, "
+                        f"{n_gpus} GPU(s), default grid (Grid::DefaultHeight)",
+            "n": n, "dtype": args.dtype, "alg": ALG_NAMES[args.alg],
+            "inputs": "Uniform(-0.1,0.1), synthetic",
+            "scaling_rule": f"weak: n = {BASE_N} * N^(1/3) rounded to 512 (flops per GPU constant); sub-records at fixed n = {FIXED_N}"}
 
 
 def load_peaks():
@@ -186,20 +209,327 @@ def run_reference(args) -> int:
             break
     v = statistics.mean(vals)
     ms = 2.0 * n_s ** 3 / (v * 1e12) * 1e3
+    other = "f64" if args.dtype == "f32" else "f32"
+    sub = None
+    if not args.n and not args.no_sub:
+        n_o = min(n_s, 4096)
+        vo, info_o = cpu_reference_rate(other, n_o, reps=2)
+        sub = {"value": vo, "unit": UNIT, **info_o}
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": len(vals),
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": args.dtype, "data": "synthetic",
-            "config": {"workload": f"El::Gemm {args.dtype} SUMMA_C n={n_full} (NN, alpha=0.5, beta=-0.5); each step = bounded sample n={n_s} of it",
-                       "grid": "1x1 (host cores)"},
+            "config": make_config(args, args.gpus, n_full),
+            "sample_note": f"each step = bounded sample n={n_s} of the workload on a 1x1 grid (host cores); the reference has no "
+                           "multi-rank CPU build on this box (no MPI), so every N runs this one process",
             "cpu_baseline": {"value": v, "unit": UNIT, **info},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
+    if sub:
+        line["fp64" if other == "f64" else "fp32"] = sub
     emit(line)
     return 0
 
 
+class Ctx:
+    """Everything a measurement needs: the grid, torch, the process group facts and a pinned host pool."""
+
+    def __init__(self, args, grid, el, lib, torch, dist, world, rank, local):
+        self.args, self.grid, self.el, self.lib, self.torch, self.dist = args, grid, el, lib, torch, dist
+        self.world, self.rank, self.local = world, rank, local
+        self.dev = f"cuda:{local}"
+        self.pool = None  # pinned host bytes, grown on demand, shared by every e2e leg
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, x: float) -> float:
+        t = self.torch.tensor([x], device=self.dev, dtype=self.torch.float64)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def host_pool(self, nbytes: int):
+        if self.pool is None or self.pool.numel() < nbytes:
+            self.pool = None
+            self.pool = self.torch.empty(nbytes, dtype=self.torch.uint8, pin_memory=True)
+        return self.pool
+
+
+def dist_matvec(ctx: Ctx, M, X):
+    """M @ X for an [MC,MR] zero-aligned DistMatrix M (height x width) and a full (width x nv) fp64 tensor X
+    that every rank holds: each rank multiplies its local entries in fp64 and the partial rows are summed over
+    the ranks with ONE torch.distributed all_reduce. Plain torch + NCCL — independent of this library's own
+    redistribution and GEMM code, which is what it is used to check."""
+    torch = ctx.torch
+    g = ctx.grid
+    r, c, mc, mr = g.Height(), g.Width(), g.MCRank(), g.MRRank()
+    loc = M.Matrix()
+    lh, lw = loc.shape
+    out = torch.zeros((M.Height(), X.shape[1]), dtype=torch.float64, device=ctx.dev)
+    if lh and lw:
+        cols = mr + c * torch.arange(lw, device=ctx.dev)
+        rows = mc + r * torch.arange(lh, device=ctx.dev)
+        Xc = X.index_select(0, cols)
+        step = max(1, (1 << 27) // max(lw, 1))  # <= 1 GiB of fp64 temporaries per chunk
+        for i0 in range(0, lh, step):
+            i1 = min(lh, i0 + step)
+            out[rows[i0:i1]] = loc[i0:i1].double() @ Xc
+    if ctx.world > 1:
+        ctx.dist.all_reduce(out)
+    return out
+
+
+def rel_err(torch, got, want) -> float:
+    return float(torch.linalg.norm(got - want) / torch.linalg.norm(want).clamp_min(1e-300))
+
+
+# Bench-size accuracy bounds. The north-star bound is 1e-5*sqrt(k) (fp32) / 1e-13*sqrt(k) (fp64) relative
+# Frobenius error; at k = 32768 that is 1.8e-3 — loose enough to pass a single-pass TF32 product (~5e-4), which
+# is NOT fp32-accurate. The assertion therefore uses a regression bound about twice the error this kernel was
+# measured at (3xTF32, fp32 accumulation in TMEM that truncates: ~1e-4 per 16384-long accumulation chain).
+ACC_BOUND = {"f32": 2.5e-4, "f64": 2e-13}
+
+
+def measure_gemm(ctx: Ctx, dtype: str, n: int, steps: int, warmup: int, e2e_steps: int, main: bool):
+    """Time `steps` El::Gemm calls of size n on the grid (device-resident), check the result at that size, then the
+    same call with host operands (e2e). Returns the record (rank 0) or None."""
+    args, grid, el, lib, torch, dist = ctx.args, ctx.grid, ctx.el, ctx.lib, ctx.torch, ctx.dist
+    world, rank, local = ctx.world, ctx.rank, ctx.local
+    tdt = torch.float32 if dtype == "f32" else torch.float64
+    esz = 4 if dtype == "f32" else 8
+    alpha, beta = 0.5, -0.5
+    A = el.DistMatrix(grid, el.MC, el.MR, tdt).Resize(n, n)
+    B = el.DistMatrix(grid, el.MC, el.MR, tdt).Resize(n, n)
+    Cm = el.DistMatrix(grid, el.MC, el.MR, tdt).Resize(n, n)
+    gen = torch.Generator(device=ctx.dev).manual_seed(21 + rank)
+    with torch.cuda.stream(grid.stream):
+        for M in (A, B, Cm):
+            vt = M.Matrix().t()  # (local width x local height): one row per local column, contiguous
+            # filled in column blocks so the temporaries of torch.rand stay small next to 3 x 8 GiB operands
+            for j0 in range(0, vt.shape[0], 2048):
+                blk = vt[j0:j0 + 2048]
+                blk.copy_((torch.rand(blk.shape, device=ctx.dev, dtype=tdt, generator=gen) - 0.5) * 0.2)
+    grid.sync()
+
+    def step():
+        el.Gemm(el.NORMAL, el.NORMAL, alpha, A, B, beta, Cm, args.alg)
+
+    # ---- accuracy at THIS size, outside the timed region: checksum of checksums in fp64
+    #      C X == alpha A (B X) + beta C0 X for 8 random +-1 vectors (E|(C - C*) x|^2 = |C - C*|_F^2, so the
+    #      relative error of the checksums estimates the relative Frobenius error of C), plus sampled rows at N = 1
+    acc = {"bound": ACC_BOUND[dtype], "north_star_bound": (1e-5 if dtype == "f32" else 1e-13) * float(n) ** 0.5}
+    xg = torch.Generator().manual_seed(1234)
+    X = (torch.randint(0, 2, (n, 8), generator=xg).double() * 2 - 1).to(ctx.dev)
+    with torch.cuda.stream(grid.stream):
+        ABX = dist_matvec(ctx, A, dist_matvec(ctx, B, X))
+        c0X = dist_matvec(ctx, Cm, X)
+        rows = c0_rows = None
+        if world == 1:
+            rows = torch.randperm(n, device=ctx.dev, generator=gen)[:64]
+            c0_rows = Cm.Matrix()[rows].double()
+    grid.sync()
+    step()  # counts as the first warm-up step
+    grid.sync()
+    with torch.cuda.stream(grid.stream):
+        acc["checksum_rel_err"] = rel_err(torch, dist_matvec(ctx, Cm, X), alpha * ABX + beta * c0X)
+        if world == 1:
+            want = alpha * (A.Matrix()[rows].double() @ B.Matrix().double()) + beta * c0_rows
+            acc["sampled_rows_rel_err"] = rel_err(torch, Cm.Matrix()[rows].double(), want)
+            del want
+    grid.sync()
+    worst = max(acc["checksum_rel_err"], acc.get("sampled_rows_rel_err", 0.0))
+    acc["ok"] = bool(ctx.max_over_ranks(worst) <= acc["bound"])
+
+    for _ in range(max(warmup - 1, 0)):
+        step()
+    ctx.barrier()
+    sampler = ClockSampler(local)
+    if rank == 0 and main:
+        sampler.start()
+    lib.elb200_gemm_profile(1)
+    launches0 = lib.elb200_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ctx.barrier()
+    e0.record(grid.stream)
+    for _ in range(steps):
+        step()
+    e1.record(grid.stream)
+    ctx.barrier()
+    ms = e0.elapsed_time(e1) / steps
+    launches = lib.elb200_launch_count() - launches0
+    lib.elb200_gemm_profile(0)
+    k_ms, k_flop, k_n = C.c_double(), C.c_double(), C.c_int()
+    lib.elb200_gemm_profile_collect(C.byref(k_ms), C.byref(k_flop), C.byref(k_n))
+    clocks = sampler.stop() if (rank == 0 and main) else None
+    ms = ctx.max_over_ranks(ms)
+    flops = 2.0 * n ** 3
+    value = flops / (ms * 1e-3) / 1e12
+
+    # ---- e2e: the same El::Gemm through the host-operand entry point (el.GemmHost -> elb200_dist_gemm_host_*):
+    # A, B, C live in pinned HOST memory, every step uploads them, multiplies and downloads C inside the timed region.
+    e2e = None
+    e2e_error = None
+    if not args.no_e2e and e2e_steps > 0:
+        lh, lw = A.LocalHeight(), A.LocalWidth()
+        loc_bytes = max(lh, 1) * max(lw, 1) * esz
+        pool = ctx.host_pool(3 * loc_bytes)
+
+        def host_view(i):
+            return pool[i * loc_bytes:(i + 1) * loc_bytes].view(tdt).view(max(lw, 1), max(lh, 1)).t()  # column-major, ld = local height
+        hA, hB, hC = host_view(0), host_view(1), host_view(2)
+        with torch.cuda.stream(grid.stream):
+            for h, M in ((hA, A), (hB, B), (hC, Cm)):
+                if lh and lw:
+                    h.t().copy_(M.Matrix().t(), non_blocking=True)  # both sides one row per local column
+            cbX = dist_matvec(ctx, Cm, X)  # checksum of the C the host call starts from
+        grid.sync()
+
+        def e2e_step():
+            el.GemmHost(grid, el.NORMAL, el.NORMAL, n, n, n, alpha, hA, max(lh, 1), hB, max(lh, 1), beta, hC, max(lh, 1))
+
+        # first call doubles as the check of the streamed path: its result goes back up into Cm and through the same
+        # checksum (the two paths accumulate k in different chunkings, so they agree to the bound, not bit for bit)
+        e2e_step()
+        with torch.cuda.stream(grid.stream):
+            if lh and lw:
+                Cm.Matrix().t().copy_(hC.t(), non_blocking=True)
+            err = rel_err(torch, dist_matvec(ctx, Cm, X), alpha * ABX + beta * cbX)
+        grid.sync()
+        acc["e2e_checksum_rel_err"] = err
+        if ctx.max_over_ranks(err) > acc["bound"]:
+            # a mismatch voids the e2e number only: the device-resident line stands, the failure is reported in the line
+            e2e_error = f"GemmHost result fails the checksum at n={n} (rank {rank}: rel err {err:.3e}, bound {acc['bound']:.1e})"
+            print("bench.py: " + e2e_error, file=sys.stderr)
+            acc["ok"] = False
+        else:
+            ctx.barrier()
+            e0.record(grid.stream)
+            for _ in range(e2e_steps):
+                e2e_step()
+            e1.record(grid.stream)
+            ctx.barrier()
+            t = ctx.max_over_ranks(e0.elapsed_time(e1) / e2e_steps)
+            loc = lh * lw * esz
+            tot = torch.tensor([float(loc)], device=ctx.dev, dtype=torch.float64)
+            if world > 1:
+                dist.all_reduce(tot)
+            e2e = {"value": flops / (t * 1e-3) / 1e12, "unit": UNIT, "ms_per_step": t,
+                   "h2d_bytes_per_step": int(3 * tot.item()), "d2h_bytes_per_step": int(tot.item()), "steps": e2e_steps}
+    for M in (A, B, Cm):
+        M.destroy()
+    del A, B, Cm, X, ABX, c0X
+    torch.cuda.empty_cache()
+    if rank != 0:
+        return None
+    ach = (k_flop.value / (k_ms.value * 1e-3) / 1e12) if k_ms.value > 0 else None
+    rec = {"value": value, "unit": UNIT, "n": n, "dtype": dtype, "grid": f"{grid.Height()}x{grid.Width()}", "steps": steps,
+           "warmup": warmup, "ms_per_step": ms, "per_gpu_tflops": value / world, "accuracy": acc, "e2e": e2e,
+           "gpu_launches": int(launches),
+           "_kernel": {"achieved": ach, "launches_timed": k_n.value, "kernel_ms_per_step": k_ms.value / steps,
+                       "kernel_share_of_step": (k_ms.value / steps) / ms},
+           "_clocks": clocks}
+    if e2e_error:
+        rec["e2e_error"] = e2e_error
+    return rec
+
+
+def library_peaks(ctx: Ctx) -> dict:
+    """cuBLAS on this very GPU, through torch.matmul, as PRACTICAL roofline denominators (library calls used as a
+    yardstick, never on the product path): Dgemm for the fp64 kernel, TF32 GemmEx / 3 for the 3xTF32 kernel."""
+    torch = ctx.torch
+    out = {}
+    n = 8192
+    for name, dt, tf32 in (("cublas_dgemm_tflops", torch.float64, False), ("cublas_tf32_tflops", torch.float32, True)):
+        old = torch.backends.cuda.matmul.allow_tf32
+        torch.backends.cuda.matmul.allow_tf32 = tf32
+        try:
+            a = torch.rand((n, n), device=ctx.dev, dtype=dt) - 0.5
+            b = torch.rand((n, n), device=ctx.dev, dtype=dt) - 0.5
+            for _ in range(2):
+                a @ b
+            reps = 4 if dt == torch.float64 else 20
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(reps):
+                a @ b
+            e1.record()
+            torch.cuda.synchronize()
+            out[name] = 2.0 * n ** 3 * reps / (e0.elapsed_time(e1) * 1e-3) / 1e12
+            del a, b
+        finally:
+            torch.backends.cuda.matmul.allow_tf32 = old
+    out["how"] = f"torch.matmul n={n} back to back on this GPU in this run (fp64 -> cublasDgemm; fp32 with allow_tf32 -> 1xTF32 GemmEx, lossy)"
+    torch.cuda.empty_cache()
+    return out
+
+
+def roofline_of(rec: dict, dtype: str, peaks: dict, libpk: dict, n_gpus: int) -> dict:
+    k = rec["_kernel"]
+    ach = k["achieved"]
+    if dtype == "f32":
+        # 3xTF32: three tf32 UMMAs per useful MAC, tf32 rate = bf16 rate / 2  =>  bf16 / 6
+        peak = peaks["bf16_sustained"] / 6.0
+        basis = (f"{peaks['source']}: sustained bf16 {peaks['bf16_sustained']} TF/s / 6 (tf32 = bf16/2, 3 UMMAs per MAC); "
+                 f"burst-derived {peaks['bf16'] / 6.0:.1f}")
+        alt = {"bf16_burst_over_6": peaks["bf16"] / 6.0}
+        if libpk.get("cublas_tf32_tflops"):
+            alt["cublas_tf32_over_3"] = libpk["cublas_tf32_tflops"] / 3.0
+        kernel = "gemm_f32_3xtf32_kernel<cta_group::2>"
+    else:
+        peak = 40.0
+        basis = ("B200 FP64 (DMMA) nominal 40 TF/s — MEASURED_PEAKS.json holds no fp64 figure, so this is the fallback; the practical "
+                 "denominators are in peak_alt: ncu's pipe ceiling 128 flop/clk/SM x 148 SMs x 1.965 GHz = 37.2, and cublasDgemm "
+                 "measured in this run")
+        alt = {"ncu_pipe_ceiling_128flop_clk_sm": 148 * 128 * 1.965e9 / 1e12}
+        if libpk.get("cublas_dgemm_tflops"):
+            alt["cublas_dgemm"] = libpk["cublas_dgemm_tflops"]
+        kernel = "gemm_f64 (DMMA m8n8k4)"
+    traffic = None
+    for rnd in ("r02", "r01"):
+        tp = os.path.join(ROOT, "profiles", f"{rnd}_ncu_gemm_{dtype}_traffic.json")
+        if os.path.exists(tp):
+            with open(tp) as f:
+                tj = json.load(f)
+            # one ncu --set full capture of this kernel at this size (per launch, like `achieved`)
+            if tj.get("n") == rec["n"] and n_gpus == 1:
+                traffic = tj.get("dram_bytes_per_launch")
+                break
+    return {"bound": "tensor", "kernel": kernel, "achieved": ach, "peak": peak, "unit": "TFLOP/s",
+            "frac": (ach / peak) if ach else None, "traffic": traffic,
+            "frac_alt": {kk: (ach / vv if ach and vv else None) for kk, vv in alt.items()}, "peak_alt": alt,
+            "launches_timed": k["launches_timed"], "kernel_ms_per_step": k["kernel_ms_per_step"],
+            "kernel_share_of_step": k["kernel_share_of_step"], "peak_basis": basis}
+
+
+def parity_pass(ctx: Ctx) -> dict:
+    """Oracle parity of the library on THIS grid, outside every timed region: tests/dist_cases.run_all — the function
+    the -m gpu tests and tests/dist_worker.py run — compares each rank's local results with the oracle's virtual ranks
+    (redistributions bit for bit, GEMMs within the north-star bound). Every rank must pass."""
+    torch, dist = ctx.torch, ctx.dist
+    t0 = time.perf_counter()
+    out, err = {}, None
+    try:
+        from tests import dist_cases as dc
+        out = dc.run_all(ctx.grid)
+        ctx.grid.sync()
+    except Exception as ex:  # noqa: BLE001 — the failure is reported in the line and through the exit code
+        import traceback
+        err = f"rank {ctx.rank}: {type(ex).__name__}: {ex}"
+        traceback.print_exc()
+    bad = ctx.max_over_ranks(0.0 if err is None else 1.0)
+    cases = int(sum(v for v in out.values() if isinstance(v, int)))
+    rec = {"ok": bad == 0.0, "grid": f"{ctx.grid.Height()}x{ctx.grid.Width()}", "ranks": ctx.world, "cases": cases, "detail": out,
+           "checker": "oracle/ (numpy restatement pinned to the reference's own multi-rank outputs, tests/golden) via tests/dist_cases.run_all",
+           "seconds": round(time.perf_counter() - t0, 1)}
+    if err:
+        rec["error"] = err
+    return rec
+
+
 def run_ours(args) -> int:
-    import numpy as np
     import torch
     import torch.distributed as dist
 
@@ -215,15 +545,14 @@ def run_ours(args) -> int:
     from elemental_b200 import el
     from elemental_b200._lib import lib
 
-    n_gpus = world
-    n = workload_n(n_gpus, args.n)
-    tdt = torch.float32 if args.dtype == "f32" else torch.float64
-    esz = 4 if args.dtype == "f32" else 8
     grid = el.Grid(device=local)
+    line, ok = None, True
     try:
         # everything that touches the grid's streams (DistMatrices, pinned host tensors) lives inside
         # _measure and is released before the grid is closed
-        line = _measure(args, grid, el, lib, torch, dist, world, rank, local, n_gpus, n, tdt, esz)
+        ctx = Ctx(args, grid, el, lib, torch, dist, world, rank, local)
+        line, ok = _measure(ctx)
+        ctx.pool = None
     finally:
         import gc
         gc.collect()
@@ -234,155 +563,68 @@ def run_ours(args) -> int:
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
-    return 0
+    return 0 if ok else 3
 
 
-def _measure(args, grid, el, lib, torch, dist, world, rank, local, n_gpus, n, tdt, esz):
-    import numpy as np  # noqa: F401
-    A = el.DistMatrix(grid, el.MC, el.MR, tdt).Resize(n, n)
-    B = el.DistMatrix(grid, el.MC, el.MR, tdt).Resize(n, n)
-    Cm = el.DistMatrix(grid, el.MC, el.MR, tdt).Resize(n, n)
-    gen = torch.Generator(device=f"cuda:{local}").manual_seed(21 + rank)
-    with torch.cuda.stream(grid.stream):
-        for M in (A, B, Cm):
-            v = M.Matrix()
-            v.copy_((torch.rand(v.shape, device=v.device, dtype=tdt, generator=gen) - 0.5) * 0.2)
-    grid.sync()
+def _measure(ctx: Ctx):
+    args, world, rank = ctx.args, ctx.world, ctx.rank
+    n_gpus = world
+    n = workload_n(n_gpus, args.n)
+    other = "f64" if args.dtype == "f32" else "f32"
+    e2e_steps = max(1, min(args.steps, 3))
+    main = measure_gemm(ctx, args.dtype, n, args.steps, args.warmup, e2e_steps, main=True)
+    sub_steps = max(1, args.sub_steps)
+    strong = sub = None
+    if not args.no_sub and not args.n:
+        if n != FIXED_N:
+            strong = measure_gemm(ctx, args.dtype, FIXED_N, max(sub_steps, 5), 3, 0, main=False)
+        sub = measure_gemm(ctx, other, FIXED_N, sub_steps, 3, min(2, sub_steps), main=False)
+    parity = None
+    if not args.no_parity:
+        parity = parity_pass(ctx)
+    libpk = library_peaks(ctx) if rank == 0 else {}
+    ok = True
+    for rec in (main, strong, sub):
+        if rec is not None and not rec["accuracy"]["ok"]:
+            ok = False
+    if parity is not None and not parity["ok"]:
+        ok = False
+    ok = ctx.max_over_ranks(0.0 if ok else 1.0) == 0.0
+    if rank != 0:
+        return None, ok
+    peaks = load_peaks()
+    cpu = None
+    if not args.no_cpu and n_gpus == 1:
+        n_s = pick_cpu_sample(args.dtype, args.n)
+        v, info = cpu_reference_rate(args.dtype, n_s)
+        cpu = {"value": v, "unit": UNIT, **info}
+    esz = 4 if args.dtype == "f32" else 8
+    cfg = make_config(args, n_gpus, n)
+    detail = {"grid": main["grid"],
+                "l2": (f"inputs {3 * n * n * esz / n_gpus / 2**20:.0f} MiB per GPU > 126 MB L2 (no flush needed)" if 3 * n * n * esz / n_gpus > 2 * 126e6
+                       else f"inputs {3 * n * n * esz / n_gpus / 2**20:.0f} MiB per GPU fit the 126 MB L2: --n diagnostic line, not a bench value"),
+                "panel_k": "full k on 1x1; ELB200_PANEL_K (default 4096 fp32 / 2048 fp64) otherwise",
+                "per_gpu_tflops": main["per_gpu_tflops"]}
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
+    def public(rec, dtype):
+        if rec is None:
+            return None
+        out = {k: v for k, v in rec.items() if not k.startswith("_")}
+        out["roofline"] = roofline_of(rec, dtype, peaks, libpk, n_gpus)
+        return out
 
-    def step():
-        el.Gemm(el.NORMAL, el.NORMAL, 0.5, A, B, -0.5, Cm, args.alg)
-
-    for _ in range(max(args.warmup, 0)):
-        step()
-    barrier()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-    lib.elb200_gemm_profile(1)
-    launches0 = lib.elb200_launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    e0.record(grid.stream)
-    for _ in range(args.steps):
-        step()
-    e1.record(grid.stream)
-    barrier()
-    ms = e0.elapsed_time(e1) / args.steps
-    launches = lib.elb200_launch_count() - launches0
-    lib.elb200_gemm_profile(0)
-    k_ms, k_flop, k_n = C.c_double(), C.c_double(), C.c_int()
-    lib.elb200_gemm_profile_collect(C.byref(k_ms), C.byref(k_flop), C.byref(k_n))
-    clocks = sampler.stop() if rank == 0 else None
-    t = torch.tensor([ms], device=f"cuda:{local}", dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
-    flops = 2.0 * n ** 3
-    value = flops / (ms * 1e-3) / 1e12
-
-    # ---- e2e: the same El::Gemm through the host-operand entry point (el.GemmHost ->
-    # elb200_dist_gemm_host_*): A, B, C live in pinned HOST memory, every step uploads them,
-    # multiplies and downloads C inside the timed region.
-    e2e = None
-    e2e_error = None
-    if not args.no_e2e:
-        def host_like(M):
-            v = M.Matrix()
-            h = torch.empty((v.shape[1], v.shape[0]), dtype=tdt).pin_memory().t()  # column-major, ld = local height
-            with torch.cuda.stream(grid.stream):
-                h.copy_(v, non_blocking=True)
-            return h
-        hA, hB, hC0 = host_like(A), host_like(B), host_like(Cm)
-        grid.sync()
-        hC = torch.empty((hC0.shape[1], hC0.shape[0]), dtype=tdt).pin_memory().t()
-        hC.copy_(hC0)
-        e2e_steps = max(1, min(args.steps, 3))
-
-        def e2e_step():
-            el.GemmHost(grid, el.NORMAL, el.NORMAL, n, n, n, 0.5, hA, max(hA.shape[0], 1), hB, max(hB.shape[0], 1),
-                        -0.5, hC, max(hC.shape[0], 1))
-
-        # first call doubles as a check of the streamed path against the device-resident one
-        e2e_step()
-        step()  # Cm (device) started from the same C0: both now hold 0.5*A*B - 0.5*C0
-        grid.sync()
-        dev_c = Cm.Matrix().to("cpu")
-        num = float(torch.linalg.norm((dev_c - hC).double()))
-        den = float(torch.linalg.norm(dev_c.double()))
-        # the two paths accumulate k in different chunkings (one full-k GEMM per block here, k-panels
-        # there), so they agree to the north-star bound, not bit for bit
-        bound = (1e-5 if args.dtype == "f32" else 1e-13) * float(n) ** 0.5
-        # a mismatch voids the e2e number only: the device-resident line above stands, the failure is reported in
-        # the line ("e2e": null, "e2e_error") and on stderr; every rank takes the same branch (flag reduced over ranks)
-        rel = num / max(den, 1e-30)
-        bad = torch.tensor([0.0 if num <= bound * max(den, 1e-30) else 1.0], device=f"cuda:{local}", dtype=torch.float64)
-        if world > 1:
-            dist.all_reduce(bad, op=dist.ReduceOp.MAX)
-        if float(bad.item()) != 0.0:
-            e2e_error = f"GemmHost result differs from the device-resident Gemm on some rank (rank {rank}: rel err {rel:.3e}, bound {bound:.3e})"
-            print("bench.py: " + e2e_error, file=sys.stderr)
-        else:
-            e2e_error = None
-            barrier()
-            e0.record(grid.stream)
-            for _ in range(e2e_steps):
-                e2e_step()
-            e1.record(grid.stream)
-            barrier()
-            t = torch.tensor([e0.elapsed_time(e1) / e2e_steps], device=f"cuda:{local}", dtype=torch.float64)
-            if world > 1:
-                dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            loc = A.LocalHeight() * A.LocalWidth() * esz
-            e2e = {"value": flops / (float(t.item()) * 1e-3) / 1e12, "unit": UNIT, "ms_per_step": float(t.item()),
-                   "h2d_bytes_per_step": 3 * loc * n_gpus, "d2h_bytes_per_step": loc * n_gpus, "steps": e2e_steps}
-
-    if rank == 0:
-        peaks = load_peaks()
-        ach = (k_flop.value / (k_ms.value * 1e-3) / 1e12) if k_ms.value > 0 else None
-        if args.dtype == "f32":
-            # 3xTF32: three tf32 UMMAs per useful MAC, tf32 rate = bf16 rate / 2  =>  bf16 / 6
-            peak = peaks["bf16_sustained"] / 6.0
-            basis = f"{peaks['source']}: sustained bf16 {peaks['bf16_sustained']} TF/s / 6 (tf32 = bf16/2, 3 UMMAs per MAC); burst-derived {peaks['bf16'] / 6.0:.1f}"
-        else:
-            peak = 40.0
-            basis = ("B200 FP64 (DMMA == FMA rate) nominal 40 TF/s; no measured fp64 peak in MEASURED_PEAKS.json. ncu reports the pipe's "
-                     "peak_sustained as 128 flop/clk/SM = 37.2 TF/s at 1965 MHz; cublasDgemm on this pool: 35.9 TF/s (profiles/)")
-        traffic = None
-        tp = os.path.join(ROOT, "profiles", f"r01_ncu_gemm_{args.dtype}_traffic.json")
-        if os.path.exists(tp):
-            with open(tp) as f:
-                tj = json.load(f)
-            # one ncu --set full capture of this kernel at this size (per launch, like `achieved`)
-            if tj.get("n") == n and n_gpus == 1:
-                traffic = tj.get("dram_bytes_per_launch")
-        roof = {"bound": "tensor", "kernel": "gemm_f32_3xtf32_kernel<cta_group::2>" if args.dtype == "f32" else "gemm_f64_dmma_kernel",
-                "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": (ach / peak) if ach else None, "traffic": traffic,
-                "launches_timed": k_n.value, "kernel_ms_per_step": k_ms.value / args.steps, "kernel_share_of_step": (k_ms.value / args.steps) / ms,
-                "peak_basis": basis}
-        cpu = None
-        if not args.no_cpu and n_gpus == 1:
-            n_s = pick_cpu_sample(args.dtype, args.n)
-            v, info = cpu_reference_rate(args.dtype, n_s)
-            cpu = {"value": v, "unit": UNIT, **info}
-        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": args.dtype,
-                "data": "synthetic",
-                "config": {"workload": f"El::Gemm {args.dtype} {['DEFAULT','SUMMA_A_MS','SUMMA_A','SUMMA_B_MS','SUMMA_B','SUMMA_C_MS','SUMMA_C','SUMMA_DOT','CANNON'][args.alg]} n={n} (NN, alpha=0.5, beta=-0.5), [MC,MR] on a {grid.Height()}x{grid.Width()} grid",
-                           "inputs": "Uniform(-0.1,0.1), resident in HBM", "l2": (f"inputs {3 * n * n * esz / n_gpus / 2**20:.0f} MiB per GPU > 126 MB L2 (no flush needed)" if 3 * n * n * esz / n_gpus > 2 * 126e6
-                                  else f"inputs {3 * n * n * esz / n_gpus / 2**20:.0f} MiB per GPU fit the 126 MB L2: --n diagnostic line, not a bench value"),
-                           "panel_k": "full k on 1x1; ELB200_PANEL_K (default 4096 fp32 / 2048 fp64) otherwise",
-                           "per_gpu_tflops": value / n_gpus},
-                "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
-        if e2e_error:
-            line["e2e_error"] = e2e_error
-        return line
-    return None
-
+    line = {"metric": METRIC, "value": main["value"], "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": main["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": args.dtype,
+            "data": "synthetic", "config": cfg, "run_detail": detail,
+            "roofline": roofline_of(main, args.dtype, peaks, libpk, n_gpus), "cpu_baseline": cpu, "e2e": main["e2e"],
+            "gpu_launches": main["gpu_launches"], "clocks": main["_clocks"],
+            "accuracy": main["accuracy"],
+            "strong_n32768": public(strong, args.dtype) if strong is not None else ("same as the headline (N = 1)" if n == FIXED_N else None),
+            ("fp64" if other == "f64" else "fp32"): public(sub, other),
+            "parity": parity, "library_peaks": libpk, "ok": ok}
+    if main.get("e2e_error"):
+        line["e2e_error"] = main["e2e_error"]
+    return line, ok
 
 def main() -> int:
     args = parse_args()

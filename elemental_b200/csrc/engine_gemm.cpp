@@ -217,7 +217,10 @@ void SummaC(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, T
         static const bool direct_on = [] { const char* e = std::getenv("ELB200_DIRECT"); return !(e && std::atoi(e) == 0); }();
         // the two panels live in arena slots: shrink the panel width until they fit
         const int64_t vec = 16 / int64_t(sizeof(T)), nbk = Grid::Blocksize();
-        const int64_t per_k = std::max(C.lh() + vec, C.lw()) * int64_t(sizeof(T));
+        // sized from the LARGEST local extents on the grid, not this rank's: ragged matrices give ranks local
+        // heights / widths that differ by one, and every rank must derive the same Wd and take the same branch
+        // (the panels are collectives: a different kb or path on one rank would hang its peers)
+        const int64_t per_k = std::max(MaxLength(d.m, g.shape.r) + vec, MaxLength(d.n, g.shape.c)) * int64_t(sizeof(T));
         int64_t Wd = std::min<int64_t>(W, (int64_t(g.arena->slot_bytes()) / per_k - vec) / nbk * nbk);
         if (direct_on && Wd >= std::max<int64_t>(nbk, 512) && A.spec.col_align == C.spec.col_align &&
             B.spec.row_align == C.spec.row_align) {

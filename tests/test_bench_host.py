@@ -14,12 +14,19 @@ import bench  # noqa: E402
 
 
 def test_weak_scaling_sizes():
-    # flops per GPU constant: n = 16384 * N^(1/3) rounded to 512; N = 1 is BASELINE C2, N = 8 the C3 size
-    assert [bench.workload_n(n) for n in (1, 2, 4, 8)] == [16384, 20480, 26112, 32768]
+    # flops per GPU constant: n = 32768 * N^(1/3) rounded to 512; N = 1 is the size the metric is quoted on
+    assert [bench.workload_n(n) for n in (1, 2, 4, 8)] == [32768, 41472, 52224, 65536]
     assert bench.workload_n(8, 2000) == 2000
     for n_gpus in (2, 4, 8):
         per_gpu = bench.workload_n(n_gpus) ** 3 / n_gpus
-        assert abs(per_gpu / 16384 ** 3 - 1.0) < 0.03
+        assert abs(per_gpu / 32768 ** 3 - 1.0) < 0.03
+
+
+def test_both_arms_name_the_same_config():
+    import argparse
+    a = argparse.Namespace(dtype="f32", alg=6)
+    assert bench.make_config(a, 4, 52224) == bench.make_config(a, 4, 52224)
+    assert "n=52224" in bench.make_config(a, 4, 52224)["workload"]
 
 
 def test_clock_sampler_parses_reasons():

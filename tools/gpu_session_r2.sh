@@ -1,0 +1,40 @@
+#!/usr/bin/env bash
+# Round-2 GPU sessions. Everything lands in gpurun_out/<tag>/ (copy what should be judged into profiles/).
+# Plain runs first; anything under ncu comes after the same command has exited 0 without it.
+#   1 GPU : gpurun --timeout 1500 -- 'bash tools/gpu_session_r2.sh 1a'
+#   N GPUs: gpurun --gpus N --timeout 900 -- 'bash tools/gpu_session_r2.sh multi N'
+set -u
+STAGE=${1:-1a}
+N=${2:-1}
+OUT=gpurun_out/$STAGE${2:+_$2}
+mkdir -p $OUT
+log() { echo "$*" | tee -a $OUT/session.log; }
+run() { log "=== $*"; "$@" >> $OUT/session.log 2>&1; log "exit $?"; }
+TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511"
+
+case $STAGE in
+1a)
+  # parity suite (incl. tests/test_zz_no_alloc.py, collected last), the new bench line, fp64 kernel variants
+  log "=== pytest -m gpu"; timeout 1200 python -m pytest tests -m gpu -x -q > $OUT/pytest_gpu.log 2>&1; log "exit $?"; tail -3 $OUT/pytest_gpu.log | tee -a $OUT/session.log
+  log "=== pytest no_alloc alone (fresh process)"; timeout 300 python -m pytest tests/test_zz_no_alloc.py -m gpu -x -q > $OUT/pytest_no_alloc_alone.log 2>&1; log "exit $?"; tail -2 $OUT/pytest_no_alloc_alone.log | tee -a $OUT/session.log
+  log "=== bench.py"; timeout 900 python bench.py --steps 10 --warmup 5 > $OUT/bench_1gpu.json 2> $OUT/bench_1gpu.err; log "exit $?"
+  for v in "X=0" "ELB200_F64_WS=1" "ELB200_F64_TMA=1"; do
+    log "=== f64 variant $v"
+    env $v timeout 120 tools/gemm_check correctness f64 >> $OUT/f64_variants.log 2>&1; log "correctness exit $?"
+    env $v timeout 120 tools/native_bench f64 8192 >> $OUT/f64_variants.log 2>&1; log "native_bench exit $?"
+    env $v timeout 300 tools/gemm_check perf f64 16384 >> $OUT/f64_variants.log 2>&1; log "perf exit $?"
+  done
+  # one full ncu capture: the warp-specialised fp64 kernel and cublasDgemm (its launch configuration is the yardstick)
+  ELB200_F64_WS=1 timeout 600 ncu --set full --import-source on --clock-control none -k regex:'gemm_f64|dgemm|gemm_f64f64|xmma|cutlass' -c 4 \
+      -o $OUT/ncu_f64_ws tools/native_bench f64 8192 > $OUT/ncu_f64_ws.log 2>&1; log "ncu f64 exit $?"
+  timeout 600 ncu --set full --clock-control none -c 12 -o $OUT/ncu_f64_all tools/native_bench f64 4096 > $OUT/ncu_f64_all.log 2>&1; log "ncu f64 all exit $?"
+  ;;
+multi)
+  run timeout 900 $TR tests/dist_worker.py
+  run timeout 900 $TR tests/dist_worker.py --level3
+  log "=== bench.py N=$N"; timeout 900 $TR bench.py --gpus $N --steps 10 --warmup 5 > $OUT/bench_${N}gpu.json 2> $OUT/bench_${N}gpu.err; log "exit $?"
+  ;;
+*)
+  echo "unknown stage $STAGE"; exit 2;;
+esac
+tail -5 $OUT/session.log
