@@ -88,6 +88,7 @@ SIGNATURES = {
     "elb200_gemm_f32": (ci, [ci, ci, i64, i64, i64, f32, vp, i64, vp, i64, f32, vp, i64, vp]),
     "elb200_gemm_f64": (ci, [ci, ci, i64, i64, i64, f64, vp, i64, vp, i64, f64, vp, i64, vp]),
     "elb200_gemm_f32_ex": (ci, [ci, ci, i64, i64, i64, f32, vp, i64, vp, i64, f32, vp, i64, ci, vp]),
+    "elb200_gemm_f32_noalloc": (ci, [ci, ci, i64, i64, i64, f32, vp, i64, vp, i64, f32, vp, i64, vp]),
     "elb200_copy2d_f32": (ci, [i64, i64, vp, i64, i64, vp, i64, i64, vp]),
     "elb200_copy2d_f64": (ci, [i64, i64, vp, i64, i64, vp, i64, i64, vp]),
     "elb200_transpose_f32": (ci, [i64, i64, vp, i64, vp, i64, vp]),

@@ -3,6 +3,7 @@
 #include <cstdio>
 #include <cstring>
 #include <atomic>
+#include <mutex>
 
 #include "elb200_internal.h"
 
@@ -54,6 +55,31 @@ int check_gemm_args(int transA, int transB, int64_t m, int64_t n, int64_t k, con
     if (m > 0 && n > 0 && k > 0 && (!A || !B)) return ELB200_ERR_ARG;
     if (m > INT32_MAX || n > INT32_MAX || k > INT32_MAX) return ELB200_ERR_ARG;
     return ELB200_OK;
+}
+
+// ---- staging for elb200_gemm_f32_noalloc ----------------------------------------------------------
+// Two regions of ELB200_NOALLOC_MAX_ELEMS floats (A, then B): 2 x 16 MiB of device memory that every GPU
+// which loads this library holds until the process exits. Nothing in it has to start at zero: a staged
+// operand is rewritten in full by the copy that precedes the GEMM, and the pad rows between an operand's
+// height and its 4-element-rounded pitch lie outside the tensor map's extent, so TMA never reads them.
+static __device__ __align__(256) float g_noalloc_scratch[2 * size_t(ELB200_NOALLOC_MAX_ELEMS)];
+
+// Device address of the array on the CURRENT device, looked up once per device (the symbol lives in every
+// context that loads the module, at a different address each). nullptr + last_error on failure.
+float* noalloc_scratch_base() {
+    static std::mutex mu;
+    static float* base[64] = {nullptr};
+    int dev = -1;
+    if (check_cuda(cudaGetDevice(&dev), "cudaGetDevice")) return nullptr;
+    if (dev < 0 || dev >= 64) { set_last_error("elb200_gemm_f32_noalloc", "device index out of range"); return nullptr; }
+    std::lock_guard<std::mutex> lock(mu);
+    if (!base[dev]) {
+        void* p = nullptr;
+        if (check_cuda(cudaGetSymbolAddress(&p, g_noalloc_scratch), "cudaGetSymbolAddress(g_noalloc_scratch)"))
+            return nullptr;
+        base[dev] = static_cast<float*>(p);
+    }
+    return base[dev];
 }
 
 }  // namespace
@@ -128,6 +154,54 @@ int elb200_gemm_f32_ex(int transA, int transB, int64_t m, int64_t n, int64_t k, 
                          beta, C, ldc, cta_group, s);
     if (st == ELB200_ERR_CUDA) set_last_error("gemm_f32 launch", cudaGetErrorString(cudaGetLastError()));
     release();
+    return st;
+}
+
+// Allocation-free twin of elb200_gemm_f32_ex (no counterpart in the reference; see include/elb200.h).
+// Misaligned operands are staged into the file-scope device array above instead of cudaMallocAsync
+// temporaries. In host code `g_noalloc_scratch` is only a stand-in for the device symbol, so its device
+// address is resolved once per device with cudaGetSymbolAddress and that pointer is what the kernels get.
+int elb200_gemm_f32_noalloc(int transA, int transB, int64_t m, int64_t n, int64_t k, float alpha,
+                            const float* A, int64_t lda, const float* B, int64_t ldb, float beta,
+                            float* C, int64_t ldc, void* stream) {
+    int st = check_gemm_args(transA, transB, m, n, k, A, lda, B, ldb, C, ldc);
+    if (st != ELB200_OK) return st;
+    if (m == 0 || n == 0) return ELB200_OK;
+    if (k == 0 || alpha == 0.f) return elb200_scale2d_f32(m, n, beta, C, ldc, stream);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const bool a_ok = (reinterpret_cast<uintptr_t>(A) & 15u) == 0 && (lda & 3) == 0;
+    const bool b_ok = (reinterpret_cast<uintptr_t>(B) & 15u) == 0 && (ldb & 3) == 0;
+    const float* Ause = A; const float* Buse = B;
+    int64_t lda_use = lda, ldb_use = ldb;
+    if (!a_ok || !b_ok) {
+        const int64_t a_rows = transA ? k : m, a_cols = transA ? m : k;
+        const int64_t b_rows = transB ? n : k, b_cols = transB ? k : n;
+        const int64_t a_ld = (a_rows + 3) & ~int64_t(3), b_ld = (b_rows + 3) & ~int64_t(3);
+        // sizes are checked before anything is enqueued: a rejected call leaves the stream untouched
+        if ((!a_ok && a_ld * a_cols > int64_t(ELB200_NOALLOC_MAX_ELEMS)) ||
+            (!b_ok && b_ld * b_cols > int64_t(ELB200_NOALLOC_MAX_ELEMS))) {
+            set_last_error("elb200_gemm_f32_noalloc",
+                           "a misaligned operand needs more staging than ELB200_NOALLOC_MAX_ELEMS floats; "
+                           "align it to 16 bytes (base and leading dimension) or use elb200_gemm_f32");
+            return ELB200_ERR_ARG;
+        }
+        float* scratch = noalloc_scratch_base();
+        if (!scratch) return ELB200_ERR_CUDA;
+        if (!a_ok) {
+            st = elb200_copy2d_f32(a_rows, a_cols, A, 1, lda, scratch, 1, a_ld, stream);
+            if (st != ELB200_OK) return st;
+            Ause = scratch; lda_use = a_ld;
+        }
+        if (!b_ok) {
+            float* sb = scratch + ELB200_NOALLOC_MAX_ELEMS;
+            st = elb200_copy2d_f32(b_rows, b_cols, B, 1, ldb, sb, 1, b_ld, stream);
+            if (st != ELB200_OK) return st;
+            Buse = sb; ldb_use = b_ld;
+        }
+    }
+    st = gemm_f32_tensor(transA != 0, transB != 0, m, n, k, alpha, Ause, lda_use, Buse, ldb_use,
+                         beta, C, ldc, 0, s);
+    if (st == ELB200_ERR_CUDA) set_last_error("gemm_f32 launch", cudaGetErrorString(cudaGetLastError()));
     return st;
 }
 

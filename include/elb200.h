@@ -65,6 +65,22 @@ int elb200_gemm_f64(int transA, int transB, int64_t m, int64_t n, int64_t k, dou
 int elb200_gemm_f32_ex(int transA, int transB, int64_t m, int64_t n, int64_t k, float alpha,
                        const float* A, int64_t lda, const float* B, int64_t ldb, float beta,
                        float* C, int64_t ldc, int cta_group, void* stream);
+/* Allocation-free variant of elb200_gemm_f32. It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it). Same arguments, same results as
+ * elb200_gemm_f32. Operands whose base or leading dimension is not 16-byte aligned (what the TMA-fed
+ * kernel needs) are staged into a fixed device array owned by the library instead of stream-ordered
+ * temporaries: the call makes no cudaMalloc* / cudaFree* and no allocating library call.
+ * Limit: a misaligned operand may occupy at most ELB200_NOALLOC_MAX_ELEMS floats after its leading
+ * dimension is rounded up to 4 (16 MiB per operand; 32 MiB of device memory per GPU for the life of the
+ * process); larger ones are rejected with ELB200_ERR_ARG before anything is enqueued. Aligned operands
+ * of any size pass straight through. All calls share the one array: calls that may overlap on the GPU
+ * (different streams with no ordering between them) race on it — keep them on one stream or order them
+ * with events. */
+#define ELB200_NOALLOC_MAX_ELEMS (4 * 1024 * 1024)
+int elb200_gemm_f32_noalloc(int transA, int transB, int64_t m, int64_t n, int64_t k, float alpha,
+                            const float* A, int64_t lda, const float* B, int64_t ldb, float beta,
+                            float* C, int64_t ldc, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * BLAS-1 entrywise kernels (HBM-bound, 128-bit vectorised where strides allow).

@@ -355,6 +355,10 @@ int elb200_gemm_f32_ex(int ta, int tb, int64_t m, int64_t n, int64_t k, float al
                        int64_t ldb, float be, float* C, int64_t ldc, int, void* s) {
     return gemm<float>(ta, tb, m, n, k, al, A, lda, B, ldb, be, C, ldc, s);
 }
+int elb200_gemm_f32_noalloc(int ta, int tb, int64_t m, int64_t n, int64_t k, float al, const float* A, int64_t lda, const float* B,
+                            int64_t ldb, float be, float* C, int64_t ldc, void* s) {
+    return gemm<float>(ta, tb, m, n, k, al, A, lda, B, ldb, be, C, ldc, s);
+}
 int elb200_gemm_f64(int ta, int tb, int64_t m, int64_t n, int64_t k, double al, const double* A, int64_t lda, const double* B,
                     int64_t ldb, double be, double* C, int64_t ldc, void* s) {
     return gemm<double>(ta, tb, m, n, k, al, A, lda, B, ldb, be, C, ldc, s);
