@@ -12,7 +12,7 @@ HDRS      := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh $(CSRC)/*.hpp include/*.h)
 NCCL_INC  ?= /usr/include
 NCCL_LIB  ?= $(shell python -c "import nvidia.nccl, os; print(os.path.join(list(nvidia.nccl.__path__)[0], 'lib'))" 2>/dev/null)
 
-all: $(LIBDIR)/libelb200.so tools/gemm_check tools/el_gemm_driver tools/el_api_check tools/el_level3_check tools/native_bench
+all: $(LIBDIR)/libelb200.so tools/gemm_check tools/el_gemm_driver tools/el_api_check tools/el_level3_check tools/el_comm_check tools/native_bench
 
 build/%.o: $(CSRC)/%.cu $(HDRS)
 	@mkdir -p build
@@ -41,11 +41,15 @@ tools/el_api_check: tools/el_api_check.cpp include/El.hpp include/elb200.h $(LIB
 tools/el_level3_check: tools/el_level3_check.cpp include/El.hpp include/elb200.h $(LIBDIR)/libelb200.so
 	$(NVCC) -std=c++17 -O1 -Xcompiler -Wall -Iinclude -o $@ $< -L$(LIBDIR) -lelb200 -lcudart -Xlinker -rpath,'$$ORIGIN/../$(LIBDIR)'
 
+# communicator side of the facade: Grid(mpi::COMM_WORLD, r), the grid's communicators, mpi:: collectives, proxies, MultiSync
+tools/el_comm_check: tools/el_comm_check.cpp include/El.hpp include/elb200.h $(LIBDIR)/libelb200.so
+	$(NVCC) -std=c++17 -O1 -Xcompiler -Wall -Iinclude -o $@ $< -L$(LIBDIR) -lelb200 -lcudart -Xlinker -rpath,'$$ORIGIN/../$(LIBDIR)'
+
 # Python-free timings through the C ABI (e2e host-operand Gemm, fp64 kernel A/B vs cuBLAS, level-3 kernels)
 tools/native_bench: tools/native_bench.cu $(LIBDIR)/libelb200.so include/elb200.h
 	$(NVCC) $(NVFLAGS) -o $@ $< -L$(LIBDIR) -lelb200 -lcublas -Xlinker -rpath,'$$ORIGIN/../$(LIBDIR)'
 
 clean:
-	rm -rf build $(LIBDIR)/libelb200.so tools/gemm_check tools/el_gemm_driver tools/el_api_check tools/el_level3_check tools/native_bench
+	rm -rf build $(LIBDIR)/libelb200.so tools/gemm_check tools/el_gemm_driver tools/el_api_check tools/el_level3_check tools/el_comm_check tools/native_bench
 
 .PHONY: all clean

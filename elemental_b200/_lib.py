@@ -125,6 +125,22 @@ SIGNATURES = {
     "elb200_grid_info": (ci, [vp] + [C.POINTER(ci)] * 5),
     "elb200_grid_stream": (vp, [vp]),
     "elb200_grid_sync": (ci, [vp]),
+    "elb200_comm_world": (ci, [C.POINTER(vp)]),
+    "elb200_comm_create": (ci, [vp, ci, ci, C.POINTER(vp)]),
+    "elb200_comm_rank": (ci, [vp]),
+    "elb200_comm_size": (ci, [vp]),
+    "elb200_comm_split": (ci, [vp, ci, ci, C.POINTER(vp)]),
+    "elb200_comm_dup": (ci, [vp, C.POINTER(vp)]),
+    "elb200_comm_free": (ci, [vp]),
+    "elb200_comm_barrier": (ci, [vp]),
+    "elb200_grid_create_on": (ci, [vp, ci, ci, ci, C.POINTER(vp)]),
+    "elb200_grid_comm": (ci, [vp, ci, C.POINTER(vp)]),
+    "elb200_allgather": (ci, [vp, vp, i64, ci, vp, vp]),
+    "elb200_reduce_scatter": (ci, [vp, vp, i64, ci, vp, vp]),
+    "elb200_allreduce": (ci, [vp, vp, i64, ci, vp, vp]),
+    "elb200_alltoall": (ci, [vp, vp, i64, ci, vp, vp]),
+    "elb200_sendrecv": (ci, [vp, i64, ci, vp, i64, ci, ci, vp, vp]),
+    "elb200_bcast": (ci, [vp, i64, ci, ci, vp, vp]),
     "elb200_gemm_profile": (None, [ci]),
     "elb200_gemm_profile_collect": (ci, [C.POINTER(f64), C.POINTER(f64), C.POINTER(ci)]),
     "elb200_blocksize": (ci, []),
@@ -136,6 +152,10 @@ SIGNATURES = {
     "elb200_dm_info": (ci, [vp, C.POINTER(DmInfo)]),
     "elb200_dm_align": (ci, [vp, i64, i64]),
     "elb200_dm_align_with": (ci, [vp, vp]),
+    "elb200_dm_align_cols": (ci, [vp, i64]),
+    "elb200_dm_align_rows": (ci, [vp, i64]),
+    "elb200_dm_set_stream": (ci, [vp, vp]),
+    "elb200_dm_stream": (vp, [vp]),
     "elb200_dm_resize": (ci, [vp, i64, i64]),
     "elb200_dm_set_root": (ci, [vp, ci]),
     "elb200_dm_write_local": (ci, [vp, vp, i64]),

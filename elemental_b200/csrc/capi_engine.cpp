@@ -3,6 +3,7 @@
 #include <cstring>
 #include <memory>
 
+#include "capi_handles.hpp"
 #include "engine.hpp"
 #include "engine_dev.hpp"
 
@@ -10,19 +11,6 @@ namespace elb {
 void set_last_error(const char* what, const char* detail);
 }
 using namespace elb;
-
-struct elb200_grid_s {
-    std::shared_ptr<Grid> g;
-};
-struct elb200_dm_s {
-    int dtype;
-    // keeps the Grid (its streams) alive until the matrix is gone, whatever order the caller
-    // destroys handles in; declared before f/d so that it is released after them
-    std::shared_ptr<Grid> keep;
-    std::unique_ptr<DistMat<float>> f;
-    std::unique_ptr<DistMat<double>> d;
-    Grid* grid() const { return dtype == ELB200_F32 ? f->grid : d->grid; }
-};
 
 namespace {
 
@@ -41,6 +29,27 @@ int guarded(const char* where, F&& fn) {
 }
 
 bool same_dtype(elb200_dm_t a, elb200_dm_t b) { return a && b && a->dtype == b->dtype; }
+cudaStream_t dm_stream(elb200_dm_t a) { return a->dtype == ELB200_F32 ? a->f->stream : a->d->stream; }
+
+// hydrogen::MultiSync (include/hydrogen/MultiSync.hpp:31-78): on construction the master stream waits for the others,
+// on destruction the others wait for the master — all asynchronously with respect to the host.
+struct StreamJoin {
+    cudaStream_t master, other[2];
+    StreamJoin(cudaStream_t m, cudaStream_t a, cudaStream_t b) : master(m), other{a, b} {
+        if (other[1] == other[0]) other[1] = master;
+        for (cudaStream_t o : other)
+            if (o != master) { Ev e; e.record(o); e.block(master); }
+    }
+    ~StreamJoin() {
+        for (cudaStream_t o : other)
+            if (o != master) {
+                cudaEvent_t e = nullptr;
+                if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) continue;
+                if (cudaEventRecord(e, master) == cudaSuccess) cudaStreamWaitEvent(o, e, 0);
+                cudaEventDestroy(e);
+            }
+    }
+};
 
 DistSpec to_spec(const elb200_dist_spec& s) {
     DistSpec d;
@@ -308,9 +317,31 @@ int elb200_dist_gemm(int ta, int tb, double alpha, elb200_dm_t A, elb200_dm_t B,
     if (!same_dtype(A, B) || !same_dtype(A, C)) return ELB200_ERR_ARG;
     if (ta < 0 || ta > 2 || tb < 0 || tb > 2 || alg < 0 || alg > 8) return ELB200_ERR_ARG;
     return guarded("elb200_dist_gemm", [&] {
+        // MakeMultiSync(SyncInfoFromMatrix(C), SyncInfoFromMatrix(A), SyncInfoFromMatrix(B)) of Gemm_impl<GPU>
+        // (src/blas_like/level3/Gemm.cpp:172-175): the product runs on C's stream, which first waits for A's and B's;
+        // afterwards their streams wait for it.
+        StreamJoin join(dm_stream(C), dm_stream(A), dm_stream(B));
         if (A->dtype == ELB200_F32) Gemm(ta, tb, float(alpha), *A->f, *B->f, float(beta), *C->f, alg);
         else Gemm(ta, tb, alpha, *A->d, *B->d, beta, *C->d, alg);
     });
+}
+
+// SetSyncInfo / SyncInfoFromMatrix on a DistMatrix's local matrix (include/El/core/Matrix/decl.hpp, hydrogen SyncInfo):
+// the stream every operation WRITING this matrix is enqueued on. Defaults to the grid's compute stream.
+int elb200_dm_set_stream(elb200_dm_t a, void* stream) {
+    if (!a) return ELB200_ERR_ARG;
+    cudaStream_t s = stream ? static_cast<cudaStream_t>(stream) : a->grid()->stream;
+    ELB_ON(a, M.stream = s, M.stream = s);
+    return ELB200_OK;
+}
+void* elb200_dm_stream(elb200_dm_t a) { return a ? dm_stream(a) : nullptr; }
+int elb200_dm_align_cols(elb200_dm_t a, int64_t ca) {
+    if (!a) return ELB200_ERR_ARG;
+    return guarded("elb200_dm_align_cols", [&] { ELB_ON(a, M.AlignCols(ca), M.AlignCols(ca)); });
+}
+int elb200_dm_align_rows(elb200_dm_t a, int64_t ra) {
+    if (!a) return ELB200_ERR_ARG;
+    return guarded("elb200_dm_align_rows", [&] { ELB_ON(a, M.AlignRows(ra), M.AlignRows(ra)); });
 }
 
 int elb200_dist_gemm_host_f32(elb200_grid_t g, int ta, int tb, int64_t m, int64_t n, int64_t k, float alpha,

@@ -62,6 +62,7 @@ public:
     cudaStream_t comm_stream = nullptr;  // panel prefetch stream (overlap with the local GEMM)
     cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;  // host-operand streaming (GemmHost)
     ncclComm_t world = nullptr, mc_comm = nullptr, mr_comm = nullptr;
+    ncclComm_t vr_comm = nullptr;  // all ranks in VR (row-major) order; created on first use by elb200_grid_comm
     // NVLink peer-memory staging (zero-SM AllGather); nullptr -> NCCL is used instead.
     PeerArena* arena = nullptr;
     // VC ranks of the MC (grid column) / MR (grid row) / VC (world) communicator this rank belongs

@@ -128,6 +128,8 @@ void Grid::Shutdown() {
         delete arena;
         arena = nullptr;
     }
+    if (vr_comm) ncclCommDestroy(vr_comm);
+    vr_comm = nullptr;
     if (mc_comm && mc_comm != world) ncclCommDestroy(mc_comm);
     if (mr_comm && mr_comm != world) ncclCommDestroy(mr_comm);
     if (world) ncclCommDestroy(world);

@@ -14,6 +14,7 @@
 // CTA tile 128(m) x 128(n) x BK(k); 8 warps as 2(m) x 4(n), each 64 x 32: 32 DMMAs per k4 step
 // against 12 conflict-free LDS.64.
 #include <cuda_runtime.h>
+#include <atomic>
 #include <cstdint>
 #include <cstdlib>
 
@@ -206,6 +207,212 @@ cudaError_t launch(const Params& p, cudaStream_t stream) {
     count_launch();
     kern<<<dim3(unsigned(p.tiles_m) * unsigned(p.tiles_n)), kThreads, kSmemBytes, stream>>>(p);
     return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// Multi-CTA-per-SM tiles (the default since round 2). The ncu capture of cublasDgemm on this GPU shows what its
+// 36 TFLOP/s (DMMA pipe 96 % active, against 86 % for the 128 x 128 kernel above) rest on: SMALL tiles — 64 x 64 x 16,
+// four warps of 32 x 32, 116 registers — so that THREE independent CTAs share an SM: while one sits in its per-k-tile
+// barrier, waits for cp.async or runs its epilogue, the other two keep the pipe fed. One big CTA per SM (above) has
+// nobody to cover those bubbles. Same math, same padded conflict-free shared-memory pitches, same C^T trick as above,
+// with the tile shape, the stage count, the warp grid and the CTAs-per-SM target as template parameters:
+//   Tile<64, 64, 16, S, 2, 2, 3>   the cuBLAS-like shape: 128 threads, 32 x 32 per warp, three CTAs per SM
+//   Tile<128, 64, 16, S, 4, 2, 2>  256 threads, 32 x 32 per warp, two CTAs per SM (more reuse per byte from L2)
+// Operand tiles are sized exactly per majorness ([k][mn + 4] or [mn][k + 4]) so that four stages of the NN / NT
+// shapes still fit three times into the 227 KB of an SM.
+// ---------------------------------------------------------------------------------------------
+template <int BM_, int BN_, int BK_, int STAGES_, int WARPS_M_, int WARPS_N_, int MINB_>
+struct Tile {
+    static constexpr int BM = BM_, BN = BN_, BK = BK_, STAGES = STAGES_, WARPS_M = WARPS_M_, WARPS_N = WARPS_N_, MINB = MINB_;
+    static constexpr int kThreads = 32 * WARPS_M * WARPS_N;
+    static constexpr int WM = BM / WARPS_M, WN = BN / WARPS_N;  // warp tile
+    static constexpr int MI = WM / 8, NI = WN / 8;              // 8 x 8 DMMA blocks per warp tile
+    static_assert(WM % 8 == 0 && WN % 8 == 0 && BK % 4 == 0, "tile shape");
+    // smem operand tile in doubles: MN-contiguous source -> [k][mn] with pitch mn + 4, else [mn][k] with pitch k + 4
+    template <bool TA, bool TB> struct Smem {
+        static constexpr int kA = !TA ? BK * (BM + 4) : BM * (BK + 4);
+        static constexpr int kB = TB ? BK * (BN + 4) : BN * (BK + 4);
+        static constexpr int kBytes = STAGES * (kA + kB) * 8;
+    };
+};
+
+template <class C, bool MN_CONTIG, int MN, int VEC>
+__device__ __forceinline__ void load_tile_t(const double* __restrict__ X, int64_t ld, int mn0, int k0, int mn_extent,
+                                            int k_extent, uint32_t smem_tile) {
+    constexpr int kChunks = (MN * C::BK) / VEC;
+    constexpr int kIters = (kChunks + C::kThreads - 1) / C::kThreads;
+#pragma unroll
+    for (int i = 0; i < kIters; ++i) {
+        const int c = threadIdx.x + i * C::kThreads;
+        if (kChunks % C::kThreads != 0 && c >= kChunks) break;
+        int mn, kk;
+        uint32_t dst;
+        if constexpr (MN_CONTIG) {
+            constexpr int kPerRow = MN / VEC;
+            kk = c / kPerRow;
+            mn = (c % kPerRow) * VEC;
+            dst = smem_tile + uint32_t(kk * (MN + 4) + mn) * 8u;
+        } else {
+            constexpr int kPerRow = C::BK / VEC;
+            mn = c / kPerRow;
+            kk = (c % kPerRow) * VEC;
+            dst = smem_tile + uint32_t(mn * (C::BK + 4) + kk) * 8u;
+        }
+        const int gmn = mn0 + mn, gk = k0 + kk;
+        int valid;
+        if constexpr (MN_CONTIG) valid = (gk < k_extent) ? min(max(mn_extent - gmn, 0), VEC) : 0;
+        else valid = (gmn < mn_extent) ? min(max(k_extent - gk, 0), VEC) : 0;
+        const double* src = X;
+        if (valid > 0) src = MN_CONTIG ? X + int64_t(gk) * ld + gmn : X + int64_t(gmn) * ld + gk;
+        cp_async_zfill<VEC * 8>(dst, src, valid * 8);
+    }
+}
+
+template <class C, bool TA, bool TB, int VEC>
+__global__ void __launch_bounds__(C::kThreads, C::MINB) gemm_f64_tile_kernel(const Params p) {
+    constexpr int BM = C::BM, BN = C::BN, BK = C::BK, kStg = C::STAGES, MI = C::MI, NI = C::NI;
+    constexpr int kADoubles = C::template Smem<TA, TB>::kA, kBDoubles = C::template Smem<TA, TB>::kB;
+    constexpr int kStage = kADoubles + kBDoubles;
+    constexpr int kPitchA = TA ? BK + 4 : BM + 4, kPitchB = TB ? BN + 4 : BK + 4;
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    const uint32_t smem_base = smem_u32(smem_raw);
+    const double* smem_d = reinterpret_cast<const double*>(smem_raw);
+
+    int tm, tn;
+    tile_coords(blockIdx.x, p.tiles_m, p.tiles_n, tm, tn);
+    const int m0 = tm * BM, n0 = tn * BN;
+    const int num_kt = (p.k + BK - 1) / BK;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int wm = (warp % C::WARPS_M) * C::WM;  // warp's m offset in the CTA tile
+    const int wn = (warp / C::WARPS_M) * C::WN;  // warp's n offset
+    const int lr = lane >> 2, lk = lane & 3;
+
+    auto issue_stage = [&](int kt, int s) {
+        const uint32_t sa = smem_base + uint32_t(s * kStage) * 8u;
+        const uint32_t sb = sa + uint32_t(kADoubles) * 8u;
+        load_tile_t<C, !TA, BM, VEC>(p.A, p.lda, m0, kt * BK, p.m, p.k, sa);
+        load_tile_t<C, TB, BN, VEC>(p.B, p.ldb, n0, kt * BK, p.n, p.k, sb);
+    };
+
+    double acc[NI][MI][2];
+#pragma unroll
+    for (int ni = 0; ni < NI; ++ni)
+#pragma unroll
+        for (int mi = 0; mi < MI; ++mi) acc[ni][mi][0] = acc[ni][mi][1] = 0.0;
+
+#pragma unroll
+    for (int s = 0; s < kStg - 1; ++s) {
+        if (s < num_kt) issue_stage(s, s);
+        cp_async_commit();
+    }
+
+    int rd = 0, wr = kStg - 1;  // ring positions of the stage being read / refilled
+    for (int kt = 0; kt < num_kt; ++kt) {
+        cp_async_wait<kStg - 2>();
+        __syncthreads();
+        {
+            const int nk = kt + kStg - 1;
+            if (nk < num_kt) issue_stage(nk, wr);
+            cp_async_commit();
+        }
+        const double* sa = smem_d + rd * kStage;
+        const double* sb = sa + kADoubles;
+#pragma unroll
+        for (int k4 = 0; k4 < BK; k4 += 4) {
+            double bf[MI], af[NI];
+#pragma unroll
+            for (int mi = 0; mi < MI; ++mi) {
+                const int mm = wm + mi * 8 + lr, kk = k4 + lk;
+                bf[mi] = TA ? sa[mm * kPitchA + kk] : sa[kk * kPitchA + mm];
+            }
+#pragma unroll
+            for (int ni = 0; ni < NI; ++ni) {
+                const int nn = wn + ni * 8 + lr, kk = k4 + lk;
+                af[ni] = TB ? sb[kk * kPitchB + nn] : sb[nn * kPitchB + kk];
+            }
+#pragma unroll
+            for (int ni = 0; ni < NI; ++ni)
+#pragma unroll
+                for (int mi = 0; mi < MI; ++mi) dmma_m8n8k4(acc[ni][mi], af[ni], bf[mi]);
+        }
+        rd = rd + 1 == kStg ? 0 : rd + 1;
+        wr = wr + 1 == kStg ? 0 : wr + 1;
+    }
+    cp_async_wait<0>();
+
+    // epilogue: thread owns C(m..m+1, n), m = m0+wm+mi*8+2*lk, n = n0+wn+ni*8+lr
+    const bool vec_ok = ((p.ldc & 1) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15u) == 0);
+#pragma unroll
+    for (int ni = 0; ni < NI; ++ni) {
+        const int n = n0 + wn + ni * 8 + lr;
+        if (n >= p.n) continue;
+        double* ccol = p.C + int64_t(n) * p.ldc;
+#pragma unroll
+        for (int mi = 0; mi < MI; ++mi) {
+            const int m = m0 + wm + mi * 8 + 2 * lk;
+            if (m >= p.m) continue;
+            double o0 = p.alpha * acc[ni][mi][0], o1 = p.alpha * acc[ni][mi][1];
+            if (vec_ok && m + 1 < p.m) {
+                double2* ptr = reinterpret_cast<double2*>(ccol + m);
+                if (p.beta != 0.0) {
+                    const double2 c = *ptr;
+                    o0 = fma(p.beta, c.x, o0);
+                    o1 = fma(p.beta, c.y, o1);
+                }
+                *ptr = make_double2(o0, o1);
+            } else {
+                if (p.beta != 0.0) o0 = fma(p.beta, ccol[m], o0);
+                ccol[m] = o0;
+                if (m + 1 < p.m) {
+                    if (p.beta != 0.0) o1 = fma(p.beta, ccol[m + 1], o1);
+                    ccol[m + 1] = o1;
+                }
+            }
+        }
+    }
+}
+
+// cudaFuncSetAttribute is per device: remember which devices have been configured for this instantiation
+struct PerDeviceOnce {
+    std::atomic<bool> done[64];
+    bool needs(int* dev_out) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { *dev_out = -1; return true; }
+        *dev_out = dev;
+        return !done[dev].load(std::memory_order_acquire);
+    }
+    void set(int dev) { if (dev >= 0) done[dev].store(true, std::memory_order_release); }
+};
+
+template <class C, bool TA, bool TB, int VEC>
+cudaError_t launch_tile(Params p, cudaStream_t stream) {
+    auto kern = gemm_f64_tile_kernel<C, TA, TB, VEC>;
+    constexpr int smem = C::template Smem<TA, TB>::kBytes;
+    static PerDeviceOnce once;
+    int dev;
+    if (once.needs(&dev)) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        if (e != cudaSuccess) return e;
+        once.set(dev);
+    }
+    p.tiles_m = (p.m + C::BM - 1) / C::BM;
+    p.tiles_n = (p.n + C::BN - 1) / C::BN;
+    count_launch();
+    kern<<<dim3(unsigned(p.tiles_m) * unsigned(p.tiles_n)), C::kThreads, smem, stream>>>(p);
+    return cudaGetLastError();
+}
+
+// stage count per (tile, majorness): the most (<= 4) that still lets MINB CTAs share the SM's 227 KB (1 KB reserved per CTA)
+template <int BM, int BN, int WMG, int WNG, int MINB, bool TA, bool TB, int VEC>
+cudaError_t launch_tile_auto(const Params& p, cudaStream_t stream) {
+    using C4 = Tile<BM, BN, 16, 4, WMG, WNG, MINB>;
+    using C3 = Tile<BM, BN, 16, 3, WMG, WNG, MINB>;
+    constexpr int kSmPerSm = 232448;
+    if constexpr (MINB * (C4::template Smem<TA, TB>::kBytes + 1024) <= kSmPerSm) return launch_tile<C4, TA, TB, VEC>(p, stream);
+    else return launch_tile<C3, TA, TB, VEC>(p, stream);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -414,7 +621,20 @@ int gemm_f64_dmma(int transA, int transB, int64_t m, int64_t n, int64_t k, doubl
         const int st = gemm_f64_dmma_tma(transA, transB, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, stream);
         if (st >= 0) return st;  // -1: operands not TMA-able (alignment), use the cp.async kernels
     }
+    // ELB200_F64_TILE: 64 = Tile<64,64,16> x 3 CTAs / SM (default), 12864 = Tile<128,64,16> x 2 CTAs / SM, 128 = the one-CTA-per-SM kernels
+    static const int tile = [] { const char* v = std::getenv("ELB200_F64_TILE"); const int t = v ? std::atoi(v) : 0; return t == 128 || t == 12864 ? t : 64; }();
     static const bool ws = [] { const char* v = std::getenv("ELB200_F64_WS"); return v && std::atoi(v) != 0; }();
+    if (tile != 128 && !ws) {
+#define ELB_DISPATCH_T(BMv, BNv, WMG, WNG, MINB, V)                                                   \
+    if (!ta && !tb) e = launch_tile_auto<BMv, BNv, WMG, WNG, MINB, false, false, V>(p, stream);       \
+    else if (!ta && tb) e = launch_tile_auto<BMv, BNv, WMG, WNG, MINB, false, true, V>(p, stream);    \
+    else if (ta && !tb) e = launch_tile_auto<BMv, BNv, WMG, WNG, MINB, true, false, V>(p, stream);    \
+    else e = launch_tile_auto<BMv, BNv, WMG, WNG, MINB, true, true, V>(p, stream);
+        if (tile == 64) { if (aligned) { ELB_DISPATCH_T(64, 64, 2, 2, 3, 2) } else { ELB_DISPATCH_T(64, 64, 2, 2, 3, 1) } }
+        else { if (aligned) { ELB_DISPATCH_T(128, 64, 4, 2, 2, 2) } else { ELB_DISPATCH_T(128, 64, 4, 2, 2, 1) } }
+#undef ELB_DISPATCH_T
+        return e == cudaSuccess ? ELB200_OK : ELB200_ERR_CUDA;
+    }
     if (ws) {
 #define ELB_DISPATCH_WS(V)                                                \
     if (!ta && !tb) e = launch_ws<false, false, V>(p, stream);           \

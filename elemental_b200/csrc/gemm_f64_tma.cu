@@ -11,6 +11,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <cstdint>
+#include <cstdio>
 #include <cstdlib>
 #include <mutex>
 
@@ -265,6 +266,7 @@ int gemm_f64_dmma_tma(int transA, int transB, int64_t m, int64_t n, int64_t k, d
     else if (!ta && tb) e = launch<false, true>(tmA, tmB, p, stream);
     else if (ta && !tb) e = launch<true, false>(tmA, tmB, p, stream);
     else e = launch<true, true>(tmA, tmB, p, stream);
+    if (e != cudaSuccess) std::fprintf(stderr, "gemm_f64_dmma_tma: launch failed: %s\n", cudaGetErrorString(e));
     return e == cudaSuccess ? ELB200_OK : ELB200_ERR_CUDA;
 }
 

@@ -284,6 +284,11 @@ PeerArena::Ticket PeerArena::AllGather(int channel, const std::vector<int>& memb
 PeerArena::Ticket PeerArena::GatherDirect(int channel, const std::vector<int>& members, int my_index,
                                           const std::vector<Copy2D>& copies, cudaStream_t s) {
     const int g = int(members.size());
+    // argument checks come BEFORE the sequence counter moves or a wait is enqueued: a rank that throws here has
+    // not touched the collective state, so its peers are not left waiting on flags that never come
+    for (const Copy2D& c : copies)
+        if (c.width && c.height && c.dst_offset + (c.height - 1) * c.dpitch + c.width > slot_bytes_)
+            throw EngineError(ELB200_ERR_ARG, "PeerArena::GatherDirect: transfer leaves the slot");
     const uint64_t n = uses_[channel]++;
     Ticket t;
     t.channel = channel;
@@ -291,9 +296,6 @@ PeerArena::Ticket PeerArena::GatherDirect(int channel, const std::vector<int>& m
     t.seq = uint32_t(n / 2 + 1);
     for (int i = 0; i < g; ++i)
         if (i != my_index) wait_flag(flag(rank_, ACK, channel, t.slot, members[i]), t.seq - 1, s);
-    for (const Copy2D& c : copies)
-        if (c.width && c.height && c.dst_offset + (c.height - 1) * c.dpitch + c.width > slot_bytes_)
-            throw EngineError(ELB200_ERR_ARG, "PeerArena::GatherDirect: transfer leaves the slot");
     for (int i = 0; i < g; ++i) {
         cudaStream_t ls = fork(i, s);  // one lane per destination; its arrival flag follows its payload
         for (const Copy2D& c : copies) {

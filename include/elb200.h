@@ -304,7 +304,7 @@ int elb200_gemm_resolve_alg(int transA, int transB, int64_t m, int64_t n, int64_
  * ---------------------------------------------------------------------------------------- */
 typedef struct elb200_grid_s* elb200_grid_t;
 typedef struct elb200_dm_s* elb200_dm_t;
-enum { ELB200_F32 = 0, ELB200_F64 = 1 };
+enum { ELB200_F32 = 0, ELB200_F64 = 1, ELB200_BYTE = 2 /* data movement only: no reductions */ };
 #define ELB200_UNIQUE_ID_BYTES 128
 
 /* NCCL bootstrap: rank 0 calls elb200_unique_id and ships the 128 bytes to the other ranks by any
@@ -319,6 +319,63 @@ int elb200_grid_info(elb200_grid_t g, int* height, int* width, int* vc_rank, int
                      int* mr_rank);
 void* elb200_grid_stream(elb200_grid_t g); /* the grid's compute stream (cudaStream_t) */
 int elb200_grid_sync(elb200_grid_t g);     /* cudaStreamSynchronize on it */
+
+/* ------------------------------------------------------------------------------------------
+ * Communicators and per-collective entry points: what the reference binds below its copy:: and
+ * axpy_contract:: routines. A communicator stands for mpi::Comm (an AluminumComm over an MPI communicator,
+ * include/El/core/imports/mpi/aluminum_comm.hpp:93-236); there is no MPI here — it is an NCCL communicator,
+ * and when it is a Grid's MC / MR / VC communicator the collectives travel through the grid's NVLink peer
+ * arena (copy engines + stream memory operations, no SM) whenever the message fits a slot,
+ * with NCCL as the fallback (ELB200_COLL_ARENA=0 forces NCCL). Equal counts on every rank, counts in
+ * ELEMENTS of `dtype` (int64: the reference's `int` counts, src/core/imports/mpi/AllGather.hpp:11-12, cap a
+ * call at 2^31 elements), device pointers, asynchronous on the caller's stream, every rank of the
+ * communicator calls in the same order (SURVEY.md 8(b) "Threading").
+ * ---------------------------------------------------------------------------------------- */
+typedef struct elb200_comm_s* elb200_comm_t;
+enum { ELB200_COMM_MC = 0, ELB200_COMM_MR = 1, ELB200_COMM_VC = 2, ELB200_COMM_VR = 3 };
+enum { ELB200_ROW_MAJOR = 0, ELB200_COLUMN_MAJOR = 1 }; /* El::GridOrder (include/El/core/types.hpp) */
+
+/* mpi::COMM_WORLD: bootstrapped once per process from RANK / WORLD_SIZE; the NCCL id travels from rank 0
+ * through ELB200_ID_FILE (a path every rank can reach) or over TCP to MASTER_ADDR : ELB200_PORT (default
+ * MASTER_PORT + 29). Replaces MPI_Init_thread + MPI_COMM_WORLD (src/core/imports/mpi.cpp:80-91). The handle is
+ * owned by the library (elb200_comm_free on it tears the world down: El::Finalize). */
+int elb200_comm_world(elb200_comm_t* out);
+/* A communicator over an explicit NCCL id (elb200_unique_id) for callers with their own side channel. */
+int elb200_comm_create(const void* id128, int rank, int size, elb200_comm_t* out);
+int elb200_comm_rank(elb200_comm_t c);  /* mpi::Rank(comm) */
+int elb200_comm_size(elb200_comm_t c);  /* mpi::Size(comm) */
+/* mpi::Split(comm, color, key, newComm) (src/core/imports/mpi.cpp); color < 0 = MPI_UNDEFINED: *out = NULL */
+int elb200_comm_split(elb200_comm_t c, int color, int key, elb200_comm_t* out);
+int elb200_comm_dup(elb200_comm_t c, elb200_comm_t* out);   /* mpi::Dup */
+int elb200_comm_free(elb200_comm_t c);                       /* mpi::Free */
+int elb200_comm_barrier(elb200_comm_t c);                    /* mpi::Barrier: blocks the host */
+/* El::Grid(mpi::Comm comm, int height, GridOrder order) (include/El/core/Grid.hpp:19-20,
+ * src/core/Grid.cpp:74-223). Collective over `c`; height <= 0 = Grid::DefaultHeight(size); device < 0 = the
+ * current CUDA device. The grid's own NCCL communicators are created from an id broadcast over `c`. */
+int elb200_grid_create_on(elb200_comm_t c, int height, int order, int device, elb200_grid_t* out);
+/* Grid::MCComm() / MRComm() / VCComm() / VRComm() (include/El/core/Grid.hpp:62-75): `which` is an
+ * ELB200_COMM_* value. The handle borrows the grid's communicator and keeps the grid alive; release it with
+ * elb200_comm_free. VRComm is built on first use (collective over the grid). */
+int elb200_grid_comm(elb200_grid_t g, int which, elb200_comm_t* out);
+
+/* mpi::AllGather(sbuf, sc, rbuf, rc, comm, syncInfo) (src/core/imports/mpi/AllGather.hpp:8-21):
+ * rbuf[i*count .. (i+1)*count) = rank i's sbuf. */
+int elb200_allgather(const void* sbuf, void* rbuf, int64_t count, int dtype, elb200_comm_t c, void* stream);
+/* mpi::ReduceScatter(sbuf, rbuf, rc, mpi::SUM, comm, syncInfo) (ReduceScatter.hpp:36-52): sbuf holds
+ * size*count elements, rbuf gets the sum over ranks of block `rank`. sbuf == rbuf is the in-place form
+ * (ReduceScatter.hpp:149-165): the result lands at the start of the buffer. Over the arena the sum runs in
+ * communicator order on every rank (deterministic); over NCCL the order is NCCL's. */
+int elb200_reduce_scatter(const void* sbuf, void* rbuf, int64_t count, int dtype, elb200_comm_t c, void* stream);
+/* mpi::AllReduce(sbuf, rbuf, count, mpi::SUM, comm, syncInfo) (src/core/imports/mpi/AllReduce.hpp) */
+int elb200_allreduce(const void* sbuf, void* rbuf, int64_t count, int dtype, elb200_comm_t c, void* stream);
+/* mpi::AllToAll(sbuf, sc, rbuf, rc, comm, syncInfo) (src/core/imports/mpi/AllToAll.hpp): block j of sbuf goes to
+ * rank j, block i of rbuf comes from rank i, `count` elements each. */
+int elb200_alltoall(const void* sbuf, void* rbuf, int64_t count, int dtype, elb200_comm_t c, void* stream);
+/* mpi::SendRecv(sbuf, sc, to, rbuf, rc, from, comm, syncInfo) (src/core/imports/mpi/SendRecv.hpp) */
+int elb200_sendrecv(const void* sbuf, int64_t scount, int to, void* rbuf, int64_t rcount, int from, int dtype,
+                    elb200_comm_t c, void* stream);
+/* mpi::Broadcast(buf, count, root, comm, syncInfo) (src/core/imports/mpi/Broadcast.hpp) */
+int elb200_bcast(void* buf, int64_t count, int dtype, int root, elb200_comm_t c, void* stream);
 
 /* Measurement hook (bench.py roofline leg): when enabled, every LocalGemm kernel launch is
  * bracketed by CUDA events on its own stream; collect() synchronises and returns the summed device
@@ -346,6 +403,14 @@ int elb200_dm_destroy(elb200_dm_t a);
 int elb200_dm_info(elb200_dm_t a, elb200_dm_info_t* out);
 int elb200_dm_align(elb200_dm_t a, int64_t col_align, int64_t row_align);
 int elb200_dm_align_with(elb200_dm_t a, elb200_dm_t other);
+int elb200_dm_align_cols(elb200_dm_t a, int64_t col_align); /* ElementalMatrix::AlignCols */
+int elb200_dm_align_rows(elb200_dm_t a, int64_t row_align); /* ElementalMatrix::AlignRows */
+/* SetSyncInfo / SyncInfoFromMatrix on the local matrix (include/hydrogen/device/gpu/cuda/SyncInfo.hpp:14-84): the
+ * cudaStream_t that operations writing this matrix are enqueued on (NULL = back to the grid's compute stream).
+ * elb200_dist_gemm orders the three operands' streams like MakeMultiSync(C, A, B) in Gemm_impl<GPU>
+ * (src/blas_like/level3/Gemm.cpp:172-175; include/hydrogen/MultiSync.hpp:31-78). */
+int elb200_dm_set_stream(elb200_dm_t a, void* stream);
+void* elb200_dm_stream(elb200_dm_t a);
 /* AbstractDistMatrix::SetRoot (include/El/core/DistMatrix/AbstractDistMatrix.hpp:58): the VC rank
  * that holds a [CIRC,CIRC] matrix. Collective metadata; every rank passes the same root. */
 int elb200_dm_set_root(elb200_dm_t a, int root);

@@ -11,6 +11,7 @@ The procedure mirrors the reference's own tests:
 """
 from __future__ import annotations
 
+import ctypes as C
 import itertools
 
 import numpy as np
@@ -797,6 +798,69 @@ def check_gemm_dot_pipeline(grid, dtype=torch.float64) -> int:
     return cnt
 
 
+def check_collectives(grid, dtype=torch.float64) -> int:
+    """The per-collective C-ABI exports (include/elb200.h: elb200_allgather / reduce_scatter / allreduce / alltoall /
+    sendrecv / bcast — what mpi::AllGather<GPU> ... bind, src/core/imports/mpi/*.hpp) over each of the grid's four
+    communicators (Grid::MCComm / MRComm / VCComm / VRComm), at a size on the latency path and a ragged one. Values
+    are small integers, so every result — sums included, whatever the order — is exact. Device buffers are the local
+    matrices of [*,*] DistMatrices (one column), which both back ends can fill and read."""
+    lib, check = el.lib, el.check
+    npdt = NPDT[dtype]
+    code = 0 if dtype == torch.float32 else 1
+    stream = lib.elb200_grid_stream(grid._h)
+    keep, cnt = [], 0
+
+    def dev(values):
+        a = np.asarray(values, dtype=npdt).reshape(-1, 1)
+        D = el.DistMatrix(grid, el.STAR, el.STAR, dtype).Resize(a.shape[0], 1)
+        D.set_local(a)
+        keep.append(D)
+        return D, D._info().buffer
+
+    def val(rank, idx):
+        return rank * 1000 + (np.asarray(idx) % 997)
+
+    expect_rank = (grid.MCRank(), grid.MRRank(), grid.VCRank(), grid.VRRank())
+    expect_size = (grid.Height(), grid.Width(), grid.Size(), grid.Size())
+    for which in range(4):
+        ch = C.c_void_p()
+        check(lib.elb200_grid_comm(grid._h, which, C.byref(ch)), "elb200_grid_comm")
+        p, me = lib.elb200_comm_size(ch), lib.elb200_comm_rank(ch)
+        assert (me, p) == (expect_rank[which], expect_size[which]), (which, me, p)
+        for n in (7, 3001):
+            i = np.arange(n)
+            # allgather
+            S, sp = dev(val(me, i)); R, rp = dev(np.zeros(n * p))
+            check(lib.elb200_allgather(sp, rp, n, code, ch, stream), "elb200_allgather")
+            assert np.array_equal(R.get_local()[:, 0], np.concatenate([val(q, i) for q in range(p)]).astype(npdt)), ("allgather", which, n)
+            # reduce_scatter, out of place and in place (result at the start of the buffer), allreduce
+            big = np.arange(n * p)
+            S, sp = dev(val(me, big)); R, rp = dev(np.zeros(n))
+            want = sum(val(q, big[me * n:(me + 1) * n]) for q in range(p)).astype(npdt)
+            check(lib.elb200_reduce_scatter(sp, rp, n, code, ch, stream), "elb200_reduce_scatter")
+            assert np.array_equal(R.get_local()[:, 0], want), ("reduce_scatter", which, n)
+            check(lib.elb200_reduce_scatter(sp, sp, n, code, ch, stream), "elb200_reduce_scatter (in place)")
+            assert np.array_equal(S.get_local()[:n, 0], want), ("reduce_scatter in place", which, n)
+            S, sp = dev(val(me, big)); R, rp = dev(np.zeros(n * p))
+            check(lib.elb200_allreduce(sp, rp, n * p, code, ch, stream), "elb200_allreduce")
+            assert np.array_equal(R.get_local()[:, 0], sum(val(q, big) for q in range(p)).astype(npdt)), ("allreduce", which, n)
+            # alltoall: block j of rank q's buffer carries the tag 64 q + j
+            S, sp = dev(np.concatenate([val(me * 64 + j, i) for j in range(p)])); R, rp = dev(np.zeros(n * p))
+            check(lib.elb200_alltoall(sp, rp, n, code, ch, stream), "elb200_alltoall")
+            assert np.array_equal(R.get_local()[:, 0], np.concatenate([val(q * 64 + me, i) for q in range(p)]).astype(npdt)), ("alltoall", which, n)
+            # sendrecv around the ring, bcast from the last rank
+            S, sp = dev(val(me, i)); R, rp = dev(np.zeros(n))
+            check(lib.elb200_sendrecv(sp, n, (me + 1) % p, rp, n, (me - 1) % p, code, ch, stream), "elb200_sendrecv")
+            assert np.array_equal(R.get_local()[:, 0], val((me - 1) % p, i).astype(npdt)), ("sendrecv", which, n)
+            check(lib.elb200_bcast(sp, n, code, p - 1, ch, stream), "elb200_bcast")
+            assert np.array_equal(S.get_local()[:, 0], val(p - 1, i).astype(npdt)), ("bcast", which, n)
+            cnt += 7
+            grid.sync()
+            keep.clear()
+        check(lib.elb200_comm_free(ch), "elb200_comm_free")
+    return cnt
+
+
 def run_all(grid, heavy=False) -> dict:
     out = {}
     out["redist_f64"] = check_redistributions(grid, torch.float64)
@@ -807,6 +871,7 @@ def run_all(grid, heavy=False) -> dict:
     check_views_and_transpose(grid, torch.float64)
     check_contractions(grid, torch.float64)
     check_contractions(grid, torch.float32)
+    out["collectives"] = check_collectives(grid, torch.float64) + check_collectives(grid, torch.float32)
     out["gemm_f64"] = check_gemm_variants(grid, torch.float64)
     out["gemm_f32"] = check_gemm_variants(grid, torch.float32)
     check_gemm_proxies(grid, torch.float64)

@@ -240,12 +240,13 @@ ncclResult_t ncclCommSplit(ncclComm_t comm, int color, int key, ncclComm_t* out,
         if (!slot) slot = std::make_shared<Shared>(int(members.size()));
     }
     sh.barrier("ncclCommSplit");
-    ncclComm* c = new ncclComm();
-    {
+    ncclComm* c = nullptr;
+    if (color != NCCL_SPLIT_NOCOLOR) {  // NOCOLOR: this rank takes part in the call but joins no new communicator
+        c = new ncclComm();
         std::lock_guard<std::mutex> l(sh.m);
         c->sh = sh.split[color];
+        c->rank = my;
     }
-    c->rank = my;
     sh.barrier("ncclCommSplit");
     if (comm->rank == 0) {
         std::lock_guard<std::mutex> l(sh.m);
@@ -258,6 +259,32 @@ ncclResult_t ncclCommSplit(ncclComm_t comm, int color, int key, ncclComm_t* out,
 
 ncclResult_t ncclCommDestroy(ncclComm_t comm) {
     delete comm;
+    return ncclSuccess;
+}
+
+ncclResult_t ncclCommUserRank(const ncclComm_t comm, int* rank) { *rank = comm->rank; return ncclSuccess; }
+ncclResult_t ncclCommCount(const ncclComm_t comm, int* count) { *count = comm->sh->n; return ncclSuccess; }
+
+ncclResult_t ncclBroadcast(const void* sendbuf, void* recvbuf, size_t count, ncclDataType_t dt, int root, ncclComm_t comm,
+                           cudaStream_t s) {
+    if (root < 0 || root >= comm->sh->n) return ncclInvalidArgument;
+    const size_t bytes = count * dtype_size(dt);
+    sim::enqueue(s, [=] {
+        Shared& sh = *comm->sh;
+        if (bytes) {
+            if (comm->rank == root) sim::check_device_range(sendbuf, bytes, "ncclBroadcast send");
+            sim::check_device_range(recvbuf, bytes, "ncclBroadcast recv");
+        }
+        sh.send[comm->rank] = sendbuf;
+        if (sim::vtime_on()) sim::vt_at_least(sh.vt_sync(comm->rank, 20e-6 + double(bytes) / 300e9, "ncclBroadcast"));
+        sh.barrier("ncclBroadcast");
+        const bool skip = sim::dry_run() && bytes > sim::kDryKeep;
+        std::vector<char> tmp(skip ? 0 : bytes);
+        if (!skip && bytes) std::memcpy(tmp.data(), sh.send[root], bytes);
+        sh.barrier("ncclBroadcast");
+        if (!skip && bytes) std::memcpy(recvbuf, tmp.data(), bytes);
+        sh.barrier("ncclBroadcast");
+    });
     return ncclSuccess;
 }
 

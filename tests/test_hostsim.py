@@ -131,7 +131,7 @@ def test_cxx_facade_on_hostsim(simlib):
     """include/El.hpp exercised for real on CPU: tools/el_api_check.cpp and tools/el_gemm_driver.cpp
     (the counterpart of the reference's tests/blas_like/Gemm.cpp) linked against the hostsim engine."""
     out_dir = os.path.dirname(simlib)
-    for tool, args in (("el_api_check", []), ("el_level3_check", []), ("el_gemm_driver", ["--m", "150", "--n", "120", "--k", "130", "--reps", "1"]),
+    for tool, args in (("el_api_check", []), ("el_level3_check", []), ("el_comm_check", []), ("el_gemm_driver", ["--m", "150", "--n", "120", "--k", "130", "--reps", "1"]),
                        ("el_gemm_driver", ["--m", "150", "--n", "120", "--k", "130", "--reps", "1", "--f64"])):
         exe = os.path.join(out_dir, tool)
         src = os.path.join(ROOT, "tools", tool + ".cpp")
@@ -150,9 +150,12 @@ def test_cxx_facade_on_hostsim(simlib):
     r = subprocess.run(["g++", "-std=c++17", "-O1", "-I" + os.path.join(ROOT, "include"), "-I" + cuda_inc, "-o", exe, src, simlib,
                         "-Wl,-rpath," + out_dir, "-pthread"], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr[-3000:]
-    for shape in (("2", "2"), ("2", "3")):
-        r = subprocess.run([exe, *shape], capture_output=True, text=True, timeout=300, env=dict(os.environ, ELB200_ARENA_MB="8", HOSTSIM_TIMEOUT="90"))
-        assert r.returncode == 0 and "FACADE_RANKS_PASS" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+    for shape, extra in ((("2", "2"), {}), (("2", "3"), {}), (("1", "2"), {}), (("2", "1"), {}),
+                         (("2", "2"), {"ELB200_COLL_ARENA": "0"}),          # the per-collective exports over NCCL only
+                         (("2", "3"), {"ELB200_ARENA_KB": "4"})):            # messages that do not fit a slot fall back
+        r = subprocess.run([exe, *shape], capture_output=True, text=True, timeout=300,
+                           env=dict(os.environ, **{"ELB200_ARENA_MB": "8", "HOSTSIM_TIMEOUT": "90", **extra}))
+        assert r.returncode == 0 and "FACADE_RANKS_PASS" in r.stdout, (shape, extra, r.stdout[-2000:] + r.stderr[-2000:])
 
 
 # ---------------------------------------------------------------------------------------------

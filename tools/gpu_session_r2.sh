@@ -29,6 +29,48 @@ case $STAGE in
       -o $OUT/ncu_f64_ws tools/native_bench f64 8192 > $OUT/ncu_f64_ws.log 2>&1; log "ncu f64 exit $?"
   timeout 600 ncu --set full --clock-control none -c 12 -o $OUT/ncu_f64_all tools/native_bench f64 4096 > $OUT/ncu_f64_all.log 2>&1; log "ncu f64 all exit $?"
   ;;
+1b)
+  # re-run of the measurement half of 1a with small outputs: ncu reports stay in /tmp on the box, only CSV / text exports come back
+  log "=== bench.py"; timeout 900 python bench.py --steps 10 --warmup 5 > $OUT/bench_1gpu.json 2> $OUT/bench_1gpu.err; log "exit $?"
+  for v in "X=0" "ELB200_F64_WS=1" "ELB200_F64_TMA=1"; do
+    log "=== f64 variant $v"
+    echo "##### $v" >> $OUT/f64_variants.log
+    env $v timeout 120 tools/gemm_check correctness f64 >> $OUT/f64_variants.log 2>&1; log "correctness exit $?"
+    env $v timeout 120 tools/native_bench f64 8192 >> $OUT/f64_variants.log 2>&1; log "native_bench exit $?"
+    env $v timeout 300 tools/gemm_check perf f64 16384 >> $OUT/f64_variants.log 2>&1; log "perf exit $?"
+  done
+  ELB200_F64_WS=1 timeout 600 ncu --set full --import-source on --clock-control none -k regex:gemm_f64 -c 1 \
+      -o /tmp/ncu_f64_ws tools/native_bench f64 8192 > $OUT/ncu_f64_ws.log 2>&1; log "ncu f64 ws exit $?"
+  ncu -i /tmp/ncu_f64_ws.ncu-rep --page raw --csv > $OUT/ncu_f64_ws_raw.csv 2>/dev/null
+  ncu -i /tmp/ncu_f64_ws.ncu-rep --page details > $OUT/ncu_f64_ws_details.txt 2>/dev/null
+  ncu -i /tmp/ncu_f64_ws.ncu-rep --page source --csv > $OUT/ncu_f64_ws_source.csv 2>/dev/null
+  timeout 600 ncu --set full --clock-control none -c 14 -o /tmp/ncu_f64_all tools/native_bench f64 4096 > $OUT/ncu_f64_all.log 2>&1; log "ncu f64 all exit $?"
+  ncu -i /tmp/ncu_f64_all.ncu-rep --page raw --csv > $OUT/ncu_f64_all_raw.csv 2>/dev/null
+  ncu -i /tmp/ncu_f64_all.ncu-rep --page details > $OUT/ncu_f64_all_details.txt 2>/dev/null
+  du -sh $OUT | tee -a $OUT/session.log
+  ;;
+1c)
+  # fp64 tile shapes: multi-CTA-per-SM tiles (64 x 64 x 16 x 3 CTAs, 128 x 64 x 16 x 2 CTAs) against the one-CTA kernels
+  for v in "ELB200_F64_TILE=64" "ELB200_F64_TILE=12864" "ELB200_F64_TILE=128" "ELB200_F64_TILE=128 ELB200_F64_WS=1"; do
+    log "=== f64 variant $v"
+    echo "##### $v" >> $OUT/f64_variants.log
+    env $v timeout 120 tools/gemm_check correctness f64 >> $OUT/f64_variants.log 2>&1; log "correctness exit $?"
+    env $v timeout 120 tools/native_bench f64 8192 >> $OUT/f64_variants.log 2>&1; log "native_bench exit $?"
+    env $v timeout 300 tools/gemm_check perf f64 16384 >> $OUT/f64_variants.log 2>&1; log "perf exit $?"
+  done
+  echo "##### TMA" >> $OUT/f64_variants.log
+  ELB200_F64_TILE=128 ELB200_F64_TMA=1 timeout 60 tools/native_bench f64 4096 >> $OUT/f64_variants.log 2>&1; log "tma exit $?"
+  log "=== pytest kernels (default fp64 tile)"; timeout 900 python -m pytest tests/test_gpu_kernels.py -m gpu -x -q > $OUT/pytest_kernels.log 2>&1; log "exit $?"; tail -2 $OUT/pytest_kernels.log | tee -a $OUT/session.log
+  run timeout 120 tools/el_api_check
+  run timeout 120 tools/el_comm_check
+  for t in 64 12864; do
+    ELB200_F64_TILE=$t timeout 600 ncu --set full --import-source on --clock-control none -k regex:tile_kernel -c 1 \
+        -o /tmp/ncu_f64_t$t tools/native_bench f64 8192 > $OUT/ncu_f64_t$t.log 2>&1; log "ncu tile $t exit $?"
+    ncu -i /tmp/ncu_f64_t$t.ncu-rep --page raw --csv > $OUT/ncu_f64_t${t}_raw.csv 2>/dev/null
+    ncu -i /tmp/ncu_f64_t$t.ncu-rep --page details > $OUT/ncu_f64_t${t}_details.txt 2>/dev/null
+  done
+  du -sh $OUT | tee -a $OUT/session.log
+  ;;
 multi)
   run timeout 900 $TR tests/dist_worker.py
   run timeout 900 $TR tests/dist_worker.py --level3
