@@ -257,6 +257,54 @@ class Ctx:
         return self.pool
 
 
+def bind_to_gpu_numa_node(torch, local: int) -> dict:
+    """Pin this rank's host threads (and with them the first-touch placement of the pinned buffers it allocates next)
+    to the NUMA node its GPU hangs off, read from sysfs. Harmless where the box exposes one node."""
+    info = {"node": None, "cpus": None}
+    try:
+        pr = torch.cuda.get_device_properties(local)
+        bus = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        with open(f"/sys/bus/pci/devices/{bus}/numa_node") as f:
+            node = int(f.read().strip())
+        info["node"] = node
+        if node >= 0:
+            with open(f"/sys/devices/system/node/node{node}/cpulist") as f:
+                cpus = set()
+                for part in f.read().strip().split(","):
+                    a, _, b = part.partition("-")
+                    cpus.update(range(int(a), int(b or a) + 1))
+            cpus &= os.sched_getaffinity(0)
+            if cpus:
+                os.sched_setaffinity(0, cpus)
+                info["cpus"] = len(cpus)
+    except Exception as ex:  # noqa: BLE001 — a box without that sysfs layout just keeps its affinity
+        info["error"] = f"{type(ex).__name__}: {ex}"
+    return info
+
+
+def pcie_probe(ctx: Ctx) -> dict:
+    """Host <-> device copy rates with EVERY rank copying at once (1 GiB pinned, 3 repetitions each way): the ceiling the
+    e2e leg runs against on this box — PCIe switches and host memory are shared between the GPUs of a node."""
+    torch = ctx.torch
+    nbytes = 1 << 30
+    host = ctx.host_pool(nbytes)[:nbytes]
+    dev = torch.empty(nbytes, dtype=torch.uint8, device=ctx.dev)
+    out = {}
+    for name, (dst, src) in (("h2d", (dev, host)), ("d2h", (host, dev))):
+        dst.copy_(src, non_blocking=True)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ctx.barrier()
+        e0.record()
+        for _ in range(3):
+            dst.copy_(src, non_blocking=True)
+        e1.record()
+        ctx.barrier()
+        ms = ctx.max_over_ranks(e0.elapsed_time(e1) / 3)
+        out[f"{name}_gbs_per_gpu_all_ranks_at_once"] = nbytes / (ms * 1e-3) / 1e9
+    del dev
+    return out
+
+
 def dist_matvec(ctx: Ctx, M, X):
     """M @ X for an [MC,MR] zero-aligned DistMatrix M (height x width) and a full (width x nv) fp64 tensor X
     that every rank holds: each rank multiplies its local entries in fp64 and the partial rows are summed over
@@ -545,12 +593,14 @@ def run_ours(args) -> int:
     from elemental_b200 import el
     from elemental_b200._lib import lib
 
+    numa = bind_to_gpu_numa_node(torch, local)
     grid = el.Grid(device=local)
     line, ok = None, True
     try:
         # everything that touches the grid's streams (DistMatrices, pinned host tensors) lives inside
         # _measure and is released before the grid is closed
         ctx = Ctx(args, grid, el, lib, torch, dist, world, rank, local)
+        ctx.numa = numa
         line, ok = _measure(ctx)
         ctx.pool = None
     finally:
@@ -582,6 +632,7 @@ def _measure(ctx: Ctx):
     parity = None
     if not args.no_parity:
         parity = parity_pass(ctx)
+    pcie = pcie_probe(ctx) if not args.no_e2e else None
     libpk = library_peaks(ctx) if rank == 0 else {}
     ok = True
     for rec in (main, strong, sub):
@@ -600,7 +651,7 @@ def _measure(ctx: Ctx):
         cpu = {"value": v, "unit": UNIT, **info}
     esz = 4 if args.dtype == "f32" else 8
     cfg = make_config(args, n_gpus, n)
-    detail = {"grid": main["grid"],
+    detail = {"grid": main["grid"], "numa": getattr(ctx, "numa", None),
                 "l2": (f"inputs {3 * n * n * esz / n_gpus / 2**20:.0f} MiB per GPU > 126 MB L2 (no flush needed)" if 3 * n * n * esz / n_gpus > 2 * 126e6
                        else f"inputs {3 * n * n * esz / n_gpus / 2**20:.0f} MiB per GPU fit the 126 MB L2: --n diagnostic line, not a bench value"),
                 "panel_k": "full k on 1x1; ELB200_PANEL_K (default 4096 fp32 / 2048 fp64) otherwise",
@@ -621,7 +672,17 @@ def _measure(ctx: Ctx):
             "accuracy": main["accuracy"],
             "strong_n32768": public(strong, args.dtype) if strong is not None else ("same as the headline (N = 1)" if n == FIXED_N else None),
             ("fp64" if other == "f64" else "fp32"): public(sub, other),
-            "parity": parity, "library_peaks": libpk, "ok": ok}
+            "parity": parity, "library_peaks": libpk, "pcie": pcie, "ok": ok}
+    if pcie and main.get("e2e"):
+        # what the measured copy rates allow: uploads and downloads overlap (separate copy engines, full duplex), the
+        # products hide under them or they under the products
+        per_gpu_up = main["e2e"]["h2d_bytes_per_step"] / n_gpus
+        per_gpu_down = main["e2e"]["d2h_bytes_per_step"] / n_gpus
+        bound_ms = max(per_gpu_up / (pcie["h2d_gbs_per_gpu_all_ranks_at_once"] * 1e6), per_gpu_down / (pcie["d2h_gbs_per_gpu_all_ranks_at_once"] * 1e6),
+                       main["ms_per_step"])
+        line["e2e"]["bound_ms"] = bound_ms
+        line["e2e"]["frac_of_bound"] = bound_ms / main["e2e"]["ms_per_step"]
+        line["e2e"]["bound_basis"] = "max(device-resident step, per-GPU H2D bytes / measured concurrent H2D rate, D2H likewise)"
     if main.get("e2e_error"):
         line["e2e_error"] = main["e2e_error"]
     return line, ok

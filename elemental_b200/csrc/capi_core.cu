@@ -106,7 +106,7 @@ unsigned long long elb200_launch_count(void) { return g_launches.load(std::memor
 
 const char* elb200_build_info(void) {
     return "libelb200 sm_100a: gemm_f32 tcgen05 3xTF32 (TMA+TMEM, cta_group 1/2), "
-           "gemm_f64 DMMA m8n8k4 (cp.async x3, BK 32), trsm (recursive GEMM + 32x32 base), blas1 vectorised, trapezoid, lattice pack/unpack, "
+           "gemm_f64 DMMA m8n8k4 (64x64x16 tiles, 4 CTAs/SM, cp.async ring), trsm (recursive GEMM + 32x32 base), blas1 vectorised, trapezoid, lattice pack/unpack, "
            "NVLink peer-memory AllGather / ReduceScatter (copy engines + stream memops), NCCL fallback";
 }
 

@@ -22,9 +22,4 @@ int gemm_f64_dmma(int transA, int transB, int64_t m, int64_t n, int64_t k, doubl
                   const double* A, int64_t lda, const double* B, int64_t ldb, double beta,
                   double* C, int64_t ldc, cudaStream_t stream);
 
-// TMA-fed variant (gemm_f64_tma.cu, ELB200_F64_TMA=1, experimental): -1 when the operands do not qualify.
-int gemm_f64_dmma_tma(int transA, int transB, int64_t m, int64_t n, int64_t k, double alpha,
-                      const double* A, int64_t lda, const double* B, int64_t ldb, double beta,
-                      double* C, int64_t ldc, cudaStream_t stream);
-
 }  // namespace elb

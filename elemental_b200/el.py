@@ -107,10 +107,18 @@ class Grid:
     def Col(self): return self.MRRank()
     def VRRank(self): return self.MRRank() + self.width * self.MCRank()
 
+    # Grid::MCComm / MRComm / VCComm / VRComm (Grid.hpp:62-75); VRComm is built on first use (collective)
+    def MCComm(self) -> "Comm": return _grid_comm(self, 0)
+    def MRComm(self) -> "Comm": return _grid_comm(self, 1)
+    def VCComm(self) -> "Comm": return _grid_comm(self, 2)
+    def VRComm(self) -> "Comm": return _grid_comm(self, 3)
+
     def sync(self) -> None:
         check(lib.elb200_grid_sync(self._h), "Grid.sync")
 
     def close(self) -> None:
+        for c in self.__dict__.pop("_comms", {}).values():
+            c.free()
         if getattr(self, "_h", None):
             lib.elb200_grid_destroy(self._h)
             self._h = None
@@ -120,6 +128,68 @@ class Grid:
             self.close()
         except Exception:
             pass
+
+
+class Comm:
+    """mpi::Comm (include/El/core/imports/mpi/comm.hpp): a handle to a libelb200 communicator — NCCL plus, for a grid's
+    MC / MR / VC communicators, the NVLink peer arena. Obtained from Grid.MCComm() ... or Comm.world()."""
+
+    def __init__(self, handle, grid=None):
+        self._h, self._grid = handle, grid
+
+    @staticmethod
+    def world() -> "Comm":
+        h = C.c_void_p()
+        check(lib.elb200_comm_world(C.byref(h)), "mpi::COMM_WORLD")
+        return Comm(h)
+
+    def Rank(self) -> int: return lib.elb200_comm_rank(self._h)
+    def Size(self) -> int: return lib.elb200_comm_size(self._h)
+
+    def free(self) -> None:
+        if self._h:
+            lib.elb200_comm_free(self._h)
+            self._h = None
+
+
+def _grid_comm(grid: "Grid", which: int) -> Comm:
+    cache = grid.__dict__.setdefault("_comms", {})
+    if which not in cache:
+        h = C.c_void_p()
+        check(lib.elb200_grid_comm(grid._h, which, C.byref(h)), "Grid communicator")
+        cache[which] = Comm(h, grid)
+    return cache[which]
+
+
+def _coll(fn, name, *args):
+    check(fn(*args), name)
+
+
+# mpi::AllGather / ReduceScatter / AllReduce / AllToAll / SendRecv / Broadcast on torch CUDA tensors
+# (src/core/imports/mpi/*.hpp): equal counts, asynchronous on `stream` (a cudaStream_t as int, default stream 0).
+def AllGather(sbuf: torch.Tensor, rbuf: torch.Tensor, comm: Comm, stream: int = 0) -> None:
+    _coll(lib.elb200_allgather, "mpi::AllGather", sbuf.data_ptr(), rbuf.data_ptr(), sbuf.numel(), _DTYPES[sbuf.dtype], comm._h, stream)
+
+
+def ReduceScatter(sbuf: torch.Tensor, rbuf: torch.Tensor, comm: Comm, stream: int = 0) -> None:
+    _coll(lib.elb200_reduce_scatter, "mpi::ReduceScatter", sbuf.data_ptr(), rbuf.data_ptr(), rbuf.numel() if sbuf.data_ptr() != rbuf.data_ptr() else sbuf.numel() // comm.Size(),
+          _DTYPES[sbuf.dtype], comm._h, stream)
+
+
+def AllReduce(sbuf: torch.Tensor, rbuf: torch.Tensor, comm: Comm, stream: int = 0) -> None:
+    _coll(lib.elb200_allreduce, "mpi::AllReduce", sbuf.data_ptr(), rbuf.data_ptr(), sbuf.numel(), _DTYPES[sbuf.dtype], comm._h, stream)
+
+
+def AllToAll(sbuf: torch.Tensor, rbuf: torch.Tensor, comm: Comm, stream: int = 0) -> None:
+    _coll(lib.elb200_alltoall, "mpi::AllToAll", sbuf.data_ptr(), rbuf.data_ptr(), sbuf.numel() // comm.Size(), _DTYPES[sbuf.dtype], comm._h, stream)
+
+
+def SendRecv(sbuf: torch.Tensor, to: int, rbuf: torch.Tensor, frm: int, comm: Comm, stream: int = 0) -> None:
+    _coll(lib.elb200_sendrecv, "mpi::SendRecv", sbuf.data_ptr(), sbuf.numel(), to, rbuf.data_ptr(), rbuf.numel(), frm, _DTYPES[sbuf.dtype], comm._h, stream)
+
+
+def Broadcast(buf: torch.Tensor, root: int, comm: Comm, stream: int = 0) -> None:
+    _coll(lib.elb200_bcast, "mpi::Broadcast", buf.data_ptr(), buf.numel(), _DTYPES[buf.dtype], root, comm._h, stream)
 
 
 class DistMatrix:

@@ -148,6 +148,78 @@ def test_gemm_full_size_properties(grid1, dtype, alg):
         M.destroy()
 
 
+def test_collective_exports_1x1(grid1):
+    """Every per-collective export (elb200_allgather / reduce_scatter / allreduce / alltoall / sendrecv / bcast) over the
+    grid's four communicators; on one rank each is its defined local copy (src/core/imports/mpi/AllGather.hpp:17,
+    ReduceScatter.hpp:47-48). The non-degenerate forms run in tests/dist_worker.py and in bench.py's parity pass."""
+    from tests import dist_cases as dc
+    assert dc.check_collectives(grid1, torch.float64) == 56
+    assert dc.check_collectives(grid1, torch.float32) == 56
+
+
+def test_comm_api_and_python_mirror(grid1):
+    """Communicator handles: world bootstrap on one rank, split / dup / free, rank / size queries, argument errors, and
+    the el.AllGather ... wrappers on torch tensors."""
+    import ctypes as C
+    from elemental_b200 import el
+    from elemental_b200._lib import lib
+    w = C.c_void_p()
+    assert lib.elb200_comm_world(C.byref(w)) == 0 and lib.elb200_comm_size(w) == 1 and lib.elb200_comm_rank(w) == 0
+    h, d = C.c_void_p(), C.c_void_p()
+    assert lib.elb200_comm_split(w, 3, 0, C.byref(h)) == 0 and lib.elb200_comm_size(h) == 1
+    assert lib.elb200_comm_dup(h, C.byref(d)) == 0 and lib.elb200_comm_rank(d) == 0
+    none = C.c_void_p(1)
+    assert lib.elb200_comm_split(w, -1, 0, C.byref(none)) == 0 and not none.value      # MPI_UNDEFINED
+    assert lib.elb200_comm_barrier(d) == 0
+    assert lib.elb200_comm_free(d) == 0 and lib.elb200_comm_free(h) == 0
+    g2 = C.c_void_p()
+    assert lib.elb200_grid_create_on(w, 2, 1, -1, C.byref(g2)) == 2                       # height 2 does not divide 1 rank
+    assert lib.elb200_grid_create_on(w, 1, 0, -1, C.byref(g2)) == 0                       # ROW_MAJOR 1 x 1
+    assert lib.elb200_grid_destroy(g2) == 0
+    mc = grid1.MCComm()
+    assert (mc.Rank(), mc.Size(), grid1.VRComm().Size()) == (0, 1, 1)
+    x = torch.arange(10, dtype=torch.float32, device="cuda")
+    y = torch.zeros_like(x)
+    torch.cuda.synchronize()
+    el.AllGather(x, y, mc)
+    el.AllReduce(x, y, grid1.VCComm())
+    el.Broadcast(y, 0, grid1.MRComm())
+    torch.cuda.synchronize()
+    assert torch.equal(x, y)
+    assert lib.elb200_sendrecv(x.data_ptr(), 10, 1, y.data_ptr(), 10, 0, 0, mc._h, None) == 2     # peer out of range
+    assert lib.elb200_allgather(x.data_ptr(), y.data_ptr(), 10, 7, mc._h, None) == 2              # unknown dtype
+
+
+def test_matrix_streams_and_multisync(grid1):
+    """elb200_dm_set_stream / elb200_dm_stream (SetSyncInfo / SyncInfoFromMatrix) and the MakeMultiSync(C, A, B)
+    ordering inside elb200_dist_gemm: operands written on their own streams right before the call are seen."""
+    from elemental_b200 import el
+    from elemental_b200._lib import lib
+    from oracle import gemm as OG
+    n = 256
+    A = el.DistMatrix(grid1, dtype=torch.float64).Resize(n, n)
+    B = el.DistMatrix(grid1, dtype=torch.float64).Resize(n, n)
+    Cm = el.DistMatrix(grid1, dtype=torch.float64).Resize(n, n)
+    grid1.sync()
+    sa, sb = torch.cuda.Stream(), torch.cuda.Stream()
+    assert lib.elb200_dm_stream(A._h) == grid1.stream.cuda_stream
+    assert lib.elb200_dm_set_stream(A._h, sa.cuda_stream) == 0 and lib.elb200_dm_set_stream(B._h, sb.cuda_stream) == 0
+    assert lib.elb200_dm_stream(A._h) == sa.cuda_stream
+    a = OG.uniform_matrix(n, n, 5, np.float64)
+    b = OG.uniform_matrix(n, n, 6, np.float64)
+    with torch.cuda.stream(sa):
+        big = torch.randn(4096, 4096, device="cuda") @ torch.randn(4096, 4096, device="cuda")   # keeps sa busy first
+        A.Matrix().copy_(torch.from_numpy(a).cuda())
+    with torch.cuda.stream(sb):
+        B.Matrix().copy_(torch.from_numpy(b).cuda())
+    el.Gemm(el.NORMAL, el.NORMAL, 1.0, A, B, 0.0, Cm)
+    grid1.sync()
+    err = OG.frobenius_rel_err(Cm.get_local(), a @ b)
+    assert err <= OG.gemm_tolerance(np.float64, n), err
+    assert lib.elb200_dm_set_stream(A._h, None) == 0 and lib.elb200_dm_stream(A._h) == grid1.stream.cuda_stream
+    del big
+
+
 @pytest.mark.parametrize("nproc,height", [(2, 1), (2, 2), (4, 2), (8, 2)])
 def test_multi_gpu_grids(nproc, height):
     if torch.cuda.device_count() < nproc:

@@ -71,6 +71,23 @@ case $STAGE in
   done
   du -sh $OUT | tee -a $OUT/session.log
   ;;
+1d)
+  for v in "ELB200_F64_TILE=64" "ELB200_F64_TILE=644"; do
+    log "=== f64 variant $v"
+    echo "##### $v" >> $OUT/f64_variants.log
+    env $v timeout 120 tools/gemm_check correctness f64 >> $OUT/f64_variants.log 2>&1; log "correctness exit $?"
+    env $v timeout 120 tools/native_bench f64 8192 >> $OUT/f64_variants.log 2>&1; log "native_bench exit $?"
+    env $v timeout 300 tools/gemm_check perf f64 16384 >> $OUT/f64_variants.log 2>&1; log "perf exit $?"
+  done
+  for t in 64 644; do
+    ELB200_F64_TILE=$t timeout 600 ncu --set full --import-source on --clock-control none -k regex:tile_kernel -c 1 \
+        -o /tmp/ncu_f64_t$t tools/native_bench f64 8192 > $OUT/ncu_f64_t$t.log 2>&1; log "ncu tile $t exit $?"
+    ncu -i /tmp/ncu_f64_t$t.ncu-rep --page raw --csv > $OUT/ncu_f64_t${t}_raw.csv 2>/dev/null
+    ncu -i /tmp/ncu_f64_t$t.ncu-rep --page source --csv > $OUT/ncu_f64_t${t}_source.csv 2>/dev/null
+  done
+  log "=== bench.py"; timeout 900 python bench.py --steps 10 --warmup 5 > $OUT/bench_1gpu.json 2> $OUT/bench_1gpu.err; log "exit $?"
+  du -sh $OUT | tee -a $OUT/session.log
+  ;;
 multi)
   run timeout 900 $TR tests/dist_worker.py
   run timeout 900 $TR tests/dist_worker.py --level3
