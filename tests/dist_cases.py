@@ -317,6 +317,20 @@ def check_gemm_pipeline(grid, dtype=torch.float64) -> int:
     return cnt
 
 
+def check_gemm_ragged_slot_boundary(grid, dtype=torch.float64) -> int:
+    """SUMMA-C (NN, aligned) with m, n NOT divisible by the grid, so local heights / widths differ by one across ranks.
+    Every rank must derive the same panel width and take the same branch (zero-copy direct panels or the staged
+    fallback) — the decision is made from the largest local extents on the grid. tests/test_hostsim.py runs this with an
+    arena slot sized so that a rank-local decision would split the grid (ELB200_ARENA_KB=311: 75 local rows fit 512
+    panel columns, 76 do not)."""
+    cnt = 0
+    for (m, n, k) in ((151, 120, 1300), (151, 121, 1300), (150, 121, 700)):
+        err, tol = gemm_case(grid, dtype, 0, 0, el.GEMM_SUMMA_C, m, n, k, alpha=0.5, beta=-0.5)
+        assert err <= tol, (m, n, k, err, tol)
+        cnt += 1
+    return cnt
+
+
 def check_trapezoids(grid, dtype=torch.float64) -> int:
     """ScaleTrapezoid / MakeTrapezoidal / AxpyTrapezoid / MakeSymmetric (level-1 trapezoid headers) on
     several distributions, alignments and offsets: data movement and exact products only (alpha is a

@@ -89,6 +89,14 @@ def test_engine_tiny_arena_falls_back(simlib):
          env={"ELB200_ARENA_KB": "4", "ELB200_PANEL_K": "16"})
 
 
+def test_ragged_operands_at_the_slot_boundary_take_one_branch(simlib):
+    """m, n not divisible by the grid and an arena slot that holds a 512-wide panel for 75 local rows but not for 76: a
+    panel width derived from each rank's OWN local extents would send half the grid down the zero-copy path and the other
+    half down the staged one (mismatched collectives -> hang). Also run with roomy and with tiny slots."""
+    for kb in ("311", "4096", "16"):
+        _run("2x2,2x3", "--only", "check_gemm_ragged_slot_boundary,check_gemm_ragged_slot_boundary_f32", env={"ELB200_ARENA_KB": kb, "HOSTSIM_TIMEOUT": "60"})
+
+
 @pytest.mark.parametrize("grid,hwq", [("2x4", "1")])
 def test_engine_survives_shared_hardware_queues(simlib, grid, hwq):
     """HOSTSIM_HWQ=N spreads a rank's streams over N work queues executed in ISSUE order (the false dependencies

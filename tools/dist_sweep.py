@@ -51,11 +51,30 @@ def fill(grid, M, seed):
         v.copy_((torch.rand(v.shape, device=v.device, dtype=v.dtype, generator=g) - 0.5) * 0.2)
 
 
-def run_c4(el, grid, world, rank, local, max_bytes, rows):
+def verify_gather(grid, A, B1, world, local):
+    """[MC,MR] -> [MC,*] moved every entry exactly once: the sum of my gathered local matrix equals the sum of the local
+    sums of the ranks of my grid row (all entries are exactly representable partial sums in fp64 up to rounding)."""
+    dev = f"cuda:{local}"
+    with torch.cuda.stream(grid.stream):
+        mine = A.Matrix().double().sum().reshape(1)
+        got = B1.Matrix().double().sum()
+    grid.sync()
+    sums = [torch.zeros(1, dtype=torch.float64, device=dev) for _ in range(world)]
+    if world > 1:
+        dist.all_gather(sums, mine)
+    else:
+        sums = [mine]
+    r = grid.Height()
+    want = sum(float(sums[q].item()) for q in range(world) if q % r == grid.MCRank())
+    scale = max(abs(want), 1.0)
+    return abs(float(got.item()) - want) / scale
+
+
+def run_c4(el, grid, world, rank, local, max_bytes, rows, min_bytes=0):
     r, c = grid.Height(), grid.Width()
     for tdt, name, esz in ((torch.float32, "f32", 4), (torch.float64, "f64", 8)):
         for S in (1 << 20, 4 << 20, 16 << 20, 64 << 20, 256 << 20, 1 << 30, 4 << 30, 8 << 30):
-            if S > max_bytes:
+            if S > max_bytes or S < min_bytes:
                 continue
             n = int((S / esz) ** 0.5) // 64 * 64
             A = el.DistMatrix(grid, el.MC, el.MR, tdt).Resize(n, n)
@@ -63,6 +82,9 @@ def run_c4(el, grid, world, rank, local, max_bytes, rows):
             B1 = el.DistMatrix(grid, el.MC, el.STAR, tdt).Resize(n, n)
             t1 = timed(grid, lambda: el.Copy(A, B1), world, local)
             out1 = B1.LocalHeight() * B1.LocalWidth() * esz
+            if S >= (1 << 30):
+                err = verify_gather(grid, A, B1, world, local)
+                assert err < 1e-9, f"gather checksum off by {err:.3e} at S={S}"
             B2 = el.DistMatrix(grid, el.STAR, el.VR, tdt).Resize(n, n)
             t2 = timed(grid, lambda: el.Copy(A, B2), world, local)
             out2 = B2.LocalHeight() * B2.LocalWidth() * esz
@@ -110,6 +132,7 @@ def main():
     ap.add_argument("--c4", action="store_true")
     ap.add_argument("--c5", action="store_true")
     ap.add_argument("--max-bytes", type=int, default=1 << 30, help="largest global matrix of the C4 sweep")
+    ap.add_argument("--min-bytes", type=int, default=0, help="smallest global matrix of the C4 sweep")
     ap.add_argument("--k", type=int, default=262144)
     ap.add_argument("--out", default="")
     args = ap.parse_args()
@@ -124,7 +147,7 @@ def main():
     rows = []
     try:
         if args.c4:
-            run_c4(el, grid, world, rank, local, args.max_bytes, rows)
+            run_c4(el, grid, world, rank, local, args.max_bytes, rows, args.min_bytes)
         if args.c5:
             run_c5(el, grid, world, rank, local, args.k, rows)
     finally:

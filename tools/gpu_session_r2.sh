@@ -91,7 +91,29 @@ case $STAGE in
 multi)
   run timeout 900 $TR tests/dist_worker.py
   run timeout 900 $TR tests/dist_worker.py --level3
+  if [ "$N" = "2" ]; then run timeout 900 $TR tests/dist_worker.py --height 2; fi
+  log "=== el_comm_check under elrun"; timeout 600 tools/elrun $N tools/el_comm_check > $OUT/el_comm_check.log 2>&1; log "exit $?"; tail -3 $OUT/el_comm_check.log | tee -a $OUT/session.log
+  log "=== el_gemm_driver under elrun"; ELB_ID_FILE=/tmp/elb_id_$$ RANK=0 timeout 10 true; timeout 600 tools/elrun $N tools/el_comm_check --gridHeight 1 > $OUT/el_comm_check_h1.log 2>&1; log "exit $?"; tail -2 $OUT/el_comm_check_h1.log | tee -a $OUT/session.log
   log "=== bench.py N=$N"; timeout 900 $TR bench.py --gpus $N --steps 10 --warmup 5 > $OUT/bench_${N}gpu.json 2> $OUT/bench_${N}gpu.err; log "exit $?"
+  ;;
+big)
+  # 8 GPUs: parity on 2 x 4, the communicator facade, the bench line, C4 / C5 sweeps incl. the 4 and 8 GB points
+  run timeout 900 $TR tests/dist_worker.py
+  run timeout 900 $TR tests/dist_worker.py --level3
+  log "=== el_comm_check under elrun"; timeout 600 tools/elrun $N tools/el_comm_check > $OUT/el_comm_check.log 2>&1; log "exit $?"; tail -2 $OUT/el_comm_check.log | tee -a $OUT/session.log
+  log "=== bench.py N=$N"; timeout 1200 $TR bench.py --gpus $N --steps 10 --warmup 5 > $OUT/bench_${N}gpu.json 2> $OUT/bench_${N}gpu.err; log "exit $?"
+  log "=== dist_sweep c4 c5"; timeout 900 $TR tools/dist_sweep.py --c4 --c5 --out $OUT/dist_sweep_${N}gpu.json > $OUT/dist_sweep.log 2>&1; log "exit $?"
+  log "=== dist_sweep c4 large"; ELB200_ARENA_MB=4096 timeout 900 $TR tools/dist_sweep.py --c4 --min-bytes 4294967296 --max-bytes 8589934592 --out $OUT/dist_sweep_${N}gpu_large.json > $OUT/dist_sweep_large.log 2>&1; log "exit $?"
+  ;;
+switches)
+  # 4 GPUs: the opt-in switches that never met hardware — parity with each on, then its A/B
+  log "=== bench.py N=$N"; timeout 1200 $TR bench.py --gpus $N --steps 10 --warmup 5 > $OUT/bench_${N}gpu.json 2> $OUT/bench_${N}gpu.err; log "exit $?"
+  log "=== dist_sweep baseline"; timeout 900 $TR tools/dist_sweep.py --c4 --c5 --out $OUT/dist_sweep_${N}gpu.json > $OUT/dist_sweep.log 2>&1; log "exit $?"
+  log "=== AG_SPLIT parity"; ELB200_AG_SPLIT_MB=4 timeout 900 $TR tests/dist_worker.py > $OUT/dist_worker_agsplit.log 2>&1; log "exit $?"
+  log "=== AG_SPLIT sweep"; ELB200_AG_SPLIT_MB=4 timeout 900 $TR tools/dist_sweep.py --c4 --min-bytes 16777216 --out $OUT/dist_sweep_${N}gpu_agsplit.json > $OUT/dist_sweep_agsplit.log 2>&1; log "exit $?"
+  log "=== AG_SPLIT no-rotate sweep"; ELB200_AG_SPLIT_MB=4 ELB200_AG_ROTATE=0 timeout 900 $TR tools/dist_sweep.py --c4 --min-bytes 16777216 --out $OUT/dist_sweep_${N}gpu_agsplit_norot.json > $OUT/dist_sweep_agsplit_norot.log 2>&1; log "exit $?"
+  log "=== AB_PIPELINE parity"; ELB200_AB_PIPELINE=1 timeout 900 $TR tests/dist_worker.py > $OUT/dist_worker_abpipe.log 2>&1; log "exit $?"
+  log "=== DOT_PIPELINE off c5"; ELB200_DOT_PIPELINE=0 timeout 900 $TR tools/dist_sweep.py --c5 --out $OUT/dist_sweep_${N}gpu_nodotpipe.json > $OUT/dist_sweep_nodotpipe.log 2>&1; log "exit $?"
   ;;
 *)
   echo "unknown stage $STAGE"; exit 2;;
