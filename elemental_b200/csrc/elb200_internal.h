@@ -1,6 +1,7 @@
 // Internal C++ declarations shared by the .cu translation units of libelb200.
 #pragma once
 #include <cuda_runtime.h>
+#include <atomic>
 #include <cstdint>
 
 #include "../../include/elb200.h"
@@ -8,6 +9,20 @@
 namespace elb {
 
 int device_sm_count();
+
+// cudaFuncSetAttribute (dynamic shared memory opt-in) is per DEVICE: one flag per device and kernel instantiation, so a
+// process that drives several GPUs configures each of them (a process-wide `static bool` would skip the second device and
+// its first launch there would fail).
+struct PerDeviceOnce {
+    std::atomic<bool> done[64];
+    bool needs(int* dev_out) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { *dev_out = -1; return true; }
+        *dev_out = dev;
+        return !done[dev].load(std::memory_order_acquire);
+    }
+    void set(int dev) { if (dev >= 0) done[dev].store(true, std::memory_order_release); }
+};
 // every kernel launch of this library bumps a process-wide counter (bench.py's gpu_launches)
 void count_launch();
 // > 0: lattice (pack/unpack) kernels launched by this thread use at most this many CTAs

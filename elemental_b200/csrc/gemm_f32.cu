@@ -342,12 +342,13 @@ template <int CG, int AMAJ, int BMAJ>
 cudaError_t launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const Params& p, int num_sms,
                    cudaStream_t stream) {
     auto kern = gemm_f32_3xtf32_kernel<CG, AMAJ, BMAJ>;
-    static bool configured = false;
-    if (!configured) {
+    static PerDeviceOnce once;
+    int dev;
+    if (once.needs(&dev)) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              kSmemBytes);
         if (e != cudaSuccess) return e;
-        configured = true;
+        once.set(dev);
     }
     const int num_tiles = p.tiles_m * p.tiles_n;
     int clusters = num_sms / CG;

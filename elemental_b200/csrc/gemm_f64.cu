@@ -263,18 +263,6 @@ __global__ void __launch_bounds__(C::kThreads, C::MINB) gemm_f64_tile_kernel(con
     }
 }
 
-// cudaFuncSetAttribute is per device: remember which devices have been configured for this instantiation
-struct PerDeviceOnce {
-    std::atomic<bool> done[64];
-    bool needs(int* dev_out) {
-        int dev = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { *dev_out = -1; return true; }
-        *dev_out = dev;
-        return !done[dev].load(std::memory_order_acquire);
-    }
-    void set(int dev) { if (dev >= 0) done[dev].store(true, std::memory_order_release); }
-};
-
 template <class C, bool TA, bool TB, int VEC>
 cudaError_t launch_tile(Params p, cudaStream_t stream) {
     auto kern = gemm_f64_tile_kernel<C, TA, TB, VEC>;
