@@ -24,7 +24,7 @@ lib = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
 
 MAX_SEGMENTS = 64
 UNIQUE_ID_BYTES = 128
-F32, F64 = 0, 1
+F32, F64, BYTE, F16 = 0, 1, 2, 3
 MC, MR, VC, VR, STAR, CIRC = 0, 1, 2, 3, 4, 5
 DIST_NAMES = {MC: "MC", MR: "MR", VC: "VC", VR: "VR", STAR: "STAR", CIRC: "CIRC"}
 # El::GemmAlgorithm, values as in the reference enum (include/El/blas_like/level3.hpp:23-33)
@@ -87,6 +87,15 @@ SIGNATURES = {
     "elb200_launch_count": (C.c_ulonglong, []),
     "elb200_gemm_f32": (ci, [ci, ci, i64, i64, i64, f32, vp, i64, vp, i64, f32, vp, i64, vp]),
     "elb200_gemm_f64": (ci, [ci, ci, i64, i64, i64, f64, vp, i64, vp, i64, f64, vp, i64, vp]),
+    "elb200_gemm_f16": (ci, [ci, ci, i64, i64, i64, f32, vp, i64, vp, i64, f32, vp, i64, vp]),
+    "elb200_copy2d_f16": (ci, [i64, i64, vp, i64, i64, vp, i64, i64, vp]),
+    "elb200_axpy2d_f16": (ci, [i64, i64, f32, vp, i64, i64, vp, i64, i64, vp]),
+    "elb200_scale2d_f16": (ci, [i64, i64, f32, vp, i64, vp]),
+    "elb200_fill2d_f16": (ci, [i64, i64, f32, vp, i64, vp]),
+    "elb200_transpose_f16": (ci, [i64, i64, vp, i64, vp, i64, vp]),
+    "elb200_axpy2d_transpose_f16": (ci, [i64, i64, f32, vp, i64, vp, i64, vp]),
+    "elb200_lattice_f16": (ci, [ci, ci, C.POINTER(Segment), vp, i64, vp, f32, vp]),
+    "elb200_peer_reduce_axpy_f16": (ci, [ci, C.POINTER(vp), i64, C.POINTER(Segment), vp, i64, f32, vp]),
     "elb200_gemm_f32_ex": (ci, [ci, ci, i64, i64, i64, f32, vp, i64, vp, i64, f32, vp, i64, ci, vp]),
     "elb200_gemm_f32_noalloc": (ci, [ci, ci, i64, i64, i64, f32, vp, i64, vp, i64, f32, vp, i64, vp]),
     "elb200_copy2d_f32": (ci, [i64, i64, vp, i64, i64, vp, i64, i64, vp]),

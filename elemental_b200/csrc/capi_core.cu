@@ -212,6 +212,22 @@ int elb200_gemm_f32(int transA, int transB, int64_t m, int64_t n, int64_t k, flo
                               stream);
 }
 
+// half operands and result, fp32 alpha / beta / accumulation
+int elb200_gemm_f16(int transA, int transB, int64_t m, int64_t n, int64_t k, float alpha,
+                    const void* A, int64_t lda, const void* B, int64_t ldb, float beta, void* C,
+                    int64_t ldc, void* stream) {
+    int st = check_gemm_args(transA, transB, m, n, k, A, lda, B, ldb, C, ldc);
+    if (st != ELB200_OK) return st;
+    if (m == 0 || n == 0) return ELB200_OK;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (k == 0 || alpha == 0.f) return elb200_scale2d_f16(m, n, beta, C, ldc, stream);
+    st = gemm_f16_tensor(transA != 0, transB != 0, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, 0, s);
+    if (st == ELB200_ERR_ARG)
+        set_last_error("elb200_gemm_f16", "operands must be 16-byte aligned with leading dimensions that are multiples of 8 halfs");
+    if (st == ELB200_ERR_CUDA) set_last_error("gemm_f16 launch", cudaGetErrorString(cudaGetLastError()));
+    return st;
+}
+
 int elb200_gemm_f64(int transA, int transB, int64_t m, int64_t n, int64_t k, double alpha,
                     const double* A, int64_t lda, const double* B, int64_t ldb, double beta,
                     double* C, int64_t ldc, void* stream) {

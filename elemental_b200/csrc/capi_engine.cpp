@@ -29,7 +29,31 @@ int guarded(const char* where, F&& fn) {
 }
 
 bool same_dtype(elb200_dm_t a, elb200_dm_t b) { return a && b && a->dtype == b->dtype; }
-cudaStream_t dm_stream(elb200_dm_t a) { return a->dtype == ELB200_F32 ? a->f->stream : a->d->stream; }
+cudaStream_t dm_stream(elb200_dm_t a) { return a->dtype == ELB200_F32 ? a->f->stream : a->dtype == ELB200_F64 ? a->d->stream : a->h->stream; }
+bool known_dtype(int dt) { return dt == ELB200_F32 || dt == ELB200_F64 || dt == ELB200_F16; }
+bool level3_dtype(elb200_dm_t a) { return a && (a->dtype == ELB200_F32 || a->dtype == ELB200_F64); }  // the triangular family: float / double only
+
+// element type of a DistMat and the conversion of the ABI's double scalars to it
+template <class M> struct ElemOf;
+template <class T> struct ElemOf<DistMat<T>> { using type = T; };
+template <class M> typename ElemOf<std::decay_t<M>>::type sc(const M&, double v) { return typename ElemOf<std::decay_t<M>>::type(v); }
+
+// run `f` on the typed matrix (matrices) behind one, two or three handles of the same dtype
+template <class F> void on(elb200_dm_t a, F&& f) {
+    if (a->dtype == ELB200_F32) f(*a->f);
+    else if (a->dtype == ELB200_F64) f(*a->d);
+    else f(*a->h);
+}
+template <class F> void on2(elb200_dm_t a, elb200_dm_t b, F&& f) {
+    if (a->dtype == ELB200_F32) f(*a->f, *b->f);
+    else if (a->dtype == ELB200_F64) f(*a->d, *b->d);
+    else f(*a->h, *b->h);
+}
+template <class F> void on3(elb200_dm_t a, elb200_dm_t b, elb200_dm_t c, F&& f) {
+    if (a->dtype == ELB200_F32) f(*a->f, *b->f, *c->f);
+    else if (a->dtype == ELB200_F64) f(*a->d, *b->d, *c->d);
+    else f(*a->h, *b->h, *c->h);
+}
 
 // hydrogen::MultiSync (include/hydrogen/MultiSync.hpp:31-78): on construction the master stream waits for the others,
 // on destruction the others wait for the master — all asynchronously with respect to the host.
@@ -208,14 +232,15 @@ int64_t elb200_local_trrk_blocksize(void) { return Grid::LocalTrrkBlocksize(); }
 void elb200_set_local_trrk_blocksize(int64_t nb) { Grid::SetLocalTrrkBlocksize(nb); }
 
 int elb200_dm_create(elb200_grid_t g, int dtype, int col, int row, elb200_dm_t* out) {
-    if (!g || !out || (dtype != ELB200_F32 && dtype != ELB200_F64)) return ELB200_ERR_ARG;
+    if (!g || !out || !known_dtype(dtype)) return ELB200_ERR_ARG;
     *out = nullptr;
     return guarded("elb200_dm_create", [&] {
         auto h = std::make_unique<elb200_dm_s>();
         h->dtype = dtype;
         h->keep = g->g;
         if (dtype == ELB200_F32) h->f = std::make_unique<DistMat<float>>(*g->g, Dist(col), Dist(row));
-        else h->d = std::make_unique<DistMat<double>>(*g->g, Dist(col), Dist(row));
+        else if (dtype == ELB200_F64) h->d = std::make_unique<DistMat<double>>(*g->g, Dist(col), Dist(row));
+        else h->h = std::make_unique<DistMat<Half>>(*g->g, Dist(col), Dist(row));
         *out = h.release();
     });
 }
@@ -224,11 +249,12 @@ int elb200_dm_destroy(elb200_dm_t a) {
     return guarded("elb200_dm_destroy", [&] { delete a; });
 }
 
+// the triangular family below still dispatches over float / double only
 #define ELB_ON(a, expr_f, expr_d) do { if ((a)->dtype == ELB200_F32) { auto& M = *(a)->f; expr_f; } else { auto& M = *(a)->d; expr_d; } } while (0)
 
 int elb200_dm_info(elb200_dm_t a, elb200_dm_info_t* o) {
     if (!a || !o) return ELB200_ERR_ARG;
-    auto fill = [&](auto& M) {
+    on(a, [&](auto& M) {
         o->dtype = a->dtype; o->col_dist = M.spec.col; o->row_dist = M.spec.row; o->is_view = M.owner ? 0 : 1;
         o->height = M.spec.height; o->width = M.spec.width;
         o->col_align = M.spec.col_align; o->row_align = M.spec.row_align;
@@ -237,41 +263,45 @@ int elb200_dm_info(elb200_dm_t a, elb200_dm_info_t* o) {
         o->local_height = M.lh(); o->local_width = M.lw(); o->ldim = M.ldim;
         o->buffer = M.buf;
         o->root = M.spec.root;
-    };
-    ELB_ON(a, fill(M), fill(M));
+    });
     return ELB200_OK;
 }
 int elb200_dm_align(elb200_dm_t a, int64_t ca, int64_t ra) {
     if (!a) return ELB200_ERR_ARG;
-    return guarded("elb200_dm_align", [&] { ELB_ON(a, M.Align(ca, ra), M.Align(ca, ra)); });
+    return guarded("elb200_dm_align", [&] { on(a, [&](auto& M) { M.Align(ca, ra); }); });
 }
 int elb200_dm_align_with(elb200_dm_t a, elb200_dm_t o) {
     if (!a || !o) return ELB200_ERR_ARG;
     return guarded("elb200_dm_align_with", [&] {
-        const DistSpec s = o->dtype == ELB200_F32 ? o->f->spec : o->d->spec;
-        ELB_ON(a, M.AlignWith(s), M.AlignWith(s));
+        DistSpec s;
+        on(o, [&](auto& M) { s = M.spec; });
+        on(a, [&](auto& M) { M.AlignWith(s); });
     });
 }
 int elb200_dm_set_root(elb200_dm_t a, int root) {
     if (!a) return ELB200_ERR_ARG;
-    return guarded("elb200_dm_set_root", [&] { ELB_ON(a, M.SetRoot(root), M.SetRoot(root)); });
+    return guarded("elb200_dm_set_root", [&] { on(a, [&](auto& M) { M.SetRoot(root); }); });
 }
 int elb200_dm_write_local(elb200_dm_t a, const void* src, int64_t ld) {
     if (!a) return ELB200_ERR_ARG;
-    return guarded("elb200_dm_write_local", [&] { ELB_ON(a, M.WriteLocal(static_cast<const float*>(src), ld), M.WriteLocal(static_cast<const double*>(src), ld)); });
+    return guarded("elb200_dm_write_local", [&] {
+        on(a, [&](auto& M) { M.WriteLocal(static_cast<const typename ElemOf<std::decay_t<decltype(M)>>::type*>(src), ld); });
+    });
 }
 int elb200_dm_read_local(elb200_dm_t a, void* dst, int64_t ld) {
     if (!a) return ELB200_ERR_ARG;
-    return guarded("elb200_dm_read_local", [&] { ELB_ON(a, M.ReadLocal(static_cast<float*>(dst), ld), M.ReadLocal(static_cast<double*>(dst), ld)); });
+    return guarded("elb200_dm_read_local", [&] {
+        on(a, [&](auto& M) { M.ReadLocal(static_cast<typename ElemOf<std::decay_t<decltype(M)>>::type*>(dst), ld); });
+    });
 }
 int elb200_dm_resize(elb200_dm_t a, int64_t h, int64_t w) {
     if (!a) return ELB200_ERR_ARG;
-    return guarded("elb200_dm_resize", [&] { ELB_ON(a, M.Resize(h, w), M.Resize(h, w)); });
+    return guarded("elb200_dm_resize", [&] { on(a, [&](auto& M) { M.Resize(h, w); }); });
 }
 int elb200_dm_attach(elb200_dm_t a, int64_t h, int64_t w, int64_t ca, int64_t ra, void* buf, int64_t ld) {
     if (!a) return ELB200_ERR_ARG;
     return guarded("elb200_dm_attach", [&] {
-        ELB_ON(a, M.Attach(h, w, ca, ra, static_cast<float*>(buf), ld), M.Attach(h, w, ca, ra, static_cast<double*>(buf), ld));
+        on(a, [&](auto& M) { M.Attach(h, w, ca, ra, static_cast<typename ElemOf<std::decay_t<decltype(M)>>::type*>(buf), ld); });
     });
 }
 int elb200_dm_view(elb200_dm_t a, int64_t i0, int64_t i1, int64_t j0, int64_t j1, elb200_dm_t* out) {
@@ -282,35 +312,53 @@ int elb200_dm_view(elb200_dm_t a, int64_t i0, int64_t i1, int64_t j0, int64_t j1
         h->dtype = a->dtype;
         h->keep = a->keep;
         if (a->dtype == ELB200_F32) h->f = std::make_unique<DistMat<float>>(a->f->View(i0, i1, j0, j1));
-        else h->d = std::make_unique<DistMat<double>>(a->d->View(i0, i1, j0, j1));
+        else if (a->dtype == ELB200_F64) h->d = std::make_unique<DistMat<double>>(a->d->View(i0, i1, j0, j1));
+        else h->h = std::make_unique<DistMat<Half>>(a->h->View(i0, i1, j0, j1));
         *out = h.release();
     });
 }
 
 #define ELB_BINARY(NAME, CALL_F, CALL_D)                                                  \
-    if (!same_dtype(A, B)) return ELB200_ERR_ARG;                                         \
+    if (!same_dtype(A, B) || !level3_dtype(A)) return ELB200_ERR_ARG;                     \
     return guarded(NAME, [&] { if (A->dtype == ELB200_F32) { CALL_F; } else { CALL_D; } });
 
-int elb200_dm_copy(elb200_dm_t A, elb200_dm_t B) { ELB_BINARY("elb200_dm_copy", Copy(*A->f, *B->f), Copy(*A->d, *B->d)) }
-int elb200_dm_transpose(elb200_dm_t A, elb200_dm_t B) { ELB_BINARY("elb200_dm_transpose", TransposeCopy(*A->f, *B->f), TransposeCopy(*A->d, *B->d)) }
-int elb200_dm_axpy(double alpha, elb200_dm_t A, elb200_dm_t B) { ELB_BINARY("elb200_dm_axpy", Axpy(float(alpha), *A->f, *B->f), Axpy(alpha, *A->d, *B->d)) }
-int elb200_dm_axpy_contract(double alpha, elb200_dm_t A, elb200_dm_t B) { ELB_BINARY("elb200_dm_axpy_contract", AxpyContract(float(alpha), *A->f, *B->f), AxpyContract(alpha, *A->d, *B->d)) }
-int elb200_dm_contract(elb200_dm_t A, elb200_dm_t B) { ELB_BINARY("elb200_dm_contract", Contract(*A->f, *B->f), Contract(*A->d, *B->d)) }
-int elb200_dm_transpose_axpy_contract(double alpha, elb200_dm_t A, elb200_dm_t B) { ELB_BINARY("elb200_dm_transpose_axpy_contract", TransposeAxpyContract(float(alpha), *A->f, *B->f), TransposeAxpyContract(alpha, *A->d, *B->d)) }
+int elb200_dm_copy(elb200_dm_t A, elb200_dm_t B) {
+    if (!same_dtype(A, B)) return ELB200_ERR_ARG;
+    return guarded("elb200_dm_copy", [&] { on2(A, B, [&](auto& a, auto& b) { Copy(a, b); }); });
+}
+int elb200_dm_transpose(elb200_dm_t A, elb200_dm_t B) {
+    if (!same_dtype(A, B)) return ELB200_ERR_ARG;
+    return guarded("elb200_dm_transpose", [&] { on2(A, B, [&](auto& a, auto& b) { TransposeCopy(a, b); }); });
+}
+int elb200_dm_axpy(double alpha, elb200_dm_t A, elb200_dm_t B) {
+    if (!same_dtype(A, B)) return ELB200_ERR_ARG;
+    return guarded("elb200_dm_axpy", [&] { on2(A, B, [&](auto& a, auto& b) { Axpy(sc(a, alpha), a, b); }); });
+}
+int elb200_dm_axpy_contract(double alpha, elb200_dm_t A, elb200_dm_t B) {
+    if (!same_dtype(A, B)) return ELB200_ERR_ARG;
+    return guarded("elb200_dm_axpy_contract", [&] { on2(A, B, [&](auto& a, auto& b) { AxpyContract(sc(a, alpha), a, b); }); });
+}
+int elb200_dm_contract(elb200_dm_t A, elb200_dm_t B) {
+    if (!same_dtype(A, B)) return ELB200_ERR_ARG;
+    return guarded("elb200_dm_contract", [&] { on2(A, B, [&](auto& a, auto& b) { Contract(a, b); }); });
+}
+int elb200_dm_transpose_axpy_contract(double alpha, elb200_dm_t A, elb200_dm_t B) {
+    if (!same_dtype(A, B)) return ELB200_ERR_ARG;
+    return guarded("elb200_dm_transpose_axpy_contract", [&] { on2(A, B, [&](auto& a, auto& b) { TransposeAxpyContract(sc(a, alpha), a, b); }); });
+}
 
 int elb200_dm_scale(double alpha, elb200_dm_t A) {
     if (!A) return ELB200_ERR_ARG;
-    return guarded("elb200_dm_scale", [&] { ELB_ON(A, Scale(float(alpha), M), Scale(alpha, M)); });
+    return guarded("elb200_dm_scale", [&] { on(A, [&](auto& M) { Scale(sc(M, alpha), M); }); });
 }
 int elb200_dm_zero(elb200_dm_t A) {
     if (!A) return ELB200_ERR_ARG;
-    return guarded("elb200_dm_zero", [&] { ELB_ON(A, Zero(M), Zero(M)); });
+    return guarded("elb200_dm_zero", [&] { on(A, [&](auto& M) { Zero(M); }); });
 }
 int elb200_dm_local_gemm(int ta, int tb, double alpha, elb200_dm_t A, elb200_dm_t B, double beta, elb200_dm_t C) {
     if (!same_dtype(A, B) || !same_dtype(A, C)) return ELB200_ERR_ARG;
     return guarded("elb200_dm_local_gemm", [&] {
-        if (A->dtype == ELB200_F32) LocalGemm(ta, tb, float(alpha), *A->f, *B->f, float(beta), *C->f);
-        else LocalGemm(ta, tb, alpha, *A->d, *B->d, beta, *C->d);
+        on3(A, B, C, [&](auto& a, auto& b, auto& c) { LocalGemm(ta, tb, sc(a, alpha), a, b, sc(a, beta), c); });
     });
 }
 int elb200_dist_gemm(int ta, int tb, double alpha, elb200_dm_t A, elb200_dm_t B, double beta, elb200_dm_t C, int alg) {
@@ -321,8 +369,7 @@ int elb200_dist_gemm(int ta, int tb, double alpha, elb200_dm_t A, elb200_dm_t B,
         // (src/blas_like/level3/Gemm.cpp:172-175): the product runs on C's stream, which first waits for A's and B's;
         // afterwards their streams wait for it.
         StreamJoin join(dm_stream(C), dm_stream(A), dm_stream(B));
-        if (A->dtype == ELB200_F32) Gemm(ta, tb, float(alpha), *A->f, *B->f, float(beta), *C->f, alg);
-        else Gemm(ta, tb, alpha, *A->d, *B->d, beta, *C->d, alg);
+        on3(A, B, C, [&](auto& a, auto& b, auto& c) { Gemm(ta, tb, sc(a, alpha), a, b, sc(a, beta), c, alg); });
     });
 }
 
@@ -331,17 +378,17 @@ int elb200_dist_gemm(int ta, int tb, double alpha, elb200_dm_t A, elb200_dm_t B,
 int elb200_dm_set_stream(elb200_dm_t a, void* stream) {
     if (!a) return ELB200_ERR_ARG;
     cudaStream_t s = stream ? static_cast<cudaStream_t>(stream) : a->grid()->stream;
-    ELB_ON(a, M.stream = s, M.stream = s);
+    on(a, [&](auto& M) { M.stream = s; });
     return ELB200_OK;
 }
 void* elb200_dm_stream(elb200_dm_t a) { return a ? dm_stream(a) : nullptr; }
 int elb200_dm_align_cols(elb200_dm_t a, int64_t ca) {
     if (!a) return ELB200_ERR_ARG;
-    return guarded("elb200_dm_align_cols", [&] { ELB_ON(a, M.AlignCols(ca), M.AlignCols(ca)); });
+    return guarded("elb200_dm_align_cols", [&] { on(a, [&](auto& M) { M.AlignCols(ca); }); });
 }
 int elb200_dm_align_rows(elb200_dm_t a, int64_t ra) {
     if (!a) return ELB200_ERR_ARG;
-    return guarded("elb200_dm_align_rows", [&] { ELB_ON(a, M.AlignRows(ra), M.AlignRows(ra)); });
+    return guarded("elb200_dm_align_rows", [&] { on(a, [&](auto& M) { M.AlignRows(ra); }); });
 }
 
 int elb200_dist_gemm_host_f32(elb200_grid_t g, int ta, int tb, int64_t m, int64_t n, int64_t k, float alpha,
@@ -359,43 +406,43 @@ int elb200_dist_gemm_host_f64(elb200_grid_t g, int ta, int tb, int64_t m, int64_
 
 // ---- triangular rank-k family (engine_level3.cpp) ---------------------------------------------------
 int elb200_dm_scale_trapezoid(double alpha, int uplo, elb200_dm_t A, int64_t offset) {
-    if (!A) return ELB200_ERR_ARG;
+    if (!level3_dtype(A)) return ELB200_ERR_ARG;
     return guarded("elb200_dm_scale_trapezoid", [&] { ELB_ON(A, ScaleTrapezoid(float(alpha), uplo, M, offset), ScaleTrapezoid(alpha, uplo, M, offset)); });
 }
 int elb200_dm_make_trapezoidal(int uplo, elb200_dm_t A, int64_t offset) {
-    if (!A) return ELB200_ERR_ARG;
+    if (!level3_dtype(A)) return ELB200_ERR_ARG;
     return guarded("elb200_dm_make_trapezoidal", [&] { ELB_ON(A, MakeTrapezoidal(uplo, M, offset), MakeTrapezoidal(uplo, M, offset)); });
 }
 int elb200_dm_make_symmetric(int uplo, elb200_dm_t A) {
-    if (!A) return ELB200_ERR_ARG;
+    if (!level3_dtype(A)) return ELB200_ERR_ARG;
     return guarded("elb200_dm_make_symmetric", [&] { ELB_ON(A, MakeSymmetric(uplo, M), MakeSymmetric(uplo, M)); });
 }
 int elb200_dm_axpy_trapezoid(int uplo, double alpha, elb200_dm_t A, elb200_dm_t B, int64_t offset) {
     ELB_BINARY("elb200_dm_axpy_trapezoid", AxpyTrapezoid(uplo, float(alpha), *A->f, *B->f, offset), AxpyTrapezoid(uplo, alpha, *A->d, *B->d, offset))
 }
 int elb200_dm_local_trrk(int uplo, int ta, int tb, double alpha, elb200_dm_t A, elb200_dm_t B, double beta, elb200_dm_t C) {
-    if (!same_dtype(A, B) || !same_dtype(A, C) || ta < 0 || ta > 2 || tb < 0 || tb > 2) return ELB200_ERR_ARG;
+    if (!same_dtype(A, B) || !same_dtype(A, C) || !level3_dtype(A) || ta < 0 || ta > 2 || tb < 0 || tb > 2) return ELB200_ERR_ARG;
     return guarded("elb200_dm_local_trrk", [&] {
         if (A->dtype == ELB200_F32) LocalTrrk(uplo, ta, tb, float(alpha), *A->f, *B->f, float(beta), *C->f);
         else LocalTrrk(uplo, ta, tb, alpha, *A->d, *B->d, beta, *C->d);
     });
 }
 int elb200_dist_trrk(int uplo, int ta, int tb, double alpha, elb200_dm_t A, elb200_dm_t B, double beta, elb200_dm_t C) {
-    if (!same_dtype(A, B) || !same_dtype(A, C) || ta < 0 || ta > 2 || tb < 0 || tb > 2) return ELB200_ERR_ARG;
+    if (!same_dtype(A, B) || !same_dtype(A, C) || !level3_dtype(A) || ta < 0 || ta > 2 || tb < 0 || tb > 2) return ELB200_ERR_ARG;
     return guarded("elb200_dist_trrk", [&] {
         if (A->dtype == ELB200_F32) Trrk(uplo, ta, tb, float(alpha), *A->f, *B->f, float(beta), *C->f);
         else Trrk(uplo, ta, tb, alpha, *A->d, *B->d, beta, *C->d);
     });
 }
 int elb200_dist_syrk(int uplo, int trans, double alpha, elb200_dm_t A, double beta, elb200_dm_t C) {
-    if (!same_dtype(A, C) || trans < 0 || trans > 2) return ELB200_ERR_ARG;
+    if (!same_dtype(A, C) || !level3_dtype(A) || trans < 0 || trans > 2) return ELB200_ERR_ARG;
     return guarded("elb200_dist_syrk", [&] {
         if (A->dtype == ELB200_F32) Syrk(uplo, trans, float(alpha), *A->f, float(beta), *C->f);
         else Syrk(uplo, trans, alpha, *A->d, beta, *C->d);
     });
 }
 int elb200_dist_symm(int side, int uplo, double alpha, elb200_dm_t A, elb200_dm_t B, double beta, elb200_dm_t C) {
-    if (!same_dtype(A, B) || !same_dtype(A, C)) return ELB200_ERR_ARG;
+    if (!same_dtype(A, B) || !same_dtype(A, C) || !level3_dtype(A)) return ELB200_ERR_ARG;
     return guarded("elb200_dist_symm", [&] {
         if (A->dtype == ELB200_F32) Symm(side, uplo, float(alpha), *A->f, *B->f, float(beta), *C->f);
         else Symm(side, uplo, alpha, *A->d, *B->d, beta, *C->d);

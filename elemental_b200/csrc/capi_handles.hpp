@@ -14,5 +14,6 @@ struct elb200_dm_s {
     std::shared_ptr<elb::Grid> keep;
     std::unique_ptr<elb::DistMat<float>> f;
     std::unique_ptr<elb::DistMat<double>> d;
-    elb::Grid* grid() const { return dtype == ELB200_F32 ? f->grid : d->grid; }
+    std::unique_ptr<elb::DistMat<elb::Half>> h;
+    elb::Grid* grid() const { return dtype == ELB200_F32 ? f->grid : dtype == ELB200_F64 ? d->grid : h->grid; }
 };

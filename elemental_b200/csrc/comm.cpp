@@ -75,10 +75,11 @@ size_t elem_bytes(int dtype) {
         case ELB200_F32: return 4;
         case ELB200_F64: return 8;
         case ELB200_BYTE: return 1;
-        default: throw EngineError(ELB200_ERR_ARG, "unknown dtype (ELB200_F32, ELB200_F64 or ELB200_BYTE)");
+        case ELB200_F16: return 2;
+        default: throw EngineError(ELB200_ERR_ARG, "unknown dtype (ELB200_F32, ELB200_F64, ELB200_F16 or ELB200_BYTE)");
     }
 }
-ncclDataType_t nccl_type(int dtype) { return dtype == ELB200_F32 ? ncclFloat : dtype == ELB200_F64 ? ncclDouble : ncclChar; }
+ncclDataType_t nccl_type(int dtype) { return dtype == ELB200_F32 ? ncclFloat : dtype == ELB200_F64 ? ncclDouble : dtype == ELB200_F16 ? ncclHalf : ncclChar; }
 
 struct NcclOrder {  // RAII bracket around one NCCL call (group)
     elb200_comm_s& c;
@@ -401,7 +402,7 @@ int elb200_allgather(const void* sbuf, void* rbuf, int64_t count, int dtype, elb
 // ReduceScatter.hpp:149-165) is allowed: the result lands at the START of the buffer, as in the reference.
 int elb200_reduce_scatter(const void* sbuf, void* rbuf, int64_t count, int dtype, elb200_comm_t c, void* stream) {
     if (!c || count < 0 || (count > 0 && (!sbuf || !rbuf))) return ELB200_ERR_ARG;
-    if (dtype != ELB200_F32 && dtype != ELB200_F64) return ELB200_ERR_ARG;
+    if (dtype != ELB200_F32 && dtype != ELB200_F64 && dtype != ELB200_F16) return ELB200_ERR_ARG;
     return guarded("elb200_reduce_scatter", [&] {
         const size_t esz = elem_bytes(dtype), bytes = size_t(count) * esz;
         cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -424,6 +425,10 @@ int elb200_reduce_scatter(const void* sbuf, void* rbuf, int64_t count, int dtype
                 Dev<float>::fill2d(count, 1, 0.f, static_cast<float*>(rbuf), count, s);
                 Dev<float>::peer_reduce_axpy(c->size, reinterpret_cast<const float* const*>(srcs), int64_t(v.idx) * count, &seg,
                                              static_cast<float*>(rbuf), count, 1.f, s);
+            } else if (dtype == ELB200_F16) {
+                Dev<Half>::fill2d(count, 1, Half(0.f), static_cast<Half*>(rbuf), count, s);
+                Dev<Half>::peer_reduce_axpy(c->size, reinterpret_cast<const Half* const*>(srcs), int64_t(v.idx) * count, &seg,
+                                            static_cast<Half*>(rbuf), count, Half(1.f), s);
             } else {
                 Dev<double>::fill2d(count, 1, 0.0, static_cast<double*>(rbuf), count, s);
                 Dev<double>::peer_reduce_axpy(c->size, reinterpret_cast<const double* const*>(srcs), int64_t(v.idx) * count, &seg,
@@ -447,7 +452,7 @@ int elb200_reduce_scatter(const void* sbuf, void* rbuf, int64_t count, int dtype
 // mpi::AllReduce(sbuf, rbuf, count, SUM, comm, syncInfo) (src/core/imports/mpi/AllReduce.hpp)
 int elb200_allreduce(const void* sbuf, void* rbuf, int64_t count, int dtype, elb200_comm_t c, void* stream) {
     if (!c || count < 0 || (count > 0 && (!sbuf || !rbuf))) return ELB200_ERR_ARG;
-    if (dtype != ELB200_F32 && dtype != ELB200_F64) return ELB200_ERR_ARG;
+    if (dtype != ELB200_F32 && dtype != ELB200_F64 && dtype != ELB200_F16) return ELB200_ERR_ARG;
     return guarded("elb200_allreduce", [&] {
         const size_t bytes = size_t(count) * elem_bytes(dtype);
         cudaStream_t s = static_cast<cudaStream_t>(stream);

@@ -33,6 +33,11 @@ int gemm_f32_tensor(int transA, int transB, int64_t m, int64_t n, int64_t k, flo
                     const float* A, int64_t lda, const float* B, int64_t ldb, float beta, float* C,
                     int64_t ldc, int cta_group, cudaStream_t stream);
 
+// half operands (passed as void* so that host-only translation units need no cuda_fp16.h), fp32 accumulate
+int gemm_f16_tensor(int transA, int transB, int64_t m, int64_t n, int64_t k, float alpha,
+                    const void* A, int64_t lda, const void* B, int64_t ldb, float beta, void* C,
+                    int64_t ldc, int cta_group, cudaStream_t stream);
+
 int gemm_f64_dmma(int transA, int transB, int64_t m, int64_t n, int64_t k, double alpha,
                   const double* A, int64_t lda, const double* B, int64_t ldb, double beta,
                   double* C, int64_t ldc, cudaStream_t stream);

@@ -37,6 +37,20 @@ struct Ev {
 };
 void nccl_check(ncclResult_t r, const char* where);
 
+// IEEE binary16 as the engine's HOST-side element / scalar type for half matrices (the reference's
+// gpu_half_type = __half). Storage is the 16 bits; the only host arithmetic the engine needs on a scalar is construction
+// from 0 / 1 / a double and comparison with zero, both through float. Device code sees the same bits as __half.
+struct Half {
+    uint16_t bits = 0;
+    Half() = default;
+    Half(float f) : bits(from_float(f)) {}
+    Half(double d) : bits(from_float(float(d))) {}
+    Half(int i) : bits(from_float(float(i))) {}
+    operator float() const { return to_float(bits); }
+    static uint16_t from_float(float f);
+    static float to_float(uint16_t h);
+};
+
 // Mirrors El::GemmAlgorithm (reference include/El/blas_like/level3.hpp:22-35), same order and values.
 enum GemmAlg : int {
     GEMM_DEFAULT = 0, GEMM_SUMMA_A_MS = 1, GEMM_SUMMA_A = 2, GEMM_SUMMA_B_MS = 3, GEMM_SUMMA_B = 4,

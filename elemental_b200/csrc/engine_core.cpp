@@ -3,6 +3,7 @@
 #include "engine_dev.hpp"
 
 #include <cstdlib>
+#include <cstring>
 #include <mutex>
 
 namespace elb {
@@ -19,6 +20,41 @@ void cuda_check(cudaError_t e, const char* where) {
 void nccl_check(ncclResult_t r, const char* where) {
     if (r != ncclSuccess)
         throw EngineError(ELB200_ERR_NCCL, std::string(where) + ": " + ncclGetErrorString(r));
+}
+
+// ------------------------------------------------------------------ Half <-> float (round to nearest even)
+uint16_t Half::from_float(float f) {
+    uint32_t x;
+    std::memcpy(&x, &f, 4);
+    const uint32_t sign = (x >> 16) & 0x8000u;
+    x &= 0x7FFFFFFFu;
+    if (x >= 0x7F800000u) return uint16_t(sign | 0x7C00u | (x > 0x7F800000u ? 0x200u : 0u));  // inf / nan
+    if (x >= 0x477FF000u) return uint16_t(sign | 0x7C00u);                                       // rounds to inf
+    if (x < 0x33000001u) return uint16_t(sign);                                                  // rounds to zero
+    int e = int(x >> 23) - 127;
+    uint32_t m = (x & 0x7FFFFFu) | 0x800000u;
+    int shift = e >= -14 ? 13 : 13 + (-14 - e);                                                  // subnormal halves shift more
+    uint32_t h = m >> shift;
+    const uint32_t rem = m & ((1u << shift) - 1u), halfway = 1u << (shift - 1);
+    if (rem > halfway || (rem == halfway && (h & 1u))) ++h;
+    if (e >= -14) h += uint32_t(e + 15 - 1) << 10;   // h carries the implicit bit: adding (exp - 1) << 10 lets a mantissa carry bump the exponent
+    return uint16_t(sign | h);
+}
+float Half::to_float(uint16_t hb) {
+    const uint32_t sign = uint32_t(hb & 0x8000u) << 16;
+    uint32_t e = (hb >> 10) & 0x1Fu, m = hb & 0x3FFu, x;
+    if (e == 0) {
+        if (m == 0) x = sign;
+        else {
+            int sh = 0;
+            while (!(m & 0x400u)) { m <<= 1; ++sh; }
+            x = sign | uint32_t(127 - 15 - sh + 1) << 23 | (m & 0x3FFu) << 13;
+        }
+    } else if (e == 31) x = sign | 0x7F800000u | m << 13;
+    else x = sign | (e + 112u) << 23 | m << 13;
+    float f;
+    std::memcpy(&f, &x, 4);
+    return f;
 }
 
 // ------------------------------------------------------------------ blocksize stack
@@ -44,7 +80,7 @@ int64_t Grid::PanelWidth(int elem_bytes) {
     // partial last wave; measured on B200 inside El::Gemm: fp32 213 -> 221 TF/s going from 2048 to
     // 4096, fp64 28.0 -> 29.5 TF/s going from 1024 to 2048.
     static int64_t env = [] { const char* e = std::getenv("ELB200_PANEL_K"); return e ? std::atoll(e) : 0ll; }();
-    int64_t w = env > 0 ? env : (elem_bytes == 4 ? 4096 : 2048);
+    int64_t w = env > 0 ? env : 16384 / (elem_bytes > 0 ? elem_bytes : 4);  // 16 KiB of k per row: 8192 half, 4096 fp32, 2048 fp64
     const int64_t nb = Blocksize();
     if (w < nb) w = nb;
     return (w / nb) * nb;  // whole algorithmic blocks
@@ -296,5 +332,6 @@ DistMat<T> DistMat<T>::View(int64_t i0, int64_t i1, int64_t j0, int64_t j1) cons
 
 template class DistMat<float>;
 template class DistMat<double>;
+template class DistMat<Half>;
 
 }  // namespace elb

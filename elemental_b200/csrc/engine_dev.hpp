@@ -100,6 +100,41 @@ template <> struct Dev<double> {
     }
 };
 
+// half: the C ABI takes the device pointers as void* and the scalars as float
+template <> struct Dev<Half> {
+    static constexpr ncclDataType_t nccl = ncclHalf;
+    static void gemm(int ta, int tb, int64_t m, int64_t n, int64_t k, Half al, const Half* A, int64_t lda, const Half* B, int64_t ldb,
+                     Half be, Half* C, int64_t ldc, cudaStream_t s) {
+        throw_status(elb200_gemm_f16(ta, tb, m, n, k, float(al), A, lda, B, ldb, float(be), C, ldc, s), "elb200_gemm_f16");
+    }
+    static void copy2d(int64_t r, int64_t c, const Half* src, int64_t srs, int64_t scs, Half* dst, int64_t drs, int64_t dcs, cudaStream_t s) {
+        throw_status(elb200_copy2d_f16(r, c, src, srs, scs, dst, drs, dcs, s), "elb200_copy2d_f16");
+    }
+    static void transpose(int64_t r, int64_t c, const Half* A, int64_t lda, Half* B, int64_t ldb, cudaStream_t s) {
+        throw_status(elb200_transpose_f16(r, c, A, lda, B, ldb, s), "elb200_transpose_f16");
+    }
+    static void axpy2d(int64_t r, int64_t c, Half al, const Half* X, int64_t xrs, int64_t xcs, Half* Y, int64_t yrs, int64_t ycs, cudaStream_t s) {
+        throw_status(elb200_axpy2d_f16(r, c, float(al), X, xrs, xcs, Y, yrs, ycs, s), "elb200_axpy2d_f16");
+    }
+    static void axpy2d_transpose(int64_t r, int64_t c, Half al, const Half* A, int64_t lda, Half* B, int64_t ldb, cudaStream_t s) {
+        throw_status(elb200_axpy2d_transpose_f16(r, c, float(al), A, lda, B, ldb, s), "elb200_axpy2d_transpose_f16");
+    }
+    static void scale2d(int64_t r, int64_t c, Half al, Half* A, int64_t lda, cudaStream_t s) {
+        throw_status(elb200_scale2d_f16(r, c, float(al), A, lda, s), "elb200_scale2d_f16");
+    }
+    static void fill2d(int64_t r, int64_t c, Half v, Half* A, int64_t lda, cudaStream_t s) {
+        throw_status(elb200_fill2d_f16(r, c, float(v), A, lda, s), "elb200_fill2d_f16");
+    }
+    static void lattice(int mode, int nseg, const elb200_segment* segs, Half* M, int64_t ldm, Half* buf, Half al, cudaStream_t s) {
+        throw_status(elb200_lattice_f16(mode, nseg, segs, M, ldm, buf, float(al), s), "elb200_lattice_f16");
+    }
+    static void peer_reduce_axpy(int nsrc, const Half* const* srcs, int64_t off, const elb200_segment* seg, Half* M, int64_t ldm, Half al,
+                                 cudaStream_t s) {
+        throw_status(elb200_peer_reduce_axpy_f16(nsrc, reinterpret_cast<const void* const*>(srcs), off, seg, M, ldm, float(al), s),
+                     "elb200_peer_reduce_axpy_f16");
+    }
+};
+
 // Stream-ordered scratch (the reference's simple_buffer<T,Device::GPU> on the CUB pool,
 // include/hydrogen/utils/SimpleBuffer.hpp:23-123): allocated and freed on the caller's stream.
 template <typename T>

@@ -737,11 +737,14 @@ template <typename T>
 const DistMat<T>& PanelAs(const DistMat<T>& src, DistMat<T>& tmp, const DistSpec& like) { return panel_as(src, tmp, like); }
 template const DistMat<float>& PanelAs<float>(const DistMat<float>&, DistMat<float>&, const DistSpec&);
 template const DistMat<double>& PanelAs<double>(const DistMat<double>&, DistMat<double>&, const DistSpec&);
+template const DistMat<Half>& PanelAs<Half>(const DistMat<Half>&, DistMat<Half>&, const DistSpec&);
 
 template void LocalGemm<float>(int, int, float, const DistMat<float>&, const DistMat<float>&, float, DistMat<float>&);
 template void LocalGemm<double>(int, int, double, const DistMat<double>&, const DistMat<double>&, double, DistMat<double>&);
 template void Gemm<float>(int, int, float, const DistMat<float>&, const DistMat<float>&, float, DistMat<float>&, int);
 template void Gemm<double>(int, int, double, const DistMat<double>&, const DistMat<double>&, double, DistMat<double>&, int);
+template void LocalGemm<Half>(int, int, Half, const DistMat<Half>&, const DistMat<Half>&, Half, DistMat<Half>&);
+template void Gemm<Half>(int, int, Half, const DistMat<Half>&, const DistMat<Half>&, Half, DistMat<Half>&, int);
 template void GemmHost<float>(Grid&, int, int, int64_t, int64_t, int64_t, float, const float*, int64_t, const float*, int64_t, float, float*, int64_t);
 template void GemmHost<double>(Grid&, int, int, int64_t, int64_t, int64_t, double, const double*, int64_t, const double*, int64_t, double, double*, int64_t);
 

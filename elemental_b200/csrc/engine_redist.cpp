@@ -80,31 +80,31 @@ void Copy(const DistMat<T>& A, DistMat<T>& B) {
                 run_lattice<T>(ELB200_PACK, std::vector<Message>{one}, Abuf, A.ldim, slot.p, T(0), s);
                 send = slot.p;
             }
-            // Large blocks: do not wait for the whole gather. My own block goes straight from A into B (no copy
-            // into my own slot) while the peers' blocks are in flight, and each peer's block is unpacked as soon
-            // as ITS arrival flag is up — transfers from the other peers continue underneath. Small messages are
-            // latency-bound and keep the one-wait, one-launch form. OPT-IN (ELB200_AG_SPLIT_MB=4 is the intended
-            // threshold; default 0 = off) until the form has run on real NVLink hardware: the one-piece gather below
-            // is the one every committed multi-GPU number was measured with.
-            static const int64_t split_mb = [] { const char* e = std::getenv("ELB200_AG_SPLIT_MB"); return e ? std::atoll(e) : 0ll; }();
-            static const int64_t split_b = [] { const char* e = std::getenv("ELB200_AG_SPLIT_BYTES"); return e ? std::atoll(e) : 0ll; }();
-            const int64_t split_bytes = split_b > 0 ? split_b : split_mb << 20;
+            // Large blocks (>= 4 MiB per member; ELB200_AG_SPLIT_BYTES overrides, 0 disables): do not wait for the whole
+            // gather. My own block goes straight from A into B (no copy into my own slot) while the peers' blocks are in
+            // flight, and each peer's block is unpacked as soon as ITS arrival flag is up. The sends leave in ROTATION
+            // (peer.hpp AllGatherRotate), one after the other at the full link rate, so the blocks land staggered and block d
+            // is unpacked while block d + 1 is on the wire. Measured on 2 x 2 B200s (profiles/r02_dist_sweep_4gpu*.json):
+            // 1 GiB [MC,MR] -> [MC,*] 0.541 -> 0.475 ms, 256 MiB 0.167 -> 0.141 ms; all sends at once (no rotation) gained
+            // nothing and was removed. Small messages are latency-bound and keep the one-wait, one-launch form.
+            static const int64_t split_bytes = [] { const char* e = std::getenv("ELB200_AG_SPLIT_BYTES"); return e ? std::atoll(e) : (4ll << 20); }();
             if (split_bytes > 0 && plan.portion * int64_t(sizeof(T)) >= split_bytes && plan.recvs[size_t(idx)].peer == g.vc_rank) {
-                // Rotation (peer.hpp AllGatherRotate): the sends leave one after the other, so the blocks land staggered
-                // and block d is unpacked while block d + 1 is on the wire; my own block is copied underneath the
-                // sends. ELB200_AG_ROTATE=0 keeps the earlier form (all sends at once, `s` joined before my block).
-                static const bool rotate = [] { const char* e = std::getenv("ELB200_AG_ROTATE"); return !e || std::atoi(e) != 0; }();
-                PeerArena::Ticket t = rotate ? g.arena->AllGatherRotate(Grid::arena_channel(plan.comm_dist), members, idx, send,
-                                                                        size_t(mine) * sizeof(T), size_t(plan.portion) * sizeof(T), s)
-                                             : g.arena->AllGatherBegin(Grid::arena_channel(plan.comm_dist), members, idx, send,
-                                                                       size_t(mine) * sizeof(T), size_t(plan.portion) * sizeof(T), true, s);
+                PeerArena::Ticket t = g.arena->AllGatherRotate(Grid::arena_channel(plan.comm_dist), members, idx, send,
+                                                               size_t(mine) * sizeof(T), size_t(plan.portion) * sizeof(T), s);
+                // the rotation leaves a copy lane forked from `s`: join it on EVERY exit, a throwing unpack included, so the
+                // arena's fork state is never stale for the next operation and the pack scratch is not freed under the lane
+                struct Join {
+                    PeerArena* a; cudaStream_t st; bool done = false;
+                    ~Join() { if (!done) { try { a->AllGatherEnd(st); } catch (...) {} } }
+                } join{g.arena, s};
                 if (mine > 0) lattice_to_lattice<T>(s0, A.buf, A.ldim, plan.recvs[size_t(idx)].seg, B.buf, B.ldim, s);
                 for (int d = 1; d < gsz; ++d) {
                     const int i = (idx - d + gsz) % gsz;  // arrival order under the rotation
                     g.arena->WaitMember(t, members, idx, i, s);
                     run_lattice<T>(ELB200_UNPACK, std::vector<Message>{plan.recvs[size_t(i)]}, B.buf, B.ldim, static_cast<T*>(t.data), T(0), s);
                 }
-                if (rotate) g.arena->AllGatherEnd(s);  // my sends are done: `send` (A or the pack scratch) may be reused
+                g.arena->AllGatherEnd(s);  // my sends are done: `send` (A or the pack scratch) may be reused
+                join.done = true;
                 g.arena->Release(t, members, idx, s);
                 return;
             }
@@ -320,6 +320,7 @@ void TransposeAxpyContract(T alpha, const DistMat<T>& A, DistMat<T>& B) {
     template void Zero<T>(DistMat<T>&);
 ELB_INST(float)
 ELB_INST(double)
+ELB_INST(Half)
 #undef ELB_INST
 
 }  // namespace elb

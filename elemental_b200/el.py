@@ -16,16 +16,17 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import (CIRC, F32, F64, MC, MR, STAR, VC, VR, check, lib)  # noqa: F401
+from ._lib import (CIRC, F16, F32, F64, MC, MR, STAR, VC, VR, check, lib)  # noqa: F401
 
 NORMAL, TRANSPOSE, ADJOINT = 0, 1, 2  # El::Orientation (include/El/core/types.hpp)
 # El::GemmAlgorithm, values as in the reference enum (include/El/blas_like/level3.hpp:23-33)
 (GEMM_DEFAULT, GEMM_SUMMA_A_MS, GEMM_SUMMA_A, GEMM_SUMMA_B_MS, GEMM_SUMMA_B, GEMM_SUMMA_C_MS, GEMM_SUMMA_C,
  GEMM_SUMMA_DOT, GEMM_CANNON) = range(9)
 
-_DTYPES = {torch.float32: F32, torch.float64: F64, np.dtype("float32"): F32,
-           np.dtype("float64"): F64, "float32": F32, "float64": F64, F32: F32, F64: F64}
-_TORCH = {F32: torch.float32, F64: torch.float64}
+_DTYPES = {torch.float32: F32, torch.float64: F64, torch.float16: F16, np.dtype("float32"): F32,
+           np.dtype("float64"): F64, np.dtype("float16"): F16, "float32": F32, "float64": F64, "float16": F16,
+           F32: F32, F64: F64, F16: F16}
+_TORCH = {F32: torch.float32, F64: torch.float64, F16: torch.float16}
 
 
 def Blocksize() -> int:
@@ -273,7 +274,7 @@ class DistMatrix:
         dt = _TORCH[self.dtype]
         if lh == 0 or lw == 0 or not inf.buffer:
             return torch.empty((lh, lw), dtype=dt, device=f"cuda:{self.grid.device}")
-        typestr = "<f4" if self.dtype == F32 else "<f8"
+        typestr = {F32: "<f4", F64: "<f8", F16: "<f2"}[self.dtype]
         flat = torch.as_tensor(_DevBuf(inf.buffer, (lw * ld,), typestr), device=f"cuda:{self.grid.device}")
         return flat.view(lw, ld)[:, :lh].t()  # column-major (ld x lw) seen as rows x cols
 

@@ -8,6 +8,7 @@
 // Non-zero statuses become the reference's exception types: ELB200_ERR_ARG -> std::logic_error
 // (El::LogicError), anything else -> std::runtime_error (El::RuntimeError).
 #pragma once
+#include <cuda_fp16.h>
 #include <cuda_runtime_api.h>
 
 #include <cmath>
@@ -26,6 +27,7 @@
 namespace El {
 
 typedef int Int;  // reference default (no EL_USE_64BIT_INTS)
+typedef __half gpu_half_type;  // hydrogen::gpu_half_type (include/hydrogen/utils/HalfPrecision.hpp): IEEE half on the device
 
 // Values as in the reference (include/El/core/types.hpp:208-217, :464-469; level3.hpp:23-33).
 enum Dist { MC, MD, MR, VC, VR, STAR, CIRC };
@@ -130,6 +132,8 @@ inline Dist FromEngineDist(int d) {
 template <typename T> struct TypeCode;
 template <> struct TypeCode<float> { static constexpr int value = ELB200_F32; };
 template <> struct TypeCode<double> { static constexpr int value = ELB200_F64; };
+template <> struct TypeCode<__half> { static constexpr int value = ELB200_F16; };
+template <typename T> struct IsElement { static constexpr bool value = std::is_same<T, float>::value || std::is_same<T, double>::value || std::is_same<T, __half>::value; };
 }  // namespace detail
 
 // ---------------------------------------------------------------------------------------------
@@ -318,7 +322,7 @@ static const Range ALL{0, -1};
 template <typename T, Device D = Device::GPU>
 class Matrix {
     static_assert(D == Device::GPU, "elemental_b200 has no CPU path: Matrix<T, Device::GPU> only");
-    static_assert(std::is_same<T, float>::value || std::is_same<T, double>::value, "float and double only");
+    static_assert(detail::IsElement<T>::value, "float, double and gpu_half_type only");
 
 public:
     Matrix() = default;
@@ -347,7 +351,8 @@ public:
     const T* LockedBuffer(Int i, Int j) const { return buf_ + size_t(i) + size_t(j) * size_t(ld_); }
     void Resize(Int height, Int width, Int ldim = 0) {
         if (height < 0 || width < 0) throw std::logic_error("Matrix::Resize: negative dimension");
-        const Int ld = ldim > 0 ? ldim : (height > 0 ? (height + 3) / 4 * 4 : 4);  // 16-byte column pitch
+        constexpr Int q = Int(16 / sizeof(T));
+        const Int ld = ldim > 0 ? ldim : (height > 0 ? (height + q - 1) / q * q : q);  // 16-byte column pitch
         if (ld < height) throw std::logic_error("Matrix::Resize: ldim < height");
         if (!own_ && buf_) {
             if (height != h_ || width != w_) throw std::logic_error("Matrix::Resize: cannot resize a view");
@@ -415,6 +420,14 @@ template <> struct LocalOps<double> {
     static int axpy(long r, long c, double al, const double* X, long xr, long xc, double* Y, long yr, long yc, void* s) { return elb200_axpy2d_f64(r, c, al, X, xr, xc, Y, yr, yc, s); }
     static int scale(long r, long c, double al, double* A, long lda, void* s) { return elb200_scale2d_f64(r, c, al, A, lda, s); }
     static int fill(long r, long c, double v, double* A, long lda, void* s) { return elb200_fill2d_f64(r, c, v, A, lda, s); }
+};
+template <> struct LocalOps<__half> {
+    static int gemm(int ta, int tb, long m, long n, long k, __half al, const __half* A, long lda, const __half* B, long ldb, __half be, __half* C, long ldc, void* s) { return elb200_gemm_f16(ta, tb, m, n, k, float(al), A, lda, B, ldb, float(be), C, ldc, s); }
+    static int copy(long r, long c, const __half* X, long xr, long xc, __half* Y, long yr, long yc, void* s) { return elb200_copy2d_f16(r, c, X, xr, xc, Y, yr, yc, s); }
+    static int transpose(long r, long c, const __half* A, long lda, __half* B, long ldb, void* s) { return elb200_transpose_f16(r, c, A, lda, B, ldb, s); }
+    static int axpy(long r, long c, __half al, const __half* X, long xr, long xc, __half* Y, long yr, long yc, void* s) { return elb200_axpy2d_f16(r, c, float(al), X, xr, xc, Y, yr, yc, s); }
+    static int scale(long r, long c, __half al, __half* A, long lda, void* s) { return elb200_scale2d_f16(r, c, float(al), A, lda, s); }
+    static int fill(long r, long c, __half v, __half* A, long lda, void* s) { return elb200_fill2d_f16(r, c, float(v), A, lda, s); }
 };
 }  // namespace detail
 
@@ -586,7 +599,7 @@ inline void PopBlocksizeStack() { elb200_pop_blocksize(); }
 // ---------------------------------------------------------------------------------------------
 template <typename T>
 class AbstractDistMatrix {
-    static_assert(std::is_same<T, float>::value || std::is_same<T, double>::value, "float and double only");
+    static_assert(detail::IsElement<T>::value, "float, double and gpu_half_type only");
 
 public:
     virtual ~AbstractDistMatrix() { if (h_) elb200_dm_destroy(h_); }

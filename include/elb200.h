@@ -61,6 +61,15 @@ int elb200_gemm_f32(int transA, int transB, int64_t m, int64_t n, int64_t k, flo
 int elb200_gemm_f64(int transA, int transB, int64_t m, int64_t n, int64_t k, double alpha,
                     const double* A, int64_t lda, const double* B, int64_t ldb, double beta,
                     double* C, int64_t ldc, void* stream);
+/* IEEE half operands and result (device pointers to __half, passed as void* so that this header stays plain C), alpha /
+ * beta and the accumulation in FP32, one rounding to half in the epilogue: tcgen05.mma kind::f16 — the native tensor-core
+ * type, one UMMA per k-slice where the fp32 path needs three. Replaces the gpu_half_type instantiation of gpu_blas::Gemm
+ * -> cublasHgemm / cublasGemmEx (src/hydrogen/device/cuBLAS_API.cpp:417 ADD_GEMM_IMPL(__half, H);
+ * src/blas_like/level3/Gemm.cpp:455-462,505). SURVEY.md 8(f) N3. Operands must be 16-byte aligned with leading
+ * dimensions that are multiples of 8 halfs (else ELB200_ERR_ARG). */
+int elb200_gemm_f16(int transA, int transB, int64_t m, int64_t n, int64_t k, float alpha,
+                    const void* A, int64_t lda, const void* B, int64_t ldb, float beta, void* C,
+                    int64_t ldc, void* stream);
 /* Tuning/diagnostic variant: cta_group = 1 (one SM per tile) or 2 (CTA pair, cta_group::2). */
 int elb200_gemm_f32_ex(int transA, int transB, int64_t m, int64_t n, int64_t k, float alpha,
                        const float* A, int64_t lda, const float* B, int64_t ldb, float beta,
@@ -96,6 +105,18 @@ int elb200_copy2d_f32(int64_t rows, int64_t cols, const float* src, int64_t src_
 int elb200_copy2d_f64(int64_t rows, int64_t cols, const double* src, int64_t src_row_stride,
                       int64_t src_col_stride, double* dst, int64_t dst_row_stride,
                       int64_t dst_col_stride, void* stream);
+
+/* The half (__half) instantiations of the entrywise kernels (the reference instantiates Copy / Axpy / Scale / Fill /
+ * Transpose for gpu_half_type as well, src/hydrogen/blas/gpu/{Copy,Axpy,Scale,Fill,Transpose}.cu); scalars in FP32. */
+int elb200_copy2d_f16(int64_t rows, int64_t cols, const void* src, int64_t src_row_stride, int64_t src_col_stride,
+                      void* dst, int64_t dst_row_stride, int64_t dst_col_stride, void* stream);
+int elb200_axpy2d_f16(int64_t rows, int64_t cols, float alpha, const void* X, int64_t x_row_stride, int64_t x_col_stride,
+                      void* Y, int64_t y_row_stride, int64_t y_col_stride, void* stream);
+int elb200_scale2d_f16(int64_t rows, int64_t cols, float alpha, void* A, int64_t lda, void* stream);
+int elb200_fill2d_f16(int64_t rows, int64_t cols, float value, void* A, int64_t lda, void* stream);
+int elb200_transpose_f16(int64_t rows, int64_t cols, const void* A, int64_t lda, void* B, int64_t ldb, void* stream);
+int elb200_axpy2d_transpose_f16(int64_t rows, int64_t cols, float alpha, const void* A, int64_t lda, void* B, int64_t ldb,
+                                void* stream);
 
 /* B(cols x rows, ldb) = A(rows x cols, lda)^T.
  * Replaces Transpose_GPU_impl / Copy2DImpl(transA) -> cublas?geam
@@ -176,6 +197,12 @@ int elb200_lattice_f32(int mode, int nseg, const elb200_segment* segs, float* M,
                        float* buf, float alpha, void* stream);
 int elb200_lattice_f64(int mode, int nseg, const elb200_segment* segs, double* M, int64_t ldm,
                        double* buf, double alpha, void* stream);
+
+/* half instantiations of the two entries above / below (sums accumulate in FP32) */
+int elb200_lattice_f16(int mode, int nseg, const elb200_segment* segs, void* M, int64_t ldm, void* buf, float alpha,
+                       void* stream);
+int elb200_peer_reduce_axpy_f16(int nsrc, const void* const* srcs, int64_t src_offset, const elb200_segment* seg, void* M,
+                                int64_t ldm, float alpha, void* stream);
 
 /* M lattice += alpha * (srcs[0][off + e] + srcs[1][off + e] + ... ), e running over the packed
  * rows x cols block of `seg`: the receiver side of a ReduceScatter, fused with the axpy-unpack.
@@ -304,7 +331,7 @@ int elb200_gemm_resolve_alg(int transA, int transB, int64_t m, int64_t n, int64_
  * ---------------------------------------------------------------------------------------- */
 typedef struct elb200_grid_s* elb200_grid_t;
 typedef struct elb200_dm_s* elb200_dm_t;
-enum { ELB200_F32 = 0, ELB200_F64 = 1, ELB200_BYTE = 2 /* data movement only: no reductions */ };
+enum { ELB200_F32 = 0, ELB200_F64 = 1, ELB200_BYTE = 2 /* collectives, data movement only: no reductions */, ELB200_F16 = 3 /* IEEE half */ };
 #define ELB200_UNIQUE_ID_BYTES 128
 
 /* NCCL bootstrap: rank 0 calls elb200_unique_id and ships the 128 bytes to the other ranks by any

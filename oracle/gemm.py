@@ -212,6 +212,10 @@ def frobenius_rel_err(X, ref) -> float:
 
 def gemm_tolerance(dtype, k: int) -> float:
     """north_star bound: relative Frobenius error <= 1e-13*sqrt(k) (fp64) / 1e-5*sqrt(k) (fp32)."""
+    if np.dtype(dtype) == np.float16:
+        # half (SURVEY 8(f) N3): no bound in north_star and no golden vectors in the reference; products accumulate in fp32
+        # on the device and are rounded to half (eps 9.8e-4) once per SUMMA panel / partial-sum reduction
+        return 4e-3
     return (1e-13 if np.dtype(dtype) == np.float64 else 1e-5) * float(np.sqrt(max(k, 1)))
 
 

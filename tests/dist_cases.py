@@ -22,7 +22,7 @@ from oracle import dist as OD
 from oracle import gemm as OG
 from oracle import level3 as O3
 
-NPDT = {torch.float32: np.float32, torch.float64: np.float64}
+NPDT = {torch.float32: np.float32, torch.float64: np.float64, torch.float16: np.float16}
 
 
 def use_backend(module) -> None:
@@ -820,9 +820,10 @@ def check_collectives(grid, dtype=torch.float64) -> int:
     matrices of [*,*] DistMatrices (one column), which both back ends can fill and read."""
     lib, check = el.lib, el.check
     npdt = NPDT[dtype]
-    code = 0 if dtype == torch.float32 else 1
+    code = {torch.float32: 0, torch.float64: 1, torch.float16: 3}[dtype]
     stream = lib.elb200_grid_stream(grid._h)
     keep, cnt = [], 0
+    half = dtype == torch.float16  # integers up to 2048 are exact in half: smaller tags, sums stay exact
 
     def dev(values):
         a = np.asarray(values, dtype=npdt).reshape(-1, 1)
@@ -832,7 +833,7 @@ def check_collectives(grid, dtype=torch.float64) -> int:
         return D, D._info().buffer
 
     def val(rank, idx):
-        return rank * 1000 + (np.asarray(idx) % 997)
+        return (rank % 64) * 2 + (np.asarray(idx) % 2) if half else rank * 1000 + (np.asarray(idx) % 997)
 
     expect_rank = (grid.MCRank(), grid.MRRank(), grid.VCRank(), grid.VRRank())
     expect_size = (grid.Height(), grid.Width(), grid.Size(), grid.Size())
@@ -858,10 +859,10 @@ def check_collectives(grid, dtype=torch.float64) -> int:
             S, sp = dev(val(me, big)); R, rp = dev(np.zeros(n * p))
             check(lib.elb200_allreduce(sp, rp, n * p, code, ch, stream), "elb200_allreduce")
             assert np.array_equal(R.get_local()[:, 0], sum(val(q, big) for q in range(p)).astype(npdt)), ("allreduce", which, n)
-            # alltoall: block j of rank q's buffer carries the tag 64 q + j
-            S, sp = dev(np.concatenate([val(me * 64 + j, i) for j in range(p)])); R, rp = dev(np.zeros(n * p))
+            # alltoall: block j of rank q's buffer carries the tag 8 q + j
+            S, sp = dev(np.concatenate([val(me * 8 + j, i) for j in range(p)])); R, rp = dev(np.zeros(n * p))
             check(lib.elb200_alltoall(sp, rp, n, code, ch, stream), "elb200_alltoall")
-            assert np.array_equal(R.get_local()[:, 0], np.concatenate([val(q * 64 + me, i) for q in range(p)]).astype(npdt)), ("alltoall", which, n)
+            assert np.array_equal(R.get_local()[:, 0], np.concatenate([val(q * 8 + me, i) for q in range(p)]).astype(npdt)), ("alltoall", which, n)
             # sendrecv around the ring, bcast from the last rank
             S, sp = dev(val(me, i)); R, rp = dev(np.zeros(n))
             check(lib.elb200_sendrecv(sp, n, (me + 1) % p, rp, n, (me - 1) % p, code, ch, stream), "elb200_sendrecv")
@@ -875,6 +876,24 @@ def check_collectives(grid, dtype=torch.float64) -> int:
     return cnt
 
 
+def check_half(grid) -> int:
+    """the same path for IEEE half — DistMatrix<half> redistributions (bit-exact), the collectives, and
+    El::Gemm in every orientation and SUMMA variant (tcgen05 kind::f16 local products, fp32 accumulation, one rounding to half
+    per panel / reduction), against the oracle on the exact half inputs."""
+    dt = torch.float16
+    cnt = check_redistributions(grid, dt, m=23, n=17, seed=9,
+                                pairs=[((OD.MC, OD.MR), t) for t in OD.PAIRS] + [(t, (OD.MC, OD.MR)) for t in OD.PAIRS])
+    cnt += check_collectives(grid, dt)
+    for oa, ob in itertools.product((0, 1), (0, 1)):
+        for alg in (el.GEMM_SUMMA_A, el.GEMM_SUMMA_B, el.GEMM_SUMMA_C, el.GEMM_SUMMA_DOT, el.GEMM_DEFAULT):
+            err, tol = gemm_case(grid, dt, oa, ob, alg, 70, 50, 90, alpha=2.0, beta=0.5, nb=16)
+            assert err <= tol, f"half Gemm oa={oa} ob={ob} alg={alg}: {err:.3e} > {tol:.3e}"
+            cnt += 1
+    err, tol = gemm_case(grid, dt, 0, 0, el.GEMM_SUMMA_C, 520, 390, 1100, alpha=0.5, beta=-0.5)
+    assert err <= tol, ("half Gemm 520x390x1100", err, tol)
+    return cnt + 1
+
+
 def run_all(grid, heavy=False) -> dict:
     out = {}
     out["redist_f64"] = check_redistributions(grid, torch.float64)
@@ -886,6 +905,7 @@ def run_all(grid, heavy=False) -> dict:
     check_contractions(grid, torch.float64)
     check_contractions(grid, torch.float32)
     out["collectives"] = check_collectives(grid, torch.float64) + check_collectives(grid, torch.float32)
+    out["half"] = check_half(grid)
     out["gemm_f64"] = check_gemm_variants(grid, torch.float64)
     out["gemm_f32"] = check_gemm_variants(grid, torch.float32)
     check_gemm_proxies(grid, torch.float64)

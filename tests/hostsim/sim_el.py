@@ -34,13 +34,13 @@ for _name, (_res, _args) in L.SIGNATURES.items():
 assert b"hostsim" in lib.elb200_build_info()
 
 MC, MR, VC, VR, STAR, CIRC = L.MC, L.MR, L.VC, L.VR, L.STAR, L.CIRC
-F32, F64 = L.F32, L.F64
+F32, F64, F16 = L.F32, L.F64, L.F16
 NORMAL, TRANSPOSE, ADJOINT = 0, 1, 2
 (GEMM_DEFAULT, GEMM_SUMMA_A_MS, GEMM_SUMMA_A, GEMM_SUMMA_B_MS, GEMM_SUMMA_B, GEMM_SUMMA_C_MS, GEMM_SUMMA_C,
  GEMM_SUMMA_DOT, GEMM_CANNON) = range(9)
-_DTYPES = {torch.float32: F32, torch.float64: F64, np.dtype("float32"): F32, np.dtype("float64"): F64,
-           np.float32: F32, np.float64: F64, F32: F32, F64: F64}
-_NP = {F32: np.float32, F64: np.float64}
+_DTYPES = {torch.float32: F32, torch.float64: F64, torch.float16: F16, np.dtype("float32"): F32, np.dtype("float64"): F64,
+           np.dtype("float16"): F16, np.float32: F32, np.float64: F64, np.float16: F16, F32: F32, F64: F64, F16: F16}
+_NP = {F32: np.float32, F64: np.float64, F16: np.float16}
 
 
 class Elb200Error(RuntimeError):

@@ -92,6 +92,7 @@ void reduce_bytes(void* acc, const void* x, size_t n, ncclDataType_t t, ncclRedO
         case ncclInt32: reduce_into(static_cast<int32_t*>(acc), static_cast<const int32_t*>(x), n, op); break;
         case ncclFloat32: reduce_into(static_cast<float*>(acc), static_cast<const float*>(x), n, op); break;
         case ncclFloat64: reduce_into(static_cast<double*>(acc), static_cast<const double*>(x), n, op); break;
+        case ncclFloat16: reduce_into(static_cast<_Float16*>(acc), static_cast<const _Float16*>(x), n, op); break;
         default: sim::fail("hostsim NCCL: reduction on datatype %d not supported", int(t));
     }
 }

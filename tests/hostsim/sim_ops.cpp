@@ -359,6 +359,84 @@ int elb200_gemm_f32_noalloc(int ta, int tb, int64_t m, int64_t n, int64_t k, flo
                             int64_t ldb, float be, float* C, int64_t ldc, void* s) {
     return gemm<float>(ta, tb, m, n, k, al, A, lda, B, ldb, be, C, ldc, s);
 }
+// half entries: g++'s _Float16 is IEEE binary16; arithmetic in float like the device kernels
+typedef _Float16 simhalf;
+int elb200_gemm_f16(int ta, int tb, int64_t m, int64_t n, int64_t k, float al, const void* Av, int64_t lda, const void* Bv, int64_t ldb,
+                    float be, void* Cv, int64_t ldc, void* s) {
+    const simhalf* A = static_cast<const simhalf*>(Av); const simhalf* B = static_cast<const simhalf*>(Bv); simhalf* C = static_cast<simhalf*>(Cv);
+    sim::enqueue(static_cast<cudaStream_t>(s), [=] {
+        for (int64_t j = 0; j < n; ++j)
+            for (int64_t i = 0; i < m; ++i) {
+                float acc = 0.f;
+                for (int64_t l = 0; l < k; ++l) acc += float(ta ? A[l + i * lda] : A[i + l * lda]) * float(tb ? B[j + l * ldb] : B[l + j * ldb]);
+                const float old = be == 0.f ? 0.f : be * float(C[i + j * ldc]);
+                C[i + j * ldc] = simhalf(al * acc + old);
+            }
+    });
+    return ELB200_OK;
+}
+int elb200_copy2d_f16(int64_t r, int64_t c, const void* src, int64_t srs, int64_t scs, void* dst, int64_t drs, int64_t dcs, void* s) {
+    const simhalf* X = static_cast<const simhalf*>(src); simhalf* Y = static_cast<simhalf*>(dst);
+    sim::enqueue(static_cast<cudaStream_t>(s), [=] { for (int64_t j = 0; j < c; ++j) for (int64_t i = 0; i < r; ++i) Y[i * drs + j * dcs] = X[i * srs + j * scs]; });
+    return ELB200_OK;
+}
+int elb200_axpy2d_f16(int64_t r, int64_t c, float al, const void* Xv, int64_t xrs, int64_t xcs, void* Yv, int64_t yrs, int64_t ycs, void* s) {
+    const simhalf* X = static_cast<const simhalf*>(Xv); simhalf* Y = static_cast<simhalf*>(Yv);
+    sim::enqueue(static_cast<cudaStream_t>(s), [=] { for (int64_t j = 0; j < c; ++j) for (int64_t i = 0; i < r; ++i) Y[i * yrs + j * ycs] = simhalf(al * float(X[i * xrs + j * xcs]) + float(Y[i * yrs + j * ycs])); });
+    return ELB200_OK;
+}
+int elb200_scale2d_f16(int64_t r, int64_t c, float al, void* Av, int64_t lda, void* s) {
+    simhalf* A = static_cast<simhalf*>(Av);
+    sim::enqueue(static_cast<cudaStream_t>(s), [=] { for (int64_t j = 0; j < c; ++j) for (int64_t i = 0; i < r; ++i) A[i + j * lda] = al == 0.f ? simhalf(0.f) : simhalf(al * float(A[i + j * lda])); });
+    return ELB200_OK;
+}
+int elb200_fill2d_f16(int64_t r, int64_t c, float v, void* Av, int64_t lda, void* s) {
+    simhalf* A = static_cast<simhalf*>(Av);
+    sim::enqueue(static_cast<cudaStream_t>(s), [=] { for (int64_t j = 0; j < c; ++j) for (int64_t i = 0; i < r; ++i) A[i + j * lda] = simhalf(v); });
+    return ELB200_OK;
+}
+int elb200_transpose_f16(int64_t r, int64_t c, const void* Av, int64_t lda, void* Bv, int64_t ldb, void* s) {
+    const simhalf* A = static_cast<const simhalf*>(Av); simhalf* B = static_cast<simhalf*>(Bv);
+    sim::enqueue(static_cast<cudaStream_t>(s), [=] { for (int64_t j = 0; j < c; ++j) for (int64_t i = 0; i < r; ++i) B[j + i * ldb] = A[i + j * lda]; });
+    return ELB200_OK;
+}
+int elb200_axpy2d_transpose_f16(int64_t r, int64_t c, float al, const void* Av, int64_t lda, void* Bv, int64_t ldb, void* s) {
+    const simhalf* A = static_cast<const simhalf*>(Av); simhalf* B = static_cast<simhalf*>(Bv);
+    sim::enqueue(static_cast<cudaStream_t>(s), [=] { for (int64_t j = 0; j < c; ++j) for (int64_t i = 0; i < r; ++i) B[i + j * ldb] = simhalf(al * float(A[j + i * lda]) + float(B[i + j * ldb])); });
+    return ELB200_OK;
+}
+int elb200_lattice_f16(int mode, int nseg, const elb200_segment* segs, void* Mv, int64_t ldm, void* bufv, float al, void* s) {
+    simhalf* M = static_cast<simhalf*>(Mv); simhalf* buf = static_cast<simhalf*>(bufv);
+    std::vector<elb200_segment> sg(segs, segs + nseg);
+    sim::enqueue(static_cast<cudaStream_t>(s), [=] {
+        for (const elb200_segment& g : sg)
+            for (int64_t j = 0; j < g.cols; ++j)
+                for (int64_t i = 0; i < g.rows; ++i) {
+                    simhalf* mp = M + g.row0 + i * g.row_step + (g.col0 + j * g.col_step) * ldm;
+                    simhalf* bp = buf + g.buf_offset + i + j * g.rows;
+                    if (mode == ELB200_PACK) *bp = *mp;
+                    else if (mode == ELB200_UNPACK) *mp = *bp;
+                    else *mp = simhalf(al * float(*bp) + float(*mp));
+                }
+    });
+    return ELB200_OK;
+}
+int elb200_peer_reduce_axpy_f16(int nsrc, const void* const* srcs, int64_t off, const elb200_segment* seg, void* Mv, int64_t ldm, float al, void* s) {
+    simhalf* M = static_cast<simhalf*>(Mv);
+    std::vector<const simhalf*> src(nsrc);
+    for (int q = 0; q < nsrc; ++q) src[q] = static_cast<const simhalf*>(srcs[q]);
+    const elb200_segment g = *seg;
+    sim::enqueue(static_cast<cudaStream_t>(s), [=] {
+        for (int64_t j = 0; j < g.cols; ++j)
+            for (int64_t i = 0; i < g.rows; ++i) {
+                float acc = 0.f;
+                for (const simhalf* p : src) acc += float(p[off + i + j * g.rows]);
+                simhalf* mp = M + g.row0 + i * g.row_step + (g.col0 + j * g.col_step) * ldm;
+                *mp = simhalf(al * acc + float(*mp));
+            }
+    });
+    return ELB200_OK;
+}
 int elb200_gemm_f64(int ta, int tb, int64_t m, int64_t n, int64_t k, double al, const double* A, int64_t lda, const double* B,
                     int64_t ldb, double be, double* C, int64_t ldc, void* s) {
     return gemm<double>(ta, tb, m, n, k, al, A, lda, B, ldb, be, C, ldc, s);

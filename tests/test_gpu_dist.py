@@ -148,6 +148,13 @@ def test_gemm_full_size_properties(grid1, dtype, alg):
         M.destroy()
 
 
+def test_half_1x1(grid1):
+    """SURVEY 8(f) N3: DistMatrix<half> — redistributions bit-exact, collectives, El::Gemm in all orientations / SUMMA variants
+    (tcgen05 kind::f16 local products) against the oracle."""
+    from tests import dist_cases as dc
+    assert dc.check_half(grid1) == 99
+
+
 def test_collective_exports_1x1(grid1):
     """Every per-collective export (elb200_allgather / reduce_scatter / allreduce / alltoall / sendrecv / bcast) over the
     grid's four communicators; on one rank each is its defined local copy (src/core/imports/mpi/AllGather.hpp:17,

@@ -1,0 +1,116 @@
+"""SURVEY 8(f) N3 — IEEE half: the tcgen05 kind::f16 GEMM (elb200_gemm_f16) and the half instantiations of the entrywise
+kernels, through the C ABI, against numpy. The reference instantiates Gemm for gpu_half_type through cublasHgemm
+(src/hydrogen/device/cuBLAS_API.cpp:417); it holds no golden vectors for it (and its CPU half needs the external `half`
+library, absent here), so the checker is the definition: products of the exact half inputs summed in float64, rounded
+once to half. Tolerance: relative Frobenius error <= 1e-3 (half has an 11-bit significand: the final rounding alone is
+up to 4.9e-4 per entry; accumulation is fp32 in TMEM)."""
+import itertools
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = [(128, 128, 64), (256, 512, 96), (300, 200, 104), (129, 257, 40), (1000, 1000, 1000), (64, 40, 504), (8, 8, 8),
+          (513, 1, 80), (2000, 2000, 64), (4096, 4096, 4096)]
+
+
+@pytest.fixture(scope="module")
+def L():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from elemental_b200 import _lib
+    return _lib
+
+
+def colmajor_h(rows, cols, ld, seed, fill=0.0):
+    rng = np.random.default_rng(seed)
+    buf = np.full((cols, ld), fill, dtype=np.float16)
+    buf[:, :rows] = rng.uniform(-1, 1, (cols, rows)).astype(np.float16)
+    return buf  # buf[j, i] == M(i, j)
+
+
+@pytest.mark.parametrize("ta,tb", list(itertools.product([0, 1], [0, 1])))
+def test_gemm_f16_matches_definition(L, ta, tb):
+    for (m, n, k) in SHAPES:
+        for pad, beta in ((0, 0.0), (8, 0.75)):
+            ar, ac = (k, m) if ta else (m, k)
+            br, bc = (n, k) if tb else (k, n)
+            lda, ldb, ldc = (ar + 7) // 8 * 8 + pad, (br + 7) // 8 * 8 + pad, m + pad
+            A = colmajor_h(ar, ac, lda, 21)
+            B = colmajor_h(br, bc, ldb, 22)
+            C0 = colmajor_h(m, n, ldc, 23, fill=5.0)
+            if beta == 0:
+                C0[:, :m] = np.nan  # beta == 0 must not read C
+            dA, dB, dC = (torch.from_numpy(x).cuda() for x in (A, B, C0))
+            st = L.lib.elb200_gemm_f16(ta, tb, m, n, k, 0.5, dA.data_ptr(), lda, dB.data_ptr(), ldb, beta, dC.data_ptr(), ldc, None)
+            assert st == 0, L.lib.elb200_last_error()
+            torch.cuda.synchronize()
+            out = dC.cpu().numpy()
+            a = A[:, :ar].T.astype(np.float64)
+            b = B[:, :br].T.astype(np.float64)
+            opa = a.T if ta else a
+            opb = b.T if tb else b
+            ref = 0.5 * (opa @ opb) + (beta * np.nan_to_num(C0[:, :m].T.astype(np.float64)) if beta else 0.0)
+            got = out[:, :m].T.astype(np.float64)
+            assert np.isfinite(got).all(), (m, n, k, ta, tb)
+            err = np.linalg.norm(got - ref) / np.linalg.norm(ref)
+            assert err <= 1e-3, (m, n, k, ta, tb, beta, err)
+            if pad:
+                assert np.all(out[:, m:] == np.float16(5.0))  # padding rows of C untouched
+
+
+def test_gemm_f16_argument_errors_and_degenerate_cases(L):
+    x = torch.zeros(64 * 64 + 8, dtype=torch.float16, device="cuda")
+    f = L.lib.elb200_gemm_f16
+    assert f(0, 0, 64, 64, 64, 1.0, x.data_ptr() + 2, 64, x.data_ptr(), 64, 0.0, x.data_ptr(), 64, None) == 2      # misaligned base
+    assert f(0, 0, 60, 64, 64, 1.0, x.data_ptr(), 60, x.data_ptr(), 64, 0.0, x.data_ptr(), 60, None) == 2          # lda % 8 != 0
+    assert f(0, 0, 64, 64, 64, 1.0, x.data_ptr(), 32, x.data_ptr(), 64, 0.0, x.data_ptr(), 64, None) == 2          # lda < m
+    c = torch.full((8, 16), 3.0, dtype=torch.float16, device="cuda")
+    assert f(0, 0, 16, 8, 0, 1.0, None, 16, None, 1, 0.5, c.data_ptr(), 16, None) == 0                               # k == 0: C *= beta
+    torch.cuda.synchronize()
+    assert bool((c == 1.5).all())
+
+
+@pytest.mark.parametrize("rows,cols,pad", [(1, 1, 0), (37, 5, 3), (128, 64, 0), (1000, 33, 8), (4096, 257, 0)])
+def test_entrywise_f16(L, rows, cols, pad):
+    lds, ldd = rows + pad, rows + 2 * pad
+    src = colmajor_h(rows, cols, lds, 1)
+    dst0 = colmajor_h(rows, cols, ldd, 2, fill=7.0)
+    dev = lambda a: torch.from_numpy(a.copy()).cuda()  # noqa: E731
+    d, sdev = dev(dst0), dev(src)
+    assert L.lib.elb200_copy2d_f16(rows, cols, sdev.data_ptr(), 1, lds, d.data_ptr(), 1, ldd, None) == 0
+    exp = dst0.copy(); exp[:, :rows] = src[:, :rows]
+    torch.cuda.synchronize()
+    assert np.array_equal(d.cpu().numpy(), exp)
+    d = dev(dst0)
+    assert L.lib.elb200_axpy2d_f16(rows, cols, 0.375, sdev.data_ptr(), 1, lds, d.data_ptr(), 1, ldd, None) == 0
+    exp = dst0.copy()
+    exp[:, :rows] = (np.float32(0.375) * src[:, :rows].astype(np.float32) + dst0[:, :rows].astype(np.float32)).astype(np.float16)
+    torch.cuda.synchronize()
+    assert np.array_equal(d.cpu().numpy(), exp)   # one fp32 fma, one rounding to half
+    d = dev(dst0)
+    assert L.lib.elb200_scale2d_f16(rows, cols, 0.5, d.data_ptr(), ldd, None) == 0
+    exp = dst0.copy(); exp[:, :rows] = (dst0[:, :rows].astype(np.float32) * np.float32(0.5)).astype(np.float16)
+    torch.cuda.synchronize()
+    assert np.array_equal(d.cpu().numpy(), exp)
+    nan = dst0.copy(); nan[:, :rows] = np.nan
+    d = dev(nan)
+    assert L.lib.elb200_scale2d_f16(rows, cols, 0.0, d.data_ptr(), ldd, None) == 0   # exact zeros, no NaN propagation
+    assert L.lib.elb200_fill2d_f16(rows, cols, 0.0, sdev.data_ptr(), lds, None) == 0
+    torch.cuda.synchronize()
+    assert bool((d.cpu()[:, :rows] == 0).all()) and bool((sdev.cpu()[:, :rows] == 0).all())
+    # transpose, general strides (row-strided source)
+    t = torch.zeros((rows, cols + 1), dtype=torch.float16, device="cuda")   # B is cols x rows, ldb = cols + 1
+    sdev = dev(src)
+    assert L.lib.elb200_transpose_f16(rows, cols, sdev.data_ptr(), lds, t.data_ptr(), cols + 1, None) == 0
+    torch.cuda.synchronize()
+    assert np.array_equal(t.cpu().numpy()[:, :cols], src[:, :rows].T)
+    if rows >= 4:
+        half_rows = rows // 2
+        d = dev(dst0)
+        assert L.lib.elb200_copy2d_f16(half_rows, cols, sdev.data_ptr(), 2, lds, d.data_ptr(), 1, ldd, None) == 0
+        exp = dst0.copy(); exp[:, :half_rows] = src[:, 0:2 * half_rows:2]
+        torch.cuda.synchronize()
+        assert np.array_equal(d.cpu().numpy(), exp)

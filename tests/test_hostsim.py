@@ -130,8 +130,8 @@ def test_timeline_model(simlib):
     ideal8 = 2.0 * 16384 ** 3 / 8 / 230e12 * 1e3
     assert ideal8 <= ms8 <= 1.10 * ideal8, (ms8, ideal8)
     # the split + rotated gather may not be slower than the one-piece gather in the model, and is deterministic
-    g_rot = [float(x) for x in re.search(r": ([0-9.]+) / ([0-9.]+) / ([0-9.]+) ms", model("c4", "2", "4", ELB200_AG_SPLIT_MB="4")).groups()]
-    g_one = [float(x) for x in re.search(r": ([0-9.]+) / ([0-9.]+) / ([0-9.]+) ms", model("c4", "2", "4", ELB200_AG_SPLIT_MB="0")).groups()]
+    g_rot = [float(x) for x in re.search(r": ([0-9.]+) / ([0-9.]+) / ([0-9.]+) ms", model("c4", "2", "4", ELB200_AG_SPLIT_BYTES="4194304")).groups()]
+    g_one = [float(x) for x in re.search(r": ([0-9.]+) / ([0-9.]+) / ([0-9.]+) ms", model("c4", "2", "4", ELB200_AG_SPLIT_BYTES="0")).groups()]
     assert g_rot[0] <= g_one[0] and g_rot[1:] == g_one[1:], (g_rot, g_one)
 
 

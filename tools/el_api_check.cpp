@@ -86,10 +86,51 @@ static int exercise(const Grid& g) {
     return bad;
 }
 
+// gpu_half_type: the same calls on DistMatrix<gpu_half_type> and Matrix<gpu_half_type>; the product is
+// compared with the float run of the same (half-representable) inputs.
+static int exercise_half(const Grid& g) {
+    int bad = 0;
+    const Int m = 96, n = 80, k = 112;
+    DistMatrix<float> Af(g), Bf(g), Cf(g);
+    Uniform(Af, m, k, 0.f, 1.f, 1);
+    Uniform(Bf, k, n, 0.f, 1.f, 2);
+    DistMatrix<gpu_half_type, MC, MR, ELEMENT, Device::GPU> A(g), B(g), C(g);
+    A.Resize(m, k); B.Resize(k, n);
+    std::vector<float> hf(size_t(Af.LocalHeight()) * Af.LocalWidth());
+    std::vector<gpu_half_type> hh(hf.size());
+    Af.GetLocalToHost(hf.data());
+    for (size_t i = 0; i < hf.size(); ++i) { hh[i] = gpu_half_type(hf[i]); hf[i] = float(hh[i]); }
+    A.SetLocalFromHost(hh.data()); Af.SetLocalFromHost(hf.data());
+    hf.resize(size_t(Bf.LocalHeight()) * Bf.LocalWidth()); hh.resize(hf.size());
+    Bf.GetLocalToHost(hf.data());
+    for (size_t i = 0; i < hf.size(); ++i) { hh[i] = gpu_half_type(hf[i]); hf[i] = float(hh[i]); }
+    B.SetLocalFromHost(hh.data()); Bf.SetLocalFromHost(hf.data());
+    Gemm(NORMAL, NORMAL, gpu_half_type(2.f), A, B, C, GEMM_SUMMA_C);      // resize overload
+    Gemm(NORMAL, NORMAL, 2.f, Af, Bf, Cf, GEMM_SUMMA_C);
+    DistMatrix<gpu_half_type, STAR, VR> Cv(g);
+    Cv = C;                                                                 // redistribution of a half matrix
+    DistMatrix<gpu_half_type> C2(Cv);
+    hh.resize(size_t(C2.LocalHeight()) * C2.LocalWidth()); hf.resize(hh.size());
+    C2.GetLocalToHost(hh.data());
+    Cf.GetLocalToHost(hf.data());
+    double num = 0, den = 0;
+    for (size_t i = 0; i < hf.size(); ++i) { const double d = double(float(hh[i])) - hf[i]; num += d * d; den += double(hf[i]) * hf[i]; }
+    if (!(num <= 4e-3 * 4e-3 * den)) ++bad;
+    auto Cl = C.Matrix();
+    Matrix<gpu_half_type> L1(Cl.Height(), Cl.Width());
+    SetSyncInfo(L1, SyncInfoFromMatrix(Cl));
+    Copy(Cl, L1);
+    Scale(gpu_half_type(0.5f), L1);
+    Axpy(gpu_half_type(1.f), Cl, L1);
+    Synchronize(SyncInfoFromMatrix(Cl));
+    g.Synchronize();
+    return bad;
+}
+
 int main(int argc, char** argv) {
     Environment env(argc, argv);
     Grid g;  // 1 x 1 on the current device
-    int bad = exercise<float>(g) + exercise<double>(g);
+    int bad = exercise<float>(g) + exercise<double>(g) + exercise_half(g);
     if (Blocksize() != 128 || Grid::DefaultHeight(8) != 2) ++bad;
     std::printf(bad ? "EL_API_CHECK_FAIL %d\n" : "EL_API_CHECK_PASS\n", bad);
     return bad ? 1 : 0;

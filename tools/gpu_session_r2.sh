@@ -88,6 +88,22 @@ case $STAGE in
   log "=== bench.py"; timeout 900 python bench.py --steps 10 --warmup 5 > $OUT/bench_1gpu.json 2> $OUT/bench_1gpu.err; log "exit $?"
   du -sh $OUT | tee -a $OUT/session.log
   ;;
+1e)
+  # full GPU suite (half kernels, communicator exports, facade drivers), half GEMM rate, host-operand switch A/B, launch list + DRAM traffic
+  log "=== pytest -m gpu"; timeout 1500 python -m pytest tests -m gpu -x -q > $OUT/pytest_gpu.log 2>&1; log "exit $?"; tail -4 $OUT/pytest_gpu.log | tee -a $OUT/session.log
+  log "=== f16"; timeout 300 tools/native_bench f16 8192 > $OUT/f16.log 2>&1; log "exit $?"; timeout 300 tools/native_bench f16 16384 >> $OUT/f16.log 2>&1; cat $OUT/f16.log | tee -a $OUT/session.log
+  for v in "X=0" "ELB200_HOST_BRANGES=4" "ELB200_HOST_TAPER=0"; do
+    echo "=== e2e $v" >> $OUT/e2e_variants.log; env $v timeout 200 tools/native_bench e2e 16384 >> $OUT/e2e_variants.log 2>&1; env $v timeout 300 tools/native_bench e2e 32768 >> $OUT/e2e_variants.log 2>&1
+  done
+  cat $OUT/e2e_variants.log | tee -a $OUT/session.log
+  log "=== launch list"; timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 700 --csv --log-file $OUT/launches_bench.csv \
+      python bench.py --steps 2 --warmup 3 --no-cpu --no-parity --no-sub > $OUT/ncu_launches.log 2>&1; log "exit $?"
+  for dt in f32 f64; do
+    timeout 900 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum,lts__t_sector_hit_rate.pct --clock-control none -k regex:gemm_f -c 3 --csv \
+        --log-file $OUT/ncu_traffic_$dt.csv python bench.py --dtype $dt --steps 1 --warmup 1 --no-cpu --no-e2e --no-parity --no-sub > $OUT/ncu_traffic_$dt.log 2>&1; log "ncu traffic $dt exit $?"
+  done
+  du -sh $OUT | tee -a $OUT/session.log
+  ;;
 multi)
   run timeout 900 $TR tests/dist_worker.py
   run timeout 900 $TR tests/dist_worker.py --level3

@@ -7,6 +7,7 @@
 //   native_bench trapcheck      128-bit trapezoid kernel vs the scalar one vs the host definition, bit for bit
 //   native_bench l3 [n]         trapezoid kernel GB/s, elb200_trsm TFLOP/s, Syrk / Gemm through the handle ABI
 #include <cublas_v2.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 
 #include <chrono>
@@ -127,6 +128,54 @@ static int run_f64(int64_t n) {
     }
     cublasDestroy(h);
     return rel <= bound ? 0 : 1;
+}
+
+// native_bench f16 [n]: elb200_gemm_f16 (tcgen05 kind::f16) NT / NN / TN / TT against cublasGemmEx half (fp32 compute)
+__global__ void fill_half_kernel(__half* p, int64_t n, unsigned seed) {
+    for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
+        unsigned h = unsigned(i) * 2654435761u ^ (seed * 40503u + unsigned(i >> 32));
+        h ^= h >> 15; h *= 2246822519u; h ^= h >> 13;
+        p[i] = __float2half_rn((float(h & 0xFFFF) / 65536.0f - 0.5f) * 0.2f);
+    }
+}
+static int run_f16(int64_t n) {
+    __half *A, *B, *C, *R;
+    const size_t bytes = size_t(n) * n * sizeof(__half);
+    CK(cudaMalloc(&A, bytes)); CK(cudaMalloc(&B, bytes)); CK(cudaMalloc(&C, bytes)); CK(cudaMalloc(&R, bytes));
+    fill_half_kernel<<<1184, 256>>>(A, n * n, 1); fill_half_kernel<<<1184, 256>>>(B, n * n, 2); fill_half_kernel<<<1184, 256>>>(C, n * n, 3);
+    CK(cudaMemcpy(R, C, bytes, cudaMemcpyDeviceToDevice));
+    cublasHandle_t h; cublasCreate(&h);
+    const float al = 0.5f, be = -0.5f;
+    int rc = 0;
+    const double flop = 2.0 * double(n) * n * n;
+    const cublasOperation_t ops[2] = {CUBLAS_OP_N, CUBLAS_OP_T};
+    for (int ta = 0; ta < 2; ++ta)
+        for (int tb = 0; tb < 2; ++tb) {
+            CK(cudaMemcpy(C, R, bytes, cudaMemcpyDeviceToDevice));
+            __half* Rc; CK(cudaMalloc(&Rc, bytes)); CK(cudaMemcpy(Rc, R, bytes, cudaMemcpyDeviceToDevice));
+            EK(elb200_gemm_f16(ta, tb, n, n, n, al, A, n, B, n, be, C, n, nullptr));
+            cublasGemmEx(h, ops[ta], ops[tb], int(n), int(n), int(n), &al, A, CUDA_R_16F, int(n), B, CUDA_R_16F, int(n), &be, Rc, CUDA_R_16F, int(n),
+                         CUBLAS_COMPUTE_32F, CUBLAS_GEMM_DEFAULT);
+            CK(cudaDeviceSynchronize());
+            std::vector<__half> hc(size_t(n) * 16), hr(size_t(n) * 16);
+            double num = 0, den = 0;
+            for (int j = 0; j < 16; ++j) {
+                const size_t col = size_t(j) * (n / 16);
+                CK(cudaMemcpy(hc.data() + size_t(j) * n, C + col * n, n * sizeof(__half), cudaMemcpyDeviceToHost));
+                CK(cudaMemcpy(hr.data() + size_t(j) * n, Rc + col * n, n * sizeof(__half), cudaMemcpyDeviceToHost));
+            }
+            for (size_t i = 0; i < hc.size(); ++i) { const double d = double(__half2float(hc[i])) - double(__half2float(hr[i])); num += d * d; den += double(__half2float(hr[i])) * __half2float(hr[i]); }
+            const double rel = std::sqrt(num / den);
+            if (!(rel <= 2e-3)) rc = 1;
+            double ms = time_ms([&] { elb200_gemm_f16(ta, tb, n, n, n, al, A, n, B, n, be, C, n, nullptr); }, 2, 5);
+            double msc = time_ms([&] { cublasGemmEx(h, ops[ta], ops[tb], int(n), int(n), int(n), &al, A, CUDA_R_16F, int(n), B, CUDA_R_16F, int(n), &be, Rc, CUDA_R_16F,
+                                                    int(n), CUBLAS_COMPUTE_32F, CUBLAS_GEMM_DEFAULT); }, 2, 5);
+            std::printf("f16 %c%c n=%lld: elb200_gemm_f16 %.3f ms %.1f TFLOP/s | cublasGemmEx(half, fp32 compute) %.3f ms %.1f TFLOP/s | rel. diff %.2e %s\n",
+                        "NT"[ta], "NT"[tb], (long long)n, ms, flop / ms * 1e-9, msc, flop / msc * 1e-9, rel, rel <= 2e-3 ? "ok" : "FAIL");
+            cudaFree(Rc);
+        }
+    cublasDestroy(h);
+    return rc;
 }
 
 template <typename T>
@@ -252,8 +301,9 @@ int main(int argc, char** argv) {
     const int64_t n = argc > 2 ? std::atoll(argv[2]) : 0;
     if (!std::strcmp(mode, "e2e")) return run_e2e(n > 0 ? n : 16384);
     if (!std::strcmp(mode, "f64")) return run_f64(n > 0 ? n : 8192);
+    if (!std::strcmp(mode, "f16")) return run_f16(n > 0 ? n : 8192);
     if (!std::strcmp(mode, "l3")) return run_l3(n > 0 ? n : 16384);
     if (!std::strcmp(mode, "trapcheck")) return trapcheck_type<float>("f32") + trapcheck_type<double>("f64");
-    std::printf("usage: native_bench e2e|f64|l3|trapcheck [n]\n");
+    std::printf("usage: native_bench e2e|f64|f16|l3|trapcheck [n]\n");
     return 64;
 }
