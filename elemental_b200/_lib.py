@@ -114,6 +114,10 @@ SIGNATURES = {
     "elb200_lattice_f64": (ci, [ci, ci, C.POINTER(Segment), vp, i64, vp, f64, vp]),
     "elb200_peer_reduce_axpy_f32": (ci, [ci, C.POINTER(vp), i64, C.POINTER(Segment), vp, i64, f32, vp]),
     "elb200_peer_reduce_axpy_f64": (ci, [ci, C.POINTER(vp), i64, C.POINTER(Segment), vp, i64, f64, vp]),
+    "elb200_peer_allgather": (ci, [vp, ci, vp, i64, ci, C.POINTER(Segment), vp, i64, vp]),
+    "elb200_peer_exchange": (ci, [vp, ci, ci, C.POINTER(Segment), vp, i64, ci, C.POINTER(Segment), C.POINTER(ci), vp, i64, vp]),
+    "elb200_peer_reduce_scatter_f32": (ci, [vp, ci, C.POINTER(Segment), vp, i64, C.POINTER(Segment), vp, i64, f32, vp]),
+    "elb200_peer_reduce_scatter_f64": (ci, [vp, ci, C.POINTER(Segment), vp, i64, C.POINTER(Segment), vp, i64, f64, vp]),
     "elb200_trapezoid_f32": (ci, [ci, ci, i64, i64, i64, i64, i64, i64, i64, f32, vp, i64, vp, i64, vp]),
     "elb200_trapezoid_f64": (ci, [ci, ci, i64, i64, i64, i64, i64, i64, i64, f64, vp, i64, vp, i64, vp]),
     "elb200_trsm_f32": (ci, [ci, ci, ci, ci, i64, i64, f32, vp, i64, vp, i64, vp]),

@@ -358,7 +358,7 @@ int launch_lattice(int mode, int nseg, const elb200_segment* segs, T* M, int64_t
     if (mode < 0 || mode > 2) return ELB200_ERR_ARG;
     for (int k = 0; k < nseg; ++k)
         if (segs[k].rows < 0 || segs[k].cols < 0 || segs[k].row_step < 1 || segs[k].col_step < 1) return ELB200_ERR_ARG;
-    if (lattice_cta_limit() == 0) {
+    {
         int st = ELB200_OK;
         if (try_interleave<T>(mode, nseg, segs, M, ldm, buf, alpha, s, &st)) return st;
     }
@@ -387,14 +387,6 @@ int launch_lattice(int mode, int nseg, const elb200_segment* segs, T* M, int64_t
     int64_t gx = (rows_v + bx - 1) / bx;
     int64_t gy = (max_cols + by - 1) / by;
     if (gy > 1024) gy = 1024;
-    // Background mode (set by the engine while a redistribution runs underneath a local GEMM):
-    // a handful of CTAs that grid-stride over the lattice, so the copy touches few SMs.
-    const int cap = lattice_cta_limit();
-    if (cap > 0) {
-        const int64_t per_seg = std::max<int64_t>(1, cap / n);
-        if (gx > per_seg) gx = per_seg;
-        if (gx * gy > per_seg) gy = std::max<int64_t>(1, per_seg / gx);
-    }
     dim3 grid(static_cast<unsigned>(gx), static_cast<unsigned>(gy), static_cast<unsigned>(n));
     dim3 block(bx, by);
     count_launch();

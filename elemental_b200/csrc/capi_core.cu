@@ -12,9 +12,6 @@ namespace elb {
 thread_local char g_last_error[512] = "";
 std::atomic<unsigned long long> g_launches{0};
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
-thread_local int g_lattice_cta_limit = 0;
-int lattice_cta_limit() { return g_lattice_cta_limit; }
-void set_lattice_cta_limit(int ctas) { g_lattice_cta_limit = ctas > 0 ? ctas : 0; }
 
 void set_last_error(const char* what, const char* detail) {
     std::snprintf(g_last_error, sizeof(g_last_error), "%s: %s", what, detail ? detail : "");

@@ -95,10 +95,6 @@ struct NcclOrder {  // RAII bracket around one NCCL call (group)
     }
 };
 
-bool coll_arena_enabled() {
-    static const bool on = [] { const char* e = std::getenv("ELB200_COLL_ARENA"); return !e || std::atoi(e) != 0; }();
-    return on;
-}
 
 // ---- id rendezvous without MPI ---------------------------------------------------------------------------
 int env_int(const char* name, int dflt) {
@@ -210,7 +206,7 @@ struct ArenaView {
     int idx;
 };
 bool arena_view(const elb200_comm_s& c, size_t slot_need, ArenaView* v) {
-    if (!c.arena_ok || !coll_arena_enabled() || !c.grid->arena) return false;
+    if (!c.arena_ok || !c.grid->arena) return false;
     if (slot_need > c.grid->arena->slot_bytes()) return false;  // same decision on every rank: equal counts
     v->ar = c.grid->arena;
     v->channel = Grid::arena_channel(c.dist);

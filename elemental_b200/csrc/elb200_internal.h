@@ -25,9 +25,6 @@ struct PerDeviceOnce {
 };
 // every kernel launch of this library bumps a process-wide counter (bench.py's gpu_launches)
 void count_launch();
-// > 0: lattice (pack/unpack) kernels launched by this thread use at most this many CTAs
-int lattice_cta_limit();
-void set_lattice_cta_limit(int ctas);
 
 int gemm_f32_tensor(int transA, int transB, int64_t m, int64_t n, int64_t k, float alpha,
                     const float* A, int64_t lda, const float* B, int64_t ldb, float beta, float* C,

@@ -7,7 +7,6 @@
 
 namespace elb {
 
-void set_lattice_cta_limit(int ctas);  // capi_core.cu
 
 
 template <> struct Dev<float> {

@@ -212,8 +212,7 @@ void SummaC(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, T
     Grid& g = *C.grid;
     // on a 1 x 1 grid no panel moves: the whole k range is one local GEMM (C is read once)
     const int64_t W = g.size() == 1 ? std::max<int64_t>(d.k, 1) : Grid::PanelWidth(sizeof(T));
-    static const bool overlap_on = [] { const char* e = std::getenv("ELB200_OVERLAP"); return !(e && std::atoi(e) == 0); }();
-    if (g.size() > 1 && g.comm_stream && g.arena && overlap_on && !ta && !tb) {
+    if (g.size() > 1 && g.comm_stream && g.arena && !ta && !tb) {
         static const bool direct_on = [] { const char* e = std::getenv("ELB200_DIRECT"); return !(e && std::atoi(e) == 0); }();
         // the two panels live in arena slots: shrink the panel width until they fit
         const int64_t vec = 16 / int64_t(sizeof(T)), nbk = Grid::Blocksize();
@@ -230,7 +229,7 @@ void SummaC(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, T
     }
     // An SM-resident NCCL gather fights the persistent GEMM for SMs (measured: slower than no
     // overlap at all), so the pipeline is used only with the copy-engine peer arena.
-    if (g.size() == 1 || !g.comm_stream || !g.arena || !overlap_on) {
+    if (g.size() == 1 || !g.comm_stream || !g.arena) {
         DistMat<T> PA(g, ta ? STAR : MC, ta ? MC : STAR, C.stream);
         DistMat<T> PB(g, tb ? MR : STAR, tb ? STAR : MR, C.stream);
         for (int64_t k0 = 0; k0 < d.k; k0 += W) {
@@ -263,13 +262,10 @@ void SummaC(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, T
         if (p >= 2) freed[s].block(cs);
         DistMat<T> A1 = ta ? A.View(k0, k0 + kb, 0, d.m) : A.View(0, d.m, k0, k0 + kb);
         DistMat<T> B1 = tb ? B.View(0, d.n, k0, k0 + kb) : B.View(k0, k0 + kb, 0, d.n);
-        // optional cap on the CTAs of unpack kernels that run underneath a GEMM (ELB200_BG_CTAS; off by
-        // default: measured, a short full-width unpack disturbs the GEMM less than a long narrow one)
-        static const int bg_ctas = [] { const char* e = std::getenv("ELB200_BG_CTAS"); return e ? std::atoi(e) : 0; }();
-        set_lattice_cta_limit(p >= 1 ? bg_ctas : 0);
+        // (a cap on the CTAs of unpack kernels running underneath a GEMM was tried and removed: measured, a short full-width
+        // unpack disturbs the GEMM less than a long narrow one — 41.3 ms vs 42.6 / 43.9 ms of GEMM time per step at N = 2)
         const DistMat<T>& a = panel_as(A1, PA[s], C.spec);
         const DistMat<T>& b = panel_as(B1, PB[s], C.spec);
-        set_lattice_cta_limit(0);
         ready[s].record(cs);
         ready[s].block(C.stream);
         LocalGemm(ta, tb, alpha, a, b, p == 0 ? beta : T(1), C);
@@ -289,11 +285,10 @@ struct PanelPipe {
     Ev ready[2], freed[2], start;
     int64_t p = 0;
     PanelPipe(Grid& g, cudaStream_t main_stream) : on(false), cs(main_stream), ms(main_stream) {
-        // Opt-in (ELB200_AB_PIPELINE=1) until it has run on real multi-GPU hardware: unlike the SUMMA-C / Dot / Trrk
-        // pipelines, here BOTH streams run arena operations with flag waits at the same time (the reduce-scatter of
-        // panel p on the compute stream, the exchange of panel p+1 on the comm stream). Correct and race-free on
-        // hostsim; on hardware, streams that share a work queue could couple those waits.
-        static const bool overlap_on = [] { const char* e = std::getenv("ELB200_AB_PIPELINE"); return e && std::atoi(e) != 0; }();
+        // Here BOTH streams run arena operations with flag waits at the same time (the reduce-scatter of panel p on the
+        // compute stream, the exchange of panel p+1 on the comm stream), on different arena channels. Parity on 2 x 2 and
+        // 2 x 4 B200s, C6 on 1 x 2: SUMMA-B 70.7 -> 66.8 ms, SUMMA-A unchanged; ELB200_AB_PIPELINE=0 serialises them again.
+        static const bool overlap_on = [] { const char* e = std::getenv("ELB200_AB_PIPELINE"); return !(e && std::atoi(e) == 0); }();
         on = g.size() > 1 && g.comm_stream && g.arena && overlap_on;
         if (on) {
             cs = g.comm_stream;
@@ -381,7 +376,7 @@ void SummaB(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, D
 template <typename T>
 void SummaDot(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B, DistMat<T>& C, Dims d) {
     Grid& g = *C.grid;
-    static const int64_t kBlock = [] { const char* e = std::getenv("ELB200_DOT_BLOCK"); int64_t v = e ? std::atoll(e) : 0; return v > 0 ? v : int64_t(8192); }();
+    constexpr int64_t kBlock = 8192;  // output tile of the Dot variant (the reference walks 2000 x 2000 tiles, NN.hpp:492-510)
     if (g.size() == 1) {
         // one rank: every distribution is the whole matrix, the k-split and the reduction are
         // identities — multiply straight into C (beta was applied by the caller)
@@ -392,12 +387,11 @@ void SummaDot(int ta, int tb, T alpha, const DistMat<T>& A, const DistMat<T>& B,
     // pipelined against the local GEMM over two slots, like the SUMMA-C panels — the exchange of range c+1
     // (comm stream: pack, copy-engine pulls, unpack) runs under the GEMM of range c, and the tile accumulates
     // in C11 across ranges before its single reduce-scatter. ELB200_DOT_CHUNK = local k per range (default
-    // 4096 fp32 / 2048 fp64), ELB200_DOT_PIPELINE=0 restores the one-shot exchange.
-    static const bool pipe_on = [] { const char* e = std::getenv("ELB200_DOT_PIPELINE"); return !(e && std::atoi(e) == 0); }();
+    // 4096 fp32 / 2048 fp64). C5 at 2 x 4: 25.2 -> 21.7 ms (1395 -> 1624 TFLOP/s) against the one-shot exchange, which was removed.
     static const int64_t chunk_env = [] { const char* e = std::getenv("ELB200_DOT_CHUNK"); return e ? std::atoll(e) : 0ll; }();
     const int64_t chunk_local = chunk_env > 0 ? chunk_env : (sizeof(T) == 4 ? 4096 : 2048);
     const int64_t chunk = chunk_local * g.size();  // global k per range
-    if (pipe_on && g.comm_stream && d.m <= kBlock && d.n <= kBlock && d.k >= 2 * chunk) {
+    if (g.comm_stream && d.m <= kBlock && d.n <= kBlock && d.k >= 2 * chunk) {
         cudaStream_t cs = g.comm_stream;
         DistMat<T> Aks[2] = {DistMat<T>(g, ta ? VC : STAR, ta ? STAR : VC, cs), DistMat<T>(g, ta ? VC : STAR, ta ? STAR : VC, cs)};
         DistMat<T> Bks[2] = {DistMat<T>(g, tb ? STAR : VC, tb ? VC : STAR, cs), DistMat<T>(g, tb ? STAR : VC, tb ? VC : STAR, cs)};
@@ -547,8 +541,7 @@ void GemmHost(Grid& g, int ta, int tb, int64_t m, int64_t n, int64_t k, T alpha,
     // unit, unit). What is left to do after the last byte has gone up — the product and the download of the last
     // block — is pure latency on top of the PCIe-bound pipeline; with uniform blocks that was 1/8 of the product
     // plus 1/8 of the download (≈ 7 ms of 66 at n = 16384 fp32), with the taper it is one unit's worth (< 1 ms).
-    // ELB200_HOST_TAPER=0 keeps uniform blocks.
-    static const bool taper = [] { const char* e = std::getenv("ELB200_HOST_TAPER"); return !e || std::atoi(e) != 0; }();
+    constexpr bool taper = true;  // measured (B200, n = 16384 / 32768 fp32): 64.4 / 379.5 ms with the taper, 66.7 / 385.9 ms without
     std::vector<int64_t> starts;  // block j = columns [starts[j], starts[j+1])
     {
         int64_t at = 0;
@@ -576,12 +569,13 @@ void GemmHost(Grid& g, int ta, int tb, int64_t m, int64_t n, int64_t k, T alpha,
         Cin.emplace_back(g, MC, MR, s);
         PB.emplace_back(g, tb ? MR : STAR, tb ? STAR : MR, cs);
     }
-    // Opt-in (ELB200_HOST_BRANGES=R > 1; not measured on a GPU yet): blocks 1.. upload their B slice
+    // ELB200_HOST_BRANGES=R (default 4): blocks 1.. upload their B slice
     // in R k ranges and multiply each range as it lands, accumulating into the block with beta = 0 on the first;
     // the C slice goes up AFTER them into a landing block and is folded in by one axpy (C_j = acc + beta * C_j).
     // The product then trails the upload by one range instead of one block.
     constexpr int kMaxBRanges = 8;
-    static const int b_ranges_env = [] { const char* e = std::getenv("ELB200_HOST_BRANGES"); return e ? std::atoi(e) : 1; }();
+    // default 4 since round 2: 64.4 -> 62.4 ms at n = 16384, 379.5 -> 370.8 ms at n = 32768 (fp32, one B200); 1 restores whole-slice uploads
+    static const int b_ranges_env = [] { const char* e = std::getenv("ELB200_HOST_BRANGES"); return e ? std::atoi(e) : 4; }();
     const int b_ranges = product ? int(std::min<int64_t>(std::min(kMaxBRanges, std::max(1, b_ranges_env)), std::max<int64_t>(1, k / host_min_krange()))) : 1;
     const int64_t Kb = (k + b_ranges - 1) / b_ranges;
     Ev b_up[kSlots][kMaxBRanges], b_ready[kSlots][kMaxBRanges];

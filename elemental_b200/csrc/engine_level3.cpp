@@ -194,9 +194,8 @@ void Trrk(int uplo, int ta, int tb, T alpha, const DistMat<T>& Apre, const DistM
         const int64_t W = g.size() == 1 ? k : Grid::PanelWidth(sizeof(T));
         // With the copy-engine peer arena the gathers of panel p+1 run on the comm stream under the local
         // products of panel p (two panel slots, ready / freed events), as in SUMMA-C (engine_gemm.cpp); without
-        // it (one rank, NCCL only, ELB200_OVERLAP=0) everything is on C's stream.
-        static const bool overlap_on = [] { const char* e = std::getenv("ELB200_OVERLAP"); return !(e && std::atoi(e) == 0); }();
-        const bool pipe = g.size() > 1 && g.comm_stream && g.arena && overlap_on;
+        // it (one rank, NCCL only) everything is on C's stream.
+        const bool pipe = g.size() > 1 && g.comm_stream && g.arena;
         cudaStream_t ps = pipe ? g.comm_stream : C.stream;
         DistMat<T> PA[2] = {DistMat<T>(g, ta ? STAR : MC, ta ? MC : STAR, ps), DistMat<T>(g, ta ? STAR : MC, ta ? MC : STAR, ps)};
         DistMat<T> PB[2] = {DistMat<T>(g, tb ? MR : STAR, tb ? STAR : MR, ps), DistMat<T>(g, tb ? MR : STAR, tb ? STAR : MR, ps)};

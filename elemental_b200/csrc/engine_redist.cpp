@@ -43,6 +43,25 @@ void adopt_alignment(const DistMat<T>& A, DistMat<T>& B) {
 
 }  // namespace
 
+// Messages that keep less than this in an arena slot are pure latency and take the fused one-kernel forms of
+// peer_kernels.cu (ELB200_FUSED_BYTES overrides the 4 MiB default, 0 disables them). Every rank evaluates the bound on
+// rank-invariant extents, so all members of a collective choose the same form.
+static int64_t fused_bytes() {
+    static const int64_t v = [] { const char* e = std::getenv("ELB200_FUSED_BYTES"); return e ? std::atoll(e) : (4ll << 20); }();
+    return v;
+}
+template <typename T> struct FusedReduce { static constexpr bool ok = false; };
+template <> struct FusedReduce<float> {
+    static constexpr bool ok = true;
+    static int run(const elb200_peer_gather* pg, int n, const elb200_segment* packs, const float* A, int64_t lda, const elb200_segment* un, float* B,
+                   int64_t ldb, float alpha, cudaStream_t s) { return elb200_peer_reduce_scatter_f32(pg, n, packs, A, lda, un, B, ldb, alpha, s); }
+};
+template <> struct FusedReduce<double> {
+    static constexpr bool ok = true;
+    static int run(const elb200_peer_gather* pg, int n, const elb200_segment* packs, const double* A, int64_t lda, const elb200_segment* un, double* B,
+                   int64_t ldb, double alpha, cudaStream_t s) { return elb200_peer_reduce_scatter_f64(pg, n, packs, A, lda, un, B, ldb, alpha, s); }
+};
+
 template <typename T>
 void Copy(const DistMat<T>& A, DistMat<T>& B) {
     if (A.grid != B.grid) throw EngineError(ELB200_ERR_ARG, "Copy: matrices live on different grids");
@@ -108,6 +127,17 @@ void Copy(const DistMat<T>& A, DistMat<T>& B) {
                 g.arena->Release(t, members, idx, s);
                 return;
             }
+            // Small blocks: the whole gather and its unpack in ONE kernel over peer memory (peer_kernels.cu) instead of ~30
+            // stream operations — these sizes are pure latency (1 MiB on 1 x 2: 40 -> 25 us).
+            if (int64_t(gsz) * plan.portion * int64_t(sizeof(T)) < fused_bytes() && gsz <= ELB200_MAX_SEGMENTS) {
+                elb200_segment segs[ELB200_MAX_SEGMENTS];
+                int nseg = 0;
+                for (const Message& m : plan.recvs)
+                    if (m.count() > 0) segs[nseg++] = m.seg;
+                g.arena->FusedAllGather(Grid::arena_channel(plan.comm_dist), members, idx, int(sizeof(T)), send, mine, plan.portion, nseg, segs,
+                                        B.buf, B.ldim, s);
+                return;
+            }
             PeerArena::Ticket t = g.arena->AllGather(Grid::arena_channel(plan.comm_dist), members, idx, send,
                                                      size_t(mine) * sizeof(T), size_t(plan.portion) * sizeof(T), s);
             run_lattice<T>(ELB200_UNPACK, plan.recvs, B.buf, B.ldim, static_cast<T*>(t.data), T(0), s);
@@ -138,7 +168,7 @@ void Copy(const DistMat<T>& A, DistMat<T>& B) {
     // and the receivers fetch their messages from the senders' slots with the copy engines — no
     // NCCL kernels, no SMs during the transfer. Taken when the largest possible send staging fits a
     // slot, by a bound every rank evaluates identically: a whole local matrix of A ...
-    static const bool pull = [] { const char* e = std::getenv("ELB200_A2A_PULL"); return !e || std::atoi(e) != 0; }();
+    constexpr bool pull = true;  // measured at 2 x 4, 1 GiB [MC,MR] -> [*,VR]: 328 GB/s per GPU against 177 with NCCL point-to-point
     // ... times the number of ranks that hold a copy of each entry under B's distribution: a sender packs one
     // message per destination, so towards a replicated target (e.g. [MC,MR] -> [MR,*]) its staging is that many
     // times its local matrix.
@@ -148,6 +178,25 @@ void Copy(const DistMat<T>& A, DistMat<T>& B) {
     if (pull && g.arena && max_local_a <= g.arena->slot_bytes()) {
         const std::vector<int> members = g.comm_members(VC);
         const int idx = g.vc_rank;
+        if (int64_t(max_local_a) < fused_bytes() && g.size() <= ELB200_MAX_SEGMENTS && plan.sends.size() <= size_t(ELB200_MAX_SEGMENTS) &&
+            plan.recvs.size() <= size_t(ELB200_MAX_SEGMENTS)) {
+            // small: pack into my slot, flags, and the unpack straight out of the senders' slots in ONE kernel
+            elb200_segment snd[ELB200_MAX_SEGMENTS], rcv[ELB200_MAX_SEGMENTS];
+            int from[ELB200_MAX_SEGMENTS];
+            int ns = 0, nr = 0;
+            for (const Message& m : plan.sends) snd[ns++] = m.seg;
+            for (const Message& m : plan.recvs) {
+                rcv[nr] = m.seg;
+                // where the sender packed the message for me inside its slot
+                rcv[nr].buf_offset = plan_send_offset(g.shape, coord_of_vc(g.shape, m.peer), A.spec, B.spec, g.vc_rank);
+                from[nr++] = m.peer;  // VC rank == index among the world channel's members
+            }
+            const elb200_peer_gather pg = g.arena->FusedBegin(Grid::arena_channel(VC), members, idx, 0, size_t(plan.send_elems) * sizeof(T));
+            throw_status(elb200_peer_exchange(&pg, int(sizeof(T)), ns, snd, A.buf, A.ldim, nr, rcv, from, B.buf, B.ldim, s), "elb200_peer_exchange");
+            if (plan.has_self)
+                lattice_to_lattice<T>(plan.self_send.seg, A.buf, A.ldim, plan.self_recv.seg, B.buf, B.ldim, s);
+            return;
+        }
         PeerArena::Ticket t = g.arena->Publish(Grid::arena_channel(VC), members, idx, size_t(plan.send_elems) * sizeof(T), s);
         run_lattice<T>(ELB200_PACK, plan.sends, Abuf, A.ldim, static_cast<T*>(t.data), T(0), s);
         g.arena->Signal(t, members, idx, s);
@@ -263,6 +312,19 @@ void AxpyContract(T alpha, const DistMat<T>& A, DistMat<T>& B) {
         // from all members' slots, sums them in communicator order and applies the axpy-unpack.
         const std::vector<int> members = g.comm_members(plan.comm_dist);
         const int idx = g.comm_index(plan.comm_dist);
+        if constexpr (FusedReduce<T>::ok) {
+            if (int64_t(plan.group) * plan.portion * int64_t(sizeof(T)) < fused_bytes() && idx == plan.my_index &&
+                plan.packs.size() <= size_t(ELB200_MAX_SEGMENTS)) {
+                // small: pack, flags, and the sum of my portion over the members' slots + axpy-unpack in ONE kernel
+                elb200_segment pk[ELB200_MAX_SEGMENTS];
+                int np = 0;
+                for (const Message& m : plan.packs) pk[np++] = m.seg;
+                const elb200_peer_gather pg = g.arena->FusedBegin(Grid::arena_channel(plan.comm_dist), members, idx, plan.portion,
+                                                                  size_t(plan.group) * plan.portion * sizeof(T));
+                throw_status(FusedReduce<T>::run(&pg, np, pk, A.buf, A.ldim, &plan.unpack, B.buf, B.ldim, alpha, s), "elb200_peer_reduce_scatter");
+                return;
+            }
+        }
         PeerArena::Ticket t = g.arena->Publish(Grid::arena_channel(plan.comm_dist), members, idx,
                                                size_t(plan.group) * plan.portion * sizeof(T), s);
         run_lattice<T>(ELB200_PACK, plan.packs, Abuf, A.ldim, static_cast<T*>(t.data), T(0), s);

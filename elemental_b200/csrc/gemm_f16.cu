@@ -12,6 +12,8 @@
 //   warp 1      UMMA issuer         tcgen05.mma kind::f16, fp32 accumulators in TMEM (2 buffers)
 //   warps 2-5   epilogue            tcgen05.ld, alpha/beta in fp32, half stores (coalesced down the columns of C)
 // Pipelines: full[s] (TMA->issuer), empty[s] (issuer->TMA), tmem_full[a] (issuer->epilogue), tmem_empty[a] (epilogue->issuer).
+// With cta_group::2 both CTAs' loads complete on the LEADER's full[s] (cp.async.bulk.tensor.cta_group::2), where the one
+// issuer of the pair waits; the commit that frees a stage is multicast to both CTAs' empty[s].
 #include <cuda_runtime.h>
 #include <cuda.h>
 #include <cuda_fp16.h>
@@ -26,14 +28,15 @@
 namespace elb {
 namespace {
 
-constexpr int kStages = 6;
+constexpr int kStages = 6;  // 7 fit (224 KiB) and measured the same: 1275 vs 1275 TFLOP/s at n = 8192
 constexpr int kBK = 64;                       // halfs per k-block = one 128B swizzle row
 constexpr int kTileMN = 128;                  // rows of A / rows of B held per CTA per stage
 constexpr int kOperandBytes = kTileMN * kBK * 2;   // 16 KiB
 constexpr int kStageBytes = 2 * kOperandBytes;     // A, B
 constexpr int kOffAraw = 0, kOffBraw = kOperandBytes;
-constexpr int kThreads = 224;  // TMA, UMMA, 4 epilogue warps, relay
+constexpr int kThreads = 192;  // TMA, UMMA, 4 epilogue warps
 constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+static_assert(kSmemBytes <= 227 * 1024, "stage ring exceeds the 227 KiB a CTA may use");
 
 enum : int { MAJOR_K = 0, MAJOR_MN = 1 };
 
@@ -78,13 +81,17 @@ struct Params {
     int64_t ldc;
     int m, n, k;
     float alpha, beta;
-    int tiles_m, tiles_n;
+    int tiles_m, tiles_n;  // tiles_m counts cluster rows: kPairs output tiles of 128*CG rows each
 };
 
-template <int CG, int AMAJ, int BMAJ>
+// CG = CTAs per UMMA (cta_group), PAIRS = CTA pairs per cluster (1, or 2 with CG == 2: a 4-CTA cluster computing two
+// 256 x 256 tiles that are neighbours in m and share their B tile, which is loaded ONCE from L2 and multicast).
+template <int CG, int AMAJ, int BMAJ, int PAIRS>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA,
                        const __grid_constant__ CUtensorMap tmB, const Params p) {
+    static_assert(PAIRS == 1 || (PAIRS == 2 && CG == 2), "multicast needs CTA pairs");
+    constexpr int kCluster = CG * PAIRS;
     constexpr int kUmmaM = 128 * CG;
     constexpr int kUmmaN = 128 * CG;
     constexpr uint32_t kTmemCols = 2 * kUmmaN;  // two accumulator buffers
@@ -96,27 +103,28 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA,
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t bar_base = smem_base + kStages * kStageBytes;
     auto full_bar = [&](int s) { return bar_base + 8u * s; };
-    auto ready_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
-    auto empty_bar = [&](int s) { return bar_base + 8u * (2 * kStages + s); };
-    auto tfull_bar = [&](int a) { return bar_base + 8u * (3 * kStages + a); };
-    auto tempty_bar = [&](int a) { return bar_base + 8u * (3 * kStages + 2 + a); };
-    const uint32_t tmem_slot = bar_base + 8u * (3 * kStages + 4);
+    auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
+    auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kStages + a); };
+    auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kStages + 2 + a); };
+    const uint32_t tmem_slot = bar_base + 8u * (2 * kStages + 4);
     uint32_t* tmem_slot_ptr =
         reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    const uint32_t cta_rank = (CG == 2) ? cluster_ctarank() : 0u;
-    const int cluster_id = blockIdx.x / CG;
-    const int num_clusters = gridDim.x / CG;
+    const uint32_t cluster_rank = (kCluster > 1) ? cluster_ctarank() : 0u;
+    const uint32_t cta_rank = cluster_rank & uint32_t(CG - 1);  // rank inside the pair: 0 = leader
+    const uint32_t pair = cluster_rank / CG;                     // which pair of the cluster
+    const uint32_t leader = cluster_rank - cta_rank;             // cluster rank of this pair's leader
+    const int cluster_id = blockIdx.x / kCluster;
+    const int num_clusters = gridDim.x / kCluster;
     const int num_tiles = p.tiles_m * p.tiles_n;
     const int num_kb = (p.k + kBK - 1) / kBK;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; ++s) {
-            mbar_init(full_bar(s), 1);
-            mbar_init(ready_bar(s), CG);  // one relay arrival per CTA of the pair
-            mbar_init(empty_bar(s), 1);
+            mbar_init(full_bar(s), 1);       // the leader's expect_tx arrival; the bytes landing in BOTH CTAs of the pair complete on it
+            mbar_init(empty_bar(s), PAIRS);  // every pair of the cluster has consumed the stage (others' multicasts land in it too)
         }
         for (int a = 0; a < 2; ++a) {
             mbar_init(tfull_bar(a), 1);
@@ -130,45 +138,59 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA,
     }
     if (warp == 1) tmem_alloc<CG>(tmem_slot, kTmemCols);
     tc_fence_before_sync();
-    if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
+    if constexpr (kCluster > 1) cluster_sync_all(); else __syncthreads();
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot_ptr;
 
     if (warp == 0) {
-        // ------------------------------------------------------------ TMA producer
+        // ------------------------------------------------------------ TMA producer (one per CTA; completions go to the pair leader)
         if (lane == 0) {
+            auto load = [&](const CUtensorMap* tm, uint32_t bar, uint32_t dst, int c0, int c1) {
+                if constexpr (CG == 2) tma_load_2d_pair(tm, bar, dst, c0, c1, leader);
+                else tma_load_2d(tm, bar, dst, c0, c1);
+            };
             int s = 0; uint32_t ph = 0;
             for (int t = cluster_id; t < num_tiles; t += num_clusters) {
                 int tm, tn;
                 tile_coords(t, p.tiles_m, p.tiles_n, tm, tn);
-                const int m0 = tm * kUmmaM + int(cta_rank) * kTileMN;
+                const int m0 = (tm * PAIRS + int(pair)) * kUmmaM + int(cta_rank) * kTileMN;
                 const int n0 = tn * kUmmaN + int(cta_rank) * kTileMN;
                 for (int kb = 0; kb < num_kb; ++kb) {
                     mbar_wait(empty_bar(s), ph ^ 1u);
                     const uint32_t st = smem_base + s * kStageBytes;
-                    mbar_expect_tx(full_bar(s), 2 * kOperandBytes);
+                    if (cta_rank == 0) mbar_expect_tx(full_bar(s), CG * kStageBytes);
                     const int k0 = kb * kBK;
                     if constexpr (AMAJ == MAJOR_MN) {
 #pragma unroll
                         for (int j = 0; j < 2; ++j)
-                            tma_load_2d(&tmA, full_bar(s), st + kOffAraw + j * 8192, m0 + 64 * j, k0);
+                            load(&tmA, full_bar(s), st + kOffAraw + j * 8192, m0 + 64 * j, k0);
                     } else {
-                        tma_load_2d(&tmA, full_bar(s), st + kOffAraw, k0, m0);
+                        load(&tmA, full_bar(s), st + kOffAraw, k0, m0);
                     }
-                    if constexpr (BMAJ == MAJOR_MN) {
+                    if constexpr (PAIRS == 2) {
+                        // my 128 rows of B are also the 128 rows of the CTA with the same pair rank in the other pair: each of
+                        // the two fetches one 64-row half (8 KiB, 1024-aligned: the same SWIZZLE_128B image as one box) for both
+                        const uint16_t mask = uint16_t((1u << cta_rank) | (1u << (cta_rank + CG)));
+                        const uint32_t dst = st + kOffBraw + pair * 8192;
+                        const int nb = n0 + 64 * int(pair);
+                        if constexpr (BMAJ == MAJOR_MN) tma_load_2d_pair_mc(&tmB, full_bar(s), dst, nb, k0, leader, mask);
+                        else tma_load_2d_pair_mc(&tmB, full_bar(s), dst, k0, nb, leader, mask);
+                    } else if constexpr (BMAJ == MAJOR_MN) {
 #pragma unroll
                         for (int j = 0; j < 2; ++j)
-                            tma_load_2d(&tmB, full_bar(s), st + kOffBraw + j * 8192, n0 + 64 * j, k0);
+                            load(&tmB, full_bar(s), st + kOffBraw + j * 8192, n0 + 64 * j, k0);
                     } else {
-                        tma_load_2d(&tmB, full_bar(s), st + kOffBraw, k0, n0);
+                        load(&tmB, full_bar(s), st + kOffBraw, k0, n0);
                     }
                     if (++s == kStages) { s = 0; ph ^= 1u; }
                 }
             }
         }
     } else if (warp == 1) {
-        // ------------------------------------------------------------ UMMA issuer (leader CTA)
+        // ------------------------------------------------------------ UMMA issuer (the pair's leader CTA)
         if (cta_rank == 0) {
+            const uint16_t pair_mask = uint16_t(((1u << CG) - 1u) << leader);
+            const uint16_t cluster_mask = uint16_t((1u << kCluster) - 1u);
             int s = 0; uint32_t ph = 0;
             int it = 0;
             for (int t = cluster_id; t < num_tiles; t += num_clusters, ++it) {
@@ -178,7 +200,7 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA,
                 tc_fence_after_sync();
                 const uint32_t d_tmem = tmem_base + uint32_t(acc * kUmmaN);
                 for (int kb = 0; kb < num_kb; ++kb) {
-                    mbar_wait(ready_bar(s), ph);
+                    mbar_wait(full_bar(s), ph);
                     tc_fence_after_sync();
                     if (lane == 0) {
                         const uint32_t st = smem_base + s * kStageBytes;
@@ -188,29 +210,12 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA,
                             const uint64_t b_d = operand_desc<BMAJ>(st + kOffBraw, kk);
                             umma_f16<CG>(d_tmem, a_d, b_d, kIdesc, (kb | kk) != 0 ? 1u : 0u);
                         }
-                        umma_commit<CG>(empty_bar(s));
-                        if (kb == num_kb - 1) umma_commit<CG>(tfull_bar(acc));
+                        umma_commit<CG>(empty_bar(s), cluster_mask);
+                        if (kb == num_kb - 1) umma_commit<CG>(tfull_bar(acc), pair_mask);
                     }
                     __syncwarp();
                     if (++s == kStages) { s = 0; ph ^= 1u; }
                 }
-            }
-        }
-    } else if (warp == 6) {
-        // ------------------------------------------------------------ relay: "my CTA's tiles have landed" -> the issuer.
-        // With cta_group::2 the issuer lives in the leader CTA only and must know that BOTH CTAs' operand tiles are in
-        // place; each CTA's TMA completes on its own full barrier, and this warp forwards that completion to the leader's
-        // ready barrier (the job the splitter warps do in the fp32 kernel, without the arithmetic).
-        int s = 0; uint32_t ph = 0;
-        for (int t = cluster_id; t < num_tiles; t += num_clusters) {
-            for (int kb = 0; kb < num_kb; ++kb) {
-                mbar_wait(full_bar(s), ph);
-                if (lane == 0) {
-                    if constexpr (CG == 2) mbar_arrive_cluster(ready_bar(s), 0);
-                    else mbar_arrive(ready_bar(s));
-                }
-                __syncwarp();
-                if (++s == kStages) { s = 0; ph ^= 1u; }
             }
         }
     } else {
@@ -222,7 +227,7 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA,
             tile_coords(t, p.tiles_m, p.tiles_n, tm, tn);
             const int acc = it & 1;
             const uint32_t acc_ph = (it >> 1) & 1;
-            const int row = tm * kUmmaM + int(cta_rank) * kTileMN + q * 32 + lane;
+            const int row = (tm * PAIRS + int(pair)) * kUmmaM + int(cta_rank) * kTileMN + q * 32 + lane;
             const int n0 = tn * kUmmaN;
             mbar_wait(tfull_bar(acc), acc_ph);
             tc_fence_after_sync();
@@ -254,14 +259,14 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmA,
             tc_fence_before_sync();
             __syncwarp();
             if (lane == 0) {
-                if constexpr (CG == 2) mbar_arrive_cluster(tempty_bar(acc), 0);
+                if constexpr (CG == 2) mbar_arrive_cluster(tempty_bar(acc), leader);
                 else mbar_arrive(tempty_bar(acc));
             }
         }
     }
 
     tc_fence_before_sync();
-    if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
+    if constexpr (kCluster > 1) cluster_sync_all(); else __syncthreads();
     if (warp == 1) tmem_dealloc<CG>(tmem_base, kTmemCols);
 }
 
@@ -286,14 +291,15 @@ EncodeTiledFn get_encode_fn() {
 
 // Tensor map over a column-major matrix X (rows x cols, leading dimension ld, half).
 //  as_mn_major: the GEMM's M/N index runs down X's columns (contiguous) -> box 64(mn) x 64(k)
-//  else       : the GEMM's K index runs down X's columns (contiguous)   -> box 64(k)  x 128(mn)
+//  else       : the GEMM's K index runs down X's columns (contiguous)   -> box 64(k)  x 128(mn), or x 64(mn) when the
+//               128 rows are fetched as two multicast halves (half_box)
 bool encode_operand(CUtensorMap* tm, const __half* X, int64_t rows, int64_t cols, int64_t ld,
-                    bool as_mn_major) {
+                    bool as_mn_major, bool half_box = false) {
     EncodeTiledFn enc = get_encode_fn();
     if (!enc) return false;
     cuuint64_t dims[2] = {cuuint64_t(rows), cuuint64_t(cols)};
     cuuint64_t strides[1] = {cuuint64_t(ld) * 2};
-    cuuint32_t box[2] = {64u, as_mn_major ? 64u : 128u};
+    cuuint32_t box[2] = {64u, (as_mn_major || half_box) ? 64u : 128u};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<__half*>(X), dims, strides,
                      box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
@@ -301,10 +307,11 @@ bool encode_operand(CUtensorMap* tm, const __half* X, int64_t rows, int64_t cols
     return r == CUDA_SUCCESS;
 }
 
-template <int CG, int AMAJ, int BMAJ>
+template <int CG, int AMAJ, int BMAJ, int PAIRS>
 cudaError_t launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const Params& p, int num_sms,
                    cudaStream_t stream) {
-    auto kern = gemm_f16_kernel<CG, AMAJ, BMAJ>;
+    auto kern = gemm_f16_kernel<CG, AMAJ, BMAJ, PAIRS>;
+    constexpr int kCluster = CG * PAIRS;
     static PerDeviceOnce once;
     int dev;
     if (once.needs(&dev)) {
@@ -314,16 +321,16 @@ cudaError_t launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const Params&
         once.set(dev);
     }
     const int num_tiles = p.tiles_m * p.tiles_n;
-    int clusters = num_sms / CG;
+    int clusters = num_sms / kCluster;
     if (clusters > num_tiles) clusters = num_tiles;
     cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(unsigned(clusters * CG));
+    cfg.gridDim = dim3(unsigned(clusters * kCluster));
     cfg.blockDim = dim3(kThreads);
     cfg.dynamicSmemBytes = kSmemBytes;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = CG;
+    attr[0].val.clusterDim.x = kCluster;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
@@ -352,22 +359,30 @@ int gemm_f16_tensor(int transA, int transB, int64_t m, int64_t n, int64_t k, flo
     CUtensorMap tmA, tmB;
     const int64_t a_rows = a_mn ? m : k, a_cols = a_mn ? k : m;
     const int64_t b_rows = b_mn ? n : k, b_cols = b_mn ? k : n;
+    const int tile = 128 * cta_group;
+    const int tiles_m = int((m + tile - 1) / tile);
+    // Two tiles that are neighbours in m share their B tile: with ELB200_F16_MULTICAST=1 a 4-CTA cluster fetches it once
+    // and multicasts it (L2 -> SM bytes per flop drop by a quarter). OPT-IN because it measured SLOWER on B200 — 790 vs
+    // 1294 TFLOP/s at n = 8192, 819 vs 1349 at 16384 (profiles/r02_f16_multicast.log): the two pairs of a cluster then
+    // advance in lockstep through every stage (each stage's empty barrier needs both pairs' commits, each full barrier
+    // loads issued by all four CTAs), and at cluster size 4 L2 already merges most of the duplicate reads.
+    static const bool mc_on = [] { const char* v = std::getenv("ELB200_F16_MULTICAST"); return v && std::atoi(v) != 0; }();
+    const int pairs = (cta_group == 2 && tiles_m >= 2 && mc_on) ? 2 : 1;
     if (!encode_operand(&tmA, A, a_rows, a_cols, lda, a_mn)) return ELB200_ERR_TENSORMAP;
-    if (!encode_operand(&tmB, B, b_rows, b_cols, ldb, b_mn)) return ELB200_ERR_TENSORMAP;
+    if (!encode_operand(&tmB, B, b_rows, b_cols, ldb, b_mn, pairs == 2)) return ELB200_ERR_TENSORMAP;
     Params p;
     p.C = C; p.ldc = ldc; p.m = int(m); p.n = int(n); p.k = int(k);
     p.alpha = alpha; p.beta = beta;
-    const int tile = 128 * cta_group;
-    p.tiles_m = int((m + tile - 1) / tile);
+    p.tiles_m = (tiles_m + pairs - 1) / pairs;
     p.tiles_n = int((n + tile - 1) / tile);
     const int num_sms = device_sm_count();
     cudaError_t e;
-#define ELB_DISPATCH(CGV)                                                                   \
-    if (a_mn && b_mn) e = launch<CGV, MAJOR_MN, MAJOR_MN>(tmA, tmB, p, num_sms, stream);    \
-    else if (a_mn && !b_mn) e = launch<CGV, MAJOR_MN, MAJOR_K>(tmA, tmB, p, num_sms, stream); \
-    else if (!a_mn && b_mn) e = launch<CGV, MAJOR_K, MAJOR_MN>(tmA, tmB, p, num_sms, stream); \
-    else e = launch<CGV, MAJOR_K, MAJOR_K>(tmA, tmB, p, num_sms, stream);
-    if (cta_group == 2) { ELB_DISPATCH(2) } else { ELB_DISPATCH(1) }
+#define ELB_DISPATCH(CGV, PR)                                                                   \
+    if (a_mn && b_mn) e = launch<CGV, MAJOR_MN, MAJOR_MN, PR>(tmA, tmB, p, num_sms, stream);    \
+    else if (a_mn && !b_mn) e = launch<CGV, MAJOR_MN, MAJOR_K, PR>(tmA, tmB, p, num_sms, stream); \
+    else if (!a_mn && b_mn) e = launch<CGV, MAJOR_K, MAJOR_MN, PR>(tmA, tmB, p, num_sms, stream); \
+    else e = launch<CGV, MAJOR_K, MAJOR_K, PR>(tmA, tmB, p, num_sms, stream);
+    if (pairs == 2) { ELB_DISPATCH(2, 2) } else if (cta_group == 2) { ELB_DISPATCH(2, 1) } else { ELB_DISPATCH(1, 1) }
 #undef ELB_DISPATCH
     return e == cudaSuccess ? ELB200_OK : ELB200_ERR_CUDA;
 }

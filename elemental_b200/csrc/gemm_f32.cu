@@ -381,7 +381,7 @@ int gemm_f32_tensor(int transA, int transB, int64_t m, int64_t n, int64_t k, flo
     // chunks that accumulate through the epilogue's rounded fp32 FMA (beta = 1 after the first):
     // k = 262144 (BASELINE C5) then stays near 1e-4 instead of 1e-3 for < 1% more time. The bench
     // shape (k = 16384) is one launch.
-    static const int64_t kchunk = [] { const char* e = std::getenv("ELB200_F32_KCHUNK"); int64_t v = e ? std::atoll(e) : 0; return v >= 256 ? v / 32 * 32 : int64_t(16384); }();
+    constexpr int64_t kchunk = 16384;
     if (k > kchunk + kchunk / 2) {
         for (int64_t k0 = 0; k0 < k; k0 += kchunk) {
             const int64_t kc = (k - k0 < kchunk + kchunk / 2) ? k - k0 : kchunk;

@@ -30,8 +30,12 @@
 namespace elb {
 namespace {
 
+// Raster order: groups of kGroup tile columns, tile rows fastest inside a group. With four 64 x 64 CTAs on each of 148 SMs the
+// ~590 tiles in flight then form a window about kGroup wide and 590 / kGroup tall; 16 makes it 16 x 37 (8 was 8 x 74), i.e.
+// fewer distinct A / B panels per resident tile and a higher L2 hit rate (ncu at n = 32768 with 8: 1.45 TB of DRAM reads per
+// launch against 24 GB compulsory, 76 % L2 hits — far from HBM-bound at 740 GB/s, but it is energy).
 __device__ __forceinline__ void tile_coords(int t, int tiles_m, int tiles_n, int& tm, int& tn) {
-    constexpr int kGroup = 8;
+    constexpr int kGroup = 16;
     const int per_group = kGroup * tiles_m;
     const int g = t / per_group;
     const int first_n = g * kGroup;
@@ -308,17 +312,15 @@ int gemm_f64_dmma(int transA, int transB, int64_t m, int64_t n, int64_t k, doubl
                          ((reinterpret_cast<uintptr_t>(B) & 15u) == 0);
     const bool ta = transA != 0, tb = transB != 0;
     cudaError_t e;
-    // ELB200_F64_TILE (A/B measurements only): 644 = Tile<64,64,16> x 4 CTAs / SM (default), 64 = the same x 3 CTAs with one
-    // more stage, 12864 = Tile<128,64,16> x 2 CTAs / SM
-    static const int tile = [] { const char* v = std::getenv("ELB200_F64_TILE"); const int t = v ? std::atoi(v) : 0; return t == 64 || t == 12864 ? t : 644; }();
+    // Tile<64,64,16> with FOUR CTAs per SM. Measured against the alternatives on the same box (profiles/r02_f64_tile_variants_*.log):
+    // three CTAs with one more stage 35.2, Tile<128,64,16> with two CTAs 34.2, the round-1 128 x 128 x 32 one-CTA kernel 32.7,
+    // this one 35.4-35.6 TFLOP/s at n = 16384; the losers were removed.
 #define ELB_DISPATCH_T(BMv, BNv, WMG, WNG, MINB, V)                                                   \
     if (!ta && !tb) e = launch_tile_auto<BMv, BNv, WMG, WNG, MINB, false, false, V>(p, stream);       \
     else if (!ta && tb) e = launch_tile_auto<BMv, BNv, WMG, WNG, MINB, false, true, V>(p, stream);    \
     else if (ta && !tb) e = launch_tile_auto<BMv, BNv, WMG, WNG, MINB, true, false, V>(p, stream);    \
     else e = launch_tile_auto<BMv, BNv, WMG, WNG, MINB, true, true, V>(p, stream);
-    if (tile == 644) { if (aligned) { ELB_DISPATCH_T(64, 64, 2, 2, 4, 2) } else { ELB_DISPATCH_T(64, 64, 2, 2, 4, 1) } }
-    else if (tile == 64) { if (aligned) { ELB_DISPATCH_T(64, 64, 2, 2, 3, 2) } else { ELB_DISPATCH_T(64, 64, 2, 2, 3, 1) } }
-    else { if (aligned) { ELB_DISPATCH_T(128, 64, 4, 2, 2, 2) } else { ELB_DISPATCH_T(128, 64, 4, 2, 2, 1) } }
+    if (aligned) { ELB_DISPATCH_T(64, 64, 2, 2, 4, 2) } else { ELB_DISPATCH_T(64, 64, 2, 2, 4, 1) }
 #undef ELB_DISPATCH_T
     return e == cudaSuccess ? ELB200_OK : ELB200_ERR_CUDA;
 }

@@ -80,6 +80,8 @@ PeerArena* PeerArena::Create(ncclComm_t world, int rank, int size, cudaStream_t 
     ok = ok && cudaMalloc(&arena, size_t(kChannels) * kSlots * slot_bytes) == cudaSuccess;
     ok = ok && cudaMalloc(&flags, kFlagWords * sizeof(uint32_t)) == cudaSuccess;
     ok = ok && cudaMalloc(&pa->consts_, (kSeqMask + 1) * sizeof(uint32_t)) == cudaSuccess;
+    ok = ok && cudaMalloc(&pa->counters_, size_t(kChannels) * kSlots * 2 * sizeof(unsigned int)) == cudaSuccess;
+    ok = ok && cudaMemset(pa->counters_, 0, size_t(kChannels) * kSlots * 2 * sizeof(unsigned int)) == cudaSuccess;
     if (ok) {
         std::vector<uint32_t> iota(kSeqMask + 1);
         for (uint32_t i = 0; i <= kSeqMask; ++i) iota[i] = i;
@@ -130,9 +132,8 @@ PeerArena* PeerArena::Create(ncclComm_t world, int rank, int size, cudaStream_t 
         delete pa;
         return nullptr;
     }
-    // auxiliary lanes for concurrent peer transfers (ELB200_FANOUT=0 keeps everything on one stream)
-    const char* fo = std::getenv("ELB200_FANOUT");
-    pa->lanes_ = (fo && std::atoi(fo) == 0) || size < 3 ? 0 : kLanes;
+    // auxiliary lanes for concurrent peer transfers (two ranks have one peer: nothing to fan out)
+    pa->lanes_ = size < 3 ? 0 : kLanes;
     for (int i = 0; i < pa->lanes_; ++i) {
         cuda_check(cudaStreamCreateWithFlags(&pa->lane_[i], cudaStreamNonBlocking), "PeerArena lane");
         cuda_check(cudaEventCreateWithFlags(&pa->lane_done_[i], cudaEventDisableTiming), "PeerArena lane event");
@@ -200,6 +201,7 @@ PeerArena::~PeerArena() {
     if (!arena_.empty() && arena_[rank_]) cudaFree(arena_[rank_]);
     if (!flags_.empty() && flags_[rank_]) cudaFree(flags_[rank_]);
     if (consts_) cudaFree(consts_);
+    if (counters_) cudaFree(counters_);
     cudaGetLastError();
 }
 
@@ -335,6 +337,36 @@ void PeerArena::Signal(const Ticket& t, const std::vector<int>& members, int my_
         if (i != my_index) write_flag(flag(members[i], ARRIVE, t.channel, t.slot, rank_), t.seq, s);
     for (int i = 0; i < g; ++i)
         if (i != my_index) wait_flag(flag(rank_, ARRIVE, t.channel, t.slot, members[i]), t.seq, s);
+}
+
+elb200_peer_gather PeerArena::FusedBegin(int channel, const std::vector<int>& members, int my_index, int64_t portion_elems, size_t bytes) {
+    const int g = int(members.size());
+    if (bytes > slot_bytes_ || g > ELB200_MAX_SEGMENTS || g < 2)
+        throw EngineError(ELB200_ERR_ARG, "PeerArena::FusedBegin: message larger than an arena slot");
+    const uint64_t n = uses_[channel]++;
+    const int slot = int(n & 1);
+    const uint32_t seq = uint32_t(n / 2 + 1);
+    elb200_peer_gather pg;
+    std::memset(&pg, 0, sizeof(pg));
+    pg.nmembers = g; pg.my_index = my_index; pg.portion = portion_elems;
+    pg.seq = seq & kSeqMask; pg.seq_prev = (seq - 1) & kSeqMask;
+    pg.counters = counters_ + (size_t(channel) * kSlots + slot) * 2;
+    for (int i = 0; i < g; ++i) {
+        pg.slots[i] = slot_base(members[i], channel, slot);
+        pg.arrive_out[i] = flag(members[i], ARRIVE, channel, slot, rank_);
+        pg.arrive_in[i] = flag(rank_, ARRIVE, channel, slot, members[i]);  // i == my_index: my own flag word, nobody else's
+        pg.ack_in[i] = flag(rank_, ACK, channel, slot, members[i]);
+        pg.ack_out[i] = flag(members[i], ACK, channel, slot, rank_);
+    }
+    return pg;
+}
+
+void PeerArena::FusedAllGather(int channel, const std::vector<int>& members, int my_index, int elem_bytes, const void* send,
+                               int64_t send_elems, int64_t portion_elems, int nseg, const elb200_segment* recvs, void* M, int64_t ldm,
+                               cudaStream_t s) {
+    if (send_elems > portion_elems) throw EngineError(ELB200_ERR_ARG, "PeerArena::FusedAllGather: block larger than its portion");
+    const elb200_peer_gather pg = FusedBegin(channel, members, my_index, portion_elems, size_t(portion_elems) * size_t(elem_bytes) * members.size());
+    throw_status(elb200_peer_allgather(&pg, elem_bytes, send, send_elems, nseg, recvs, M, ldm, s), "elb200_peer_allgather");
 }
 
 void PeerArena::Release(const Ticket& t, const std::vector<int>& members, int my_index, cudaStream_t s) {

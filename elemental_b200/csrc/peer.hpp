@@ -18,6 +18,8 @@
 #include <cstdint>
 #include <vector>
 
+#include "../../include/elb200.h"
+
 namespace elb {
 
 class PeerArena {
@@ -57,6 +59,15 @@ public:
     Ticket AllGatherRotate(int channel, const std::vector<int>& members, int my_index, const void* send, size_t send_bytes,
                            size_t portion_bytes, cudaStream_t s);
     void AllGatherEnd(cudaStream_t s) { join(s); }
+    // Small messages: a whole collective in ONE kernel (peer_kernels.cu: elb200_peer_allgather / _exchange / _reduce_scatter) —
+    // peer stores or loads, flags and the pack / unpack lattices instead of 20-40 stream operations. FusedBegin takes the
+    // channel's next slot and sequence number, exactly like AllGather / Publish, and returns the descriptor those kernels
+    // want; the kernel itself waits for the previous acks and acknowledges at its end (no Release). `bytes` = what the
+    // operation keeps in one slot (checked against the slot size).
+    elb200_peer_gather FusedBegin(int channel, const std::vector<int>& members, int my_index, int64_t portion_elems, size_t bytes);
+    // the gather through it (recvs: UNPACK segments relative to the slot base)
+    void FusedAllGather(int channel, const std::vector<int>& members, int my_index, int elem_bytes, const void* send, int64_t send_elems,
+                        int64_t portion_elems, int nseg, const elb200_segment* recvs, void* M, int64_t ldm, cudaStream_t s);
     // Call after the last read of ticket.data has been enqueued on `s`.
     void Release(const Ticket& t, const std::vector<int>& members, int my_index, cudaStream_t s);
 
@@ -109,6 +120,7 @@ private:
     std::vector<char*> arena_;       // per rank: base of its arena as mapped in THIS process
     std::vector<uint32_t*> flags_;   // per rank: base of its flag block
     uint32_t* consts_ = nullptr;     // consts_[i] == i, source of the 4-byte flag writes
+    unsigned int* counters_ = nullptr;  // 2 words per (channel, slot) for the fused kernels, zero between launches
     uint64_t uses_[kChannels] = {0, 0, 0};
     enum { kLanes = 4 };
     int lanes_ = 0;  // 0: no fan-out, everything on the caller's stream

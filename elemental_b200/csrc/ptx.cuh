@@ -35,12 +35,15 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
-// Arrive on the barrier at the same smem offset in CTA `cta` of this cluster.
+// Arrive on the barrier at the same smem offset in CTA `cta` of this cluster. Default semantics (release at CTA scope):
+// the `.release.cluster` form compiles to MEMBAR.ALL.GPU + ERRBAR in front of every arrive — about 1800 cycles each when
+// measured per stage in the half GEMM — and buys nothing here: what the waiter consumes afterwards is either TMEM
+// (ordered by tcgen05.fence / wait::ld) or shared memory already published with fence.proxy.async before the arrive.
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t cta) {
     asm volatile(
         "{\n\t.reg .b32 ra;\n\t"
         "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
-        "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}"
+        "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t}"
         ::"r"(bar), "r"(cta)
         : "memory");
 }
@@ -89,6 +92,32 @@ __device__ __forceinline__ void tma_load_2d(const CUtensorMap* d, uint32_t bar, 
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
         " [%0], [%1, {%3, %4}], [%2];"
         ::"r"(dst), "l"(reinterpret_cast<uint64_t>(d)), "r"(bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+
+// The cta_group::2 forms: the completion is signalled on the barrier at the same offset in the LEADER of the CTA pair
+// the data lands in (the even rank of the pair), which is where the pair's one UMMA issuer waits — no relay hop.
+// `leader` = this CTA's own pair leader (cluster rank & ~1); only its pair bit matters to the hardware.
+__device__ __forceinline__ void tma_load_2d_pair(const CUtensorMap* d, uint32_t bar, uint32_t dst,
+                                                 int32_t c0, int32_t c1, uint32_t leader) {
+    asm volatile(
+        "{\n\t.reg .b32 rb;\n\t"
+        "mapa.shared::cluster.u32 rb, %2, %5;\n\t"
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4}], [rb];\n\t}"
+        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(d)), "r"(bar), "r"(c0), "r"(c1), "r"(leader)
+        : "memory");
+}
+// ... and multicast: ONE L2 read, the box lands at the same offset in every CTA of `mask` (cluster ranks), each
+// destination's pair leader gets the bytes that landed in that destination.
+__device__ __forceinline__ void tma_load_2d_pair_mc(const CUtensorMap* d, uint32_t bar, uint32_t dst,
+                                                    int32_t c0, int32_t c1, uint32_t leader, uint16_t mask) {
+    asm volatile(
+        "{\n\t.reg .b32 rb;\n\t"
+        "mapa.shared::cluster.u32 rb, %2, %5;\n\t"
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
+        " [%0], [%1, {%3, %4}], [rb], %6;\n\t}"
+        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(d)), "r"(bar), "r"(c0), "r"(c1), "r"(leader), "h"(mask)
         : "memory");
 }
 
@@ -164,9 +193,9 @@ __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint6
 }
 
 // All previously issued UMMAs of this thread arrive on `bar` when complete.
-// CG==2: multicast the arrival to the same barrier offset in both CTAs of the pair.
+// CG==2: multicast the arrival to the same barrier offset in the CTAs of `mask` (cluster ranks; default: a 2-CTA cluster's pair).
 template <int CG>
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
+__device__ __forceinline__ void umma_commit(uint32_t bar, uint16_t mask = 3) {
     if constexpr (CG == 1) {
         asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
                      ::"r"(bar) : "memory");
@@ -174,7 +203,7 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
         asm volatile(
             "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64"
             " [%0], %1;"
-            ::"r"(bar), "h"(static_cast<uint16_t>(3))
+            ::"r"(bar), "h"(mask)
             : "memory");
     }
 }

@@ -219,6 +219,47 @@ int elb200_peer_reduce_axpy_f64(int nsrc, const double* const* srcs, int64_t src
                                 void* stream);
 
 
+/* Fused small-message collectives over NVLink peer memory: ONE kernel per rank does the whole collective — waits for the
+ * members' acks of the slot's previous use, moves the data with peer stores / loads, raises an arrival flag, waits for the
+ * other members' flags, puts the result into the destination matrix and acknowledges — where the copy-engine forms take
+ * 20-40 stream operations (57-122 us at 1 MiB on 2 x 4 B200s). The descriptor is filled by the engine's PeerArena (slots and
+ * flags are device addresses mapped in this process, some of them peer memory); `counters` are two zeroed words of local
+ * device memory that the kernels leave zeroed. Collective: every member launches the same operation with the same seq.
+ *   elb200_peer_allgather       PUSH: my packed block into every member's slot, then UNPACK my slot into M through `segs`.
+ *                               Replaces pack + mpi::AllGather + unpack of copy::RowAllGather / ColAllGather
+ *                               (include/El/blas_like/level1/Copy/RowAllGather.hpp:53-75; src/core/imports/mpi/AllGather.hpp:8-21).
+ *   elb200_peer_exchange        PULL: PACK `sends` (offsets from MY slot base) out of A, then UNPACK `recvs` into B, recvs[q]
+ *                               read from the slot of member recv_member[q] at recvs[q].buf_offset (where that member packed
+ *                               its message for me). Replaces pack + mpi::AllToAll / SendRecv + unpack of
+ *                               copy::ColAllToAllDemote / Promote / Exchange (Copy/ColAllToAllDemote.hpp:17-80, Copy/Exchange.hpp;
+ *                               src/core/imports/mpi/AllToAll.hpp, SendRecv.hpp).
+ *   elb200_peer_reduce_scatter  PULL: PACK `packs` (member i's portion at i * portion) out of A, then B-lattice(unpack) +=
+ *                               alpha * (sum over the members' slots, in member order, of the portion at my_index * portion).
+ *                               Same arithmetic and order as elb200_peer_reduce_axpy. Replaces zero-fill + pack +
+ *                               mpi::ReduceScatter + InterleaveMatrixUpdate of AxpyContract (level1/AxpyContract.hpp:318-337;
+ *                               src/core/imports/mpi/ReduceScatter.hpp:36-52).
+ * The first two only move data: elem_bytes is 2, 4 or 8. */
+typedef struct elb200_peer_gather {
+    int nmembers, my_index;
+    int64_t portion;                         /* elements per member block inside a slot (allgather, reduce_scatter) */
+    void* slots[ELB200_MAX_SEGMENTS];        /* slots[i]: base of the slot in member i's arena (slots[my_index]: mine) */
+    uint32_t* arrive_out[ELB200_MAX_SEGMENTS]; /* in member i's flag block: "the data of <me> is in place"                   */
+    uint32_t* arrive_in[ELB200_MAX_SEGMENTS];  /* local: "member i's data is in place"; [my_index]: my own CTAs' stores are  */
+    uint32_t* ack_in[ELB200_MAX_SEGMENTS];     /* local: "member i has finished reading the previous contents"               */
+    uint32_t* ack_out[ELB200_MAX_SEGMENTS];    /* in member i's flag block: "<me> has finished reading"                      */
+    uint32_t seq, seq_prev;
+    unsigned int* counters;
+} elb200_peer_gather;
+int elb200_peer_allgather(const elb200_peer_gather* pg, int elem_bytes, const void* send, int64_t send_elems, int nseg,
+                          const elb200_segment* segs, void* M, int64_t ldm, void* stream);
+int elb200_peer_exchange(const elb200_peer_gather* pg, int elem_bytes, int nsend, const elb200_segment* sends, const void* A,
+                         int64_t lda, int nrecv, const elb200_segment* recvs, const int* recv_member, void* B, int64_t ldb,
+                         void* stream);
+int elb200_peer_reduce_scatter_f32(const elb200_peer_gather* pg, int npack, const elb200_segment* packs, const float* A, int64_t lda,
+                                   const elb200_segment* unpack, float* B, int64_t ldb, float alpha, void* stream);
+int elb200_peer_reduce_scatter_f64(const elb200_peer_gather* pg, int npack, const elb200_segment* packs, const double* A, int64_t lda,
+                                   const elb200_segment* unpack, double* B, int64_t ldb, double alpha, void* stream);
+
 /* Trapezoid-masked entrywise ops on the LOCAL part of an element-cyclic matrix. Local entry (i,j) of
  * the rows x cols column-major block Y is global entry (row0 + i*row_step, col0 + j*col_step); with
  * uplo = ELB200_LOWER the trapezoid is { gi >= gj - offset }, with ELB200_UPPER { gi <= gj - offset }
@@ -353,7 +394,7 @@ int elb200_grid_sync(elb200_grid_t g);     /* cudaStreamSynchronize on it */
  * include/El/core/imports/mpi/aluminum_comm.hpp:93-236); there is no MPI here — it is an NCCL communicator,
  * and when it is a Grid's MC / MR / VC communicator the collectives travel through the grid's NVLink peer
  * arena (copy engines + stream memory operations, no SM) whenever the message fits a slot,
- * with NCCL as the fallback (ELB200_COLL_ARENA=0 forces NCCL). Equal counts on every rank, counts in
+ * with NCCL as the fallback (ELB200_P2P=0 forces NCCL). Equal counts on every rank, counts in
  * ELEMENTS of `dtype` (int64: the reference's `int` counts, src/core/imports/mpi/AllGather.hpp:11-12, cap a
  * call at 2^31 elements), device pointers, asynchronous on the caller's stream, every rank of the
  * communicator calls in the same order (SURVEY.md 8(b) "Threading").

@@ -6,6 +6,8 @@
 #include <atomic>
 #include <cstdio>
 #include <cstring>
+#include <chrono>
+#include <thread>
 #include <vector>
 
 #include "../../include/elb200.h"
@@ -17,9 +19,6 @@ namespace elb {
 thread_local char g_last_error[512] = "";
 std::atomic<unsigned long long> g_launches{0};
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
-thread_local int g_lattice_cta_limit = 0;
-int lattice_cta_limit() { return g_lattice_cta_limit; }
-void set_lattice_cta_limit(int ctas) { g_lattice_cta_limit = ctas > 0 ? ctas : 0; }
 void set_last_error(const char* what, const char* detail) {
     std::snprintf(g_last_error, sizeof(g_last_error), "%s: %s", what, detail ? detail : "");
 }
@@ -436,6 +435,139 @@ int elb200_peer_reduce_axpy_f16(int nsrc, const void* const* srcs, int64_t off, 
             }
     });
     return ELB200_OK;
+}
+// the fused one-kernel collectives of peer_kernels.cu as host routines on the caller's stream: same protocol, same flags
+// (device memory is host memory here)
+namespace {
+void fused_spin(const uint32_t* f, uint32_t want, const char* what) {
+    const auto t0 = std::chrono::steady_clock::now();
+    while (__atomic_load_n(f, __ATOMIC_ACQUIRE) != want) {
+        if (std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() > sim::wait_timeout_seconds())
+            sim::fail("fused peer collective: %s flag never reached %u (deadlock?)", what, want);
+        std::this_thread::yield();
+    }
+}
+void fused_wait_acks(const elb200_peer_gather& pg) {
+    for (int i = 0; i < pg.nmembers; ++i)
+        if (i != pg.my_index) fused_spin(pg.ack_in[i], pg.seq_prev, "ack");
+}
+void fused_publish_and_wait(const elb200_peer_gather& pg) {
+    for (int i = 0; i < pg.nmembers; ++i)
+        __atomic_store_n(i == pg.my_index ? pg.arrive_in[i] : pg.arrive_out[i], pg.seq, __ATOMIC_RELEASE);
+    for (int i = 0; i < pg.nmembers; ++i) fused_spin(pg.arrive_in[i], pg.seq, "arrive");
+}
+void fused_acknowledge(const elb200_peer_gather& pg) {
+    for (int i = 0; i < pg.nmembers; ++i)
+        if (i != pg.my_index) __atomic_store_n(pg.ack_out[i], pg.seq, __ATOMIC_RELEASE);
+}
+// modelled time: one launch, the payload over NVLink, two flag round trips
+void fused_vt(double bytes) { sim::vt_op(sim::RES_HBM, sim::kLaunch + bytes / sim::kRateNvlink + 2.0 * sim::kFlagLatency); }
+bool fused_args_ok(const elb200_peer_gather* pg, int elem_bytes) {
+    return pg && pg->nmembers >= 2 && pg->nmembers <= ELB200_MAX_SEGMENTS && pg->my_index >= 0 && pg->my_index < pg->nmembers && pg->counters &&
+           (elem_bytes == 2 || elem_bytes == 4 || elem_bytes == 8);
+}
+}  // namespace
+int elb200_peer_allgather(const elb200_peer_gather* pgp, int elem_bytes, const void* send, int64_t send_elems, int nseg,
+                          const elb200_segment* segs, void* M, int64_t ldm, void* s) {
+    if (!fused_args_ok(pgp, elem_bytes) || send_elems > pgp->portion) return ELB200_ERR_ARG;
+    const elb200_peer_gather pg = *pgp;
+    std::vector<elb200_segment> sg(segs, segs + nseg);
+    sim::enqueue(static_cast<cudaStream_t>(s), [=] {
+        const size_t eb = size_t(elem_bytes);
+        fused_vt(double(send_elems) * double(eb) * pg.nmembers);
+        fused_wait_acks(pg);
+        for (int i = 0; i < pg.nmembers; ++i) {
+            char* dst = static_cast<char*>(pg.slots[i]) + size_t(pg.my_index) * size_t(pg.portion) * eb;
+            if (send_elems) { sim::check_device_range(dst, size_t(send_elems) * eb, "fused gather slot"); std::memcpy(dst, send, size_t(send_elems) * eb); }
+        }
+        fused_publish_and_wait(pg);
+        const char* buf = static_cast<const char*>(pg.slots[pg.my_index]);
+        for (const elb200_segment& g : sg)
+            for (int64_t j = 0; j < g.cols; ++j)
+                for (int64_t i = 0; i < g.rows; ++i)
+                    std::memcpy(static_cast<char*>(M) + size_t(g.row0 + i * g.row_step + (g.col0 + j * g.col_step) * ldm) * eb,
+                                buf + size_t(g.buf_offset + i + j * g.rows) * eb, eb);
+        fused_acknowledge(pg);
+    });
+    return ELB200_OK;
+}
+int elb200_peer_exchange(const elb200_peer_gather* pgp, int elem_bytes, int nsend, const elb200_segment* sends, const void* A, int64_t lda,
+                         int nrecv, const elb200_segment* recvs, const int* recv_member, void* B, int64_t ldb, void* s) {
+    if (!fused_args_ok(pgp, elem_bytes) || nsend < 0 || nrecv < 0 || nsend > ELB200_MAX_SEGMENTS || nrecv > ELB200_MAX_SEGMENTS) return ELB200_ERR_ARG;
+    const elb200_peer_gather pg = *pgp;
+    std::vector<elb200_segment> snd(sends, sends + nsend), rcv(recvs, recvs + nrecv);
+    std::vector<int> from(recv_member, recv_member + nrecv);
+    for (int m : from)
+        if (m < 0 || m >= pg.nmembers) return ELB200_ERR_ARG;
+    sim::enqueue(static_cast<cudaStream_t>(s), [=] {
+        const size_t eb = size_t(elem_bytes);
+        double bytes = 0;
+        for (const elb200_segment& g : rcv) bytes += double(g.rows) * double(g.cols) * double(eb);
+        fused_vt(bytes);
+        fused_wait_acks(pg);
+        char* mine = static_cast<char*>(pg.slots[pg.my_index]);
+        for (const elb200_segment& g : snd) {
+            if (g.rows > 0 && g.cols > 0) sim::check_device_range(mine + size_t(g.buf_offset) * eb, size_t(g.rows * g.cols) * eb, "fused exchange slot");
+            for (int64_t j = 0; j < g.cols; ++j)
+                for (int64_t i = 0; i < g.rows; ++i)
+                    std::memcpy(mine + size_t(g.buf_offset + i + j * g.rows) * eb,
+                                static_cast<const char*>(A) + size_t(g.row0 + i * g.row_step + (g.col0 + j * g.col_step) * lda) * eb, eb);
+        }
+        fused_publish_and_wait(pg);
+        for (size_t q = 0; q < rcv.size(); ++q) {
+            const elb200_segment& g = rcv[q];
+            const char* src = static_cast<const char*>(pg.slots[from[q]]);
+            if (g.rows > 0 && g.cols > 0) sim::check_device_range(src + size_t(g.buf_offset) * eb, size_t(g.rows * g.cols) * eb, "fused exchange peer slot");
+            for (int64_t j = 0; j < g.cols; ++j)
+                for (int64_t i = 0; i < g.rows; ++i)
+                    std::memcpy(static_cast<char*>(B) + size_t(g.row0 + i * g.row_step + (g.col0 + j * g.col_step) * ldb) * eb,
+                                src + size_t(g.buf_offset + i + j * g.rows) * eb, eb);
+        }
+        fused_acknowledge(pg);
+    });
+    return ELB200_OK;
+}
+extern "C++" {
+namespace {
+template <typename T>
+int fused_reduce_scatter(const elb200_peer_gather* pgp, int npack, const elb200_segment* packs, const T* A, int64_t lda, const elb200_segment* unpack,
+                         T* B, int64_t ldb, T alpha, void* s) {
+    if (!fused_args_ok(pgp, int(sizeof(T))) || npack < 0 || npack > ELB200_MAX_SEGMENTS || !unpack || unpack->rows * unpack->cols > pgp->portion)
+        return ELB200_ERR_ARG;
+    const elb200_peer_gather pg = *pgp;
+    std::vector<elb200_segment> pk(packs, packs + npack);
+    const elb200_segment un = *unpack;
+    sim::enqueue(static_cast<cudaStream_t>(s), [=] {
+        fused_vt(double(un.rows) * double(un.cols) * sizeof(T) * pg.nmembers);
+        fused_wait_acks(pg);
+        T* mine = static_cast<T*>(pg.slots[pg.my_index]);
+        for (const elb200_segment& g : pk) {
+            if (g.rows > 0 && g.cols > 0) sim::check_device_range(mine + g.buf_offset, size_t(g.rows * g.cols) * sizeof(T), "fused reduce slot");
+            for (int64_t j = 0; j < g.cols; ++j)
+                for (int64_t i = 0; i < g.rows; ++i) mine[g.buf_offset + i + j * g.rows] = A[g.row0 + i * g.row_step + (g.col0 + j * g.col_step) * lda];
+        }
+        fused_publish_and_wait(pg);
+        const int64_t off = int64_t(pg.my_index) * pg.portion;
+        for (int64_t j = 0; j < un.cols; ++j)
+            for (int64_t i = 0; i < un.rows; ++i) {
+                T sum = T(0);
+                for (int q = 0; q < pg.nmembers; ++q) sum += static_cast<const T*>(pg.slots[q])[off + i + j * un.rows];
+                T* mp = B + un.row0 + i * un.row_step + (un.col0 + j * un.col_step) * ldb;
+                *mp += alpha * sum;
+            }
+        fused_acknowledge(pg);
+    });
+    return ELB200_OK;
+}
+}  // namespace
+}  // extern "C++"
+int elb200_peer_reduce_scatter_f32(const elb200_peer_gather* pg, int npack, const elb200_segment* packs, const float* A, int64_t lda,
+                                   const elb200_segment* unpack, float* B, int64_t ldb, float alpha, void* s) {
+    return fused_reduce_scatter<float>(pg, npack, packs, A, lda, unpack, B, ldb, alpha, s);
+}
+int elb200_peer_reduce_scatter_f64(const elb200_peer_gather* pg, int npack, const elb200_segment* packs, const double* A, int64_t lda,
+                                   const elb200_segment* unpack, double* B, int64_t ldb, double alpha, void* s) {
+    return fused_reduce_scatter<double>(pg, npack, packs, A, lda, unpack, B, ldb, alpha, s);
 }
 int elb200_gemm_f64(int ta, int tb, int64_t m, int64_t n, int64_t k, double al, const double* A, int64_t lda, const double* B,
                     int64_t ldb, double be, double* C, int64_t ldc, void* s) {

@@ -29,8 +29,7 @@ def simlib():
 
 def _run(grid, *args, env=None, timeout=900):
     # ELB200_HOST_KRANGE=16: the host-operand Gemm streams A in several k ranges at the small k of the cases
-    # ELB200_AB_PIPELINE=1: the opt-in SUMMA-A / SUMMA-B panel pipeline is exercised here
-    e = dict(os.environ, HOSTSIM_TIMEOUT="90", ELB200_ARENA_MB="8", OMP_NUM_THREADS="1", ELB200_HOST_KRANGE="16", ELB200_AB_PIPELINE="1")
+    e = dict(os.environ, HOSTSIM_TIMEOUT="90", ELB200_ARENA_MB="8", OMP_NUM_THREADS="1", ELB200_HOST_KRANGE="16")
     e.update(env or {})
     r = subprocess.run([sys.executable, WORKER, grid, *args], capture_output=True, text=True, timeout=timeout, cwd=ROOT, env=e)
     assert r.returncode == 0 and "HOSTSIM_PASS" in r.stdout, (r.stdout[-3000:] + r.stderr[-6000:])
@@ -55,10 +54,13 @@ def test_engine_2x2_peer_arena_all_cases(simlib):
 def test_engine_2x4_bench_grid(simlib):
     """The 8-GPU grid shape of BASELINE C3 (2 x 4): redistributions, contractions, all Gemm variants, the
     level-3 family, and the reference's own per-rank outputs."""
-    # ELB200_AG_SPLIT_BYTES=1: every arena AllGather takes the split form (own block straight from the source,
-    # each peer's block unpacked on ITS arrival); the other runs use the one-wait form at these sizes
+    # ELB200_FUSED_BYTES=0: the copy-engine forms (pull exchange, receiver-side reduce) instead of the fused one-kernel
+    # collectives every other run takes at these sizes; ELB200_AG_SPLIT_BYTES=1: every arena AllGather in the split form
+    # (own block straight from the source, each peer's block unpacked on ITS arrival)
     out = _run("2x4", "--only", "check_redistributions,check_contractions,check_gemm_variants_f64,check_gemm_proxies_f32,run_level3,check_fuzz",
-               env={"ELB200_AG_SPLIT_BYTES": "1"})
+               env={"ELB200_AG_SPLIT_BYTES": "1", "ELB200_FUSED_BYTES": "0"})
+    # ... and the one-wait copy-engine AllGather alternating with fused exchanges / reductions on the same channels
+    _run("2x4", "--only", "check_redistributions,check_contractions,check_collectives", env={"ELB200_FUSED_BYTES": "2048"})
     assert "'level3_ref_golden': 60" in out and "'dist_ref_golden': 164" in out
 
 
@@ -70,7 +72,8 @@ def test_engine_3x2_nccl_fallback(simlib):
 
 
 @pytest.mark.parametrize("grid,env,extra", [("1x2,2x1", {}, ",run_level3"),
-                                             ("2x3", {"ELB200_P2P": "0"}, ",run_level3"), ("2x2", {"ELB200_DIRECT": "0", "ELB200_AG_SPLIT_BYTES": "1"}, "")])
+                                             ("2x3", {"ELB200_P2P": "0"}, ",run_level3"), ("2x2", {"ELB200_DIRECT": "0", "ELB200_AG_SPLIT_BYTES": "1"}, ""),
+                                             ("2x2", {"ELB200_AB_PIPELINE": "0"}, "")])
 def test_engine_multi_panel_pipeline(simlib, grid, env, extra):
     """Narrow panels (ELB200_PANEL_K=512, k = 1300): several panels per Gemm through the two-slot
     gather | GEMM pipeline, zero-copy direct panels, staged panels (2 x 2 and 2 x 4
@@ -159,7 +162,7 @@ def test_cxx_facade_on_hostsim(simlib):
                         "-Wl,-rpath," + out_dir, "-pthread"], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr[-3000:]
     for shape, extra in ((("2", "2"), {}), (("2", "3"), {}), (("1", "2"), {}), (("2", "1"), {}),
-                         (("2", "2"), {"ELB200_COLL_ARENA": "0"}),          # the per-collective exports over NCCL only
+                         (("2", "2"), {"ELB200_P2P": "0"}),          # the per-collective exports over NCCL only
                          (("2", "3"), {"ELB200_ARENA_KB": "4"})):            # messages that do not fit a slot fall back
         r = subprocess.run([exe, *shape], capture_output=True, text=True, timeout=300,
                            env=dict(os.environ, **{"ELB200_ARENA_MB": "8", "HOSTSIM_TIMEOUT": "90", **extra}))

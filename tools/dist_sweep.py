@@ -127,10 +127,33 @@ def run_c5(el, grid, world, rank, local, k, rows):
     grid.sync()
 
 
+def run_c6(el, grid, world, rank, local, rows):
+    """Stationary-A / stationary-B SUMMA on shapes with several panels (not a BASELINE config; the A/B shape for the
+    SUMMA-A / B panel pipeline, ELB200_AB_PIPELINE): fp32, m = k = 32768, n = 16384 for A; m = 16384, n = k = 32768 for B."""
+    r, c = grid.Height(), grid.Width()
+    tdt = torch.float32
+    for alg, label, (m, n, k) in ((el.GEMM_SUMMA_A, "GEMM_SUMMA_A", (32768, 16384, 32768)), (el.GEMM_SUMMA_B, "GEMM_SUMMA_B", (16384, 32768, 32768))):
+        A = el.DistMatrix(grid, el.MC, el.MR, tdt).Resize(m, k)
+        B = el.DistMatrix(grid, el.MC, el.MR, tdt).Resize(k, n)
+        Cm = el.DistMatrix(grid, el.MC, el.MR, tdt).Resize(m, n)
+        for i, M in enumerate((A, B, Cm)):
+            fill(grid, M, 17 * (i + 1) + rank)
+        t = timed(grid, lambda: el.Gemm(el.NORMAL, el.NORMAL, 0.5, A, B, -0.5, Cm, alg), world, local, warm=1, reps=3)
+        tf = 2.0 * m * n * k / t / 1e9
+        rows.append({"config": "C6", "alg": label, "dtype": "f32", "grid": f"{r}x{c}", "m": m, "n": n, "k": k, "ms": t, "TFLOPs": tf,
+                     "TFLOPs_per_gpu": tf / (r * c), "ab_pipeline": os.environ.get("ELB200_AB_PIPELINE", "default")})
+        if rank == 0:
+            print(f"C6 f32 {r}x{c} m={m} n={n} k={k} {label:14s} {t:9.2f} ms  {tf:8.1f} TFLOP/s  ({tf / (r * c):.1f} per GPU)", flush=True)
+        del A, B, Cm
+        gc.collect()
+        grid.sync()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--c4", action="store_true")
     ap.add_argument("--c5", action="store_true")
+    ap.add_argument("--c6", action="store_true", help="SUMMA-A / SUMMA-B on multi-panel shapes")
     ap.add_argument("--max-bytes", type=int, default=1 << 30, help="largest global matrix of the C4 sweep")
     ap.add_argument("--min-bytes", type=int, default=0, help="smallest global matrix of the C4 sweep")
     ap.add_argument("--k", type=int, default=262144)
@@ -150,6 +173,8 @@ def main():
             run_c4(el, grid, world, rank, local, args.max_bytes, rows, args.min_bytes)
         if args.c5:
             run_c5(el, grid, world, rank, local, args.k, rows)
+        if args.c6:
+            run_c6(el, grid, world, rank, local, rows)
     finally:
         gc.collect()
         torch.cuda.synchronize()

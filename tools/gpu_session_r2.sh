@@ -104,6 +104,95 @@ case $STAGE in
   done
   du -sh $OUT | tee -a $OUT/session.log
   ;;
+1f)
+  # the half GEMM under ncu (it runs at 40 % of cublasGemmEx: where does the stage time go?), fp64 with the wider raster group
+  log "=== f16"; timeout 300 tools/native_bench f16 8192 > $OUT/f16.log 2>&1; log "exit $?"; cat $OUT/f16.log | tee -a $OUT/session.log
+  timeout 600 ncu --set full --import-source on --clock-control none -k regex:gemm_f16 -c 1 -o /tmp/ncu_f16 tools/native_bench f16 8192 > $OUT/ncu_f16.log 2>&1; log "ncu f16 exit $?"
+  ncu -i /tmp/ncu_f16.ncu-rep --page raw --csv > $OUT/ncu_f16_raw.csv 2>/dev/null
+  ncu -i /tmp/ncu_f16.ncu-rep --page details > $OUT/ncu_f16_details.txt 2>/dev/null
+  timeout 600 ncu --set full --clock-control none -k regex:cutlass -c 1 -o /tmp/ncu_f16_cublas tools/native_bench f16 8192 > $OUT/ncu_f16_cublas.log 2>&1; log "ncu f16 cublas exit $?"
+  ncu -i /tmp/ncu_f16_cublas.ncu-rep --page details > $OUT/ncu_f16_cublas_details.txt 2>/dev/null
+  ncu -i /tmp/ncu_f16_cublas.ncu-rep --page raw --csv > $OUT/ncu_f16_cublas_raw.csv 2>/dev/null
+  log "=== f64"; timeout 300 tools/native_bench f64 8192 > $OUT/f64.log 2>&1; timeout 300 tools/gemm_check perf f64 16384 >> $OUT/f64.log 2>&1; grep TFLOP $OUT/f64.log | tee -a $OUT/session.log
+  du -sh $OUT | tee -a $OUT/session.log
+  ;;
+f16dbg)
+  # the half GEMM without the relay warp; where the stage time goes: 1 = no C stores, 2 = no loads, 4 = no UMMAs
+  log "=== test_gpu_half"; timeout 600 python -m pytest tests/test_gpu_half.py -m gpu -x -q > $OUT/pytest_half.log 2>&1; log "exit $?"; tail -2 $OUT/pytest_half.log | tee -a $OUT/session.log
+  for d in 0 1 2 4 3 6; do
+    echo "##### ELB200_F16_DEBUG=$d" >> $OUT/f16.log
+    ELB200_F16_DEBUG=$d timeout 120 tools/native_bench f16 8192 >> $OUT/f16.log 2>&1
+  done
+  cat $OUT/f16.log | tee -a $OUT/session.log
+  ;;
+arrive)
+  # cross-CTA arrives without the GPU-scope membar: fp32 correctness + rate, half with 6 / 7 stages
+  log "=== gemm_check correctness"; timeout 600 tools/gemm_check correctness > $OUT/correctness.log 2>&1; log "exit $?"; tail -2 $OUT/correctness.log | tee -a $OUT/session.log
+  log "=== gemm_check perf f32"; timeout 600 tools/gemm_check perf f32 8192 16384 > $OUT/perf_f32.log 2>&1; log "exit $?"; grep TFLOP $OUT/perf_f32.log | tee -a $OUT/session.log
+  for st in 6 7; do
+    echo "##### ELB200_F16_STAGES=$st" >> $OUT/f16.log
+    ELB200_F16_STAGES=$st timeout 120 tools/native_bench f16 8192 >> $OUT/f16.log 2>&1
+    ELB200_F16_STAGES=$st timeout 120 tools/native_bench f16 16384 >> $OUT/f16.log 2>&1
+  done
+  cat $OUT/f16.log | tee -a $OUT/session.log
+  log "=== pytest gemm + half"; timeout 900 python -m pytest tests/test_gpu_kernels.py tests/test_gpu_half.py -m gpu -x -q > $OUT/pytest.log 2>&1; log "exit $?"; tail -2 $OUT/pytest.log | tee -a $OUT/session.log
+  ;;
+f16mc)
+  # the half GEMM with 4-CTA clusters and the B tile multicast: parity, then on / off
+  log "=== test_gpu_half"; timeout 600 python -m pytest tests/test_gpu_half.py -m gpu -x -q > $OUT/pytest_half.log 2>&1; log "exit $?"; tail -4 $OUT/pytest_half.log | tee -a $OUT/session.log
+  for mc in 1 0; do
+    echo "##### ELB200_F16_MULTICAST=$mc" >> $OUT/f16.log
+    ELB200_F16_MULTICAST=$mc timeout 120 tools/native_bench f16 8192 >> $OUT/f16.log 2>&1
+    ELB200_F16_MULTICAST=$mc timeout 120 tools/native_bench f16 16384 >> $OUT/f16.log 2>&1
+  done
+  cat $OUT/f16.log | tee -a $OUT/session.log
+  ;;
+final8)
+  # the round's last multi-GPU session, most important first; a step is skipped once DEADLINE seconds have passed
+  DEADLINE=${DEADLINE:-300}
+  T0=$(date +%s); el() { echo $(( $(date +%s) - T0 )); }
+  late() { if [ $(el) -gt $DEADLINE ]; then log "=== SKIP $1 (t=$(el)s)"; return 0; fi; log "=== $1 (t=$(el)s)"; return 1; }
+  late "bench.py N=$N" || { timeout 600 $TR bench.py --gpus $N --steps 10 --warmup 3 > $OUT/bench_${N}gpu.json 2> $OUT/bench_${N}gpu.err; log "exit $? (t=$(el)s)"; }
+  late "dist_sweep c4 c5" || { timeout 300 $TR tools/dist_sweep.py --c4 --c5 --out $OUT/dist_sweep_${N}gpu.json > $OUT/dist_sweep.log 2>&1; log "exit $? (t=$(el)s)"; }
+  late "c6 default" || { timeout 200 $TR tools/dist_sweep.py --c6 --out $OUT/c6_${N}gpu.json > $OUT/c6.log 2>&1; log "exit $? (t=$(el)s)"; }
+  late "c6 no AB pipeline" || { ELB200_AB_PIPELINE=0 timeout 200 $TR tools/dist_sweep.py --c6 --out $OUT/c6_${N}gpu_noabpipe.json > $OUT/c6_noabpipe.log 2>&1; log "exit $? (t=$(el)s)"; }
+  late "c4 small, fused collectives off" || { ELB200_FUSED_BYTES=0 timeout 200 $TR tools/dist_sweep.py --c4 --max-bytes 67108864 --out $OUT/dist_sweep_${N}gpu_nofused.json > $OUT/dist_sweep_nofused.log 2>&1; log "exit $? (t=$(el)s)"; }
+  late "c4 4-8 GB" || { ELB200_ARENA_MB=4096 timeout 300 $TR tools/dist_sweep.py --c4 --min-bytes 4294967296 --max-bytes 8589934592 --out $OUT/dist_sweep_${N}gpu_large.json > $OUT/dist_sweep_large.log 2>&1; log "exit $? (t=$(el)s)"; }
+  late "c4 large, gather in one piece" || { ELB200_AG_SPLIT_BYTES=0 timeout 200 $TR tools/dist_sweep.py --c4 --min-bytes 268435456 --out $OUT/dist_sweep_${N}gpu_onepiece.json > $OUT/dist_sweep_onepiece.log 2>&1; log "exit $? (t=$(el)s)"; }
+  late "c4 large over NCCL" || { ELB200_P2P=0 timeout 200 $TR tools/dist_sweep.py --c4 --min-bytes 268435456 --out $OUT/dist_sweep_${N}gpu_nccl.json > $OUT/dist_sweep_nccl.log 2>&1; log "exit $? (t=$(el)s)"; }
+  grep -h "^C[456] f32" $OUT/dist_sweep.log $OUT/c6.log $OUT/c6_noabpipe.log 2>/dev/null | cut -c1-150 | tee -a $OUT/session.log
+  ;;
+final1)
+  # the round's last 1-GPU session: the whole GPU suite with the final library, the bench line, the ncu evidence
+  log "=== pytest -m gpu"; timeout 1500 python -m pytest tests -m gpu -x -q > $OUT/pytest_gpu.log 2>&1; log "exit $?"; tail -3 $OUT/pytest_gpu.log | tee -a $OUT/session.log
+  log "=== bench.py"; timeout 900 python bench.py --steps 10 --warmup 5 > $OUT/bench_1gpu.json 2> $OUT/bench_1gpu.err; log "exit $?"
+  log "=== bench.py reference arm"; timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > $OUT/bench_reference.json 2> $OUT/bench_reference.err; log "exit $?"
+  log "=== launch list"; timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 700 --csv --log-file $OUT/launches_bench.csv \
+      python bench.py --steps 2 --warmup 3 --no-cpu --no-parity --no-sub > $OUT/ncu_launches.log 2>&1; log "exit $?"
+  for dt in f32 f64; do
+    timeout 900 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum,lts__t_sector_hit_rate.pct --clock-control none -k regex:gemm_f -c 3 --csv \
+        --log-file $OUT/ncu_traffic_$dt.csv python bench.py --dtype $dt --steps 1 --warmup 1 --no-cpu --no-e2e --no-parity --no-sub > $OUT/ncu_traffic_$dt.log 2>&1; log "ncu traffic $dt exit $?"
+  done
+  timeout 600 ncu --set full --import-source on --clock-control none -k regex:gemm_f32 -c 1 -o /tmp/ncu_f32 tools/gemm_check perf f32 8192 > $OUT/ncu_f32.log 2>&1; log "ncu f32 exit $?"
+  ncu -i /tmp/ncu_f32.ncu-rep --page raw --csv > $OUT/ncu_f32_raw.csv 2>/dev/null
+  ncu -i /tmp/ncu_f32.ncu-rep --page details > $OUT/ncu_f32_details.txt 2>/dev/null
+  timeout 600 ncu --set full --import-source on --clock-control none -k regex:gemm_f16 -c 1 -o /tmp/ncu_f16 tools/native_bench f16 8192 > $OUT/ncu_f16.log 2>&1; log "ncu f16 exit $?"
+  ncu -i /tmp/ncu_f16.ncu-rep --page raw --csv > $OUT/ncu_f16_raw.csv 2>/dev/null
+  ncu -i /tmp/ncu_f16.ncu-rep --page details > $OUT/ncu_f16_details.txt 2>/dev/null
+  timeout 300 tools/native_bench f16 8192 > $OUT/f16.log 2>&1; timeout 300 tools/native_bench f16 16384 >> $OUT/f16.log 2>&1; cat $OUT/f16.log | tee -a $OUT/session.log
+  du -sh $OUT | tee -a $OUT/session.log
+  ;;
+fused)
+  # fused small-message AllGather: parity, then the C4 sweep with it on / off; SUMMA-A / B panel pipeline A/B (C6)
+  run timeout 900 $TR tests/dist_worker.py
+  if [ "$N" = "2" ]; then run timeout 900 $TR tests/dist_worker.py --height 2; fi
+  log "=== dist_sweep c4 (fused gather on)"; timeout 900 $TR tools/dist_sweep.py --c4 --out $OUT/dist_sweep_${N}gpu.json > $OUT/dist_sweep.log 2>&1; log "exit $?"
+  log "=== dist_sweep c4 small (fused collectives off)"; ELB200_FUSED_BYTES=0 timeout 900 $TR tools/dist_sweep.py --c4 --max-bytes 67108864 --out $OUT/dist_sweep_${N}gpu_nofused.json > $OUT/dist_sweep_nofused.log 2>&1; log "exit $?"
+  log "=== dist_sweep c4 small (fused up to 1 GiB)"; ELB200_FUSED_BYTES=1073741824 timeout 900 $TR tools/dist_sweep.py --c4 --max-bytes 268435456 --out $OUT/dist_sweep_${N}gpu_allfused.json > $OUT/dist_sweep_allfused.log 2>&1; log "exit $?"
+  log "=== c6 default"; timeout 900 $TR tools/dist_sweep.py --c6 --out $OUT/c6_${N}gpu.json > $OUT/c6.log 2>&1; log "exit $?"
+  log "=== c6 no AB pipeline"; ELB200_AB_PIPELINE=0 timeout 900 $TR tools/dist_sweep.py --c6 --out $OUT/c6_${N}gpu_noabpipe.json > $OUT/c6_noabpipe.log 2>&1; log "exit $?"
+  grep -h "C6\|1.0 MiB\|  4.0 MiB\|16.0 MiB\| 64.0 MiB\|256.0 MiB\|1024.0 MiB" $OUT/dist_sweep.log $OUT/dist_sweep_nofused.log $OUT/dist_sweep_allfused.log $OUT/c6.log $OUT/c6_noabpipe.log | tee -a $OUT/session.log
+  ;;
 multi)
   run timeout 900 $TR tests/dist_worker.py
   run timeout 900 $TR tests/dist_worker.py --level3

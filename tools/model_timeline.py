@@ -156,16 +156,14 @@ def main():
 
     rows = [
         ("C2 fp32 n=16384 1x1", "38.7 ms (227.5 TF/s)", ["gemm", "1", "1", "16384", "f32"], None),
-        ("e2e fp32 n=16384 1x1, uniform blocks (as measured)", "67.8 ms (129.8 TF/s)", ["e2e", "1", "1", "16384", "f32"], {"ELB200_HOST_TAPER": "0"}),
-        ("e2e fp32 n=16384 1x1, tapered tail (default)", "not measured yet", ["e2e", "1", "1", "16384", "f32"], None),
-        ("e2e fp32 n=16384 1x1, tapered tail + B in 4 k ranges", "not measured yet", ["e2e", "1", "1", "16384", "f32"], {"ELB200_HOST_BRANGES": "4"}),
+        ("e2e fp32 n=16384 1x1, tapered tail, whole B slices (ELB200_HOST_BRANGES=1)", "64.4 ms (136.5 TF/s)", ["e2e", "1", "1", "16384", "f32"], {"ELB200_HOST_BRANGES": "1"}),
+        ("e2e fp32 n=16384 1x1, tapered tail + B in 4 k ranges (default)", "62.4 ms (140.9 TF/s)", ["e2e", "1", "1", "16384", "f32"], None),
         ("fp32 n=32768 2x4", "40.9 ms (1720.9 TF/s)", ["gemm", "2", "4", "32768", "f32"], None),
         ("C3 fp64 n=32768 2x4", "292 ms (240.7 TF/s)", ["gemm", "2", "4", "32768", "f64"], None),
         ("C4 1 GiB 2x2, gather in one piece (round-1 default)", "0.54 / 0.55 / 0.61 ms", ["c4", "2", "2"], {"ELB200_AG_SPLIT_BYTES": "0"}),
         ("C4 1 GiB 2x2, split gather with rotation (default since round 2)", "0.475 / 0.55 / 0.61 ms", ["c4", "2", "2"], None),
         ("C4 1 GiB 2x4, gather in one piece", "1.28 / 0.36 / 0.82 ms", ["c4", "2", "4"], {"ELB200_AG_SPLIT_BYTES": "0"}),
         ("C4 1 GiB 2x4, split gather with rotation (default)", "see profiles/r02_dist_sweep_8gpu.json", ["c4", "2", "4"], None),
-        ("C5 fp32 k=262144 2x4, no k-range pipeline", "25.2 ms (1395 TF/s)", ["c5", "2", "4"], {"ELB200_DOT_PIPELINE": "0"}),
         ("C5 fp32 k=262144 2x4, k-range pipeline (default)", "21.7 ms (1624 TF/s)", ["c5", "2", "4"], None),
     ]
     w = max(len(r[0]) for r in rows)

@@ -3,7 +3,6 @@
 //   native_bench e2e [n]        El::Gemm fp32 NN with HOST operands (elb200_dist_gemm_host_f32, pinned memory,
 //                               H2D + D2H inside the timed region) on a 1 x 1 grid: the bench's `e2e` leg
 //   native_bench f64 [n]        elb200_gemm_f64 NT: time + max relative difference to cublasDgemm
-//                               (ELB200_F64_TILE=64 | 644 | 12864 selects the tile shape)
 //   native_bench trapcheck      128-bit trapezoid kernel vs the scalar one vs the host definition, bit for bit
 //   native_bench l3 [n]         trapezoid kernel GB/s, elb200_trsm TFLOP/s, Syrk / Gemm through the handle ABI
 #include <cublas_v2.h>
@@ -114,9 +113,8 @@ static int run_f64(int64_t n) {
     }
     for (size_t i = 0; i < hc.size(); ++i) { num += (hc[i] - hr[i]) * (hc[i] - hr[i]); den += hr[i] * hr[i]; }
     const double rel = std::sqrt(num / den), bound = 1e-13 * std::sqrt(double(n));
-    const char* ws = std::getenv("ELB200_F64_TILE");
-    std::printf("f64 kernel (ELB200_F64_TILE=%s) n=%lld NT: rel. Frobenius difference to cublasDgemm %.3e (bound %.1e) %s\n",
-                ws ? ws : "default", (long long)n, rel, bound, rel <= bound ? "ok" : "FAIL");
+    std::printf("f64 kernel n=%lld NT: rel. Frobenius difference to cublasDgemm %.3e (bound %.1e) %s\n",
+                (long long)n, rel, bound, rel <= bound ? "ok" : "FAIL");
     const double flop = 2.0 * double(n) * n * n;
     double ms = time_ms([&] { elb200_gemm_f64(0, 1, n, n, n, al, A, n, B, n, be, C, n, nullptr); }, 1, 3);
     std::printf("f64 elb200_gemm_f64 NT n=%lld: %.3f ms  %.2f TFLOP/s\n", (long long)n, ms, flop / ms * 1e-9);
