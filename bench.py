@@ -518,11 +518,18 @@ def roofline_of(rec: dict, dtype: str, peaks: dict, libpk: dict, n_gpus: int) ->
     k = rec["_kernel"]
     ach = k["achieved"]
     if dtype == "f32":
-        # 3xTF32: three tf32 UMMAs per useful MAC, tf32 rate = bf16 rate / 2  =>  bf16 / 6
-        peak = peaks["bf16_sustained"] / 6.0
-        basis = (f"{peaks['source']}: sustained bf16 {peaks['bf16_sustained']} TF/s / 6 (tf32 = bf16/2, 3 UMMAs per MAC); "
-                 f"burst-derived {peaks['bf16'] / 6.0:.1f}")
-        alt = {"bf16_burst_over_6": peaks["bf16"] / 6.0}
+        # 3xTF32: three tf32 UMMAs per useful MAC, tf32 rate = bf16 rate / 2  =>  bf16 / 6. The kernel runs inside a long
+        # step, so the SUSTAINED bf16 figure is the first choice — but a peak has to bound what it measures: since the
+        # round-2 kernel the achieved rate exceeds sustained / 6 (tf32 MMAs at half the bf16 rate draw less power than the
+        # bf16 GEMM MEASURED_PEAKS.json timed, so the clocks under the cap are higher), and then the burst figure is the
+        # denominator; the other one stays in peak_alt.
+        sus, burst = peaks["bf16_sustained"] / 6.0, peaks["bf16"] / 6.0
+        use_burst = bool(ach) and ach > sus
+        peak = burst if use_burst else sus
+        basis = (f"{peaks['source']}: {'burst' if use_burst else 'sustained'} bf16 {peaks['bf16'] if use_burst else peaks['bf16_sustained']} TF/s / 6 "
+                 f"(tf32 = bf16/2, 3 UMMAs per MAC); {'sustained' if use_burst else 'burst'}-derived {sus if use_burst else burst:.1f}"
+                 + (" is below the achieved rate and cannot be the bound" if use_burst else ""))
+        alt = {"bf16_sustained_over_6" if use_burst else "bf16_burst_over_6": sus if use_burst else burst}
         if libpk.get("cublas_tf32_tflops"):
             alt["cublas_tf32_over_3"] = libpk["cublas_tf32_tflops"] / 3.0
         kernel = "gemm_f32_3xtf32_kernel<cta_group::2>"

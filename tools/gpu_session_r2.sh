@@ -164,23 +164,30 @@ final8)
   ;;
 final1)
   # the round's last 1-GPU session: the whole GPU suite with the final library, the bench line, the ncu evidence
-  log "=== pytest -m gpu"; timeout 1500 python -m pytest tests -m gpu -x -q > $OUT/pytest_gpu.log 2>&1; log "exit $?"; tail -3 $OUT/pytest_gpu.log | tee -a $OUT/session.log
-  log "=== bench.py"; timeout 900 python bench.py --steps 10 --warmup 5 > $OUT/bench_1gpu.json 2> $OUT/bench_1gpu.err; log "exit $?"
-  log "=== bench.py reference arm"; timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > $OUT/bench_reference.json 2> $OUT/bench_reference.err; log "exit $?"
-  log "=== launch list"; timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 700 --csv --log-file $OUT/launches_bench.csv \
-      python bench.py --steps 2 --warmup 3 --no-cpu --no-parity --no-sub > $OUT/ncu_launches.log 2>&1; log "exit $?"
-  for dt in f32 f64; do
-    timeout 900 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum,lts__t_sector_hit_rate.pct --clock-control none -k regex:gemm_f -c 3 --csv \
-        --log-file $OUT/ncu_traffic_$dt.csv python bench.py --dtype $dt --steps 1 --warmup 1 --no-cpu --no-e2e --no-parity --no-sub > $OUT/ncu_traffic_$dt.log 2>&1; log "ncu traffic $dt exit $?"
-  done
-  timeout 600 ncu --set full --import-source on --clock-control none -k regex:gemm_f32 -c 1 -o /tmp/ncu_f32 tools/gemm_check perf f32 8192 > $OUT/ncu_f32.log 2>&1; log "ncu f32 exit $?"
+  log "=== pytest -m gpu"; timeout 900 python -m pytest tests -m gpu -x -q > $OUT/pytest_gpu.log 2>&1; log "exit $?"; tail -3 $OUT/pytest_gpu.log | tee -a $OUT/session.log
+  log "=== bench.py"; timeout 600 python bench.py --steps 10 --warmup 5 > $OUT/bench_1gpu.json 2> $OUT/bench_1gpu.err; log "exit $?"
+  timeout 300 ncu --set full --import-source on --clock-control none -k regex:gemm_f32 -c 1 -o /tmp/ncu_f32 tools/gemm_check perf f32 8192 > $OUT/ncu_f32.log 2>&1; log "ncu f32 exit $?"
   ncu -i /tmp/ncu_f32.ncu-rep --page raw --csv > $OUT/ncu_f32_raw.csv 2>/dev/null
   ncu -i /tmp/ncu_f32.ncu-rep --page details > $OUT/ncu_f32_details.txt 2>/dev/null
-  timeout 600 ncu --set full --import-source on --clock-control none -k regex:gemm_f16 -c 1 -o /tmp/ncu_f16 tools/native_bench f16 8192 > $OUT/ncu_f16.log 2>&1; log "ncu f16 exit $?"
+  timeout 300 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum,lts__t_sector_hit_rate.pct --clock-control none -k regex:gemm_f -c 3 --csv \
+      --log-file $OUT/ncu_traffic_f32.csv python bench.py --dtype f32 --steps 1 --warmup 1 --no-cpu --no-e2e --no-parity --no-sub > $OUT/ncu_traffic_f32.log 2>&1; log "ncu traffic f32 exit $?"
+  log "=== launch list"; timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 700 --csv --log-file $OUT/launches_bench.csv \
+      python bench.py --steps 2 --warmup 3 --no-cpu --no-parity --no-sub > $OUT/ncu_launches.log 2>&1; log "exit $?"
+  timeout 120 tools/native_bench f16 8192 > $OUT/f16.log 2>&1; timeout 120 tools/native_bench f16 16384 >> $OUT/f16.log 2>&1; cat $OUT/f16.log | tee -a $OUT/session.log
+  timeout 200 ncu --set full --import-source on --clock-control none -k regex:gemm_f16 -c 1 -o /tmp/ncu_f16 tools/native_bench f16 8192 > $OUT/ncu_f16.log 2>&1; log "ncu f16 exit $?"
   ncu -i /tmp/ncu_f16.ncu-rep --page raw --csv > $OUT/ncu_f16_raw.csv 2>/dev/null
   ncu -i /tmp/ncu_f16.ncu-rep --page details > $OUT/ncu_f16_details.txt 2>/dev/null
-  timeout 300 tools/native_bench f16 8192 > $OUT/f16.log 2>&1; timeout 300 tools/native_bench f16 16384 >> $OUT/f16.log 2>&1; cat $OUT/f16.log | tee -a $OUT/session.log
   du -sh $OUT | tee -a $OUT/session.log
+  ;;
+ncu32)
+  # the default (cta_group::2) fp32 kernel under ncu --set full; gemm_check launches the cta_group::1 form first
+  timeout 300 ncu --set full --import-source on --clock-control none --kernel-name-base demangled -k regex:'gemm_f32_3xtf32_kernel<.int.2' -c 1 -o /tmp/ncu_f32 tools/gemm_check perf f32 8192 > $OUT/ncu_f32.log 2>&1; log "ncu f32 exit $?"
+  ncu -i /tmp/ncu_f32.ncu-rep --page raw --csv > $OUT/ncu_f32_raw.csv 2>/dev/null
+  ncu -i /tmp/ncu_f32.ncu-rep --page details > $OUT/ncu_f32_details.txt 2>/dev/null
+  grep -E "Duration|Cluster Size|Compute \(SM\) Throughput" $OUT/ncu_f32_details.txt | tee -a $OUT/session.log
+  ;;
+par4)
+  run timeout 300 $TR tests/dist_worker.py
   ;;
 fused)
   # fused small-message AllGather: parity, then the C4 sweep with it on / off; SUMMA-A / B panel pipeline A/B (C6)
