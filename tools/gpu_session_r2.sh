@@ -186,6 +186,12 @@ ncu32)
   ncu -i /tmp/ncu_f32.ncu-rep --page details > $OUT/ncu_f32_details.txt 2>/dev/null
   grep -E "Duration|Cluster Size|Compute \(SM\) Throughput" $OUT/ncu_f32_details.txt | tee -a $OUT/session.log
   ;;
+benchN)
+  log "=== bench.py N=$N"; timeout 400 $TR bench.py --gpus $N --steps 10 --warmup 3 > $OUT/bench_${N}gpu.json 2> $OUT/bench_${N}gpu.err; log "exit $?"
+  ;;
+skew)
+  log "=== bench.py N=$N (kernel time per rank)"; timeout 300 $TR bench.py --gpus $N --steps 10 --warmup 3 --no-sub --no-parity --no-cpu --no-e2e > $OUT/bench_${N}gpu.json 2> $OUT/bench_${N}gpu.err; log "exit $?"
+  ;;
 par4)
   run timeout 300 $TR tests/dist_worker.py
   ;;
