@@ -115,6 +115,26 @@ SIGNATURES = {
     "elb200_peer_reduce_axpy_f32": (ci, [ci, C.POINTER(vp), i64, C.POINTER(Segment), vp, i64, f32, vp]),
     "elb200_peer_reduce_axpy_f64": (ci, [ci, C.POINTER(vp), i64, C.POINTER(Segment), vp, i64, f64, vp]),
     "elb200_peer_allgather": (ci, [vp, ci, vp, i64, ci, C.POINTER(Segment), vp, i64, vp]),
+    "elb200_zdm_create": (ci, [vp, ci, ci, ci, C.POINTER(vp)]),
+    "elb200_zdm_destroy": (ci, [vp]),
+    "elb200_zdm_plane": (ci, [vp, ci, C.POINTER(vp)]),
+    "elb200_zdm_resize": (ci, [vp, i64, i64]),
+    "elb200_zdm_align": (ci, [vp, i64, i64]),
+    "elb200_zdm_align_with": (ci, [vp, vp]),
+    "elb200_zdm_set_root": (ci, [vp, ci]),
+    "elb200_zdm_set_stream": (ci, [vp, vp]),
+    "elb200_zdm_view": (ci, [vp, i64, i64, i64, i64, C.POINTER(vp)]),
+    "elb200_zdm_write_local": (ci, [vp, vp, i64]),
+    "elb200_zdm_read_local": (ci, [vp, vp, i64]),
+    "elb200_zdm_copy": (ci, [vp, vp]),
+    "elb200_zdm_transpose": (ci, [vp, vp, ci]),
+    "elb200_zdm_zero": (ci, [vp]),
+    "elb200_zdm_scale": (ci, [f64, f64, vp]),
+    "elb200_zdm_axpy": (ci, [f64, f64, vp, vp]),
+    "elb200_zdm_axpy_contract": (ci, [f64, f64, vp, vp]),
+    "elb200_zdm_gemm": (ci, [ci, ci, f64, f64, vp, vp, f64, f64, vp, ci]),
+    "elb200_gemm_c32": (ci, [ci, ci, i64, i64, i64, C.POINTER(f32), vp, i64, vp, i64, C.POINTER(f32), vp, i64, vp]),
+    "elb200_gemm_c64": (ci, [ci, ci, i64, i64, i64, C.POINTER(f64), vp, i64, vp, i64, C.POINTER(f64), vp, i64, vp]),
     "elb200_peer_exchange": (ci, [vp, ci, ci, C.POINTER(Segment), vp, i64, ci, C.POINTER(Segment), C.POINTER(ci), vp, i64, vp]),
     "elb200_peer_reduce_scatter_f32": (ci, [vp, ci, C.POINTER(Segment), vp, i64, C.POINTER(Segment), vp, i64, f32, vp]),
     "elb200_peer_reduce_scatter_f64": (ci, [vp, ci, C.POINTER(Segment), vp, i64, C.POINTER(Segment), vp, i64, f64, vp]),

@@ -127,7 +127,6 @@ __device__ __forceinline__ void lattice_items(const elb200_segment& sg, int64_t&
     }
     item_base += items;
 }
-__host__ __device__ inline int64_t seg_items(const elb200_segment& sg) { return (sg.rows + kRun - 1) / kRun * sg.cols; }
 
 // ---- PUSH all-gather -------------------------------------------------------------------------------------------------
 template <typename E>  // E: unsigned integer of the element size

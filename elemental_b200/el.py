@@ -310,6 +310,8 @@ class DistMatrix:
 
 def Copy(A: DistMatrix, B: DistMatrix) -> None:
     """B = A (DistMatrix::operator=; src/core/DistMatrix/ElementMatrix/*.cpp)."""
+    if isinstance(A, ComplexDistMatrix):
+        return ZCopy(A, B)
     check(lib.elb200_dm_copy(A._h, B._h), "Copy")
 
 
@@ -351,6 +353,8 @@ def LocalGemm(orientA, orientB, alpha, A: DistMatrix, B: DistMatrix, beta, C_: D
 def Gemm(orientA, orientB, alpha, A: DistMatrix, B: DistMatrix, beta, C_: DistMatrix,
          alg: int = GEMM_DEFAULT) -> None:
     """El::Gemm(orientA, orientB, alpha, A, B, beta, C, alg) (src/blas_like/level3/Gemm.cpp:273-302)."""
+    if isinstance(A, ComplexDistMatrix):
+        return ZGemm(orientA, orientB, alpha, A, B, beta, C_, alg)
     check(lib.elb200_dist_gemm(orientA, orientB, alpha, A._h, B._h, beta, C_._h, alg), "Gemm")
 
 
@@ -455,3 +459,24 @@ def gemm_local(orientA, orientB, alpha, A: torch.Tensor, lda, B: torch.Tensor, l
         st = lib.elb200_gemm_f64(orientA, orientB, m, n, k, alpha, A.data_ptr(), lda, B.data_ptr(), ldb,
                                  beta, C_.data_ptr(), ldc, stream)
     check(st, "gemm_local")
+
+
+# ---- complex instantiations: planar storage, 4M on the real kernels (csrc/capi_complex.cpp) ----
+from . import _zdm as _zdm_mod  # noqa: E402
+
+_z = _zdm_mod.bind(lib, check, _lib.DmInfo)
+ComplexDistMatrix, ZCopy, ZTranspose, ZZero, ZScale, ZAxpy, ZAxpyContract, ZGemm = (
+    _z.ComplexDistMatrix, _z.ZCopy, _z.ZTranspose, _z.ZZero, _z.ZScale, _z.ZAxpy, _z.ZAxpyContract, _z.ZGemm)
+
+
+def gemm_local_complex(orientA, orientB, alpha, A: torch.Tensor, lda, B: torch.Tensor, ldb, beta, C_: torch.Tensor, ldc, m, n, k,
+                       stream: int = 0) -> None:
+    """Gemm(Matrix<Complex<T>,Device::GPU>) on raw interleaved column-major device buffers (the cublasCgemm / Zgemm call of
+    src/hydrogen/device/cuBLAS_API.cpp:419-427): elb200_gemm_c32 / _c64."""
+    if C_.dtype not in (torch.complex64, torch.complex128) or not (A.dtype == B.dtype == C_.dtype):
+        raise TypeError("gemm_local_complex: complex64 or complex128 operands of one dtype")
+    R = C.c_float if C_.dtype == torch.complex64 else C.c_double
+    al, be = complex(alpha), complex(beta)
+    fn = lib.elb200_gemm_c32 if C_.dtype == torch.complex64 else lib.elb200_gemm_c64
+    check(fn(orientA, orientB, m, n, k, (R * 2)(al.real, al.imag), A.data_ptr(), lda, B.data_ptr(), ldb, (R * 2)(be.real, be.imag),
+             C_.data_ptr(), ldc, stream), "gemm_local_complex")

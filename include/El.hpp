@@ -12,6 +12,7 @@
 #include <cuda_runtime_api.h>
 
 #include <cmath>
+#include <complex>
 #include <cstdint>
 #include <cstdlib>
 #include <exception>
@@ -27,6 +28,7 @@
 namespace El {
 
 typedef int Int;  // reference default (no EL_USE_64BIT_INTS)
+template <typename Real> using Complex = std::complex<Real>;  // El::Complex<Real> (include/El/core/Element/Complex/decl.hpp)
 typedef __half gpu_half_type;  // hydrogen::gpu_half_type (include/hydrogen/utils/HalfPrecision.hpp): IEEE half on the device
 
 // Values as in the reference (include/El/core/types.hpp:208-217, :464-469; level3.hpp:23-33).
@@ -134,6 +136,11 @@ template <> struct TypeCode<float> { static constexpr int value = ELB200_F32; };
 template <> struct TypeCode<double> { static constexpr int value = ELB200_F64; };
 template <> struct TypeCode<__half> { static constexpr int value = ELB200_F16; };
 template <typename T> struct IsElement { static constexpr bool value = std::is_same<T, float>::value || std::is_same<T, double>::value || std::is_same<T, __half>::value; };
+// Complex<float> / Complex<double>: storable in a Matrix (interleaved, the reference's layout); the routines that take
+// them are the complex section at the end of this header
+template <typename T> struct IsComplex { static constexpr bool value = false; };
+template <typename R> struct IsComplex<std::complex<R>> { static constexpr bool value = std::is_same<R, float>::value || std::is_same<R, double>::value; };
+template <typename T> struct IsStorable { static constexpr bool value = IsElement<T>::value || IsComplex<T>::value; };
 }  // namespace detail
 
 // ---------------------------------------------------------------------------------------------
@@ -322,7 +329,7 @@ static const Range ALL{0, -1};
 template <typename T, Device D = Device::GPU>
 class Matrix {
     static_assert(D == Device::GPU, "elemental_b200 has no CPU path: Matrix<T, Device::GPU> only");
-    static_assert(detail::IsElement<T>::value, "float, double and gpu_half_type only");
+    static_assert(detail::IsStorable<T>::value, "float, double, gpu_half_type, Complex<float> and Complex<double> only");
 
 public:
     Matrix() = default;
@@ -1092,6 +1099,148 @@ double FrobeniusNorm(const AbstractDistMatrix<T>& A) {
     long double s = 0;
     for (T v : host) s += (long double)v * (long double)v;
     return double(std::sqrt(s));
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// Complex instantiations: DistMatrix<Complex<float|double>,U,V,ELEMENT,Device::GPU>, El::Gemm, Copy, Transpose /
+// Adjoint, Axpy, Scale, Zero on them, and Gemm(Matrix<Complex<T>>) — the reference's complex instantiations of
+// src/blas_like/level3/Gemm.cpp:504-506 and the ElementMatrix / level-1 sources (El/macros/Instantiate.h). The engine
+// stores a complex DistMatrix PLANAR and multiplies with four real products (elb200_zdm_*, csrc/capi_complex.cpp), so the
+// local matrix is not addressable as one interleaved device buffer: local data crosses through SetLocalFromHost /
+// GetLocalToHost (interleaved, ld = LocalHeight()), Get / Set, or the real planes.
+// ---------------------------------------------------------------------------------------------
+namespace detail {
+template <typename R>
+class ComplexDistMatrixBase {
+public:
+    typedef Complex<R> value_type;
+    virtual ~ComplexDistMatrixBase() { if (h_) elb200_zdm_destroy(h_); }
+    ComplexDistMatrixBase(const ComplexDistMatrixBase&) = delete;
+    ComplexDistMatrixBase& operator=(const ComplexDistMatrixBase&) = delete;
+
+    void Resize(Int height, Int width) { Check(elb200_zdm_resize(h_, height, width), "Resize"); }
+    void Align(Int colAlign, Int rowAlign, bool = true) { Check(elb200_zdm_align(h_, colAlign, rowAlign), "Align"); }
+    void AlignWith(const ComplexDistMatrixBase<R>& A) { Check(elb200_zdm_align_with(h_, A.Handle()), "AlignWith"); }
+    void SetRoot(int root) { Check(elb200_zdm_set_root(h_, root), "SetRoot"); }
+    void SetSyncInfo(const SyncInfo<Device::GPU>& si) { Check(elb200_zdm_set_stream(h_, si.Stream()), "SetSyncInfo"); }
+    const El::Grid& Grid() const { return *grid_; }
+    Int Height() const { return Int(Info().height); }
+    Int Width() const { return Int(Info().width); }
+    Int LocalHeight() const { return Int(Info().local_height); }
+    Int LocalWidth() const { return Int(Info().local_width); }
+    Int ColAlign() const { return Int(Info().col_align); }
+    Int RowAlign() const { return Int(Info().row_align); }
+    Int ColShift() const { return Int(Info().col_shift); }
+    Int RowShift() const { return Int(Info().row_shift); }
+    Int ColStride() const { return Int(Info().col_stride); }
+    Int RowStride() const { return Int(Info().row_stride); }
+    Dist ColDist() const { return FromEngineDist(Info().col_dist); }
+    Dist RowDist() const { return FromEngineDist(Info().row_dist); }
+    Int GlobalRow(Int iLoc) const { const auto d = Info(); return Int(d.col_shift + iLoc * d.col_stride); }
+    Int GlobalCol(Int jLoc) const { const auto d = Info(); return Int(d.row_shift + jLoc * d.row_stride); }
+    cudaStream_t Stream() const { return static_cast<cudaStream_t>(elb200_dm_stream(Plane(0))); }
+    elb200_zdm_t Handle() const { return h_; }
+    elb200_dm_t Plane(int imag) const { elb200_dm_t p = nullptr; Check(elb200_zdm_plane(h_, imag, &p), "Plane"); return p; }
+    // interleaved host <-> local matrix, leading dimension LocalHeight() on the host side; synchronous
+    void SetLocalFromHost(const Complex<R>* host) {
+        Check(elb200_zdm_write_local(h_, host, LocalHeight() > 0 ? LocalHeight() : 1), "SetLocalFromHost");
+        if (cudaStreamSynchronize(Stream()) != cudaSuccess) throw std::runtime_error("SetLocalFromHost: stream synchronisation failed");
+    }
+    void GetLocalToHost(Complex<R>* host) const {
+        Check(elb200_zdm_read_local(h_, host, LocalHeight() > 0 ? LocalHeight() : 1), "GetLocalToHost");
+        if (cudaStreamSynchronize(Stream()) != cudaSuccess) throw std::runtime_error("GetLocalToHost: stream synchronisation failed");
+    }
+
+protected:
+    ComplexDistMatrixBase(const El::Grid& g, Dist U, Dist V) : grid_(&g) {
+        Check(elb200_zdm_create(g.Handle(), TypeCode<R>::value, ToEngineDist(U), ToEngineDist(V), &h_), "DistMatrix<Complex>");
+    }
+    ComplexDistMatrixBase(const El::Grid& g, std::nullptr_t) : grid_(&g) {}
+    void MoveFrom(ComplexDistMatrixBase& o) noexcept {
+        if (this != &o) { if (h_) elb200_zdm_destroy(h_); grid_ = o.grid_; h_ = o.h_; o.h_ = nullptr; }
+    }
+    elb200_dm_info_t Info() const {
+        elb200_dm_info_t d;
+        Check(elb200_dm_info(Plane(0), &d), "DistMatrix<Complex>::Info");
+        return d;
+    }
+    const El::Grid* grid_;
+    elb200_zdm_t h_ = nullptr;
+};
+}  // namespace detail
+
+template <typename R, Dist U, Dist V>
+class DistMatrix<Complex<R>, U, V, ELEMENT, Device::GPU> : public detail::ComplexDistMatrixBase<R> {
+    static_assert(std::is_same<R, float>::value || std::is_same<R, double>::value, "Complex<float> and Complex<double> only");
+
+public:
+    explicit DistMatrix(const El::Grid& g) : detail::ComplexDistMatrixBase<R>(g, U, V) {}
+    DistMatrix(Int height, Int width, const El::Grid& g) : DistMatrix(g) { this->Resize(height, width); }
+    DistMatrix(DistMatrix&& o) noexcept : detail::ComplexDistMatrixBase<R>(*o.grid_, nullptr) { this->MoveFrom(o); }
+    DistMatrix& operator=(DistMatrix&& o) noexcept { this->MoveFrom(o); return *this; }
+    // redistribution from any (U2,V2): the real path applied to both planes
+    DistMatrix& operator=(const detail::ComplexDistMatrixBase<R>& A) {
+        detail::Check(elb200_zdm_copy(A.Handle(), this->Handle()), "DistMatrix<Complex>::operator=");
+        return *this;
+    }
+    DistMatrix& operator=(const DistMatrix& A) { return *this = static_cast<const detail::ComplexDistMatrixBase<R>&>(A); }
+};
+
+template <typename R>
+void Copy(const detail::ComplexDistMatrixBase<R>& A, detail::ComplexDistMatrixBase<R>& B) {
+    detail::Check(elb200_zdm_copy(A.Handle(), B.Handle()), "Copy");
+}
+template <typename R>
+void Transpose(const detail::ComplexDistMatrixBase<R>& A, detail::ComplexDistMatrixBase<R>& B, bool conjugate = false) {
+    detail::Check(elb200_zdm_transpose(A.Handle(), B.Handle(), conjugate ? 1 : 0), "Transpose");
+}
+template <typename R>
+void Adjoint(const detail::ComplexDistMatrixBase<R>& A, detail::ComplexDistMatrixBase<R>& B) { Transpose(A, B, true); }
+template <typename R>
+void Zero(detail::ComplexDistMatrixBase<R>& A) { detail::Check(elb200_zdm_zero(A.Handle()), "Zero"); }
+template <typename R>
+void Scale(Complex<R> alpha, detail::ComplexDistMatrixBase<R>& A) {
+    detail::Check(elb200_zdm_scale(double(alpha.real()), double(alpha.imag()), A.Handle()), "Scale");
+}
+template <typename R>
+void Axpy(Complex<R> alpha, const detail::ComplexDistMatrixBase<R>& X, detail::ComplexDistMatrixBase<R>& Y) {
+    detail::Check(elb200_zdm_axpy(double(alpha.real()), double(alpha.imag()), X.Handle(), Y.Handle()), "Axpy");
+}
+// C := alpha op(A) op(B) + beta C; ADJOINT is the conjugate transpose
+template <typename R>
+void Gemm(Orientation orientA, Orientation orientB, Complex<R> alpha, const detail::ComplexDistMatrixBase<R>& A,
+          const detail::ComplexDistMatrixBase<R>& B, Complex<R> beta, detail::ComplexDistMatrixBase<R>& C, GemmAlgorithm alg = GEMM_DEFAULT) {
+    detail::Check(elb200_zdm_gemm(int(orientA), int(orientB), double(alpha.real()), double(alpha.imag()), A.Handle(), B.Handle(),
+                                  double(beta.real()), double(beta.imag()), C.Handle(), int(alg)), "Gemm");
+}
+template <typename R>
+void Gemm(Orientation orientA, Orientation orientB, Complex<R> alpha, const detail::ComplexDistMatrixBase<R>& A,
+          const detail::ComplexDistMatrixBase<R>& B, detail::ComplexDistMatrixBase<R>& C, GemmAlgorithm alg = GEMM_DEFAULT) {
+    C.Resize(orientA == NORMAL ? A.Height() : A.Width(), orientB == NORMAL ? B.Width() : B.Height());
+    Gemm(orientA, orientB, alpha, A, B, Complex<R>(0), C, alg);
+}
+// Gemm(Matrix<Complex<T>,Device::GPU>): interleaved local matrices (the cublasCgemm / Zgemm call of the reference)
+namespace detail {
+inline int LocalComplexGemm(int ta, int tb, long m, long n, long k, Complex<float> al, const Complex<float>* A, long lda, const Complex<float>* B,
+                            long ldb, Complex<float> be, Complex<float>* C, long ldc, void* s) {
+    const float a2[2] = {al.real(), al.imag()}, b2[2] = {be.real(), be.imag()};
+    return elb200_gemm_c32(ta, tb, m, n, k, a2, A, lda, B, ldb, b2, C, ldc, s);
+}
+inline int LocalComplexGemm(int ta, int tb, long m, long n, long k, Complex<double> al, const Complex<double>* A, long lda, const Complex<double>* B,
+                            long ldb, Complex<double> be, Complex<double>* C, long ldc, void* s) {
+    const double a2[2] = {al.real(), al.imag()}, b2[2] = {be.real(), be.imag()};
+    return elb200_gemm_c64(ta, tb, m, n, k, a2, A, lda, B, ldb, b2, C, ldc, s);
+}
+}  // namespace detail
+template <typename R>
+void Gemm(Orientation orientA, Orientation orientB, Complex<R> alpha, const Matrix<Complex<R>>& A, const Matrix<Complex<R>>& B, Complex<R> beta,
+          Matrix<Complex<R>>& C) {
+    const Int m = orientA == NORMAL ? A.Height() : A.Width(), ka = orientA == NORMAL ? A.Width() : A.Height();
+    const Int n = orientB == NORMAL ? B.Width() : B.Height(), kb = orientB == NORMAL ? B.Height() : B.Width();
+    if (ka != kb || C.Height() != m || C.Width() != n) throw std::logic_error("Gemm: nonconformal matrices");
+    detail::Check(detail::LocalComplexGemm(int(orientA), int(orientB), m, n, ka, alpha, A.LockedBuffer(), A.LDim(), B.LockedBuffer(), B.LDim(),
+                                           beta, C.Buffer(), C.LDim(), C.GetSyncInfo().Stream()), "Gemm");
 }
 
 }  // namespace El

@@ -566,6 +566,43 @@ int elb200_dist_gemm_host_f64(elb200_grid_t g, int transA, int transB, int64_t m
                               double alpha, const double* A, int64_t lda, const double* B, int64_t ldb,
                               double beta, double* C, int64_t ldc);
 
+/* ---- Complex instantiations: El::Gemm, redistributions and entrywise routines for Complex<float> /
+ * Complex<double> (reference: src/blas_like/level3/Gemm.cpp:504-506 and the complex instantiations of
+ * the sources under src/core/DistMatrix/ElementMatrix and src/blas_like/level1 via include/El/macros/Instantiate.h),
+ * built on the real ABI ("4M").
+ * A complex DistMatrix is stored PLANAR — a real and an imaginary DistMatrix (elb200_zdm_plane) with one distribution and
+ * alignment — so every redistribution is the real path applied to both planes and El::Gemm is four real El::Gemm calls
+ * plus entrywise combinations (csrc/capi_complex.cpp). The reference's interleaved (re, im) layout exists at the
+ * boundary: elb200_zdm_write_local / read_local take interleaved HOST or DEVICE buffers (ld in complex elements), and
+ * elb200_gemm_c32 / _c64 multiply interleaved local matrices (the Gemm(Matrix<Complex<T>,GPU>) -> cublasCgemm / Zgemm of
+ * src/hydrogen/device/cuBLAS_API.cpp:419-427). real_dtype is ELB200_F32 or ELB200_F64; scalars are (re, im) pairs. */
+typedef struct elb200_zdm_s* elb200_zdm_t;
+int elb200_zdm_create(elb200_grid_t g, int real_dtype, int col_dist, int row_dist, elb200_zdm_t* out);
+int elb200_zdm_destroy(elb200_zdm_t a);
+int elb200_zdm_plane(elb200_zdm_t a, int imag, elb200_dm_t* out); /* borrowed: the real (0) / imaginary (1) DistMatrix */
+int elb200_zdm_resize(elb200_zdm_t a, int64_t height, int64_t width);
+int elb200_zdm_align(elb200_zdm_t a, int64_t col_align, int64_t row_align);
+int elb200_zdm_align_with(elb200_zdm_t a, elb200_zdm_t other);
+int elb200_zdm_set_root(elb200_zdm_t a, int root);
+int elb200_zdm_set_stream(elb200_zdm_t a, void* stream);
+int elb200_zdm_view(elb200_zdm_t a, int64_t i0, int64_t i1, int64_t j0, int64_t j1, elb200_zdm_t* out);
+int elb200_zdm_write_local(elb200_zdm_t a, const void* interleaved, int64_t ld);
+int elb200_zdm_read_local(elb200_zdm_t a, void* interleaved, int64_t ld);
+int elb200_zdm_copy(elb200_zdm_t A, elb200_zdm_t B);                     /* B = A, any pair of distributions */
+int elb200_zdm_transpose(elb200_zdm_t A, elb200_zdm_t B, int conjugate); /* Transpose / Adjoint (level1/Transpose.hpp) */
+int elb200_zdm_zero(elb200_zdm_t A);
+int elb200_zdm_scale(double alpha_re, double alpha_im, elb200_zdm_t A);
+int elb200_zdm_axpy(double alpha_re, double alpha_im, elb200_zdm_t X, elb200_zdm_t Y);
+int elb200_zdm_axpy_contract(double alpha_re, double alpha_im, elb200_zdm_t A, elb200_zdm_t B);
+/* El::Gemm(orientA, orientB, alpha, A, B, beta, C, alg) for complex DistMatrices; ELB200_OP_C is the conjugate transpose. */
+int elb200_zdm_gemm(int transA, int transB, double alpha_re, double alpha_im, elb200_zdm_t A, elb200_zdm_t B, double beta_re,
+                    double beta_im, elb200_zdm_t C, int alg);
+/* Local complex GEMM on interleaved column-major device matrices; alpha, beta point to (re, im). beta == 0 never reads C. */
+int elb200_gemm_c32(int transA, int transB, int64_t m, int64_t n, int64_t k, const float* alpha, const void* A, int64_t lda,
+                    const void* B, int64_t ldb, const float* beta, void* C, int64_t ldc, void* stream);
+int elb200_gemm_c64(int transA, int transB, int64_t m, int64_t n, int64_t k, const double* alpha, const void* A, int64_t lda,
+                    const void* B, int64_t ldb, const double* beta, void* C, int64_t ldc, void* stream);
+
 #ifdef __cplusplus
 } /* extern "C" */
 #endif

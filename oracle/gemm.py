@@ -17,12 +17,16 @@ NORMAL, TRANSPOSE, ADJOINT = 0, 1, 2
 
 
 def op(X: np.ndarray, orient: int) -> np.ndarray:
-    return X if orient == NORMAL else X.T
+    if orient == NORMAL:
+        return X
+    return X.conj().T if (orient == ADJOINT and np.iscomplexobj(X)) else X.T
 
 
 def gemm_global(orientA, orientB, alpha, A, B, beta, C, acc=np.float64) -> np.ndarray:
     """C = alpha op(A) op(B) + beta C computed in `acc` precision on the global matrices: the value
     every distributed variant approximates. Result is returned in `acc`."""
+    if np.iscomplexobj(A) or np.iscomplexobj(B) or np.iscomplexobj(C) or isinstance(alpha, complex) or isinstance(beta, complex):
+        acc = np.complex128
     P = op(np.asarray(A, dtype=acc), orientA) @ op(np.asarray(B, dtype=acc), orientB)
     return acc(alpha) * P + (acc(beta) * np.asarray(C, dtype=acc) if beta != 0 else 0)
 
@@ -187,6 +191,30 @@ def dist_gemm(g: Grid, orientA, orientB, alpha, A, B, beta, C, alg=GEMM_DEFAULT,
     return Cd.to_global()
 
 
+def dist_gemm_complex(g: Grid, orientA, orientB, alpha, A, B, beta, C, alg=GEMM_DEFAULT, nb=128) -> np.ndarray:
+    """El::Gemm for Complex<float|double> (src/blas_like/level3/Gemm.cpp:504-506) the way THIS path computes it
+    (elemental_b200/csrc/capi_complex.cpp, "4M"): with op(A) = Ar' + i sa Ai', op(B) = Br' + i sb Bi' (sa, sb = -1 for
+    ADJOINT) the product is four REAL El::Gemm calls on the planes — each restated by dist_gemm above and pinned to the
+    reference's real outputs —
+        T = Ar'Br' - sa sb Ai'Bi',   U = sb Ar'Bi' + sa Ai'Br',   C = alpha (T + iU) + beta C.
+    Pinned against the reference's own complex outputs by tests/test_oracle.py (tests/golden/ref_gemm_complex_1x1.npz)."""
+    real = np.float32 if np.dtype(C.dtype) == np.complex64 else np.float64
+    oa, ob = (NORMAL if orientA == NORMAL else TRANSPOSE), (NORMAL if orientB == NORMAL else TRANSPOSE)
+    sa, sb = (-1.0 if orientA == ADJOINT else 1.0), (-1.0 if orientB == ADJOINT else 1.0)
+    Ar, Ai = np.ascontiguousarray(A.real, dtype=real), np.ascontiguousarray(A.imag, dtype=real)
+    Br, Bi = np.ascontiguousarray(B.real, dtype=real), np.ascontiguousarray(B.imag, dtype=real)
+    Z = np.zeros(C.shape, dtype=real)
+    T = dist_gemm(g, oa, ob, 1.0, Ar, Br, 0.0, Z, alg, nb)
+    T = dist_gemm(g, oa, ob, -sa * sb, Ai, Bi, 1.0, T, alg, nb)
+    U = dist_gemm(g, oa, ob, sb, Ar, Bi, 0.0, Z, alg, nb)
+    U = dist_gemm(g, oa, ob, sa, Ai, Br, 1.0, U, alg, nb)
+    al, be = complex(alpha), complex(beta)
+    Cr, Ci = C.real.astype(real), C.imag.astype(real)
+    out_r = real(al.real) * T - real(al.imag) * U + (real(be.real) * Cr - real(be.imag) * Ci if be != 0 else 0)
+    out_i = real(al.real) * U + real(al.imag) * T + (real(be.real) * Ci + real(be.imag) * Cr if be != 0 else 0)
+    return (out_r + 1j * out_i).astype(C.dtype)
+
+
 def summa_nnc_1x1(alpha, A: np.ndarray, B: np.ndarray, beta, C: np.ndarray, nb: int = 128) -> np.ndarray:
     """The reference's CPU El::Gemm(NORMAL,NORMAL,...,GEMM_SUMMA_C) on a 1 x 1 grid, without the
     virtual-rank bookkeeping: Scale(beta,C) (Gemm.cpp:282), then per nb-panel a local copy of A1
@@ -204,8 +232,9 @@ def summa_nnc_1x1(alpha, A: np.ndarray, B: np.ndarray, beta, C: np.ndarray, nb: 
 
 
 def frobenius_rel_err(X, ref) -> float:
-    ref = np.asarray(ref, dtype=np.float64)
-    d = np.asarray(X, dtype=np.float64) - ref
+    acc = np.complex128 if (np.iscomplexobj(X) or np.iscomplexobj(ref)) else np.float64
+    ref = np.asarray(ref, dtype=acc)
+    d = np.asarray(X, dtype=acc) - ref
     den = np.linalg.norm(ref)
     return float(np.linalg.norm(d) / (den if den > 0 else 1.0))
 
@@ -216,6 +245,9 @@ def gemm_tolerance(dtype, k: int) -> float:
         # half: no bound in north_star and no golden vectors in the reference; products accumulate in fp32
         # on the device and are rounded to half (eps 9.8e-4) once per SUMMA panel / partial-sum reduction
         return 4e-3
+    if np.dtype(dtype).kind == "c":
+        # complex: a complex dot product of length k sums 2k real products per component
+        return gemm_tolerance(np.float32 if np.dtype(dtype) == np.complex64 else np.float64, 2 * k)
     return (1e-13 if np.dtype(dtype) == np.float64 else 1e-5) * float(np.sqrt(max(k, 1)))
 
 

@@ -79,6 +79,7 @@ def main() -> int:
     print(f"wrote {len(meta)} Gemm cases, {len(L)} index rows, {len(H)} grid heights to {OUT}")
     make_dist_golden()
     make_level3_golden()
+    make_complex_golden()
     return 0
 
 
@@ -182,7 +183,47 @@ def make_level3_golden() -> None:
     print(f"wrote level-3 reference runs for grids {[f'{h}x{n // h}' for n, h in LEVEL3_GRIDS]}")
 
 
+def lcg_complex_matrix(h: int, w: int, seed: int, dtype) -> np.ndarray:
+    """fill_lcg_complex of gemm_ref.cpp: real part from stream `seed`, imaginary part from stream `seed + 1000`."""
+    real = np.float32 if np.dtype(dtype) == np.complex64 else np.float64
+    return (lcg_matrix(h, w, seed, real) + 1j * lcg_matrix(h, w, seed + 1000, real)).astype(dtype)
+
+
+def make_complex_golden() -> None:
+    """tests/golden/ref_gemm_complex_1x1.npz: the reference's own El::Gemm<Complex<float|double>> (SURVEY 8(f) N3;
+    src/blas_like/level3/Gemm.cpp:504-506) on one rank — orientations NORMAL / TRANSPOSE / ADJOINT, all five
+    GemmAlgorithm values, complex alpha and beta. Inputs come from the restated LCG (checked bit for bit on case 0),
+    only the reference's C is stored. meta columns: type (0 c32, 1 c64), id, orientA, orientB, alg, m, n, k, nb,
+    alpha re, alpha im, beta re, beta im."""
+    with tempfile.TemporaryDirectory() as tmp:
+        subprocess.run([REF_BIN, "--golden-complex", tmp], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        arrays, meta = {}, []
+        for ln in open(os.path.join(tmp, "index_complex.txt")):
+            t, cid, oa, ob, alg, m, n, k, nb, ar, ai, br, bi = ln.split()
+            cid, oa, ob, alg, m, n, k, nb = map(int, (cid, oa, ob, alg, m, n, k, nb))
+            dt = np.complex64 if t == "c32" else np.complex128
+            shapes = {"A": (k, m) if oa else (m, k), "B": (n, k) if ob else (k, n), "C0": (m, n), "C": (m, n)}
+            for name, (h, w) in shapes.items():
+                if name != "C" and cid != 0:
+                    continue
+                raw = np.fromfile(os.path.join(tmp, f"{t}_{cid}_{name}.bin"), dtype=dt)
+                assert raw.size == h * w, (ln, name, raw.size)
+                mat = raw.reshape(w, h).T.copy()
+                if name == "C":
+                    arrays[f"{t}_{cid}_C"] = mat
+                else:
+                    seed = 3 * cid + {"A": 0, "B": 1, "C0": 2}[name]
+                    assert np.array_equal(mat, lcg_complex_matrix(h, w, seed, dt)), (ln, name)
+            meta.append((0 if t == "c32" else 1, cid, oa, ob, alg, m, n, k, nb, float(ar), float(ai), float(br), float(bi)))
+        arrays["meta"] = np.array(meta, dtype=np.float64)
+        np.savez_compressed(os.path.join(OUT, "ref_gemm_complex_1x1.npz"), **arrays)
+    print(f"wrote {len(meta)} complex Gemm cases to {OUT}")
+
+
 if __name__ == "__main__":
+    if "--complex-only" in sys.argv:
+        make_complex_golden()
+        sys.exit(0)
     if "--level3-only" in sys.argv:
         make_level3_golden()
         sys.exit(0)

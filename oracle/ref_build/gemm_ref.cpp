@@ -90,6 +90,53 @@ static void golden_cases(const std::string& dir, const char* tname, std::ofstrea
                 }
 }
 
+// Complex instantiations (src/blas_like/level3/Gemm.cpp:504-506 via El/macros/Instantiate.h): the reference's own
+// El::Gemm<Complex<float|double>> on one rank, orientations NORMAL / TRANSPOSE / ADJOINT, complex alpha and beta.
+template <typename R>
+static void fill_lcg_complex(Matrix<Complex<R>>& M, unsigned seed) {
+    Matrix<R> re(M.Height(), M.Width()), im(M.Height(), M.Width());
+    fill_lcg(re, seed);
+    fill_lcg(im, seed + 1000);
+    for (Int j = 0; j < M.Width(); ++j)
+        for (Int i = 0; i < M.Height(); ++i) M.Set(i, j, Complex<R>(re.Get(i, j), im.Get(i, j)));
+}
+template <typename R>
+static void golden_cases_complex(const std::string& dir, const char* tname, std::ofstream& index) {
+    using T = Complex<R>;
+    const Grid& g = Grid::Default();
+    struct Case { Int m, n, k; Int nb; double ar, ai, br, bi; bool all; };
+    const Case cases[] = {{37, 29, 53, 16, 2.0, -0.5, 3.0, 0.25, true}, {5, 130, 41, 32, 1.0, 0.0, 0.0, 0.0, false},
+                          {64, 48, 40, 128, 0.5, 0.0, -0.5, 0.0, false}};
+    const Orientation os[3] = {NORMAL, TRANSPOSE, ADJOINT};
+    const GemmAlgorithm algs[] = {GEMM_DEFAULT, GEMM_SUMMA_A, GEMM_SUMMA_B, GEMM_SUMMA_C, GEMM_SUMMA_DOT};
+    int id = 0;
+    for (const Case& c : cases)
+        for (int ia = 0; ia < 3; ++ia)
+            for (int ib = 0; ib < 3; ++ib)
+                for (GemmAlgorithm alg : algs) {
+                    if (!c.all && !((ia == 0 || ia == 2) && (ib == 0 || ib == 2) && (alg == GEMM_DEFAULT || alg == GEMM_SUMMA_C))) continue;
+                    DistMatrix<T> A(g), B(g), C(g);
+                    A.Resize(ia ? c.k : c.m, ia ? c.m : c.k);
+                    B.Resize(ib ? c.n : c.k, ib ? c.k : c.n);
+                    C.Resize(c.m, c.n);
+                    fill_lcg_complex(A.Matrix(), 3 * id + 0);
+                    fill_lcg_complex(B.Matrix(), 3 * id + 1);
+                    fill_lcg_complex(C.Matrix(), 3 * id + 2);
+                    const std::string base = dir + "/" + tname + "_" + std::to_string(id);
+                    if (id == 0) {
+                        dump(base + "_A.bin", A.LockedMatrix());
+                        dump(base + "_B.bin", B.LockedMatrix());
+                        dump(base + "_C0.bin", C.LockedMatrix());
+                    }
+                    SetBlocksize(c.nb);
+                    Gemm(os[ia], os[ib], T(R(c.ar), R(c.ai)), A, B, T(R(c.br), R(c.bi)), C, alg);
+                    dump(base + "_C.bin", C.LockedMatrix());
+                    index << tname << " " << id << " " << ia << " " << ib << " " << int(alg) << " " << c.m << " " << c.n << " "
+                          << c.k << " " << c.nb << " " << c.ar << " " << c.ai << " " << c.br << " " << c.bi << "\n";
+                    ++id;
+                }
+}
+
 // ---------------------------------------------------------------------------------------------
 // Multi-rank golden run (ELB_STUB_NP processes over stub/mpi_stub.cpp): what the REFERENCE puts
 // on every rank after each (U,V) -> (U2,V2) redistribution and after El::Gemm on an r x c grid.
@@ -360,6 +407,13 @@ int main(int argc, char* argv[]) {
         std::printf("REF_GEMM_SECONDS %.6f n=%d dtype=%s\n", t, int(n), argv[2]);
         return 0;
     }
+    if (argc >= 3 && !std::strcmp(argv[1], "--golden-complex")) {
+        const std::string dir = argv[2];
+        std::ofstream index(dir + "/index_complex.txt");
+        golden_cases_complex<float>(dir, "c32", index);
+        golden_cases_complex<double>(dir, "c64", index);
+        return 0;
+    }
     if (argc >= 3 && !std::strcmp(argv[1], "--golden")) {
         const std::string dir = argv[2];
         std::ofstream index(dir + "/index.txt");
@@ -378,6 +432,6 @@ int main(int argc, char* argv[]) {
         for (int p = 1; p <= 64; ++p) tab << "H " << p << " " << Grid::DefaultHeight(p) << "\n";
         return 0;
     }
-    std::printf("usage: gemm_ref --bench f32|f64 n | --golden dir | --dist-golden dir gridHeight (under ELB_STUB_NP)\n");
+    std::printf("usage: gemm_ref --bench f32|f64 n | --golden dir | --golden-complex dir | --dist-golden dir gridHeight (under ELB_STUB_NP)\n");
     return 64;
 }

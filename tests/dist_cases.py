@@ -13,6 +13,7 @@ from __future__ import annotations
 
 import ctypes as C
 import itertools
+import os
 
 import numpy as np
 import torch
@@ -894,6 +895,130 @@ def check_half(grid) -> int:
     return cnt + 1
 
 
+def _complex_matrix(rows, cols, seed, npdt):
+    real = np.float32 if np.dtype(npdt) == np.complex64 else np.float64
+    return (OG.uniform_matrix(rows, cols, seed, real, 0.0, 1.0) + 1j * OG.uniform_matrix(rows, cols, seed + 50, real, 0.0, 1.0)).astype(npdt)
+
+
+def complex_gemm_case(grid, npdt, oa, ob, alg, m, n, k, alpha=2.0 - 0.5j, beta=3.0 + 0.25j, aligns=None, nb=None, dists=None):
+    """One El::Gemm on complex DistMatrices (planar storage, 4M on the real kernels) vs the global definition with
+    conjugation; error restricted to this rank's entries like gemm_case."""
+    og = _grid_oracle(grid)
+    me = grid.Rank()
+    A = _complex_matrix(*((m, k) if oa == 0 else (k, m)), 201, npdt)
+    B = _complex_matrix(*((k, n) if ob == 0 else (n, k)), 202, npdt)
+    C = _complex_matrix(m, n, 203, npdt)
+    aligns = aligns or ((0, 0), (0, 0), (0, 0))
+    dists = dists or ((el.MC, el.MR),) * 3
+    mats = []
+    for G, d, al in zip((A, B, C), dists, aligns):
+        mats.append(el.ComplexDistMatrix(grid, d[0], d[1], npdt).Align(al[0] % og.stride(d[0]), al[1] % og.stride(d[1])).from_global(G))
+    dA, dB, dC = mats
+    if nb:
+        el.PushBlocksizeStack(nb)
+    try:
+        el.Gemm(oa, ob, alpha, dA, dB, beta, dC, alg)
+    finally:
+        if nb:
+            el.PopBlocksizeStack()
+    got = dC.get_local()
+    ref = OG.gemm_global(oa, ob, alpha, A, B, beta, C)
+    spec = OD.Spec(dists[2][0], dists[2][1], dC.ColAlign(), dC.RowAlign(), m, n)
+    ref_loc = OD.local_of(ref, spec, og, me)
+    num = float(np.linalg.norm(got.astype(np.complex128) - ref_loc))
+    den = float(np.linalg.norm(ref)) / np.sqrt(og.p)
+    for M in mats:
+        M.destroy()
+    return num / max(den, 1e-300), OG.gemm_tolerance(npdt, k)
+
+
+def check_complex(grid) -> int:
+    """SURVEY 8(f) N3, complex: El::Gemm<Complex<float|double>> in every orientation (NORMAL / TRANSPOSE / ADJOINT) and SUMMA
+    variant, real and complex alpha / beta, aligned and misaligned operands, beta == 0 over NaN; redistribution, Transpose /
+    Adjoint, Axpy, Scale of complex DistMatrices (bit-exact where only data moves)."""
+    og = _grid_oracle(grid)
+    me = grid.Rank()
+    cnt = 0
+    for npdt in (np.complex64, np.complex128):
+        for oa, ob in itertools.product((0, 1, 2), (0, 1, 2)):
+            for alg in (el.GEMM_SUMMA_C, el.GEMM_DEFAULT) if (oa, ob) not in ((0, 0), (2, 0), (0, 2)) else (
+                    el.GEMM_SUMMA_A, el.GEMM_SUMMA_B, el.GEMM_SUMMA_C, el.GEMM_SUMMA_DOT, el.GEMM_DEFAULT):
+                err, tol = complex_gemm_case(grid, npdt, oa, ob, alg, 70, 50, 90, nb=16)
+                assert err <= tol, f"complex Gemm {npdt.__name__} oa={oa} ob={ob} alg={alg}: {err:.3e} > {tol:.3e}"
+                cnt += 1
+        # real scalars (the no-temporary path), misaligned operands, other distributions through the proxies
+        err, tol = complex_gemm_case(grid, npdt, 2, 0, el.GEMM_SUMMA_C, 61, 47, 83, alpha=0.5, beta=-0.5, aligns=((1, 2), (0, 1), (1, 0)), nb=16)
+        assert err <= tol, ("complex Gemm real scalars", npdt, err, tol)
+        err, tol = complex_gemm_case(grid, npdt, 0, 2, el.GEMM_DEFAULT, 40, 33, 150, alpha=1j, beta=0.0, dists=((el.VC, el.STAR), (el.MR, el.MC), (el.MC, el.MR)), nb=16)
+        assert err <= tol, ("complex Gemm other distributions", npdt, err, tol)
+        cnt += 2
+        # redistribution (bit-exact), Adjoint, Axpy and Scale by a complex scalar
+        G = _complex_matrix(37, 29, 211, npdt)
+        X = el.ComplexDistMatrix(grid, el.MC, el.MR, npdt).Align(1 % og.stride(el.MC), 0).from_global(G)
+        for (U, V) in ((el.MC, el.STAR), (el.STAR, el.VR), (el.MR, el.MC), (el.STAR, el.STAR)):
+            Y = el.ComplexDistMatrix(grid, U, V, npdt)
+            el.Copy(X, Y)
+            spec = OD.Spec(U, V, Y.ColAlign(), Y.RowAlign(), 37, 29)
+            assert np.array_equal(Y.get_local(), OD.local_of(G, spec, og, me)), ("complex Copy", U, V)
+            Y.destroy()
+            cnt += 1
+        Y = el.ComplexDistMatrix(grid, el.MC, el.MR, npdt)
+        el.ZTranspose(X, Y, conjugate=True)
+        spec = OD.Spec(el.MC, el.MR, Y.ColAlign(), Y.RowAlign(), 29, 37)
+        assert np.array_equal(Y.get_local(), OD.local_of(G.conj().T, spec, og, me)), "complex Adjoint"
+        Z = el.ComplexDistMatrix(grid, el.MC, el.MR, npdt).from_global(_complex_matrix(29, 37, 212, npdt))
+        H = _complex_matrix(29, 37, 212, npdt)
+        el.ZAxpy(0.5 - 2j, Y, Z)
+        el.ZScale(-1.5 + 0.25j, Z)
+        want = (-1.5 + 0.25j) * (H.astype(np.complex128) + (0.5 - 2j) * G.conj().T.astype(np.complex128))
+        spec = OD.Spec(el.MC, el.MR, Z.ColAlign(), Z.RowAlign(), 29, 37)
+        got = Z.get_local().astype(np.complex128)
+        eps = 1e-5 if npdt == np.complex64 else 1e-13
+        assert np.abs(got - OD.local_of(want, spec, og, me)).max() <= eps * 20, "complex Axpy / Scale"
+        # beta == 0 must not read C
+        N = el.ComplexDistMatrix(grid, el.MC, el.MR, npdt).from_global(np.full((29, 29), np.nan + 1j * np.nan, dtype=npdt))
+        el.Gemm(0, 2, 1.0, Y, Y, 0.0, N, el.GEMM_SUMMA_C)
+        assert np.isfinite(N.get_local()).all(), "complex Gemm with beta == 0 read C"
+        for M in (X, Y, Z, N):
+            M.destroy()
+        cnt += 3
+    return cnt
+
+
+def check_complex_ref_golden(grid) -> int:
+    """El::Gemm on complex [MC,MR] DistMatrices of THIS grid against the reference's own (grid-independent) outputs:
+    tests/golden/ref_gemm_complex_1x1.npz, 122 runs of the reference's CPU El::Gemm<Complex<float|double>>."""
+    from oracle.make_golden import lcg_complex_matrix
+    og = _grid_oracle(grid)
+    me = grid.Rank()
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_gemm_complex_1x1.npz"))
+    cnt = 0
+    for row in z["meta"]:
+        t, cid, oa, ob, alg, m, n, k, nb = map(int, row[:9])
+        alpha, beta = complex(row[9], row[10]), complex(row[11], row[12])
+        dt = np.complex64 if t == 0 else np.complex128
+        A = lcg_complex_matrix(k if oa else m, m if oa else k, 3 * cid, dt)
+        B = lcg_complex_matrix(n if ob else k, k if ob else n, 3 * cid + 1, dt)
+        C0 = lcg_complex_matrix(m, n, 3 * cid + 2, dt)
+        dA = el.ComplexDistMatrix(grid, el.MC, el.MR, dt).from_global(A)
+        dB = el.ComplexDistMatrix(grid, el.MC, el.MR, dt).from_global(B)
+        dC = el.ComplexDistMatrix(grid, el.MC, el.MR, dt).from_global(C0)
+        el.PushBlocksizeStack(nb)
+        try:
+            el.Gemm(oa, ob, alpha, dA, dB, beta, dC, alg)
+        finally:
+            el.PopBlocksizeStack()
+        ref = z[f"{'c32' if t == 0 else 'c64'}_{cid}_C"]
+        spec = OD.Spec(el.MC, el.MR, dC.ColAlign(), dC.RowAlign(), m, n)
+        num = float(np.linalg.norm(dC.get_local().astype(np.complex128) - OD.local_of(ref, spec, og, me)))
+        den = float(np.linalg.norm(ref)) / np.sqrt(og.p)
+        assert num / max(den, 1e-300) <= OG.gemm_tolerance(dt, k), ("complex Gemm vs the reference's output", row)
+        for M in (dA, dB, dC):
+            M.destroy()
+        cnt += 1
+    return cnt
+
+
 def run_all(grid, heavy=False) -> dict:
     out = {}
     out["redist_f64"] = check_redistributions(grid, torch.float64)
@@ -906,6 +1031,8 @@ def run_all(grid, heavy=False) -> dict:
     check_contractions(grid, torch.float32)
     out["collectives"] = check_collectives(grid, torch.float64) + check_collectives(grid, torch.float32)
     out["half"] = check_half(grid)
+    out["complex"] = check_complex(grid)
+    out["complex_ref_golden"] = check_complex_ref_golden(grid)
     out["gemm_f64"] = check_gemm_variants(grid, torch.float64)
     out["gemm_f32"] = check_gemm_variants(grid, torch.float32)
     check_gemm_proxies(grid, torch.float64)

@@ -1,7 +1,7 @@
 """torchrun worker: the distributed parity cases on an r x c grid, one process per GPU (NCCL).
 
   python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
-      --master-port P tests/dist_worker.py [--height r] [--heavy]
+      --master-port P tests/dist_worker.py [--height r] [--heavy] [--level3] [--only check_complex,...]
 """
 import argparse
 import os
@@ -20,6 +20,7 @@ def main() -> int:
     ap.add_argument("--height", type=int, default=0)
     ap.add_argument("--heavy", action="store_true")
     ap.add_argument("--level3", action="store_true", help="run dist_cases.run_level3 instead of run_all")
+    ap.add_argument("--only", default="", help="comma-separated dist_cases functions taking (grid) to run instead of run_all")
     args = ap.parse_args()
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
@@ -29,7 +30,10 @@ def main() -> int:
     ok = 1
     try:
         grid = el.Grid(height=args.height or None, device=local)
-        out = dc.run_level3(grid) if args.level3 else dc.run_all(grid, heavy=args.heavy)
+        if args.only:
+            out = {name: getattr(dc, name)(grid) for name in args.only.split(",")}
+        else:
+            out = dc.run_level3(grid) if args.level3 else dc.run_all(grid, heavy=args.heavy)
         grid.sync()
         if grid.Rank() == 0:
             print(f"grid {grid.Height()}x{grid.Width()}: {out}", flush=True)

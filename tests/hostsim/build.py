@@ -15,7 +15,7 @@ CSRC = os.path.join(ROOT, "elemental_b200", "csrc")
 SAN = os.environ.get("HOSTSIM_SANITIZE", "")
 OUT = os.path.join(HERE, "_build" + ("_" + SAN if SAN else ""))
 LIB = os.path.join(OUT, "libelb200_hostsim.so")
-ENGINE = ["engine_core.cpp", "engine_gemm.cpp", "engine_redist.cpp", "engine_level3.cpp", "peer.cpp", "plan.cpp", "capi_engine.cpp", "comm.cpp"]
+ENGINE = ["engine_core.cpp", "engine_gemm.cpp", "engine_redist.cpp", "engine_level3.cpp", "peer.cpp", "plan.cpp", "capi_engine.cpp", "capi_complex.cpp", "comm.cpp"]
 DOUBLES = ["sim_cuda.cpp", "sim_nccl.cpp", "sim_ops.cpp"]
 CUDA_INC = os.environ.get("CUDA_HOME", "/usr/local/cuda") + "/include"
 FLAGS = ["-std=c++17", "-O2", "-g", "-fPIC", "-pthread", "-Wall", "-Wno-unused-function", "-DELB200_HOSTSIM",

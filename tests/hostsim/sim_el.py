@@ -188,7 +188,10 @@ class DistMatrix:
             pass
 
 
-def Copy(A, B): check(lib.elb200_dm_copy(A._h, B._h), "Copy")
+def Copy(A, B):
+    if isinstance(A, ComplexDistMatrix):
+        return ZCopy(A, B)
+    check(lib.elb200_dm_copy(A._h, B._h), "Copy")
 def Transpose(A, B): check(lib.elb200_dm_transpose(A._h, B._h), "Transpose")
 def Axpy(alpha, X, Y): check(lib.elb200_dm_axpy(alpha, X._h, Y._h), "Axpy")
 def Scale(alpha, A): check(lib.elb200_dm_scale(alpha, A._h), "Scale")
@@ -203,6 +206,8 @@ def LocalGemm(orientA, orientB, alpha, A, B, beta, C_):
 
 
 def Gemm(orientA, orientB, alpha, A, B, beta, C_, alg: int = GEMM_DEFAULT):
+    if isinstance(A, ComplexDistMatrix):
+        return ZGemm(orientA, orientB, alpha, A, B, beta, C_, alg)
     check(lib.elb200_dist_gemm(orientA, orientB, alpha, A._h, B._h, beta, C_._h, alg), "Gemm")
 
 
@@ -285,6 +290,14 @@ def Trsm(side: int, uplo: int, orientation: int, diag: int, alpha, A, B, checkIf
 def GemmHost(grid, orientA, orientB, m, n, k, alpha, A: torch.Tensor, lda, B: torch.Tensor, ldb, beta, C_: torch.Tensor, ldc):
     fn = lib.elb200_dist_gemm_host_f32 if C_.dtype == torch.float32 else lib.elb200_dist_gemm_host_f64
     check(fn(grid._h, orientA, orientB, m, n, k, alpha, A.data_ptr(), lda, B.data_ptr(), ldb, beta, C_.data_ptr(), ldc), "GemmHost")
+
+
+# complex instantiations: the same mirror file as the product binding, bound to the hostsim library
+from elemental_b200 import _zdm as _zdm_mod  # noqa: E402
+
+_z = _zdm_mod.bind(lib, check, L.DmInfo)
+ComplexDistMatrix, ZCopy, ZTranspose, ZZero, ZScale, ZAxpy, ZAxpyContract, ZGemm = (
+    _z.ComplexDistMatrix, _z.ZCopy, _z.ZTranspose, _z.ZZero, _z.ZScale, _z.ZAxpy, _z.ZAxpyContract, _z.ZGemm)
 
 
 def run_grid(r: int, c: int, fn: Callable[["Grid"], object], timeout: Optional[float] = None) -> list:

@@ -100,6 +100,18 @@ def test_ragged_operands_at_the_slot_boundary_take_one_branch(simlib):
         _run("2x2,2x3", "--only", "check_gemm_ragged_slot_boundary,check_gemm_ragged_slot_boundary_f32", env={"ELB200_ARENA_KB": kb, "HOSTSIM_TIMEOUT": "60"})
 
 
+def test_complex_instantiations_on_hostsim(simlib):
+    """SURVEY 8(f) N3, complex (csrc/capi_complex.cpp: planar storage, 4M on the real paths): the parity cases and the
+    reference's own complex El::Gemm outputs on the grid shapes run_all does not visit here, the copy-engine forms under
+    them, and the local interleaved elb200_gemm_c32 / _c64 (the CPU twin of tests/test_gpu_complex.py)."""
+    out = _run("1x2,2x1,2x3", "--only", "check_complex,check_complex_ref_golden")
+    assert out.count("'check_complex': 72") == 3 and out.count("'check_complex_ref_golden': 122") == 3
+    _run("2x4", "--only", "check_complex", env={"ELB200_FUSED_BYTES": "0", "ELB200_AG_SPLIT_BYTES": "1"})
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "hostsim", "complex_local_check.py")], capture_output=True, text=True,
+                       timeout=600, cwd=ROOT, env=dict(os.environ, HOSTSIM_TIMEOUT="60"))
+    assert r.returncode == 0 and "COMPLEX_LOCAL_PASS 216" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
 @pytest.mark.parametrize("grid,hwq", [("2x4", "1")])
 def test_engine_survives_shared_hardware_queues(simlib, grid, hwq):
     """HOSTSIM_HWQ=N spreads a rank's streams over N work queues executed in ISSUE order (the false dependencies

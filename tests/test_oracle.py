@@ -362,3 +362,30 @@ def test_level3_restatement_equals_global_definition():
                         -0.5, C, nb=8)
                 ref = O3.trrk_global(uplo, oa, ob, 0.5, A, B, -0.5, C0, np.float64)
                 assert OG.frobenius_rel_err(C.to_global(), ref) < 1e-14, (g.r, g.c, uplo, oa, ob)
+
+
+def test_complex_gemm_oracle_reproduces_reference_outputs():
+    """SURVEY 8(f) N3, complex: the reference's own El::Gemm<Complex<float|double>> outputs (122 runs: NORMAL / TRANSPOSE /
+    ADJOINT x five GemmAlgorithm values, complex alpha and beta; tests/golden/ref_gemm_complex_1x1.npz) are reproduced
+    (a) by the global definition with conjugation and (b) by the 4M composition over the pinned real restatement
+    (oracle.gemm.dist_gemm_complex) on 1 x 1, 2 x 2 and 2 x 3 virtual grids — the arithmetic the product path runs."""
+    from oracle.make_golden import lcg_complex_matrix
+    z = np.load(os.path.join(GOLD, "ref_gemm_complex_1x1.npz"))
+    meta = z["meta"]
+    assert len(meta) == 122
+    for row in meta:
+        t, cid, oa, ob, alg, m, n, k, nb = map(int, row[:9])
+        alpha, beta = complex(row[9], row[10]), complex(row[11], row[12])
+        dt = np.complex64 if t == 0 else np.complex128
+        A = lcg_complex_matrix(k if oa else m, m if oa else k, 3 * cid, dt)
+        B = lcg_complex_matrix(n if ob else k, k if ob else n, 3 * cid + 1, dt)
+        C0 = lcg_complex_matrix(m, n, 3 * cid + 2, dt)
+        ref = z[f"{'c32' if t == 0 else 'c64'}_{cid}_C"]
+        tol = OG.gemm_tolerance(dt, k)
+        assert OG.frobenius_rel_err(OG.gemm_global(oa, ob, alpha, A, B, beta, C0), ref) <= tol, row
+        for shape in ((1, 1), (2, 2), (2, 3)):
+            if shape != (1, 1) and cid % 3:
+                continue  # every third case on the larger virtual grids keeps the CPU suite short
+            got = OG.dist_gemm_complex(OD.Grid(*shape), oa, ob, alpha, A, B, beta, C0, alg, nb)
+            assert got.dtype == dt
+            assert OG.frobenius_rel_err(got, ref) <= tol, (row, shape)

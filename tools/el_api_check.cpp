@@ -127,10 +127,81 @@ static int exercise_half(const Grid& g) {
     return bad;
 }
 
+// Complex<float> / Complex<double>: DistMatrix<Complex<R>>, El::Gemm with ADJOINT and complex scalars, Adjoint,
+// redistribution, Axpy / Scale, and Gemm(Matrix<Complex<R>>), checked against a host evaluation of the definition.
+template <typename R>
+static int exercise_complex(const Grid& g) {
+    typedef Complex<R> Cx;
+    int bad = 0;
+    const Int m = 45, n = 38, k = 52;
+    auto fill = [](std::vector<Cx>& v, unsigned seed) {
+        unsigned long long s = 0x9E3779B97F4A7C15ull * (seed + 1);
+        for (Cx& z : v) {
+            s = s * 6364136223846793005ull + 1442695040888963407ull; const R re = R(double((s >> 11) & ((1ull << 53) - 1)) / double(1ull << 53) - 0.5);
+            s = s * 6364136223846793005ull + 1442695040888963407ull; const R im = R(double((s >> 11) & ((1ull << 53) - 1)) / double(1ull << 53) - 0.5);
+            z = Cx(re, im);
+        }
+    };
+    // 1 x 1 grid: the local matrix is the global one, column-major with ld = height
+    std::vector<Cx> hA(size_t(k) * m), hB(size_t(k) * n), hC(size_t(m) * n), out(size_t(m) * n);
+    fill(hA, 1); fill(hB, 2); fill(hC, 3);
+    DistMatrix<Cx, MC, MR, ELEMENT, Device::GPU> A(k, m, g), B(k, n, g), C(m, n, g);   // A is k x m: used as A^H
+    A.SetLocalFromHost(hA.data()); B.SetLocalFromHost(hB.data()); C.SetLocalFromHost(hC.data());
+    const Cx alpha(R(2), R(-0.5)), beta(R(0.25), R(3));
+    Gemm(ADJOINT, NORMAL, alpha, A, B, beta, C, GEMM_SUMMA_C);
+    C.GetLocalToHost(out.data());
+    double num = 0, den = 0;
+    for (Int j = 0; j < n; ++j)
+        for (Int i = 0; i < m; ++i) {
+            std::complex<double> acc(0, 0);
+            for (Int l = 0; l < k; ++l) acc += std::conj(std::complex<double>(hA[size_t(l) + size_t(i) * k])) * std::complex<double>(hB[size_t(l) + size_t(j) * k]);
+            const std::complex<double> want = std::complex<double>(alpha) * acc + std::complex<double>(beta) * std::complex<double>(hC[size_t(i) + size_t(j) * m]);
+            num += std::norm(std::complex<double>(out[size_t(i) + size_t(j) * m]) - want); den += std::norm(want);
+        }
+    const double tol = (sizeof(R) == 4 ? 1e-5 : 1e-13) * std::sqrt(2.0 * k);
+    if (!(num <= tol * tol * den)) ++bad;
+    // Adjoint into another distribution and back; Axpy / Scale with complex scalars
+    DistMatrix<Cx, STAR, VR> Ah(g);
+    DistMatrix<Cx> At(g), A2(g);
+    Adjoint(A, At);                       // m x k
+    Ah = At;                              // redistribution
+    A2 = Ah;
+    std::vector<Cx> back(size_t(m) * k);
+    A2.GetLocalToHost(back.data());
+    for (Int j = 0; j < k; ++j)
+        for (Int i = 0; i < m; ++i)
+            if (back[size_t(i) + size_t(j) * m] != std::conj(hA[size_t(j) + size_t(i) * k])) { ++bad; i = m; j = k; }
+    Axpy(Cx(R(0), R(1)), At, A2);         // A2 = (1 + i) A^H
+    Scale(Cx(R(0.5), R(-0.5)), A2);       // (0.5 - 0.5 i)(1 + i) = 1  ->  A2 = A^H again (up to rounding)
+    A2.GetLocalToHost(back.data());
+    for (Int j = 0; j < k && !bad; ++j)
+        for (Int i = 0; i < m; ++i)
+            if (std::abs(std::complex<double>(back[size_t(i) + size_t(j) * m]) - std::conj(std::complex<double>(hA[size_t(j) + size_t(i) * k]))) > (sizeof(R) == 4 ? 1e-6 : 1e-14)) { ++bad; break; }
+    Zero(A2);
+    // local interleaved matrices
+    Matrix<Cx> La(k, m), Lb(k, n), Lc(m, n);   // LDim() may exceed the height (16-byte pitch)
+    auto up = [&](Matrix<Cx>& M, const std::vector<Cx>& h) {
+        cudaStream_t st = M.GetSyncInfo().Stream();
+        return cudaMemcpy2DAsync(M.Buffer(), size_t(M.LDim()) * sizeof(Cx), h.data(), size_t(M.Height()) * sizeof(Cx), size_t(M.Height()) * sizeof(Cx),
+                                 size_t(M.Width()), cudaMemcpyHostToDevice, st) == cudaSuccess && cudaStreamSynchronize(st) == cudaSuccess;
+    };
+    if (!up(La, hA) || !up(Lb, hB) || !up(Lc, hC)) ++bad;
+    Gemm(ADJOINT, NORMAL, alpha, La, Lb, beta, Lc);
+    Synchronize(SyncInfoFromMatrix(Lc));
+    std::vector<Cx> out2(out.size());
+    if (cudaMemcpy2DAsync(out2.data(), size_t(m) * sizeof(Cx), Lc.LockedBuffer(), size_t(Lc.LDim()) * sizeof(Cx), size_t(m) * sizeof(Cx), size_t(n),
+                          cudaMemcpyDeviceToHost, Lc.GetSyncInfo().Stream()) != cudaSuccess || cudaStreamSynchronize(Lc.GetSyncInfo().Stream()) != cudaSuccess) ++bad;
+    double d2 = 0;
+    for (size_t i = 0; i < out.size(); ++i) d2 += std::norm(std::complex<double>(out2[i]) - std::complex<double>(out[i]));
+    if (!(d2 <= 4 * tol * tol * den)) ++bad;
+    g.Synchronize();
+    return bad;
+}
+
 int main(int argc, char** argv) {
     Environment env(argc, argv);
     Grid g;  // 1 x 1 on the current device
-    int bad = exercise<float>(g) + exercise<double>(g) + exercise_half(g);
+    int bad = exercise<float>(g) + exercise<double>(g) + exercise_half(g) + exercise_complex<float>(g) + exercise_complex<double>(g);
     if (Blocksize() != 128 || Grid::DefaultHeight(8) != 2) ++bad;
     std::printf(bad ? "EL_API_CHECK_FAIL %d\n" : "EL_API_CHECK_PASS\n", bad);
     return bad ? 1 : 0;

@@ -192,6 +192,11 @@ benchN)
 skew)
   log "=== bench.py N=$N (kernel time per rank)"; timeout 300 $TR bench.py --gpus $N --steps 10 --warmup 3 --no-sub --no-parity --no-cpu --no-e2e > $OUT/bench_${N}gpu.json 2> $OUT/bench_${N}gpu.err; log "exit $?"
   ;;
+zfinal)
+  # complex instantiations on a B200: the facade check (no torch), then the GPU test file
+  log "=== el_api_check"; timeout 60 tools/el_api_check > $OUT/el_api_check.log 2>&1; log "exit $?"; tail -1 $OUT/el_api_check.log | tee -a $OUT/session.log
+  log "=== pytest test_gpu_complex"; timeout 170 python -m pytest tests/test_gpu_complex.py -m gpu -x -q > $OUT/pytest_complex.log 2>&1; log "exit $?"; tail -3 $OUT/pytest_complex.log | tee -a $OUT/session.log
+  ;;
 par4)
   run timeout 300 $TR tests/dist_worker.py
   ;;
