@@ -197,6 +197,9 @@ zfinal)
   log "=== el_api_check"; timeout 60 tools/el_api_check > $OUT/el_api_check.log 2>&1; log "exit $?"; tail -1 $OUT/el_api_check.log | tee -a $OUT/session.log
   log "=== pytest test_gpu_complex"; timeout 170 python -m pytest tests/test_gpu_complex.py -m gpu -x -q > $OUT/pytest_complex.log 2>&1; log "exit $?"; tail -3 $OUT/pytest_complex.log | tee -a $OUT/session.log
   ;;
+zpar)
+  run timeout 150 $TR tests/dist_worker.py --only check_complex,check_complex_ref_golden
+  ;;
 par4)
   run timeout 300 $TR tests/dist_worker.py
   ;;
