@@ -223,11 +223,13 @@ def test_race_detector_selftest(tsanlib):
 
 @pytest.mark.parametrize("grid,only,panel_k", [("2x2", "check_gemm_pipeline,check_contractions,check_gemm_dot_pipeline,check_gemm_variants_f64", "512"),
                                                 ("2x4", "check_gemm_pipeline,check_gemm_dot_pipeline", "512"),
-                                                ("2x2", "check_level3,check_trsm", "16")])
+                                                ("2x2", "check_level3,check_trsm", "16"),
+                                                ("2x2", "check_complex,check_collectives,check_redistributions", "512")])
 def test_engine_is_race_free_under_tsan(tsanlib, grid, only, panel_k):
     """The multi-panel SUMMA-C pipeline (zero-copy direct panels, slot hand-back), the k-range pipeline of SUMMA-Dot
     (exchange on the comm stream under the GEMM), the panel pipeline of Trrk / Syrk, the Trsm block loop, the peer-arena reductions and
-    exchanges and the level-3 family under ThreadSanitizer: no report.  (The remaining cases — run_all, run_level3,
+    exchanges, the level-3 family, the fused one-kernel collectives and the complex path (planes on one stream, temporaries)
+    under ThreadSanitizer: no report.  (The remaining cases — run_all, run_level3,
     the four-stream host-operand Gemm — were run the same way by hand and are clean too; they are left out of the
     default suite for time.)"""
     _, rt = tsanlib
