@@ -982,6 +982,11 @@ def check_complex(grid) -> int:
         for M in (X, Y, Z, N):
             M.destroy()
         cnt += 3
+        # degenerate shapes: k == 0 is C = beta C, an empty C is a no-op, 1 x 1 x 1
+        for (m, n, k) in ((5, 4, 0), (0, 4, 3), (5, 0, 3), (1, 1, 1)):
+            err, tol = complex_gemm_case(grid, npdt, 0, 0, el.GEMM_DEFAULT, m, n, k, alpha=2.0 - 1.0j, beta=0.5 + 0.5j)
+            assert err <= max(tol, 1e-6), ("complex Gemm degenerate shape", npdt, m, n, k, err)
+            cnt += 1
     return cnt
 
 

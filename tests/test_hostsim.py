@@ -105,7 +105,7 @@ def test_complex_instantiations_on_hostsim(simlib):
     reference's own complex El::Gemm outputs on the grid shapes run_all does not visit here, the copy-engine forms under
     them, and the local interleaved elb200_gemm_c32 / _c64 (the CPU twin of tests/test_gpu_complex.py)."""
     out = _run("1x2,2x1,2x3", "--only", "check_complex,check_complex_ref_golden")
-    assert out.count("'check_complex': 72") == 3 and out.count("'check_complex_ref_golden': 122") == 3
+    assert out.count("'check_complex': 80") == 3 and out.count("'check_complex_ref_golden': 122") == 3
     _run("2x4", "--only", "check_complex", env={"ELB200_FUSED_BYTES": "0", "ELB200_AG_SPLIT_BYTES": "1"})
     r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "hostsim", "complex_local_check.py")], capture_output=True, text=True,
                        timeout=600, cwd=ROOT, env=dict(os.environ, HOSTSIM_TIMEOUT="60"))
